@@ -1,0 +1,195 @@
+/* pcp.h — C-ABI of libpcp_b200.so: the B200 (sm_100a) implementation of the PointNet point-cloud
+ * hot path of MAPieschl/PointCloudProcessing.
+ *
+ * The reference has NO FFI / plugin / op-registration layer (it is 100 % Python on TensorFlow,
+ * SURVEY.md §0.1, §8b): the boundary this library sits behind is the Keras Model/Layer contract
+ * of point_cloud_analysis/pointnet/PointNet.py and the PointCloudSet preprocessing contract of
+ * point_cloud_analysis/pointcloud/PointCloudSet.py.  Each entry point below cites the reference
+ * symbol (file:line under /root/reference/point_cloud_analysis/) whose arithmetic it replaces.
+ * The Python mirror of that contract (pointcloudprocessing_b200/pointnet, /pointcloud) binds these
+ * symbols with ctypes (pointcloudprocessing_b200/_ffi.py); INTEGRATION.md shows the stub a
+ * reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 (PCP_OK) or a negative pcp_status; pcp_last_error() gives the
+ *     thread-local message; no C++ exception crosses the boundary;
+ *   - plain pointers and sizes only.  Pointers named d_* are DEVICE pointers (e.g.
+ *     torch.Tensor.data_ptr()), h_* are HOST pointers; the caller owns every tensor buffer;
+ *   - launches are asynchronous on the cudaStream_t passed as `stream` (void*, 0 = default stream);
+ *     the *_host entry points copy H2D/D2H themselves and synchronise before returning;
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *     PCP_ERR_CUDA.
+ */
+#ifndef PCP_H_
+#define PCP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum pcp_status {
+    PCP_OK = 0,
+    PCP_ERR_INVALID = -1,      /* bad argument */
+    PCP_ERR_CUDA = -2,         /* CUDA runtime error (message in pcp_last_error) */
+    PCP_ERR_NOMEM = -3,
+    PCP_ERR_NOTFOUND = -4,     /* unknown tensor name */
+    PCP_ERR_UNSUPPORTED = -5,  /* shape outside what the kernels cover */
+    PCP_ERR_STATE = -6         /* call order (e.g. forward before prepare) */
+} pcp_status;
+
+typedef void *pcp_stream;      /* cudaStream_t */
+
+const char *pcp_last_error(void);
+int pcp_version(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+uint64_t pcp_launch_count(void);
+int pcp_device_info(int *sm_count, int *cc_major, int *cc_minor, size_t *total_mem);
+
+/* ---- memory / stream plumbing (for callers without torch) ---- */
+int pcp_malloc(void **d_ptr, size_t bytes);
+int pcp_free(void *d_ptr);
+int pcp_malloc_host(void **h_ptr, size_t bytes);          /* pinned */
+int pcp_free_host(void *h_ptr);
+int pcp_memcpy_h2d(void *d_dst, const void *h_src, size_t bytes, pcp_stream stream);
+int pcp_memcpy_d2h(void *h_dst, const void *d_src, size_t bytes, pcp_stream stream);
+int pcp_memset(void *d_ptr, int value, size_t bytes, pcp_stream stream);
+int pcp_stream_sync(pcp_stream stream);
+
+/* ---- preprocessing ---- */
+
+/* PointCloudNormalization.call (pointnet/PointNet.py:691-706): per cloud centroid, centre,
+ * max distance, scale = max(maxdist, 1e-7), divide.  x,y: (b, n, 3) f32 contiguous.
+ * d_centroid (b*3) and d_scale (b) may be NULL.  One HBM read + one write (24 B/point). */
+int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale,
+                      pcp_stream stream);
+
+/* PointCloudSet._parse_function jitter (pointcloud/PointCloudSet.py:335-337):
+ * y = x + noise * stdev_axis.  d_noise != NULL: explicit noise tensor (parity tests).
+ * d_noise == NULL: noise = Philox4x32-10 + Box-Muller, one Philox block per point, counter =
+ * global point index + offset (shard-invariant).  npoints = b*n. */
+int pcp_jitter_f32(const float *d_x, int64_t npoints, const float h_stdev[3], uint64_t seed, uint64_t offset,
+                   const float *d_noise, float *d_y, pcp_stream stream);
+/* the N(0,1) tensor pcp_jitter_f32 uses when d_noise == NULL: (npoints, 3) f32 */
+int pcp_philox_normal_f32(int64_t npoints, uint64_t seed, uint64_t offset, float *d_noise, pcp_stream stream);
+
+/* Rotation augmentation (not in the reference; DCM convention utils/mat_ops.py:6-39):
+ * y = x . R^T per cloud, d_R (b, 3, 3). */
+int pcp_rotate_f32(const float *d_x, int b, int64_t n, const float *d_R, float *d_y, pcp_stream stream);
+
+/* PointCloudSet._adjust_to_input_width (pointcloud/PointCloudSet.py:443-470) on the device:
+ * cloud c has h_n_in[c] valid points at d_x + c*n_in_stride*3; output is exactly n_out points:
+ * the first n_out (truncate, :455-456) or all points followed by duplicates of
+ * x[floor(U(0,N))] (:459-467) drawn from Philox(seed, cloud, slot).  Labels (int32, may be NULL)
+ * are gathered with the same indices.  d_n_in: device int32[b]. */
+int pcp_resize_to_width_f32(const float *d_x, const int32_t *d_labels, int b, int64_t n_in_stride,
+                            const int32_t *d_n_in, int64_t n_out, uint64_t seed, float *d_y,
+                            int32_t *d_labels_out, pcp_stream stream);
+
+/* ---- sampling (north_star operators; no reference implementation, contract = oracle/sampling.py) ---- */
+
+/* Farthest-point sampling: x (b, n, 3) -> idx (b, s) int32; first index = start; fp32
+ * ((dx*dx + dy*dy) + dz*dz) without FMA, lowest index wins ties. */
+int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, pcp_stream stream);
+/* out[c, j, :] = x[c, idx[c, j], :] ; labels likewise when non-NULL */
+int pcp_gather_points_f32(const float *d_x, const int32_t *d_labels, int b, int64_t n, const int32_t *d_idx, int s,
+                          float *d_out, int32_t *d_labels_out, pcp_stream stream);
+
+/* Voxel-grid downsample: key = floor((p - origin)/voxel) per axis; per-voxel centroid (double
+ * accumulate) and count, voxels ordered lexicographically by (kx,ky,kz).  h_origin == NULL ->
+ * per-cloud minimum corner.  Outputs are padded to n rows per cloud; d_nvox (b) int32 gives the
+ * number of valid rows.  Workspace from pcp_voxel_workspace_bytes. */
+int pcp_voxel_workspace_bytes(int b, int64_t n, size_t *bytes);
+int pcp_voxel_f32(const float *d_x, int b, int64_t n, const float *h_origin, float voxel, float *d_out_xyz,
+                  int32_t *d_out_count, int32_t *d_nvox, void *d_workspace, size_t workspace_bytes,
+                  pcp_stream stream);
+
+/* ---- model: PointNet (pointnet/PointNet.py:84-292) ---- */
+
+typedef struct pcp_model pcp_model;
+
+#define PCP_PRECISION_FP32 0   /* CUDA-core fp32 FMA path: the 1e-3 contract */
+#define PCP_PRECISION_BF16 1   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate in TMEM: the 2e-2 contract */
+
+#define PCP_HEAD_CLS 1u        /* classification_output */
+#define PCP_HEAD_SEG 2u        /* segmentation_output   */
+
+typedef struct pcp_model_desc {
+    int32_t num_classes;               /* classification_output_width, PointNet.py:86 */
+    int32_t num_parts;                 /* segmentation_output_width,   PointNet.py:87 */
+    int32_t vanilla;                   /* PointNet.py:91 */
+    int32_t regularize_input_transform;    /* PointNet.py:92 */
+    int32_t regularize_feature_transform;  /* PointNet.py:93 */
+    float dropout_rate;                /* PointNet.py:88 */
+    int32_t precision;                 /* PCP_PRECISION_* */
+} pcp_model_desc;
+
+int pcp_model_create(const pcp_model_desc *desc, pcp_model **out);
+int pcp_model_destroy(pcp_model *m);
+
+/* tensor table: names follow the reference's layer names ("<layer>/kernel", "<layer>/bias",
+ * "<layer>/bn/gamma|beta|moving_mean|moving_variance", "input_transform/w", ...). */
+int pcp_model_num_tensors(const pcp_model *m);
+int pcp_model_tensor_info(const pcp_model *m, int index, char *name_buf, size_t name_buf_len, size_t *count,
+                          int *trainable_group);
+int pcp_model_set_tensor(pcp_model *m, const char *name, const float *h_data, size_t count);
+int pcp_model_get_tensor(pcp_model *m, const char *name, float *h_data, size_t count);
+
+/* Fold inference BN (y = x*s + t), build device weight images (fp32 and packed bf16 UMMA tiles).
+ * Must be called after set_tensor and before forward; training steps re-run it lazily. */
+int pcp_model_prepare(pcp_model *m);
+/* (re)allocate the activation workspace for up to b clouds of n points (outside the hot path). */
+int pcp_model_reserve(pcp_model *m, int b, int64_t n);
+
+/* PointNet.call(pc, training=False) (PointNet.py:197-292).  d_x (b,n,3) f32.  Outputs (each may
+ * be NULL): d_cls (b,C) probabilities, d_seg (b,n,P) probabilities, d_R (b,3,3), and the
+ * pre-softmax logits.  heads: PCP_HEAD_* mask of the heads to evaluate (the reference always
+ * evaluates both). */
+int pcp_model_forward(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
+                      float *d_R, float *d_cls_logits, float *d_seg_logits, pcp_stream stream);
+/* same, HOST buffers: H2D of x, forward, D2H of the requested outputs, stream sync. */
+int pcp_model_predict_host(pcp_model *m, const float *h_x, int b, int64_t n, uint32_t heads, float *h_cls,
+                           float *h_seg, float *h_R, pcp_stream stream);
+/* intermediate pooled features of the last forward: which = 0 input T-Net, 1 feature T-Net,
+ * 2 global features; (b,1024) f32 copied to the host (tests). */
+int pcp_model_get_pooled(pcp_model *m, int which, int b, float *h_out);
+
+/* ---- training (pointnet_train.py:310-351) ---- */
+#define PCP_GROUP_SHARED 0
+#define PCP_GROUP_INPUT_TRANSFORM 1
+#define PCP_GROUP_CLS_HEAD 2
+#define PCP_GROUP_SEG_HEAD 3
+/* PointNet.freeze_* / thaw_* (PointNet.py:294-342): frozen => no gradient and BN in inference mode */
+int pcp_model_set_trainable(pcp_model *m, int group, int flag);
+
+typedef struct pcp_train_config {
+    float w_cls, w_seg, w_rot;     /* loss_weights, pointnet_train.py:340-344 */
+    float lr0, decay_rate;         /* ExponentialDecay, pointnet_train.py:310-315 */
+    int32_t decay_steps;
+    float beta1, beta2, eps;       /* keras Adam defaults 0.9 / 0.999 / 1e-7 */
+    uint64_t dropout_seed;
+    int32_t use_dropout_masks;     /* 1: d_mask1/d_mask2 given explicitly (parity tests) */
+} pcp_train_config;
+
+/* One training step on the local shard: forward (training BN on thawed layers, dropout),
+ * losses (SCCE on probabilities clip 1e-7, MSE on R), backward into the flat gradient buffer.
+ * h_metrics (8 floats): loss, cls_loss, seg_loss, se3_loss, cls_acc, seg_acc, se3_rmse, reg_loss.
+ * global_batch: the loss mean divides by this (data parallel: sum over ranks == global mean). */
+int pcp_model_loss_backward(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *d_y_cls,
+                            const int32_t *d_y_seg, const float *d_y_se3, const pcp_train_config *cfg,
+                            int global_batch, const float *d_mask1, const float *d_mask2, float *h_metrics,
+                            pcp_stream stream);
+/* flat fp32 gradient buffer (device) for the NCCL all-reduce done by the host side */
+int pcp_model_grad_buffer(pcp_model *m, float **d_grads, size_t *count);
+/* fused Adam + ExponentialDecay over the flat buffer; step is 0-based (lr uses step, bias
+ * correction uses step+1), frozen tensors are skipped. */
+int pcp_model_adam_step(pcp_model *m, const pcp_train_config *cfg, int64_t step, pcp_stream stream);
+/* copy one gradient tensor to the host (tests) */
+int pcp_model_get_grad(pcp_model *m, const char *name, float *h_data, size_t count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCP_H_ */

@@ -1,0 +1,405 @@
+// elementwise.cu — per-cloud normalisation, jitter, rotation, resize-to-width, gather.
+// HBM-bound streaming kernels: 24 B/point algorithmic traffic (12 read + 12 written).
+//   pcp_normalize_f32      <- PointCloudNormalization.call   (pointnet/PointNet.py:691-706)
+//   pcp_jitter_f32         <- PointCloudSet._parse_function  (pointcloud/PointCloudSet.py:335-337)
+//   pcp_resize_to_width_f32<- _adjust_to_input_width         (pointcloud/PointCloudSet.py:443-470)
+//   pcp_rotate_f32         <- new (DCM convention utils/mat_ops.py:6-39)
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace pcp {
+
+constexpr int kNormThreads = 512;
+
+// One thread-block CLUSTER per cloud.  Each CTA stages its slice of the cloud in shared memory
+// with 128-bit loads (the only HBM read), the cluster reduces centroid (double) and max distance
+// through distributed shared memory, and each CTA writes its slice back normalised.
+__global__ void __launch_bounds__(kNormThreads)
+normalize_cluster_kernel(const float *__restrict__ x, int64_t n, float *__restrict__ y,
+                         float *__restrict__ centroid_out, float *__restrict__ scale_out, int cs, int64_t ppc)
+{
+    extern __shared__ float4 smem4[];
+    float *sm = reinterpret_cast<float *>(smem4);
+    __shared__ double red_d[kNormThreads / 32][3];
+    __shared__ double part_sum[3];
+    __shared__ float red_f[kNormThreads / 32];
+    __shared__ float part_max;
+
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank();
+    const int64_t cloud = blockIdx.x / cs;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    const int64_t p0 = min(n, (int64_t)rank * ppc), p1 = min(n, p0 + ppc);
+    const int64_t np = p1 - p0, nf = np * 3;
+    const float *src = x + (cloud * n + p0) * 3;
+    float *dst = y + (cloud * n + p0) * 3;
+    // element i of the slice lives at sm[off + i] so that 16-byte global and shared addresses line up
+    const int off = (int)((reinterpret_cast<uintptr_t>(src) & 15u) >> 2);
+    const bool dst_same = ((reinterpret_cast<uintptr_t>(dst) & 15u) >> 2) == (unsigned)off;
+
+    const int64_t nvec = (off + nf + 3) >> 2;
+    for (int64_t v = tid; v < nvec; v += kNormThreads) {
+        const int64_t base = 4 * v - off;
+        if (base >= 0 && base + 3 < nf) {
+            const float4 q = __ldg(reinterpret_cast<const float4 *>(src + base));
+            smem4[v] = q;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (base + j >= 0 && base + j < nf) sm[4 * v + j] = __ldg(src + base + j);
+        }
+    }
+    __syncthreads();
+
+    // ---- centroid: double accumulation => correctly rounded mean (oracle/pointnet_numpy.py:normalize) ----
+    double sx = 0, sy = 0, sz = 0;
+    for (int64_t i = tid; i < np; i += kNormThreads) {
+        sx += (double)sm[off + 3 * i];
+        sy += (double)sm[off + 3 * i + 1];
+        sz += (double)sm[off + 3 * i + 2];
+    }
+    sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
+    if (lane == 0) { red_d[warp][0] = sx; red_d[warp][1] = sy; red_d[warp][2] = sz; }
+    __syncthreads();
+    if (tid < 3) {
+        double s = 0;
+        for (int w = 0; w < kNormThreads / 32; ++w) s += red_d[w][tid];
+        part_sum[tid] = s;
+    }
+    cluster.sync();
+    double tot[3] = {0, 0, 0};
+    for (int r = 0; r < cs; ++r) {
+        const double *rp = cluster.map_shared_rank(part_sum, r);
+        tot[0] += rp[0]; tot[1] += rp[1]; tot[2] += rp[2];
+    }
+    const float cx = (float)(tot[0] / (double)n), cy = (float)(tot[1] / (double)n), cz = (float)(tot[2] / (double)n);
+
+    // ---- max squared distance: (dx*dx + dy*dy) + dz*dz, separate roundings ----
+    float md = 0.f;
+    for (int64_t i = tid; i < np; i += kNormThreads) {
+        const float dx = __fsub_rn(sm[off + 3 * i], cx);
+        const float dy = __fsub_rn(sm[off + 3 * i + 1], cy);
+        const float dz = __fsub_rn(sm[off + 3 * i + 2], cz);
+        const float dd = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+        md = fmaxf(md, dd);
+    }
+    md = warp_max(md);
+    if (lane == 0) red_f[warp] = md;
+    __syncthreads();
+    if (tid == 0) {
+        float m = 0.f;
+        for (int w = 0; w < kNormThreads / 32; ++w) m = fmaxf(m, red_f[w]);
+        part_max = m;
+    }
+    cluster.sync();
+    float gmax = 0.f;
+    for (int r = 0; r < cs; ++r) gmax = fmaxf(gmax, *cluster.map_shared_rank(&part_max, r));
+    const float scale = fmaxf(__fsqrt_rn(gmax), 1e-7f);   // sqrt is monotone: sqrt(max d^2) == max sqrt(d^2)
+    if (rank == 0 && tid == 0) {
+        if (centroid_out) { centroid_out[cloud * 3] = cx; centroid_out[cloud * 3 + 1] = cy; centroid_out[cloud * 3 + 2] = cz; }
+        if (scale_out) scale_out[cloud] = scale;
+    }
+
+    // ---- write back: (x - c) / scale, true divide ----
+    const float c3[3] = {cx, cy, cz};
+    if (dst_same) {
+        for (int64_t v = tid; v < nvec; v += kNormThreads) {
+            const int64_t base = 4 * v - off;
+            // (p0*3 + base) % 3 == base % 3 (mod with negatives handled below)
+            int comp = (int)(((base % 3) + 3) % 3);
+            if (base >= 0 && base + 3 < nf) {
+                float4 q = smem4[v];
+                float r[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    r[j] = __fdiv_rn(__fsub_rn(r[j], c3[comp]), scale);
+                    comp = comp == 2 ? 0 : comp + 1;
+                }
+                *reinterpret_cast<float4 *>(dst + base) = make_float4(r[0], r[1], r[2], r[3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (base + j >= 0 && base + j < nf) dst[base + j] = __fdiv_rn(__fsub_rn(sm[4 * v + j], c3[comp]), scale);
+                    comp = comp == 2 ? 0 : comp + 1;
+                }
+            }
+        }
+    } else {
+        for (int64_t i = tid; i < nf; i += kNormThreads) dst[i] = __fdiv_rn(__fsub_rn(sm[off + i], c3[i % 3]), scale);
+    }
+    cluster.sync();   // keep part_sum / part_max alive until every peer has read them
+}
+
+// ---- streaming kernels: 4 points (3 x float4) per thread-iteration ----
+__device__ __forceinline__ void box_muller3(const uint32_t r[4], float out[3]) {
+    // u in (0,1]: (r + 1) * 2^-32 ; normals: sqrt(-2 ln u0) * {cos,sin}(2 pi u1), sqrt(-2 ln u2) * cos(2 pi u3)
+    const float u0 = ((float)(r[0] >> 8) + 1.0f) * (1.0f / 16777216.0f);
+    const float u1 = (float)(r[1] >> 8) * (1.0f / 16777216.0f);
+    const float u2 = ((float)(r[2] >> 8) + 1.0f) * (1.0f / 16777216.0f);
+    const float u3 = (float)(r[3] >> 8) * (1.0f / 16777216.0f);
+    const float ra = sqrtf(-2.0f * logf(u0)), rb = sqrtf(-2.0f * logf(u2));
+    float s, c;
+    sincospif(2.0f * u1, &s, &c);
+    out[0] = ra * c; out[1] = ra * s;
+    out[2] = rb * cospif(2.0f * u3);
+}
+
+__device__ __forceinline__ void point_noise(int64_t point, uint64_t seed, uint64_t offset, float out[3]) {
+    const uint64_t ctr = (uint64_t)point + offset;
+    uint32_t c[4] = {(uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, 0u};
+    philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+    box_muller3(c, out);
+}
+
+__global__ void __launch_bounds__(256)
+philox_normal_kernel(int64_t npoints, uint64_t seed, uint64_t offset, float *__restrict__ out)
+{
+    for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < npoints; p += (int64_t)gridDim.x * blockDim.x) {
+        float z[3];
+        point_noise(p, seed, offset, z);
+        out[3 * p] = z[0]; out[3 * p + 1] = z[1]; out[3 * p + 2] = z[2];
+    }
+}
+
+// y = x + noise * stdev (fp32 multiply, then add — PointCloudSet.py:337 is not fused)
+template <bool kExplicitNoise>
+__global__ void __launch_bounds__(256)
+jitter_kernel(const float *__restrict__ x, const float *__restrict__ noise, int64_t npoints, float sx, float sy, float sz,
+              uint64_t seed, uint64_t offset, float *__restrict__ y, int vec_ok)
+{
+    const float sd[3] = {sx, sy, sz};
+    const int64_t ngroups = npoints >> 2;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t t0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (vec_ok) {
+        for (int64_t g = t0; g < ngroups; g += stride) {
+            const float4 *xs = reinterpret_cast<const float4 *>(x) + 3 * g;
+            float4 a = __ldg(xs), b = __ldg(xs + 1), c = __ldg(xs + 2);
+            float v[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+            float z[12];
+            if (kExplicitNoise) {
+                const float4 *ns = reinterpret_cast<const float4 *>(noise) + 3 * g;
+                float4 na = __ldg(ns), nb = __ldg(ns + 1), nc = __ldg(ns + 2);
+                z[0] = na.x; z[1] = na.y; z[2] = na.z; z[3] = na.w; z[4] = nb.x; z[5] = nb.y; z[6] = nb.z; z[7] = nb.w;
+                z[8] = nc.x; z[9] = nc.y; z[10] = nc.z; z[11] = nc.w;
+            } else {
+#pragma unroll
+                for (int p = 0; p < 4; ++p) point_noise(4 * g + p, seed, offset, z + 3 * p);
+            }
+#pragma unroll
+            for (int j = 0; j < 12; ++j) v[j] = __fadd_rn(v[j], __fmul_rn(z[j], sd[j % 3]));
+            float4 *ys = reinterpret_cast<float4 *>(y) + 3 * g;
+            ys[0] = make_float4(v[0], v[1], v[2], v[3]);
+            ys[1] = make_float4(v[4], v[5], v[6], v[7]);
+            ys[2] = make_float4(v[8], v[9], v[10], v[11]);
+        }
+    }
+    const int64_t tail0 = vec_ok ? (ngroups << 2) : 0;
+    for (int64_t p = tail0 + t0; p < npoints; p += stride) {
+        float z[3];
+        if (kExplicitNoise) { z[0] = noise[3 * p]; z[1] = noise[3 * p + 1]; z[2] = noise[3 * p + 2]; }
+        else point_noise(p, seed, offset, z);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) y[3 * p + j] = __fadd_rn(x[3 * p + j], __fmul_rn(z[j], sd[j]));
+    }
+}
+
+// y_j = (x0*R[j][0] + x1*R[j][1]) + x2*R[j][2]  (no FMA), R per cloud.  grid.y = cloud.
+__global__ void __launch_bounds__(256)
+rotate_kernel(const float *__restrict__ x, int64_t n, const float *__restrict__ R, float *__restrict__ y, int vec_ok)
+{
+    const int64_t cloud = blockIdx.y;
+    __shared__ float r[9];
+    if (threadIdx.x < 9) r[threadIdx.x] = R[cloud * 9 + threadIdx.x];
+    __syncthreads();
+    const float *xc = x + cloud * n * 3;
+    float *yc = y + cloud * n * 3;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t t0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t ngroups = n >> 2;
+    auto rot = [&](const float *p, float *q) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            q[j] = __fadd_rn(__fadd_rn(__fmul_rn(p[0], r[3 * j]), __fmul_rn(p[1], r[3 * j + 1])), __fmul_rn(p[2], r[3 * j + 2]));
+    };
+    if (vec_ok) {
+        for (int64_t g = t0; g < ngroups; g += stride) {
+            const float4 *xs = reinterpret_cast<const float4 *>(xc) + 3 * g;
+            float4 a = __ldg(xs), b = __ldg(xs + 1), c = __ldg(xs + 2);
+            float v[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+            float o[12];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) rot(v + 3 * p, o + 3 * p);
+            float4 *ys = reinterpret_cast<float4 *>(yc) + 3 * g;
+            ys[0] = make_float4(o[0], o[1], o[2], o[3]);
+            ys[1] = make_float4(o[4], o[5], o[6], o[7]);
+            ys[2] = make_float4(o[8], o[9], o[10], o[11]);
+        }
+    }
+    const int64_t tail0 = vec_ok ? (ngroups << 2) : 0;
+    for (int64_t p = tail0 + t0; p < n; p += stride) {
+        float v[3] = {xc[3 * p], xc[3 * p + 1], xc[3 * p + 2]}, o[3];
+        rot(v, o);
+        yc[3 * p] = o[0]; yc[3 * p + 1] = o[1]; yc[3 * p + 2] = o[2];
+    }
+}
+
+// _adjust_to_input_width: slot j < N -> point j; slot j >= N -> point floor(u * N), u from Philox(seed; cloud, j)
+__global__ void __launch_bounds__(256)
+resize_kernel(const float *__restrict__ x, const int32_t *__restrict__ labels, int64_t n_in_stride,
+              const int32_t *__restrict__ n_in, int64_t n_out, uint64_t seed, float *__restrict__ y,
+              int32_t *__restrict__ labels_out)
+{
+    const int64_t cloud = blockIdx.y;
+    const int64_t N = n_in[cloud];
+    const float *xc = x + cloud * n_in_stride * 3;
+    float *yc = y + cloud * n_out * 3;
+    for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n_out; j += (int64_t)gridDim.x * blockDim.x) {
+        int64_t srcp = j;
+        if (j >= N) {
+            uint32_t c[4] = {(uint32_t)j, (uint32_t)(j >> 32), (uint32_t)cloud, 0x5e512eu};
+            philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+            // floor(U(0,N)) with U = r * 2^-32 evaluated exactly in integers
+            srcp = N > 0 ? (int64_t)(((uint64_t)c[0] * (uint64_t)N) >> 32) : 0;
+        }
+        float vx = 0.f, vy = 0.f, vz = 0.f;
+        int32_t lb = 0;
+        if (N > 0) {
+            vx = xc[3 * srcp]; vy = xc[3 * srcp + 1]; vz = xc[3 * srcp + 2];
+            if (labels) lb = labels[cloud * n_in_stride + srcp];
+        }
+        yc[3 * j] = vx; yc[3 * j + 1] = vy; yc[3 * j + 2] = vz;
+        if (labels_out) labels_out[cloud * n_out + j] = lb;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+gather_kernel(const float *__restrict__ x, const int32_t *__restrict__ labels, int64_t n, const int32_t *__restrict__ idx,
+              int s, float *__restrict__ out, int32_t *__restrict__ labels_out)
+{
+    const int64_t cloud = blockIdx.y;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < s; j += gridDim.x * blockDim.x) {
+        const int64_t i = idx[cloud * s + j];
+        const float *p = x + (cloud * n + i) * 3;
+        float *q = out + (cloud * s + j) * 3;
+        q[0] = p[0]; q[1] = p[1]; q[2] = p[2];
+        if (labels_out) labels_out[cloud * s + j] = labels[cloud * n + i];
+    }
+}
+
+static int stream_grid(int64_t work_items, int threads) {
+    int64_t blocks = (work_items + threads - 1) / threads;
+    const int64_t cap = (int64_t)sm_count() * 8;          // multiple of the SM count, grid-stride beyond
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+}  // namespace pcp
+
+using namespace pcp;
+
+extern "C" int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale,
+                                 pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && d_y && b >= 0 && n >= 1, PCP_ERR_INVALID, "pcp_normalize_f32: bad arguments (b=%d n=%lld)", b, (long long)n);
+    if (b == 0) return PCP_OK;
+    // cluster size: slice must fit in shared memory; widen further while the grid under-fills the GPU
+    const int64_t max_slice_bytes = 200 * 1024;
+    int cs = 1;
+    while (cs < 16 && (n * 12 / cs > max_slice_bytes || ((int64_t)b * cs < 2 * sm_count() && n / cs > 4096))) cs *= 2;
+    PCP_REQUIRE(n * 12 / cs <= max_slice_bytes, PCP_ERR_UNSUPPORTED,
+                "pcp_normalize_f32: n=%lld exceeds the cluster-resident limit (%lld points)", (long long)n,
+                (long long)(16 * max_slice_bytes / 12));
+    const int64_t ppc = (((n + cs - 1) / cs) + 3) & ~(int64_t)3;
+    const size_t smem = (size_t)(ppc * 3 + 8) * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(normalize_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        PCP_CUDA_OK(cudaFuncSetAttribute(normalize_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((int64_t)b * cs));
+    cfg.blockDim = dim3(kNormThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = as_stream(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, normalize_cluster_kernel, d_x, n, d_y, d_centroid, d_scale, cs, ppc));
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+extern "C" int pcp_philox_normal_f32(int64_t npoints, uint64_t seed, uint64_t offset, float *d_noise, pcp_stream stream)
+{
+    PCP_REQUIRE(d_noise && npoints >= 0, PCP_ERR_INVALID, "pcp_philox_normal_f32: bad arguments");
+    if (npoints == 0) return PCP_OK;
+    philox_normal_kernel<<<stream_grid(npoints, 256), 256, 0, as_stream(stream)>>>(npoints, seed, offset, d_noise);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+extern "C" int pcp_jitter_f32(const float *d_x, int64_t npoints, const float h_stdev[3], uint64_t seed, uint64_t offset,
+                              const float *d_noise, float *d_y, pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && d_y && h_stdev && npoints >= 0, PCP_ERR_INVALID, "pcp_jitter_f32: bad arguments");
+    if (npoints == 0) return PCP_OK;
+    const int vec_ok = ((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y) |
+                         reinterpret_cast<uintptr_t>(d_noise)) & 15u) == 0;
+    const int grid = stream_grid((npoints + 3) / 4, 256);
+    if (d_noise)
+        jitter_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(d_x, d_noise, npoints, h_stdev[0], h_stdev[1], h_stdev[2], seed, offset, d_y, vec_ok);
+    else
+        jitter_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(d_x, nullptr, npoints, h_stdev[0], h_stdev[1], h_stdev[2], seed, offset, d_y, vec_ok);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+extern "C" int pcp_rotate_f32(const float *d_x, int b, int64_t n, const float *d_R, float *d_y, pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && d_y && d_R && b >= 0 && n >= 0, PCP_ERR_INVALID, "pcp_rotate_f32: bad arguments");
+    if (b == 0 || n == 0) return PCP_OK;
+    PCP_REQUIRE(b <= 65535, PCP_ERR_UNSUPPORTED, "pcp_rotate_f32: b > 65535");
+    const int vec_ok = (((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y)) & 15u) == 0) && (n % 4 == 0);
+    int gx = (int)((n / 4 + 255) / 256);
+    const int cap = (sm_count() * 8 + b - 1) / b;
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    rotate_kernel<<<dim3(gx, b), 256, 0, as_stream(stream)>>>(d_x, n, d_R, d_y, vec_ok);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+extern "C" int pcp_resize_to_width_f32(const float *d_x, const int32_t *d_labels, int b, int64_t n_in_stride,
+                                       const int32_t *d_n_in, int64_t n_out, uint64_t seed, float *d_y,
+                                       int32_t *d_labels_out, pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && d_y && d_n_in && b >= 0 && n_out >= 0 && n_in_stride >= 0, PCP_ERR_INVALID, "pcp_resize_to_width_f32: bad arguments");
+    PCP_REQUIRE(!d_labels_out || d_labels, PCP_ERR_INVALID, "pcp_resize_to_width_f32: labels_out without labels");
+    if (b == 0 || n_out == 0) return PCP_OK;
+    PCP_REQUIRE(b <= 65535, PCP_ERR_UNSUPPORTED, "pcp_resize_to_width_f32: b > 65535");
+    int gx = (int)((n_out + 255) / 256);
+    if (gx > 1024) gx = 1024;
+    resize_kernel<<<dim3(gx, b), 256, 0, as_stream(stream)>>>(d_x, d_labels, n_in_stride, d_n_in, n_out, seed, d_y, d_labels_out);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+extern "C" int pcp_gather_points_f32(const float *d_x, const int32_t *d_labels, int b, int64_t n, const int32_t *d_idx, int s,
+                                     float *d_out, int32_t *d_labels_out, pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && d_idx && d_out && b >= 0 && s >= 0, PCP_ERR_INVALID, "pcp_gather_points_f32: bad arguments");
+    PCP_REQUIRE(!d_labels_out || d_labels, PCP_ERR_INVALID, "pcp_gather_points_f32: labels_out without labels");
+    if (b == 0 || s == 0) return PCP_OK;
+    PCP_REQUIRE(b <= 65535, PCP_ERR_UNSUPPORTED, "pcp_gather_points_f32: b > 65535");
+    gather_kernel<<<dim3((s + 255) / 256, b), 256, 0, as_stream(stream)>>>(d_x, d_labels, n, d_idx, s, d_out, d_labels_out);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}

@@ -1,0 +1,498 @@
+// model.cu — pcp_model lifecycle, tensor table, inference BN fold, and the fp32 forward pass
+// (PointNet.call, pointnet/PointNet.py:197-292) expressed as a sequence of fused GEMM launches.
+#include <cmath>
+#include <cstring>
+
+#include "gemm_simt.cuh"
+#include "model.cuh"
+
+namespace pcp {
+
+static const float kBnEps = 1e-3f;   // keras BatchNormalization default epsilon
+
+static void add_tensor(pcp_model *m, const std::string &name, size_t count, int group, bool is_stat, int *slot)
+{
+    TensorSpec t;
+    t.name = name; t.offset = m->n_params; t.count = count; t.group = group; t.is_stat = is_stat;
+    m->n_params += (count + 3) & ~(size_t)3;     // keep every tensor 16-byte aligned in the flat buffer
+    m->index[name] = (int)m->tensors.size();
+    if (slot) *slot = (int)m->tensors.size();
+    m->tensors.push_back(t);
+}
+
+static void add_layer(pcp_model *m, int id, const std::string &name, int cin, int cout, bool has_bn, int group)
+{
+    LayerSpec &L = m->layers[id];
+    L.name = name; L.cin = cin; L.cout = cout; L.has_bn = has_bn; L.present = true; L.group = group;
+    add_tensor(m, name + "/kernel", (size_t)cin * cout, group, false, &L.t_kernel);
+    if (has_bn) {
+        add_tensor(m, name + "/bn/gamma", cout, group, false, &L.t_gamma);
+        add_tensor(m, name + "/bn/beta", cout, group, false, &L.t_beta);
+        add_tensor(m, name + "/bn/moving_mean", cout, group, true, &L.t_mean);
+        add_tensor(m, name + "/bn/moving_variance", cout, group, true, &L.t_var);
+    } else {
+        add_tensor(m, name + "/bias", cout, group, false, &L.t_bias);
+    }
+}
+
+static void add_tnet(pcp_model *m, int first, const std::string &tn, int k, int group, int *t_w, int *t_b)
+{
+    const int w[5] = {64, 128, 1024, 512, 256};          // layer_widths, PointNet.py:384
+    add_layer(m, first + 0, tn + "_convolution_layer_1_convolution_layer", k, w[0], true, group);
+    add_layer(m, first + 1, tn + "_convolution_layer_2_convolution_layer", w[0], w[1], true, group);
+    add_layer(m, first + 2, tn + "_convolution_layer_3_convolution_layer", w[1], w[2], true, group);
+    add_layer(m, first + 3, tn + "_dense_layer_1_dense_layer", w[2], w[3], true, group);
+    add_layer(m, first + 4, tn + "_dense_layer_2_dense_layer", w[3], w[4], true, group);
+    add_tensor(m, tn + "/w", (size_t)256 * k * k, group, false, t_w);
+    add_tensor(m, tn + "/b", (size_t)k * k, group, false, t_b);
+}
+
+static void build_spec(pcp_model *m)
+{
+    const int C = m->desc.num_classes, P = m->desc.num_parts;
+    const bool full = !m->desc.vanilla;
+    if (full) add_tnet(m, L_IT_C1, "input_transform", 3, PCP_GROUP_INPUT_TRANSFORM, &m->t_it_w, &m->t_it_b);
+    add_layer(m, L_S1_1, "s1_l1_64_convolution_layer", 3, 64, true, PCP_GROUP_SHARED);
+    add_layer(m, L_S1_2, "s1_l2_64_convolution_layer", 64, 64, true, PCP_GROUP_SHARED);
+    if (full) add_tnet(m, L_FT_C1, "feature_transform", 64, PCP_GROUP_SHARED, &m->t_ft_w, &m->t_ft_b);
+    add_layer(m, L_S2_1, "s2_l1_64_convolution_layer", 64, 64, true, PCP_GROUP_SHARED);
+    add_layer(m, L_S2_2, "s2_l2_128_convolution_layer", 64, 128, true, PCP_GROUP_SHARED);
+    add_layer(m, L_S2_3, "s2_l3_1024_convolution_layer", 128, 1024, true, PCP_GROUP_SHARED);
+    add_layer(m, L_CLS1, "s3_l1_512_dense_layer", 1024, 512, true, PCP_GROUP_CLS_HEAD);
+    add_layer(m, L_CLS2, "s3_l2_256_dense_layer", 512, 256, true, PCP_GROUP_CLS_HEAD);
+    add_layer(m, L_CLS3, "output_dense_layer", 256, C, false, PCP_GROUP_CLS_HEAD);
+    add_layer(m, L_SEG1, "seg_l1_512_convolution_layer", 1088, 512, true, PCP_GROUP_SEG_HEAD);
+    add_layer(m, L_SEG2, "seg_l2_256_convolution_layer", 512, 256, true, PCP_GROUP_SEG_HEAD);
+    add_layer(m, L_SEG3, "seg_l3_128_convolution_layer", 256, 128, true, PCP_GROUP_SEG_HEAD);
+    add_layer(m, L_SEG4, "seg_l4_128_convolution_layer", 128, 128, true, PCP_GROUP_SEG_HEAD);
+    add_layer(m, L_SEG5, "seg_l5_output_convolution_layer", 128, P, false, PCP_GROUP_SEG_HEAD);
+    // folded image layout
+    size_t off = 0;
+    auto take = [&](size_t cnt) { size_t o = off; off += (cnt + 3) & ~(size_t)3; return o; };
+    for (int i = 0; i < L_COUNT; ++i) {
+        LayerSpec &L = m->layers[i];
+        if (!L.present) continue;
+        L.fold_w = take((size_t)L.cin * L.cout);
+        L.fold_t = take(L.cout);
+    }
+    if (full) {
+        m->fold_it_w = take(256 * 9); m->fold_it_t = take(9);
+        m->fold_ft_w = take(256 * 4096); m->fold_ft_t = take(4096);
+    }
+    m->n_fold = off;
+}
+
+static void init_defaults(pcp_model *m)
+{
+    // Keras build-time state: BN gamma=1, beta=0, mean=0, var=1 (PointNet.py:528); TNet b = identity (:416).
+    // Kernels are left at zero: the host side (pointnet/PointNet.py mirror) draws Glorot-uniform values.
+    for (auto &t : m->tensors) {
+        const std::string &nm = t.name;
+        float fill = 0.f;
+        if (nm.size() > 9 && nm.compare(nm.size() - 9, 9, "/bn/gamma") == 0) fill = 1.f;
+        if (nm.size() > 19 && nm.compare(nm.size() - 19, 19, "/bn/moving_variance") == 0) fill = 1.f;
+        if (fill != 0.f) for (size_t i = 0; i < t.count; ++i) m->h_params[t.offset + i] = fill;
+    }
+    auto eye = [&](int ti, int k) {
+        if (ti < 0) return;
+        for (int i = 0; i < k; ++i) m->h_params[m->tensors[ti].offset + (size_t)i * k + i] = 1.f;
+    };
+    eye(m->t_it_b, 3);
+    eye(m->t_ft_b, 64);
+}
+
+static int ws_alloc(Workspace &ws, float **p, size_t count)
+{
+    void *q = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&q, (count ? count : 1) * sizeof(float)));
+    ws.allocs.push_back(q);
+    *p = reinterpret_cast<float *>(q);
+    return PCP_OK;
+}
+
+static void ws_free(Workspace &ws)
+{
+    for (void *p : ws.allocs) cudaFree(p);
+    if (ws.pin_x) cudaFreeHost(ws.pin_x);
+    if (ws.pin_out) cudaFreeHost(ws.pin_out);
+    ws = Workspace();
+}
+
+__global__ void __launch_bounds__(256)
+softmax_rows_kernel(const float *__restrict__ z, float *__restrict__ p, int64_t rows, int cols)
+{
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < rows; r += (int64_t)gridDim.x * blockDim.x) {
+        const float *zr = z + r * cols;
+        float mx = zr[0];
+        for (int c = 1; c < cols; ++c) mx = fmaxf(mx, zr[c]);
+        float s = 0.f;
+        for (int c = 0; c < cols; ++c) s += expf(zr[c] - mx);
+        const float inv = 1.0f / s;
+        for (int c = 0; c < cols; ++c) p[r * cols + c] = expf(zr[c] - mx) * inv;
+    }
+}
+
+__global__ void eye3_kernel(float *R, int b)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < b) {
+#pragma unroll
+        for (int j = 0; j < 9; ++j) R[i * 9 + j] = (j % 4 == 0) ? 1.f : 0.f;
+    }
+}
+
+int model_sync_host(pcp_model *m)
+{
+    if (m->dev_newer) {
+        PCP_CUDA_OK(cudaDeviceSynchronize());
+        PCP_CUDA_OK(cudaMemcpy(m->h_params.data(), m->d_params, m->n_params * sizeof(float), cudaMemcpyDeviceToHost));
+        m->dev_newer = false;
+    }
+    return PCP_OK;
+}
+
+int softmax_rows(const float *d_logits, float *d_prob, int64_t rows, int cols, cudaStream_t st)
+{
+    if (rows <= 0) return PCP_OK;
+    int64_t blocks = (rows + 255) / 256;
+    if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+    softmax_rows_kernel<<<(unsigned)blocks, 256, 0, st>>>(d_logits, d_prob, rows, cols);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+// C = act(A . Wfold + t): one ConvLayer / DenseLayer in inference form (PointNet.py:554-566, :642-654)
+static int layer_fwd(pcp_model *m, int id, const float *A, int64_t M, float *C, bool relu, cudaStream_t st,
+                     float *colmax = nullptr, int groups = 1, int64_t rows_per_group = 0)
+{
+    const LayerSpec &L = m->layers[id];
+    GemmArgs g;
+    g.A = A; g.lda = L.cin; g.B = m->d_fold + L.fold_w; g.ldb = L.cout; g.C = C; g.ldc = L.cout;
+    g.bias = m->d_fold + L.fold_t; g.N = L.cout; g.K = L.cin; g.relu = relu ? 1 : 0;
+    if (colmax) {
+        g.groups = groups; g.M = (int)rows_per_group; g.strideA = rows_per_group * L.cin;
+        g.strideC = rows_per_group * L.cout; g.colmax = colmax; g.strideColmax = L.cout;
+    } else {
+        g.M = (int)M;
+    }
+    return gemm_f32(g, st);
+}
+
+// TNet tail: pooled (bc,1024) -> dense 512 -> 256 -> (256 x K^2) + b  (PointNet.py:431-442)
+static int tnet_tail(pcp_model *m, int first, size_t fold_w, size_t fold_t, int k, const float *pooled, int bc, float *out,
+                     cudaStream_t st)
+{
+    Workspace &ws = m->ws;
+    PCP_TRY(layer_fwd(m, first + 3, pooled, bc, ws.d512, true, st));
+    PCP_TRY(layer_fwd(m, first + 4, ws.d512, bc, ws.d256, true, st));
+    GemmArgs g;
+    g.A = ws.d256; g.lda = 256; g.B = m->d_fold + fold_w; g.ldb = k * k; g.C = out; g.ldc = k * k;
+    g.bias = m->d_fold + fold_t; g.M = bc; g.N = k * k; g.K = 256;
+    return gemm_f32(g, st);
+}
+
+int model_forward_fp32(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
+                       float *d_R, float *d_cls_logits, float *d_seg_logits, cudaStream_t st)
+{
+    Workspace &ws = m->ws;
+    const bool full = !m->desc.vanilla;
+    const int C = m->desc.num_classes, P = m->desc.num_parts;
+    for (int c0 = 0; c0 < b; c0 += ws.cap_b) {
+        const int bc = std::min(ws.cap_b, b - c0);
+        const int64_t M = (int64_t)bc * n;
+        const float *x = d_x + (int64_t)c0 * n * 3;
+        float *g1 = ws.g1 + (int64_t)c0 * 1024, *g2 = ws.g2 + (int64_t)c0 * 1024, *g3 = ws.g3 + (int64_t)c0 * 1024;
+        PCP_TRY(pcp_normalize_f32(x, bc, n, ws.pcn, nullptr, nullptr, st));                       // :202
+        const float *X3 = ws.pcn;
+        float *Rout = d_R ? d_R + (int64_t)c0 * 9 : ws.R;
+        if (full) {
+            PCP_CUDA_OK(cudaMemsetAsync(g1, 0, (size_t)bc * 1024 * sizeof(float), st));
+            PCP_TRY(layer_fwd(m, L_IT_C1, ws.pcn, M, ws.h64a, true, st));                          // TNet.call :423
+            PCP_TRY(layer_fwd(m, L_IT_C2, ws.h64a, M, ws.h128, true, st));                         // :424
+            PCP_TRY(layer_fwd(m, L_IT_C3, ws.h128, M, nullptr, true, st, g1, bc, n));              // :425 + reduce_max :429
+            PCP_TRY(tnet_tail(m, L_IT_C1, m->fold_it_w, m->fold_it_t, 3, g1, bc, Rout, st));       // :431-442
+            GemmArgs g;                                                                            // X = pc @ R  :207
+            g.A = ws.pcn; g.lda = 3; g.strideA = n * 3; g.B = Rout; g.ldb = 3; g.strideB = 9;
+            g.C = ws.xr; g.ldc = 3; g.strideC = n * 3; g.M = (int)n; g.N = 3; g.K = 3; g.groups = bc;
+            PCP_TRY(gemm_f32(g, st));
+            X3 = ws.xr;
+        } else if (d_R) {
+            eye3_kernel<<<(bc + 255) / 256, 256, 0, st>>>(Rout, bc);                                // :211
+            PCP_CHECK_LAUNCH();
+        }
+        PCP_TRY(layer_fwd(m, L_S1_1, X3, M, ws.h64a, true, st));                                   // :217
+        PCP_TRY(layer_fwd(m, L_S1_2, ws.h64a, M, ws.h64b, true, st));                              // :220
+        const float *X64 = ws.h64b;
+        if (full) {
+            PCP_CUDA_OK(cudaMemsetAsync(g2, 0, (size_t)bc * 1024 * sizeof(float), st));
+            PCP_TRY(layer_fwd(m, L_FT_C1, ws.h64b, M, ws.h64a, true, st));
+            PCP_TRY(layer_fwd(m, L_FT_C2, ws.h64a, M, ws.h128, true, st));
+            PCP_TRY(layer_fwd(m, L_FT_C3, ws.h128, M, nullptr, true, st, g2, bc, n));
+            PCP_TRY(tnet_tail(m, L_FT_C1, m->fold_ft_w, m->fold_ft_t, 64, g2, bc, ws.R64, st));     // :227
+            GemmArgs g;                                                                            // X_64 = X @ R_64 :228
+            g.A = ws.h64b; g.lda = 64; g.strideA = n * 64; g.B = ws.R64; g.ldb = 64; g.strideB = 4096;
+            g.C = ws.x64; g.ldc = 64; g.strideC = n * 64; g.M = (int)n; g.N = 64; g.K = 64; g.groups = bc;
+            PCP_TRY(gemm_f32(g, st));
+            X64 = ws.x64;
+        }
+        PCP_CUDA_OK(cudaMemsetAsync(g3, 0, (size_t)bc * 1024 * sizeof(float), st));
+        PCP_TRY(layer_fwd(m, L_S2_1, X64, M, ws.h64a, true, st));                                  // :236
+        PCP_TRY(layer_fwd(m, L_S2_2, ws.h64a, M, ws.h128, true, st));                              // :239
+        PCP_TRY(layer_fwd(m, L_S2_3, ws.h128, M, nullptr, true, st, g3, bc, n));                   // :242 + :248
+
+        if (heads & PCP_HEAD_CLS) {                                                                // :252-263
+            PCP_TRY(layer_fwd(m, L_CLS1, g3, bc, ws.d512, true, st));
+            PCP_TRY(layer_fwd(m, L_CLS2, ws.d512, bc, ws.d256, true, st));
+            float *logits = d_cls_logits ? d_cls_logits + (int64_t)c0 * C : ws.clslog;
+            PCP_TRY(layer_fwd(m, L_CLS3, ws.d256, bc, logits, false, st));
+            if (d_cls) PCP_TRY(softmax_rows(logits, d_cls + (int64_t)c0 * C, bc, C, st));
+        }
+        if (heads & PCP_HEAD_SEG) {                                                                // :268-290
+            // concat([X_64, tile(global)]) . W1  ==  X_64 . W1[0:64] + (global . W1[64:1088])  — the
+            // second term is constant per cloud and becomes a per-cloud bias vector.
+            const LayerSpec &S1 = m->layers[L_SEG1];
+            GemmArgs gv;
+            gv.A = g3; gv.lda = 1024; gv.B = m->d_fold + S1.fold_w + (size_t)64 * 512; gv.ldb = 512;
+            gv.C = ws.gvec; gv.ldc = 512; gv.bias = m->d_fold + S1.fold_t; gv.M = bc; gv.N = 512; gv.K = 1024;
+            PCP_TRY(gemm_f32(gv, st));
+            GemmArgs g;
+            g.A = X64; g.lda = 64; g.strideA = n * 64; g.B = m->d_fold + S1.fold_w; g.ldb = 512; g.strideB = 0;
+            g.C = ws.s512; g.ldc = 512; g.strideC = n * 512; g.bias = ws.gvec; g.strideBias = 512;
+            g.M = (int)n; g.N = 512; g.K = 64; g.groups = bc; g.relu = 1;
+            PCP_TRY(gemm_f32(g, st));
+            PCP_TRY(layer_fwd(m, L_SEG2, ws.s512, M, ws.s256, true, st));
+            PCP_TRY(layer_fwd(m, L_SEG3, ws.s256, M, ws.s128a, true, st));
+            PCP_TRY(layer_fwd(m, L_SEG4, ws.s128a, M, ws.s128b, true, st));
+            float *logits = d_seg_logits ? d_seg_logits + (int64_t)c0 * n * P : ws.seglog;
+            PCP_TRY(layer_fwd(m, L_SEG5, ws.s128b, M, logits, false, st));
+            if (d_seg) PCP_TRY(softmax_rows(logits, d_seg + (int64_t)c0 * n * P, M, P, st));
+        }
+    }
+    return PCP_OK;
+}
+
+int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
+                       float *d_R, float *d_cls_logits, float *d_seg_logits, cudaStream_t st);
+int model_prepare_bf16(pcp_model *m);
+void model_destroy_bf16(pcp_model *m);
+
+}  // namespace pcp
+
+using namespace pcp;
+
+extern "C" int pcp_model_create(const pcp_model_desc *desc, pcp_model **out)
+{
+    PCP_REQUIRE(desc && out, PCP_ERR_INVALID, "pcp_model_create: null argument");
+    PCP_REQUIRE(desc->num_classes >= 1 && desc->num_parts >= 1, PCP_ERR_INVALID, "pcp_model_create: widths must be >= 1");
+    PCP_REQUIRE(desc->precision == PCP_PRECISION_FP32 || desc->precision == PCP_PRECISION_BF16, PCP_ERR_INVALID,
+                "pcp_model_create: unknown precision %d", desc->precision);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        set_error("pcp_model_create: no CUDA device (%s) — this library has no CPU fallback", cudaGetErrorString(e));
+        return PCP_ERR_CUDA;
+    }
+    pcp_model *m = new pcp_model();
+    m->desc = *desc;
+    build_spec(m);
+    m->h_params.assign(m->n_params, 0.f);
+    init_defaults(m);
+    if (cudaMalloc(&m->d_params, m->n_params * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&m->d_fold, m->n_fold * sizeof(float)) != cudaSuccess) {
+        set_error("pcp_model_create: cudaMalloc failed");
+        delete m;
+        return PCP_ERR_NOMEM;
+    }
+    *out = m;
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_destroy(pcp_model *m)
+{
+    if (!m) return PCP_OK;
+    ws_free(m->ws);
+    model_destroy_bf16(m);
+    cudaFree(m->d_params); cudaFree(m->d_fold);
+    cudaFree(m->d_grads); cudaFree(m->d_adam_m); cudaFree(m->d_adam_v);
+    delete m;
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_num_tensors(const pcp_model *m) { return m ? (int)m->tensors.size() : 0; }
+
+extern "C" int pcp_model_tensor_info(const pcp_model *m, int index, char *name_buf, size_t name_buf_len, size_t *count,
+                                     int *trainable_group)
+{
+    PCP_REQUIRE(m && index >= 0 && index < (int)m->tensors.size(), PCP_ERR_INVALID, "pcp_model_tensor_info: bad index");
+    const TensorSpec &t = m->tensors[index];
+    if (name_buf && name_buf_len) { strncpy(name_buf, t.name.c_str(), name_buf_len - 1); name_buf[name_buf_len - 1] = 0; }
+    if (count) *count = t.count;
+    if (trainable_group) *trainable_group = t.is_stat ? -1 : t.group;
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_set_tensor(pcp_model *m, const char *name, const float *h_data, size_t count)
+{
+    PCP_REQUIRE(m && name && h_data, PCP_ERR_INVALID, "pcp_model_set_tensor: null argument");
+    auto it = m->index.find(name);
+    PCP_REQUIRE(it != m->index.end(), PCP_ERR_NOTFOUND, "pcp_model_set_tensor: unknown tensor '%s'", name);
+    const TensorSpec &t = m->tensors[it->second];
+    PCP_REQUIRE(t.count == count, PCP_ERR_INVALID, "pcp_model_set_tensor: '%s' has %zu elements, got %zu", name, t.count, count);
+    PCP_TRY(model_sync_host(m));
+    memcpy(m->h_params.data() + t.offset, h_data, count * sizeof(float));
+    m->prepared = false;
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_get_tensor(pcp_model *m, const char *name, float *h_data, size_t count)
+{
+    PCP_REQUIRE(m && name && h_data, PCP_ERR_INVALID, "pcp_model_get_tensor: null argument");
+    auto it = m->index.find(name);
+    PCP_REQUIRE(it != m->index.end(), PCP_ERR_NOTFOUND, "pcp_model_get_tensor: unknown tensor '%s'", name);
+    const TensorSpec &t = m->tensors[it->second];
+    PCP_REQUIRE(t.count == count, PCP_ERR_INVALID, "pcp_model_get_tensor: '%s' has %zu elements, got %zu", name, t.count, count);
+    PCP_TRY(model_sync_host(m));
+    memcpy(h_data, m->h_params.data() + t.offset, count * sizeof(float));
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_prepare(pcp_model *m)
+{
+    PCP_REQUIRE(m, PCP_ERR_INVALID, "pcp_model_prepare: null model");
+    PCP_TRY(model_sync_host(m));
+    std::vector<float> fold(m->n_fold, 0.f);
+    const float *P = m->h_params.data();
+    for (int i = 0; i < L_COUNT; ++i) {
+        const LayerSpec &L = m->layers[i];
+        if (!L.present) continue;
+        const float *W = P + m->tensors[L.t_kernel].offset;
+        float *Wf = fold.data() + L.fold_w, *tf = fold.data() + L.fold_t;
+        if (L.has_bn) {
+            const float *g = P + m->tensors[L.t_gamma].offset, *be = P + m->tensors[L.t_beta].offset;
+            const float *mu = P + m->tensors[L.t_mean].offset, *var = P + m->tensors[L.t_var].offset;
+            for (int c = 0; c < L.cout; ++c) {
+                const float s = g[c] / sqrtf(var[c] + kBnEps);       // inference BN: y = x*s + t
+                tf[c] = be[c] - mu[c] * s;
+                for (int k = 0; k < L.cin; ++k) Wf[(size_t)k * L.cout + c] = W[(size_t)k * L.cout + c] * s;
+            }
+        } else {
+            const float *bias = P + m->tensors[L.t_bias].offset;
+            memcpy(Wf, W, (size_t)L.cin * L.cout * sizeof(float));
+            memcpy(tf, bias, L.cout * sizeof(float));
+        }
+    }
+    if (!m->desc.vanilla) {
+        memcpy(fold.data() + m->fold_it_w, P + m->tensors[m->t_it_w].offset, 256 * 9 * sizeof(float));
+        memcpy(fold.data() + m->fold_it_t, P + m->tensors[m->t_it_b].offset, 9 * sizeof(float));
+        memcpy(fold.data() + m->fold_ft_w, P + m->tensors[m->t_ft_w].offset, (size_t)256 * 4096 * sizeof(float));
+        memcpy(fold.data() + m->fold_ft_t, P + m->tensors[m->t_ft_b].offset, 4096 * sizeof(float));
+    }
+    PCP_CUDA_OK(cudaMemcpy(m->d_fold, fold.data(), m->n_fold * sizeof(float), cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemcpy(m->d_params, m->h_params.data(), m->n_params * sizeof(float), cudaMemcpyHostToDevice));
+    if (m->desc.precision == PCP_PRECISION_BF16) PCP_TRY(model_prepare_bf16(m));
+    m->prepared = true;
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_reserve(pcp_model *m, int b, int64_t n)
+{
+    PCP_REQUIRE(m && b >= 1 && n >= 1, PCP_ERR_INVALID, "pcp_model_reserve: bad arguments");
+    Workspace &ws = m->ws;
+    if (ws.total_b >= b && ws.cap_n == n) return PCP_OK;
+    ws_free(ws);
+    const int C = m->desc.num_classes, P = m->desc.num_parts;
+    const bool fp32 = m->desc.precision == PCP_PRECISION_FP32;
+    // fp32 path materialises per-point activations: bound a chunk to ~192k points
+    const int64_t max_pts = fp32 ? 196608 : ((int64_t)1 << 40);
+    int cap_b = (int)std::max<int64_t>(1, std::min<int64_t>(b, max_pts / n));
+    ws.cap_b = cap_b; ws.cap_n = n; ws.total_b = b;
+    const size_t Mc = (size_t)cap_b * (size_t)n;
+    if (fp32) {
+        PCP_TRY(ws_alloc(ws, &ws.pcn, Mc * 3)); PCP_TRY(ws_alloc(ws, &ws.xr, Mc * 3));
+        PCP_TRY(ws_alloc(ws, &ws.h64a, Mc * 64)); PCP_TRY(ws_alloc(ws, &ws.h64b, Mc * 64));
+        PCP_TRY(ws_alloc(ws, &ws.x64, Mc * 64)); PCP_TRY(ws_alloc(ws, &ws.h128, Mc * 128));
+        PCP_TRY(ws_alloc(ws, &ws.s512, Mc * 512)); PCP_TRY(ws_alloc(ws, &ws.s256, Mc * 256));
+        PCP_TRY(ws_alloc(ws, &ws.s128a, Mc * 128)); PCP_TRY(ws_alloc(ws, &ws.s128b, Mc * 128));
+        PCP_TRY(ws_alloc(ws, &ws.seglog, Mc * P));
+    }
+    PCP_TRY(ws_alloc(ws, &ws.g1, (size_t)b * 1024)); PCP_TRY(ws_alloc(ws, &ws.g2, (size_t)b * 1024));
+    PCP_TRY(ws_alloc(ws, &ws.g3, (size_t)b * 1024));
+    PCP_TRY(ws_alloc(ws, &ws.d512, (size_t)b * 512)); PCP_TRY(ws_alloc(ws, &ws.d256, (size_t)b * 256));
+    PCP_TRY(ws_alloc(ws, &ws.R, (size_t)b * 9)); PCP_TRY(ws_alloc(ws, &ws.R64, (size_t)b * 4096));
+    PCP_TRY(ws_alloc(ws, &ws.gvec, (size_t)b * 512)); PCP_TRY(ws_alloc(ws, &ws.clslog, (size_t)b * C));
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_forward(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
+                                 float *d_R, float *d_cls_logits, float *d_seg_logits, pcp_stream stream)
+{
+    PCP_REQUIRE(m && d_x && b >= 1 && n >= 1, PCP_ERR_INVALID, "pcp_model_forward: bad arguments");
+    PCP_REQUIRE(m->prepared, PCP_ERR_STATE, "pcp_model_forward: call pcp_model_prepare first");
+    PCP_REQUIRE(!(d_cls || d_cls_logits) || (heads & PCP_HEAD_CLS), PCP_ERR_INVALID, "pcp_model_forward: cls output without PCP_HEAD_CLS");
+    PCP_REQUIRE(!(d_seg || d_seg_logits) || (heads & PCP_HEAD_SEG), PCP_ERR_INVALID, "pcp_model_forward: seg output without PCP_HEAD_SEG");
+    if (m->ws.total_b < b || m->ws.cap_n != n) PCP_TRY(pcp_model_reserve(m, b, n));
+    if (m->desc.precision == PCP_PRECISION_BF16)
+        return model_forward_bf16(m, d_x, b, n, heads, d_cls, d_seg, d_R, d_cls_logits, d_seg_logits, as_stream(stream));
+    return model_forward_fp32(m, d_x, b, n, heads, d_cls, d_seg, d_R, d_cls_logits, d_seg_logits, as_stream(stream));
+}
+
+extern "C" int pcp_model_predict_host(pcp_model *m, const float *h_x, int b, int64_t n, uint32_t heads, float *h_cls,
+                                      float *h_seg, float *h_R, pcp_stream stream)
+{
+    PCP_REQUIRE(m && h_x && b >= 1 && n >= 1, PCP_ERR_INVALID, "pcp_model_predict_host: bad arguments");
+    if (m->ws.total_b < b || m->ws.cap_n != n) PCP_TRY(pcp_model_reserve(m, b, n));
+    Workspace &ws = m->ws;
+    const int C = m->desc.num_classes, P = m->desc.num_parts;
+    const size_t xb = (size_t)b * n * 3 * sizeof(float);
+    const size_t cls_cnt = (h_cls ? (size_t)b * C : 0), seg_cnt = (h_seg ? (size_t)b * n * P : 0), r_cnt = (h_R ? (size_t)b * 9 : 0);
+    cudaStream_t st = as_stream(stream);
+    if (!ws.stage_x) {
+        PCP_TRY(ws_alloc(ws, &ws.stage_x, (size_t)ws.total_b * ws.cap_n * 3));
+        PCP_TRY(ws_alloc(ws, &ws.stage_cls, (size_t)ws.total_b * C));
+        PCP_TRY(ws_alloc(ws, &ws.stage_seg, (size_t)ws.total_b * ws.cap_n * P));
+        PCP_TRY(ws_alloc(ws, &ws.stage_R, (size_t)ws.total_b * 9));
+    }
+    if (ws.pin_x_bytes < xb) {
+        if (ws.pin_x) cudaFreeHost(ws.pin_x);
+        ws.pin_x = nullptr; ws.pin_x_bytes = 0;
+        PCP_CUDA_OK(cudaMallocHost(reinterpret_cast<void **>(&ws.pin_x), xb));
+        ws.pin_x_bytes = xb;
+    }
+    const size_t ob = (cls_cnt + seg_cnt + r_cnt) * sizeof(float);
+    if (ws.pin_out_bytes < ob) {
+        if (ws.pin_out) cudaFreeHost(ws.pin_out);
+        ws.pin_out = nullptr; ws.pin_out_bytes = 0;
+        PCP_CUDA_OK(cudaMallocHost(reinterpret_cast<void **>(&ws.pin_out), ob));
+        ws.pin_out_bytes = ob;
+    }
+    // pageable -> pinned staging -> device (the pinned hop keeps the H2D copy at full PCIe rate)
+    memcpy(ws.pin_x, h_x, xb);
+    PCP_CUDA_OK(cudaMemcpyAsync(ws.stage_x, ws.pin_x, xb, cudaMemcpyHostToDevice, st));
+    PCP_TRY(pcp_model_forward(m, ws.stage_x, b, n, heads, h_cls ? ws.stage_cls : nullptr, h_seg ? ws.stage_seg : nullptr,
+                              h_R ? ws.stage_R : nullptr, nullptr, nullptr, stream));
+    float *po = ws.pin_out;
+    if (h_cls) PCP_CUDA_OK(cudaMemcpyAsync(po, ws.stage_cls, cls_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (h_seg) PCP_CUDA_OK(cudaMemcpyAsync(po + cls_cnt, ws.stage_seg, seg_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (h_R) PCP_CUDA_OK(cudaMemcpyAsync(po + cls_cnt + seg_cnt, ws.stage_R, r_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+    PCP_CUDA_OK(cudaStreamSynchronize(st));
+    if (h_cls) memcpy(h_cls, po, cls_cnt * sizeof(float));
+    if (h_seg) memcpy(h_seg, po + cls_cnt, seg_cnt * sizeof(float));
+    if (h_R) memcpy(h_R, po + cls_cnt + seg_cnt, r_cnt * sizeof(float));
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_get_pooled(pcp_model *m, int which, int b, float *h_out)
+{
+    PCP_REQUIRE(m && h_out && which >= 0 && which <= 2 && b >= 1 && b <= m->ws.total_b, PCP_ERR_INVALID, "pcp_model_get_pooled: bad arguments");
+    const float *src = which == 0 ? m->ws.g1 : (which == 1 ? m->ws.g2 : m->ws.g3);
+    PCP_CUDA_OK(cudaDeviceSynchronize());
+    PCP_CUDA_OK(cudaMemcpy(h_out, src, (size_t)b * 1024 * sizeof(float), cudaMemcpyDeviceToHost));
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_set_trainable(pcp_model *m, int group, int flag)
+{
+    PCP_REQUIRE(m && group >= 0 && group < 4, PCP_ERR_INVALID, "pcp_model_set_trainable: bad group %d", group);
+    m->trainable[group] = flag != 0;
+    return PCP_OK;
+}

@@ -1,0 +1,118 @@
+"""Host-side operators over the C-ABI (include/pcp.h) — the preprocessing half of the hot path.
+
+Inputs are CUDA torch tensors (device memory plumbing only; every FLOP runs in libpcp_b200.so).
+Names follow the reference: normalisation = PointCloudNormalization (pointnet/PointNet.py:681-706),
+jitter = PointCloudSet._parse_function (pointcloud/PointCloudSet.py:335-337), resize =
+PointCloudSet._adjust_to_input_width (:443-470); FPS / voxel / rotation are the north_star operators.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _ffi
+
+
+def _chk_cloud(x):
+    if not (isinstance(x, torch.Tensor) and x.is_cuda and x.dtype == torch.float32 and x.dim() == 3 and x.shape[-1] == 3):
+        raise TypeError("expected a CUDA float32 tensor of shape (b, n, 3)")
+    return x.contiguous()
+
+
+def normalize(x: torch.Tensor, return_stats: bool = False):
+    """(x - centroid) / max(maxdist, 1e-7) per cloud; optionally (centroid (b,1,3), scale (b,1,1))."""
+    x = _chk_cloud(x)
+    b, n, _ = x.shape
+    y = torch.empty_like(x)
+    cen = torch.empty((b, 1, 3), device=x.device, dtype=torch.float32) if return_stats else None
+    sc = torch.empty((b, 1, 1), device=x.device, dtype=torch.float32) if return_stats else None
+    if b and n:
+        _ffi.check(_ffi.load().pcp_normalize_f32(_ffi.ptr(x), b, n, _ffi.ptr(y), _ffi.ptr(cen), _ffi.ptr(sc), _ffi.stream_ptr()))
+    return (y, (cen, sc)) if return_stats else y
+
+
+def philox_normal(npoints: int, seed: int, offset: int = 0, device="cuda") -> torch.Tensor:
+    out = torch.empty((npoints, 3), device=device, dtype=torch.float32)
+    _ffi.check(_ffi.load().pcp_philox_normal_f32(npoints, seed, offset, _ffi.ptr(out), _ffi.stream_ptr()))
+    return out
+
+
+def jitter(x: torch.Tensor, stdev_m, seed: int = 0, offset: int = 0, noise: torch.Tensor | None = None) -> torch.Tensor:
+    """x + N(0,1) * stdev_axis.  noise=None draws Philox noise indexed by global point id + offset."""
+    x = _chk_cloud(x)
+    sd = np.ascontiguousarray(np.asarray(stdev_m, np.float32).reshape(3))
+    y = torch.empty_like(x)
+    if noise is not None:
+        noise = noise.contiguous()
+        assert noise.shape == x.shape and noise.dtype == torch.float32 and noise.is_cuda
+    _ffi.check(_ffi.load().pcp_jitter_f32(_ffi.ptr(x), x.shape[0] * x.shape[1], _ffi.fptr(sd), seed, offset,
+                                          _ffi.ptr(noise), _ffi.ptr(y), _ffi.stream_ptr()))
+    return y
+
+
+def rotate(x: torch.Tensor, R: torch.Tensor) -> torch.Tensor:
+    """y = x . R^T per cloud; R (b,3,3)."""
+    x = _chk_cloud(x)
+    R = R.to(device=x.device, dtype=torch.float32).contiguous()
+    assert R.shape == (x.shape[0], 3, 3)
+    y = torch.empty_like(x)
+    _ffi.check(_ffi.load().pcp_rotate_f32(_ffi.ptr(x), x.shape[0], x.shape[1], _ffi.ptr(R), _ffi.ptr(y), _ffi.stream_ptr()))
+    return y
+
+
+def farthest_point_sample(x: torch.Tensor, s: int, start: int = 0) -> torch.Tensor:
+    """(b, n, 3) -> (b, s) int32 indices, bit-exact with oracle/sampling.py:fps."""
+    x = _chk_cloud(x)
+    b, n, _ = x.shape
+    idx = torch.empty((b, s), device=x.device, dtype=torch.int32)
+    _ffi.check(_ffi.load().pcp_fps_f32(_ffi.ptr(x), b, n, s, start, _ffi.ptr(idx), _ffi.stream_ptr()))
+    return idx
+
+
+def gather_points(x: torch.Tensor, idx: torch.Tensor, labels: torch.Tensor | None = None):
+    x = _chk_cloud(x)
+    b, n, _ = x.shape
+    idx = idx.contiguous()
+    s = idx.shape[1]
+    out = torch.empty((b, s, 3), device=x.device, dtype=torch.float32)
+    lo = None
+    if labels is not None:
+        labels = labels.to(torch.int32).contiguous()
+        lo = torch.empty((b, s), device=x.device, dtype=torch.int32)
+    _ffi.check(_ffi.load().pcp_gather_points_f32(_ffi.ptr(x), _ffi.ptr(labels), b, n, _ffi.ptr(idx), s, _ffi.ptr(out),
+                                                 _ffi.ptr(lo), _ffi.stream_ptr()))
+    return (out, lo) if labels is not None else out
+
+
+def resize_to_width(x: torch.Tensor, n_valid: torch.Tensor, width: int, seed: int = 0, labels: torch.Tensor | None = None):
+    """_adjust_to_input_width on the device: x (b, n_max, 3) with n_valid[c] real points per cloud."""
+    x = _chk_cloud(x)
+    b, nmax, _ = x.shape
+    nv = n_valid.to(device=x.device, dtype=torch.int32).contiguous()
+    y = torch.empty((b, width, 3), device=x.device, dtype=torch.float32)
+    lo = None
+    if labels is not None:
+        labels = labels.to(torch.int32).contiguous()
+        lo = torch.empty((b, width), device=x.device, dtype=torch.int32)
+    _ffi.check(_ffi.load().pcp_resize_to_width_f32(_ffi.ptr(x), _ffi.ptr(labels), b, nmax, _ffi.ptr(nv), width, seed,
+                                                   _ffi.ptr(y), _ffi.ptr(lo), _ffi.stream_ptr()))
+    return (y, lo) if labels is not None else y
+
+
+def voxel_downsample(x: torch.Tensor, voxel: float, origin=None):
+    """Voxel-grid downsample: returns (centroids (b, n, 3) padded, counts (b, n) int32, nvox (b,) int32)."""
+    x = _chk_cloud(x)
+    b, n, _ = x.shape
+    lib = _ffi.load()
+    nbytes = C.c_size_t(0)
+    _ffi.check(lib.pcp_voxel_workspace_bytes(b, n, C.byref(nbytes)))
+    ws = torch.empty((nbytes.value,), device=x.device, dtype=torch.uint8)
+    out = torch.zeros((b, n, 3), device=x.device, dtype=torch.float32)
+    cnt = torch.zeros((b, n), device=x.device, dtype=torch.int32)
+    nv = torch.zeros((b,), device=x.device, dtype=torch.int32)
+    org = None if origin is None else np.ascontiguousarray(np.asarray(origin, np.float32).reshape(3))
+    _ffi.check(lib.pcp_voxel_f32(_ffi.ptr(x), b, n, _ffi.fptr(org), float(voxel), _ffi.ptr(out), _ffi.ptr(cnt), _ffi.ptr(nv),
+                                 _ffi.ptr(ws), nbytes.value, _ffi.stream_ptr()))
+    return out, cnt, nv
