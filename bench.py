@@ -1,0 +1,289 @@
+#!/usr/bin/env python
+"""bench.py — the measurement contract.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Metric (BASELINE.json): PointNet clouds/sec at 1024 points per cloud (classification inference,
+full network with both T-Nets) — whole-job aggregate over N GPUs; FPS downsampling Mpts/s is
+reported beside it in the same JSON line ("fps").  A step = one pass of the hot path over one
+batch of `clouds_per_step` synthetic clouds per GPU (the reference's C1 batch of 32 is reported
+separately as "batch32" — at 32 clouds the pass is launch-latency bound, not a throughput figure).
+
+  value      device-resident inputs, CUDA-event timed, max over ranks
+  e2e        the same metric through the reference-facing API (PointNet.__call__ on HOST arrays ->
+             pcp_model_predict_host): pinned H2D of the step's clouds + forward + D2H of the outputs
+  roofline   the fused tcgen05 chain kernel: algorithmic FLOPs / CUDA-event time of its launches
+  cpu_baseline / --impl reference
+             oracle/pointnet_torch.py (PyTorch CPU fp32 restatement of the reference's TensorFlow
+             graph — TensorFlow itself cannot be installed here) on all host cores, bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+N_POINTS = 1024
+C_CLASSES, P_PARTS = 23, 12
+# algorithmic MACs: trunk per point, small-M per cloud, hoisted seg head
+MAC_TRUNK_PT = 434_569
+MAC_SMALL_CLOUD = 3_022_848
+MAC_SEG_PT, MAC_SEG_CLOUD = 214_528, 524_288
+
+
+def flops_per_cloud(n, seg=False):
+    f = 2 * (MAC_TRUNK_PT * n + MAC_SMALL_CLOUD)
+    if seg:
+        f += 2 * (MAC_SEG_PT * n + MAC_SEG_CLOUD)
+    return f
+
+
+def load_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"], "bf16_tflops_sustained": d.get("bf16_tflops_sustained"),
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i].lower().startswith("active") for r in self.rows)]
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm)}
+
+
+def cpu_reference_rate(sample_clouds, steps, warmup, threads):
+    """Reference arm / cpu_baseline: the PyTorch-CPU restatement of the reference graph (all outputs,
+    like PointNet.call) on `threads` host threads.  Returns clouds/s and ms per step."""
+    from oracle import pointnet_numpy as onp
+    from oracle import pointnet_torch as opt
+    from tests import synth
+    torch.set_num_threads(threads)
+    p = opt.to_torch(onp.make_params(C_CLASSES, P_PARTS, seed=7))
+    x = torch.from_numpy(synth.gaussian_clouds(1001, sample_clouds, N_POINTS))
+    with torch.no_grad():
+        for _ in range(warmup):
+            opt.forward(x, p)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            opt.forward(x, p)
+        dt = (time.perf_counter() - t0) / steps
+    return sample_clouds / dt, dt * 1e3
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sample = 64
+    rate, ms = cpu_reference_rate(sample, max(1, args.steps), max(1, args.warmup), cores)
+    line = {
+        "impl": "reference", "metric": "pointnet_clouds_per_sec_1024pts", "value": rate, "unit": "clouds/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C1: PointNet inference, 1024 pts/cloud, full net (T-Nets on), all outputs (cls+seg+R) as PointNet.call returns",
+                   "clouds_per_step": sample, "points": N_POINTS, "classes": C_CLASSES, "parts": P_PARTS},
+        "cpu_baseline": {"value": rate, "unit": "clouds/s", "cores": cores, "kind": "port",
+                         "sample": f"{sample} clouds x {N_POINTS} pts per step, oracle/pointnet_torch.py (PyTorch CPU fp32 restatement; TensorFlow not installable here)"},
+        "e2e": {"value": rate, "unit": "clouds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--clouds", type=int, default=4096, help="clouds per GPU per step")
+    ap.add_argument("--skip-extras", action="store_true", help="skip fps / batch32 / all-outputs / cpu baseline (profiling runs)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from oracle import pointnet_numpy as onp          # weights generator only (synthetic, seeded)
+    from pointcloudprocessing_b200 import _ffi, ops
+    from pointcloudprocessing_b200.pointnet import PointNet
+    from tests import synth
+
+    lib = _ffi.load()
+    peaks = load_peaks()
+    W = max(3, args.warmup)
+    K = args.steps
+    B = args.clouds
+    model = PointNet(C_CLASSES, P_PARTS, 0.3, 42, precision="bf16")
+    model.set_weights_dict(onp.make_params(C_CLASSES, P_PARTS, seed=7))
+
+    # inputs: NBUF distinct device batches cycled so the working set (NBUF x 50 MB) exceeds the 126 MB L2
+    NBUF = 4
+    rng_seed = 1001 + 17 * rank
+    base = synth.gaussian_clouds(rng_seed, min(B, 512), N_POINTS)
+    reps = (B + base.shape[0] - 1) // base.shape[0]
+    host = np.concatenate([base] * reps, 0)[:B]
+    xs = []
+    for i in range(NBUF):
+        xs.append(torch.from_numpy(np.roll(host, i * 7, axis=0).copy()).to(dev))
+    pinned = [torch.from_numpy(np.roll(host, i * 7, axis=0).copy()).pin_memory() for i in range(2)]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warm):
+        for i in range(warm):
+            fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps
+
+    # ---- headline: device-resident inputs ----
+    def step_dev(i):
+        model(xs[i % NBUF], heads=("cls",))
+
+    sampler = ClockSampler(local_rank)
+    _ffi.check(lib.pcp_model_enable_timing(model._handle, 0))
+    timed(step_dev, 2, W)                                # warm-up outside the clock sample
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.pcp_launch_count()
+    _ffi.check(lib.pcp_model_enable_timing(model._handle, 1))
+    ms_step = timed(step_dev, K, 0)
+    chain_ms, chain_n = C.c_float(), C.c_int()
+    _ffi.check(lib.pcp_model_chain_time(model._handle, C.byref(chain_ms), C.byref(chain_n)))
+    _ffi.check(lib.pcp_model_enable_timing(model._handle, 0))
+    launches = int(lib.pcp_launch_count() - launches0)
+    clocks = sampler.stop() if rank == 0 else None
+    value = world * B / (ms_step * 1e-3)
+
+    # ---- e2e: host buffers through the public API, H2D + forward + D2H inside the timed region ----
+    def step_host(i):
+        model(pinned[i % 2].numpy(), heads=("cls",))
+
+    ms_e2e = timed(step_host, max(3, K // 2), 2)
+    e2e_value = world * B / (ms_e2e * 1e-3)
+    h2d = B * N_POINTS * 3 * 4
+    d2h = B * C_CLASSES * 4 + B * 9 * 4
+
+    extras = {}
+    if not args.skip_extras:
+        # all three outputs, as the reference's PointNet.call always computes them
+        def step_all(i):
+            model(xs[i % NBUF][:1024])
+        ms_all = timed(step_all, max(3, K // 4), 2)
+        extras["all_outputs"] = {"value": world * 1024 / (ms_all * 1e-3), "unit": "clouds/s", "clouds_per_step": 1024,
+                                 "note": "cls + seg + R; segmentation head still on the fp32 CUDA-core path this round"}
+        x32 = xs[0][:32].contiguous()
+        ms32 = timed(lambda i: model(x32, heads=("cls",)), 50, 10)
+        extras["batch32"] = {"value": world * 32 / (ms32 * 1e-3), "unit": "clouds/s", "ms_per_batch": ms32,
+                             "note": "BASELINE config 1 batch (32 x 1024): launch-latency bound"}
+        # FPS (BASELINE config 2): 64 x 100 000 -> 1024
+        scans = torch.from_numpy(synth.lidar_scans(2002, 64, 100_000)).to(dev)
+        ms_fps = timed(lambda i: ops.farthest_point_sample(scans, 1024), 3, 1)
+        extras["fps"] = {"metric": "fps_downsampling_mpts_per_sec", "value": world * 64 * 100_000 / (ms_fps * 1e-3) / 1e6, "unit": "Mpts/s",
+                         "ms_per_step": ms_fps, "config": "C2: 64 x 100000 -> 1024, register/cluster resident",
+                         "effective_GBps": 64 * 1024 * 100_000 * 20 / (ms_fps * 1e-3) / 1e9,
+                         "effective_frac_of_hbm": 64 * 1024 * 100_000 * 20 / (ms_fps * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                         "note": "effective = 20 B per point-distance update (SURVEY §8d); on-chip resident, may exceed 1.0"}
+        del scans
+
+    if rank == 0:
+        # roofline of the dominant kernel (chain_kernel: 3 launches per forward)
+        chain_flops = 2.0 * MAC_TRUNK_PT * N_POINTS * B * K                     # algorithmic FLOPs of all timed chain launches
+        achieved = chain_flops / (chain_ms.value * 1e-3) / 1e12 if chain_ms.value > 0 else None
+        peak = peaks["bf16_tflops_sustained"] or peaks["bf16_tflops"]
+        roofline = {"bound": "tensor", "kernel": "chain_kernel (tcgen05)", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                    "frac": (achieved / peak) if achieved else None, "traffic": None,
+                    "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)",
+                    "launches": chain_n.value, "kernel_share_of_step": chain_ms.value / (ms_step * K) if ms_step > 0 else None,
+                    "algorithmic": f"2*{MAC_TRUNK_PT} FLOP/point x {N_POINTS} pts x {B} clouds per 3 launches"}
+        cores = os.cpu_count() or 1
+        cpu = None
+        if not args.skip_extras:
+            rate, ms_cpu = cpu_reference_rate(64, 3, 1, cores)
+            cpu = {"value": rate, "unit": "clouds/s", "cores": cores, "kind": "port",
+                   "sample": "64 clouds x 1024 pts x 3 steps, oracle/pointnet_torch.py on all host cores (all outputs)"}
+        line = {
+            "metric": "pointnet_clouds_per_sec_1024pts", "value": value, "unit": "clouds/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "C1-shaped: PointNet classification inference, 1024 pts/cloud, full net (both T-Nets), outputs cls+R",
+                       "clouds_per_step_per_gpu": B, "points": N_POINTS, "classes": C_CLASSES, "parts": P_PARTS, "parallelism": f"batch-shard x{world}, no collective",
+                       "l2": f"{NBUF} rotating input batches ({NBUF * B * N_POINTS * 12 / 1e6:.0f} MB > 126 MB L2)"},
+            "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": e2e_value, "unit": "clouds/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
+            "roofline": roofline, "cpu_baseline": cpu, "gflop_per_cloud": flops_per_cloud(N_POINTS) / 1e9,
+            "model_tflops": value * flops_per_cloud(N_POINTS) / 1e12,
+        }
+        line.update(extras)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -62,7 +62,8 @@ int pcp_stream_sync(pcp_stream stream);
 
 /* PointCloudNormalization.call (pointnet/PointNet.py:691-706): per cloud centroid, centre,
  * max distance, scale = max(maxdist, 1e-7), divide.  x,y: (b, n, 3) f32 contiguous.
- * d_centroid (b*3) and d_scale (b) may be NULL.  One HBM read + one write (24 B/point). */
+ * d_centroid (b*3) and d_scale (b) may be NULL; d_y may be NULL when both statistics are
+ * requested (statistics-only pass).  One HBM read + one write (24 B/point). */
 int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale,
                       pcp_stream stream);
 
@@ -155,6 +156,17 @@ int pcp_model_predict_host(pcp_model *m, const float *h_x, int b, int64_t n, uin
 /* intermediate pooled features of the last forward: which = 0 input T-Net, 1 feature T-Net,
  * 2 global features; (b,1024) f32 copied to the host (tests). */
 int pcp_model_get_pooled(pcp_model *m, int which, int b, float *h_out);
+
+/* Measurement hook (bench.py's roofline): when enabled, every fused chain-kernel launch is
+ * bracketed by CUDA events on its own stream; pcp_model_chain_time drains them and returns the
+ * summed device time and the launch count since the last call. */
+int pcp_model_enable_timing(pcp_model *m, int flag);
+int pcp_model_chain_time(pcp_model *m, float *ms_total, int *launches);
+
+/* Tensor-core self-test (used by tests only): D (128 x N) = A (128 x K) . B (N x K)^T through one
+ * tcgen05.mma chain with bf16-rounded operands; validates the shared-memory operand image, the
+ * descriptors and the TMEM read-back in isolation.  Host pointers, synchronous. */
+int pcp_selftest_umma(const float *h_a, const float *h_b, int N, int K, float *h_d);
 
 /* ---- training (pointnet_train.py:310-351) ---- */
 #define PCP_GROUP_SHARED 0

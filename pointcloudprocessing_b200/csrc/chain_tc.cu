@@ -1,8 +1,626 @@
-// chain_tc.cu — tcgen05 / TMEM fused per-point MLP chains (bf16 operands, fp32 accumulate).
+// chain_tc.cu — the per-point MLP chains of PointNet (pointnet/PointNet.py:215-248, TNet.call :423-429)
+// as ONE fused tcgen05 kernel per chain: raw points -> normalise -> 3->64 (CUDA-core FMA) ->
+// 64->64/128 mid layers (tcgen05.mma, accumulators in TMEM, BN-folded bias + ReLU epilogue writing the
+// next layer's bf16 operand straight into swizzled shared memory) -> 128->1024 final layer evaluated
+// TRANSPOSED (D[channel, point] = W3^T . H2^T) so the global max-pool over points is a pure in-thread
+// FMNMX over TMEM columns -> per-cloud atomicMax.  No per-point activation ever reaches HBM: the chain
+// reads 12 B/point and writes 4 KB/cloud.
+//
+// Warp roles (320 threads, 1 CTA/SM, persistent over a contiguous range of 128-point tiles):
+//   warps 0-3  front: normalise + L0 + mid-layer epilogues (TMEM -> regs -> bf16 -> smem)
+//   warps 4-7  final epilogue: TMEM -> running per-channel max -> atomicMax
+//   warp  8    MMA issuer (one thread): interleaves mid-layer MMAs of tile i+1 with the final layer of tile i
+//   warp  9    loader (one thread): weight images via cp.async.bulk (TMA engine) + TMEM allocation
+#include <cstring>
+#include <vector>
+
+#include "gemm_simt.cuh"
 #include "model.cuh"
+#include "umma.cuh"
+
 namespace pcp {
-int model_forward_bf16(pcp_model *, const float *, int, int64_t, uint32_t, float *, float *, float *, float *, float *, cudaStream_t)
-{ set_error("bf16 path not built yet"); return PCP_ERR_UNSUPPORTED; }
-int model_prepare_bf16(pcp_model *) { set_error("bf16 path not built yet"); return PCP_ERR_UNSUPPORTED; }
-void model_destroy_bf16(pcp_model *) {}
+
+using namespace umma;
+
+constexpr int kTP = 128;            // points per tile
+constexpr int kChainThreads = 320;
+constexpr int kRing = 4;            // W3 ring slots (16 KB each: 128 channels x 64 K)
+constexpr uint32_t kW3Tile = 16384;
+
+// shared-memory carve (bytes from a 1024-aligned base)
+constexpr uint32_t kOffA0 = 0, kOffA1 = 16384, kOffH2 = 32768, kOffWM = 98304, kOffWC = 131072, kOffW3 = 147456;
+constexpr uint32_t kChainSmem = kOffW3 + kRing * kW3Tile + 1024;   // + alignment slack
+__device__ __forceinline__ uint32_t wm_slot(int s) { return s == 0 ? 0u : (s == 1 ? 8192u : 16384u); }
+
+struct ChainParams {
+    const float *x; int64_t n; int b;
+    const float *centroid, *scale;        // (b,3), (b)
+    const float *R;                       // (b,9) or nullptr: X = pcn @ R before L0 (PointNet.py:207)
+    const float *l0;                      // [64][4]: w0, w1, w2, t (BN folded)
+    int nmid;                             // mid layers (all K = 64)
+    int mid_n[3];                         // output widths; the last one is 128
+    int mid_slot[3];                      // smem weight slot
+    const uint8_t *mid_w[3];              // bf16 SW128 images (rows = mid_n, K = 64)
+    int64_t mid_cloud_stride[3];          // bytes between clouds for a per-cloud layer, 0 = shared
+    const float *mid_t[3];
+    const uint8_t *w3;                    // 16 tiles (j = channel block, h = K half) of 16 KB
+    const float *t3;                      // 1024
+    float *gmax;                          // (b,1024), zero-initialised
+    int tiles_per_cloud;
+    int64_t total_tiles;
+};
+
+struct ChainShared {
+    uint64_t a_full, mid_full, wmid_full;
+    uint64_t h2_full[2], h2_empty[2], acc_full[2], acc_empty[2], wc_full[2], wc_empty[2];
+    uint64_t w3_full[kRing], w3_empty[kRing];
+    uint32_t tmem_base;
+    alignas(16) float l0[64 * 4];
+    alignas(16) float mid_t[3][128];
+};
+
+__global__ void __launch_bounds__(kChainThreads, 1)
+chain_kernel(const ChainParams p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ ChainShared sh;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t *A0 = base + kOffA0, *A1 = base + kOffA1, *H2 = base + kOffH2, *WM = base + kOffWM, *WC = base + kOffWC, *W3 = base + kOffW3;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int64_t t_begin = (int64_t)blockIdx.x * p.total_tiles / gridDim.x;
+    const int64_t t_end = (int64_t)(blockIdx.x + 1) * p.total_tiles / gridDim.x;
+    const int64_t ntiles = t_end - t_begin;
+
+    if (tid == 0) {
+        mbar_init(&sh.a_full, 128); mbar_init(&sh.mid_full, 1); mbar_init(&sh.wmid_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&sh.h2_full[i], 128); mbar_init(&sh.h2_empty[i], 1);
+            mbar_init(&sh.acc_full[i], 1); mbar_init(&sh.acc_empty[i], 128);
+            mbar_init(&sh.wc_full[i], 1); mbar_init(&sh.wc_empty[i], 1);
+        }
+        for (int i = 0; i < kRing; ++i) { mbar_init(&sh.w3_full[i], 1); mbar_init(&sh.w3_empty[i], 1); }
+        fence_barrier_init();
+    }
+    if (warp == 9) tmem_alloc(&sh.tmem_base, 512);
+    for (int i = tid; i < 256; i += kChainThreads) sh.l0[i] = p.l0[i];
+    for (int l = 0; l < p.nmid; ++l)
+        for (int i = tid; i < p.mid_n[l]; i += kChainThreads) sh.mid_t[l][i] = p.mid_t[l][i];
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = sh.tmem_base;
+
+    if (warp < 4) {
+        // =========================== front: L0 + mid-layer epilogues ===========================
+        const int row = tid;
+        uint32_t mid_phase = 0;
+        for (int64_t it = 0; it < ntiles; ++it) {
+            const int64_t t = t_begin + it;
+            const int64_t cloud = t / p.tiles_per_cloud;
+            const int64_t pi = min((t % p.tiles_per_cloud) * (int64_t)kTP + row, p.n - 1);   // clamp: duplicates do not change a max
+            const float *px = p.x + (cloud * p.n + pi) * 3;
+            const float cx = __ldg(p.centroid + cloud * 3), cy = __ldg(p.centroid + cloud * 3 + 1), cz = __ldg(p.centroid + cloud * 3 + 2);
+            const float sc = __ldg(p.scale + cloud);
+            float q0 = __fdiv_rn(__fsub_rn(__ldg(px), cx), sc), q1 = __fdiv_rn(__fsub_rn(__ldg(px + 1), cy), sc),
+                  q2 = __fdiv_rn(__fsub_rn(__ldg(px + 2), cz), sc);                             // PointNet.py:691-706
+            if (p.R) {
+                const float *R = p.R + cloud * 9;
+                const float r0 = q0 * __ldg(R) + q1 * __ldg(R + 3) + q2 * __ldg(R + 6);
+                const float r1 = q0 * __ldg(R + 1) + q1 * __ldg(R + 4) + q2 * __ldg(R + 7);
+                const float r2 = q0 * __ldg(R + 2) + q1 * __ldg(R + 5) + q2 * __ldg(R + 8);
+                q0 = r0; q1 = r1; q2 = r2;
+            }
+            // L0: 3 -> 64 on CUDA cores (K = 3 is not tensor-core work), BN folded, ReLU, bf16 -> A0
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float o[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const float4 w = *reinterpret_cast<const float4 *>(&sh.l0[(c * 8 + e) * 4]);
+                    const float v = fmaf(q2, w.z, fmaf(q1, w.y, fmaf(q0, w.x, w.w)));
+                    o[e] = v > 0.f ? v : 0.f;
+                }
+                *reinterpret_cast<uint4 *>(A0 + sw128_offset(128, row, c * 8)) =
+                    make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+            }
+            fence_proxy_async();
+            mbar_arrive(&sh.a_full);
+            for (int l = 0; l < p.nmid; ++l) {
+                mbar_wait(&sh.mid_full, mid_phase, 1);
+                mid_phase ^= 1;
+                tc_fence_after();
+                const bool last = (l == p.nmid - 1);
+                uint8_t *out = last ? H2 + (it & 1) * 32768 : ((l & 1) ? A0 : A1);
+                if (last && it >= 2) mbar_wait(&sh.h2_empty[it & 1], ((it >> 1) - 1) & 1, 2);
+                const int N = p.mid_n[l];
+                for (int c0 = 0; c0 < N; c0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        float o[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const float f = __uint_as_float(v[c * 8 + e]) + sh.mid_t[l][c0 + c * 8 + e];
+                            o[e] = f > 0.f ? f : 0.f;
+                        }
+                        *reinterpret_cast<uint4 *>(out + sw128_offset(128, row, c0 + c * 8)) =
+                            make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+                    }
+                }
+                tc_fence_before();
+                fence_proxy_async();
+                mbar_arrive(last ? &sh.h2_full[it & 1] : &sh.a_full);
+            }
+        }
+    } else if (warp < 8) {
+        // =========================== final epilogue: max over points ===========================
+        const int ch = tid - 128;
+        const uint32_t lane_base = (uint32_t)((warp - 4) * 32) << 16;
+        float mx[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) mx[j] = -3.0e38f;
+        int64_t cur_cloud = -1;
+        uint64_t g = 0;
+        auto flush = [&](int64_t cloud) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float v = mx[j] + __ldg(p.t3 + j * 128 + ch);       // max(relu(x + t)) == relu(max(x) + t)
+                v = v > 0.f ? v : 0.f;
+                atomicMax(reinterpret_cast<unsigned int *>(p.gmax + cloud * 1024 + j * 128 + ch), __float_as_uint(v));
+                mx[j] = -3.0e38f;
+            }
+        };
+        for (int64_t it = 0; it < ntiles; ++it) {
+            const int64_t cloud = (t_begin + it) / p.tiles_per_cloud;
+            if (cloud != cur_cloud) {
+                if (cur_cloud >= 0) flush(cur_cloud);
+                cur_cloud = cloud;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t buf = (uint32_t)(g & 1);
+                mbar_wait(&sh.acc_full[buf], (uint32_t)((g >> 1) & 1), 3);
+                tc_fence_after();
+                float m = mx[j];
+#pragma unroll
+                for (int c0 = 0; c0 < 128; c0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld32(tmem + lane_base + 128 + buf * 128 + c0, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) m = fmaxf(m, __uint_as_float(v[e]));
+                }
+                tc_fence_before();
+                mbar_arrive(&sh.acc_empty[buf]);
+                mx[j] = m;
+                ++g;
+            }
+        }
+        if (cur_cloud >= 0) flush(cur_cloud);
+    } else if (warp == 8) {
+        // =========================== MMA issuer ===========================
+        if (lane == 0 && ntiles > 0) {
+            mbar_wait(&sh.wmid_full, 0, 4);
+            int64_t mid_it = 0, fin_it = 0;
+            int mid_l = 0, fin_j = 0, fin_h = 0;
+            uint32_t a_cnt = 0;
+            uint64_t g = 0, r = 0;
+            bool h2_ok = false, acc_ok = false;
+            const uint32_t idesc_fin = make_idesc_bf16(128, 128);
+            long long spin_t0 = clock64();
+            while (mid_it < ntiles || fin_it < ntiles) {
+                // mid-layer work first (it is on the critical path of the next tile), but never block on it:
+                // the per-cloud weight image of tile k is only requested once the W3 ring of tile k-2 has
+                // been issued, so a blocking wait here could starve the ring and deadlock.
+                bool mid_ready = mid_it < ntiles && mbar_test(&sh.a_full, a_cnt & 1);
+                const bool percloud = mid_ready && p.mid_cloud_stride[mid_l] != 0;
+                if (percloud) mid_ready = mbar_test(&sh.wc_full[mid_it & 1], (uint32_t)((mid_it >> 1) & 1));
+                if (mid_ready) {
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32((mid_l & 1) ? A1 : A0);
+                    const uint32_t b_addr = smem_u32(percloud ? WC + (mid_it & 1) * 8192 : WM + wm_slot(p.mid_slot[mid_l]));
+                    const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.mid_n[mid_l]);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) mma_bf16_ss(tmem, make_sdesc(a_addr + k * 32), make_sdesc(b_addr + k * 32), idesc, k > 0);
+                    mma_commit(&sh.mid_full);
+                    if (percloud) mma_commit(&sh.wc_empty[mid_it & 1]);
+                    ++a_cnt;
+                    if (++mid_l == p.nmid) { mid_l = 0; ++mid_it; }
+                    spin_t0 = clock64();
+                    continue;
+                }
+                if (fin_it < ntiles) {
+                    const int s = (int)(fin_it & 1);
+                    bool go = true;
+                    if (!h2_ok) { h2_ok = mbar_test(&sh.h2_full[s], (uint32_t)((fin_it >> 1) & 1)); go = h2_ok; }
+                    const uint32_t buf = (uint32_t)(g & 1);
+                    if (go && !acc_ok) { acc_ok = (g < 2) || mbar_test(&sh.acc_empty[buf], (uint32_t)(((g >> 1) - 1) & 1)); go = acc_ok; }
+                    const uint32_t slot = (uint32_t)(r % kRing);
+                    if (go) go = mbar_test(&sh.w3_full[slot], (uint32_t)((r / kRing) & 1));
+                    if (go) {
+                        tc_fence_after();
+                        const uint32_t a_addr = smem_u32(W3 + slot * kW3Tile);
+                        const uint32_t b_addr = smem_u32(H2 + s * 32768 + fin_h * 16384);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            mma_bf16_ss(tmem + 128 + buf * 128, make_sdesc(a_addr + k * 32), make_sdesc(b_addr + k * 32), idesc_fin, (fin_h | k) > 0);
+                        mma_commit(&sh.w3_empty[slot]);
+                        ++r;
+                        if (++fin_h == 2) {
+                            fin_h = 0;
+                            mma_commit(&sh.acc_full[buf]);
+                            ++g; acc_ok = false;
+                            if (++fin_j == 8) { fin_j = 0; mma_commit(&sh.h2_empty[s]); ++fin_it; h2_ok = false; }
+                        }
+                        spin_t0 = clock64();
+                        continue;
+                    }
+                }
+                if (clock64() - spin_t0 > 4000000000ll) {
+                    g_mbar_timeout_info[0] = 0xdead0100u; g_mbar_timeout_info[1] = blockIdx.x;
+                    g_mbar_timeout_info[2] = (unsigned)mid_it; g_mbar_timeout_info[3] = (unsigned)fin_it;
+                    __threadfence_system();
+                    __trap();
+                }
+            }
+        }
+    } else {
+        // =========================== loader ===========================
+        if (lane == 0 && ntiles > 0) {
+            uint32_t bytes = 0;
+            for (int l = 0; l < p.nmid; ++l) if (p.mid_cloud_stride[l] == 0) bytes += (uint32_t)p.mid_n[l] * 128u;
+            mbar_arrive_expect_tx(&sh.wmid_full, bytes);
+            for (int l = 0; l < p.nmid; ++l)
+                if (p.mid_cloud_stride[l] == 0) bulk_g2s(WM + wm_slot(p.mid_slot[l]), p.mid_w[l], (uint32_t)p.mid_n[l] * 128u, &sh.wmid_full);
+            int pc_layer = -1;
+            for (int l = 0; l < p.nmid; ++l) if (p.mid_cloud_stride[l] != 0) pc_layer = l;
+            auto issue_wc = [&](int64_t it) {
+                if (pc_layer < 0) return;
+                if (it >= 2) mbar_wait(&sh.wc_empty[it & 1], (uint32_t)(((it >> 1) - 1) & 1), 6);
+                const int64_t cloud = (t_begin + it) / p.tiles_per_cloud;
+                mbar_arrive_expect_tx(&sh.wc_full[it & 1], 8192);
+                bulk_g2s(WC + (it & 1) * 8192, p.mid_w[pc_layer] + cloud * p.mid_cloud_stride[pc_layer], 8192, &sh.wc_full[it & 1]);
+            };
+            issue_wc(0);
+            if (ntiles > 1) issue_wc(1);
+            uint64_t r = 0;
+            for (int64_t it = 0; it < ntiles; ++it) {
+                for (int gi = 0; gi < 16; ++gi) {
+                    const uint32_t slot = (uint32_t)(r % kRing);
+                    if (r >= kRing) mbar_wait(&sh.w3_empty[slot], (uint32_t)(((r / kRing) - 1) & 1), 7);
+                    mbar_arrive_expect_tx(&sh.w3_full[slot], kW3Tile);
+                    bulk_g2s(W3 + slot * kW3Tile, p.w3 + (size_t)gi * kW3Tile, kW3Tile, &sh.w3_full[slot]);
+                    ++r;
+                }
+                if (it + 2 < ntiles) issue_wc(it + 2);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc(tmem, 512);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Self-test GEMM: D (128 x N) = A (128 x K) . B (N x K)^T from pre-packed SW128 images, one CTA.
+// Validates descriptors / swizzle / TMEM mapping in isolation (tests/test_gpu_umma.py).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1)
+umma_selftest_kernel(const uint8_t *__restrict__ a_img, const uint8_t *__restrict__ b_img, int N, int K, float *__restrict__ d)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full, done;
+    __shared__ uint32_t tmem_base;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const uint32_t a_bytes = 128u * K * 2u, b_bytes = (uint32_t)N * K * 2u;
+    uint8_t *A = base, *B = base + a_bytes;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (tid == 0) { mbar_init(&full, 1); mbar_init(&done, 1); fence_barrier_init(); }
+    if (warp == 0) tmem_alloc(&tmem_base, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base;
+    if (tid == 0) {
+        mbar_arrive_expect_tx(&full, a_bytes + b_bytes);
+        bulk_g2s(A, a_img, a_bytes, &full);
+        bulk_g2s(B, b_img, b_bytes, &full);
+        mbar_wait(&full, 0, 8);
+        tc_fence_after();
+        const uint32_t idesc = make_idesc_bf16(128, (uint32_t)N);
+        for (int kb = 0; kb < K / 64; ++kb)
+            for (int k = 0; k < 4; ++k)
+                mma_bf16_ss(tmem, make_sdesc(smem_u32(A) + kb * (128 * 128) + k * 32),
+                            make_sdesc(smem_u32(B) + kb * (N * 128) + k * 32), idesc, (kb | k) > 0);
+        mma_commit(&done);
+    }
+    mbar_wait(&done, 0, 9);
+    tc_fence_after();
+    for (int c0 = 0; c0 < N; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+        tmem_ld_wait();
+        for (int e = 0; e < 32; ++e) d[(size_t)tid * N + c0 + e] = __uint_as_float(v[e]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+static inline uint16_t f2bf(float f)
+{
+    uint32_t u; memcpy(&u, &f, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+
+// W: (cin x cout) row-major fp32; image rows = cout, K = cin (cin multiple of 64)
+static void pack_b_image(const float *W, int cin, int cout, std::vector<uint16_t> &img)
+{
+    img.assign((size_t)cin * cout, 0);
+    for (int r = 0; r < cout; ++r)
+        for (int k = 0; k < cin; ++k) img[sw128_offset((uint32_t)cout, (uint32_t)r, (uint32_t)k) / 2] = f2bf(W[(size_t)k * cout + r]);
+}
+
+// final layer 128 -> 1024: 16 tiles (j, h): rows = channels j*128.., K = inputs h*64..
+static void pack_w3_image(const float *W, std::vector<uint16_t> &img)
+{
+    img.assign((size_t)128 * 1024, 0);
+    for (int j = 0; j < 8; ++j)
+        for (int h = 0; h < 2; ++h) {
+            uint16_t *tile = img.data() + (size_t)(j * 2 + h) * (kW3Tile / 2);
+            for (int r = 0; r < 128; ++r)
+                for (int k = 0; k < 64; ++k) tile[sw128_offset(128, (uint32_t)r, (uint32_t)k) / 2] = f2bf(W[(size_t)(h * 64 + k) * 1024 + j * 128 + r]);
+        }
+}
+
+struct TcChain {
+    uint8_t *mid_w[3] = {nullptr, nullptr, nullptr};
+    const float *mid_t[3] = {nullptr, nullptr, nullptr};
+    int mid_n[3] = {0, 0, 0};
+    int nmid = 0;
+    uint8_t *w3 = nullptr;
+    const float *t3 = nullptr;
+    float *l0 = nullptr;
+};
+
+struct TcState {
+    TcChain A, B, C;
+    uint8_t *wc = nullptr; size_t wc_clouds = 0;     // per-cloud folded (R64 . W_s2_1) images
+    float *centroid = nullptr, *scale = nullptr; size_t stat_clouds = 0;
+    std::vector<void *> allocs;
+    bool attr_set = false;
+    bool timing = false;                                  // CUDA-event pairs around every chain launch (bench.py roofline)
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> events;
+};
+
+static int dev_upload(TcState *ts, const void *src, size_t bytes, void **dst)
+{
+    PCP_CUDA_OK(cudaMalloc(dst, bytes));
+    ts->allocs.push_back(*dst);
+    PCP_CUDA_OK(cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice));
+    return PCP_OK;
+}
+
+static int build_chain(pcp_model *m, TcState *ts, TcChain &c, int l0_id, const int *mid_ids, int nmid, int fin_id,
+                       const std::vector<float> &fold)
+{
+    const LayerSpec &L0 = m->layers[l0_id];
+    std::vector<float> l0(256);
+    for (int ch = 0; ch < 64; ++ch) {
+        for (int k = 0; k < 3; ++k) l0[ch * 4 + k] = fold[L0.fold_w + (size_t)k * 64 + ch];
+        l0[ch * 4 + 3] = fold[L0.fold_t + ch];
+    }
+    PCP_TRY(dev_upload(ts, l0.data(), l0.size() * 4, reinterpret_cast<void **>(&c.l0)));
+    c.nmid = nmid;
+    std::vector<uint16_t> img;
+    for (int i = 0; i < nmid; ++i) {
+        if (mid_ids[i] < 0) { c.mid_w[i] = nullptr; c.mid_n[i] = 64; c.mid_t[i] = nullptr; continue; }
+        const LayerSpec &L = m->layers[mid_ids[i]];
+        pack_b_image(fold.data() + L.fold_w, L.cin, L.cout, img);
+        PCP_TRY(dev_upload(ts, img.data(), img.size() * 2, reinterpret_cast<void **>(&c.mid_w[i])));
+        c.mid_n[i] = L.cout;
+        c.mid_t[i] = m->d_fold + L.fold_t;
+    }
+    const LayerSpec &F = m->layers[fin_id];
+    pack_w3_image(fold.data() + F.fold_w, img);
+    PCP_TRY(dev_upload(ts, img.data(), img.size() * 2, reinterpret_cast<void **>(&c.w3)));
+    c.t3 = m->d_fold + F.fold_t;
+    return PCP_OK;
+}
+
+void model_destroy_bf16(pcp_model *m)
+{
+    if (!m->tc) return;
+    TcState *ts = reinterpret_cast<TcState *>(m->tc);
+    for (void *p : ts->allocs) cudaFree(p);
+    cudaFree(ts->wc); cudaFree(ts->centroid); cudaFree(ts->scale);
+    delete ts;
+    m->tc = nullptr;
+}
+
+int model_prepare_bf16(pcp_model *m)
+{
+    model_destroy_bf16(m);
+    TcState *ts = new TcState();
+    m->tc = ts;
+    std::vector<float> fold(m->n_fold);
+    PCP_CUDA_OK(cudaMemcpy(fold.data(), m->d_fold, m->n_fold * sizeof(float), cudaMemcpyDeviceToHost));
+    if (!m->desc.vanilla) {
+        const int midA[1] = {L_IT_C2};
+        PCP_TRY(build_chain(m, ts, ts->A, L_IT_C1, midA, 1, L_IT_C3, fold));
+        const int midB[3] = {L_S1_2, L_FT_C1, L_FT_C2};
+        PCP_TRY(build_chain(m, ts, ts->B, L_S1_1, midB, 3, L_FT_C3, fold));
+        const int midC[3] = {L_S1_2, -1, L_S2_2};                       // -1: per-cloud R64 . W(s2_l1_64)
+        PCP_TRY(build_chain(m, ts, ts->C, L_S1_1, midC, 3, L_S2_3, fold));
+        ts->C.mid_t[1] = m->d_fold + m->layers[L_S2_1].fold_t;
+    } else {
+        const int midC[3] = {L_S1_2, L_S2_1, L_S2_2};
+        PCP_TRY(build_chain(m, ts, ts->C, L_S1_1, midC, 3, L_S2_3, fold));
+    }
+    return PCP_OK;
+}
+
+// per-cloud fold: image_b(n, k) = bf16( sum_m R64_b[k][m] * W[m][n] )  —  X_64 . W == X . (R64 . W)  (PointNet.py:228,236)
+__global__ void __launch_bounds__(256)
+fold_r64_kernel(const float *__restrict__ R64, const float *__restrict__ W, uint8_t *__restrict__ img)
+{
+    __shared__ float sW[64 * 64];
+    const int64_t cloud = blockIdx.x;
+    for (int i = threadIdx.x; i < 4096; i += 256) sW[i] = W[i];
+    __syncthreads();
+    const float *R = R64 + cloud * 4096;
+    uint16_t *out = reinterpret_cast<uint16_t *>(img + cloud * 8192);
+    for (int e = threadIdx.x; e < 4096; e += 256) {
+        const int k = e >> 6, n = e & 63;
+        float acc = 0.f;
+#pragma unroll 8
+        for (int mm = 0; mm < 64; ++mm) acc = fmaf(__ldg(R + k * 64 + mm), sW[mm * 64 + n], acc);
+        const __nv_bfloat16 h = __float2bfloat16_rn(acc);
+        out[sw128_offset(64, (uint32_t)n, (uint32_t)k) / 2] = *reinterpret_cast<const uint16_t *>(&h);
+    }
+}
+
+static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, int64_t n, const float *R, const uint8_t *wc,
+                        float *gmax, cudaStream_t st)
+{
+    ChainParams p;
+    memset(&p, 0, sizeof(p));
+    p.x = d_x; p.n = n; p.b = b; p.centroid = ts->centroid; p.scale = ts->scale; p.R = R; p.l0 = c.l0;
+    p.nmid = c.nmid;
+    for (int i = 0; i < c.nmid; ++i) {
+        p.mid_n[i] = c.mid_n[i];
+        p.mid_t[i] = c.mid_t[i];
+        p.mid_w[i] = c.mid_w[i];
+        p.mid_cloud_stride[i] = 0;
+        if (!c.mid_w[i]) { p.mid_w[i] = wc; p.mid_cloud_stride[i] = 8192; }
+        // slot: 8 KB slots 0/1 for 64-row images, the 16 KB slot 2 for the 128-row image
+        p.mid_slot[i] = (c.mid_n[i] == 128) ? 2 : (i == 0 ? 0 : 1);
+    }
+    p.w3 = c.w3; p.t3 = c.t3; p.gmax = gmax;
+    p.tiles_per_cloud = (int)((n + kTP - 1) / kTP);
+    p.total_tiles = (int64_t)p.tiles_per_cloud * b;
+    if (!ts->attr_set) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kChainSmem));
+        ts->attr_set = true;
+    }
+    const int grid = (int)std::min<int64_t>(p.total_tiles, sm_count());
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ts->timing) {
+        PCP_CUDA_OK(cudaEventCreate(&e0)); PCP_CUDA_OK(cudaEventCreate(&e1));
+        PCP_CUDA_OK(cudaEventRecord(e0, st));
+    }
+    chain_kernel<<<grid, kChainThreads, kChainSmem, st>>>(p);
+    PCP_CHECK_LAUNCH();
+    if (ts->timing) {
+        PCP_CUDA_OK(cudaEventRecord(e1, st));
+        ts->events.emplace_back(e0, e1);
+    }
+    return PCP_OK;
+}
+
+int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
+                       float *d_R, float *d_cls_logits, float *d_seg_logits, cudaStream_t st)
+{
+    TcState *ts = reinterpret_cast<TcState *>(m->tc);
+    PCP_REQUIRE(ts, PCP_ERR_STATE, "bf16 path: model not prepared");
+    Workspace &ws = m->ws;
+    const bool full = !m->desc.vanilla;
+    const int C = m->desc.num_classes;
+    if (ts->stat_clouds < (size_t)b) {
+        cudaFree(ts->centroid); cudaFree(ts->scale); cudaFree(ts->wc);
+        ts->centroid = ts->scale = nullptr; ts->wc = nullptr; ts->stat_clouds = 0;
+        PCP_CUDA_OK(cudaMalloc(&ts->centroid, (size_t)b * 3 * sizeof(float)));
+        PCP_CUDA_OK(cudaMalloc(&ts->scale, (size_t)b * sizeof(float)));
+        PCP_CUDA_OK(cudaMalloc(&ts->wc, (size_t)b * 8192));
+        ts->stat_clouds = (size_t)b;
+    }
+    // per-cloud centroid / scale only (the chains normalise on the fly; nothing per-point is written)
+    PCP_TRY(pcp_normalize_f32(d_x, b, n, nullptr, ts->centroid, ts->scale, st));
+    float *Rout = d_R ? d_R : ws.R;
+    PCP_CUDA_OK(cudaMemsetAsync(ws.g3, 0, (size_t)b * 1024 * sizeof(float), st));
+    if (full) {
+        PCP_CUDA_OK(cudaMemsetAsync(ws.g1, 0, (size_t)b * 1024 * sizeof(float), st));
+        PCP_CUDA_OK(cudaMemsetAsync(ws.g2, 0, (size_t)b * 1024 * sizeof(float), st));
+        PCP_TRY(launch_chain(ts, ts->A, d_x, b, n, nullptr, nullptr, ws.g1, st));
+        PCP_TRY(model_tnet_tail(m, 0, ws.g1, b, Rout, st));
+        PCP_TRY(launch_chain(ts, ts->B, d_x, b, n, Rout, nullptr, ws.g2, st));
+        PCP_TRY(model_tnet_tail(m, 1, ws.g2, b, ws.R64, st));
+        fold_r64_kernel<<<b, 256, 0, st>>>(ws.R64, m->d_fold + m->layers[L_S2_1].fold_w, ts->wc);
+        PCP_CHECK_LAUNCH();
+        PCP_TRY(launch_chain(ts, ts->C, d_x, b, n, Rout, ts->wc, ws.g3, st));
+    } else {
+        if (d_R) PCP_TRY(model_eye3(d_R, b, st));
+        PCP_TRY(launch_chain(ts, ts->C, d_x, b, n, nullptr, nullptr, ws.g3, st));
+    }
+    if (heads & PCP_HEAD_CLS) PCP_TRY(model_cls_head(m, ws.g3, b, d_cls, d_cls_logits, st));
+    if (heads & PCP_HEAD_SEG) PCP_TRY(model_seg_head_fp32(m, d_x, b, n, full ? Rout : nullptr, full ? ws.R64 : nullptr, ws.g3, d_seg, d_seg_logits, st));
+    (void)C;
+    return PCP_OK;
+}
+
+}  // namespace pcp
+
+using namespace pcp;
+
+extern "C" int pcp_model_enable_timing(pcp_model *m, int flag)
+{
+    PCP_REQUIRE(m, PCP_ERR_INVALID, "pcp_model_enable_timing: null model");
+    PCP_REQUIRE(m->tc, PCP_ERR_STATE, "pcp_model_enable_timing: bf16 model not prepared");
+    reinterpret_cast<TcState *>(m->tc)->timing = flag != 0;
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_chain_time(pcp_model *m, float *ms_total, int *launches)
+{
+    PCP_REQUIRE(m && ms_total && launches, PCP_ERR_INVALID, "pcp_model_chain_time: null argument");
+    PCP_REQUIRE(m->tc, PCP_ERR_STATE, "pcp_model_chain_time: bf16 model not prepared");
+    TcState *ts = reinterpret_cast<TcState *>(m->tc);
+    float tot = 0.f;
+    for (auto &ev : ts->events) {
+        PCP_CUDA_OK(cudaEventSynchronize(ev.second));
+        float ms = 0.f;
+        PCP_CUDA_OK(cudaEventElapsedTime(&ms, ev.first, ev.second));
+        tot += ms;
+        cudaEventDestroy(ev.first); cudaEventDestroy(ev.second);
+    }
+    *ms_total = tot;
+    *launches = (int)ts->events.size();
+    ts->events.clear();
+    return PCP_OK;
+}
+
+// D (128 x N) = A (128 x K) . B (N x K)^T through tcgen05 (host fp32 in/out; operands rounded to bf16).
+extern "C" int pcp_selftest_umma(const float *h_a, const float *h_b, int N, int K, float *h_d)
+{
+    PCP_REQUIRE(h_a && h_b && h_d && N % 32 == 0 && N >= 32 && N <= 256 && K % 64 == 0 && K >= 64 && K <= 256, PCP_ERR_INVALID,
+                "pcp_selftest_umma: N in {32..256 step 32}, K in {64,128,192,256}");
+    std::vector<uint16_t> ai((size_t)128 * K), bi((size_t)N * K);
+    for (int r = 0; r < 128; ++r) for (int k = 0; k < K; ++k) ai[sw128_offset(128, r, k) / 2] = f2bf(h_a[(size_t)r * K + k]);
+    for (int r = 0; r < N; ++r) for (int k = 0; k < K; ++k) bi[sw128_offset(N, r, k) / 2] = f2bf(h_b[(size_t)r * K + k]);
+    uint8_t *da = nullptr, *db = nullptr; float *dd = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&da, ai.size() * 2)); PCP_CUDA_OK(cudaMalloc(&db, bi.size() * 2)); PCP_CUDA_OK(cudaMalloc(&dd, (size_t)128 * N * 4));
+    PCP_CUDA_OK(cudaMemcpy(da, ai.data(), ai.size() * 2, cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemcpy(db, bi.data(), bi.size() * 2, cudaMemcpyHostToDevice));
+    const size_t smem = ai.size() * 2 + bi.size() * 2 + 1024;
+    PCP_CUDA_OK(cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    umma_selftest_kernel<<<1, 128, smem>>>(da, db, N, K, dd);
+    PCP_CHECK_LAUNCH();
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        unsigned info[4] = {0, 0, 0, 0};
+        cudaMemcpyFromSymbol(info, g_mbar_timeout_info, sizeof(info));
+        set_error("pcp_selftest_umma: %s (timeout info %08x %u %u %u)", cudaGetErrorString(e), info[0], info[1], info[2], info[3]);
+        return PCP_ERR_CUDA;
+    }
+    PCP_CUDA_OK(cudaMemcpy(h_d, dd, (size_t)128 * N * 4, cudaMemcpyDeviceToHost));
+    cudaFree(da); cudaFree(db); cudaFree(dd);
+    return PCP_OK;
 }

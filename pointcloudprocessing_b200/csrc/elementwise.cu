@@ -106,7 +106,9 @@ normalize_cluster_kernel(const float *__restrict__ x, int64_t n, float *__restri
 
     // ---- write back: (x - c) / scale, true divide ----
     const float c3[3] = {cx, cy, cz};
-    if (dst_same) {
+    if (y == nullptr) {
+        // statistics only (the fused model path normalises inside its first chain kernel)
+    } else if (dst_same) {
         for (int64_t v = tid; v < nvec; v += kNormThreads) {
             const int64_t base = 4 * v - off;
             // (p0*3 + base) % 3 == base % 3 (mod with negatives handled below)
@@ -306,7 +308,7 @@ using namespace pcp;
 extern "C" int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale,
                                  pcp_stream stream)
 {
-    PCP_REQUIRE(d_x && d_y && b >= 0 && n >= 1, PCP_ERR_INVALID, "pcp_normalize_f32: bad arguments (b=%d n=%lld)", b, (long long)n);
+    PCP_REQUIRE(d_x && (d_y || (d_centroid && d_scale)) && b >= 0 && n >= 1, PCP_ERR_INVALID, "pcp_normalize_f32: bad arguments (b=%d n=%lld)", b, (long long)n);
     if (b == 0) return PCP_OK;
     // cluster size: slice must fit in shared memory; widen further while the grid under-fills the GPU
     const int64_t max_slice_bytes = 200 * 1024;

@@ -191,6 +191,109 @@ static int tnet_tail(pcp_model *m, int first, size_t fold_w, size_t fold_t, int 
     return gemm_f32(g, st);
 }
 
+
+// Segmentation head (PointNet.py:268-290) from X_64 (bc*n, 64) and the global features (bc, 1024).
+// concat([X_64, tile(global)]) . W1  ==  X_64 . W1[0:64] + (global . W1[64:1088]) — the second term is
+// constant per cloud and becomes a per-cloud bias vector (the tile/concat tensors never exist).
+static int seg_from_x64(pcp_model *m, const float *X64, const float *g3, int bc, int64_t n, float *d_seg, float *d_seg_logits,
+                        cudaStream_t st)
+{
+    Workspace &ws = m->ws;
+    const int P = m->desc.num_parts;
+    const int64_t M = (int64_t)bc * n;
+    const LayerSpec &S1 = m->layers[L_SEG1];
+    GemmArgs gv;
+    gv.A = g3; gv.lda = 1024; gv.B = m->d_fold + S1.fold_w + (size_t)64 * 512; gv.ldb = 512;
+    gv.C = ws.gvec; gv.ldc = 512; gv.bias = m->d_fold + S1.fold_t; gv.M = bc; gv.N = 512; gv.K = 1024;
+    PCP_TRY(gemm_f32(gv, st));
+    GemmArgs g;
+    g.A = X64; g.lda = 64; g.strideA = n * 64; g.B = m->d_fold + S1.fold_w; g.ldb = 512; g.strideB = 0;
+    g.C = ws.s512; g.ldc = 512; g.strideC = n * 512; g.bias = ws.gvec; g.strideBias = 512;
+    g.M = (int)n; g.N = 512; g.K = 64; g.groups = bc; g.relu = 1;
+    PCP_TRY(gemm_f32(g, st));
+    PCP_TRY(layer_fwd(m, L_SEG2, ws.s512, M, ws.s256, true, st));
+    PCP_TRY(layer_fwd(m, L_SEG3, ws.s256, M, ws.s128a, true, st));
+    PCP_TRY(layer_fwd(m, L_SEG4, ws.s128a, M, ws.s128b, true, st));
+    float *logits = d_seg_logits ? d_seg_logits : ws.seglog;
+    PCP_TRY(layer_fwd(m, L_SEG5, ws.s128b, M, logits, false, st));
+    if (d_seg) PCP_TRY(softmax_rows(logits, d_seg, M, P, st));
+    return PCP_OK;
+}
+
+static int ensure_point_ws(pcp_model *m);
+static int model_cls_head_chunk_impl(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st);
+static int model_cls_head_chunk(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st)
+{
+    return model_cls_head_chunk_impl(m, g3, b, d_cls, d_cls_logits, st);
+}
+
+int model_tnet_tail(pcp_model *m, int which, const float *pooled, int bc, float *out, cudaStream_t st)
+{
+    return which == 0 ? tnet_tail(m, L_IT_C1, m->fold_it_w, m->fold_it_t, 3, pooled, bc, out, st)
+                      : tnet_tail(m, L_FT_C1, m->fold_ft_w, m->fold_ft_t, 64, pooled, bc, out, st);
+}
+
+int model_eye3(float *d_R, int b, cudaStream_t st)
+{
+    eye3_kernel<<<(b + 255) / 256, 256, 0, st>>>(d_R, b);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+// classification head (PointNet.py:252-263): dense 512 -> 256 -> C (+bias) -> softmax
+int model_cls_head(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st)
+{
+    return model_cls_head_chunk(m, g3, b, d_cls, d_cls_logits, st);
+}
+
+static int model_cls_head_chunk_impl(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st)
+{
+    Workspace &ws = m->ws;
+    const int C = m->desc.num_classes;
+    PCP_TRY(layer_fwd(m, L_CLS1, g3, b, ws.d512, true, st));
+    PCP_TRY(layer_fwd(m, L_CLS2, ws.d512, b, ws.d256, true, st));
+    float *logits = d_cls_logits ? d_cls_logits : ws.clslog;
+    PCP_TRY(layer_fwd(m, L_CLS3, ws.d256, b, logits, false, st));
+    if (d_cls) PCP_TRY(softmax_rows(logits, d_cls, b, C, st));
+    return PCP_OK;
+}
+
+// Segmentation head for the bf16 trunk: X_64 is rebuilt in fp32 from the raw points (4 288 MAC/point)
+// and the head runs on the fp32 GEMM path.  R / R64 null => vanilla.
+int model_seg_head_fp32(pcp_model *m, const float *d_x, int b, int64_t n, const float *d_R, const float *d_R64, const float *g3,
+                        float *d_seg, float *d_seg_logits, cudaStream_t st)
+{
+    PCP_TRY(ensure_point_ws(m));
+    Workspace &ws = m->ws;
+    const int P = m->desc.num_parts;
+    for (int c0 = 0; c0 < b; c0 += ws.cap_b) {
+        const int bc = std::min(ws.cap_b, b - c0);
+        const int64_t M = (int64_t)bc * n;
+        PCP_TRY(pcp_normalize_f32(d_x + (int64_t)c0 * n * 3, bc, n, ws.pcn, nullptr, nullptr, st));
+        const float *X3 = ws.pcn;
+        if (d_R) {
+            GemmArgs g;
+            g.A = ws.pcn; g.lda = 3; g.strideA = n * 3; g.B = d_R + (int64_t)c0 * 9; g.ldb = 3; g.strideB = 9;
+            g.C = ws.xr; g.ldc = 3; g.strideC = n * 3; g.M = (int)n; g.N = 3; g.K = 3; g.groups = bc;
+            PCP_TRY(gemm_f32(g, st));
+            X3 = ws.xr;
+        }
+        PCP_TRY(layer_fwd(m, L_S1_1, X3, M, ws.h64a, true, st));
+        PCP_TRY(layer_fwd(m, L_S1_2, ws.h64a, M, ws.h64b, true, st));
+        const float *X64 = ws.h64b;
+        if (d_R64) {
+            GemmArgs g;
+            g.A = ws.h64b; g.lda = 64; g.strideA = n * 64; g.B = d_R64 + (int64_t)c0 * 4096; g.ldb = 64; g.strideB = 4096;
+            g.C = ws.x64; g.ldc = 64; g.strideC = n * 64; g.M = (int)n; g.N = 64; g.K = 64; g.groups = bc;
+            PCP_TRY(gemm_f32(g, st));
+            X64 = ws.x64;
+        }
+        PCP_TRY(seg_from_x64(m, X64, g3 + (int64_t)c0 * 1024, bc, n, d_seg ? d_seg + (int64_t)c0 * n * P : nullptr,
+                             d_seg_logits ? d_seg_logits + (int64_t)c0 * n * P : nullptr, st));
+    }
+    return PCP_OK;
+}
+
 int model_forward_fp32(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
                        float *d_R, float *d_cls_logits, float *d_seg_logits, cudaStream_t st)
 {
@@ -240,33 +343,12 @@ int model_forward_fp32(pcp_model *m, const float *d_x, int b, int64_t n, uint32_
         PCP_TRY(layer_fwd(m, L_S2_2, ws.h64a, M, ws.h128, true, st));                              // :239
         PCP_TRY(layer_fwd(m, L_S2_3, ws.h128, M, nullptr, true, st, g3, bc, n));                   // :242 + :248
 
-        if (heads & PCP_HEAD_CLS) {                                                                // :252-263
-            PCP_TRY(layer_fwd(m, L_CLS1, g3, bc, ws.d512, true, st));
-            PCP_TRY(layer_fwd(m, L_CLS2, ws.d512, bc, ws.d256, true, st));
-            float *logits = d_cls_logits ? d_cls_logits + (int64_t)c0 * C : ws.clslog;
-            PCP_TRY(layer_fwd(m, L_CLS3, ws.d256, bc, logits, false, st));
-            if (d_cls) PCP_TRY(softmax_rows(logits, d_cls + (int64_t)c0 * C, bc, C, st));
-        }
-        if (heads & PCP_HEAD_SEG) {                                                                // :268-290
-            // concat([X_64, tile(global)]) . W1  ==  X_64 . W1[0:64] + (global . W1[64:1088])  — the
-            // second term is constant per cloud and becomes a per-cloud bias vector.
-            const LayerSpec &S1 = m->layers[L_SEG1];
-            GemmArgs gv;
-            gv.A = g3; gv.lda = 1024; gv.B = m->d_fold + S1.fold_w + (size_t)64 * 512; gv.ldb = 512;
-            gv.C = ws.gvec; gv.ldc = 512; gv.bias = m->d_fold + S1.fold_t; gv.M = bc; gv.N = 512; gv.K = 1024;
-            PCP_TRY(gemm_f32(gv, st));
-            GemmArgs g;
-            g.A = X64; g.lda = 64; g.strideA = n * 64; g.B = m->d_fold + S1.fold_w; g.ldb = 512; g.strideB = 0;
-            g.C = ws.s512; g.ldc = 512; g.strideC = n * 512; g.bias = ws.gvec; g.strideBias = 512;
-            g.M = (int)n; g.N = 512; g.K = 64; g.groups = bc; g.relu = 1;
-            PCP_TRY(gemm_f32(g, st));
-            PCP_TRY(layer_fwd(m, L_SEG2, ws.s512, M, ws.s256, true, st));
-            PCP_TRY(layer_fwd(m, L_SEG3, ws.s256, M, ws.s128a, true, st));
-            PCP_TRY(layer_fwd(m, L_SEG4, ws.s128a, M, ws.s128b, true, st));
-            float *logits = d_seg_logits ? d_seg_logits + (int64_t)c0 * n * P : ws.seglog;
-            PCP_TRY(layer_fwd(m, L_SEG5, ws.s128b, M, logits, false, st));
-            if (d_seg) PCP_TRY(softmax_rows(logits, d_seg + (int64_t)c0 * n * P, M, P, st));
-        }
+        if (heads & PCP_HEAD_CLS)                                                                  // :252-263
+            PCP_TRY(model_cls_head_chunk(m, g3, bc, d_cls ? d_cls + (int64_t)c0 * C : nullptr,
+                                         d_cls_logits ? d_cls_logits + (int64_t)c0 * C : nullptr, st));
+        if (heads & PCP_HEAD_SEG)
+            PCP_TRY(seg_from_x64(m, X64, g3, bc, n, d_seg ? d_seg + (int64_t)c0 * n * P : nullptr,
+                                 d_seg_logits ? d_seg_logits + (int64_t)c0 * n * P : nullptr, st));
     }
     return PCP_OK;
 }
@@ -279,6 +361,23 @@ void model_destroy_bf16(pcp_model *m);
 }  // namespace pcp
 
 using namespace pcp;
+
+namespace pcp {
+static int ensure_point_ws(pcp_model *m)
+{
+    Workspace &ws = m->ws;
+    if (ws.pcn) return PCP_OK;
+    const int P = m->desc.num_parts;
+    const size_t Mc = (size_t)ws.cap_b * (size_t)ws.cap_n;
+    PCP_TRY(ws_alloc(ws, &ws.pcn, Mc * 3)); PCP_TRY(ws_alloc(ws, &ws.xr, Mc * 3));
+    PCP_TRY(ws_alloc(ws, &ws.h64a, Mc * 64)); PCP_TRY(ws_alloc(ws, &ws.h64b, Mc * 64));
+    PCP_TRY(ws_alloc(ws, &ws.x64, Mc * 64)); PCP_TRY(ws_alloc(ws, &ws.h128, Mc * 128));
+    PCP_TRY(ws_alloc(ws, &ws.s512, Mc * 512)); PCP_TRY(ws_alloc(ws, &ws.s256, Mc * 256));
+    PCP_TRY(ws_alloc(ws, &ws.s128a, Mc * 128)); PCP_TRY(ws_alloc(ws, &ws.s128b, Mc * 128));
+    PCP_TRY(ws_alloc(ws, &ws.seglog, Mc * P));
+    return PCP_OK;
+}
+}  // namespace pcp
 
 extern "C" int pcp_model_create(const pcp_model_desc *desc, pcp_model **out)
 {
@@ -403,18 +502,10 @@ extern "C" int pcp_model_reserve(pcp_model *m, int b, int64_t n)
     const int C = m->desc.num_classes, P = m->desc.num_parts;
     const bool fp32 = m->desc.precision == PCP_PRECISION_FP32;
     // fp32 path materialises per-point activations: bound a chunk to ~192k points
-    const int64_t max_pts = fp32 ? 196608 : ((int64_t)1 << 40);
+    const int64_t max_pts = 196608;
     int cap_b = (int)std::max<int64_t>(1, std::min<int64_t>(b, max_pts / n));
     ws.cap_b = cap_b; ws.cap_n = n; ws.total_b = b;
-    const size_t Mc = (size_t)cap_b * (size_t)n;
-    if (fp32) {
-        PCP_TRY(ws_alloc(ws, &ws.pcn, Mc * 3)); PCP_TRY(ws_alloc(ws, &ws.xr, Mc * 3));
-        PCP_TRY(ws_alloc(ws, &ws.h64a, Mc * 64)); PCP_TRY(ws_alloc(ws, &ws.h64b, Mc * 64));
-        PCP_TRY(ws_alloc(ws, &ws.x64, Mc * 64)); PCP_TRY(ws_alloc(ws, &ws.h128, Mc * 128));
-        PCP_TRY(ws_alloc(ws, &ws.s512, Mc * 512)); PCP_TRY(ws_alloc(ws, &ws.s256, Mc * 256));
-        PCP_TRY(ws_alloc(ws, &ws.s128a, Mc * 128)); PCP_TRY(ws_alloc(ws, &ws.s128b, Mc * 128));
-        PCP_TRY(ws_alloc(ws, &ws.seglog, Mc * P));
-    }
+    if (fp32) PCP_TRY(ensure_point_ws(m));
     PCP_TRY(ws_alloc(ws, &ws.g1, (size_t)b * 1024)); PCP_TRY(ws_alloc(ws, &ws.g2, (size_t)b * 1024));
     PCP_TRY(ws_alloc(ws, &ws.g3, (size_t)b * 1024));
     PCP_TRY(ws_alloc(ws, &ws.d512, (size_t)b * 512)); PCP_TRY(ws_alloc(ws, &ws.d256, (size_t)b * 256));
@@ -452,32 +543,15 @@ extern "C" int pcp_model_predict_host(pcp_model *m, const float *h_x, int b, int
         PCP_TRY(ws_alloc(ws, &ws.stage_seg, (size_t)ws.total_b * ws.cap_n * P));
         PCP_TRY(ws_alloc(ws, &ws.stage_R, (size_t)ws.total_b * 9));
     }
-    if (ws.pin_x_bytes < xb) {
-        if (ws.pin_x) cudaFreeHost(ws.pin_x);
-        ws.pin_x = nullptr; ws.pin_x_bytes = 0;
-        PCP_CUDA_OK(cudaMallocHost(reinterpret_cast<void **>(&ws.pin_x), xb));
-        ws.pin_x_bytes = xb;
-    }
-    const size_t ob = (cls_cnt + seg_cnt + r_cnt) * sizeof(float);
-    if (ws.pin_out_bytes < ob) {
-        if (ws.pin_out) cudaFreeHost(ws.pin_out);
-        ws.pin_out = nullptr; ws.pin_out_bytes = 0;
-        PCP_CUDA_OK(cudaMallocHost(reinterpret_cast<void **>(&ws.pin_out), ob));
-        ws.pin_out_bytes = ob;
-    }
-    // pageable -> pinned staging -> device (the pinned hop keeps the H2D copy at full PCIe rate)
-    memcpy(ws.pin_x, h_x, xb);
-    PCP_CUDA_OK(cudaMemcpyAsync(ws.stage_x, ws.pin_x, xb, cudaMemcpyHostToDevice, st));
+    // The caller's buffers are used directly: pinned memory (cudaMallocHost / torch pin_memory) is DMA'd
+    // at full PCIe rate, pageable memory is staged by the driver.
+    PCP_CUDA_OK(cudaMemcpyAsync(ws.stage_x, h_x, xb, cudaMemcpyHostToDevice, st));
     PCP_TRY(pcp_model_forward(m, ws.stage_x, b, n, heads, h_cls ? ws.stage_cls : nullptr, h_seg ? ws.stage_seg : nullptr,
                               h_R ? ws.stage_R : nullptr, nullptr, nullptr, stream));
-    float *po = ws.pin_out;
-    if (h_cls) PCP_CUDA_OK(cudaMemcpyAsync(po, ws.stage_cls, cls_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
-    if (h_seg) PCP_CUDA_OK(cudaMemcpyAsync(po + cls_cnt, ws.stage_seg, seg_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
-    if (h_R) PCP_CUDA_OK(cudaMemcpyAsync(po + cls_cnt + seg_cnt, ws.stage_R, r_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (h_cls) PCP_CUDA_OK(cudaMemcpyAsync(h_cls, ws.stage_cls, cls_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (h_seg) PCP_CUDA_OK(cudaMemcpyAsync(h_seg, ws.stage_seg, seg_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (h_R) PCP_CUDA_OK(cudaMemcpyAsync(h_R, ws.stage_R, r_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
     PCP_CUDA_OK(cudaStreamSynchronize(st));
-    if (h_cls) memcpy(h_cls, po, cls_cnt * sizeof(float));
-    if (h_seg) memcpy(h_seg, po + cls_cnt, seg_cnt * sizeof(float));
-    if (h_R) memcpy(h_R, po + cls_cnt + seg_cnt, r_cnt * sizeof(float));
     return PCP_OK;
 }
 

@@ -84,4 +84,9 @@ int model_sync_host(pcp_model *m);
 int model_forward_fp32(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
                        float *d_R, float *d_cls_logits, float *d_seg_logits, cudaStream_t st);
 int softmax_rows(const float *d_logits, float *d_prob, int64_t rows, int cols, cudaStream_t st);
+int model_tnet_tail(pcp_model *m, int which, const float *pooled, int bc, float *out, cudaStream_t st);
+int model_eye3(float *d_R, int b, cudaStream_t st);
+int model_cls_head(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st);
+int model_seg_head_fp32(pcp_model *m, const float *d_x, int b, int64_t n, const float *d_R, const float *d_R64, const float *g3,
+                        float *d_seg, float *d_seg_logits, cudaStream_t st);
 }

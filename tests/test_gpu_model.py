@@ -109,3 +109,22 @@ def test_trainability_listing_matches_reference_log(lib):
                        "seg_l1_512_convolution_layer", "seg_l2_256_convolution_layer", "seg_l3_128_convolution_layer",
                        "seg_l4_128_convolution_layer", "seg_l5_output_convolution_layer"]
     assert [v for v in t.values()] == [False] + [True] * 10 + [False] * 5
+
+
+@pytest.mark.parametrize("b,n", [(600, 1024), (40, 8192)])
+def test_bf16_many_tiles_per_cta_matches_fp32_path(lib, b, n):
+    """Persistent-CTA steady state (tens of tiles per CTA, ring/phase wrap-around): the tcgen05 path
+    must agree with the fp32 CUDA-core path on the pooled global features and the class logits, and
+    a few clouds are checked against the oracle directly."""
+    mb, p = build("bf16")
+    mf, _ = build("fp32")
+    x = synth.gaussian_clouds(77, b, n)
+    xd = torch.from_numpy(x).cuda()
+    ob = mb.forward_with_logits(xd, heads=("cls",))
+    of = mf.forward_with_logits(xd, heads=("cls",))
+    assert rel_err(mb.pooled_features(2, b), mf.pooled_features(2, b)) <= 2e-2
+    assert rel_err(ob["cls_logits"].cpu().numpy(), of["cls_logits"].cpu().numpy()) <= 2e-2
+    assert rel_err(ob["R"].cpu().numpy(), of["R"].cpu().numpy()) <= 2e-2
+    sel = [0, b // 2, b - 1]
+    ref = oracle_forward(x[sel], p, False)
+    assert rel_err(ob["cls_logits"].cpu().numpy()[sel], ref["cls_logits"]) <= 2e-2

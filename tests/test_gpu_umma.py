@@ -1,0 +1,25 @@
+"""GPU: the tcgen05 building blocks in isolation — shared-memory operand image (K-major SWIZZLE_128B),
+smem/instruction descriptors, TMEM read-back — against a NumPy bf16-rounded matmul."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def bf16_round(a):
+    return torch.from_numpy(a).to(torch.bfloat16).to(torch.float32).numpy()
+
+
+@pytest.mark.parametrize("N,K", [(64, 64), (128, 64), (128, 128), (256, 128), (32, 256)])
+def test_umma_gemm_matches_bf16_matmul(lib, N, K):
+    from pointcloudprocessing_b200 import _ffi
+    rng = np.random.default_rng(N * 1000 + K)
+    a = rng.standard_normal((128, K)).astype(np.float32)
+    b = rng.standard_normal((N, K)).astype(np.float32)
+    d = np.zeros((128, N), np.float32)
+    _ffi.check(lib.pcp_selftest_umma(_ffi.fptr(a), _ffi.fptr(b), N, K, _ffi.fptr(d)))
+    ref = bf16_round(a).astype(np.float64) @ bf16_round(b).astype(np.float64).T
+    assert np.abs(d - ref).max() <= 1e-3 * np.abs(ref).max()
