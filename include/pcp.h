@@ -167,6 +167,8 @@ int pcp_model_chain_time(pcp_model *m, float *ms_total, int *launches);
  * tcgen05.mma chain with bf16-rounded operands; validates the shared-memory operand image, the
  * descriptors and the TMEM read-back in isolation.  Host pointers, synchronous. */
 int pcp_selftest_umma(const float *h_a, const float *h_b, int N, int K, float *h_d);
+/* same with a CTA pair (cluster of 2, cta_group::2): D (256 x N) = A (256 x K) . B (N x K)^T */
+int pcp_selftest_umma2(const float *h_a, const float *h_b, int N, int K, float *h_d);
 
 /* ---- training (pointnet_train.py:310-351) ---- */
 #define PCP_GROUP_SHARED 0

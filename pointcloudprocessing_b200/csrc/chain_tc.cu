@@ -24,13 +24,7 @@ using namespace umma;
 
 constexpr int kTP = 128;            // points per tile
 constexpr int kChainThreads = 320;
-constexpr int kRing = 4;            // W3 ring slots (16 KB each: 128 channels x 64 K)
-constexpr uint32_t kW3Tile = 16384;
-
-// shared-memory carve (bytes from a 1024-aligned base)
-constexpr uint32_t kOffA0 = 0, kOffA1 = 16384, kOffH2 = 32768, kOffWM = 98304, kOffWC = 131072, kOffW3 = 147456;
-constexpr uint32_t kChainSmem = kOffW3 + kRing * kW3Tile + 1024;   // + alignment slack
-__device__ __forceinline__ uint32_t wm_slot(int s) { return s == 0 ? 0u : (s == 1 ? 8192u : 16384u); }
+constexpr uint32_t kW3Tile = 16384;  // one W3 operand tile: 128 channels x 64 K, bf16
 
 struct ChainParams {
     const float *x; int64_t n; int b;
@@ -48,261 +42,8 @@ struct ChainParams {
     float *gmax;                          // (b,1024), zero-initialised
     int tiles_per_cloud;
     int64_t total_tiles;
+    unsigned long long *trace;            // development only (PCP_CHAIN_TRACE): per-role event timestamps of cluster 0
 };
-
-struct ChainShared {
-    uint64_t a_full, mid_full, wmid_full;
-    uint64_t h2_full[2], h2_empty[2], acc_full[2], acc_empty[2], wc_full[2], wc_empty[2];
-    uint64_t w3_full[kRing], w3_empty[kRing];
-    uint32_t tmem_base;
-    alignas(16) float l0[64 * 4];
-    alignas(16) float mid_t[3][128];
-};
-
-__global__ void __launch_bounds__(kChainThreads, 1)
-chain_kernel(const ChainParams p)
-{
-    extern __shared__ uint8_t smem_raw[];
-    __shared__ ChainShared sh;
-    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint8_t *A0 = base + kOffA0, *A1 = base + kOffA1, *H2 = base + kOffH2, *WM = base + kOffWM, *WC = base + kOffWC, *W3 = base + kOffW3;
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int64_t t_begin = (int64_t)blockIdx.x * p.total_tiles / gridDim.x;
-    const int64_t t_end = (int64_t)(blockIdx.x + 1) * p.total_tiles / gridDim.x;
-    const int64_t ntiles = t_end - t_begin;
-
-    if (tid == 0) {
-        mbar_init(&sh.a_full, 128); mbar_init(&sh.mid_full, 1); mbar_init(&sh.wmid_full, 1);
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(&sh.h2_full[i], 128); mbar_init(&sh.h2_empty[i], 1);
-            mbar_init(&sh.acc_full[i], 1); mbar_init(&sh.acc_empty[i], 128);
-            mbar_init(&sh.wc_full[i], 1); mbar_init(&sh.wc_empty[i], 1);
-        }
-        for (int i = 0; i < kRing; ++i) { mbar_init(&sh.w3_full[i], 1); mbar_init(&sh.w3_empty[i], 1); }
-        fence_barrier_init();
-    }
-    if (warp == 9) tmem_alloc(&sh.tmem_base, 512);
-    for (int i = tid; i < 256; i += kChainThreads) sh.l0[i] = p.l0[i];
-    for (int l = 0; l < p.nmid; ++l)
-        for (int i = tid; i < p.mid_n[l]; i += kChainThreads) sh.mid_t[l][i] = p.mid_t[l][i];
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = sh.tmem_base;
-
-    if (warp < 4) {
-        // =========================== front: L0 + mid-layer epilogues ===========================
-        const int row = tid;
-        uint32_t mid_phase = 0;
-        for (int64_t it = 0; it < ntiles; ++it) {
-            const int64_t t = t_begin + it;
-            const int64_t cloud = t / p.tiles_per_cloud;
-            const int64_t pi = min((t % p.tiles_per_cloud) * (int64_t)kTP + row, p.n - 1);   // clamp: duplicates do not change a max
-            const float *px = p.x + (cloud * p.n + pi) * 3;
-            const float cx = __ldg(p.centroid + cloud * 3), cy = __ldg(p.centroid + cloud * 3 + 1), cz = __ldg(p.centroid + cloud * 3 + 2);
-            const float sc = __ldg(p.scale + cloud);
-            float q0 = __fdiv_rn(__fsub_rn(__ldg(px), cx), sc), q1 = __fdiv_rn(__fsub_rn(__ldg(px + 1), cy), sc),
-                  q2 = __fdiv_rn(__fsub_rn(__ldg(px + 2), cz), sc);                             // PointNet.py:691-706
-            if (p.R) {
-                const float *R = p.R + cloud * 9;
-                const float r0 = q0 * __ldg(R) + q1 * __ldg(R + 3) + q2 * __ldg(R + 6);
-                const float r1 = q0 * __ldg(R + 1) + q1 * __ldg(R + 4) + q2 * __ldg(R + 7);
-                const float r2 = q0 * __ldg(R + 2) + q1 * __ldg(R + 5) + q2 * __ldg(R + 8);
-                q0 = r0; q1 = r1; q2 = r2;
-            }
-            // L0: 3 -> 64 on CUDA cores (K = 3 is not tensor-core work), BN folded, ReLU, bf16 -> A0
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                float o[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const float4 w = *reinterpret_cast<const float4 *>(&sh.l0[(c * 8 + e) * 4]);
-                    const float v = fmaf(q2, w.z, fmaf(q1, w.y, fmaf(q0, w.x, w.w)));
-                    o[e] = v > 0.f ? v : 0.f;
-                }
-                *reinterpret_cast<uint4 *>(A0 + sw128_offset(128, row, c * 8)) =
-                    make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
-            }
-            fence_proxy_async();
-            mbar_arrive(&sh.a_full);
-            for (int l = 0; l < p.nmid; ++l) {
-                mbar_wait(&sh.mid_full, mid_phase, 1);
-                mid_phase ^= 1;
-                tc_fence_after();
-                const bool last = (l == p.nmid - 1);
-                uint8_t *out = last ? H2 + (it & 1) * 32768 : ((l & 1) ? A0 : A1);
-                if (last && it >= 2) mbar_wait(&sh.h2_empty[it & 1], ((it >> 1) - 1) & 1, 2);
-                const int N = p.mid_n[l];
-                for (int c0 = 0; c0 < N; c0 += 32) {
-                    uint32_t v[32];
-                    tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        float o[8];
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const float f = __uint_as_float(v[c * 8 + e]) + sh.mid_t[l][c0 + c * 8 + e];
-                            o[e] = f > 0.f ? f : 0.f;
-                        }
-                        *reinterpret_cast<uint4 *>(out + sw128_offset(128, row, c0 + c * 8)) =
-                            make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
-                    }
-                }
-                tc_fence_before();
-                fence_proxy_async();
-                mbar_arrive(last ? &sh.h2_full[it & 1] : &sh.a_full);
-            }
-        }
-    } else if (warp < 8) {
-        // =========================== final epilogue: max over points ===========================
-        const int ch = tid - 128;
-        const uint32_t lane_base = (uint32_t)((warp - 4) * 32) << 16;
-        float mx[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) mx[j] = -3.0e38f;
-        int64_t cur_cloud = -1;
-        uint64_t g = 0;
-        auto flush = [&](int64_t cloud) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                float v = mx[j] + __ldg(p.t3 + j * 128 + ch);       // max(relu(x + t)) == relu(max(x) + t)
-                v = v > 0.f ? v : 0.f;
-                atomicMax(reinterpret_cast<unsigned int *>(p.gmax + cloud * 1024 + j * 128 + ch), __float_as_uint(v));
-                mx[j] = -3.0e38f;
-            }
-        };
-        for (int64_t it = 0; it < ntiles; ++it) {
-            const int64_t cloud = (t_begin + it) / p.tiles_per_cloud;
-            if (cloud != cur_cloud) {
-                if (cur_cloud >= 0) flush(cur_cloud);
-                cur_cloud = cloud;
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const uint32_t buf = (uint32_t)(g & 1);
-                mbar_wait(&sh.acc_full[buf], (uint32_t)((g >> 1) & 1), 3);
-                tc_fence_after();
-                float m = mx[j];
-#pragma unroll
-                for (int c0 = 0; c0 < 128; c0 += 32) {
-                    uint32_t v[32];
-                    tmem_ld32(tmem + lane_base + 128 + buf * 128 + c0, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int e = 0; e < 32; ++e) m = fmaxf(m, __uint_as_float(v[e]));
-                }
-                tc_fence_before();
-                mbar_arrive(&sh.acc_empty[buf]);
-                mx[j] = m;
-                ++g;
-            }
-        }
-        if (cur_cloud >= 0) flush(cur_cloud);
-    } else if (warp == 8) {
-        // =========================== MMA issuer ===========================
-        if (lane == 0 && ntiles > 0) {
-            mbar_wait(&sh.wmid_full, 0, 4);
-            int64_t mid_it = 0, fin_it = 0;
-            int mid_l = 0, fin_j = 0, fin_h = 0;
-            uint32_t a_cnt = 0;
-            uint64_t g = 0, r = 0;
-            bool h2_ok = false, acc_ok = false;
-            const uint32_t idesc_fin = make_idesc_bf16(128, 128);
-            long long spin_t0 = clock64();
-            while (mid_it < ntiles || fin_it < ntiles) {
-                // mid-layer work first (it is on the critical path of the next tile), but never block on it:
-                // the per-cloud weight image of tile k is only requested once the W3 ring of tile k-2 has
-                // been issued, so a blocking wait here could starve the ring and deadlock.
-                bool mid_ready = mid_it < ntiles && mbar_test(&sh.a_full, a_cnt & 1);
-                const bool percloud = mid_ready && p.mid_cloud_stride[mid_l] != 0;
-                if (percloud) mid_ready = mbar_test(&sh.wc_full[mid_it & 1], (uint32_t)((mid_it >> 1) & 1));
-                if (mid_ready) {
-                    tc_fence_after();
-                    const uint32_t a_addr = smem_u32((mid_l & 1) ? A1 : A0);
-                    const uint32_t b_addr = smem_u32(percloud ? WC + (mid_it & 1) * 8192 : WM + wm_slot(p.mid_slot[mid_l]));
-                    const uint32_t idesc = make_idesc_bf16(128, (uint32_t)p.mid_n[mid_l]);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) mma_bf16_ss(tmem, make_sdesc(a_addr + k * 32), make_sdesc(b_addr + k * 32), idesc, k > 0);
-                    mma_commit(&sh.mid_full);
-                    if (percloud) mma_commit(&sh.wc_empty[mid_it & 1]);
-                    ++a_cnt;
-                    if (++mid_l == p.nmid) { mid_l = 0; ++mid_it; }
-                    spin_t0 = clock64();
-                    continue;
-                }
-                if (fin_it < ntiles) {
-                    const int s = (int)(fin_it & 1);
-                    bool go = true;
-                    if (!h2_ok) { h2_ok = mbar_test(&sh.h2_full[s], (uint32_t)((fin_it >> 1) & 1)); go = h2_ok; }
-                    const uint32_t buf = (uint32_t)(g & 1);
-                    if (go && !acc_ok) { acc_ok = (g < 2) || mbar_test(&sh.acc_empty[buf], (uint32_t)(((g >> 1) - 1) & 1)); go = acc_ok; }
-                    const uint32_t slot = (uint32_t)(r % kRing);
-                    if (go) go = mbar_test(&sh.w3_full[slot], (uint32_t)((r / kRing) & 1));
-                    if (go) {
-                        tc_fence_after();
-                        const uint32_t a_addr = smem_u32(W3 + slot * kW3Tile);
-                        const uint32_t b_addr = smem_u32(H2 + s * 32768 + fin_h * 16384);
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            mma_bf16_ss(tmem + 128 + buf * 128, make_sdesc(a_addr + k * 32), make_sdesc(b_addr + k * 32), idesc_fin, (fin_h | k) > 0);
-                        mma_commit(&sh.w3_empty[slot]);
-                        ++r;
-                        if (++fin_h == 2) {
-                            fin_h = 0;
-                            mma_commit(&sh.acc_full[buf]);
-                            ++g; acc_ok = false;
-                            if (++fin_j == 8) { fin_j = 0; mma_commit(&sh.h2_empty[s]); ++fin_it; h2_ok = false; }
-                        }
-                        spin_t0 = clock64();
-                        continue;
-                    }
-                }
-                if (clock64() - spin_t0 > 4000000000ll) {
-                    g_mbar_timeout_info[0] = 0xdead0100u; g_mbar_timeout_info[1] = blockIdx.x;
-                    g_mbar_timeout_info[2] = (unsigned)mid_it; g_mbar_timeout_info[3] = (unsigned)fin_it;
-                    __threadfence_system();
-                    __trap();
-                }
-            }
-        }
-    } else {
-        // =========================== loader ===========================
-        if (lane == 0 && ntiles > 0) {
-            uint32_t bytes = 0;
-            for (int l = 0; l < p.nmid; ++l) if (p.mid_cloud_stride[l] == 0) bytes += (uint32_t)p.mid_n[l] * 128u;
-            mbar_arrive_expect_tx(&sh.wmid_full, bytes);
-            for (int l = 0; l < p.nmid; ++l)
-                if (p.mid_cloud_stride[l] == 0) bulk_g2s(WM + wm_slot(p.mid_slot[l]), p.mid_w[l], (uint32_t)p.mid_n[l] * 128u, &sh.wmid_full);
-            int pc_layer = -1;
-            for (int l = 0; l < p.nmid; ++l) if (p.mid_cloud_stride[l] != 0) pc_layer = l;
-            auto issue_wc = [&](int64_t it) {
-                if (pc_layer < 0) return;
-                if (it >= 2) mbar_wait(&sh.wc_empty[it & 1], (uint32_t)(((it >> 1) - 1) & 1), 6);
-                const int64_t cloud = (t_begin + it) / p.tiles_per_cloud;
-                mbar_arrive_expect_tx(&sh.wc_full[it & 1], 8192);
-                bulk_g2s(WC + (it & 1) * 8192, p.mid_w[pc_layer] + cloud * p.mid_cloud_stride[pc_layer], 8192, &sh.wc_full[it & 1]);
-            };
-            issue_wc(0);
-            if (ntiles > 1) issue_wc(1);
-            uint64_t r = 0;
-            for (int64_t it = 0; it < ntiles; ++it) {
-                for (int gi = 0; gi < 16; ++gi) {
-                    const uint32_t slot = (uint32_t)(r % kRing);
-                    if (r >= kRing) mbar_wait(&sh.w3_empty[slot], (uint32_t)(((r / kRing) - 1) & 1), 7);
-                    mbar_arrive_expect_tx(&sh.w3_full[slot], kW3Tile);
-                    bulk_g2s(W3 + slot * kW3Tile, p.w3 + (size_t)gi * kW3Tile, kW3Tile, &sh.w3_full[slot]);
-                    ++r;
-                }
-                if (it + 2 < ntiles) issue_wc(it + 2);
-            }
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 9) tmem_dealloc(tmem, 512);
-}
 
 // ---------------------------------------------------------------------------------------------
 // Self-test GEMM: D (128 x N) = A (128 x K) . B (N x K)^T from pre-packed SW128 images, one CTA.
@@ -350,6 +91,485 @@ umma_selftest_kernel(const uint8_t *__restrict__ a_img, const uint8_t *__restric
     if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
+
+// =============================================================================================
+// chain2_kernel — CTA-PAIR version (cluster of 2, tcgen05 cta_group::2).
+//   * Each CTA of the pair runs the front chain for its own 128-point tile; every MMA spans both SMs
+//     (M = 256): mid layers  D[256 pts, N] = A[256 pts, 64] . W^T  (each CTA holds N/2 weight rows),
+//     final layer            D[256 ch, 128 pts] = W3^T[256 ch, 128] . H2^T  (each CTA holds 128 channel
+//     rows of W3 and contributes 64 of the 128 point columns).
+//   * W3 is RESIDENT: each CTA keeps its 4 x [128 ch x 128 K] bf16 tiles (128 KB) in shared memory for the
+//     whole persistent kernel — zero steady-state weight traffic (v1 re-streamed 256 KB per tile from L2).
+//   * H2 is single-buffered but split in two 64-point halves with their own full/empty barriers and the
+//     final layer walks (half, channel-block): half 0 of the next tile is refilled while half 1 computes.
+//   * Only the leader CTA issues MMAs; completions are multicast to both CTAs' mbarriers; the follower's
+//     threads arrive on the leader's barriers through mapa + mbarrier.arrive.release.cluster.
+// =============================================================================================
+constexpr uint32_t kC2OffW3 = 0, kC2OffA0 = 131072, kC2OffA1 = 147456, kC2OffH2 = 163840, kC2OffWM = 196608, kC2OffWC = 212992;
+constexpr uint32_t kChain2Smem = kC2OffWC + 2 * 4096 + 1024;
+__device__ __forceinline__ uint32_t wm2_slot(int s) { return s == 0 ? 0u : (s == 1 ? 4096u : 8192u); }
+
+constexpr int kTraceEvents = 2048;
+// role: 0 front (warp 0), 1 final epilogue (warp 4), 2 MMA issuer, 3 loader; slot = (cta*4 + role)
+__device__ __forceinline__ void trace_ev(const ChainParams &p, uint32_t rank, int role, uint32_t &cnt, uint32_t code)
+{
+    if (p.trace && blockIdx.x < 2 && cnt < kTraceEvents) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.trace[((size_t)(rank * 4 + role) * kTraceEvents + cnt) * 2] = code;
+        p.trace[((size_t)(rank * 4 + role) * kTraceEvents + cnt) * 2 + 1] = t;
+        ++cnt;
+    }
+}
+
+struct Chain2Shared {
+    uint64_t a_full, mid_full, wready, wres_full;
+    uint64_t h2_full[2], h2_empty[2], acc_full[2], acc_empty[2], wc_full[2], wc_ready[2], wc_empty[2];
+    uint32_t tmem_base;
+    alignas(16) float l0[64 * 4];
+    alignas(16) float mid_t[3][128];
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kChainThreads, 1)
+chain2_kernel(const ChainParams p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ Chain2Shared sh;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t *W3 = base + kC2OffW3, *A0 = base + kC2OffA0, *A1 = base + kC2OffA1, *H2 = base + kC2OffH2, *WM = base + kC2OffWM, *WC = base + kC2OffWC;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int64_t ncl = gridDim.x >> 1, cl = blockIdx.x >> 1;
+    const int ppc = (p.tiles_per_cloud + 1) >> 1;                        // pair-steps per cloud
+    const int64_t total_steps = (int64_t)ppc * p.b;
+    const int64_t s_begin = cl * total_steps / ncl, s_end = (cl + 1) * total_steps / ncl;
+    const int64_t nsteps = s_end - s_begin;
+
+    if (tid == 0) {
+        mbar_init(&sh.a_full, 8); mbar_init(&sh.mid_full, 1); mbar_init(&sh.wready, 2); mbar_init(&sh.wres_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&sh.h2_full[i], 4); mbar_init(&sh.h2_empty[i], 1);
+            mbar_init(&sh.acc_full[i], 1); mbar_init(&sh.acc_empty[i], 8);
+            mbar_init(&sh.wc_full[i], 1); mbar_init(&sh.wc_ready[i], 2); mbar_init(&sh.wc_empty[i], 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 9) tmem_alloc2(&sh.tmem_base, 512);
+    for (int i = tid; i < 256; i += kChainThreads) sh.l0[i] = p.l0[i];
+    for (int l = 0; l < p.nmid; ++l)
+        for (int i = tid; i < p.mid_n[l]; i += kChainThreads) sh.mid_t[l][i] = p.mid_t[l][i];
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem = sh.tmem_base;
+
+    if (warp < 4) {
+        // =========================== front (both CTAs): L0 + mid-layer epilogues ===========================
+        const int row = tid;
+        const int half = warp >> 1;
+        uint32_t mid_phase = 0;
+        uint32_t tcnt = 0;
+        const bool tr = (tid == 0);
+        for (int64_t it = 0; it < nsteps; ++it) {
+            if (tr) trace_ev(p, rank, 0, tcnt, 0x100);
+            const int64_t st = s_begin + it;
+            const int64_t cloud = st / ppc;
+            const int64_t tile = 2 * (st % ppc) + rank;
+            const int64_t pi = min(tile * (int64_t)kTP + row, p.n - 1);
+            const float *px = p.x + (cloud * p.n + pi) * 3;
+            const float cx = __ldg(p.centroid + cloud * 3), cy = __ldg(p.centroid + cloud * 3 + 1), cz = __ldg(p.centroid + cloud * 3 + 2);
+            const float sc = __ldg(p.scale + cloud);
+            float q0 = __fdiv_rn(__fsub_rn(__ldg(px), cx), sc), q1 = __fdiv_rn(__fsub_rn(__ldg(px + 1), cy), sc),
+                  q2 = __fdiv_rn(__fsub_rn(__ldg(px + 2), cz), sc);
+            if (p.R) {
+                const float *R = p.R + cloud * 9;
+                const float r0 = q0 * __ldg(R) + q1 * __ldg(R + 3) + q2 * __ldg(R + 6);
+                const float r1 = q0 * __ldg(R + 1) + q1 * __ldg(R + 4) + q2 * __ldg(R + 7);
+                const float r2 = q0 * __ldg(R + 2) + q1 * __ldg(R + 5) + q2 * __ldg(R + 8);
+                q0 = r0; q1 = r1; q2 = r2;
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float o[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const float4 w = *reinterpret_cast<const float4 *>(&sh.l0[(c * 8 + e) * 4]);
+                    const float v = fmaf(q2, w.z, fmaf(q1, w.y, fmaf(q0, w.x, w.w)));
+                    o[e] = v > 0.f ? v : 0.f;
+                }
+                *reinterpret_cast<uint4 *>(A0 + sw128_offset(128, row, c * 8)) =
+                    make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+            }
+            // one arrival per WARP (8 per pair), not per thread: 256 serialized smem atomics per hand-off
+            // were the dominant latency of the whole pipeline
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) { if (rank == 0) mbar_arrive(&sh.a_full); else mbar_arrive_cluster(&sh.a_full, 0); }
+            if (tr) trace_ev(p, rank, 0, tcnt, 0x101);
+            for (int l = 0; l < p.nmid; ++l) {
+                mbar_wait(&sh.mid_full, mid_phase, 11);
+                if (tr) trace_ev(p, rank, 0, tcnt, 0x110 + l);
+                mid_phase ^= 1;
+                tc_fence_after();
+                const bool last = (l == p.nmid - 1);
+                uint8_t *out = last ? H2 : ((l & 1) ? A0 : A1);
+                if (last && it >= 1) mbar_wait(&sh.h2_empty[half], (uint32_t)((it - 1) & 1), 12);
+                if (tr && last) trace_ev(p, rank, 0, tcnt, 0x120);
+                const int N = p.mid_n[l];
+                for (int c0 = 0; c0 < N; c0 += 64) {
+                    uint32_t va[32], vb[32];
+                    const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + c0;
+                    tmem_ld32(taddr, va); tmem_ld32(taddr + 32, vb);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        float o[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const uint32_t raw = c < 4 ? va[c * 8 + e] : vb[(c - 4) * 8 + e];
+                            const float f = __uint_as_float(raw) + sh.mid_t[l][c0 + c * 8 + e];
+                            o[e] = f > 0.f ? f : 0.f;
+                        }
+                        *reinterpret_cast<uint4 *>(out + sw128_offset(128, row, c0 + c * 8)) =
+                            make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+                    }
+                }
+                tc_fence_before();
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    uint64_t *bar = last ? &sh.h2_full[half] : &sh.a_full;
+                    if (rank == 0) mbar_arrive(bar); else mbar_arrive_cluster(bar, 0);
+                }
+                if (tr) trace_ev(p, rank, 0, tcnt, 0x130 + l);
+            }
+        }
+    } else if (warp < 8) {
+        // =========================== final epilogue (both CTAs) ===========================
+        const int ch = tid - 128;
+        const uint32_t lane_base = (uint32_t)((warp - 4) * 32) << 16;
+        float mx[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) mx[j] = -3.0e38f;
+        int64_t cur_cloud = -1;
+        uint64_t g = 0;
+        uint32_t tcnt = 0;
+        auto flush = [&](int64_t cloud) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int c = (j * 2 + (int)rank) * 128 + ch;
+                float v = mx[j] + __ldg(p.t3 + c);
+                v = v > 0.f ? v : 0.f;
+                atomicMax(reinterpret_cast<unsigned int *>(p.gmax + cloud * 1024 + c), __float_as_uint(v));
+                mx[j] = -3.0e38f;
+            }
+        };
+        for (int64_t it = 0; it < nsteps; ++it) {
+            const int64_t cloud = (s_begin + it) / ppc;
+            if (cloud != cur_cloud) {
+                if (cur_cloud >= 0) flush(cur_cloud);
+                cur_cloud = cloud;
+            }
+#pragma unroll
+            for (int hj = 0; hj < 8; ++hj) {
+                const int j = hj & 3;
+                const uint32_t buf = (uint32_t)(g & 1);
+                mbar_wait(&sh.acc_full[buf], (uint32_t)((g >> 1) & 1), 13);
+                if (tid == 128) trace_ev(p, rank, 1, tcnt, 0x200 + hj);
+                tc_fence_after();
+                // all 128 columns in flight at once, TMEM buffer released before the arithmetic
+                uint32_t v0[32], v1[32], v2[32], v3[32];
+                const uint32_t taddr = tmem + lane_base + 128 + buf * 128;
+                tmem_ld32(taddr, v0); tmem_ld32(taddr + 32, v1); tmem_ld32(taddr + 64, v2); tmem_ld32(taddr + 96, v3);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster_relaxed(&sh.acc_empty[buf], 0);
+                if (tid == 128) trace_ev(p, rank, 1, tcnt, 0x210 + hj);
+                float m0 = mx[j], m1 = -3.0e38f, m2 = -3.0e38f, m3 = -3.0e38f;      // 4 independent chains (FMNMX3)
+#pragma unroll
+                for (int e = 0; e < 32; e += 2) {
+                    m0 = fmaxf(fmaxf(m0, __uint_as_float(v0[e])), __uint_as_float(v0[e + 1]));
+                    m1 = fmaxf(fmaxf(m1, __uint_as_float(v1[e])), __uint_as_float(v1[e + 1]));
+                    m2 = fmaxf(fmaxf(m2, __uint_as_float(v2[e])), __uint_as_float(v2[e + 1]));
+                    m3 = fmaxf(fmaxf(m3, __uint_as_float(v3[e])), __uint_as_float(v3[e + 1]));
+                }
+                const float m = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+                mx[j] = m;
+                ++g;
+            }
+        }
+        if (cur_cloud >= 0) flush(cur_cloud);
+    } else if (warp == 8) {
+        // =========================== MMA issuer (leader CTA only) ===========================
+        if (rank == 0 && lane == 0 && nsteps > 0) {
+            mbar_wait_cluster(&sh.wready, 0, 14);
+            int64_t mid_it = 0, fin_it = 0;
+            int mid_l = 0, fin_hf = 0, fin_j = 0, fin_kb = 0;
+            uint32_t a_cnt = 0;
+            uint64_t g = 0;
+            bool h2_ok = false, acc_ok = false;
+            const uint32_t idesc_fin = make_idesc_bf16(256, 128);
+            long long spin_t0 = clock64();
+            uint32_t tcnt = 0;
+            while (mid_it < nsteps || fin_it < nsteps) {
+                bool mid_ready = mid_it < nsteps && mbar_test(&sh.a_full, a_cnt & 1);
+                const bool percloud = mid_ready && p.mid_cloud_stride[mid_l] != 0;
+                if (percloud) mid_ready = mbar_test(&sh.wc_ready[mid_it & 1], (uint32_t)((mid_it >> 1) & 1));
+                if (mid_ready) {
+                    trace_ev(p, rank, 2, tcnt, 0x300 + mid_l);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32((mid_l & 1) ? A1 : A0);
+                    const uint32_t b_addr = smem_u32(percloud ? WC + (mid_it & 1) * 4096 : WM + wm2_slot(p.mid_slot[mid_l]));
+                    const uint32_t idesc = make_idesc_bf16(256, (uint32_t)p.mid_n[mid_l]);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) mma2_bf16_ss(tmem, make_sdesc(a_addr + k * 32), make_sdesc(b_addr + k * 32), idesc, k > 0);
+                    mma2_commit_mc(&sh.mid_full, 3);
+                    if (percloud) mma2_commit_mc(&sh.wc_empty[mid_it & 1], 3);
+                    ++a_cnt;
+                    if (++mid_l == p.nmid) { mid_l = 0; ++mid_it; }
+                    spin_t0 = clock64();
+                    continue;
+                }
+                if (fin_it < nsteps) {
+                    bool go = true;
+                    if (!h2_ok) { h2_ok = mbar_test(&sh.h2_full[fin_hf], (uint32_t)(fin_it & 1)); go = h2_ok; }
+                    const uint32_t buf = (uint32_t)(g & 1);
+                    if (go && !acc_ok) { acc_ok = (g < 2) || mbar_test(&sh.acc_empty[buf], (uint32_t)(((g >> 1) - 1) & 1)); go = acc_ok; }
+                    if (go) {
+                        trace_ev(p, rank, 2, tcnt, 0x400 + fin_hf * 16 + fin_j * 2 + fin_kb);
+                        tc_fence_after();
+                        const uint32_t a_addr = smem_u32(W3 + fin_j * 32768 + fin_kb * 16384);
+                        const uint32_t b_addr = smem_u32(H2 + fin_kb * 16384 + fin_hf * 8192);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            mma2_bf16_ss(tmem + 128 + buf * 128, make_sdesc(a_addr + k * 32), make_sdesc(b_addr + k * 32), idesc_fin, (fin_kb | k) > 0);
+                        if (++fin_kb == 2) {
+                            fin_kb = 0;
+                            mma2_commit_mc(&sh.acc_full[buf], 3);
+                            ++g; acc_ok = false;
+                            if (++fin_j == 4) {
+                                fin_j = 0;
+                                mma2_commit_mc(&sh.h2_empty[fin_hf], 3);
+                                h2_ok = false;
+                                if (++fin_hf == 2) { fin_hf = 0; ++fin_it; }
+                            }
+                        }
+                        spin_t0 = clock64();
+                        continue;
+                    }
+                }
+                if (clock64() - spin_t0 > 4000000000ll) {
+                    g_mbar_timeout_info[0] = 0xdead0200u; g_mbar_timeout_info[1] = blockIdx.x;
+                    g_mbar_timeout_info[2] = (unsigned)mid_it; g_mbar_timeout_info[3] = (unsigned)fin_it;
+                    __threadfence_system();
+                    __trap();
+                }
+            }
+        }
+    } else {
+        // =========================== loader (both CTAs) ===========================
+        if (lane == 0 && nsteps > 0) {
+            uint32_t bytes = 8 * kW3Tile;
+            for (int l = 0; l < p.nmid; ++l) if (p.mid_cloud_stride[l] == 0) bytes += (uint32_t)p.mid_n[l] * 64u;
+            mbar_arrive_expect_tx(&sh.wres_full, bytes);
+            for (int j = 0; j < 4; ++j)
+                for (int kb = 0; kb < 2; ++kb)
+                    bulk_g2s(W3 + j * 32768 + kb * 16384, p.w3 + (size_t)(((j * 2 + rank) * 2) + kb) * kW3Tile, kW3Tile, &sh.wres_full);
+            for (int l = 0; l < p.nmid; ++l)
+                if (p.mid_cloud_stride[l] == 0)
+                    bulk_g2s(WM + wm2_slot(p.mid_slot[l]), p.mid_w[l] + (size_t)rank * p.mid_n[l] * 64u, (uint32_t)p.mid_n[l] * 64u, &sh.wres_full);
+            mbar_wait(&sh.wres_full, 0, 15);
+            mbar_arrive_cluster(&sh.wready, 0);
+            int pc_layer = -1;
+            for (int l = 0; l < p.nmid; ++l) if (p.mid_cloud_stride[l] != 0) pc_layer = l;
+            if (pc_layer >= 0) {
+                for (int64_t it = 0; it < nsteps; ++it) {
+                    const int s = (int)(it & 1);
+                    if (it >= 2) mbar_wait(&sh.wc_empty[s], (uint32_t)(((it >> 1) - 1) & 1), 16);
+                    const int64_t cloud = (s_begin + it) / ppc;
+                    mbar_arrive_expect_tx(&sh.wc_full[s], 4096);
+                    bulk_g2s(WC + s * 4096, p.mid_w[pc_layer] + cloud * p.mid_cloud_stride[pc_layer] + (size_t)rank * 4096, 4096, &sh.wc_full[s]);
+                    mbar_wait(&sh.wc_full[s], (uint32_t)((it >> 1) & 1), 17);
+                    mbar_arrive_cluster(&sh.wc_ready[s], 0);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 9) tmem_dealloc2(tmem, 512);
+}
+
+// 2-CTA self-test: D (256 x N) = A (256 x K) . B (N x K)^T with cta_group::2 (tests/test_gpu_umma.py)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+umma2_selftest_kernel(const uint8_t *__restrict__ a_img, const uint8_t *__restrict__ b_img, int N, int K, float *__restrict__ d)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full, ready, done;
+    __shared__ uint32_t tmem_base;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const uint32_t rank = cluster_ctarank();
+    const uint32_t a_bytes = 128u * K * 2u, bh_bytes = (uint32_t)(N / 2) * K * 2u;
+    uint8_t *A = base, *B = base + a_bytes;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (tid == 0) { mbar_init(&full, 1); mbar_init(&ready, 2); mbar_init(&done, 1); fence_barrier_init(); }
+    if (warp == 0) tmem_alloc2(&tmem_base, 256);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base;
+    if (tid == 0) {
+        // per K-block: this CTA's 128 A rows and its N/2 B rows (contiguous inside each K-block of the full images)
+        mbar_arrive_expect_tx(&full, a_bytes + bh_bytes);
+        for (int kb = 0; kb < K / 64; ++kb) {
+            bulk_g2s(A + kb * (128 * 128), a_img + (size_t)kb * (256 * 128) + (size_t)rank * (128 * 128), 128 * 128, &full);
+            bulk_g2s(B + kb * ((N / 2) * 128), b_img + (size_t)kb * (N * 128) + (size_t)rank * ((N / 2) * 128), (N / 2) * 128, &full);
+        }
+        mbar_wait(&full, 0, 18);
+        mbar_arrive_cluster(&ready, 0);
+        if (rank == 0) {
+            mbar_wait_cluster(&ready, 0, 19);
+            tc_fence_after();
+            const uint32_t idesc = make_idesc_bf16(256, (uint32_t)N);
+            for (int kb = 0; kb < K / 64; ++kb)
+                for (int k = 0; k < 4; ++k)
+                    mma2_bf16_ss(tmem, make_sdesc(smem_u32(A) + kb * (128 * 128) + k * 32),
+                                 make_sdesc(smem_u32(B) + kb * ((N / 2) * 128) + k * 32), idesc, (kb | k) > 0);
+            mma2_commit_mc(&done, 3);
+        }
+    }
+    mbar_wait(&done, 0, 20);
+    tc_fence_after();
+    for (int c0 = 0; c0 < N; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+        tmem_ld_wait();
+        for (int e = 0; e < 32; ++e) d[(size_t)(rank * 128 + tid) * N + c0 + e] = __uint_as_float(v[e]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 0) tmem_dealloc2(tmem, 256);
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Micro-benchmark (development): issue rate of back-to-back tcgen05.mma from shared-memory operands.
+// out[0] = cycles, out[1] = MMAs issued.  mode 0: cta_group::1; the operands are whatever is in smem.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(288, 1)
+umma_rate_kernel(int N, int iters, int kblocks, int mode, long long *out)
+{
+    // mode bits: 1 = warps 4-7 stream tcgen05.ld from the idle accumulator half, 2 = warps 1-3 stream st.shared.v4,
+    //            4 = warps 1-3 spin on an mbarrier that never completes, 8 = MMA thread polls an mbarrier between batches
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t done, never;
+    __shared__ uint32_t tmem_base;
+    __shared__ volatile int stop;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < (128 * 128 + 256 * 128) * kblocks / 4 + 8192; i += 288) reinterpret_cast<uint32_t *>(base)[i] = 0x3c003c00u;
+    if (tid == 0) { mbar_init(&done, 1); mbar_init(&never, 1); stop = 0; fence_barrier_init(); }
+    if (warp == 0) tmem_alloc(&tmem_base, 512);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base;
+    uint8_t *scratch = base + (128 * 128 + 256 * 128) * kblocks;
+    if (tid == 0) {
+        const uint32_t a0 = smem_u32(base), b0 = a0 + 128 * 128 * kblocks;
+        const uint32_t idesc = make_idesc_bf16(128, (uint32_t)N);
+        const long long t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+            if (mode & 8) { (void)mbar_test(&never, 0); (void)mbar_test(&never, 0); tc_fence_after(); }
+            for (int kb = 0; kb < kblocks; ++kb)
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    mma_bf16_ss(tmem, make_sdesc(a0 + kb * 16384 + k * 32), make_sdesc(b0 + kb * (N * 128) + k * 32), idesc, (kb | k) > 0);
+        }
+        mma_commit(&done);
+        mbar_wait(&done, 0, 30);
+        const long long t1 = clock64();
+        out[0] = t1 - t0;
+        out[1] = (long long)iters * kblocks * 4;
+        stop = 1;
+    } else if (warp >= 4 && warp < 8 && (mode & 1)) {
+        uint32_t acc = 0;
+        long long n = 0;
+        const long long t0 = clock64();
+        while (!stop) {
+            uint32_t v0[32], v1[32], v2[32], v3[32];
+            const uint32_t ta = tmem + ((uint32_t)((warp - 4) * 32) << 16) + 256;
+            tmem_ld32(ta, v0); tmem_ld32(ta + 32, v1); tmem_ld32(ta + 64, v2); tmem_ld32(ta + 96, v3);
+            tmem_ld_wait();
+            acc += v0[0] ^ v1[1] ^ v2[2] ^ v3[3];
+            ++n;
+        }
+        const long long t1 = clock64();
+        if ((tid & 31) == 0) { out[2 + (warp - 4) * 2] = t1 - t0; out[3 + (warp - 4) * 2] = n; }
+        if (acc == 0x12345678u) out[1] = 0;
+    } else if (warp >= 1 && warp < 4 && (mode & 2)) {
+        uint32_t i = 0;
+        while (!stop) {
+            *reinterpret_cast<uint4 *>(scratch + ((tid * 16 + (i++ & 7) * 4096) & 32767)) = make_uint4(i, i, i, i);
+        }
+    } else if (warp >= 1 && warp < 4 && (mode & 4)) {
+        while (!stop) (void)mbar_try(&never, 0);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+
+// Micro-benchmark (development): tcgen05.ld throughput.  out[w] = cycles for `iters` x (4 x 32x32b.x32) per warp.
+__global__ void __launch_bounds__(128, 1)
+tmem_ld_rate_kernel(int iters, int nwarps, int pack16, long long *out)
+{
+    __shared__ uint32_t tmem_base;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    if (warp == 0) tmem_alloc(&tmem_base, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base;
+    if (warp < nwarps) {
+        uint32_t acc = 0;
+        const uint32_t ta = tmem + ((uint32_t)(warp * 32) << 16);
+        const long long t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+            uint32_t v0[32], v1[32], v2[32], v3[32];
+            if (pack16) {
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "
+                             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                             "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                             : "=r"(v0[0]), "=r"(v0[1]), "=r"(v0[2]), "=r"(v0[3]), "=r"(v0[4]), "=r"(v0[5]), "=r"(v0[6]), "=r"(v0[7]),
+                               "=r"(v0[8]), "=r"(v0[9]), "=r"(v0[10]), "=r"(v0[11]), "=r"(v0[12]), "=r"(v0[13]), "=r"(v0[14]), "=r"(v0[15]),
+                               "=r"(v0[16]), "=r"(v0[17]), "=r"(v0[18]), "=r"(v0[19]), "=r"(v0[20]), "=r"(v0[21]), "=r"(v0[22]), "=r"(v0[23]),
+                               "=r"(v0[24]), "=r"(v0[25]), "=r"(v0[26]), "=r"(v0[27]), "=r"(v0[28]), "=r"(v0[29]), "=r"(v0[30]), "=r"(v0[31])
+                             : "r"(ta) : "memory");
+                tmem_ld_wait();
+                acc += v0[3];
+            } else {
+                tmem_ld32(ta, v0); tmem_ld32(ta + 32, v1); tmem_ld32(ta + 64, v2); tmem_ld32(ta + 96, v3);
+                tmem_ld_wait();
+                acc += v0[3] ^ v1[5] ^ v2[7] ^ v3[9];
+            }
+        }
+        const long long t1 = clock64();
+        if (tid % 32 == 0) out[warp] = t1 - t0;
+        if (acc == 0x12345u) out[7] = 1;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 512);
+}
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -508,16 +728,35 @@ static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, 
     p.tiles_per_cloud = (int)((n + kTP - 1) / kTP);
     p.total_tiles = (int64_t)p.tiles_per_cloud * b;
     if (!ts->attr_set) {
-        PCP_CUDA_OK(cudaFuncSetAttribute(chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kChainSmem));
+        PCP_CUDA_OK(cudaFuncSetAttribute(chain2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kChain2Smem));
         ts->attr_set = true;
     }
-    const int grid = (int)std::min<int64_t>(p.total_tiles, sm_count());
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ts->timing) {
         PCP_CUDA_OK(cudaEventCreate(&e0)); PCP_CUDA_OK(cudaEventCreate(&e1));
         PCP_CUDA_OK(cudaEventRecord(e0, st));
     }
-    chain_kernel<<<grid, kChainThreads, kChainSmem, st>>>(p);
+    const int64_t steps = (int64_t)((p.tiles_per_cloud + 1) / 2) * b;
+    const int ncl = (int)std::min<int64_t>(steps, sm_count() / 2);
+    static const char *trace_path = getenv("PCP_CHAIN_TRACE");          // development aid: dump role timelines of cluster 0
+    unsigned long long *d_trace = nullptr;
+    const size_t trace_bytes = (size_t)8 * kTraceEvents * 2 * sizeof(unsigned long long);
+    if (trace_path) {
+        PCP_CUDA_OK(cudaMalloc(&d_trace, trace_bytes));
+        PCP_CUDA_OK(cudaMemsetAsync(d_trace, 0, trace_bytes, st));
+        p.trace = d_trace;
+    }
+    chain2_kernel<<<2 * ncl, kChainThreads, kChain2Smem, st>>>(p);
+    if (trace_path) {
+        std::vector<unsigned long long> h(trace_bytes / 8);
+        PCP_CUDA_OK(cudaStreamSynchronize(st));
+        PCP_CUDA_OK(cudaMemcpy(h.data(), d_trace, trace_bytes, cudaMemcpyDeviceToHost));
+        cudaFree(d_trace);
+        static int seq = 0;
+        char name[512];
+        snprintf(name, sizeof(name), "%s.%d.bin", trace_path, seq++);
+        if (FILE *f = fopen(name, "wb")) { fwrite(h.data(), 1, trace_bytes, f); fclose(f); }
+    }
     PCP_CHECK_LAUNCH();
     if (ts->timing) {
         PCP_CUDA_OK(cudaEventRecord(e1, st));
@@ -597,7 +836,68 @@ extern "C" int pcp_model_chain_time(pcp_model *m, float *ms_total, int *launches
     return PCP_OK;
 }
 
-// D (128 x N) = A (128 x K) . B (N x K)^T through tcgen05 (host fp32 in/out; operands rounded to bf16).
+// D (M x N) = A (M x K) . B (N x K)^T through tcgen05 (host fp32 in/out; operands rounded to bf16).
+// M = 128: one CTA, cta_group::1.  M = 256: CTA pair, cta_group::2.
+static int selftest_umma_pair(const float *h_a, const float *h_b, int N, int K, float *h_d)
+{
+    std::vector<uint16_t> ai((size_t)256 * K), bi((size_t)N * K);
+    for (int r = 0; r < 256; ++r) for (int k = 0; k < K; ++k) ai[sw128_offset(256, r, k) / 2] = f2bf(h_a[(size_t)r * K + k]);
+    for (int r = 0; r < N; ++r) for (int k = 0; k < K; ++k) bi[sw128_offset(N, r, k) / 2] = f2bf(h_b[(size_t)r * K + k]);
+    uint8_t *da = nullptr, *db = nullptr; float *dd = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&da, ai.size() * 2)); PCP_CUDA_OK(cudaMalloc(&db, bi.size() * 2)); PCP_CUDA_OK(cudaMalloc(&dd, (size_t)256 * N * 4));
+    PCP_CUDA_OK(cudaMemcpy(da, ai.data(), ai.size() * 2, cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemcpy(db, bi.data(), bi.size() * 2, cudaMemcpyHostToDevice));
+    const size_t smem = (size_t)128 * K * 2 + (size_t)(N / 2) * K * 2 + 1024;
+    PCP_CUDA_OK(cudaFuncSetAttribute(umma2_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    umma2_selftest_kernel<<<2, 128, smem>>>(da, db, N, K, dd);
+    PCP_CHECK_LAUNCH();
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        unsigned info[4] = {0, 0, 0, 0};
+        cudaMemcpyFromSymbol(info, g_mbar_timeout_info, sizeof(info));
+        set_error("pcp_selftest_umma(pair): %s (timeout info %08x %u %u %u)", cudaGetErrorString(e), info[0], info[1], info[2], info[3]);
+        return PCP_ERR_CUDA;
+    }
+    PCP_CUDA_OK(cudaMemcpy(h_d, dd, (size_t)256 * N * 4, cudaMemcpyDeviceToHost));
+    cudaFree(da); cudaFree(db); cudaFree(dd);
+    return PCP_OK;
+}
+
+extern "C" int pcp_selftest_umma_rate(int N, int iters, int kblocks, int nctas, int mode, long long *h_out)
+{
+    long long *d = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&d, 80));
+    PCP_CUDA_OK(cudaMemset(d, 0, 80));
+    const size_t smem = (size_t)(128 * 128 + 256 * 128) * kblocks + 32768 + 1024;
+    PCP_CUDA_OK(cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    umma_rate_kernel<<<nctas, 288, smem>>>(N, iters, kblocks, mode, d);
+    PCP_CHECK_LAUNCH();
+    PCP_CUDA_OK(cudaDeviceSynchronize());
+    PCP_CUDA_OK(cudaMemcpy(h_out, d, 80, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return PCP_OK;
+}
+
+extern "C" int pcp_selftest_tmem_ld_rate(int iters, int nwarps, int pack16, long long *h_out)
+{
+    long long *d = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&d, 64));
+    PCP_CUDA_OK(cudaMemset(d, 0, 64));
+    tmem_ld_rate_kernel<<<1, 128>>>(iters, nwarps, pack16, d);
+    PCP_CHECK_LAUNCH();
+    PCP_CUDA_OK(cudaDeviceSynchronize());
+    PCP_CUDA_OK(cudaMemcpy(h_out, d, 64, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return PCP_OK;
+}
+
+extern "C" int pcp_selftest_umma2(const float *h_a, const float *h_b, int N, int K, float *h_d)
+{
+    PCP_REQUIRE(h_a && h_b && h_d && N % 32 == 0 && N >= 32 && N <= 256 && K % 64 == 0 && K >= 64 && K <= 256, PCP_ERR_INVALID,
+                "pcp_selftest_umma2: N in {32..256 step 32}, K in {64,128,192,256}");
+    return selftest_umma_pair(h_a, h_b, N, K, h_d);
+}
+
 extern "C" int pcp_selftest_umma(const float *h_a, const float *h_b, int N, int K, float *h_d)
 {
     PCP_REQUIRE(h_a && h_b && h_d && N % 32 == 0 && N >= 32 && N <= 256 && K % 64 == 0 && K >= 64 && K <= 256, PCP_ERR_INVALID,

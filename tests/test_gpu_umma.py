@@ -23,3 +23,16 @@ def test_umma_gemm_matches_bf16_matmul(lib, N, K):
     _ffi.check(lib.pcp_selftest_umma(_ffi.fptr(a), _ffi.fptr(b), N, K, _ffi.fptr(d)))
     ref = bf16_round(a).astype(np.float64) @ bf16_round(b).astype(np.float64).T
     assert np.abs(d - ref).max() <= 1e-3 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("N,K", [(64, 64), (128, 64), (128, 128), (256, 128)])
+def test_umma_pair_gemm_matches_bf16_matmul(lib, N, K):
+    """cta_group::2: one MMA across a CTA pair (M = 256; A rows and B rows split across the two CTAs)."""
+    from pointcloudprocessing_b200 import _ffi
+    rng = np.random.default_rng(N * 1000 + K + 1)
+    a = rng.standard_normal((256, K)).astype(np.float32)
+    b = rng.standard_normal((N, K)).astype(np.float32)
+    d = np.zeros((256, N), np.float32)
+    _ffi.check(lib.pcp_selftest_umma2(_ffi.fptr(a), _ffi.fptr(b), N, K, _ffi.fptr(d)))
+    ref = bf16_round(a).astype(np.float64) @ bf16_round(b).astype(np.float64).T
+    assert np.abs(d - ref).max() <= 1e-3 * np.abs(ref).max()
