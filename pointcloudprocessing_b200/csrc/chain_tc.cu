@@ -124,7 +124,7 @@ __device__ __forceinline__ void trace_ev(const ChainParams &p, uint32_t rank, in
 
 struct Chain2Shared {
     uint64_t a_full, mid_full, wready, wres_full;
-    uint64_t h2_full[2], h2_empty[2], acc_full[2], acc_empty[2], wc_full[2], wc_ready[2], wc_empty[2];
+    uint64_t h2_full[2], h2_empty[2], acc_full[3], acc_empty[3], wc_full[2], wc_ready[2], wc_empty[2];
     uint32_t tmem_base;
     alignas(16) float l0[64 * 4];
     alignas(16) float mid_t[3][128];
@@ -150,9 +150,9 @@ chain2_kernel(const ChainParams p)
         mbar_init(&sh.a_full, 8); mbar_init(&sh.mid_full, 1); mbar_init(&sh.wready, 2); mbar_init(&sh.wres_full, 1);
         for (int i = 0; i < 2; ++i) {
             mbar_init(&sh.h2_full[i], 4); mbar_init(&sh.h2_empty[i], 1);
-            mbar_init(&sh.acc_full[i], 1); mbar_init(&sh.acc_empty[i], 8);
             mbar_init(&sh.wc_full[i], 1); mbar_init(&sh.wc_ready[i], 2); mbar_init(&sh.wc_empty[i], 1);
         }
+        for (int i = 0; i < 3; ++i) { mbar_init(&sh.acc_full[i], 1); mbar_init(&sh.acc_empty[i], 8); }
         fence_barrier_init();
     }
     if (warp == 9) tmem_alloc2(&sh.tmem_base, 512);
@@ -172,24 +172,32 @@ chain2_kernel(const ChainParams p)
         uint32_t mid_phase = 0;
         uint32_t tcnt = 0;
         const bool tr = (tid == 0);
-        for (int64_t it = 0; it < nsteps; ++it) {
-            if (tr) trace_ev(p, rank, 0, tcnt, 0x100);
+        // normalised (and R-rotated) coordinates of this thread's point for pair-step `it`; evaluated one step
+        // ahead so the global-load + divide latency hides behind the wait for the first mid-layer MMA
+        auto load_point = [&](int64_t it, float &q0, float &q1, float &q2) {
             const int64_t st = s_begin + it;
             const int64_t cloud = st / ppc;
             const int64_t tile = 2 * (st % ppc) + rank;
-            const int64_t pi = min(tile * (int64_t)kTP + row, p.n - 1);
+            const int64_t pi = min(tile * (int64_t)kTP + row, p.n - 1);      // clamp: duplicates do not change a max
             const float *px = p.x + (cloud * p.n + pi) * 3;
             const float cx = __ldg(p.centroid + cloud * 3), cy = __ldg(p.centroid + cloud * 3 + 1), cz = __ldg(p.centroid + cloud * 3 + 2);
             const float sc = __ldg(p.scale + cloud);
-            float q0 = __fdiv_rn(__fsub_rn(__ldg(px), cx), sc), q1 = __fdiv_rn(__fsub_rn(__ldg(px + 1), cy), sc),
-                  q2 = __fdiv_rn(__fsub_rn(__ldg(px + 2), cz), sc);
-            if (p.R) {
+            q0 = __fdiv_rn(__fsub_rn(__ldg(px), cx), sc);                    // PointNet.py:691-706
+            q1 = __fdiv_rn(__fsub_rn(__ldg(px + 1), cy), sc);
+            q2 = __fdiv_rn(__fsub_rn(__ldg(px + 2), cz), sc);
+            if (p.R) {                                                       // X = pc @ R (PointNet.py:207)
                 const float *R = p.R + cloud * 9;
                 const float r0 = q0 * __ldg(R) + q1 * __ldg(R + 3) + q2 * __ldg(R + 6);
                 const float r1 = q0 * __ldg(R + 1) + q1 * __ldg(R + 4) + q2 * __ldg(R + 7);
                 const float r2 = q0 * __ldg(R + 2) + q1 * __ldg(R + 5) + q2 * __ldg(R + 8);
                 q0 = r0; q1 = r1; q2 = r2;
             }
+        };
+        float q0 = 0.f, q1 = 0.f, q2 = 0.f, nq0 = 0.f, nq1 = 0.f, nq2 = 0.f;
+        if (nsteps > 0) load_point(0, nq0, nq1, nq2);
+        for (int64_t it = 0; it < nsteps; ++it) {
+            if (tr) trace_ev(p, rank, 0, tcnt, 0x100);
+            q0 = nq0; q1 = nq1; q2 = nq2;
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
                 float o[8];
@@ -208,6 +216,7 @@ chain2_kernel(const ChainParams p)
             __syncwarp();
             if (lane == 0) { if (rank == 0) mbar_arrive(&sh.a_full); else mbar_arrive_cluster(&sh.a_full, 0); }
             if (tr) trace_ev(p, rank, 0, tcnt, 0x101);
+            if (it + 1 < nsteps) load_point(it + 1, nq0, nq1, nq2);
             for (int l = 0; l < p.nmid; ++l) {
                 mbar_wait(&sh.mid_full, mid_phase, 11);
                 if (tr) trace_ev(p, rank, 0, tcnt, 0x110 + l);
@@ -275,8 +284,8 @@ chain2_kernel(const ChainParams p)
 #pragma unroll
             for (int hj = 0; hj < 8; ++hj) {
                 const int j = hj & 3;
-                const uint32_t buf = (uint32_t)(g & 1);
-                mbar_wait(&sh.acc_full[buf], (uint32_t)((g >> 1) & 1), 13);
+                const uint32_t buf = (uint32_t)(g % 3);      // three TMEM accumulator buffers (TMEM: 128 mid + 3 x 128)
+                mbar_wait(&sh.acc_full[buf], (uint32_t)((g / 3) & 1), 13);
                 if (tid == 128) trace_ev(p, rank, 1, tcnt, 0x200 + hj);
                 tc_fence_after();
                 // all 128 columns in flight at once, TMEM buffer released before the arithmetic
@@ -304,67 +313,85 @@ chain2_kernel(const ChainParams p)
         if (cur_cloud >= 0) flush(cur_cloud);
     } else if (warp == 8) {
         // =========================== MMA issuer (leader CTA only) ===========================
-        if (rank == 0 && lane == 0 && nsteps > 0) {
+        // The whole warp runs this loop with warp-uniform state; only lane 0 issues (predicated asm).
+        // One iteration issues a complete accumulator granule (8 MMAs = 2 K-blocks) so that the ~150-cycle
+        // mbarrier polls of the next iteration overlap with tensor work already queued.
+        if (rank == 0 && nsteps > 0) {
             mbar_wait_cluster(&sh.wready, 0, 14);
+            const uint32_t lo_a0 = (smem_u32(A0) & 0x3FFFFu) >> 4, lo_a1 = (smem_u32(A1) & 0x3FFFFu) >> 4;
+            const uint32_t lo_h2 = (smem_u32(H2) & 0x3FFFFu) >> 4, lo_w3 = (smem_u32(W3) & 0x3FFFFu) >> 4;
+            const uint32_t lo_wm = (smem_u32(WM) & 0x3FFFFu) >> 4, lo_wc = (smem_u32(WC) & 0x3FFFFu) >> 4;
             int64_t mid_it = 0, fin_it = 0;
-            int mid_l = 0, fin_hf = 0, fin_j = 0, fin_kb = 0;
+            int mid_l = 0, fin_hf = 0, fin_j = 0;
             uint32_t a_cnt = 0;
             uint64_t g = 0;
             bool h2_ok = false, acc_ok = false;
             const uint32_t idesc_fin = make_idesc_bf16(256, 128);
-            long long spin_t0 = clock64();
+            uint32_t idle = 0;
             uint32_t tcnt = 0;
             while (mid_it < nsteps || fin_it < nsteps) {
                 bool mid_ready = mid_it < nsteps && mbar_test(&sh.a_full, a_cnt & 1);
                 const bool percloud = mid_ready && p.mid_cloud_stride[mid_l] != 0;
                 if (percloud) mid_ready = mbar_test(&sh.wc_ready[mid_it & 1], (uint32_t)((mid_it >> 1) & 1));
                 if (mid_ready) {
-                    trace_ev(p, rank, 2, tcnt, 0x300 + mid_l);
                     tc_fence_after();
-                    const uint32_t a_addr = smem_u32((mid_l & 1) ? A1 : A0);
-                    const uint32_t b_addr = smem_u32(percloud ? WC + (mid_it & 1) * 4096 : WM + wm2_slot(p.mid_slot[mid_l]));
+                    const uint32_t a_lo = (mid_l & 1) ? lo_a1 : lo_a0;
+                    const uint32_t b_lo = percloud ? lo_wc + (uint32_t)(mid_it & 1) * (4096u >> 4) : lo_wm + (wm2_slot(p.mid_slot[mid_l]) >> 4);
                     const uint32_t idesc = make_idesc_bf16(256, (uint32_t)p.mid_n[mid_l]);
+                    if (elect_one_sync()) {
+                        trace_ev(p, rank, 2, tcnt, 0x300 + mid_l);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) mma2_bf16_ss(tmem, make_sdesc(a_addr + k * 32), make_sdesc(b_addr + k * 32), idesc, k > 0);
-                    mma2_commit_mc(&sh.mid_full, 3);
-                    if (percloud) mma2_commit_mc(&sh.wc_empty[mid_it & 1], 3);
+                        for (int k = 0; k < 4; ++k)
+                            mma2_bf16_ss(tmem, sdesc_from_lo(a_lo + k * 2), sdesc_from_lo(b_lo + k * 2), idesc, k > 0);
+                        mma2_commit_mc(&sh.mid_full, 3);
+                        if (percloud) mma2_commit_mc(&sh.wc_empty[mid_it & 1], 3);
+                    }
+                    __syncwarp();
                     ++a_cnt;
                     if (++mid_l == p.nmid) { mid_l = 0; ++mid_it; }
-                    spin_t0 = clock64();
+                    idle = 0;
                     continue;
                 }
                 if (fin_it < nsteps) {
                     bool go = true;
                     if (!h2_ok) { h2_ok = mbar_test(&sh.h2_full[fin_hf], (uint32_t)(fin_it & 1)); go = h2_ok; }
-                    const uint32_t buf = (uint32_t)(g & 1);
-                    if (go && !acc_ok) { acc_ok = (g < 2) || mbar_test(&sh.acc_empty[buf], (uint32_t)(((g >> 1) - 1) & 1)); go = acc_ok; }
+                    const uint32_t buf = (uint32_t)(g % 3);
+                    if (go && !acc_ok) { acc_ok = (g < 3) || mbar_test(&sh.acc_empty[buf], (uint32_t)(((g / 3) - 1) & 1)); go = acc_ok; }
+                    // at most two final granules in flight: a mid-layer MMA (critical path of the next tile) then
+                    // queues behind <= ~1.5 granules of tensor work instead of 3
+                    if (go && g >= 2) go = mbar_test(&sh.acc_full[(g - 2) % 3], (uint32_t)(((g - 2) / 3) & 1));
                     if (go) {
-                        trace_ev(p, rank, 2, tcnt, 0x400 + fin_hf * 16 + fin_j * 2 + fin_kb);
                         tc_fence_after();
-                        const uint32_t a_addr = smem_u32(W3 + fin_j * 32768 + fin_kb * 16384);
-                        const uint32_t b_addr = smem_u32(H2 + fin_kb * 16384 + fin_hf * 8192);
+                        const uint32_t a_lo = lo_w3 + (uint32_t)fin_j * (32768u >> 4);
+                        const uint32_t b_lo = lo_h2 + (uint32_t)fin_hf * (8192u >> 4);
+                        const uint32_t d = tmem + 128 + buf * 128;
+                        const bool last_j = (fin_j == 3);
+                        if (elect_one_sync()) {
+                            trace_ev(p, rank, 2, tcnt, 0x400 + fin_hf * 16 + fin_j * 2);
 #pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            mma2_bf16_ss(tmem + 128 + buf * 128, make_sdesc(a_addr + k * 32), make_sdesc(b_addr + k * 32), idesc_fin, (fin_kb | k) > 0);
-                        if (++fin_kb == 2) {
-                            fin_kb = 0;
+                            for (int kk = 0; kk < 8; ++kk)      // kk = kb*4 + k : K-block stride 16 KB, K-step 32 B
+                                mma2_bf16_ss(d, sdesc_from_lo(a_lo + (kk >> 2) * (16384u >> 4) + (kk & 3) * 2),
+                                             sdesc_from_lo(b_lo + (kk >> 2) * (16384u >> 4) + (kk & 3) * 2), idesc_fin, kk > 0);
                             mma2_commit_mc(&sh.acc_full[buf], 3);
-                            ++g; acc_ok = false;
-                            if (++fin_j == 4) {
-                                fin_j = 0;
-                                mma2_commit_mc(&sh.h2_empty[fin_hf], 3);
-                                h2_ok = false;
-                                if (++fin_hf == 2) { fin_hf = 0; ++fin_it; }
-                            }
+                            if (last_j) mma2_commit_mc(&sh.h2_empty[fin_hf], 3);
                         }
-                        spin_t0 = clock64();
+                        __syncwarp();
+                        ++g; acc_ok = false;
+                        if (++fin_j == 4) {
+                            fin_j = 0;
+                            h2_ok = false;
+                            if (++fin_hf == 2) { fin_hf = 0; ++fin_it; }
+                        }
+                        idle = 0;
                         continue;
                     }
                 }
-                if (clock64() - spin_t0 > 4000000000ll) {
-                    g_mbar_timeout_info[0] = 0xdead0200u; g_mbar_timeout_info[1] = blockIdx.x;
-                    g_mbar_timeout_info[2] = (unsigned)mid_it; g_mbar_timeout_info[3] = (unsigned)fin_it;
-                    __threadfence_system();
+                if (++idle > 20000000u) {            // ~seconds of fruitless polling: protocol bug, never hang the GPU
+                    if (lane == 0) {
+                        g_mbar_timeout_info[0] = 0xdead0200u; g_mbar_timeout_info[1] = blockIdx.x;
+                        g_mbar_timeout_info[2] = (unsigned)mid_it; g_mbar_timeout_info[3] = (unsigned)fin_it;
+                        __threadfence_system();
+                    }
                     __trap();
                 }
             }
@@ -458,118 +485,6 @@ umma2_selftest_kernel(const uint8_t *__restrict__ a_img, const uint8_t *__restri
 }
 
 
-// ---------------------------------------------------------------------------------------------
-// Micro-benchmark (development): issue rate of back-to-back tcgen05.mma from shared-memory operands.
-// out[0] = cycles, out[1] = MMAs issued.  mode 0: cta_group::1; the operands are whatever is in smem.
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(288, 1)
-umma_rate_kernel(int N, int iters, int kblocks, int mode, long long *out)
-{
-    // mode bits: 1 = warps 4-7 stream tcgen05.ld from the idle accumulator half, 2 = warps 1-3 stream st.shared.v4,
-    //            4 = warps 1-3 spin on an mbarrier that never completes, 8 = MMA thread polls an mbarrier between batches
-    extern __shared__ uint8_t smem_raw[];
-    __shared__ uint64_t done, never;
-    __shared__ uint32_t tmem_base;
-    __shared__ volatile int stop;
-    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    const int tid = threadIdx.x, warp = tid >> 5;
-    for (int i = tid; i < (128 * 128 + 256 * 128) * kblocks / 4 + 8192; i += 288) reinterpret_cast<uint32_t *>(base)[i] = 0x3c003c00u;
-    if (tid == 0) { mbar_init(&done, 1); mbar_init(&never, 1); stop = 0; fence_barrier_init(); }
-    if (warp == 0) tmem_alloc(&tmem_base, 512);
-    fence_proxy_async();
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = tmem_base;
-    uint8_t *scratch = base + (128 * 128 + 256 * 128) * kblocks;
-    if (tid == 0) {
-        const uint32_t a0 = smem_u32(base), b0 = a0 + 128 * 128 * kblocks;
-        const uint32_t idesc = make_idesc_bf16(128, (uint32_t)N);
-        const long long t0 = clock64();
-        for (int it = 0; it < iters; ++it) {
-            if (mode & 8) { (void)mbar_test(&never, 0); (void)mbar_test(&never, 0); tc_fence_after(); }
-            for (int kb = 0; kb < kblocks; ++kb)
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    mma_bf16_ss(tmem, make_sdesc(a0 + kb * 16384 + k * 32), make_sdesc(b0 + kb * (N * 128) + k * 32), idesc, (kb | k) > 0);
-        }
-        mma_commit(&done);
-        mbar_wait(&done, 0, 30);
-        const long long t1 = clock64();
-        out[0] = t1 - t0;
-        out[1] = (long long)iters * kblocks * 4;
-        stop = 1;
-    } else if (warp >= 4 && warp < 8 && (mode & 1)) {
-        uint32_t acc = 0;
-        long long n = 0;
-        const long long t0 = clock64();
-        while (!stop) {
-            uint32_t v0[32], v1[32], v2[32], v3[32];
-            const uint32_t ta = tmem + ((uint32_t)((warp - 4) * 32) << 16) + 256;
-            tmem_ld32(ta, v0); tmem_ld32(ta + 32, v1); tmem_ld32(ta + 64, v2); tmem_ld32(ta + 96, v3);
-            tmem_ld_wait();
-            acc += v0[0] ^ v1[1] ^ v2[2] ^ v3[3];
-            ++n;
-        }
-        const long long t1 = clock64();
-        if ((tid & 31) == 0) { out[2 + (warp - 4) * 2] = t1 - t0; out[3 + (warp - 4) * 2] = n; }
-        if (acc == 0x12345678u) out[1] = 0;
-    } else if (warp >= 1 && warp < 4 && (mode & 2)) {
-        uint32_t i = 0;
-        while (!stop) {
-            *reinterpret_cast<uint4 *>(scratch + ((tid * 16 + (i++ & 7) * 4096) & 32767)) = make_uint4(i, i, i, i);
-        }
-    } else if (warp >= 1 && warp < 4 && (mode & 4)) {
-        while (!stop) (void)mbar_try(&never, 0);
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, 512);
-}
-
-
-// Micro-benchmark (development): tcgen05.ld throughput.  out[w] = cycles for `iters` x (4 x 32x32b.x32) per warp.
-__global__ void __launch_bounds__(128, 1)
-tmem_ld_rate_kernel(int iters, int nwarps, int pack16, long long *out)
-{
-    __shared__ uint32_t tmem_base;
-    const int tid = threadIdx.x, warp = tid >> 5;
-    if (warp == 0) tmem_alloc(&tmem_base, 512);
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = tmem_base;
-    if (warp < nwarps) {
-        uint32_t acc = 0;
-        const uint32_t ta = tmem + ((uint32_t)(warp * 32) << 16);
-        const long long t0 = clock64();
-        for (int it = 0; it < iters; ++it) {
-            uint32_t v0[32], v1[32], v2[32], v3[32];
-            if (pack16) {
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.pack::16b.b32 "
-                             "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                             "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                             : "=r"(v0[0]), "=r"(v0[1]), "=r"(v0[2]), "=r"(v0[3]), "=r"(v0[4]), "=r"(v0[5]), "=r"(v0[6]), "=r"(v0[7]),
-                               "=r"(v0[8]), "=r"(v0[9]), "=r"(v0[10]), "=r"(v0[11]), "=r"(v0[12]), "=r"(v0[13]), "=r"(v0[14]), "=r"(v0[15]),
-                               "=r"(v0[16]), "=r"(v0[17]), "=r"(v0[18]), "=r"(v0[19]), "=r"(v0[20]), "=r"(v0[21]), "=r"(v0[22]), "=r"(v0[23]),
-                               "=r"(v0[24]), "=r"(v0[25]), "=r"(v0[26]), "=r"(v0[27]), "=r"(v0[28]), "=r"(v0[29]), "=r"(v0[30]), "=r"(v0[31])
-                             : "r"(ta) : "memory");
-                tmem_ld_wait();
-                acc += v0[3];
-            } else {
-                tmem_ld32(ta, v0); tmem_ld32(ta + 32, v1); tmem_ld32(ta + 64, v2); tmem_ld32(ta + 96, v3);
-                tmem_ld_wait();
-                acc += v0[3] ^ v1[5] ^ v2[7] ^ v3[9];
-            }
-        }
-        const long long t1 = clock64();
-        if (tid % 32 == 0) out[warp] = t1 - t0;
-        if (acc == 0x12345u) out[7] = 1;
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, 512);
-}
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -860,34 +775,6 @@ static int selftest_umma_pair(const float *h_a, const float *h_b, int N, int K, 
     }
     PCP_CUDA_OK(cudaMemcpy(h_d, dd, (size_t)256 * N * 4, cudaMemcpyDeviceToHost));
     cudaFree(da); cudaFree(db); cudaFree(dd);
-    return PCP_OK;
-}
-
-extern "C" int pcp_selftest_umma_rate(int N, int iters, int kblocks, int nctas, int mode, long long *h_out)
-{
-    long long *d = nullptr;
-    PCP_CUDA_OK(cudaMalloc(&d, 80));
-    PCP_CUDA_OK(cudaMemset(d, 0, 80));
-    const size_t smem = (size_t)(128 * 128 + 256 * 128) * kblocks + 32768 + 1024;
-    PCP_CUDA_OK(cudaFuncSetAttribute(umma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    umma_rate_kernel<<<nctas, 288, smem>>>(N, iters, kblocks, mode, d);
-    PCP_CHECK_LAUNCH();
-    PCP_CUDA_OK(cudaDeviceSynchronize());
-    PCP_CUDA_OK(cudaMemcpy(h_out, d, 80, cudaMemcpyDeviceToHost));
-    cudaFree(d);
-    return PCP_OK;
-}
-
-extern "C" int pcp_selftest_tmem_ld_rate(int iters, int nwarps, int pack16, long long *h_out)
-{
-    long long *d = nullptr;
-    PCP_CUDA_OK(cudaMalloc(&d, 64));
-    PCP_CUDA_OK(cudaMemset(d, 0, 64));
-    tmem_ld_rate_kernel<<<1, 128>>>(iters, nwarps, pack16, d);
-    PCP_CHECK_LAUNCH();
-    PCP_CUDA_OK(cudaDeviceSynchronize());
-    PCP_CUDA_OK(cudaMemcpy(h_out, d, 64, cudaMemcpyDeviceToHost));
-    cudaFree(d);
     return PCP_OK;
 }
 

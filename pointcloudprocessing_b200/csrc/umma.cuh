@@ -53,7 +53,7 @@ __device__ __forceinline__ bool mbar_try(uint64_t *bar, uint32_t parity)
 }
 // Bounded wait: a protocol bug must never hang the GPU — after ~2 s the kernel records where it
 // was stuck and traps (the launch then fails with an error instead of wedging the device).
-__device__ unsigned int g_mbar_timeout_info[4];
+static __device__ unsigned int g_mbar_timeout_info[4];
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int tag = 0)
 {
     if (mbar_try(bar, parity)) return;
@@ -219,6 +219,32 @@ __device__ __forceinline__ void mma2_commit_mc(uint64_t *bar, uint16_t mask)
 __device__ __forceinline__ void mma2_commit(uint64_t *bar)
 {
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// elect.sync: exactly one lane of the (converged) warp gets a non-zero result.  ptxas recognises the pattern and
+// treats the guarded region as single-threaded (no per-operand uniformisation loop).
+__device__ __forceinline__ uint32_t elect_one_sync()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred;
+}
+// Warp-uniform issue forms: EVERY lane of the issuing warp executes the statement with identical (uniform)
+// operands and only the lane with `lead != 0` actually issues.  Keeping the surrounding control flow
+// warp-uniform lets ptxas hold descriptors in uniform registers (no per-MMA ELECT/R2UR broadcast loop).
+constexpr uint64_t kSdescHi = ((uint64_t)1 << 16) | ((uint64_t)(1024u >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+__device__ __forceinline__ uint64_t sdesc_from_lo(uint32_t lo) { return kSdescHi | (uint64_t)lo; }   // lo = (smem addr & 0x3FFFF) >> 4
+__device__ __forceinline__ void mma2_bf16_ss_lead(uint32_t lead, uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+                 "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(lead) : "memory");
+}
+__device__ __forceinline__ void mma2_commit_mc_lead(uint32_t lead, uint64_t *bar, uint16_t mask)
+{
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t"
+                 "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+                 ::"r"(smem_u32(bar)), "h"(mask), "r"(lead) : "memory");
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi)
