@@ -23,7 +23,7 @@ namespace pcp {
 using namespace umma;
 
 constexpr int kTP = 128;            // points per tile
-constexpr int kChainThreads = 320;
+constexpr int kChainThreads = 352;   // 11 warps: 4 front, 4 final-epilogue, mid issuer, loader, final issuer
 constexpr uint32_t kW3Tile = 16384;  // one W3 operand tile: 128 channels x 64 K, bf16
 
 struct ChainParams {
@@ -110,6 +110,7 @@ constexpr uint32_t kChain2Smem = kC2OffWC + 2 * 4096 + 1024;
 __device__ __forceinline__ uint32_t wm2_slot(int s) { return s == 0 ? 0u : (s == 1 ? 4096u : 8192u); }
 
 constexpr int kTraceEvents = 2048;
+constexpr uint64_t kFinalInFlight = 1;   // final-layer accumulator granules allowed in the tensor queue at once
 // role: 0 front (warp 0), 1 final epilogue (warp 4), 2 MMA issuer, 3 loader; slot = (cta*4 + role)
 __device__ __forceinline__ void trace_ev(const ChainParams &p, uint32_t rank, int role, uint32_t &cnt, uint32_t code)
 {
@@ -214,7 +215,10 @@ chain2_kernel(const ChainParams p)
             // were the dominant latency of the whole pipeline
             fence_proxy_async();
             __syncwarp();
-            if (lane == 0) { if (rank == 0) mbar_arrive(&sh.a_full); else mbar_arrive_cluster(&sh.a_full, 0); }
+            // Follower CTA -> leader barrier: relaxed cluster-scope arrive.  The payload (this CTA's smem) was made
+            // visible to the async proxy by fence.proxy.async above, in program order before the arrive; a
+            // release.cluster here costs ~0.5 us of MEMBAR on the critical path of every layer.
+            if (lane == 0) { if (rank == 0) mbar_arrive(&sh.a_full); else mbar_arrive_cluster_relaxed(&sh.a_full, 0); }
             if (tr) trace_ev(p, rank, 0, tcnt, 0x101);
             if (it + 1 < nsteps) load_point(it + 1, nq0, nq1, nq2);
             for (int l = 0; l < p.nmid; ++l) {
@@ -250,7 +254,7 @@ chain2_kernel(const ChainParams p)
                 __syncwarp();
                 if (lane == 0) {
                     uint64_t *bar = last ? &sh.h2_full[half] : &sh.a_full;
-                    if (rank == 0) mbar_arrive(bar); else mbar_arrive_cluster(bar, 0);
+                    if (rank == 0) mbar_arrive(bar); else mbar_arrive_cluster_relaxed(bar, 0);
                 }
                 if (tr) trace_ev(p, rank, 0, tcnt, 0x130 + l);
             }
@@ -312,91 +316,74 @@ chain2_kernel(const ChainParams p)
         }
         if (cur_cloud >= 0) flush(cur_cloud);
     } else if (warp == 8) {
-        // =========================== MMA issuer (leader CTA only) ===========================
-        // The whole warp runs this loop with warp-uniform state; only lane 0 issues (predicated asm).
-        // One iteration issues a complete accumulator granule (8 MMAs = 2 K-blocks) so that the ~150-cycle
-        // mbarrier polls of the next iteration overlap with tensor work already queued.
+        // =========================== mid-layer MMA issuer (leader CTA only) ===========================
+        // Two independent issuing warps (mid layers here, final layer in warp 10) replace a single polling
+        // state machine: every hand-off is a hardware-suspended mbarrier wait (wake-up ~100 cycles) instead of
+        // a ~150-cycle test_wait poll per barrier per iteration, which had made the issuer the bottleneck.
         if (rank == 0 && nsteps > 0) {
             mbar_wait_cluster(&sh.wready, 0, 14);
             const uint32_t lo_a0 = (smem_u32(A0) & 0x3FFFFu) >> 4, lo_a1 = (smem_u32(A1) & 0x3FFFFu) >> 4;
-            const uint32_t lo_h2 = (smem_u32(H2) & 0x3FFFFu) >> 4, lo_w3 = (smem_u32(W3) & 0x3FFFFu) >> 4;
             const uint32_t lo_wm = (smem_u32(WM) & 0x3FFFFu) >> 4, lo_wc = (smem_u32(WC) & 0x3FFFFu) >> 4;
-            int64_t mid_it = 0, fin_it = 0;
-            int mid_l = 0, fin_hf = 0, fin_j = 0;
-            uint32_t a_cnt = 0;
-            uint64_t g = 0;
-            bool h2_ok = false, acc_ok = false;
-            const uint32_t idesc_fin = make_idesc_bf16(256, 128);
-            uint32_t idle = 0;
-            uint32_t tcnt = 0;
-            while (mid_it < nsteps || fin_it < nsteps) {
-                bool mid_ready = mid_it < nsteps && mbar_test(&sh.a_full, a_cnt & 1);
-                const bool percloud = mid_ready && p.mid_cloud_stride[mid_l] != 0;
-                if (percloud) mid_ready = mbar_test(&sh.wc_ready[mid_it & 1], (uint32_t)((mid_it >> 1) & 1));
-                if (mid_ready) {
+            uint32_t a_cnt = 0, tcnt = 0;
+            for (int64_t it = 0; it < nsteps; ++it) {
+                for (int l = 0; l < p.nmid; ++l) {
+                    mbar_wait(&sh.a_full, a_cnt & 1, 24);
+                    ++a_cnt;
+                    const bool percloud = p.mid_cloud_stride[l] != 0;
+                    if (percloud) mbar_wait(&sh.wc_ready[it & 1], (uint32_t)((it >> 1) & 1), 25);
                     tc_fence_after();
-                    const uint32_t a_lo = (mid_l & 1) ? lo_a1 : lo_a0;
-                    const uint32_t b_lo = percloud ? lo_wc + (uint32_t)(mid_it & 1) * (4096u >> 4) : lo_wm + (wm2_slot(p.mid_slot[mid_l]) >> 4);
-                    const uint32_t idesc = make_idesc_bf16(256, (uint32_t)p.mid_n[mid_l]);
+                    const uint32_t a_lo = (l & 1) ? lo_a1 : lo_a0;
+                    const uint32_t b_lo = percloud ? lo_wc + (uint32_t)(it & 1) * (4096u >> 4) : lo_wm + (wm2_slot(p.mid_slot[l]) >> 4);
+                    const uint32_t idesc = make_idesc_bf16(256, (uint32_t)p.mid_n[l]);
                     if (elect_one_sync()) {
-                        trace_ev(p, rank, 2, tcnt, 0x300 + mid_l);
+                        trace_ev(p, rank, 2, tcnt, 0x300 + l);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             mma2_bf16_ss(tmem, sdesc_from_lo(a_lo + k * 2), sdesc_from_lo(b_lo + k * 2), idesc, k > 0);
                         mma2_commit_mc(&sh.mid_full, 3);
-                        if (percloud) mma2_commit_mc(&sh.wc_empty[mid_it & 1], 3);
+                        if (percloud) mma2_commit_mc(&sh.wc_empty[it & 1], 3);
                     }
                     __syncwarp();
-                    ++a_cnt;
-                    if (++mid_l == p.nmid) { mid_l = 0; ++mid_it; }
-                    idle = 0;
-                    continue;
                 }
-                if (fin_it < nsteps) {
-                    bool go = true;
-                    if (!h2_ok) { h2_ok = mbar_test(&sh.h2_full[fin_hf], (uint32_t)(fin_it & 1)); go = h2_ok; }
-                    const uint32_t buf = (uint32_t)(g % 3);
-                    if (go && !acc_ok) { acc_ok = (g < 3) || mbar_test(&sh.acc_empty[buf], (uint32_t)(((g / 3) - 1) & 1)); go = acc_ok; }
-                    // at most two final granules in flight: a mid-layer MMA (critical path of the next tile) then
-                    // queues behind <= ~1.5 granules of tensor work instead of 3
-                    if (go && g >= 2) go = mbar_test(&sh.acc_full[(g - 2) % 3], (uint32_t)(((g - 2) / 3) & 1));
-                    if (go) {
+            }
+        }
+    } else if (warp == 10) {
+        // =========================== final-layer MMA issuer (leader CTA only) ===========================
+        if (rank == 0 && nsteps > 0) {
+            mbar_wait_cluster(&sh.wready, 0, 26);
+            const uint32_t lo_h2 = (smem_u32(H2) & 0x3FFFFu) >> 4, lo_w3 = (smem_u32(W3) & 0x3FFFFu) >> 4;
+            const uint32_t idesc_fin = make_idesc_bf16(256, 128);
+            uint64_t g = 0;
+            uint32_t tcnt = 0;
+            for (int64_t it = 0; it < nsteps; ++it) {
+                for (int hf = 0; hf < 2; ++hf) {
+                    mbar_wait(&sh.h2_full[hf], (uint32_t)(it & 1), 27);
+                    for (int j = 0; j < 4; ++j, ++g) {
+                        const uint32_t buf = (uint32_t)(g % 3);
+                        if (g >= 3) mbar_wait(&sh.acc_empty[buf], (uint32_t)(((g / 3) - 1) & 1), 28);
+                        // keep at most kFinalInFlight granules queued so a mid-layer MMA (critical path of the
+                        // next tile, issued by warp 8 into the same tensor FIFO) never waits long
+                        if (g >= kFinalInFlight)
+                            mbar_wait(&sh.acc_full[(g - kFinalInFlight) % 3], (uint32_t)(((g - kFinalInFlight) / 3) & 1), 29);
                         tc_fence_after();
-                        const uint32_t a_lo = lo_w3 + (uint32_t)fin_j * (32768u >> 4);
-                        const uint32_t b_lo = lo_h2 + (uint32_t)fin_hf * (8192u >> 4);
+                        const uint32_t a_lo = lo_w3 + (uint32_t)j * (32768u >> 4);
+                        const uint32_t b_lo = lo_h2 + (uint32_t)hf * (8192u >> 4);
                         const uint32_t d = tmem + 128 + buf * 128;
-                        const bool last_j = (fin_j == 3);
                         if (elect_one_sync()) {
-                            trace_ev(p, rank, 2, tcnt, 0x400 + fin_hf * 16 + fin_j * 2);
+                            trace_ev(p, rank, 3, tcnt, 0x400 + hf * 16 + j * 2);
 #pragma unroll
                             for (int kk = 0; kk < 8; ++kk)      // kk = kb*4 + k : K-block stride 16 KB, K-step 32 B
                                 mma2_bf16_ss(d, sdesc_from_lo(a_lo + (kk >> 2) * (16384u >> 4) + (kk & 3) * 2),
                                              sdesc_from_lo(b_lo + (kk >> 2) * (16384u >> 4) + (kk & 3) * 2), idesc_fin, kk > 0);
                             mma2_commit_mc(&sh.acc_full[buf], 3);
-                            if (last_j) mma2_commit_mc(&sh.h2_empty[fin_hf], 3);
+                            if (j == 3) mma2_commit_mc(&sh.h2_empty[hf], 3);
                         }
                         __syncwarp();
-                        ++g; acc_ok = false;
-                        if (++fin_j == 4) {
-                            fin_j = 0;
-                            h2_ok = false;
-                            if (++fin_hf == 2) { fin_hf = 0; ++fin_it; }
-                        }
-                        idle = 0;
-                        continue;
                     }
-                }
-                if (++idle > 20000000u) {            // ~seconds of fruitless polling: protocol bug, never hang the GPU
-                    if (lane == 0) {
-                        g_mbar_timeout_info[0] = 0xdead0200u; g_mbar_timeout_info[1] = blockIdx.x;
-                        g_mbar_timeout_info[2] = (unsigned)mid_it; g_mbar_timeout_info[3] = (unsigned)fin_it;
-                        __threadfence_system();
-                    }
-                    __trap();
                 }
             }
         }
-    } else {
+    } else if (warp == 9) {
         // =========================== loader (both CTAs) ===========================
         if (lane == 0 && nsteps > 0) {
             uint32_t bytes = 8 * kW3Tile;

@@ -30,10 +30,10 @@ def events(slot):
     return [(int(c), int(t)) for c, t in ev[:n]]
 
 
-mma, e0, e1, f0, f1 = events(2), events(1), events(5), events(0), events(4)
+mma, fin, e0, e1, f0, f1 = events(2), events(3), events(1), events(5), events(0), events(4)
 t0 = mma[0][1]
 # granules in issue order: final events 0x400 + hf*16 + j*2 + kb ; a granule completes at kb == 1
-gr = [[c, t, t] for c, t in mma if c >= 0x400]
+gr = [[c, t, t] for c, t in fin if c >= 0x400]
 seen0 = [t for c, t in e0 if 0x200 <= c < 0x210]
 arr0 = [t for c, t in e0 if 0x210 <= c < 0x220]
 seen1 = [t for c, t in e1 if 0x200 <= c < 0x210]
@@ -43,5 +43,12 @@ for g in range(160, min(184, len(gr) - 2)):
     nxt = gr[g + 2][1] - t0 if g + 2 < len(gr) else -1
     print(f"g={g:4d} code={gr[g][0]:x}  {gr[g][1]-t0:8d} {gr[g][2]-t0:8d}   {seen0[g]-t0:8d} {seen1[g]-t0:8d}   {arr0[g]-t0:8d} {arr1[g]-t0:8d}    next {nxt:8d}")
 print("mid issues (code, t):", [(hex(c), t - t0) for c, t in mma if c < 0x400][60:72])
+W = 200000
+def win(ev, lo=W, hi=W + 9000):
+    return [(hex(c), t - t0) for c, t in ev if lo <= t - t0 < hi]
+print("WINDOW front0:", win(f0))
+print("WINDOW front1:", win(f1))
+print("WINDOW final :", win(fin))
+print("WINDOW mma   :", win(mma))
 print("front0:", [(hex(c), t - t0) for c, t in f0][220:245])
 print("front1:", [(hex(c), t - t0) for c, t in f1][220:245])
