@@ -560,6 +560,7 @@ static int build_chain(pcp_model *m, TcState *ts, TcChain &c, int l0_id, const i
 
 void model_destroy_bf16(pcp_model *m)
 {
+    heads_tc_destroy(m);
     if (!m->tc) return;
     TcState *ts = reinterpret_cast<TcState *>(m->tc);
     for (void *p : ts->allocs) cudaFree(p);
@@ -575,6 +576,7 @@ int model_prepare_bf16(pcp_model *m)
     m->tc = ts;
     std::vector<float> fold(m->n_fold);
     PCP_CUDA_OK(cudaMemcpy(fold.data(), m->d_fold, m->n_fold * sizeof(float), cudaMemcpyDeviceToHost));
+    PCP_TRY(heads_tc_prepare(m, fold));
     if (!m->desc.vanilla) {
         const int midA[1] = {L_IT_C2};
         PCP_TRY(build_chain(m, ts, ts->A, L_IT_C1, midA, 1, L_IT_C3, fold));
@@ -595,18 +597,26 @@ __global__ void __launch_bounds__(256)
 fold_r64_kernel(const float *__restrict__ R64, const float *__restrict__ W, uint8_t *__restrict__ img)
 {
     __shared__ float sW[64 * 64];
+    __shared__ float sR[64 * 65];
     const int64_t cloud = blockIdx.x;
-    for (int i = threadIdx.x; i < 4096; i += 256) sW[i] = W[i];
-    __syncthreads();
     const float *R = R64 + cloud * 4096;
+    for (int i = threadIdx.x; i < 4096; i += 256) { sW[i] = W[i]; sR[(i >> 6) * 65 + (i & 63)] = R[i]; }
+    __syncthreads();
     uint16_t *out = reinterpret_cast<uint16_t *>(img + cloud * 8192);
-    for (int e = threadIdx.x; e < 4096; e += 256) {
-        const int k = e >> 6, n = e & 63;
-        float acc = 0.f;
-#pragma unroll 8
-        for (int mm = 0; mm < 64; ++mm) acc = fmaf(__ldg(R + k * 64 + mm), sW[mm * 64 + n], acc);
-        const __nv_bfloat16 h = __float2bfloat16_rn(acc);
-        out[sw128_offset(64, (uint32_t)n, (uint32_t)k) / 2] = *reinterpret_cast<const uint16_t *>(&h);
+    // thread -> (k, 16 consecutive n): sR reads are conflict-free (stride 65), sW reads broadcast-friendly
+    const int k = threadIdx.x >> 2, n0 = (threadIdx.x & 3) * 16;
+    float acc[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+    for (int mm = 0; mm < 64; ++mm) {
+        const float r = sR[k * 65 + mm];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc[j] = fmaf(r, sW[mm * 64 + n0 + j], acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const __nv_bfloat16 h = __float2bfloat16_rn(acc[j]);
+        out[sw128_offset(64, (uint32_t)(n0 + j), (uint32_t)k) / 2] = *reinterpret_cast<const uint16_t *>(&h);
     }
 }
 
@@ -691,9 +701,9 @@ int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_
         PCP_CUDA_OK(cudaMemsetAsync(ws.g1, 0, (size_t)b * 1024 * sizeof(float), st));
         PCP_CUDA_OK(cudaMemsetAsync(ws.g2, 0, (size_t)b * 1024 * sizeof(float), st));
         PCP_TRY(launch_chain(ts, ts->A, d_x, b, n, nullptr, nullptr, ws.g1, st));
-        PCP_TRY(model_tnet_tail(m, 0, ws.g1, b, Rout, st));
+        PCP_TRY(heads_tc_tnet_tail(m, 0, ws.g1, b, Rout, st));
         PCP_TRY(launch_chain(ts, ts->B, d_x, b, n, Rout, nullptr, ws.g2, st));
-        PCP_TRY(model_tnet_tail(m, 1, ws.g2, b, ws.R64, st));
+        PCP_TRY(heads_tc_tnet_tail(m, 1, ws.g2, b, ws.R64, st));
         fold_r64_kernel<<<b, 256, 0, st>>>(ws.R64, m->d_fold + m->layers[L_S2_1].fold_w, ts->wc);
         PCP_CHECK_LAUNCH();
         PCP_TRY(launch_chain(ts, ts->C, d_x, b, n, Rout, ts->wc, ws.g3, st));
@@ -701,8 +711,9 @@ int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_
         if (d_R) PCP_TRY(model_eye3(d_R, b, st));
         PCP_TRY(launch_chain(ts, ts->C, d_x, b, n, nullptr, nullptr, ws.g3, st));
     }
-    if (heads & PCP_HEAD_CLS) PCP_TRY(model_cls_head(m, ws.g3, b, d_cls, d_cls_logits, st));
-    if (heads & PCP_HEAD_SEG) PCP_TRY(model_seg_head_fp32(m, d_x, b, n, full ? Rout : nullptr, full ? ws.R64 : nullptr, ws.g3, d_seg, d_seg_logits, st));
+    if ((heads & PCP_HEAD_CLS) && (d_cls || d_cls_logits)) PCP_TRY(heads_tc_cls(m, ws.g3, b, d_cls, d_cls_logits, st));
+    if ((heads & PCP_HEAD_SEG) && (d_seg || d_seg_logits))
+        PCP_TRY(heads_tc_seg(m, d_x, b, n, ts->centroid, ts->scale, full ? Rout : nullptr, full ? ws.R64 : nullptr, ws.g3, d_seg, d_seg_logits, st));
     (void)C;
     return PCP_OK;
 }

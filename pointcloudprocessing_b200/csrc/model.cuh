@@ -77,6 +77,7 @@ struct pcp_model {
     void *train_ws = nullptr;
     // bf16 tensor-core images (chain_tc.cu)
     void *tc = nullptr;
+    void *tc_heads = nullptr;   // heads_tc.cu
 };
 
 namespace pcp {
@@ -87,6 +88,12 @@ int softmax_rows(const float *d_logits, float *d_prob, int64_t rows, int cols, c
 int model_tnet_tail(pcp_model *m, int which, const float *pooled, int bc, float *out, cudaStream_t st);
 int model_eye3(float *d_R, int b, cudaStream_t st);
 int model_cls_head(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st);
+int heads_tc_prepare(pcp_model *m, const std::vector<float> &fold);
+void heads_tc_destroy(pcp_model *m);
+int heads_tc_tnet_tail(pcp_model *m, int which, const float *pooled, int b, float *out, cudaStream_t st);
+int heads_tc_cls(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st);
+int heads_tc_seg(pcp_model *m, const float *d_x, int b, int64_t n, const float *centroid, const float *scale, const float *d_R,
+                 const float *d_R64, const float *g3, float *d_seg, float *d_seg_logits, cudaStream_t st);
 int model_seg_head_fp32(pcp_model *m, const float *d_x, int b, int64_t n, const float *d_R, const float *d_R64, const float *g3,
                         float *d_seg, float *d_seg_logits, cudaStream_t st);
 }

@@ -1,0 +1,231 @@
+// tc_gemm.cu — generic bf16 tcgen05 GEMM: 128 x BNt output tile per CTA, K streamed in 64-element blocks
+// through a 3-stage shared-memory ring.  A tiles are converted (fp32 -> bf16 if needed) and written by four
+// producer warps straight into the K-major SWIZZLE_128B operand image; weight tiles arrive pre-packed by
+// cp.async.bulk; one elected thread issues tcgen05.mma; the producer warps then run the epilogue
+// (TMEM -> registers -> bias / ReLU / softmax -> global).  96 KB smem + 128 TMEM columns => 2 CTAs per SM.
+#include <cstring>
+
+#include "tc_gemm.cuh"
+#include "umma.cuh"
+
+namespace pcp {
+
+using namespace umma;
+
+constexpr int kGemmThreads = 192;     // warps 0-3 producer + epilogue, warp 4 MMA issuer, warp 5 weight loader
+constexpr int kGemmStages = 3;
+constexpr uint32_t kGemmStageBytes = 32768;   // 16 KB A + up to 16 KB B
+constexpr uint32_t kGemmSmem = kGemmStages * kGemmStageBytes + 1024;
+
+__global__ void __launch_bounds__(kGemmThreads, 2)
+tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full[kGemmStages], empty[kGemmStages], acc_full;
+    __shared__ uint32_t tmem_base;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nt = blockIdx.x;
+    const int g = blockIdx.y / mtiles, mt = blockIdx.y % mtiles;
+    const int row0 = mt * 128;
+    const int rows_valid = min(128, p.M - row0);
+    const int KT = p.K >> 6;
+    const uint32_t b_tile_bytes = (uint32_t)bnt * 128u;
+
+    if (tid == 0) {
+        for (int i = 0; i < kGemmStages; ++i) { mbar_init(&full[i], 5); mbar_init(&empty[i], 1); }
+        mbar_init(&acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 4) tmem_alloc(&tmem_base, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base;
+
+    if (warp < 4) {
+        // ---------------- A producer: 8 threads per row (16 B chunks), 16 rows per pass ----------------
+        const int chunk = tid & 7, rsub = tid >> 3;
+        const char *Abase = reinterpret_cast<const char *>(p.A);
+        const size_t esz = p.a_f32 ? 4 : 2;
+        const size_t a_off = ((size_t)g * p.a_group_stride + (size_t)row0 * p.lda) * esz;
+        // software pipeline: the global loads of k-tile kt+1 are in flight while k-tile kt is written to smem
+        auto load_tile = [&](int kt, uint4 (&v)[8]) {
+#pragma unroll
+            for (int pass = 0; pass < 8; ++pass) {
+                const int r = pass * 16 + rsub;
+                v[pass] = make_uint4(0u, 0u, 0u, 0u);
+                if (r < rows_valid) {
+                    const char *src = Abase + a_off + ((size_t)r * p.lda + (size_t)kt * 64 + chunk * 8) * esz;
+                    if (p.a_f32) {
+                        const float4 f0 = __ldg(reinterpret_cast<const float4 *>(src));
+                        const float4 f1 = __ldg(reinterpret_cast<const float4 *>(src) + 1);
+                        v[pass] = make_uint4(pack_bf16x2(f0.x, f0.y), pack_bf16x2(f0.z, f0.w), pack_bf16x2(f1.x, f1.y), pack_bf16x2(f1.z, f1.w));
+                    } else {
+                        v[pass] = __ldg(reinterpret_cast<const uint4 *>(src));
+                    }
+                }
+            }
+        };
+        uint4 cur[8], nxt[8];
+        load_tile(0, cur);
+        for (int kt = 0; kt < KT; ++kt) {
+            const int s = kt % kGemmStages;
+            if (kt + 1 < KT) load_tile(kt + 1, nxt);
+            if (kt >= kGemmStages) mbar_wait(&empty[s], (uint32_t)(((kt / kGemmStages) - 1) & 1), 40);
+            uint8_t *As = base + s * kGemmStageBytes;
+#pragma unroll
+            for (int pass = 0; pass < 8; ++pass)
+                *reinterpret_cast<uint4 *>(As + sw128_offset(128, (uint32_t)(pass * 16 + rsub), (uint32_t)chunk * 8)) = cur[pass];
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full[s]);
+#pragma unroll
+            for (int pass = 0; pass < 8; ++pass) cur[pass] = nxt[pass];
+        }
+        // ---------------- epilogue: thread = output row ----------------
+        mbar_wait(&acc_full, 0, 41);
+        tc_fence_after();
+        const int row = tid;
+        const bool row_ok = row < rows_valid;
+        const float *bias = p.bias ? p.bias + (size_t)g * p.bias_group_stride : nullptr;
+        const size_t c_off = (size_t)g * p.c_group_stride + (size_t)(row0 + row) * p.ldc;
+        for (int c0 = 0; c0 < bnt; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+            tmem_ld_wait();
+            float o[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+                const int n = nt * bnt + c0 + e;
+                float f = __uint_as_float(v[e]) + ((bias && n < p.N) ? __ldg(bias + n) : 0.f);
+                if (p.relu) f = f > 0.f ? f : 0.f;
+                o[e] = f;
+            }
+            if (row_ok) {
+                const int nbase = nt * bnt + c0;
+                if (p.C32) {
+                    float *dst = p.C32 + c_off + nbase;
+                    if (nbase + 32 <= p.N && (p.ldc & 3) == 0 && (((uintptr_t)dst & 15u) == 0)) {
+#pragma unroll
+                        for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4 *>(dst + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) if (nbase + e < p.N) dst[e] = o[e];
+                    }
+                }
+                if (p.C16) {
+                    __nv_bfloat16 *dst = p.C16 + c_off + nbase;
+                    if (nbase + 32 <= p.N && (p.ldc & 7) == 0 && (((uintptr_t)dst & 15u) == 0)) {
+#pragma unroll
+                        for (int e = 0; e < 32; e += 8)
+                            *reinterpret_cast<uint4 *>(dst + e) = make_uint4(pack_bf16x2(o[e], o[e + 1]), pack_bf16x2(o[e + 2], o[e + 3]),
+                                                                            pack_bf16x2(o[e + 4], o[e + 5]), pack_bf16x2(o[e + 6], o[e + 7]));
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) if (nbase + e < p.N) dst[e] = __float2bfloat16_rn(o[e]);
+                    }
+                }
+                if (p.Csoftmax && c0 == 0) {      // N <= 32: the whole row is in this chunk
+                    float mx = -3.0e38f;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) if (e < p.N) mx = fmaxf(mx, o[e]);
+                    float sum = 0.f;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) { o[e] = (e < p.N) ? __expf(o[e] - mx) : 0.f; sum += o[e]; }
+                    const float inv = 1.0f / sum;
+                    float *dst = p.Csoftmax + c_off;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) if (e < p.N) dst[e] = o[e] * inv;
+                }
+            }
+        }
+    } else if (warp == 4) {
+        // ---------------- MMA issuer ----------------
+        const uint32_t idesc = make_idesc_bf16(128, (uint32_t)bnt);
+        const uint32_t lo_base = (smem_u32(base) & 0x3FFFFu) >> 4;
+        for (int kt = 0; kt < KT; ++kt) {
+            const int s = kt % kGemmStages;
+            mbar_wait(&full[s], (uint32_t)((kt / kGemmStages) & 1), 42);
+            tc_fence_after();
+            const uint32_t a_lo = lo_base + (uint32_t)s * (kGemmStageBytes >> 4), b_lo = a_lo + (16384u >> 4);
+            if (elect_one_sync()) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) mma_bf16_ss(tmem, sdesc_from_lo(a_lo + k * 2), sdesc_from_lo(b_lo + k * 2), idesc, (kt | k) > 0);
+                mma_commit(&empty[s]);
+                if (kt == KT - 1) mma_commit(&acc_full);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ---------------- weight-tile loader ----------------
+        if (lane == 0) {
+            const uint8_t *img = p.Bimg + (size_t)g * p.b_group_stride + (size_t)nt * KT * b_tile_bytes;
+            for (int kt = 0; kt < KT; ++kt) {
+                const int s = kt % kGemmStages;
+                if (kt >= kGemmStages) mbar_wait(&empty[s], (uint32_t)(((kt / kGemmStages) - 1) & 1), 43);
+                mbar_arrive_expect_tx(&full[s], b_tile_bytes);
+                bulk_g2s(base + s * kGemmStageBytes + 16384, img + (size_t)kt * b_tile_bytes, b_tile_bytes, &full[s]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc(tmem, 128);
+}
+
+static inline uint16_t f2bf_host(float f)
+{
+    uint32_t u; memcpy(&u, &f, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+
+size_t gemm_b_image_bytes(int K, int N)
+{
+    const int bnt = tc_gemm_bn_tile(N);
+    const int ntiles = (N + bnt - 1) / bnt;
+    return (size_t)ntiles * (K / 64) * bnt * 128;
+}
+
+void pack_gemm_b_image(const float *W, int K, int N, std::vector<uint16_t> &img)
+{
+    const int bnt = tc_gemm_bn_tile(N), ntiles = (N + bnt - 1) / bnt, KT = K / 64;
+    img.assign(gemm_b_image_bytes(K, N) / 2, 0);
+    for (int nt = 0; nt < ntiles; ++nt)
+        for (int kt = 0; kt < KT; ++kt) {
+            uint16_t *tile = img.data() + ((size_t)nt * KT + kt) * (bnt * 64);
+            for (int r = 0; r < bnt; ++r) {
+                const int n = nt * bnt + r;
+                if (n >= N) continue;
+                for (int k = 0; k < 64; ++k) tile[sw128_offset((uint32_t)bnt, (uint32_t)r, (uint32_t)k) / 2] = f2bf_host(W[(size_t)(kt * 64 + k) * N + n]);
+            }
+        }
+}
+
+int tc_gemm(const TcGemmParams &p, cudaStream_t st)
+{
+    PCP_REQUIRE(p.A && p.Bimg && (p.C32 || p.C16 || p.Csoftmax), PCP_ERR_INVALID, "tc_gemm: null operand");
+    PCP_REQUIRE(p.K >= 64 && p.K % 64 == 0, PCP_ERR_UNSUPPORTED, "tc_gemm: K=%d must be a multiple of 64", p.K);
+    PCP_REQUIRE(p.N >= 1 && (p.N <= 128 || p.N % 128 == 0), PCP_ERR_UNSUPPORTED, "tc_gemm: N=%d must be <= 128 or a multiple of 128", p.N);
+    PCP_REQUIRE(!p.Csoftmax || p.N <= 32, PCP_ERR_UNSUPPORTED, "tc_gemm: softmax epilogue needs N <= 32");
+    PCP_REQUIRE((p.lda % (p.a_f32 ? 4 : 8)) == 0, PCP_ERR_UNSUPPORTED, "tc_gemm: lda must keep 16-byte row chunks aligned");
+    if (p.M <= 0 || p.groups <= 0) return PCP_OK;
+    const int bnt_img = tc_gemm_bn_tile(p.N);   // MMA N (multiple of 16); the epilogue reads 32-column TMEM chunks and masks n >= N
+    const int ntiles = (p.N + bnt_img - 1) / bnt_img;
+    const int mtiles = (p.M + 127) / 128;
+    const int64_t gy = (int64_t)mtiles * p.groups;
+    static bool attr = false;
+    if (!attr) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
+        attr = true;
+    }
+    PCP_REQUIRE(gy <= 65535, PCP_ERR_UNSUPPORTED, "tc_gemm: %lld row tiles exceed one launch", (long long)gy);
+    tc_gemm_kernel<<<dim3(ntiles, (unsigned)gy), kGemmThreads, kGemmSmem, st>>>(p, bnt_img, mtiles);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+}  // namespace pcp
