@@ -183,8 +183,10 @@ typedef struct pcp_train_config {
     float lr0, decay_rate;         /* ExponentialDecay, pointnet_train.py:310-315 */
     int32_t decay_steps;
     float beta1, beta2, eps;       /* keras Adam defaults 0.9 / 0.999 / 1e-7 */
-    uint64_t dropout_seed;
+    uint64_t dropout_seed;         /* Philox key of the Dropout masks (vary it per step) */
+    int64_t sample_offset;         /* global index of this shard's first cloud: masks are shard-count invariant */
     int32_t use_dropout_masks;     /* 1: d_mask1/d_mask2 given explicitly (parity tests) */
+    int32_t skip_unweighted_heads; /* 1: skip the segmentation head when it is frozen and w_seg == 0 (its metrics read 0) */
 } pcp_train_config;
 
 /* One training step on the local shard: forward (training BN on thawed layers, dropout),
@@ -195,11 +197,21 @@ int pcp_model_loss_backward(pcp_model *m, const float *d_x, int b, int64_t n, co
                             const int32_t *d_y_seg, const float *d_y_se3, const pcp_train_config *cfg,
                             int global_batch, const float *d_mask1, const float *d_mask2, float *h_metrics,
                             pcp_stream stream);
+/* keras Model.evaluate / the validation pass of fit (pointnet_train.py:221-228): inference-mode forward and the
+ * same 8 metrics as pcp_model_loss_backward (feature-transform regulariser excluded: R64 is not materialised at
+ * inference).  Label pointers may be NULL (that loss reads 0; NULL d_y_seg skips the segmentation head). */
+int pcp_model_evaluate(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *d_y_cls, const int32_t *d_y_seg,
+                       const float *d_y_se3, const pcp_train_config *cfg, float *h_metrics, pcp_stream stream);
 /* flat fp32 gradient buffer (device) for the NCCL all-reduce done by the host side */
 int pcp_model_grad_buffer(pcp_model *m, float **d_grads, size_t *count);
 /* fused Adam + ExponentialDecay over the flat buffer; step is 0-based (lr uses step, bias
  * correction uses step+1), frozen tensors are skipped. */
 int pcp_model_adam_step(pcp_model *m, const pcp_train_config *cfg, int64_t step, pcp_stream stream);
+/* outputs of the last training-mode forward, copied to the host (tests / metrics): which = 0 cls probabilities
+ * (b,C), 1 seg probabilities (b,n,P), 2 R (b,3,3), 3 R64 (b,64,64), 4 global features (b,1024) */
+int pcp_model_get_train_output(pcp_model *m, int which, float *h_out, size_t count);
+/* zero the Adam moments: a fresh optimizer is compiled for every training profile (pointnet_train.py:310-319) */
+int pcp_model_reset_optimizer(pcp_model *m);
 /* copy one gradient tensor to the host (tests) */
 int pcp_model_get_grad(pcp_model *m, const char *name, float *h_data, size_t count);
 

@@ -38,7 +38,8 @@ class TrainConfig(C.Structure):
         ("w_cls", C.c_float), ("w_seg", C.c_float), ("w_rot", C.c_float),
         ("lr0", C.c_float), ("decay_rate", C.c_float), ("decay_steps", C.c_int32),
         ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
-        ("dropout_seed", C.c_uint64), ("use_dropout_masks", C.c_int32),
+        ("dropout_seed", C.c_uint64), ("sample_offset", C.c_int64), ("use_dropout_masks", C.c_int32),
+        ("skip_unweighted_heads", C.c_int32),
     ]
 
 
@@ -85,9 +86,12 @@ SIGNATURES = {
     "pcp_selftest_umma2": (_i32, [_fp, _fp, _i32, _i32, _fp]),
     "pcp_model_set_trainable": (_i32, [_vp, _i32, _i32]),
     "pcp_model_loss_backward": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, C.POINTER(TrainConfig), _i32, _vp, _vp, _fp, _vp]),
+    "pcp_model_evaluate": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, C.POINTER(TrainConfig), _fp, _vp]),
     "pcp_model_grad_buffer": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),
     "pcp_model_adam_step": (_i32, [_vp, C.POINTER(TrainConfig), _i64, _vp]),
+    "pcp_model_reset_optimizer": (_i32, [_vp]),
     "pcp_model_get_grad": (_i32, [_vp, C.c_char_p, _fp, _sz]),
+    "pcp_model_get_train_output": (_i32, [_vp, _i32, _fp, _sz]),
 }
 
 

@@ -411,6 +411,7 @@ extern "C" int pcp_model_destroy(pcp_model *m)
     if (!m) return PCP_OK;
     ws_free(m->ws);
     model_destroy_bf16(m);
+    train_destroy(m);
     cudaFree(m->d_params); cudaFree(m->d_fold);
     cudaFree(m->d_grads); cudaFree(m->d_adam_m); cudaFree(m->d_adam_v);
     delete m;
@@ -518,7 +519,7 @@ extern "C" int pcp_model_forward(pcp_model *m, const float *d_x, int b, int64_t 
                                  float *d_R, float *d_cls_logits, float *d_seg_logits, pcp_stream stream)
 {
     PCP_REQUIRE(m && d_x && b >= 1 && n >= 1, PCP_ERR_INVALID, "pcp_model_forward: bad arguments");
-    PCP_REQUIRE(m->prepared, PCP_ERR_STATE, "pcp_model_forward: call pcp_model_prepare first");
+    if (!m->prepared) PCP_TRY(pcp_model_prepare(m));      // parameters changed (set_tensor / training step): refold lazily
     PCP_REQUIRE(!(d_cls || d_cls_logits) || (heads & PCP_HEAD_CLS), PCP_ERR_INVALID, "pcp_model_forward: cls output without PCP_HEAD_CLS");
     PCP_REQUIRE(!(d_seg || d_seg_logits) || (heads & PCP_HEAD_SEG), PCP_ERR_INVALID, "pcp_model_forward: seg output without PCP_HEAD_SEG");
     if (m->ws.total_b < b || m->ws.cap_n != n) PCP_TRY(pcp_model_reserve(m, b, n));

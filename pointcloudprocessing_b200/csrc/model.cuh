@@ -94,6 +94,7 @@ int heads_tc_tnet_tail(pcp_model *m, int which, const float *pooled, int b, floa
 int heads_tc_cls(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st);
 int heads_tc_seg(pcp_model *m, const float *d_x, int b, int64_t n, const float *centroid, const float *scale, const float *d_R,
                  const float *d_R64, const float *g3, float *d_seg, float *d_seg_logits, cudaStream_t st);
+void train_destroy(pcp_model *m);
 int model_seg_head_fp32(pcp_model *m, const float *d_x, int b, int64_t n, const float *d_R, const float *d_R64, const float *g3,
                         float *d_seg, float *d_seg_logits, cudaStream_t st);
 }

@@ -1,4 +1,14 @@
-// train.cu — training step of pointnet_train.py:310-351: losses, backward, fused Adam.
+// train.cu — the training step of pointnet_train.py:310-351 on the device: training-mode forward of
+// PointNet.call (pointnet/PointNet.py:197-292: batch-statistics BatchNormalization on thawed layers,
+// Dropout), the three losses (SCCE on probabilities with the 1e-7 clip, MSE on R, T-Net regulariser
+// PointNet.py:447-451), the full backward pass into one flat gradient buffer, and fused keras Adam.
+//
+// Structure: every weighted layer is Z = A . W (GEMM), then BN (batch or moving statistics) + ReLU as an
+// elementwise pass.  Pre-BN activations Z are kept for the backward pass; post-activation tensors are
+// recomputed from Z when a weight gradient needs them.  The reduce_max over points (PointNet.py:248,429) is
+// fused with BN + ReLU into one column-max pass and its gradient is split evenly between tied maxima (the
+// tf.reduce_max convention).  GEMMs go through train_mm_* below: fp32 CUDA-core tiles in
+// PCP_PRECISION_FP32, bf16 tcgen05 tiles with fp32 accumulation in PCP_PRECISION_BF16 (tc_train.cu).
 #include <cmath>
 #include <cstring>
 
@@ -7,10 +17,15 @@
 
 namespace pcp {
 
+static const float kBnEpsT = 1e-3f;       // keras BatchNormalization epsilon
+static const float kBnMomentum = 0.99f;   // PointNet.py:502,528
+
+// ------------------------------------------------------------------------------------------------
 // Fused keras Adam over the flat parameter buffer (pointnet_train.py:317-319):
 //   m = b1*m + (1-b1)*g ; v = b2*v + (1-b2)*g^2 ; w -= alpha * m / (sqrt(v) + eps),
 //   alpha = lr * sqrt(1-b2^t) / (1-b1^t).  28 B/parameter of HBM traffic (read w,g,m,v; write w,m,v).
 // `mask` holds one byte per 4-float group: 0 => frozen / BN statistic, skipped.
+// ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 adam_kernel(float4 *__restrict__ w, const float4 *__restrict__ g, float4 *__restrict__ m, float4 *__restrict__ v,
             const unsigned char *__restrict__ mask, size_t n4, float alpha, float b1, float b2, float eps)
@@ -29,10 +44,409 @@ adam_kernel(float4 *__restrict__ w, const float4 *__restrict__ g, float4 *__rest
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Column-wise kernels over a row-major (rows x C) activation.  C is a multiple of 64, C <= 1024.
+// Thread mapping (256 threads): C >= 256 -> each thread owns C/256 strided columns of one row lane;
+// C < 256 -> 256/C row lanes run side by side.  Loads are coalesced across the columns of a row.
+// ------------------------------------------------------------------------------------------------
+struct BnP {
+    const float *mean, *sc, *beta, *inv;      // pre = (z - mean) * sc + beta ; xhat = (z - mean) * inv ; sc = gamma * inv
+};
+
+__device__ __forceinline__ float bn_pre(float z, float mean, float sc, float beta) { return fmaf(z - mean, sc, beta); }
+
+struct ColMap {
+    int cpt, lanes, col0, lane;
+    __device__ ColMap(int C) {
+        cpt = C >= 256 ? C / 256 : 1;
+        lanes = C >= 256 ? 1 : 256 / C;
+        col0 = C >= 256 ? (int)threadIdx.x : (int)threadIdx.x % C;
+        lane = C >= 256 ? 0 : (int)threadIdx.x / C;
+    }
+};
+
+// cross-lane reduction of up to 4 per-thread doubles into lane 0 (shared scratch: 256 doubles)
+__device__ __forceinline__ void lane_reduce(double *sh, const ColMap &cm, int C, double (&v)[4])
+{
+    if (cm.lanes == 1) return;
+    __syncthreads();
+    sh[threadIdx.x] = v[0];
+    __syncthreads();
+    if (cm.lane == 0) {
+        double s = 0;
+        for (int l = 0; l < cm.lanes; ++l) s += sh[l * C + cm.col0];
+        v[0] = s;
+    }
+}
+
+// sum / sum of squares per column (BatchNormalization batch statistics, biased variance)
+__global__ void __launch_bounds__(256)
+colstats_kernel(const float *__restrict__ Z, int64_t rows, int C, double *__restrict__ sum, double *__restrict__ sumsq)
+{
+    __shared__ double sh[256];
+    const ColMap cm(C);
+    const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
+    const int64_t r0 = (int64_t)blockIdx.x * per, r1 = min(rows, r0 + per);
+    double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
+    for (int64_t r = r0 + cm.lane; r < r1; r += cm.lanes) {
+        const float *zr = Z + r * C;
+#pragma unroll 4
+        for (int j = 0; j < cm.cpt; ++j) {
+            const double z = (double)__ldg(zr + cm.col0 + j * 256);
+            s[j] += z; q[j] += z * z;
+        }
+    }
+    lane_reduce(sh, cm, C, s);
+    lane_reduce(sh, cm, C, q);
+    if (cm.lane == 0 && r1 > r0)
+        for (int j = 0; j < cm.cpt; ++j) {
+            atomicAdd(sum + cm.col0 + j * 256, s[j]);
+            atomicAdd(sumsq + cm.col0 + j * 256, q[j]);
+        }
+}
+
+// batch statistics -> (mean, inv, sc, beta) and the moving-average update; or the moving statistics when the
+// layer is frozen (keras: training and trainable)
+__global__ void bn_finalize_kernel(const double *__restrict__ sum, const double *__restrict__ sumsq, double rows, int C, int batch,
+                                   const float *__restrict__ gamma, const float *__restrict__ beta_in, float *__restrict__ mov_mean,
+                                   float *__restrict__ mov_var, float *__restrict__ mean, float *__restrict__ inv, float *__restrict__ sc,
+                                   float *__restrict__ beta, float eps, float momentum)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float mu, var;
+    if (batch) {
+        const double m = sum[c] / rows;
+        double v = sumsq[c] / rows - m * m;
+        if (v < 0) v = 0;
+        mu = (float)m; var = (float)v;
+        mov_mean[c] = momentum * mov_mean[c] + (1.f - momentum) * mu;
+        mov_var[c] = momentum * mov_var[c] + (1.f - momentum) * var;
+    } else {
+        mu = mov_mean[c]; var = mov_var[c];
+    }
+    const float iv = 1.0f / sqrtf(var + eps);
+    mean[c] = mu; inv[c] = iv; sc[c] = gamma[c] * iv; beta[c] = beta_in[c];
+}
+
+// Y = relu((Z - mean) * sc + beta)
+__global__ void __launch_bounds__(256)
+bn_act_kernel(const float4 *__restrict__ Z, int64_t n4, int C4, BnP p, float4 *__restrict__ Y)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C4) * 4;
+        const float4 z = __ldg(Z + i);
+        const float4 mu = __ldg(reinterpret_cast<const float4 *>(p.mean + c)), s = __ldg(reinterpret_cast<const float4 *>(p.sc + c)),
+                     be = __ldg(reinterpret_cast<const float4 *>(p.beta + c));
+        float4 y;
+        y.x = fmaxf(bn_pre(z.x, mu.x, s.x, be.x), 0.f); y.y = fmaxf(bn_pre(z.y, mu.y, s.y, be.y), 0.f);
+        y.z = fmaxf(bn_pre(z.z, mu.z, s.z, be.z), 0.f); y.w = fmaxf(bn_pre(z.w, mu.w, s.w, be.w), 0.f);
+        Y[i] = y;
+    }
+}
+
+// per cloud: gmax[cloud, c] = max over the cloud's points of relu(bn(Z))   (zero-initialised; values >= 0)
+__global__ void __launch_bounds__(256)
+bn_relu_colmax_kernel(const float *__restrict__ Z, int64_t n, int C, BnP p, float *__restrict__ gmax)
+{
+    const ColMap cm(C);
+    const int64_t cloud = blockIdx.y;
+    const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+    const int64_t r0 = (int64_t)blockIdx.x * per, r1 = min(n, r0 + per);
+    float mu[4], s[4], be[4], mx[4];
+    for (int j = 0; j < cm.cpt; ++j) {
+        const int c = cm.col0 + j * 256;
+        mu[j] = p.mean[c]; s[j] = p.sc[c]; be[j] = p.beta[c]; mx[j] = 0.f;
+    }
+    for (int64_t r = r0 + cm.lane; r < r1; r += cm.lanes) {
+        const float *zr = Z + (cloud * n + r) * C;
+#pragma unroll 4
+        for (int j = 0; j < cm.cpt; ++j) mx[j] = fmaxf(mx[j], bn_pre(__ldg(zr + cm.col0 + j * 256), mu[j], s[j], be[j]));
+    }
+    if (r1 > r0)
+        for (int j = 0; j < cm.cpt; ++j)
+            atomicMax(reinterpret_cast<unsigned int *>(gmax + cloud * C + cm.col0 + j * 256), __float_as_uint(mx[j]));
+}
+
+// tie count of the per-cloud maximum (even gradient split of tf.reduce_max)
+__global__ void __launch_bounds__(256)
+pool_count_kernel(const float *__restrict__ Z, int64_t n, int C, BnP p, const float *__restrict__ gmax, int *__restrict__ cnt)
+{
+    const ColMap cm(C);
+    const int64_t cloud = blockIdx.y;
+    const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+    const int64_t r0 = (int64_t)blockIdx.x * per, r1 = min(n, r0 + per);
+    float mu[4], s[4], be[4], g[4];
+    int k[4] = {0, 0, 0, 0};
+    for (int j = 0; j < cm.cpt; ++j) {
+        const int c = cm.col0 + j * 256;
+        mu[j] = p.mean[c]; s[j] = p.sc[c]; be[j] = p.beta[c]; g[j] = gmax[cloud * C + c];
+    }
+    for (int64_t r = r0 + cm.lane; r < r1; r += cm.lanes) {
+        const float *zr = Z + (cloud * n + r) * C;
+#pragma unroll 4
+        for (int j = 0; j < cm.cpt; ++j) {
+            const float y = fmaxf(bn_pre(__ldg(zr + cm.col0 + j * 256), mu[j], s[j], be[j]), 0.f);
+            k[j] += (y == g[j]) ? 1 : 0;
+        }
+    }
+    if (r1 > r0)
+        for (int j = 0; j < cm.cpt; ++j)
+            if (k[j]) atomicAdd(cnt + cloud * C + cm.col0 + j * 256, k[j]);
+}
+
+// dY[p, c] = dG[cloud, c] / cnt[cloud, c] where relu(bn(Z))[p, c] equals the pooled maximum, else 0
+__global__ void __launch_bounds__(256)
+pool_bwd_kernel(const float4 *__restrict__ Z, int64_t n4_per_cloud, int64_t total4, int C4, BnP p, const float *__restrict__ gmax,
+                const float *__restrict__ dG, const int *__restrict__ cnt, float4 *__restrict__ dY)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total4; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C4) * 4;
+        const int64_t cloud = i / n4_per_cloud;
+        const float4 z = __ldg(Z + i);
+        const float zz[4] = {z.x, z.y, z.z, z.w};
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float y = fmaxf(bn_pre(zz[j], p.mean[c + j], p.sc[c + j], p.beta[c + j]), 0.f);
+            const int64_t gi = cloud * (C4 * 4) + c + j;
+            o[j] = (y == gmax[gi]) ? dG[gi] / (float)cnt[gi] : 0.f;
+        }
+        dY[i] = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+// BN + ReLU backward, reduction half: s1[c] = sum dyh, s2[c] = sum dyh * xhat, dyh = dY * [pre > 0]
+__global__ void __launch_bounds__(256)
+bn_bwd_reduce_kernel(const float *__restrict__ dY, const float *__restrict__ Z, int64_t rows, int C, BnP p, int relu,
+                     double *__restrict__ s1, double *__restrict__ s2)
+{
+    __shared__ double sh[256];
+    const ColMap cm(C);
+    const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
+    const int64_t r0 = (int64_t)blockIdx.x * per, r1 = min(rows, r0 + per);
+    float mu[4], s[4], be[4], iv[4];
+    double a[4] = {0, 0, 0, 0}, b[4] = {0, 0, 0, 0};
+    for (int j = 0; j < cm.cpt; ++j) {
+        const int c = cm.col0 + j * 256;
+        mu[j] = p.mean[c]; s[j] = p.sc[c]; be[j] = p.beta[c]; iv[j] = p.inv[c];
+    }
+    for (int64_t r = r0 + cm.lane; r < r1; r += cm.lanes) {
+#pragma unroll 4
+        for (int j = 0; j < cm.cpt; ++j) {
+            const int64_t idx = r * C + cm.col0 + j * 256;
+            const float zc = __ldg(Z + idx) - mu[j];
+            float dy = __ldg(dY + idx);
+            if (relu && !(fmaf(zc, s[j], be[j]) > 0.f)) dy = 0.f;
+            a[j] += (double)dy; b[j] += (double)dy * (double)(zc * iv[j]);
+        }
+    }
+    lane_reduce(sh, cm, C, a);
+    lane_reduce(sh, cm, C, b);
+    if (cm.lane == 0 && r1 > r0)
+        for (int j = 0; j < cm.cpt; ++j) {
+            atomicAdd(s1 + cm.col0 + j * 256, a[j]);
+            atomicAdd(s2 + cm.col0 + j * 256, b[j]);
+        }
+}
+
+// BN + ReLU backward, elementwise half (in place on dY):
+//   batch statistics : dZ = sc * (dyh - s1/rows - xhat * s2/rows)
+//   moving statistics: dZ = sc * dyh
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(float4 *__restrict__ dY, const float4 *__restrict__ Z, int64_t n4, int C4, BnP p, int relu, int batch,
+                    const double *__restrict__ s1, const double *__restrict__ s2, float inv_rows)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C4) * 4;
+        const float4 z = __ldg(Z + i);
+        float4 d = dY[i];
+        const float zz[4] = {z.x, z.y, z.z, z.w};
+        float dd[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float zc = zz[j] - p.mean[c + j];
+            float dy = dd[j];
+            if (relu && !(fmaf(zc, p.sc[c + j], p.beta[c + j]) > 0.f)) dy = 0.f;
+            if (batch) dy = dy - (float)s1[c + j] * inv_rows - (zc * p.inv[c + j]) * ((float)s2[c + j] * inv_rows);
+            dd[j] = p.sc[c + j] * dy;
+        }
+        dY[i] = make_float4(dd[0], dd[1], dd[2], dd[3]);
+    }
+}
+
+__global__ void store_bn_grads_kernel(const double *__restrict__ s1, const double *__restrict__ s2, int C, float *__restrict__ dgamma,
+                                      float *__restrict__ dbeta)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < C) { dgamma[c] = (float)s2[c]; dbeta[c] = (float)s1[c]; }
+}
+
+// out[g, c] (+)= sum over the group's rows of X[(g*rpg + r), c]   (bias gradients; per-cloud sums of the seg head)
+__global__ void __launch_bounds__(256)
+group_colsum_kernel(const float *__restrict__ X, int64_t rpg, int C, float *__restrict__ out)
+{
+    const int64_t g = blockIdx.y;
+    const int64_t per = (rpg + gridDim.x - 1) / gridDim.x;
+    const int64_t r0 = (int64_t)blockIdx.x * per, r1 = min(rpg, r0 + per);
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float s = 0.f;
+        for (int64_t r = r0; r < r1; ++r) s += __ldg(X + (g * rpg + r) * C + c);
+        if (r1 > r0) atomicAdd(out + g * C + c, s);
+    }
+}
+
+// Philox keep-mask (Dropout, PointNet.py:255,260): counter = (global sample id, unit, layer), kept units scaled by 1/(1-rate)
+__device__ __forceinline__ float dropout_factor(uint64_t seed, uint64_t sample, uint32_t unit, uint32_t layer, float rate, float scale)
+{
+    uint32_t c[4] = {(uint32_t)sample, (uint32_t)(sample >> 32), unit, layer};
+    philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+    const float u = (float)(c[0] >> 8) * (1.0f / 16777216.0f);
+    return u >= rate ? scale : 0.f;
+}
+
+// H = Y * factor ; explicit mask (0/1 floats) when given, else Philox.  Also used for the backward (dY = dH * factor).
+__global__ void __launch_bounds__(256)
+dropout_kernel(const float *Y, int64_t rows, int C, const float *__restrict__ mask, uint64_t seed, int64_t sample0,
+               uint32_t layer, float rate, float *H)
+{
+    const float scale = 1.0f / (1.0f - rate);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < rows * C; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / C;
+        const int c = (int)(i % C);
+        const float f = mask ? mask[i] * scale : dropout_factor(seed, (uint64_t)(sample0 + r), (uint32_t)c, layer, rate, scale);
+        H[i] = Y[i] * f;
+    }
+}
+
+// softmax + SCCE on probabilities (keras from_logits=False: clip to [1e-7, 1-1e-7], -log; pointnet_train.py:337-338)
+// one thread per row; C <= 64.  dlogits = gscale * (p - onehot) unless the label probability is clipped (zero gradient).
+__global__ void __launch_bounds__(256)
+softmax_ce_kernel(const float *__restrict__ logits, int64_t rows, int C, const int32_t *__restrict__ labels, float gscale,
+                  float *__restrict__ prob, float *__restrict__ dlogits, double *__restrict__ loss_sum, double *__restrict__ correct)
+{
+    double lsum = 0, csum = 0;
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < rows; r += (int64_t)gridDim.x * blockDim.x) {
+        const float *z = logits + r * C;
+        float mx = z[0]; int am = 0;
+        for (int c = 1; c < C; ++c) if (z[c] > mx) { mx = z[c]; am = c; }
+        float s = 0.f;
+        for (int c = 0; c < C; ++c) s += expf(z[c] - mx);
+        const float inv = 1.0f / s;
+        const int y = labels[r];
+        const float py = expf(z[y] - mx) * inv;
+        const bool clipped = (py < 1e-7f) || (py > 1.0f - 1e-7f);
+        const float pc = fminf(fmaxf(py, 1e-7f), 1.0f - 1e-7f);
+        lsum += (double)(-logf(pc));
+        csum += (am == y) ? 1.0 : 0.0;
+        for (int c = 0; c < C; ++c) {
+            const float p = expf(z[c] - mx) * inv;
+            if (prob) prob[r * C + c] = p;
+            if (dlogits) dlogits[r * C + c] = clipped ? 0.f : gscale * (p - (c == y ? 1.f : 0.f));
+        }
+    }
+    lsum = warp_sum(lsum); csum = warp_sum(csum);
+    if ((threadIdx.x & 31) == 0) { atomicAdd(loss_sum, lsum); atomicAdd(correct, csum); }
+}
+
+// MSE(R, y_se3) (pointnet_train.py:339): dR += gscale * 2 (R - y); sq_sum += sum (R - y)^2
+__global__ void mse_kernel(const float *__restrict__ R, const float *__restrict__ y, int64_t count, float gscale, float *__restrict__ dR,
+                           double *__restrict__ sq_sum)
+{
+    double s = 0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+        const float d = R[i] - y[i];
+        s += (double)d * d;
+        if (dR) dR[i] += gscale * 2.f * d;
+    }
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) atomicAdd(sq_sum, s);
+}
+
+// T-Net orthogonality regulariser (PointNet.py:447-451): L = 1e-3 * sum_b 1/2 ||I - m m^T||_F^2 ; dm += -2e-3 (I - m m^T) m
+// one block per cloud; k = 3 or 64 (shared memory 2 * k*k floats)
+__global__ void __launch_bounds__(256)
+tnet_reg_kernel(const float *__restrict__ Mx, int k, float *__restrict__ dM, double *__restrict__ loss_sum)
+{
+    extern __shared__ float shm[];
+    float *m = shm, *D = shm + k * k;
+    __shared__ double red[8];
+    const float *src = Mx + (int64_t)blockIdx.x * k * k;
+    for (int i = threadIdx.x; i < k * k; i += blockDim.x) m[i] = src[i];
+    __syncthreads();
+    double l = 0;
+    for (int i = threadIdx.x; i < k * k; i += blockDim.x) {
+        const int r = i / k, c = i % k;
+        float acc = 0.f;
+        for (int j = 0; j < k; ++j) acc = fmaf(m[r * k + j], m[c * k + j], acc);
+        const float d = (r == c ? 1.f : 0.f) - acc;
+        D[i] = d;
+        l += 0.5 * (double)d * d;
+    }
+    __syncthreads();
+    if (dM) {
+        float *dst = dM + (int64_t)blockIdx.x * k * k;
+        for (int i = threadIdx.x; i < k * k; i += blockDim.x) {
+            const int r = i / k, c = i % k;
+            float acc = 0.f;
+            for (int j = 0; j < k; ++j) acc = fmaf(D[r * k + j], m[j * k + c], acc);
+            dst[i] += -2.0e-3f * acc;
+        }
+    }
+    l = warp_sum(l);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = l;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        atomicAdd(loss_sum, 1.0e-3 * t);
+    }
+}
+
+__global__ void axpy_kernel(float *__restrict__ y, const float *__restrict__ x, int64_t n, float a)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] += a * x[i];
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+struct TL {                       // one weighted layer's training record
+    int id = -1;
+    float *Z = nullptr;           // pre-BN output (rows x cout)
+    int64_t rows = 0;
+    int cin = 0, cout = 0;
+    bool has_bn = false, batch = false, trainable = false;
+    float *mean = nullptr, *inv = nullptr, *sc = nullptr, *beta = nullptr;
+    double *red = nullptr;        // 2 * cout doubles (forward: sum / sumsq ; backward: s1 / s2)
+    BnP bnp() const { return BnP{mean, sc, beta, inv}; }
+};
+
 struct TrainState {
     unsigned char *d_mask = nullptr;
     bool mask_valid = false;
     bool trainable_seen[4] = {false, false, false, false};
+    // activation arena
+    int b = 0; int64_t n = 0;
+    char *arena = nullptr; size_t arena_bytes = 0;
+    TL L[L_COUNT];
+    float *pcn = nullptr, *X3 = nullptr, *X2 = nullptr, *X64 = nullptr;
+    float *g1 = nullptr, *g2 = nullptr, *g3 = nullptr;             // pooled (b x 1024)
+    int *cnt = nullptr;                                            // (b x 1024) tie counts
+    float *R = nullptr, *R64 = nullptr, *dR = nullptr, *dR64 = nullptr;
+    float *Ys[8] = {nullptr};                                      // small-layer activations (rows = b)
+    float *H1 = nullptr, *H2 = nullptr;                            // after dropout
+    float *cls_logits = nullptr, *cls_prob = nullptr, *seg_logits = nullptr, *seg_prob = nullptr;
+    float *gvec = nullptr, *dgvec = nullptr;                       // per-cloud bias of seg_l1 (b x 512) and its gradient
+    float *dg1 = nullptr, *dg2 = nullptr, *dg3 = nullptr;
+    float *dsmall[4] = {nullptr};                                  // (b x 512), (b x 256), (b x C) ...
+    // per-point scratch
+    float *Y64a = nullptr, *Y64b = nullptr, *Y128 = nullptr, *Y128b = nullptr, *Y256 = nullptr, *Y512 = nullptr;
+    float *G1024 = nullptr, *G512 = nullptr, *G256 = nullptr, *G128a = nullptr, *G128b = nullptr, *G64a = nullptr, *G64b = nullptr;
+    float *GP = nullptr, *dX64 = nullptr, *dX2 = nullptr, *dX3 = nullptr;
+    double *metrics = nullptr;                                     // 8 doubles
+    bool have_seg = false;
+    char *eval_buf = nullptr; size_t eval_bytes = 0;               // pcp_model_evaluate: metrics + logits
 };
 
 static int ensure_train_buffers(pcp_model *m)
@@ -59,6 +473,504 @@ static int ensure_train_buffers(pcp_model *m)
         PCP_CUDA_OK(cudaMemcpy(ts->d_mask, mask.data(), mask.size(), cudaMemcpyHostToDevice));
         for (int g = 0; g < 4; ++g) ts->trainable_seen[g] = m->trainable[g];
         ts->mask_valid = true;
+    }
+    return PCP_OK;
+}
+
+void train_destroy(pcp_model *m)
+{
+    if (!m->train_ws) return;
+    TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
+    cudaFree(ts->d_mask);
+    cudaFree(ts->arena);
+    cudaFree(ts->eval_buf);
+    delete ts;
+    m->train_ws = nullptr;
+}
+
+// (re)build the activation arena for b clouds of n points
+static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
+{
+    if (ts->arena && ts->b == b && ts->n == n) return PCP_OK;
+    cudaFree(ts->arena);
+    ts->arena = nullptr; ts->b = 0; ts->n = 0;
+    const int64_t M = (int64_t)b * n;
+    const int C = m->desc.num_classes, P = m->desc.num_parts;
+    std::vector<std::pair<void **, size_t>> req;
+    auto want = [&](auto **p, size_t bytes) { req.emplace_back(reinterpret_cast<void **>(p), (bytes + 255) & ~(size_t)255); };
+    static const int kPointLayers[] = {L_IT_C1, L_IT_C2, L_IT_C3, L_S1_1, L_S1_2, L_FT_C1, L_FT_C2, L_FT_C3, L_S2_1, L_S2_2, L_S2_3,
+                                       L_SEG1, L_SEG2, L_SEG3, L_SEG4, L_SEG5};
+    for (int i = 0; i < L_COUNT; ++i) {
+        TL &t = ts->L[i];
+        t = TL();
+        const LayerSpec &S = m->layers[i];
+        if (!S.present) continue;
+        bool per_point = false;
+        for (int id : kPointLayers) per_point = per_point || (id == i);
+        t.id = i; t.rows = per_point ? M : b; t.cin = S.cin; t.cout = S.cout; t.has_bn = S.has_bn;
+        if (i != L_SEG5 && i != L_CLS3) want(&t.Z, (size_t)t.rows * S.cout * 4);
+        if (S.has_bn) {
+            want(&t.mean, S.cout * 4); want(&t.inv, S.cout * 4); want(&t.sc, S.cout * 4); want(&t.beta, S.cout * 4);
+            want(&t.red, (size_t)S.cout * 2 * 8);
+        }
+    }
+    want(&ts->pcn, M * 12); want(&ts->X3, M * 12); want(&ts->X2, M * 256); want(&ts->X64, M * 256);
+    want(&ts->g1, (size_t)b * 4096); want(&ts->g2, (size_t)b * 4096); want(&ts->g3, (size_t)b * 4096); want(&ts->cnt, (size_t)b * 4096);
+    want(&ts->dg1, (size_t)b * 4096); want(&ts->dg2, (size_t)b * 4096); want(&ts->dg3, (size_t)b * 4096);
+    want(&ts->R, (size_t)b * 36); want(&ts->dR, (size_t)b * 36); want(&ts->R64, (size_t)b * 16384); want(&ts->dR64, (size_t)b * 16384);
+    for (int i = 0; i < 8; ++i) want(&ts->Ys[i], (size_t)b * 512 * 4);
+    want(&ts->H1, (size_t)b * 2048); want(&ts->H2, (size_t)b * 1024);
+    want(&ts->cls_logits, (size_t)b * C * 4); want(&ts->cls_prob, (size_t)b * C * 4);
+    want(&ts->seg_logits, (size_t)M * P * 4); want(&ts->seg_prob, (size_t)M * P * 4);
+    want(&ts->gvec, (size_t)b * 2048); want(&ts->dgvec, (size_t)b * 2048);
+    for (int i = 0; i < 4; ++i) want(&ts->dsmall[i], (size_t)b * 4096 * 4);
+    want(&ts->Y64a, M * 256); want(&ts->Y64b, M * 256); want(&ts->Y128, M * 512); want(&ts->Y128b, M * 512);
+    want(&ts->Y256, M * 1024); want(&ts->Y512, M * 2048);
+    want(&ts->G1024, M * 4096); want(&ts->G512, M * 2048); want(&ts->G256, M * 1024); want(&ts->G128a, M * 512); want(&ts->G128b, M * 512);
+    want(&ts->G64a, M * 256); want(&ts->G64b, M * 256); want(&ts->GP, (size_t)M * P * 4);
+    want(&ts->dX64, M * 256); want(&ts->dX2, M * 256); want(&ts->dX3, M * 12);
+    want(&ts->metrics, 8 * 8);
+    size_t total = 0;
+    for (auto &r : req) total += r.second;
+    PCP_CUDA_OK(cudaMalloc(&ts->arena, total));
+    size_t off = 0;
+    for (auto &r : req) { *r.first = ts->arena + off; off += r.second; }
+    ts->arena_bytes = total; ts->b = b; ts->n = n;
+    return PCP_OK;
+}
+
+static inline int grid_for(int64_t work, int per_block = 256, int waves = 8)
+{
+    const int64_t g = (work + per_block - 1) / per_block;
+    return (int)std::max<int64_t>(1, std::min<int64_t>(g, (int64_t)sm_count() * waves));
+}
+
+// ---- GEMM wrappers (row-major fp32 activations; W is (cin x cout) row-major inside the flat parameter buffer) ----
+// C (rows x cout) = A (rows x cin) . W  [+ bias]          groups > 1: per-group bias (stride cout), rows per group
+static int mm_nn(const float *A, int64_t rows, int cin, const float *W, int ldw, int cout, float *Cc, const float *bias, cudaStream_t st,
+                 int groups = 1, int64_t bias_stride = 0)
+{
+    GemmArgs g;
+    g.A = A; g.lda = cin; g.B = W; g.ldb = ldw; g.C = Cc; g.ldc = cout; g.bias = bias; g.N = cout; g.K = cin;
+    if (groups > 1) {
+        const int64_t rpg = rows / groups;
+        g.groups = groups; g.M = (int)rpg; g.strideA = rpg * cin; g.strideC = rpg * cout; g.strideBias = bias_stride;
+    } else {
+        g.M = (int)rows;
+    }
+    return gemm_f32(g, st);
+}
+// dA (rows x cin) (+)= dZ (rows x cout) . W^T
+static int mm_nt(const float *dZ, int64_t rows, int cout, const float *W, int ldw, int cin, float *dA, bool accumulate, cudaStream_t st)
+{
+    GemmArgs g;
+    g.A = dZ; g.lda = cout; g.B = W; g.ldb = ldw; g.transB = 1; g.C = dA; g.ldc = cin; g.M = (int)rows; g.N = cin; g.K = cout;
+    g.accumulate = accumulate ? 1 : 0;
+    return gemm_f32(g, st);
+}
+// dW (cin x cout) += A^T (cin x rows) . dZ (rows x cout)   — split-K over the rows, atomics into the zeroed gradient buffer
+static int mm_tn(const float *A, int64_t rows, int cin, const float *dZ, int cout, float *dW, int lddw, cudaStream_t st)
+{
+    GemmArgs g;
+    g.A = A; g.lda = cin; g.transA = 1; g.B = dZ; g.ldb = cout; g.C = dW; g.ldc = lddw; g.M = cin; g.N = cout; g.K = (int)rows;
+    const int64_t blocks = (int64_t)((cin + 127) / 128) * ((cout + 63) / 64);
+    int64_t sk = (4 * (int64_t)sm_count() + blocks - 1) / blocks;
+    sk = std::min<int64_t>(sk, std::max<int64_t>(1, rows / 128));
+    sk = std::max<int64_t>(1, std::min<int64_t>(sk, 4096));
+    g.splitk = (int)sk;
+    if (sk == 1) g.accumulate = 1;
+    return gemm_f32(g, st);
+}
+
+static inline float *param(pcp_model *m, int ti) { return m->d_params + m->tensors[ti].offset; }
+static inline float *grad(pcp_model *m, int ti) { return m->d_grads + m->tensors[ti].offset; }
+
+// BN statistics + (mean, inv, sc, beta) for layer t whose Z is filled
+static int bn_prepare(pcp_model *m, TL &t, cudaStream_t st)
+{
+    const LayerSpec &S = m->layers[t.id];
+    if (t.batch) {
+        PCP_CUDA_OK(cudaMemsetAsync(t.red, 0, (size_t)t.cout * 16, st));
+        colstats_kernel<<<grid_for(t.rows, 64, 4), 256, 0, st>>>(t.Z, t.rows, t.cout, t.red, t.red + t.cout);
+        PCP_CHECK_LAUNCH();
+    }
+    bn_finalize_kernel<<<(t.cout + 127) / 128, 128, 0, st>>>(t.red, t.red + t.cout, (double)t.rows, t.cout, t.batch ? 1 : 0, param(m, S.t_gamma),
+                                                           param(m, S.t_beta), param(m, S.t_mean), param(m, S.t_var), t.mean, t.inv, t.sc,
+                                                           t.beta, kBnEpsT, kBnMomentum);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+static int bn_act(const TL &t, float *Y, cudaStream_t st)
+{
+    const int64_t n4 = t.rows * t.cout / 4;
+    bn_act_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<const float4 *>(t.Z), n4, t.cout / 4, t.bnp(), reinterpret_cast<float4 *>(Y));
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+// forward of one BN layer: Z = A . W ; statistics ; optionally Y = relu(bn(Z))
+static int layer_fwd_train(pcp_model *m, TL &t, const float *A, float *Y, cudaStream_t st)
+{
+    const LayerSpec &S = m->layers[t.id];
+    PCP_TRY(mm_nn(A, t.rows, t.cin, param(m, S.t_kernel), t.cout, t.cout, t.Z, nullptr, st));
+    PCP_TRY(bn_prepare(m, t, st));
+    if (Y) PCP_TRY(bn_act(t, Y, st));
+    return PCP_OK;
+}
+
+// reduce_max over the points of each cloud of relu(bn(Z))
+static int pool_fwd(const TL &t, int b, int64_t n, float *g, cudaStream_t st)
+{
+    PCP_CUDA_OK(cudaMemsetAsync(g, 0, (size_t)b * t.cout * 4, st));
+    const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((n + 63) / 64, std::max<int64_t>(1, (int64_t)sm_count() * 8 / b)));
+    bn_relu_colmax_kernel<<<dim3(gx, b), 256, 0, st>>>(t.Z, n, t.cout, t.bnp(), g);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+// G (rows x cout) holds dY on entry, dZ on exit; BN parameter gradients are written when the layer trains
+static int bn_bwd(pcp_model *m, TL &t, float *G, bool relu, cudaStream_t st)
+{
+    const LayerSpec &S = m->layers[t.id];
+    const int64_t n4 = t.rows * t.cout / 4;
+    if (t.batch) {
+        PCP_CUDA_OK(cudaMemsetAsync(t.red, 0, (size_t)t.cout * 16, st));
+        bn_bwd_reduce_kernel<<<grid_for(t.rows, 64, 4), 256, 0, st>>>(G, t.Z, t.rows, t.cout, t.bnp(), relu ? 1 : 0, t.red, t.red + t.cout);
+        PCP_CHECK_LAUNCH();
+        if (t.trainable) {
+            store_bn_grads_kernel<<<(t.cout + 127) / 128, 128, 0, st>>>(t.red, t.red + t.cout, t.cout, grad(m, S.t_gamma), grad(m, S.t_beta));
+            PCP_CHECK_LAUNCH();
+        }
+    }
+    bn_bwd_apply_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(G), reinterpret_cast<const float4 *>(t.Z), n4, t.cout / 4, t.bnp(),
+                                                     relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, 1.0f / (float)t.rows);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+// gradient of the per-cloud max-pool into G (M x cout), then BN backward in place
+static int pool_bwd(pcp_model *m, TL &t, int b, int64_t n, const float *g, const float *dg, int *cnt, float *G, cudaStream_t st)
+{
+    PCP_CUDA_OK(cudaMemsetAsync(cnt, 0, (size_t)b * t.cout * 4, st));
+    const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((n + 63) / 64, std::max<int64_t>(1, (int64_t)sm_count() * 8 / b)));
+    pool_count_kernel<<<dim3(gx, b), 256, 0, st>>>(t.Z, n, t.cout, t.bnp(), g, cnt);
+    PCP_CHECK_LAUNCH();
+    const int64_t total4 = t.rows * t.cout / 4;
+    pool_bwd_kernel<<<grid_for(total4), 256, 0, st>>>(reinterpret_cast<const float4 *>(t.Z), n * t.cout / 4, total4, t.cout / 4, t.bnp(), g, dg, cnt,
+                                                     reinterpret_cast<float4 *>(G));
+    PCP_CHECK_LAUNCH();
+    return bn_bwd(m, t, G, true, st);
+}
+
+// weight gradient + input gradient of a layer whose dZ is in G
+static int layer_bwd_mm(pcp_model *m, TL &t, const float *Ain, const float *G, float *dA, bool accumulate, cudaStream_t st)
+{
+    const LayerSpec &S = m->layers[t.id];
+    if (t.trainable) PCP_TRY(mm_tn(Ain, t.rows, t.cin, G, t.cout, grad(m, S.t_kernel), t.cout, st));
+    if (dA) PCP_TRY(mm_nt(G, t.rows, t.cout, param(m, S.t_kernel), t.cout, t.cin, dA, accumulate, st));
+    return PCP_OK;
+}
+
+static int colsum(const float *X, int groups, int64_t rpg, int C, float *out, cudaStream_t st)
+{
+    const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((rpg + 255) / 256, std::max<int64_t>(1, (int64_t)sm_count() * 4 / groups)));
+    group_colsum_kernel<<<dim3(gx, groups), 256, 0, st>>>(X, rpg, C, out);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+// T-Net tail forward (PointNet.py:431-442): g (b x 1024) -> dense 512 -> 256 -> (256 x k^2) + b
+static int tnet_tail_fwd(pcp_model *m, TrainState *ts, int first, int t_w, int t_b, int k, const float *g, float *Y1, float *Y2, float *out,
+                         cudaStream_t st)
+{
+    PCP_TRY(layer_fwd_train(m, ts->L[first + 3], g, Y1, st));
+    PCP_TRY(layer_fwd_train(m, ts->L[first + 4], Y1, Y2, st));
+    return mm_nn(Y2, ts->b, 256, param(m, t_w), k * k, k * k, out, param(m, t_b), st);
+}
+
+// T-Net tail backward: dM (b x k^2) -> dg (b x 1024)
+static int tnet_tail_bwd(pcp_model *m, TrainState *ts, int first, int t_w, int t_b, int k, bool trainable, const float *g, const float *Y1,
+                         const float *Y2, const float *dM, float *dg, cudaStream_t st)
+{
+    const int b = ts->b;
+    float *d256 = ts->dsmall[1], *d512 = ts->dsmall[0];
+    if (trainable) {
+        PCP_TRY(mm_tn(Y2, b, 256, dM, k * k, grad(m, t_w), k * k, st));
+        PCP_TRY(colsum(dM, 1, b, k * k, grad(m, t_b), st));
+    }
+    PCP_TRY(mm_nt(dM, b, k * k, param(m, t_w), k * k, 256, d256, false, st));
+    PCP_TRY(bn_bwd(m, ts->L[first + 4], d256, true, st));
+    PCP_TRY(layer_bwd_mm(m, ts->L[first + 4], Y1, d256, d512, false, st));
+    PCP_TRY(bn_bwd(m, ts->L[first + 3], d512, true, st));
+    PCP_TRY(layer_bwd_mm(m, ts->L[first + 3], g, d512, dg, false, st));
+    return PCP_OK;
+}
+
+static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *y_cls, const int32_t *y_seg, const float *y_se3,
+                           const pcp_train_config *cfg, int global_batch, const float *mask1, const float *mask2, float *h_metrics,
+                           cudaStream_t st)
+{
+    TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
+    PCP_TRY(ensure_arena(m, ts, b, n));
+    const int64_t M = (int64_t)b * n;
+    const int C = m->desc.num_classes, P = m->desc.num_parts;
+    const bool full = !m->desc.vanilla;
+    const bool tr_sh = m->trainable[PCP_GROUP_SHARED], tr_it = m->trainable[PCP_GROUP_INPUT_TRANSFORM] && full;
+    const bool tr_cls = m->trainable[PCP_GROUP_CLS_HEAD], tr_seg = m->trainable[PCP_GROUP_SEG_HEAD];
+    const float rate = m->desc.dropout_rate;
+    const bool seg_needed = !(cfg->skip_unweighted_heads && cfg->w_seg == 0.f && !tr_seg);
+    const bool do_seg_bwd = seg_needed && cfg->w_seg != 0.f && y_seg;
+    const bool do_cls_bwd = cfg->w_cls != 0.f && y_cls;
+    for (int i = 0; i < L_COUNT; ++i) {
+        TL &t = ts->L[i];
+        if (t.id < 0) continue;
+        t.trainable = m->trainable[m->layers[i].group];
+        t.batch = t.has_bn && t.trainable;                       // keras: batch statistics only when training AND trainable
+    }
+    PCP_CUDA_OK(cudaMemsetAsync(m->d_grads, 0, m->n_params * sizeof(float), st));
+    PCP_CUDA_OK(cudaMemsetAsync(ts->metrics, 0, 64, st));
+    TL *L = ts->L;
+
+    // =========================================== forward ===========================================
+    PCP_TRY(pcp_normalize_f32(d_x, b, n, ts->pcn, nullptr, nullptr, st));                               // PointNet.py:202
+    const float *X3 = ts->pcn;
+    if (full) {
+        PCP_TRY(layer_fwd_train(m, L[L_IT_C1], ts->pcn, ts->Y64a, st));                                 // TNet.call :423
+        PCP_TRY(layer_fwd_train(m, L[L_IT_C2], ts->Y64a, ts->Y128, st));                                // :424
+        PCP_TRY(layer_fwd_train(m, L[L_IT_C3], ts->Y128, nullptr, st));                                 // :425
+        PCP_TRY(pool_fwd(L[L_IT_C3], b, n, ts->g1, st));                                                // :429
+        PCP_TRY(tnet_tail_fwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, ts->g1, ts->Ys[0], ts->Ys[1], ts->R, st));
+        GemmArgs g;                                                                                     // X = pc @ R  :207
+        g.A = ts->pcn; g.lda = 3; g.strideA = n * 3; g.B = ts->R; g.ldb = 3; g.strideB = 9;
+        g.C = ts->X3; g.ldc = 3; g.strideC = n * 3; g.M = (int)n; g.N = 3; g.K = 3; g.groups = b;
+        PCP_TRY(gemm_f32(g, st));
+        X3 = ts->X3;
+    } else {
+        PCP_TRY(model_eye3(ts->R, b, st));
+    }
+    PCP_TRY(layer_fwd_train(m, L[L_S1_1], X3, ts->Y64a, st));                                           // :217
+    PCP_TRY(layer_fwd_train(m, L[L_S1_2], ts->Y64a, ts->X2, st));                                       // :220
+    const float *X64 = ts->X2;
+    if (full) {
+        PCP_TRY(layer_fwd_train(m, L[L_FT_C1], ts->X2, ts->Y64a, st));
+        PCP_TRY(layer_fwd_train(m, L[L_FT_C2], ts->Y64a, ts->Y128, st));
+        PCP_TRY(layer_fwd_train(m, L[L_FT_C3], ts->Y128, nullptr, st));
+        PCP_TRY(pool_fwd(L[L_FT_C3], b, n, ts->g2, st));
+        PCP_TRY(tnet_tail_fwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, ts->g2, ts->Ys[2], ts->Ys[3], ts->R64, st));   // :227
+        GemmArgs g;                                                                                     // X_64 = X @ R_64 :228
+        g.A = ts->X2; g.lda = 64; g.strideA = n * 64; g.B = ts->R64; g.ldb = 64; g.strideB = 4096;
+        g.C = ts->X64; g.ldc = 64; g.strideC = n * 64; g.M = (int)n; g.N = 64; g.K = 64; g.groups = b;
+        PCP_TRY(gemm_f32(g, st));
+        X64 = ts->X64;
+    }
+    PCP_TRY(layer_fwd_train(m, L[L_S2_1], X64, ts->Y64a, st));                                          // :236
+    PCP_TRY(layer_fwd_train(m, L[L_S2_2], ts->Y64a, ts->Y128, st));                                     // :239
+    PCP_TRY(layer_fwd_train(m, L[L_S2_3], ts->Y128, nullptr, st));                                      // :242
+    PCP_TRY(pool_fwd(L[L_S2_3], b, n, ts->g3, st));                                                     // :248
+
+    // ---- classification head (:252-263) ----
+    const float *Yc1 = ts->Ys[4], *Yc2 = ts->Ys[5];
+    PCP_TRY(layer_fwd_train(m, L[L_CLS1], ts->g3, ts->Ys[4], st));
+    const bool use_drop = rate > 0.f;
+    const float *H1 = Yc1, *H2 = Yc2;
+    if (use_drop) {
+        dropout_kernel<<<grid_for((int64_t)b * 512), 256, 0, st>>>(Yc1, b, 512, cfg->use_dropout_masks ? mask1 : nullptr, cfg->dropout_seed,
+                                                                   cfg->sample_offset, 1u, rate, ts->H1);
+        PCP_CHECK_LAUNCH();
+        H1 = ts->H1;
+    }
+    PCP_TRY(layer_fwd_train(m, L[L_CLS2], H1, ts->Ys[5], st));
+    if (use_drop) {
+        dropout_kernel<<<grid_for((int64_t)b * 256), 256, 0, st>>>(Yc2, b, 256, cfg->use_dropout_masks ? mask2 : nullptr, cfg->dropout_seed,
+                                                                   cfg->sample_offset, 2u, rate, ts->H2);
+        PCP_CHECK_LAUNCH();
+        H2 = ts->H2;
+    }
+    {
+        const LayerSpec &S = m->layers[L_CLS3];
+        PCP_TRY(mm_nn(H2, b, 256, param(m, S.t_kernel), C, C, ts->cls_logits, param(m, S.t_bias), st));
+    }
+    float *dlog_cls = ts->dsmall[2];
+    PCP_REQUIRE(C <= 4096 && P <= 4096, PCP_ERR_UNSUPPORTED, "training supports up to 4096 classes / parts");
+    if (y_cls) {
+        softmax_ce_kernel<<<grid_for(b, 256, 1), 256, 0, st>>>(ts->cls_logits, b, C, y_cls, cfg->w_cls / (float)global_batch, ts->cls_prob, dlog_cls,
+                                                               ts->metrics + 0, ts->metrics + 4);
+        PCP_CHECK_LAUNCH();
+    }
+
+    // ---- segmentation head (:268-290): concat([X_64, tile(global)]) . W1 = X_64 . W1[0:64] + global . W1[64:1088] ----
+    ts->have_seg = seg_needed;
+    if (seg_needed) {
+        const LayerSpec &S1 = m->layers[L_SEG1];
+        PCP_TRY(mm_nn(ts->g3, b, 1024, param(m, S1.t_kernel) + (size_t)64 * 512, 512, 512, ts->gvec, nullptr, st));
+        TL &t1 = L[L_SEG1];
+        PCP_TRY(mm_nn(X64, M, 64, param(m, S1.t_kernel), 512, 512, t1.Z, ts->gvec, st, b, 512));
+        PCP_TRY(bn_prepare(m, t1, st));
+        PCP_TRY(bn_act(t1, ts->Y512, st));
+        PCP_TRY(layer_fwd_train(m, L[L_SEG2], ts->Y512, ts->Y256, st));
+        PCP_TRY(layer_fwd_train(m, L[L_SEG3], ts->Y256, ts->Y128, st));
+        PCP_TRY(layer_fwd_train(m, L[L_SEG4], ts->Y128, ts->Y128b, st));
+        const LayerSpec &S5 = m->layers[L_SEG5];
+        PCP_TRY(mm_nn(ts->Y128b, M, 128, param(m, S5.t_kernel), P, P, ts->seg_logits, param(m, S5.t_bias), st));
+        if (y_seg) {
+            softmax_ce_kernel<<<grid_for(M), 256, 0, st>>>(ts->seg_logits, M, P, y_seg, cfg->w_seg / ((float)global_batch * (float)n), ts->seg_prob,
+                                                           do_seg_bwd ? ts->GP : nullptr, ts->metrics + 1, ts->metrics + 5);
+            PCP_CHECK_LAUNCH();
+        }
+    }
+
+    // =========================================== backward ===========================================
+    PCP_CUDA_OK(cudaMemsetAsync(ts->dg3, 0, (size_t)b * 4096, st));
+    PCP_CUDA_OK(cudaMemsetAsync(ts->dX64, 0, (size_t)M * 256, st));
+    PCP_CUDA_OK(cudaMemsetAsync(ts->dR, 0, (size_t)b * 36, st));
+    PCP_CUDA_OK(cudaMemsetAsync(ts->dR64, 0, (size_t)b * 16384, st));
+    const bool trunk_bwd = tr_sh || tr_it;
+
+    if (do_cls_bwd && (tr_cls || trunk_bwd)) {
+        const LayerSpec &S3 = m->layers[L_CLS3];
+        float *d256 = ts->dsmall[1], *d512 = ts->dsmall[0];
+        if (tr_cls) {
+            PCP_TRY(mm_tn(H2, b, 256, dlog_cls, C, grad(m, S3.t_kernel), C, st));
+            PCP_TRY(colsum(dlog_cls, 1, b, C, grad(m, S3.t_bias), st));
+        }
+        PCP_TRY(mm_nt(dlog_cls, b, C, param(m, S3.t_kernel), C, 256, d256, false, st));
+        if (use_drop) {
+            dropout_kernel<<<grid_for((int64_t)b * 256), 256, 0, st>>>(d256, b, 256, cfg->use_dropout_masks ? mask2 : nullptr, cfg->dropout_seed,
+                                                                       cfg->sample_offset, 2u, rate, d256);
+            PCP_CHECK_LAUNCH();
+        }
+        PCP_TRY(bn_bwd(m, L[L_CLS2], d256, true, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_CLS2], H1, d256, d512, false, st));
+        if (use_drop) {
+            dropout_kernel<<<grid_for((int64_t)b * 512), 256, 0, st>>>(d512, b, 512, cfg->use_dropout_masks ? mask1 : nullptr, cfg->dropout_seed,
+                                                                       cfg->sample_offset, 1u, rate, d512);
+            PCP_CHECK_LAUNCH();
+        }
+        PCP_TRY(bn_bwd(m, L[L_CLS1], d512, true, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_CLS1], ts->g3, d512, trunk_bwd ? ts->dg3 : nullptr, true, st));
+    }
+
+    if (do_seg_bwd && (tr_seg || trunk_bwd)) {
+        const LayerSpec &S5 = m->layers[L_SEG5], &S1 = m->layers[L_SEG1];
+        // Y128b (seg_l4 output) is still live from the forward pass; the others are recomputed from Z
+        if (tr_seg) {
+            PCP_TRY(mm_tn(ts->Y128b, M, 128, ts->GP, P, grad(m, S5.t_kernel), P, st));
+            PCP_TRY(colsum(ts->GP, 1, M, P, grad(m, S5.t_bias), st));
+        }
+        PCP_TRY(mm_nt(ts->GP, M, P, param(m, S5.t_kernel), P, 128, ts->G128a, false, st));
+        PCP_TRY(bn_bwd(m, L[L_SEG4], ts->G128a, true, st));
+        PCP_TRY(bn_act(L[L_SEG3], ts->Y128, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_SEG4], ts->Y128, ts->G128a, ts->G128b, false, st));
+        PCP_TRY(bn_bwd(m, L[L_SEG3], ts->G128b, true, st));
+        PCP_TRY(bn_act(L[L_SEG2], ts->Y256, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_SEG3], ts->Y256, ts->G128b, ts->G256, false, st));
+        PCP_TRY(bn_bwd(m, L[L_SEG2], ts->G256, true, st));
+        PCP_TRY(bn_act(L[L_SEG1], ts->Y512, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_SEG2], ts->Y512, ts->G256, ts->G512, false, st));
+        PCP_TRY(bn_bwd(m, L[L_SEG1], ts->G512, true, st));
+        // per-cloud sums of dZ1: gradient of the hoisted global term
+        PCP_CUDA_OK(cudaMemsetAsync(ts->dgvec, 0, (size_t)b * 2048, st));
+        PCP_TRY(colsum(ts->G512, b, n, 512, ts->dgvec, st));
+        if (tr_seg) {
+            PCP_TRY(mm_tn(X64, M, 64, ts->G512, 512, grad(m, S1.t_kernel), 512, st));
+            PCP_TRY(mm_tn(ts->g3, b, 1024, ts->dgvec, 512, grad(m, S1.t_kernel) + (size_t)64 * 512, 512, st));
+        }
+        if (trunk_bwd) {
+            PCP_TRY(mm_nt(ts->G512, M, 512, param(m, S1.t_kernel), 512, 64, ts->dX64, true, st));
+            PCP_TRY(mm_nt(ts->dgvec, b, 512, param(m, S1.t_kernel) + (size_t)64 * 512, 512, 1024, ts->dg3, true, st));
+        }
+    }
+
+    // rotation loss + regularisers act on R / R64 directly
+    if (y_se3) {
+        mse_kernel<<<grid_for((int64_t)b * 9, 256, 1), 256, 0, st>>>(ts->R, y_se3, (int64_t)b * 9, cfg->w_rot / ((float)global_batch * 9.f),
+                                                                    (tr_it && cfg->w_rot != 0.f) ? ts->dR : nullptr, ts->metrics + 2);
+        PCP_CHECK_LAUNCH();
+    }
+    if (full && m->desc.regularize_input_transform) {
+        tnet_reg_kernel<<<b, 32, 2 * 9 * sizeof(float), st>>>(ts->R, 3, tr_it ? ts->dR : nullptr, ts->metrics + 3);
+        PCP_CHECK_LAUNCH();
+    }
+    if (full && m->desc.regularize_feature_transform) {
+        tnet_reg_kernel<<<b, 256, 2 * 4096 * sizeof(float), st>>>(ts->R64, 64, tr_sh ? ts->dR64 : nullptr, ts->metrics + 3);
+        PCP_CHECK_LAUNCH();
+    }
+
+    if (trunk_bwd) {
+        // ---- mlp_2 (:234-248) ----
+        PCP_TRY(pool_bwd(m, L[L_S2_3], b, n, ts->g3, ts->dg3, ts->cnt, ts->G1024, st));
+        PCP_TRY(bn_act(L[L_S2_2], ts->Y128, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_S2_3], ts->Y128, ts->G1024, ts->G128a, false, st));
+        PCP_TRY(bn_bwd(m, L[L_S2_2], ts->G128a, true, st));
+        PCP_TRY(bn_act(L[L_S2_1], ts->Y64a, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_S2_2], ts->Y64a, ts->G128a, ts->G64a, false, st));
+        PCP_TRY(bn_bwd(m, L[L_S2_1], ts->G64a, true, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_S2_1], X64, ts->G64a, ts->dX64, true, st));
+        float *dX2 = ts->dX64;                     // vanilla: X_64 is X (:231)
+        if (full) {
+            // X_64 = X @ R_64: dR_64 = X^T . dX_64 per cloud ; dX = dX_64 . R_64^T
+            GemmArgs g;
+            g.A = ts->X2; g.lda = 64; g.strideA = n * 64; g.transA = 1; g.B = ts->dX64; g.ldb = 64; g.strideB = n * 64;
+            g.C = ts->dR64; g.ldc = 64; g.strideC = 4096; g.M = 64; g.N = 64; g.K = (int)n; g.groups = b; g.accumulate = 1;
+            PCP_TRY(gemm_f32(g, st));
+            GemmArgs h;
+            h.A = ts->dX64; h.lda = 64; h.strideA = n * 64; h.B = ts->R64; h.ldb = 64; h.strideB = 4096; h.transB = 1;
+            h.C = ts->dX2; h.ldc = 64; h.strideC = n * 64; h.M = (int)n; h.N = 64; h.K = 64; h.groups = b;
+            PCP_TRY(gemm_f32(h, st));
+            dX2 = ts->dX2;
+            // ---- feature T-Net ----
+            PCP_TRY(tnet_tail_bwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, tr_sh, ts->g2, ts->Ys[2], ts->Ys[3], ts->dR64, ts->dg2, st));
+            PCP_TRY(pool_bwd(m, L[L_FT_C3], b, n, ts->g2, ts->dg2, ts->cnt, ts->G1024, st));
+            PCP_TRY(bn_act(L[L_FT_C2], ts->Y128, st));
+            PCP_TRY(layer_bwd_mm(m, L[L_FT_C3], ts->Y128, ts->G1024, ts->G128a, false, st));
+            PCP_TRY(bn_bwd(m, L[L_FT_C2], ts->G128a, true, st));
+            PCP_TRY(bn_act(L[L_FT_C1], ts->Y64a, st));
+            PCP_TRY(layer_bwd_mm(m, L[L_FT_C2], ts->Y64a, ts->G128a, ts->G64a, false, st));
+            PCP_TRY(bn_bwd(m, L[L_FT_C1], ts->G64a, true, st));
+            PCP_TRY(layer_bwd_mm(m, L[L_FT_C1], ts->X2, ts->G64a, dX2, true, st));
+        }
+        // ---- mlp_1 (:215-223): dX2 holds dY of s1_l2 ----
+        PCP_TRY(bn_bwd(m, L[L_S1_2], dX2, true, st));
+        PCP_TRY(bn_act(L[L_S1_1], ts->Y64a, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_S1_2], ts->Y64a, dX2, ts->G64b, false, st));
+        PCP_TRY(bn_bwd(m, L[L_S1_1], ts->G64b, true, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_S1_1], X3, ts->G64b, (full && tr_it) ? ts->dX3 : nullptr, false, st));
+        if (full && tr_it) {
+            // X = pc @ R: dR += pc^T . dX per cloud
+            GemmArgs g;
+            g.A = ts->pcn; g.lda = 3; g.strideA = n * 3; g.transA = 1; g.B = ts->dX3; g.ldb = 3; g.strideB = n * 3;
+            g.C = ts->dR; g.ldc = 3; g.strideC = 9; g.M = 3; g.N = 3; g.K = (int)n; g.groups = b; g.accumulate = 1;
+            PCP_TRY(gemm_f32(g, st));
+        }
+    }
+    if (full && tr_it) {
+        // ---- input T-Net: gradient enters through R only ----
+        PCP_TRY(tnet_tail_bwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, true, ts->g1, ts->Ys[0], ts->Ys[1], ts->dR, ts->dg1, st));
+        PCP_TRY(pool_bwd(m, L[L_IT_C3], b, n, ts->g1, ts->dg1, ts->cnt, ts->G1024, st));
+        PCP_TRY(bn_act(L[L_IT_C2], ts->Y128, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_IT_C3], ts->Y128, ts->G1024, ts->G128a, false, st));
+        PCP_TRY(bn_bwd(m, L[L_IT_C2], ts->G128a, true, st));
+        PCP_TRY(bn_act(L[L_IT_C1], ts->Y64a, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_IT_C2], ts->Y64a, ts->G128a, ts->G64a, false, st));
+        PCP_TRY(bn_bwd(m, L[L_IT_C1], ts->G64a, true, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_IT_C1], ts->pcn, ts->G64a, nullptr, false, st));
+    }
+    m->dev_newer = true;          // BN moving statistics were updated on the device
+    m->prepared = false;
+
+    if (h_metrics) {
+        double hm[8];
+        PCP_CUDA_OK(cudaMemcpyAsync(hm, ts->metrics, 64, cudaMemcpyDeviceToHost, st));
+        PCP_CUDA_OK(cudaStreamSynchronize(st));
+        const double cls_loss = y_cls ? hm[0] / b : 0.0, seg_loss = (seg_needed && y_seg) ? hm[1] / ((double)b * n) : 0.0;
+        const double se3 = y_se3 ? hm[2] / ((double)b * 9) : 0.0, reg = hm[3];
+        h_metrics[1] = (float)cls_loss; h_metrics[2] = (float)seg_loss; h_metrics[3] = (float)se3;
+        h_metrics[4] = y_cls ? (float)(hm[4] / b) : 0.f;
+        h_metrics[5] = (seg_needed && y_seg) ? (float)(hm[5] / ((double)b * n)) : 0.f;
+        h_metrics[6] = (float)sqrt(se3);
+        h_metrics[7] = (float)reg;
+        h_metrics[0] = (float)(cfg->w_cls * cls_loss + cfg->w_seg * seg_loss + cfg->w_rot * se3 + reg);
     }
     return PCP_OK;
 }
@@ -97,6 +1009,15 @@ extern "C" int pcp_model_adam_step(pcp_model *m, const pcp_train_config *cfg, in
     return PCP_OK;
 }
 
+extern "C" int pcp_model_reset_optimizer(pcp_model *m)
+{
+    PCP_REQUIRE(m, PCP_ERR_INVALID, "pcp_model_reset_optimizer: null model");
+    PCP_TRY(ensure_train_buffers(m));
+    PCP_CUDA_OK(cudaMemset(m->d_adam_m, 0, m->n_params * sizeof(float)));
+    PCP_CUDA_OK(cudaMemset(m->d_adam_v, 0, m->n_params * sizeof(float)));
+    return PCP_OK;
+}
+
 extern "C" int pcp_model_get_grad(pcp_model *m, const char *name, float *h_data, size_t count)
 {
     PCP_REQUIRE(m && name && h_data, PCP_ERR_INVALID, "pcp_model_get_grad: null argument");
@@ -115,8 +1036,91 @@ extern "C" int pcp_model_loss_backward(pcp_model *m, const float *d_x, int b, in
                                        int global_batch, const float *d_mask1, const float *d_mask2, float *h_metrics,
                                        pcp_stream stream)
 {
-    (void)m; (void)d_x; (void)b; (void)n; (void)d_y_cls; (void)d_y_seg; (void)d_y_se3; (void)cfg; (void)global_batch;
-    (void)d_mask1; (void)d_mask2; (void)h_metrics; (void)stream;
-    set_error("pcp_model_loss_backward: training backward is not built in this revision");
-    return PCP_ERR_UNSUPPORTED;
+    PCP_REQUIRE(m && d_x && cfg && b >= 1 && n >= 1 && global_batch >= b, PCP_ERR_INVALID, "pcp_model_loss_backward: bad arguments");
+    PCP_REQUIRE((int64_t)b * n < ((int64_t)1 << 23), PCP_ERR_UNSUPPORTED, "pcp_model_loss_backward: b*n must stay below 8.3 M points per shard");
+    PCP_REQUIRE(!cfg->use_dropout_masks || m->desc.dropout_rate <= 0.f || (d_mask1 && d_mask2), PCP_ERR_INVALID,
+                "pcp_model_loss_backward: use_dropout_masks set but masks are null");
+    PCP_REQUIRE(m->desc.dropout_rate < 1.f, PCP_ERR_INVALID, "pcp_model_loss_backward: dropout rate must be < 1");
+    PCP_TRY(ensure_train_buffers(m));
+    // the device copy of the parameters is the master during training
+    if (!m->dev_newer && !m->prepared)
+        PCP_CUDA_OK(cudaMemcpy(m->d_params, m->h_params.data(), m->n_params * sizeof(float), cudaMemcpyHostToDevice));
+    return train_step_impl(m, d_x, b, n, d_y_cls, d_y_seg, d_y_se3, cfg, global_batch, d_mask1, d_mask2, h_metrics, as_stream(stream));
+}
+
+// Inference-mode forward + the compiled losses / metrics (keras Model.evaluate / validation pass of fit,
+// pointnet_train.py:221-228): no gradients, BN on moving statistics, no dropout.
+extern "C" int pcp_model_evaluate(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *d_y_cls, const int32_t *d_y_seg,
+                                  const float *d_y_se3, const pcp_train_config *cfg, float *h_metrics, pcp_stream stream)
+{
+    PCP_REQUIRE(m && d_x && cfg && h_metrics && b >= 1 && n >= 1, PCP_ERR_INVALID, "pcp_model_evaluate: bad arguments");
+    PCP_TRY(ensure_train_buffers(m));
+    TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
+    cudaStream_t st = as_stream(stream);
+    const int C = m->desc.num_classes, P = m->desc.num_parts;
+    const int64_t M = (int64_t)b * n;
+    const size_t need = (size_t)b * C * 4 + (size_t)M * P * 4 + (size_t)b * 36 + 64 + 1024;
+    if (ts->eval_bytes < need) {
+        cudaFree(ts->eval_buf);
+        ts->eval_buf = nullptr; ts->eval_bytes = 0;
+        PCP_CUDA_OK(cudaMalloc(&ts->eval_buf, need));
+        ts->eval_bytes = need;
+    }
+    double *met = reinterpret_cast<double *>(ts->eval_buf);
+    float *cls_logits = reinterpret_cast<float *>(ts->eval_buf + 256);
+    float *R = cls_logits + (((size_t)b * C + 63) & ~(size_t)63);
+    float *seg_logits = R + (((size_t)b * 9 + 63) & ~(size_t)63);
+    const bool want_seg = d_y_seg != nullptr;
+    PCP_CUDA_OK(cudaMemsetAsync(met, 0, 64, st));
+    PCP_TRY(pcp_model_forward(m, d_x, b, n, PCP_HEAD_CLS | (want_seg ? PCP_HEAD_SEG : 0u), nullptr, nullptr, R, cls_logits,
+                              want_seg ? seg_logits : nullptr, stream));
+    if (d_y_cls) {
+        softmax_ce_kernel<<<grid_for(b, 256, 1), 256, 0, st>>>(cls_logits, b, C, d_y_cls, 0.f, nullptr, nullptr, met + 0, met + 4);
+        PCP_CHECK_LAUNCH();
+    }
+    if (want_seg) {
+        softmax_ce_kernel<<<grid_for(M), 256, 0, st>>>(seg_logits, M, P, d_y_seg, 0.f, nullptr, nullptr, met + 1, met + 5);
+        PCP_CHECK_LAUNCH();
+    }
+    if (d_y_se3) {
+        mse_kernel<<<grid_for((int64_t)b * 9, 256, 1), 256, 0, st>>>(R, d_y_se3, (int64_t)b * 9, 0.f, nullptr, met + 2);
+        PCP_CHECK_LAUNCH();
+    }
+    if (!m->desc.vanilla && m->desc.regularize_input_transform) {
+        tnet_reg_kernel<<<b, 32, 2 * 9 * sizeof(float), st>>>(R, 3, nullptr, met + 3);
+        PCP_CHECK_LAUNCH();
+    }
+    double hm[8];
+    PCP_CUDA_OK(cudaMemcpyAsync(hm, met, 64, cudaMemcpyDeviceToHost, st));
+    PCP_CUDA_OK(cudaStreamSynchronize(st));
+    const double cls_loss = d_y_cls ? hm[0] / b : 0.0, seg_loss = want_seg ? hm[1] / ((double)b * n) : 0.0;
+    const double se3 = d_y_se3 ? hm[2] / ((double)b * 9) : 0.0, reg = hm[3];
+    h_metrics[1] = (float)cls_loss; h_metrics[2] = (float)seg_loss; h_metrics[3] = (float)se3;
+    h_metrics[4] = d_y_cls ? (float)(hm[4] / b) : 0.f;
+    h_metrics[5] = want_seg ? (float)(hm[5] / ((double)b * n)) : 0.f;
+    h_metrics[6] = (float)sqrt(se3);
+    h_metrics[7] = (float)reg;
+    h_metrics[0] = (float)(cfg->w_cls * cls_loss + cfg->w_seg * seg_loss + cfg->w_rot * se3 + reg);
+    return PCP_OK;
+}
+
+extern "C" int pcp_model_get_train_output(pcp_model *m, int which, float *h_out, size_t count)
+{
+    PCP_REQUIRE(m && h_out && m->train_ws, PCP_ERR_INVALID, "pcp_model_get_train_output: no training step has run");
+    TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
+    PCP_REQUIRE(ts->arena, PCP_ERR_STATE, "pcp_model_get_train_output: no training step has run");
+    const int C = m->desc.num_classes, P = m->desc.num_parts;
+    const float *src = nullptr; size_t have = 0;
+    switch (which) {
+    case 0: src = ts->cls_prob; have = (size_t)ts->b * C; break;
+    case 1: src = ts->have_seg ? ts->seg_prob : nullptr; have = (size_t)ts->b * ts->n * P; break;
+    case 2: src = ts->R; have = (size_t)ts->b * 9; break;
+    case 3: src = m->desc.vanilla ? nullptr : ts->R64; have = (size_t)ts->b * 4096; break;
+    case 4: src = ts->g3; have = (size_t)ts->b * 1024; break;
+    default: break;
+    }
+    PCP_REQUIRE(src && have == count, PCP_ERR_INVALID, "pcp_model_get_train_output: output %d unavailable or count mismatch (%zu vs %zu)", which, have, count);
+    PCP_CUDA_OK(cudaDeviceSynchronize());
+    PCP_CUDA_OK(cudaMemcpy(h_out, src, count * sizeof(float), cudaMemcpyDeviceToHost));
+    return PCP_OK;
 }

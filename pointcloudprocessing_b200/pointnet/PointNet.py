@@ -396,6 +396,159 @@ class PointNet:
                 outs[j].append(o[j])
         return [np.concatenate(o, 0) for o in outs]
 
+    # ------------------------------------------------------------------ training (pointnet_train.py:221-228, :310-351)
+    def compile(self, optimizer=None, loss=None, loss_weights=None, metrics=None, **kwargs):
+        """keras Model.compile as the reference driver calls it (pointnet_train.py:334-351): Adam (+ ExponentialDecay),
+        SCCE on the two softmax outputs, MSE on `se3`, per-output loss weights.  Resets the optimizer state (a fresh
+        optimizer is compiled for every training profile, pointnet_train.py:310-319)."""
+        from . import keras_compat as K
+        opt = optimizer if optimizer is not None else K.Adam()
+        if not isinstance(opt, K.Adam):
+            raise TypeError("only Adam (the reference's optimizer) is implemented on the device")
+        lw = {"classification_output": 1.0, "segmentation_output": 1.0, "se3": 1.0}
+        lw.update(loss_weights or {})
+        self._compiled = {"optimizer": opt, "loss_weights": lw}
+        self._step = 0
+        self._dropout_seed = (self._random_seed if isinstance(self._random_seed, int) else 0) * 7919 + 12345
+        self._adam_reset = True
+        return self
+
+    def _train_config(self, explicit_masks=False, sample_offset=0, skip_unweighted_heads=False):
+        if self._compiled is None:
+            raise RuntimeError("call compile() before training")
+        opt, lw = self._compiled["optimizer"], self._compiled["loss_weights"]
+        lr0, steps, rate = opt.schedule()
+        return _ffi.TrainConfig(lw["classification_output"], lw["segmentation_output"], lw["se3"], lr0, rate, steps,
+                                opt.beta_1, opt.beta_2, opt.epsilon, (self._dropout_seed + self._step) & (2**64 - 1), sample_offset,
+                                int(explicit_masks), int(skip_unweighted_heads))
+
+    def _grad_tensor(self) -> torch.Tensor:
+        """The library's flat fp32 gradient buffer as a zero-copy torch tensor (one NCCL bucket)."""
+        if getattr(self, "_grads", None) is None:
+            p, cnt = C.c_void_p(), C.c_size_t()
+            _ffi.check(self._lib.pcp_model_grad_buffer(self._handle, C.byref(p), C.byref(cnt)))
+
+            class _Dev:
+                __cuda_array_interface__ = {"shape": (cnt.value,), "typestr": "<f4", "data": (p.value, False), "version": 2}
+            self._grads = torch.as_tensor(_Dev(), device=torch.device("cuda", torch.cuda.current_device()))
+        return self._grads
+
+    @staticmethod
+    def _labels_to_device(y, dev):
+        yc = y.get("classification_output") if y else None
+        ys = y.get("segmentation_output") if y else None
+        yr = y.get("se3") if y else None
+        conv = lambda a, dt: None if a is None else torch.as_tensor(np.asarray(a) if not isinstance(a, torch.Tensor) else a).to(device=dev, dtype=dt).contiguous()
+        return conv(yc, torch.int32), conv(ys, torch.int32), conv(yr, torch.float32)
+
+    METRIC_KEYS = ["loss", "classification_output_loss", "segmentation_output_loss", "se3_loss",
+                   "classification_output_sparse_categorical_accuracy", "segmentation_output_sparse_categorical_accuracy",
+                   "se3_root_mean_squared_error", "regularization_loss"]
+
+    def train_on_batch(self, x, y, dropout_masks=None, global_batch=None, sample_offset=0, skip_unweighted_heads=False,
+                       apply=True, return_dict=True):
+        """One optimisation step: training-mode forward, losses, backward, [gradient all-reduce], Adam.
+        `x` (b,n,3) and labels may be NumPy (copied H2D here) or CUDA tensors.  Under torch.distributed the flat gradient
+        bucket is all-reduced (SUM; the loss already divides by the global batch) before the identical Adam step."""
+        import torch.distributed as dist
+        dev = torch.device("cuda", torch.cuda.current_device())
+        xd = (x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(x, np.float32)))).to(dev, torch.float32).contiguous()
+        b, n, _ = xd.shape
+        yc, ys, yr = self._labels_to_device(y, dev)
+        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        gb = int(global_batch) if global_batch is not None else b * world
+        m1 = m2 = None
+        if dropout_masks is not None:
+            m1 = torch.as_tensor(np.asarray(dropout_masks[0], np.float32)).to(dev).contiguous()
+            m2 = torch.as_tensor(np.asarray(dropout_masks[1], np.float32)).to(dev).contiguous()
+        cfg = self._train_config(dropout_masks is not None, sample_offset, skip_unweighted_heads)
+        met = np.zeros(8, np.float32)
+        st = _ffi.stream_ptr()
+        _ffi.check(self._lib.pcp_model_loss_backward(self._handle, _ffi.ptr(xd), b, n, _ffi.ptr(yc), _ffi.ptr(ys), _ffi.ptr(yr), C.byref(cfg), gb,
+                                                     _ffi.ptr(m1), _ffi.ptr(m2), _ffi.fptr(met), st))
+        if world > 1:
+            dist.all_reduce(self._grad_tensor(), op=dist.ReduceOp.SUM)       # NCCL over NVLink: one 16.9 MB bucket
+        if apply:
+            if getattr(self, "_adam_reset", False):
+                self._reset_adam_state()
+            _ffi.check(self._lib.pcp_model_adam_step(self._handle, C.byref(cfg), self._step, st))
+            self._step += 1
+        return dict(zip(self.METRIC_KEYS, map(float, met))) if return_dict else met
+
+    def _reset_adam_state(self):
+        _ffi.check(self._lib.pcp_model_reset_optimizer(self._handle))
+        self._adam_reset = False
+
+    def test_on_batch(self, x, y, return_dict=True):
+        dev = torch.device("cuda", torch.cuda.current_device())
+        xd = (x if isinstance(x, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(x, np.float32)))).to(dev, torch.float32).contiguous()
+        b, n, _ = xd.shape
+        yc, ys, yr = self._labels_to_device(y, dev)
+        cfg = self._train_config()
+        met = np.zeros(8, np.float32)
+        _ffi.check(self._lib.pcp_model_evaluate(self._handle, _ffi.ptr(xd), b, n, _ffi.ptr(yc), _ffi.ptr(ys), _ffi.ptr(yr), C.byref(cfg),
+                                                _ffi.fptr(met), _ffi.stream_ptr()))
+        return dict(zip(self.METRIC_KEYS, map(float, met))) if return_dict else met
+
+    def evaluate(self, x, steps=None, verbose=0, return_dict=True):
+        """keras Model.evaluate over an iterator of (x, labels) batches: metric means over `steps` batches."""
+        tot, cnt = np.zeros(8, np.float64), 0
+        for i, (xb, yb) in enumerate(x):
+            if steps is not None and i >= steps:
+                break
+            tot += self.test_on_batch(xb, yb, return_dict=False)
+            cnt += 1
+        mean = tot / max(cnt, 1)
+        return dict(zip(self.METRIC_KEYS, map(float, mean))) if return_dict else list(map(float, mean))
+
+    def fit(self, x=None, validation_data=None, epochs=1, verbose=1, callbacks=None, steps_per_epoch=None, validation_steps=None, **kwargs):
+        """keras Model.fit as the reference driver calls it (pointnet_train.py:221-228): `x` / `validation_data` are
+        (infinite) iterators of (points (b,n,3), {'classification_output','segmentation_output','se3'}) batches.
+        Returns a History whose `.history` has the reference's 14 keys (7 metrics + their val_ twins)."""
+        from . import keras_compat as K
+        if steps_per_epoch is None:
+            raise ValueError("steps_per_epoch is required (the reference passes count // batch_size)")
+        hist = K.History()
+        cbs = [hist] + list(callbacks or [])
+        for cb in cbs:
+            cb.set_model(self)
+            cb.on_train_begin()
+        self.stop_training = False
+        it = iter(x)
+        keys = self.METRIC_KEYS[:7]
+        for epoch in range(epochs):
+            tot = np.zeros(8, np.float64)
+            for _ in range(steps_per_epoch):
+                xb, yb = next(it)
+                tot += self.train_on_batch(xb, yb, return_dict=False)
+            logs = {k: float(v) for k, v in zip(keys, tot[:7] / steps_per_epoch)}
+            if validation_data is not None and validation_steps:
+                val = self.evaluate(iter(validation_data), steps=validation_steps)
+                logs.update({f"val_{k}": val[k] for k in keys})
+            if verbose:
+                print(f"Epoch {epoch + 1}/{epochs} - " + " - ".join(f"{k}: {v:.4f}" for k, v in logs.items()))
+            for cb in cbs:
+                cb.on_epoch_end(epoch, logs)
+            if self.stop_training:
+                break
+        for cb in cbs:
+            cb.on_train_end()
+        return hist
+
+    def gradients_dict(self) -> dict:
+        """Every gradient tensor of the last loss_backward (tests)."""
+        out = {}
+        for name, cnt in self.tensor_table():
+            a = np.empty(cnt, np.float32)
+            _ffi.check(self._lib.pcp_model_get_grad(self._handle, name.encode(), _ffi.fptr(a), cnt))
+            out[name] = a
+        return out
+
+    def train_output(self, which: int, count: int) -> np.ndarray:
+        a = np.empty(count, np.float32)
+        _ffi.check(self._lib.pcp_model_get_train_output(self._handle, which, _ffi.fptr(a), count))
+        return a
+
     # ------------------------------------------------------------------ freeze / thaw (PointNet.py:294-342)
     def _sync_trainable(self):
         if self._handle is None:
