@@ -140,6 +140,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--clouds", type=int, default=4096, help="clouds per GPU per step")
+    ap.add_argument("--train-precision", default="fp32", choices=["fp32", "bf16"])
     ap.add_argument("--skip-extras", action="store_true", help="skip fps / batch32 / all-outputs / cpu baseline (profiling runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -237,12 +238,18 @@ def main():
             model(xs[i % NBUF][:1024])
         ms_all = timed(step_all, max(3, K // 4), 2)
         extras["all_outputs"] = {"value": world * 1024 / (ms_all * 1e-3), "unit": "clouds/s", "clouds_per_step": 1024,
-                                 "note": "cls + seg + R; segmentation head still on the fp32 CUDA-core path this round"}
+                                 "note": "cls + seg + R (what PointNet.call returns); seg head on tcgen05 (tc_gemm), hoisted global term"}
         x32 = xs[0][:32].contiguous()
         ms32 = timed(lambda i: model(x32, heads=("cls",)), 50, 10)
         extras["batch32"] = {"value": world * 32 / (ms32 * 1e-3), "unit": "clouds/s", "ms_per_batch": ms32,
                              "note": "BASELINE config 1 batch (32 x 1024): launch-latency bound"}
-        # FPS (BASELINE config 2): 64 x 100 000 -> 1024
+        # BASELINE config 4: segmentation inference 128 x 2048, per-point logits
+        x4 = torch.from_numpy(synth.gaussian_clouds(4004 + rank, 128, 2048)).to(dev)
+        ms4 = timed(lambda i: model(x4), 10, 3)
+        extras["seg_c4"] = {"value": world * 128 / (ms4 * 1e-3), "unit": "clouds/s", "ms_per_step": ms4, "config": "C4: 128 x 2048, cls + seg + R",
+                            "model_tflops": world * 128 * flops_per_cloud(2048, seg=True) / (ms4 * 1e-3) / 1e12}
+        del x4
+        # BASELINE config 2: FPS 64 x 100 000 -> 1024
         scans = torch.from_numpy(synth.lidar_scans(2002, 64, 100_000)).to(dev)
         ms_fps = timed(lambda i: ops.farthest_point_sample(scans, 1024), 3, 1)
         extras["fps"] = {"metric": "fps_downsampling_mpts_per_sec", "value": world * 64 * 100_000 / (ms_fps * 1e-3) / 1e6, "unit": "Mpts/s",
@@ -250,7 +257,51 @@ def main():
                          "effective_GBps": 64 * 1024 * 100_000 * 20 / (ms_fps * 1e-3) / 1e9,
                          "effective_frac_of_hbm": 64 * 1024 * 100_000 * 20 / (ms_fps * 1e-3) / 1e9 / peaks["hbm_gbs"],
                          "note": "effective = 20 B per point-distance update (SURVEY §8d); on-chip resident, may exceed 1.0"}
-        del scans
+        # streaming kernels on the same LiDAR-sized batch (76.8 MB < L2: two alternating batches)
+        scans2 = scans.flip(0).contiguous()
+        pair = [scans, scans2]
+        npts = 64 * 100_000
+        ms_norm = timed(lambda i: ops.normalize(pair[i & 1]), 10, 3)
+        ms_jit = timed(lambda i: ops.jitter(pair[i & 1], (0.1, 0.1, 0.1), seed=5), 10, 3)
+        Rr = torch.eye(3, device=dev).repeat(64, 1, 1)
+        ms_rot = timed(lambda i: ops.rotate(pair[i & 1], Rr), 10, 3)
+        ms_vox = timed(lambda i: ops.voxel_downsample(pair[i & 1], 0.7), 5, 2)
+        stream = lambda ms: {"GBps": npts * 24 / (ms * 1e-3) / 1e9, "frac_of_hbm": npts * 24 / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "ms": ms}
+        extras["streaming"] = {"config": "64 x 100000 points, 24 B/point algorithmic (12 read + 12 written)", "normalize": stream(ms_norm),
+                               "jitter_philox": stream(ms_jit), "rotate": stream(ms_rot),
+                               "voxel": {"Mpts_per_s": world * npts / (ms_vox * 1e-3) / 1e6, "ms": ms_vox, "voxel_m": 0.7,
+                                         "note": "key + radix sort + segmented reduce; includes torch allocation of outputs/workspace"}}
+        del scans, scans2, pair
+        # BASELINE config 5: 8 raw scans of 131 072 points -> voxel 0.7 m -> resize 8192 -> normalise -> classify
+        from pointcloudprocessing_b200 import pipeline
+        raw = torch.from_numpy(synth.lidar_scans(5005 + rank, 8, 131_072)).to(dev)
+        ms5 = timed(lambda i: pipeline.classify_scans(model, raw, 0.7, 8192), 10, 3)
+        extras["e2e_c5"] = {"value": world * 8 / (ms5 * 1e-3), "unit": "scans/s", "ms_per_step": ms5,
+                            "config": "C5: 8 x 131072 raw points -> voxel 0.7 m (V ~ 12.8k) -> first 8192 (reference truncate) -> PointNet cls, full net"}
+        del raw
+        # BASELINE config 3: training step, classification_pretrain profile (kc46_lidar_config.json:44-68), global batch 256
+        from pointcloudprocessing_b200.pointnet import keras_compat as Kc
+        tb = max(1, 256 // world)
+        tm = PointNet(C_CLASSES, P_PARTS, 0.3, 42, precision=args.train_precision)
+        tm.set_weights_dict(onp.make_params(C_CLASSES, P_PARTS, seed=7, trained_like=False))
+        tm.thaw_shared_network(); tm.thaw_input_transform(); tm.thaw_classification_head(); tm.freeze_segmentation_head()
+        tm.compile(optimizer=Kc.Adam(learning_rate=Kc.ExponentialDecay(1e-4, 7000, 0.7)),
+                   loss_weights={"classification_output": 1.0, "segmentation_output": 0.0, "se3": 0.0})
+        rng = np.random.default_rng(3003 + rank)
+        xt = torch.from_numpy(synth.gaussian_clouds(3003 + rank, tb, N_POINTS)).to(dev)
+        yt = {"classification_output": torch.from_numpy(rng.integers(0, C_CLASSES, tb).astype(np.int32)).to(dev),
+              "segmentation_output": torch.from_numpy(rng.integers(0, P_PARTS, (tb, N_POINTS)).astype(np.int32)).to(dev),
+              "se3": torch.eye(3, device=dev).repeat(tb, 1, 1)}
+        last = {}
+
+        def step_train(i):
+            last.update(tm.train_on_batch(ops.jitter(xt, (0.1, 0.1, 0.1), seed=i), yt, global_batch=tb * world, sample_offset=rank * tb))
+        ms_tr = timed(step_train, 5, 3)
+        extras["train_c3"] = {"value": world * tb / (ms_tr * 1e-3), "unit": "clouds/s", "ms_per_step": ms_tr, "global_batch": tb * world,
+                              "precision": args.train_precision, "loss": last.get("loss"),
+                              "config": "C3: PointNet training step (jitter + fwd + bwd + grad all-reduce + Adam), classification_pretrain profile, 1024 pts",
+                              "note": "both heads forward like the reference; per-shard BN statistics"}
+        del tm, xt, yt
 
     if rank == 0:
         # roofline of the dominant kernel (chain_kernel: 3 launches per forward)

@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(256)
 fold_seg1_kernel(const float *__restrict__ R64, const float *__restrict__ W, uint8_t *__restrict__ img)
 {
     __shared__ float sR[64 * 65];
-    __shared__ float sW[64 * 64];
+    __shared__ __align__(16) float sW[64 * 64];
     const int64_t cloud = blockIdx.y;
     const int c0 = blockIdx.x * 64;               // 64-column slice of the 512 outputs
     for (int i = threadIdx.x; i < 4096; i += 256) {
@@ -203,10 +203,16 @@ fold_seg1_kernel(const float *__restrict__ R64, const float *__restrict__ W, uin
     float acc[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+#pragma unroll 4
     for (int mm = 0; mm < 64; ++mm) {
         const float r = sR[k * 65 + mm];
+        const float4 *w4 = reinterpret_cast<const float4 *>(&sW[mm * 64 + n0]);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) acc[j] = fmaf(r, sW[mm * 64 + n0 + j], acc[j]);
+        for (int q = 0; q < 4; ++q) {
+            const float4 w = w4[q];
+            acc[4 * q] = fmaf(r, w.x, acc[4 * q]); acc[4 * q + 1] = fmaf(r, w.y, acc[4 * q + 1]);
+            acc[4 * q + 2] = fmaf(r, w.z, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(r, w.w, acc[4 * q + 3]);
+        }
     }
 #pragma unroll
     for (int j = 0; j < 16; ++j) {

@@ -115,6 +115,9 @@ static void ws_free(Workspace &ws)
     for (void *p : ws.allocs) cudaFree(p);
     if (ws.pin_x) cudaFreeHost(ws.pin_x);
     if (ws.pin_out) cudaFreeHost(ws.pin_out);
+    if (ws.copy_stream) cudaStreamDestroy(ws.copy_stream);
+    if (ws.ev_start) cudaEventDestroy(ws.ev_start);
+    for (cudaEvent_t e : ws.ev_copied) cudaEventDestroy(e);
     ws = Workspace();
 }
 
@@ -544,13 +547,52 @@ extern "C" int pcp_model_predict_host(pcp_model *m, const float *h_x, int b, int
         PCP_TRY(ws_alloc(ws, &ws.stage_seg, (size_t)ws.total_b * ws.cap_n * P));
         PCP_TRY(ws_alloc(ws, &ws.stage_R, (size_t)ws.total_b * 9));
     }
-    // The caller's buffers are used directly: pinned memory (cudaMallocHost / torch pin_memory) is DMA'd
-    // at full PCIe rate, pageable memory is staged by the driver.
-    PCP_CUDA_OK(cudaMemcpyAsync(ws.stage_x, h_x, xb, cudaMemcpyHostToDevice, st));
-    PCP_TRY(pcp_model_forward(m, ws.stage_x, b, n, heads, h_cls ? ws.stage_cls : nullptr, h_seg ? ws.stage_seg : nullptr,
-                              h_R ? ws.stage_R : nullptr, nullptr, nullptr, stream));
+    // The caller's buffers are used directly: pinned memory (cudaMallocHost / torch pin_memory) is DMA'd at full PCIe
+    // rate, pageable memory is staged by the driver.  The batch is cut into chunks: a copy stream moves chunk i+1 to the
+    // device while the compute stream runs the forward of chunk i, and each chunk's results go back as soon as they exist.
+    if (!ws.copy_stream) {
+        PCP_CUDA_OK(cudaStreamCreateWithFlags(&ws.copy_stream, cudaStreamNonBlocking));
+        PCP_CUDA_OK(cudaEventCreateWithFlags(&ws.ev_start, cudaEventDisableTiming));
+    }
+    // Chunk sizes grow geometrically (256 K points, then x3): the first copy is short, so compute starts early, and every
+    // later copy hides behind the forward of the chunk before it while the per-forward fixed cost is paid only ~4 times.
+    std::vector<int> bounds(1, 0);
+    {
+        int64_t pts = (int64_t)1 << 18;
+        while (bounds.back() < b) {
+            int cb = (int)std::max<int64_t>(1, pts / n);
+            if (b - bounds.back() - cb < cb) cb = b - bounds.back();      // fold a short tail into this chunk
+            bounds.push_back(std::min(b, bounds.back() + cb));
+            pts *= 3;
+        }
+    }
+    const int nchunks = (int)bounds.size() - 1;
+    while ((int)ws.ev_copied.size() < nchunks) {
+        cudaEvent_t e;
+        PCP_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ws.ev_copied.push_back(e);
+    }
+    // the copy stream may not overwrite the staging buffer before earlier work on the caller's stream has finished
+    PCP_CUDA_OK(cudaEventRecord(ws.ev_start, st));
+    PCP_CUDA_OK(cudaStreamWaitEvent(ws.copy_stream, ws.ev_start, 0));
+    for (int i = 0; i < nchunks; ++i) {
+        const int c0 = bounds[i], bc = bounds[i + 1] - c0;
+        PCP_CUDA_OK(cudaMemcpyAsync(ws.stage_x + (size_t)c0 * n * 3, h_x + (size_t)c0 * n * 3, (size_t)bc * n * 3 * sizeof(float),
+                                    cudaMemcpyHostToDevice, ws.copy_stream));
+        PCP_CUDA_OK(cudaEventRecord(ws.ev_copied[i], ws.copy_stream));
+    }
+    for (int i = 0; i < nchunks; ++i) {
+        const int c0 = bounds[i], bc = bounds[i + 1] - c0;
+        PCP_CUDA_OK(cudaStreamWaitEvent(st, ws.ev_copied[i], 0));
+        PCP_TRY(pcp_model_forward(m, ws.stage_x + (size_t)c0 * n * 3, bc, n, heads, h_cls ? ws.stage_cls + (size_t)c0 * C : nullptr,
+                                  h_seg ? ws.stage_seg + (size_t)c0 * n * P : nullptr, h_R ? ws.stage_R + (size_t)c0 * 9 : nullptr,
+                                  nullptr, nullptr, stream));
+        if (h_seg)       // the only large result: stream it back per chunk
+            PCP_CUDA_OK(cudaMemcpyAsync(h_seg + (size_t)c0 * n * P, ws.stage_seg + (size_t)c0 * n * P, (size_t)bc * n * P * sizeof(float),
+                                        cudaMemcpyDeviceToHost, st));
+    }
+    (void)xb; (void)seg_cnt;
     if (h_cls) PCP_CUDA_OK(cudaMemcpyAsync(h_cls, ws.stage_cls, cls_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
-    if (h_seg) PCP_CUDA_OK(cudaMemcpyAsync(h_seg, ws.stage_seg, seg_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (h_R) PCP_CUDA_OK(cudaMemcpyAsync(h_R, ws.stage_R, r_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
     PCP_CUDA_OK(cudaStreamSynchronize(st));
     return PCP_OK;

@@ -51,6 +51,9 @@ struct Workspace {
     float *stage_cls = nullptr, *stage_seg = nullptr, *stage_R = nullptr;
     float *pin_x = nullptr, *pin_out = nullptr;   // pinned host staging
     size_t pin_x_bytes = 0, pin_out_bytes = 0;
+    cudaStream_t copy_stream = nullptr;            // predict_host: H2D of chunk i+1 overlaps the forward of chunk i
+    cudaEvent_t ev_start = nullptr;
+    std::vector<cudaEvent_t> ev_copied;
     std::vector<void *> allocs;
 };
 

@@ -50,39 +50,66 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
         const char *Abase = reinterpret_cast<const char *>(p.A);
         const size_t esz = p.a_f32 ? 4 : 2;
         const size_t a_off = ((size_t)g * p.a_group_stride + (size_t)row0 * p.lda) * esz;
-        // software pipeline: the global loads of k-tile kt+1 are in flight while k-tile kt is written to smem
-        auto load_tile = [&](int kt, uint4 (&v)[8]) {
+        // Rows past the end of the matrix are clamped to the last valid row instead of predicated: every load is
+        // unconditional, so the compiler issues all loads of a k-tile back to back (ONE memory round trip per tile —
+        // predicated loads had been serialised into eight dependent round trips, 3.7 us per k-tile); the duplicated
+        // rows only produce output rows that the epilogue never stores.
+        const char *rowp[8];
 #pragma unroll
-            for (int pass = 0; pass < 8; ++pass) {
-                const int r = pass * 16 + rsub;
-                v[pass] = make_uint4(0u, 0u, 0u, 0u);
-                if (r < rows_valid) {
-                    const char *src = Abase + a_off + ((size_t)r * p.lda + (size_t)kt * 64 + chunk * 8) * esz;
-                    if (p.a_f32) {
-                        const float4 f0 = __ldg(reinterpret_cast<const float4 *>(src));
-                        const float4 f1 = __ldg(reinterpret_cast<const float4 *>(src) + 1);
-                        v[pass] = make_uint4(pack_bf16x2(f0.x, f0.y), pack_bf16x2(f0.z, f0.w), pack_bf16x2(f1.x, f1.y), pack_bf16x2(f1.z, f1.w));
-                    } else {
-                        v[pass] = __ldg(reinterpret_cast<const uint4 *>(src));
-                    }
-                }
-            }
-        };
-        uint4 cur[8], nxt[8];
-        load_tile(0, cur);
-        for (int kt = 0; kt < KT; ++kt) {
+        for (int pass = 0; pass < 8; ++pass) {
+            const int r = min(pass * 16 + rsub, rows_valid - 1);
+            rowp[pass] = Abase + a_off + ((size_t)r * p.lda + (size_t)chunk * 8) * esz;
+        }
+        auto publish = [&](int kt, const uint4 (&v)[8]) {
             const int s = kt % kGemmStages;
-            if (kt + 1 < KT) load_tile(kt + 1, nxt);
             if (kt >= kGemmStages) mbar_wait(&empty[s], (uint32_t)(((kt / kGemmStages) - 1) & 1), 40);
             uint8_t *As = base + s * kGemmStageBytes;
 #pragma unroll
             for (int pass = 0; pass < 8; ++pass)
-                *reinterpret_cast<uint4 *>(As + sw128_offset(128, (uint32_t)(pass * 16 + rsub), (uint32_t)chunk * 8)) = cur[pass];
+                *reinterpret_cast<uint4 *>(As + sw128_offset(128, (uint32_t)(pass * 16 + rsub), (uint32_t)chunk * 8)) = v[pass];
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(&full[s]);
+        };
+        if (p.a_f32) {
+            // fp32 activations (pooled features): one k-tile (16 x float4) in flight, converted to bf16 on arrival
+            float4 raw[16];
+            auto issue = [&](int kt) {
 #pragma unroll
-            for (int pass = 0; pass < 8; ++pass) cur[pass] = nxt[pass];
+                for (int pass = 0; pass < 8; ++pass) {
+                    const float4 *src = reinterpret_cast<const float4 *>(rowp[pass] + (size_t)kt * 256);
+                    raw[2 * pass] = __ldg(src);
+                    raw[2 * pass + 1] = __ldg(src + 1);
+                }
+            };
+            issue(0);
+            for (int kt = 0; kt < KT; ++kt) {
+                uint4 v[8];
+#pragma unroll
+                for (int pass = 0; pass < 8; ++pass) {
+                    const float4 f0 = raw[2 * pass], f1 = raw[2 * pass + 1];
+                    v[pass] = make_uint4(pack_bf16x2(f0.x, f0.y), pack_bf16x2(f0.z, f0.w), pack_bf16x2(f1.x, f1.y), pack_bf16x2(f1.z, f1.w));
+                }
+                if (kt + 1 < KT) issue(kt + 1);
+                publish(kt, v);
+            }
+        } else {
+            // bf16 activations: two k-tiles (2 x 8 x 16 B) in flight
+            uint4 r0[8], r1[8];
+            auto issue = [&](int kt, uint4 (&dst)[8]) {
+#pragma unroll
+                for (int pass = 0; pass < 8; ++pass) dst[pass] = __ldg(reinterpret_cast<const uint4 *>(rowp[pass] + (size_t)kt * 128));
+            };
+            issue(0, r0);
+            if (KT > 1) issue(1, r1);
+            for (int kt = 0; kt < KT; kt += 2) {
+                publish(kt, r0);
+                if (kt + 2 < KT) issue(kt + 2, r0);
+                if (kt + 1 < KT) {
+                    publish(kt + 1, r1);
+                    if (kt + 3 < KT) issue(kt + 3, r1);
+                }
+            }
         }
         // ---------------- epilogue: thread = output row ----------------
         mbar_wait(&acc_full, 0, 41);
