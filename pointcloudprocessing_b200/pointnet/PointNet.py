@@ -446,7 +446,7 @@ class PointNet:
                    "se3_root_mean_squared_error", "regularization_loss"]
 
     def train_on_batch(self, x, y, dropout_masks=None, global_batch=None, sample_offset=0, skip_unweighted_heads=False,
-                       apply=True, return_dict=True):
+                       apply=True, return_dict=True, allreduce=True):
         """One optimisation step: training-mode forward, losses, backward, [gradient all-reduce], Adam.
         `x` (b,n,3) and labels may be NumPy (copied H2D here) or CUDA tensors.  Under torch.distributed the flat gradient
         bucket is all-reduced (SUM; the loss already divides by the global batch) before the identical Adam step."""
@@ -466,7 +466,7 @@ class PointNet:
         st = _ffi.stream_ptr()
         _ffi.check(self._lib.pcp_model_loss_backward(self._handle, _ffi.ptr(xd), b, n, _ffi.ptr(yc), _ffi.ptr(ys), _ffi.ptr(yr), C.byref(cfg), gb,
                                                      _ffi.ptr(m1), _ffi.ptr(m2), _ffi.fptr(met), st))
-        if world > 1:
+        if world > 1 and allreduce:
             dist.all_reduce(self._grad_tensor(), op=dist.ReduceOp.SUM)       # NCCL over NVLink: one 16.9 MB bucket
         if apply:
             if getattr(self, "_adam_reset", False):
