@@ -215,6 +215,26 @@ int pcp_model_reset_optimizer(pcp_model *m);
 /* copy one gradient tensor to the host (tests) */
 int pcp_model_get_grad(pcp_model *m, const char *name, float *h_data, size_t count);
 
+/* ---- host-side data plumbing either side of the path (no GPU needed) ---- */
+
+/* CRC32C (Castagnoli) and the TFRecord masked form ((crc >> 15 | crc << 17) + 0xa282ead8) used by
+ * tf.io.TFRecordWriter (pointcloud/PointCloudSet.py:251-288). */
+uint32_t pcp_crc32c(const void *h_data, size_t bytes);
+uint32_t pcp_crc32c_masked(const void *h_data, size_t bytes);
+/* Walk a TFRecord file image: payload offset / length of every record.  verify_crc: 0 none, 1 length CRCs,
+ * 2 length + payload CRCs.  h_offsets / h_lengths may be NULL (count only). */
+int pcp_tfrecord_scan(const uint8_t *h_buf, size_t bytes, int verify_crc, uint64_t *h_offsets, uint64_t *h_lengths,
+                      size_t capacity, size_t *count);
+/* Decode one tf.train.Example of the PointCloudSet schema (pointcloud/PointCloudSet.py:100-105, :306-323):
+ * observations float[width*3], class_label int64, part_labels int64[width] (written as int32), se3 float[9]. */
+int pcp_example_decode(const uint8_t *h_rec, size_t bytes, int64_t width, float *h_obs, int64_t *h_class_label,
+                       int32_t *h_part_labels, float *h_se3);
+/* Parse one AftrBurner frame text ("(x, y, z) class part" per line) with the semantics of
+ * PointCloudSet.add_from_aftr_output (pointcloud/PointCloudSet.py:161-198).  Label lists are '\n'-separated. */
+int pcp_parse_aftr_frame(const char *h_text, size_t bytes, const char *class_labels_nl, const char *part_labels_nl,
+                         double *h_xyz, int32_t *h_part, size_t capacity, size_t *count, int32_t *class_label,
+                         size_t *h_nonfinite);
+
 #ifdef __cplusplus
 }
 #endif
