@@ -516,16 +516,36 @@ class PointNet:
         self.stop_training = False
         it = iter(x)
         keys = self.METRIC_KEYS[:7]
+        import torch.distributed as dist
+        from .. import parallel
+        rank, world = parallel.world()
         for epoch in range(epochs):
             tot = np.zeros(8, np.float64)
             for _ in range(steps_per_epoch):
                 xb, yb = next(it)
-                tot += self.train_on_batch(xb, yb, return_dict=False)
-            logs = {k: float(v) for k, v in zip(keys, tot[:7] / steps_per_epoch)}
+                if world > 1:        # every rank draws the same global batch and trains on its own contiguous shard
+                    gb = len(xb)
+                    xb, yb, off = parallel.shard_batch(xb, yb)
+                    tot += self.train_on_batch(xb, yb, global_batch=gb, sample_offset=off, return_dict=False)
+                else:
+                    tot += self.train_on_batch(xb, yb, return_dict=False)
+            logs_vec = tot[:7] / steps_per_epoch
+            if world > 1:
+                self._average_bn_statistics()
+            val_vec = None
             if validation_data is not None and validation_steps:
                 val = self.evaluate(iter(validation_data), steps=validation_steps)
-                logs.update({f"val_{k}": val[k] for k in keys})
-            if verbose:
+                val_vec = np.array([val[k] for k in keys], np.float64)
+            if world > 1:            # identical logs on every rank => identical callback decisions (no divergent early stop)
+                dev = torch.device("cuda", torch.cuda.current_device())
+                t = torch.from_numpy(np.concatenate([logs_vec, val_vec if val_vec is not None else np.zeros(0)])).to(dev)
+                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+                t = (t / world).cpu().numpy()
+                logs_vec, val_vec = t[:7], (t[7:] if val_vec is not None else None)
+            logs = {k: float(v) for k, v in zip(keys, logs_vec)}
+            if val_vec is not None:
+                logs.update({f"val_{k}": float(v) for k, v in zip(keys, val_vec)})
+            if verbose and rank == 0:
                 print(f"Epoch {epoch + 1}/{epochs} - " + " - ".join(f"{k}: {v:.4f}" for k, v in logs.items()))
             for cb in cbs:
                 cb.on_epoch_end(epoch, logs)
@@ -534,6 +554,21 @@ class PointNet:
         for cb in cbs:
             cb.on_train_end()
         return hist
+
+    def _average_bn_statistics(self):
+        """Data parallel: BN moving statistics are accumulated per shard; average them across ranks once per epoch so
+        every rank validates (and checkpoints) the same model."""
+        import torch.distributed as dist
+        dev = torch.device("cuda", torch.cuda.current_device())
+        w = self.get_weights_dict()
+        names = [k for k in w if "/bn/moving_" in k]
+        flat = torch.from_numpy(np.concatenate([w[k] for k in names])).to(dev)
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+        flat = (flat / dist.get_world_size()).cpu().numpy()
+        o = 0
+        for k in names:
+            self.set_tensor(k, flat[o:o + w[k].size])
+            o += w[k].size
 
     def gradients_dict(self) -> dict:
         """Every gradient tensor of the last loss_backward (tests)."""
