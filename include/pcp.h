@@ -170,6 +170,10 @@ int pcp_selftest_umma(const float *h_a, const float *h_b, int N, int K, float *h
 /* same with a CTA pair (cluster of 2, cta_group::2): D (256 x N) = A (256 x K) . B (N x K)^T */
 int pcp_selftest_umma2(const float *h_a, const float *h_b, int N, int K, float *h_d);
 
+/* weight-gradient self-test (tests only): dW (cin x cout) = A^T (cin x rows) . dZ (rows x cout) through the MN-major
+ * tcgen05 split-K kernel of the bf16 training step; operands rounded to bf16, fp32 accumulate.  Host pointers. */
+int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t rows, int cin, int cout, float *h_dw);
+
 /* ---- training (pointnet_train.py:310-351) ---- */
 #define PCP_GROUP_SHARED 0
 #define PCP_GROUP_INPUT_TRANSFORM 1

@@ -1,0 +1,265 @@
+// tc_train.cu — tensor-core pieces of the training step (PCP_PRECISION_BF16): bf16 operands, fp32 accumulation in TMEM.
+//   * pack_weight_image: fp32 weights in the flat parameter buffer -> the packed SWIZZLE_128B bf16 image tc_gemm streams
+//     (forward: W as (K=cin x N=cout); input gradient: W^T as (K=cout x N=cin)).  Runs every step: weights change.
+//   * tc_wgrad_kernel: the weight gradient dW (cin x cout) += A^T (cin x rows) . dZ (rows x cout).  Both operands are
+//     row-major activations, i.e. MN-MAJOR for the MMA (the contraction index `rows` is the slow one), so the kernel
+//     uses tcgen05's MN-major SWIZZLE_128B operand form: producer warps convert fp32 -> bf16 and write 16-byte chunks
+//     (8 consecutive channels of one row) straight into the canonical ((8,n),(8,k)):((1,LBO),(8,SBO)) layout — no
+//     transpose anywhere.  The reduction over rows is split across CTAs (split-K) and finished with fp32 atomics into the
+//     zero-initialised flat gradient buffer.
+#include <cstring>
+#include <vector>
+
+#include "tc_gemm.cuh"
+#include "tc_train.cuh"
+#include "umma.cuh"
+
+namespace pcp {
+
+using namespace umma;
+
+// ------------------------------------------------------------------------------------------------
+// weight image packer: element (k, n) of the logical (K x N) matrix is W[k*ldw + n] (transpose = 0) or W[n*ldw + k]
+// (transpose = 1); tiles [nt][kt] of (bnt rows x 64 K) bf16, K-major SWIZZLE_128B (tc_gemm.cu:pack_gemm_b_image)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+pack_weight_image_kernel(const float *__restrict__ W, int K, int N, int ldw, int transpose, int bnt, uint16_t *__restrict__ img)
+{
+    const int KT = K >> 6, ntiles = (N + bnt - 1) / bnt;
+    const int64_t total = (int64_t)ntiles * KT * bnt * 64;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        // decode i as (tile, r, k) with k fastest so that global reads of the non-transposed case are strided by ldw but
+        // the writes stay inside one 128-byte swizzle row
+        const int k = (int)(i & 63);
+        const int64_t t = i >> 6;
+        const int r = (int)(t % bnt);
+        const int64_t tile = t / bnt;
+        const int kt = (int)(tile % KT), nt = (int)(tile / KT);
+        const int n = nt * bnt + r, kk = kt * 64 + k;
+        float v = 0.f;
+        if (n < N) v = transpose ? __ldg(W + (int64_t)n * ldw + kk) : __ldg(W + (int64_t)kk * ldw + n);
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        img[tile * (bnt * 64) + sw128_offset((uint32_t)bnt, (uint32_t)r, (uint32_t)k) / 2] = *reinterpret_cast<const uint16_t *>(&h);
+    }
+}
+
+int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, uint8_t *d_img, cudaStream_t st)
+{
+    PCP_REQUIRE(K >= 64 && K % 64 == 0, PCP_ERR_UNSUPPORTED, "pack_weight_image: K=%d must be a multiple of 64", K);
+    const int bnt = tc_gemm_bn_tile(N);
+    const int64_t total = (int64_t)((N + bnt - 1) / bnt) * (K / 64) * bnt * 64;
+    const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)sm_count() * 8);
+    pack_weight_image_kernel<<<grid, 256, 0, st>>>(d_W, K, N, ldw, transpose ? 1 : 0, bnt, reinterpret_cast<uint16_t *>(d_img));
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// wgrad
+// ------------------------------------------------------------------------------------------------
+constexpr int kWgThreads = 288;                 // warps 0-7 producers (+ epilogue on warps 0-3), warp 8 MMA issuer
+constexpr int kWgStages = 3;
+constexpr uint32_t kWgTile = 16384;             // one operand tile: 128 (MN) x 64 (K = rows) bf16
+constexpr uint32_t kWgStageBytes = 2 * kWgTile;
+constexpr uint32_t kWgSmem = kWgStages * kWgStageBytes + 1024;
+constexpr uint32_t kWgSBO = 1024;               // stride between groups of 8 rows (K)
+constexpr uint32_t kWgLBO = 8192;               // stride between groups of 64 channels (MN)
+
+// MN-major SWIZZLE_128B shared-memory descriptor
+__device__ __forceinline__ uint64_t make_sdesc_mn(uint32_t saddr)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(kWgLBO >> 4) << 16;
+    d |= (uint64_t)(kWgSBO >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+struct WgradParams {
+    const float *A; int64_t lda;          // (rows x cin) fp32 row-major
+    const float *Z; int64_t ldz;          // (rows x cout) fp32 row-major (dZ)
+    float *dW; int64_t lddw;              // (cin x cout) fp32, accumulated with atomics
+    int64_t rows;
+    int cin, cout;
+    int64_t rows_per_split;               // multiple of 64
+};
+
+__global__ void __launch_bounds__(kWgThreads, 2)
+tc_wgrad_kernel(const WgradParams p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t full[kWgStages], empty[kWgStages], acc_full;
+    __shared__ uint32_t tmem_base;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n0 = blockIdx.x * 128, m0 = blockIdx.y * 128;
+    const int64_t r_begin = (int64_t)blockIdx.z * p.rows_per_split;
+    const int64_t r_end = min(p.rows, r_begin + p.rows_per_split);
+    const int KT = (int)((r_end - r_begin + 63) >> 6);
+
+    if (tid == 0) {
+        for (int i = 0; i < kWgStages; ++i) { mbar_init(&full[i], 8); mbar_init(&empty[i], 1); }
+        mbar_init(&acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 8) tmem_alloc(&tmem_base, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base;
+    if (KT <= 0) {                                   // empty split: nothing to add (uniform per CTA)
+        __syncthreads();
+        if (warp == 8) tmem_dealloc(tmem, 128);
+        return;
+    }
+
+    if (warp < 8) {
+        // ---------------- producers: 4 A chunks + 4 Z chunks (16 B = 8 channels of one row) per thread per k-tile ----------------
+        // chunk c = tid + 256*j : row k = c / 16 (0..63), channel group q = c % 16 (channels q*8 .. q*8+7)
+        int krow[4], q[4];
+        uint32_t soff[4];
+        bool a_ok[4], z_ok[4];
+        const float *ap[4], *zp[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = tid + 256 * j;
+            krow[j] = c >> 4; q[j] = c & 15;
+            soff[j] = (uint32_t)(q[j] >> 3) * kWgLBO + (uint32_t)(krow[j] >> 3) * kWgSBO + (uint32_t)(krow[j] & 7) * 128u +
+                      (uint32_t)(((q[j] & 7) ^ (krow[j] & 7)) << 4);
+            const int ma = m0 + q[j] * 8, nz = n0 + q[j] * 8;
+            a_ok[j] = ma + 8 <= p.cin; z_ok[j] = nz + 8 <= p.cout;
+            ap[j] = p.A + (a_ok[j] ? ma : 0);            // clamped column: loads stay unconditional, invalid chunks are zeroed
+            zp[j] = p.Z + (z_ok[j] ? nz : 0);
+        }
+        float4 ra[8], rz[8];
+        auto issue = [&](int kt) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t r = min(r_begin + (int64_t)kt * 64 + krow[j], p.rows - 1);     // clamped row, zeroed below
+                const float4 *sa = reinterpret_cast<const float4 *>(ap[j] + r * p.lda);
+                const float4 *sz = reinterpret_cast<const float4 *>(zp[j] + r * p.ldz);
+                ra[2 * j] = __ldg(sa); ra[2 * j + 1] = __ldg(sa + 1);
+                rz[2 * j] = __ldg(sz); rz[2 * j + 1] = __ldg(sz + 1);
+            }
+        };
+        issue(0);
+        for (int kt = 0; kt < KT; ++kt) {
+            const int s = kt % kWgStages;
+            uint4 va[4], vz[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const bool row_ok = r_begin + (int64_t)kt * 64 + krow[j] < r_end;
+                const float4 a0 = ra[2 * j], a1 = ra[2 * j + 1], z0 = rz[2 * j], z1 = rz[2 * j + 1];
+                va[j] = (row_ok && a_ok[j]) ? make_uint4(pack_bf16x2(a0.x, a0.y), pack_bf16x2(a0.z, a0.w), pack_bf16x2(a1.x, a1.y), pack_bf16x2(a1.z, a1.w))
+                                            : make_uint4(0u, 0u, 0u, 0u);
+                vz[j] = (row_ok && z_ok[j]) ? make_uint4(pack_bf16x2(z0.x, z0.y), pack_bf16x2(z0.z, z0.w), pack_bf16x2(z1.x, z1.y), pack_bf16x2(z1.z, z1.w))
+                                            : make_uint4(0u, 0u, 0u, 0u);
+            }
+            if (kt + 1 < KT) issue(kt + 1);
+            if (kt >= kWgStages) mbar_wait(&empty[s], (uint32_t)(((kt / kWgStages) - 1) & 1), 50);
+            uint8_t *As = base + s * kWgStageBytes, *Zs = As + kWgTile;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                *reinterpret_cast<uint4 *>(As + soff[j]) = va[j];
+                *reinterpret_cast<uint4 *>(Zs + soff[j]) = vz[j];
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full[s]);
+        }
+        // ---------------- epilogue (warps 0-3): TMEM lane = input channel m, columns = output channels ----------------
+        if (warp < 4) {
+            mbar_wait(&acc_full, 0, 51);
+            tc_fence_after();
+            const int m = m0 + tid;
+            for (int c0 = 0; c0 < 128; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
+                tmem_ld_wait();
+                if (m < p.cin) {
+                    float *dst = p.dW + (int64_t)m * p.lddw + n0 + c0;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e)
+                        if (n0 + c0 + e < p.cout) atomicAdd(dst + e, __uint_as_float(v[e]));
+                }
+            }
+        }
+    } else {
+        // ---------------- MMA issuer: D[128 cin, 128 cout] += A^T[128, 16] . Z[16, 128] per instruction ----------------
+        const uint32_t idesc = make_idesc_bf16(128, 128) | (1u << 15) | (1u << 16);      // a_major = b_major = MN
+        for (int kt = 0; kt < KT; ++kt) {
+            const int s = kt % kWgStages;
+            mbar_wait(&full[s], (uint32_t)((kt / kWgStages) & 1), 52);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(base) + s * kWgStageBytes, z_addr = a_addr + kWgTile;
+            if (elect_one_sync()) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)        // 16 rows (two 8-row groups) per MMA
+                    mma_bf16_ss(tmem, make_sdesc_mn(a_addr + k * 2 * kWgSBO), make_sdesc_mn(z_addr + k * 2 * kWgSBO), idesc, (kt | k) > 0);
+                mma_commit(&empty[s]);
+                if (kt == KT - 1) mma_commit(&acc_full);
+            }
+            __syncwarp();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) tmem_dealloc(tmem, 128);
+}
+
+int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ, int64_t ldz, int cout, float *dW, int64_t lddw,
+             cudaStream_t st)
+{
+    PCP_REQUIRE(A && dZ && dW, PCP_ERR_INVALID, "tc_wgrad: null operand");
+    PCP_REQUIRE(cin % 8 == 0 && cout % 8 == 0 && lda % 4 == 0 && ldz % 4 == 0, PCP_ERR_UNSUPPORTED,
+                "tc_wgrad: cin=%d / cout=%d must be multiples of 8 and the leading dimensions multiples of 4", cin, cout);
+    PCP_REQUIRE((((uintptr_t)A | (uintptr_t)dZ) & 15u) == 0, PCP_ERR_UNSUPPORTED, "tc_wgrad: operands must be 16-byte aligned");
+    if (rows <= 0) return PCP_OK;
+    WgradParams p;
+    p.A = A; p.lda = lda; p.Z = dZ; p.ldz = ldz; p.dW = dW; p.lddw = lddw; p.rows = rows; p.cin = cin; p.cout = cout;
+    const int mt = (cin + 127) / 128, nt = (cout + 127) / 128;
+    const int64_t ktiles = (rows + 63) / 64;
+    int64_t splits = std::max<int64_t>(1, (2 * (int64_t)sm_count()) / ((int64_t)mt * nt));      // ~2 CTAs per SM in flight
+    splits = std::min<int64_t>(splits, std::max<int64_t>(1, ktiles / 4));                        // at least 4 k-tiles per split
+    splits = std::min<int64_t>(splits, 65535);
+    const int64_t kps = (ktiles + splits - 1) / splits;
+    p.rows_per_split = kps * 64;
+    splits = (ktiles + kps - 1) / kps;
+    static bool attr = false;
+    if (!attr) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWgSmem));
+        attr = true;
+    }
+    tc_wgrad_kernel<<<dim3(nt, mt, (unsigned)splits), kWgThreads, kWgSmem, st>>>(p);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+}  // namespace pcp
+
+using namespace pcp;
+
+// test hook: dW (cin x cout) = A^T . dZ with bf16-rounded operands, host in / host out, synchronous
+extern "C" int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t rows, int cin, int cout, float *h_dw)
+{
+    PCP_REQUIRE(h_a && h_dz && h_dw && rows >= 1 && cin >= 8 && cout >= 8, PCP_ERR_INVALID, "pcp_selftest_wgrad: bad arguments");
+    float *da = nullptr, *dz = nullptr, *dw = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&da, (size_t)rows * cin * 4)); PCP_CUDA_OK(cudaMalloc(&dz, (size_t)rows * cout * 4));
+    PCP_CUDA_OK(cudaMalloc(&dw, (size_t)cin * cout * 4));
+    PCP_CUDA_OK(cudaMemcpy(da, h_a, (size_t)rows * cin * 4, cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemcpy(dz, h_dz, (size_t)rows * cout * 4, cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemset(dw, 0, (size_t)cin * cout * 4));
+    int rc = tc_wgrad(da, cin, rows, cin, dz, cout, cout, dw, cout, nullptr);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (rc == PCP_OK && e != cudaSuccess) {
+        unsigned info[4] = {0, 0, 0, 0};
+        cudaMemcpyFromSymbol(info, g_mbar_timeout_info, sizeof(info));
+        set_error("pcp_selftest_wgrad: %s (timeout info %08x %u %u %u)", cudaGetErrorString(e), info[0], info[1], info[2], info[3]);
+        rc = PCP_ERR_CUDA;
+    }
+    if (rc == PCP_OK) PCP_CUDA_OK(cudaMemcpy(h_dw, dw, (size_t)cin * cout * 4, cudaMemcpyDeviceToHost));
+    cudaFree(da); cudaFree(dz); cudaFree(dw);
+    return rc;
+}

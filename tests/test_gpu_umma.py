@@ -36,3 +36,26 @@ def test_umma_pair_gemm_matches_bf16_matmul(lib, N, K):
     _ffi.check(lib.pcp_selftest_umma2(_ffi.fptr(a), _ffi.fptr(b), N, K, _ffi.fptr(d)))
     ref = bf16_round(a).astype(np.float64) @ bf16_round(b).astype(np.float64).T
     assert np.abs(d - ref).max() <= 1e-3 * np.abs(ref).max()
+
+
+def _bf16_round(a):
+    import torch
+    return torch.from_numpy(a).to(torch.bfloat16).to(torch.float32).numpy()
+
+
+@pytest.mark.parametrize("rows,cin,cout", [(64, 128, 128), (200, 64, 64), (1000, 128, 1024), (4096, 64, 128), (333, 512, 256), (96, 1024, 512),
+                                            (70000, 128, 1024), (50, 256, 4096), (129, 64, 512)])
+def test_wgrad_mn_major_tensor_core(lib, rows, cin, cout):
+    """dW = A^T . dZ on tcgen05 with MN-major SWIZZLE_128B operands (tc_train.cu): exact up to fp32 summation order once
+    the operands are rounded to bf16 like the kernel rounds them."""
+    import ctypes as C
+    rng = np.random.default_rng(rows + cin)
+    a = rng.standard_normal((rows, cin)).astype(np.float32)
+    dz = rng.standard_normal((rows, cout)).astype(np.float32)
+    dw = np.zeros((cin, cout), np.float32)
+    fp = lambda x: x.ctypes.data_as(C.POINTER(C.c_float))
+    st = lib.pcp_selftest_wgrad(fp(a), fp(dz), rows, cin, cout, fp(dw))
+    assert st == 0, lib.pcp_last_error()
+    ref = _bf16_round(a).astype(np.float64).T @ _bf16_round(dz).astype(np.float64)
+    err = np.abs(dw - ref).max() / np.abs(ref).max()
+    assert err < 2e-5, err
