@@ -173,6 +173,10 @@ int pcp_selftest_umma2(const float *h_a, const float *h_b, int N, int K, float *
 /* weight-gradient self-test (tests only): dW (cin x cout) = A^T (cin x rows) . dZ (rows x cout) through the MN-major
  * tcgen05 split-K kernel of the bf16 training step; operands rounded to bf16, fp32 accumulate.  Host pointers. */
 int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t rows, int cin, int cout, float *h_dw);
+/* forward / input-gradient GEMM self-test (tests only): C (rows x n) (+)= A (rows x k) . W through the device-side
+ * weight-image packer + tcgen05 GEMM of the bf16 training step; W is (k x n) row-major, or (n x k) row-major when
+ * transpose_w (dA = dZ . W^T).  Host pointers; h_c is read when accumulate != 0. */
+int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate, float *h_c);
 
 /* ---- training (pointnet_train.py:310-351) ---- */
 #define PCP_GROUP_SHARED 0

@@ -35,9 +35,31 @@ def normalize(pc):
     return c / scale
 
 
+_GEMM_BF16 = False
+
+
+class bf16_gemms:
+    """Context manager: model the product's precision="bf16" TRAINING arithmetic — the operands of every layer GEMM whose
+    contraction length is a multiple of 64 are rounded to bf16 (straight-through for autograd), products and sums stay
+    fp32.  The 3-channel input layers and the per-cloud pc@R / X@R64 products stay fp32, as on the device."""
+    def __enter__(self):
+        global _GEMM_BF16
+        self._old, _GEMM_BF16 = _GEMM_BF16, True
+
+    def __exit__(self, *a):
+        global _GEMM_BF16
+        _GEMM_BF16 = self._old
+
+
+def _mm(x, w):
+    if _GEMM_BF16 and x.shape[-1] % 64 == 0:
+        x, w = x.bfloat16().float(), w.bfloat16().float()
+    return x @ w
+
+
 def _layer(x, p, name, training, bn_train_layers, act=True, new_stats=None):
     """PointNet.py:554-566 / :642-654."""
-    y = x @ p[f"{name}/kernel"]
+    y = _mm(x, p[f"{name}/kernel"])
     if f"{name}/bias" in p:
         y = y + p[f"{name}/bias"]
     if f"{name}/bn/gamma" in p:
@@ -65,7 +87,7 @@ def _tnet(x, p, name, k, training, bnl, new_stats):
     h = torch.amax(h, dim=1)            # even gradient split on ties, like tf.reduce_max
     for nm in names[3:]:
         h = _layer(h, p, nm, training, bnl, new_stats=new_stats)
-    m = (h @ p[f"{name}/w"]).reshape(-1, k, k) + p[f"{name}/b"]
+    m = _mm(h, p[f"{name}/w"]).reshape(-1, k, k) + p[f"{name}/b"]
     return m
 
 

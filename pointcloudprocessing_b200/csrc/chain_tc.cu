@@ -563,8 +563,8 @@ void model_destroy_bf16(pcp_model *m)
     heads_tc_destroy(m);
     if (!m->tc) return;
     TcState *ts = reinterpret_cast<TcState *>(m->tc);
-    for (void *p : ts->allocs) cudaFree(p);
-    cudaFree(ts->wc); cudaFree(ts->centroid); cudaFree(ts->scale);
+    for (void *p : ts->allocs) PCP_RELEASE(cudaFree(p));
+    PCP_RELEASE(cudaFree(ts->wc)); PCP_RELEASE(cudaFree(ts->centroid)); PCP_RELEASE(cudaFree(ts->scale));
     delete ts;
     m->tc = nullptr;
 }

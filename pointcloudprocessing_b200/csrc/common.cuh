@@ -1,5 +1,6 @@
 // common.cuh — shared host/device helpers for libpcp_b200.so (sm_100a only).
 #pragma once
+#include <cstdio>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -20,6 +21,17 @@ void count_launch(int n = 1);
             pcp::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
             return PCP_ERR_CUDA;                                                                  \
         }                                                                                         \
+    } while (0)
+
+// teardown paths cannot return an error: a failing release is reported on stderr and cleared so it does not surface later
+// as somebody else's "last error"
+#define PCP_RELEASE(call)                                                                        \
+    do {                                                                                        \
+        cudaError_t _e = (call);                                                                \
+        if (_e != cudaSuccess) {                                                                \
+            fprintf(stderr, "pcp: %s:%d: %s -> %s\n", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+            (void)cudaGetLastError();                                                           \
+        }                                                                                       \
     } while (0)
 
 #define PCP_CHECK_LAUNCH()                                                                      \

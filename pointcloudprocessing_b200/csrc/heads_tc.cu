@@ -60,10 +60,10 @@ void heads_tc_destroy(pcp_model *m)
 {
     if (!m->tc_heads) return;
     TcHeads *h = reinterpret_cast<TcHeads *>(m->tc_heads);
-    for (void *p : h->allocs) cudaFree(p);
-    cudaFree(h->d512); cudaFree(h->d256);
-    cudaFree(h->h0); cudaFree(h->h1); cudaFree(h->s512); cudaFree(h->s256); cudaFree(h->s128a); cudaFree(h->s128b);
-    cudaFree(h->wseg_img); cudaFree(h->gvec);
+    for (void *p : h->allocs) PCP_RELEASE(cudaFree(p));
+    PCP_RELEASE(cudaFree(h->d512)); PCP_RELEASE(cudaFree(h->d256));
+    PCP_RELEASE(cudaFree(h->h0)); PCP_RELEASE(cudaFree(h->h1)); PCP_RELEASE(cudaFree(h->s512)); PCP_RELEASE(cudaFree(h->s256)); PCP_RELEASE(cudaFree(h->s128a)); PCP_RELEASE(cudaFree(h->s128b));
+    PCP_RELEASE(cudaFree(h->wseg_img)); PCP_RELEASE(cudaFree(h->gvec));
     delete h;
     m->tc_heads = nullptr;
 }

@@ -112,12 +112,12 @@ static int ws_alloc(Workspace &ws, float **p, size_t count)
 
 static void ws_free(Workspace &ws)
 {
-    for (void *p : ws.allocs) cudaFree(p);
-    if (ws.pin_x) cudaFreeHost(ws.pin_x);
-    if (ws.pin_out) cudaFreeHost(ws.pin_out);
-    if (ws.copy_stream) cudaStreamDestroy(ws.copy_stream);
-    if (ws.ev_start) cudaEventDestroy(ws.ev_start);
-    for (cudaEvent_t e : ws.ev_copied) cudaEventDestroy(e);
+    for (void *p : ws.allocs) PCP_RELEASE(cudaFree(p));
+    if (ws.pin_x) PCP_RELEASE(cudaFreeHost(ws.pin_x));
+    if (ws.pin_out) PCP_RELEASE(cudaFreeHost(ws.pin_out));
+    if (ws.copy_stream) PCP_RELEASE(cudaStreamDestroy(ws.copy_stream));
+    if (ws.ev_start) PCP_RELEASE(cudaEventDestroy(ws.ev_start));
+    for (cudaEvent_t e : ws.ev_copied) PCP_RELEASE(cudaEventDestroy(e));
     ws = Workspace();
 }
 
@@ -415,8 +415,8 @@ extern "C" int pcp_model_destroy(pcp_model *m)
     ws_free(m->ws);
     model_destroy_bf16(m);
     train_destroy(m);
-    cudaFree(m->d_params); cudaFree(m->d_fold);
-    cudaFree(m->d_grads); cudaFree(m->d_adam_m); cudaFree(m->d_adam_v);
+    PCP_RELEASE(cudaFree(m->d_params)); PCP_RELEASE(cudaFree(m->d_fold));
+    PCP_RELEASE(cudaFree(m->d_grads)); PCP_RELEASE(cudaFree(m->d_adam_m)); PCP_RELEASE(cudaFree(m->d_adam_v));
     delete m;
     return PCP_OK;
 }

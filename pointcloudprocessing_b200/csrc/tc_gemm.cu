@@ -136,10 +136,17 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
                     float *dst = p.C32 + c_off + nbase;
                     if (nbase + 32 <= p.N && (p.ldc & 3) == 0 && (((uintptr_t)dst & 15u) == 0)) {
 #pragma unroll
-                        for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4 *>(dst + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
+                        for (int e = 0; e < 32; e += 4) {
+                            float4 q = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
+                            if (p.accumulate) {
+                                const float4 c = *reinterpret_cast<const float4 *>(dst + e);
+                                q.x += c.x; q.y += c.y; q.z += c.z; q.w += c.w;
+                            }
+                            *reinterpret_cast<float4 *>(dst + e) = q;
+                        }
                     } else {
 #pragma unroll
-                        for (int e = 0; e < 32; ++e) if (nbase + e < p.N) dst[e] = o[e];
+                        for (int e = 0; e < 32; ++e) if (nbase + e < p.N) dst[e] = p.accumulate ? dst[e] + o[e] : o[e];
                     }
                 }
                 if (p.C16) {

@@ -26,6 +26,7 @@ struct TcGemmParams {
     int M = 0, N = 0, K = 0;            // M rows per group; K multiple of 64
     int groups = 1;
     int relu = 0;
+    int accumulate = 0;                 // C32 += result (input-gradient accumulation); no bias / relu / softmax
 };
 
 // tile rows of the packed weight image for an N-column layer

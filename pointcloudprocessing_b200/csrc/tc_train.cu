@@ -263,3 +263,33 @@ extern "C" int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t r
     cudaFree(da); cudaFree(dz); cudaFree(dw);
     return rc;
 }
+
+// test hook: C (rows x n) (+)= A (rows x k) . W with the device-packed weight image; W is (k x n) row-major, or (n x k)
+// row-major when transpose_w (the input-gradient form dA = dZ . W^T); host in / host out, synchronous
+extern "C" int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate,
+                                  float *h_c)
+{
+    PCP_REQUIRE(h_a && h_w && h_c && rows >= 1 && k >= 64 && n >= 1, PCP_ERR_INVALID, "pcp_selftest_tc_mm: bad arguments");
+    float *da = nullptr, *dw = nullptr, *dc = nullptr;
+    uint8_t *img = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&da, (size_t)rows * k * 4)); PCP_CUDA_OK(cudaMalloc(&dw, (size_t)k * n * 4));
+    PCP_CUDA_OK(cudaMalloc(&dc, (size_t)rows * n * 4)); PCP_CUDA_OK(cudaMalloc(&img, gemm_b_image_bytes(k, n)));
+    PCP_CUDA_OK(cudaMemcpy(da, h_a, (size_t)rows * k * 4, cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemcpy(dw, h_w, (size_t)k * n * 4, cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemcpy(dc, h_c, (size_t)rows * n * 4, cudaMemcpyHostToDevice));
+    int rc = pack_weight_image(dw, k, n, transpose_w ? k : n, transpose_w != 0, img, nullptr);
+    if (rc == PCP_OK) {
+        TcGemmParams p;
+        p.A = da; p.a_f32 = 1; p.lda = k; p.Bimg = img; p.C32 = dc; p.ldc = n; p.M = (int)rows; p.N = n; p.K = k;
+        p.accumulate = accumulate ? 1 : 0;
+        rc = tc_gemm(p, nullptr);
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    if (rc == PCP_OK && e != cudaSuccess) {
+        set_error("pcp_selftest_tc_mm: %s", cudaGetErrorString(e));
+        rc = PCP_ERR_CUDA;
+    }
+    if (rc == PCP_OK) PCP_CUDA_OK(cudaMemcpy(h_c, dc, (size_t)rows * n * 4, cudaMemcpyDeviceToHost));
+    cudaFree(da); cudaFree(dw); cudaFree(dc); cudaFree(img);
+    return rc;
+}

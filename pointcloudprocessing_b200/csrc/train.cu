@@ -14,6 +14,8 @@
 
 #include "gemm_simt.cuh"
 #include "model.cuh"
+#include "tc_gemm.cuh"
+#include "tc_train.cuh"
 
 namespace pcp {
 
@@ -447,6 +449,7 @@ struct TrainState {
     double *metrics = nullptr;                                     // 8 doubles
     bool have_seg = false;
     char *eval_buf = nullptr; size_t eval_bytes = 0;               // pcp_model_evaluate: metrics + logits
+    uint8_t *tc_img = nullptr;                                     // scratch bf16 weight image of the tensor-core GEMMs (4 MB)
 };
 
 static int ensure_train_buffers(pcp_model *m)
@@ -481,9 +484,10 @@ void train_destroy(pcp_model *m)
 {
     if (!m->train_ws) return;
     TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
-    cudaFree(ts->d_mask);
-    cudaFree(ts->arena);
-    cudaFree(ts->eval_buf);
+    PCP_RELEASE(cudaFree(ts->d_mask));
+    PCP_RELEASE(cudaFree(ts->arena));
+    PCP_RELEASE(cudaFree(ts->eval_buf));
+    PCP_RELEASE(cudaFree(ts->tc_img));
     delete ts;
     m->train_ws = nullptr;
 }
@@ -546,10 +550,27 @@ static inline int grid_for(int64_t work, int per_block = 256, int waves = 8)
 }
 
 // ---- GEMM wrappers (row-major fp32 activations; W is (cin x cout) row-major inside the flat parameter buffer) ----
+// PCP_PRECISION_BF16: operands are rounded to bf16 and multiplied on tcgen05 with fp32 accumulation (tc_gemm / tc_wgrad);
+// shapes the tensor-core tiles do not cover (K = 3 inputs, 9 / C / P wide outputs as a contraction) stay on the fp32 path.
+struct TcCtx {
+    bool on = false;
+    uint8_t *img = nullptr;       // scratch weight image (re-packed before every GEMM: the weights change every step)
+    size_t img_bytes = 0;
+};
+static thread_local TcCtx g_tc;
+
 // C (rows x cout) = A (rows x cin) . W  [+ bias]          groups > 1: per-group bias (stride cout), rows per group
 static int mm_nn(const float *A, int64_t rows, int cin, const float *W, int ldw, int cout, float *Cc, const float *bias, cudaStream_t st,
                  int groups = 1, int64_t bias_stride = 0)
 {
+    if (g_tc.on && cin % 64 == 0 && (cout <= 128 || cout % 128 == 0) && gemm_b_image_bytes(cin, cout) <= g_tc.img_bytes) {
+        PCP_TRY(pack_weight_image(W, cin, cout, ldw, false, g_tc.img, st));
+        TcGemmParams p;
+        const int64_t rpg = rows / groups;
+        p.A = A; p.a_f32 = 1; p.lda = cin; p.a_group_stride = rpg * cin; p.Bimg = g_tc.img; p.bias = bias; p.bias_group_stride = bias_stride;
+        p.C32 = Cc; p.ldc = cout; p.c_group_stride = rpg * cout; p.M = (int)rpg; p.N = cout; p.K = cin; p.groups = groups;
+        return tc_gemm(p, st);
+    }
     GemmArgs g;
     g.A = A; g.lda = cin; g.B = W; g.ldb = ldw; g.C = Cc; g.ldc = cout; g.bias = bias; g.N = cout; g.K = cin;
     if (groups > 1) {
@@ -563,6 +584,13 @@ static int mm_nn(const float *A, int64_t rows, int cin, const float *W, int ldw,
 // dA (rows x cin) (+)= dZ (rows x cout) . W^T
 static int mm_nt(const float *dZ, int64_t rows, int cout, const float *W, int ldw, int cin, float *dA, bool accumulate, cudaStream_t st)
 {
+    if (g_tc.on && cout % 64 == 0 && (cin <= 128 || cin % 128 == 0) && gemm_b_image_bytes(cout, cin) <= g_tc.img_bytes) {
+        PCP_TRY(pack_weight_image(W, cout, cin, ldw, true, g_tc.img, st));
+        TcGemmParams p;
+        p.A = dZ; p.a_f32 = 1; p.lda = cout; p.Bimg = g_tc.img; p.C32 = dA; p.ldc = cin; p.M = (int)rows; p.N = cin; p.K = cout;
+        p.accumulate = accumulate ? 1 : 0;
+        return tc_gemm(p, st);
+    }
     GemmArgs g;
     g.A = dZ; g.lda = cout; g.B = W; g.ldb = ldw; g.transB = 1; g.C = dA; g.ldc = cin; g.M = (int)rows; g.N = cin; g.K = cout;
     g.accumulate = accumulate ? 1 : 0;
@@ -571,6 +599,8 @@ static int mm_nt(const float *dZ, int64_t rows, int cout, const float *W, int ld
 // dW (cin x cout) += A^T (cin x rows) . dZ (rows x cout)   — split-K over the rows, atomics into the zeroed gradient buffer
 static int mm_tn(const float *A, int64_t rows, int cin, const float *dZ, int cout, float *dW, int lddw, cudaStream_t st)
 {
+    if (g_tc.on && cin % 8 == 0 && cout % 8 == 0 && ((((uintptr_t)A | (uintptr_t)dZ) & 15u) == 0))
+        return tc_wgrad(A, cin, rows, cin, dZ, cout, cout, dW, lddw, st);
     GemmArgs g;
     g.A = A; g.lda = cin; g.transA = 1; g.B = dZ; g.ldb = cout; g.C = dW; g.ldc = lddw; g.M = cin; g.N = cout; g.K = (int)rows;
     const int64_t blocks = (int64_t)((cin + 127) / 128) * ((cout + 63) / 64);
@@ -713,6 +743,10 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
 {
     TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
     PCP_TRY(ensure_arena(m, ts, b, n));
+    const size_t kImgBytes = (size_t)4 << 20;
+    if (!ts->tc_img) PCP_CUDA_OK(cudaMalloc(&ts->tc_img, kImgBytes));
+    g_tc.on = m->desc.precision == PCP_PRECISION_BF16;
+    g_tc.img = ts->tc_img; g_tc.img_bytes = kImgBytes;
     const int64_t M = (int64_t)b * n;
     const int C = m->desc.num_classes, P = m->desc.num_parts;
     const bool full = !m->desc.vanilla;
@@ -1061,7 +1095,7 @@ extern "C" int pcp_model_evaluate(pcp_model *m, const float *d_x, int b, int64_t
     const int64_t M = (int64_t)b * n;
     const size_t need = (size_t)b * C * 4 + (size_t)M * P * 4 + (size_t)b * 36 + 64 + 1024;
     if (ts->eval_bytes < need) {
-        cudaFree(ts->eval_buf);
+        PCP_RELEASE(cudaFree(ts->eval_buf));
         ts->eval_buf = nullptr; ts->eval_bytes = 0;
         PCP_CUDA_OK(cudaMalloc(&ts->eval_buf, need));
         ts->eval_bytes = need;

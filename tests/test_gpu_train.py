@@ -261,3 +261,69 @@ def test_fit_history_keys_and_loss_decreases(lib):
     assert all(len(v) == 4 for v in h.values())
     assert h["loss"][-1] < h["loss"][0]
     assert h["segmentation_output_sparse_categorical_accuracy"][-1] > 0.7
+
+
+@pytest.mark.parametrize("vanilla,trainable,weights,reg", [
+    (False, ALL, (1.0, 0.5, 0.25), (True, True)),
+    (False, SEG_ONLY, (0.0, 1.0, 0.0), (False, False)),
+    (True, ALL, (1.0, 1.0, 0.0), (False, False)),
+])
+def test_bf16_tensor_core_training_step(lib, vanilla, trainable, weights, reg):
+    """precision="bf16": the layer GEMMs of the training step (forward, input-gradient, weight-gradient) run on tcgen05
+    with bf16-rounded operands and fp32 accumulation; BN statistics, losses and Adam stay fp32.
+
+    What is checked where.  The three GEMM forms are pinned EXACTLY (2e-5 against the float64 product of the rounded
+    operands) by test_gpu_umma.py::test_training_gemm_device_packed_image / test_wgrad_mn_major_tensor_core, and the
+    step's wiring is pinned by the fp32 tests above — the bf16 step is the same code with only the GEMM dispatch changed.
+    An element-wise gradient comparison is not meaningful here: rounding activations to bf16 makes the gradient of a
+    small random-weight batch a chaotic function of round-off (the oracle itself, with bf16-rounded GEMM operands
+    [oracle.pointnet_torch.bf16_gemms], moves its gradients by 30-45 % relative L2 when the input is perturbed by 1e-6).
+    So this test bounds what is stable: the loss within north_star's 2e-2, probabilities within 0.25 absolute, and each
+    kernel gradient's direction (cosine >= 0.6) and norm (within 2x) against the bf16-rounding oracle."""
+    C, P, b, n = 8, 8, 12, 256
+    m, p = build(C, P, vanilla, trainable, weights, reg, precision="bf16")
+    x, y, masks = make_batch(21, b, n, C, P)
+    met = m.train_on_batch(x, y, dropout_masks=masks, apply=False)
+    tp = opt.to_torch(p, requires_grad=True)
+    with opt.bf16_gemms():
+        out, loss, parts = oracle_step(x, y, masks, tp, vanilla, trainable, weights, reg, {})
+    loss = float(loss.detach())
+    assert abs(met["loss"] - loss) <= 2e-2 * max(1.0, abs(loss)), (met["loss"], loss)
+    cls_d, seg_d = m.train_output(0, b * C).reshape(b, C), m.train_output(1, b * n * P).reshape(b, n, P)
+    cls_r, seg_r = out["cls"].detach().numpy(), out["seg"].detach().numpy()
+    assert np.abs(cls_d - cls_r).max() <= 0.25 and np.abs(seg_d - seg_r).max() <= 0.25, (np.abs(cls_d - cls_r).max(), np.abs(seg_d - seg_r).max())
+    assert (seg_d.argmax(-1) == seg_r.argmax(-1)).mean() >= 0.85
+    grads = m.gradients_dict()
+    keep = trainable_names(p, trainable, vanilla)
+    bad = {}
+    for k in keep:
+        if not k.endswith("/kernel") or tp[k].grad is None:
+            continue
+        g_ref = tp[k].grad.numpy().astype(np.float64).ravel()
+        g = grads[k].astype(np.float64).ravel()
+        nr, nd = np.linalg.norm(g_ref), np.linalg.norm(g)
+        if nr < 1e-12:
+            continue
+        cos = float(g @ g_ref / (nr * nd + 1e-300))
+        if cos < 0.6 or not (0.5 <= nd / nr <= 2.0):
+            bad[k] = (cos, nd / nr)
+    assert not bad, bad
+    for k in p:
+        if k not in keep and "moving_" not in k:
+            assert not grads[k].any(), k
+
+
+def test_bf16_fit_learns(lib):
+    from pointcloudprocessing_b200.pointnet import keras_compat as K
+    C, P, b, n = 4, 3, 16, 128
+    m, _ = build(C, P, False, ALL, (1.0, 1.0, 0.0), lr=2e-3, precision="bf16")
+    x, y, _ = make_batch(9, b, n, C, P)
+    y["classification_output"] = (np.arange(b) % C).astype(np.int32)
+    y["segmentation_output"] = (x[..., 0] > np.median(x[..., 0], axis=1, keepdims=True)).astype(np.int32)
+
+    def gen():
+        while True:
+            yield x, y
+    h = m.fit(x=gen(), epochs=4, verbose=0, steps_per_epoch=10).history
+    assert h["loss"][-1] < h["loss"][0]
+    assert h["segmentation_output_sparse_categorical_accuracy"][-1] > 0.7

@@ -59,3 +59,26 @@ def test_wgrad_mn_major_tensor_core(lib, rows, cin, cout):
     ref = _bf16_round(a).astype(np.float64).T @ _bf16_round(dz).astype(np.float64)
     err = np.abs(dw - ref).max() / np.abs(ref).max()
     assert err < 2e-5, err
+
+
+@pytest.mark.parametrize("rows,k,n,transpose,acc", [(768, 64, 64, 0, 0), (768, 64, 128, 0, 0), (768, 128, 1024, 0, 0), (6, 1024, 512, 0, 0),
+                                                    (6, 256, 9, 0, 0), (6, 256, 4096, 0, 0), (768, 128, 8, 0, 0), (300, 512, 256, 0, 0),
+                                                    (768, 64, 3, 1, 0), (768, 1024, 128, 1, 0), (768, 128, 64, 1, 1), (6, 512, 1024, 1, 0),
+                                                    (1000, 256, 512, 1, 1), (100, 4096, 256, 1, 0)])
+def test_training_gemm_device_packed_image(lib, rows, k, n, transpose, acc):
+    """Forward (A . W) and input-gradient (dZ . W^T, optionally accumulating) GEMMs of the bf16 training step: weight image
+    packed on the device every step (tc_train.cu pack_weight_image) + tc_gemm, against the float64 product of the
+    bf16-rounded operands."""
+    import ctypes as C
+    rng = np.random.default_rng(rows * 7 + k + n)
+    a = (rng.standard_normal((rows, k)) + 3.0).astype(np.float32)
+    w = rng.standard_normal((n, k) if transpose else (k, n)).astype(np.float32)
+    c0 = rng.standard_normal((rows, n)).astype(np.float32)
+    c = c0.copy()
+    fp = lambda x: x.ctypes.data_as(C.POINTER(C.c_float))
+    st = lib.pcp_selftest_tc_mm(fp(a), fp(w), rows, k, n, transpose, acc, fp(c))
+    assert st == 0, lib.pcp_last_error()
+    wr = _bf16_round(w).astype(np.float64)
+    ref = _bf16_round(a).astype(np.float64) @ (wr.T if transpose else wr) + (c0 if acc else 0.0)
+    err = np.abs(c - ref).max() / np.abs(ref).max()
+    assert err < 2e-5, err
