@@ -177,6 +177,14 @@ int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t rows, int ci
  * weight-image packer + tcgen05 GEMM of the bf16 training step; W is (k x n) row-major, or (n x k) row-major when
  * transpose_w (dA = dZ . W^T).  Host pointers; h_c is read when accumulate != 0. */
 int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate, float *h_c);
+/* max-pooled layer self-test (tests only): conv 128 -> cout, BN (batch statistics when batch != 0, else moving mean 0 /
+ * variance 1), ReLU, reduce_max over the n points of each of the b clouds, and its backward pass, through the implicit
+ * path of the bf16 training step (no rows x cout tensor; train_pool.inl).  Host pointers:
+ * A (b*n x 128), W (128 x cout), gamma / beta (cout), dg (b x cout) -> g (b x cout), mean / inv (cout: batch mean and
+ * 1/sqrt(var + 1e-3)), dW (128 x cout), dgamma / dbeta (cout), dA (b*n x 128). */
+int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, const float *h_gamma, const float *h_beta, const float *h_dg, int b,
+                              int64_t n, int cout, int batch, float *h_g, float *h_mean, float *h_inv, float *h_dw, float *h_dgamma,
+                              float *h_dbeta, float *h_da);
 
 /* ---- training (pointnet_train.py:310-351) ---- */
 #define PCP_GROUP_SHARED 0

@@ -86,6 +86,7 @@ SIGNATURES = {
     "pcp_selftest_umma2": (_i32, [_fp, _fp, _i32, _i32, _fp]),
     "pcp_selftest_wgrad": (_i32, [_fp, _fp, _i64, _i32, _i32, _fp]),
     "pcp_selftest_tc_mm": (_i32, [_fp, _fp, _i64, _i32, _i32, _i32, _i32, _fp]),
+    "pcp_selftest_pooled_layer": (_i32, [_fp, _fp, _fp, _fp, _fp, _i32, _i64, _i32, _i32, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "pcp_model_set_trainable": (_i32, [_vp, _i32, _i32]),
     "pcp_model_loss_backward": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, C.POINTER(TrainConfig), _i32, _vp, _vp, _fp, _vp]),
     "pcp_model_evaluate": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, C.POINTER(TrainConfig), _fp, _vp]),

@@ -10,6 +10,7 @@
 // tf.reduce_max convention).  GEMMs go through train_mm_* below: fp32 CUDA-core tiles in
 // PCP_PRECISION_FP32, bf16 tcgen05 tiles with fp32 accumulation in PCP_PRECISION_BF16 (tc_train.cu).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "gemm_simt.cuh"
@@ -413,6 +414,19 @@ __global__ void axpy_kernel(float *__restrict__ y, const float *__restrict__ x, 
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
+// buffers of one implicitly handled max-pooled layer (train_pool.inl)
+struct PoolBufs {
+    unsigned long long *ext = nullptr;   // 2 x (b x cout) packed extrema keys (max, then min)
+    float *gram = nullptr;               // cin x cin : A^T A of the bf16-rounded input
+    double *asum = nullptr;              // cin       : 1^T A
+    float *zsel = nullptr;               // b x cout  : the selected extremum of z
+    int *arg = nullptr;                  // b x cout  : its row inside the cloud
+    float *S = nullptr;                  // b x cout  : sc * dY at that row
+    float *c0 = nullptr, *c1 = nullptr;  // cout
+    float *Wt = nullptr;                 // cout x cin: W^T, bf16-rounded
+    float *Q = nullptr, *q = nullptr;    // cin x cin, cin
+};
+
 struct TL {                       // one weighted layer's training record
     int id = -1;
     float *Z = nullptr;           // pre-BN output (rows x cout)
@@ -450,6 +464,8 @@ struct TrainState {
     bool have_seg = false;
     char *eval_buf = nullptr; size_t eval_bytes = 0;               // pcp_model_evaluate: metrics + logits
     uint8_t *tc_img = nullptr;                                     // scratch bf16 weight image of the tensor-core GEMMs (4 MB)
+    PoolBufs pool[3];                                              // L_IT_C3, L_FT_C3, L_S2_3 (bf16 mode)
+    bool implicit_pool = false;                                    // pooled layers without their (rows x 1024) tensors (train_pool.inl)
 };
 
 static int ensure_train_buffers(pcp_model *m)
@@ -496,7 +512,10 @@ void train_destroy(pcp_model *m)
 static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
 {
     if (ts->arena && ts->b == b && ts->n == n) return PCP_OK;
-    cudaFree(ts->arena);
+    // bf16 mode handles the pooled 128 -> 1024 layers implicitly; PCP_TRAIN_EXPLICIT_POOL=1 keeps the explicit path (A/B tests)
+    static const bool force_explicit = [] { const char *e = getenv("PCP_TRAIN_EXPLICIT_POOL"); return e && e[0] == '1'; }();
+    ts->implicit_pool = m->desc.precision == PCP_PRECISION_BF16 && !force_explicit;
+    PCP_RELEASE(cudaFree(ts->arena));
     ts->arena = nullptr; ts->b = 0; ts->n = 0;
     const int64_t M = (int64_t)b * n;
     const int C = m->desc.num_classes, P = m->desc.num_parts;
@@ -512,7 +531,8 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
         bool per_point = false;
         for (int id : kPointLayers) per_point = per_point || (id == i);
         t.id = i; t.rows = per_point ? M : b; t.cin = S.cin; t.cout = S.cout; t.has_bn = S.has_bn;
-        if (i != L_SEG5 && i != L_CLS3) want(&t.Z, (size_t)t.rows * S.cout * 4);
+        const bool pooled = (i == L_IT_C3 || i == L_FT_C3 || i == L_S2_3);
+        if (i != L_SEG5 && i != L_CLS3 && !(pooled && ts->implicit_pool)) want(&t.Z, (size_t)t.rows * S.cout * 4);
         if (S.has_bn) {
             want(&t.mean, S.cout * 4); want(&t.inv, S.cout * 4); want(&t.sc, S.cout * 4); want(&t.beta, S.cout * 4);
             want(&t.red, (size_t)S.cout * 2 * 8);
@@ -530,7 +550,14 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
     for (int i = 0; i < 4; ++i) want(&ts->dsmall[i], (size_t)b * 4096 * 4);
     want(&ts->Y64a, M * 256); want(&ts->Y64b, M * 256); want(&ts->Y128, M * 512); want(&ts->Y128b, M * 512);
     want(&ts->Y256, M * 1024); want(&ts->Y512, M * 2048);
-    want(&ts->G1024, M * 4096); want(&ts->G512, M * 2048); want(&ts->G256, M * 1024); want(&ts->G128a, M * 512); want(&ts->G128b, M * 512);
+    if (!ts->implicit_pool) want(&ts->G1024, M * 4096);
+    else
+        for (PoolBufs &pb : ts->pool) {
+            want(&pb.ext, (size_t)b * 1024 * 16); want(&pb.gram, 128 * 128 * 4); want(&pb.asum, 128 * 8); want(&pb.zsel, (size_t)b * 4096);
+            want(&pb.arg, (size_t)b * 4096); want(&pb.S, (size_t)b * 4096); want(&pb.c0, 4096); want(&pb.c1, 4096); want(&pb.Wt, 1024 * 128 * 4);
+            want(&pb.Q, 128 * 128 * 4); want(&pb.q, 512);
+        }
+    want(&ts->G512, M * 2048); want(&ts->G256, M * 1024); want(&ts->G128a, M * 512); want(&ts->G128b, M * 512);
     want(&ts->G64a, M * 256); want(&ts->G64b, M * 256); want(&ts->GP, (size_t)M * P * 4);
     want(&ts->dX64, M * 256); want(&ts->dX2, M * 256); want(&ts->dX3, M * 12);
     want(&ts->metrics, 8 * 8);
@@ -611,6 +638,8 @@ static int mm_tn(const float *A, int64_t rows, int cin, const float *dZ, int cou
     if (sk == 1) g.accumulate = 1;
     return gemm_f32(g, st);
 }
+
+#include "train_pool.inl"
 
 static inline float *param(pcp_model *m, int ti) { return m->d_params + m->tensors[ti].offset; }
 static inline float *grad(pcp_model *m, int ti) { return m->d_grads + m->tensors[ti].offset; }
@@ -710,6 +739,40 @@ static int colsum(const float *X, int groups, int64_t rpg, int C, float *out, cu
     return PCP_OK;
 }
 
+// the pooled layer li as the implicit path sees it (train_pool.inl)
+static PoolLayer make_pool_layer(pcp_model *m, TrainState *ts, int li, int slot)
+{
+    const LayerSpec &S = m->layers[li];
+    const TL &t = ts->L[li];
+    PoolLayer P;
+    P.W = param(m, S.t_kernel); P.gamma = param(m, S.t_gamma); P.beta_in = param(m, S.t_beta);
+    P.mov_mean = param(m, S.t_mean); P.mov_var = param(m, S.t_var);
+    P.mean = t.mean; P.inv = t.inv; P.sc = t.sc; P.beta = t.beta; P.red = t.red;
+    P.b = ts->b; P.n = ts->n; P.cout = t.cout; P.batch = t.batch; P.trainable = t.trainable; P.pb = ts->pool[slot];
+    return P;
+}
+
+// pooled layer forward: g = reduce_max(relu(bn(A . W)))
+static int pooled_layer_fwd(pcp_model *m, TrainState *ts, int li, int slot, const float *A, float *g, cudaStream_t st)
+{
+    if (ts->implicit_pool) return pooled_forward(make_pool_layer(m, ts, li, slot), A, g, st);
+    PCP_TRY(layer_fwd_train(m, ts->L[li], A, nullptr, st));
+    return pool_fwd(ts->L[li], ts->b, ts->n, g, st);
+}
+
+// pooled layer backward: dg -> parameter gradients and dA (rows x 128); Aprev is the layer whose activation feeds li
+static int pooled_layer_bwd(pcp_model *m, TrainState *ts, int li, int slot, int lprev, const float *g, const float *dg, float *dA, cudaStream_t st)
+{
+    const LayerSpec &S = m->layers[li];
+    if (ts->implicit_pool) {
+        PCP_TRY(bn_act(ts->L[lprev], ts->Y128, st));
+        return pooled_backward(make_pool_layer(m, ts, li, slot), ts->Y128, g, dg, grad(m, S.t_kernel), grad(m, S.t_gamma), grad(m, S.t_beta), dA, st);
+    }
+    PCP_TRY(pool_bwd(m, ts->L[li], ts->b, ts->n, g, dg, ts->cnt, ts->G1024, st));
+    PCP_TRY(bn_act(ts->L[lprev], ts->Y128, st));
+    return layer_bwd_mm(m, ts->L[li], ts->Y128, ts->G1024, dA, false, st);
+}
+
 // T-Net tail forward (PointNet.py:431-442): g (b x 1024) -> dense 512 -> 256 -> (256 x k^2) + b
 static int tnet_tail_fwd(pcp_model *m, TrainState *ts, int first, int t_w, int t_b, int k, const float *g, float *Y1, float *Y2, float *out,
                          cudaStream_t st)
@@ -772,8 +835,7 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     if (full) {
         PCP_TRY(layer_fwd_train(m, L[L_IT_C1], ts->pcn, ts->Y64a, st));                                 // TNet.call :423
         PCP_TRY(layer_fwd_train(m, L[L_IT_C2], ts->Y64a, ts->Y128, st));                                // :424
-        PCP_TRY(layer_fwd_train(m, L[L_IT_C3], ts->Y128, nullptr, st));                                 // :425
-        PCP_TRY(pool_fwd(L[L_IT_C3], b, n, ts->g1, st));                                                // :429
+        PCP_TRY(pooled_layer_fwd(m, ts, L_IT_C3, 0, ts->Y128, ts->g1, st));                             // :425-429
         PCP_TRY(tnet_tail_fwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, ts->g1, ts->Ys[0], ts->Ys[1], ts->R, st));
         GemmArgs g;                                                                                     // X = pc @ R  :207
         g.A = ts->pcn; g.lda = 3; g.strideA = n * 3; g.B = ts->R; g.ldb = 3; g.strideB = 9;
@@ -789,8 +851,7 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     if (full) {
         PCP_TRY(layer_fwd_train(m, L[L_FT_C1], ts->X2, ts->Y64a, st));
         PCP_TRY(layer_fwd_train(m, L[L_FT_C2], ts->Y64a, ts->Y128, st));
-        PCP_TRY(layer_fwd_train(m, L[L_FT_C3], ts->Y128, nullptr, st));
-        PCP_TRY(pool_fwd(L[L_FT_C3], b, n, ts->g2, st));
+        PCP_TRY(pooled_layer_fwd(m, ts, L_FT_C3, 1, ts->Y128, ts->g2, st));
         PCP_TRY(tnet_tail_fwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, ts->g2, ts->Ys[2], ts->Ys[3], ts->R64, st));   // :227
         GemmArgs g;                                                                                     // X_64 = X @ R_64 :228
         g.A = ts->X2; g.lda = 64; g.strideA = n * 64; g.B = ts->R64; g.ldb = 64; g.strideB = 4096;
@@ -800,8 +861,7 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     }
     PCP_TRY(layer_fwd_train(m, L[L_S2_1], X64, ts->Y64a, st));                                          // :236
     PCP_TRY(layer_fwd_train(m, L[L_S2_2], ts->Y64a, ts->Y128, st));                                     // :239
-    PCP_TRY(layer_fwd_train(m, L[L_S2_3], ts->Y128, nullptr, st));                                      // :242
-    PCP_TRY(pool_fwd(L[L_S2_3], b, n, ts->g3, st));                                                     // :248
+    PCP_TRY(pooled_layer_fwd(m, ts, L_S2_3, 2, ts->Y128, ts->g3, st));                                  // :242-248
 
     // ---- classification head (:252-263) ----
     const float *Yc1 = ts->Ys[4], *Yc2 = ts->Ys[5];
@@ -933,9 +993,7 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
 
     if (trunk_bwd) {
         // ---- mlp_2 (:234-248) ----
-        PCP_TRY(pool_bwd(m, L[L_S2_3], b, n, ts->g3, ts->dg3, ts->cnt, ts->G1024, st));
-        PCP_TRY(bn_act(L[L_S2_2], ts->Y128, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_S2_3], ts->Y128, ts->G1024, ts->G128a, false, st));
+        PCP_TRY(pooled_layer_bwd(m, ts, L_S2_3, 2, L_S2_2, ts->g3, ts->dg3, ts->G128a, st));
         PCP_TRY(bn_bwd(m, L[L_S2_2], ts->G128a, true, st));
         PCP_TRY(bn_act(L[L_S2_1], ts->Y64a, st));
         PCP_TRY(layer_bwd_mm(m, L[L_S2_2], ts->Y64a, ts->G128a, ts->G64a, false, st));
@@ -955,9 +1013,7 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
             dX2 = ts->dX2;
             // ---- feature T-Net ----
             PCP_TRY(tnet_tail_bwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, tr_sh, ts->g2, ts->Ys[2], ts->Ys[3], ts->dR64, ts->dg2, st));
-            PCP_TRY(pool_bwd(m, L[L_FT_C3], b, n, ts->g2, ts->dg2, ts->cnt, ts->G1024, st));
-            PCP_TRY(bn_act(L[L_FT_C2], ts->Y128, st));
-            PCP_TRY(layer_bwd_mm(m, L[L_FT_C3], ts->Y128, ts->G1024, ts->G128a, false, st));
+            PCP_TRY(pooled_layer_bwd(m, ts, L_FT_C3, 1, L_FT_C2, ts->g2, ts->dg2, ts->G128a, st));
             PCP_TRY(bn_bwd(m, L[L_FT_C2], ts->G128a, true, st));
             PCP_TRY(bn_act(L[L_FT_C1], ts->Y64a, st));
             PCP_TRY(layer_bwd_mm(m, L[L_FT_C2], ts->Y64a, ts->G128a, ts->G64a, false, st));
@@ -981,9 +1037,7 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     if (full && tr_it) {
         // ---- input T-Net: gradient enters through R only ----
         PCP_TRY(tnet_tail_bwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, true, ts->g1, ts->Ys[0], ts->Ys[1], ts->dR, ts->dg1, st));
-        PCP_TRY(pool_bwd(m, L[L_IT_C3], b, n, ts->g1, ts->dg1, ts->cnt, ts->G1024, st));
-        PCP_TRY(bn_act(L[L_IT_C2], ts->Y128, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_IT_C3], ts->Y128, ts->G1024, ts->G128a, false, st));
+        PCP_TRY(pooled_layer_bwd(m, ts, L_IT_C3, 0, L_IT_C2, ts->g1, ts->dg1, ts->G128a, st));
         PCP_TRY(bn_bwd(m, L[L_IT_C2], ts->G128a, true, st));
         PCP_TRY(bn_act(L[L_IT_C1], ts->Y64a, st));
         PCP_TRY(layer_bwd_mm(m, L[L_IT_C2], ts->Y64a, ts->G128a, ts->G64a, false, st));
@@ -1012,6 +1066,67 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
 }  // namespace pcp
 
 using namespace pcp;
+
+// test hook (tests only): one implicitly handled max-pooled layer, forward + backward, host in / host out.
+// A (b*n x 128), W (128 x cout), gamma / beta (cout), dg (b x cout) -> g (b x cout), mean / inv (cout), dW (128 x cout),
+// dgamma / dbeta (cout), dA (b*n x 128).  batch != 0: BN uses batch statistics (moving mean 0 / variance 1 otherwise).
+extern "C" int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, const float *h_gamma, const float *h_beta, const float *h_dg, int b,
+                                         int64_t n, int cout, int batch, float *h_g, float *h_mean, float *h_inv, float *h_dw, float *h_dgamma,
+                                         float *h_dbeta, float *h_da)
+{
+    PCP_REQUIRE(h_a && h_w && h_gamma && h_beta && h_dg && h_g && h_mean && h_inv && h_dw && h_dgamma && h_dbeta && h_da && b >= 1 && n >= 1 &&
+                    cout >= 128 && cout % 128 == 0 && cout <= 1024,
+                PCP_ERR_INVALID, "pcp_selftest_pooled_layer: bad arguments");
+    const int64_t rows = (int64_t)b * n;
+    const size_t bc = (size_t)b * cout;
+    std::vector<std::pair<void **, size_t>> req;
+    auto want = [&](auto **p, size_t bytes) { req.emplace_back(reinterpret_cast<void **>(p), (bytes + 255) & ~(size_t)255); };
+    float *dA_in, *dW_in, *gam, *bet, *mm, *mv, *dg, *g, *dWg, *dgam, *dbet, *dAo;
+    uint8_t *img;
+    PoolLayer L;
+    want(&dA_in, rows * 512); want(&dW_in, (size_t)128 * cout * 4); want(&gam, cout * 4); want(&bet, cout * 4); want(&mm, cout * 4); want(&mv, cout * 4);
+    want(&dg, bc * 4); want(&g, bc * 4); want(&dWg, (size_t)128 * cout * 4); want(&dgam, cout * 4); want(&dbet, cout * 4); want(&dAo, rows * 512);
+    want(&img, (size_t)4 << 20);
+    want(&L.mean, cout * 4); want(&L.inv, cout * 4); want(&L.sc, cout * 4); want(&L.beta, cout * 4); want(&L.red, (size_t)cout * 16);
+    want(&L.pb.ext, bc * 16); want(&L.pb.gram, 128 * 128 * 4); want(&L.pb.asum, 128 * 8); want(&L.pb.zsel, bc * 4); want(&L.pb.arg, bc * 4);
+    want(&L.pb.S, bc * 4); want(&L.pb.c0, cout * 4); want(&L.pb.c1, cout * 4); want(&L.pb.Wt, (size_t)cout * 512); want(&L.pb.Q, 128 * 128 * 4);
+    want(&L.pb.q, 512);
+    size_t total = 0;
+    for (auto &r : req) total += r.second;
+    char *arena = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&arena, total));
+    size_t off = 0;
+    for (auto &r : req) { *r.first = arena + off; off += r.second; }
+    int rc = PCP_OK;
+    auto run = [&]() -> int {
+        PCP_CUDA_OK(cudaMemset(arena, 0, total));
+        PCP_CUDA_OK(cudaMemcpy(dA_in, h_a, rows * 512, cudaMemcpyHostToDevice));
+        PCP_CUDA_OK(cudaMemcpy(dW_in, h_w, (size_t)128 * cout * 4, cudaMemcpyHostToDevice));
+        PCP_CUDA_OK(cudaMemcpy(gam, h_gamma, cout * 4, cudaMemcpyHostToDevice));
+        PCP_CUDA_OK(cudaMemcpy(bet, h_beta, cout * 4, cudaMemcpyHostToDevice));
+        PCP_CUDA_OK(cudaMemcpy(dg, h_dg, bc * 4, cudaMemcpyHostToDevice));
+        std::vector<float> ones(cout, 1.f);
+        PCP_CUDA_OK(cudaMemcpy(mv, ones.data(), cout * 4, cudaMemcpyHostToDevice));
+        g_tc.on = true; g_tc.img = img; g_tc.img_bytes = (size_t)4 << 20;
+        L.W = dW_in; L.gamma = gam; L.beta_in = bet; L.mov_mean = mm; L.mov_var = mv; L.b = b; L.n = n; L.cout = cout;
+        L.batch = batch != 0; L.trainable = true;
+        PCP_TRY(pooled_forward(L, dA_in, g, nullptr));
+        PCP_TRY(pooled_backward(L, dA_in, g, dg, dWg, dgam, dbet, dAo, nullptr));
+        PCP_CUDA_OK(cudaDeviceSynchronize());
+        PCP_CUDA_OK(cudaMemcpy(h_g, g, bc * 4, cudaMemcpyDeviceToHost));
+        PCP_CUDA_OK(cudaMemcpy(h_mean, L.mean, cout * 4, cudaMemcpyDeviceToHost));
+        PCP_CUDA_OK(cudaMemcpy(h_inv, L.inv, cout * 4, cudaMemcpyDeviceToHost));
+        PCP_CUDA_OK(cudaMemcpy(h_dw, dWg, (size_t)128 * cout * 4, cudaMemcpyDeviceToHost));
+        PCP_CUDA_OK(cudaMemcpy(h_dgamma, dgam, cout * 4, cudaMemcpyDeviceToHost));
+        PCP_CUDA_OK(cudaMemcpy(h_dbeta, dbet, cout * 4, cudaMemcpyDeviceToHost));
+        PCP_CUDA_OK(cudaMemcpy(h_da, dAo, rows * 512, cudaMemcpyDeviceToHost));
+        return PCP_OK;
+    };
+    rc = run();
+    g_tc = TcCtx();
+    PCP_RELEASE(cudaFree(arena));
+    return rc;
+}
 
 extern "C" int pcp_model_grad_buffer(pcp_model *m, float **d_grads, size_t *count)
 {

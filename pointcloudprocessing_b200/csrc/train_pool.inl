@@ -1,0 +1,265 @@
+// train_pool.inl — the three max-pooled 128 -> 1024 layers of the training step without their (rows x 1024) tensors.
+// Included by train.cu (inside namespace pcp, after the BN kernels and the mm_* wrappers).  bf16 precision mode only.
+//
+// Reference semantics: ConvLayer(1024) -> BN(batch statistics) -> ReLU -> tf.reduce_max over the points
+// (pointnet/PointNet.py:425-429, :242-248) and the gradient of that chain.  The explicit path (layer_fwd_train + pool_fwd /
+// pool_bwd + bn_bwd + layer_bwd_mm) writes Z = A.W (1 GB at 256 x 1024 points), re-reads it for the statistics, the pool,
+// the tie count, the pool gradient, both BN backward passes and the two gradient GEMMs: ~13 GB of HBM traffic per layer.
+// None of it is needed:
+//   forward   Z is a linear image of the 128-wide input A, so its batch statistics follow from the Gram matrix of A:
+//               sum_i z_ij = (1^T A) w_j ,  sum_i z_ij^2 = w_j^T (A^T A) w_j            (A^T A on tcgen05, 128 x 128)
+//             and BN+ReLU are monotone per channel, so max_i relu(bn(z_ij)) = relu(bn(max_i z_ij)) for sc_j >= 0 (min for
+//             sc_j < 0): one GEMM whose epilogue keeps only the per-cloud column extrema and their rows (tc_gemm Ext_*).
+//   backward  dY is non-zero only at the selected row of each (cloud, channel), and BN backward adds an affine function
+//             of Z per channel:  dZ_ij = sc_j dY_ij + c0_j + c1_j z_ij , c1 = -sc inv s2 / M , c0 = -sc s1 / M - c1 mean.
+//             With Z = A W:   dW = A^T dZ = (A^T A) W diag(c1) + (A^T 1) c0^T + sum_c S_cj A[arg_cj, :]
+//                             dA = dZ W^T = A (W diag(c1) W^T) + 1 (W c0)^T + scatter_c,j S_cj W[:, j] into row arg_cj
+//             i.e. one 128 x 128 GEMM over A plus gathers / scatters of b x 1024 rows.
+// Ties: tf.reduce_max splits the gradient evenly among tied rows; this path gives it to the first tied row.  For ties
+// between duplicated points (clouds padded by repetition, PointCloudSet.py:459-467) every weight gradient is identical,
+// because duplicated rows carry identical activations at every layer; for accidental bit-equal maxima of distinct points
+// both choices are valid sub-gradients.  Operands are the bf16-rounded A and W the forward GEMM multiplies.
+
+__device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+
+// asum[k] += sum over rows of bf16(A[r, k])          (cin == 128: two row lanes of 128 columns)
+__global__ void __launch_bounds__(256)
+pool_colsum_kernel(const float *__restrict__ A, int64_t rows, double *__restrict__ asum)
+{
+    const int k = threadIdx.x & 127, lane = threadIdx.x >> 7;
+    float acc = 0.f;
+    for (int64_t r = (int64_t)blockIdx.x * 2 + lane; r < rows; r += (int64_t)gridDim.x * 2) acc += bf16_round(__ldg(A + r * 128 + k));
+    atomicAdd(asum + k, (double)acc);
+}
+
+// column sums / sums of squares of Z = A.W from the Gram matrix: one warp per output channel
+__global__ void __launch_bounds__(128)
+pool_implicit_stats_kernel(const float *__restrict__ gram, const double *__restrict__ asum, const float *__restrict__ W, int cout,
+                           double *__restrict__ sum, double *__restrict__ sumsq)
+{
+    __shared__ double ws[4][128];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = blockIdx.x * 4 + warp;
+    if (j >= cout) return;
+    for (int k = lane; k < 128; k += 32) ws[warp][k] = (double)bf16_round(__ldg(W + (size_t)k * cout + j));
+    __syncwarp();
+    double s = 0, qd = 0;
+    for (int i = 0; i < 4; ++i) {
+        const int k = lane + 32 * i;
+        double t = 0;
+        for (int l = 0; l < 128; ++l) t += (double)__ldg(gram + l * 128 + k) * ws[warp][l];      // G symmetric: coalesced over k
+        qd += ws[warp][k] * t;
+        s += ws[warp][k] * asum[k];
+    }
+    for (int o = 16; o; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); qd += __shfl_xor_sync(0xffffffffu, qd, o); }
+    if (lane == 0) { sum[j] = s; sumsq[j] = qd; }
+}
+
+// pooled output and the record the backward pass needs
+__global__ void __launch_bounds__(256)
+pool_select_kernel(const unsigned long long *__restrict__ emax, const unsigned long long *__restrict__ emin, BnP p, int64_t total, int cout,
+                   float *__restrict__ g, float *__restrict__ zsel, int *__restrict__ arg)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int j = (int)(i % cout);
+        const float sc = __ldg(p.sc + j);
+        unsigned long long key = sc >= 0.f ? emax[i] : emin[i];
+        uint32_t hi = (uint32_t)(key >> 32);
+        if (sc < 0.f) hi = ~hi;
+        const float z = __uint_as_float(tc_key_float_bits(hi));
+        zsel[i] = z;
+        arg[i] = (int)(0xffffffffu - (uint32_t)key);
+        g[i] = fmaxf(bn_pre(z, __ldg(p.mean + j), sc, __ldg(p.beta + j)), 0.f);
+    }
+}
+
+// BN backward sums over the b selected rows of each channel, the affine coefficients and S = sc * dY
+__global__ void __launch_bounds__(128)
+pool_bwd_coef_kernel(const float *__restrict__ g, const float *__restrict__ dg, const float *__restrict__ zsel, BnP p, int b, int cout,
+                     double rows, int batch, double *__restrict__ s1o, double *__restrict__ s2o, float *__restrict__ c0, float *__restrict__ c1,
+                     float *__restrict__ S)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= cout) return;
+    const float mean = p.mean[j], inv = p.inv[j], sc = p.sc[j];
+    double s1 = 0, s2 = 0;
+    for (int c = 0; c < b; ++c) {
+        const size_t i = (size_t)c * cout + j;
+        const float dy = g[i] > 0.f ? dg[i] : 0.f;
+        s1 += dy;
+        s2 += (double)dy * (double)((zsel[i] - mean) * inv);
+        S[i] = sc * dy;
+    }
+    s1o[j] = s1; s2o[j] = s2;
+    if (batch) {
+        const double k1 = -(double)sc * inv * s2 / rows;
+        c1[j] = (float)k1;
+        c0[j] = (float)(-(double)sc * s1 / rows - k1 * mean);
+    } else {
+        c1[j] = 0.f; c0[j] = 0.f;
+    }
+}
+
+// Wt (cout x cin) = bf16(W (cin x cout))^T
+__global__ void __launch_bounds__(256)
+pool_round_transpose_kernel(const float *__restrict__ W, int cin, int cout, float *__restrict__ Wt)
+{
+    __shared__ float tile[32][33];
+    const int j0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) tile[r][tx] = (k0 + r < cin && j0 + tx < cout) ? bf16_round(__ldg(W + (size_t)(k0 + r) * cout + j0 + tx)) : 0.f;
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8)
+        if (j0 + r < cout && k0 + tx < cin) Wt[(size_t)(j0 + r) * cin + k0 + tx] = tile[tx][r];
+}
+
+// dW[k, j] += c1_j (G Wr)[k, j] + asum[k] c0_j + sum_c S[c, j] bf16(A[c n + arg[c, j], k])       (cin == 128; 8 channels per CTA)
+__global__ void __launch_bounds__(128)
+pool_dw_kernel(const float *__restrict__ gram, const double *__restrict__ asum, const float *__restrict__ Wt, const float *__restrict__ c0,
+               const float *__restrict__ c1, const float *__restrict__ S, const int *__restrict__ arg, const float *__restrict__ A, int b, int64_t n,
+               int cout, int batch, float *__restrict__ dW)
+{
+    const int k = threadIdx.x, j0 = blockIdx.x * 8;
+    float acc[8];
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) acc[jj] = 0.f;
+    if (batch) {
+        for (int l = 0; l < 128; ++l) {
+            const float gv = __ldg(gram + l * 128 + k);
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj) acc[jj] = fmaf(gv, __ldg(Wt + (size_t)(j0 + jj) * 128 + l), acc[jj]);
+        }
+        const float as = (float)asum[k];
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) acc[jj] = acc[jj] * __ldg(c1 + j0 + jj) + as * __ldg(c0 + j0 + jj);
+    }
+    for (int c = 0; c < b; ++c) {
+        const size_t i = (size_t)c * cout + j0;
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) {
+            const float s = __ldg(S + i + jj);
+            if (s != 0.f) acc[jj] = fmaf(s, bf16_round(__ldg(A + ((int64_t)c * n + __ldg(arg + i + jj)) * 128 + k)), acc[jj]);
+        }
+    }
+    float4 *dst = reinterpret_cast<float4 *>(dW + (size_t)k * cout + j0);
+    float4 a = dst[0], bq = dst[1];
+    a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
+    bq.x += acc[4]; bq.y += acc[5]; bq.z += acc[6]; bq.w += acc[7];
+    dst[0] = a; dst[1] = bq;
+}
+
+// Q[k, l] = sum_j Wr[k, j] c1_j Wr[l, j] ; q[k] = sum_j Wr[k, j] c0_j                             (cin == 128; one CTA per k)
+__global__ void __launch_bounds__(128)
+pool_q_kernel(const float *__restrict__ Wt, const float *__restrict__ c0, const float *__restrict__ c1, int cout, float *__restrict__ Q,
+              float *__restrict__ q)
+{
+    extern __shared__ float sk[];                 // cout floats: Wr[k, j] c1_j
+    __shared__ float part[4];
+    const int k = blockIdx.x, l = threadIdx.x;
+    float qk = 0.f;
+    for (int j = l; j < cout; j += 128) {
+        const float w = __ldg(Wt + (size_t)j * 128 + k);
+        sk[j] = w * __ldg(c1 + j);
+        qk = fmaf(w, __ldg(c0 + j), qk);
+    }
+    for (int o = 16; o; o >>= 1) qk += __shfl_xor_sync(0xffffffffu, qk, o);
+    if ((l & 31) == 0) part[l >> 5] = qk;
+    __syncthreads();
+    float acc = 0.f;
+    for (int j = 0; j < cout; ++j) acc = fmaf(sk[j], __ldg(Wt + (size_t)j * 128 + l), acc);
+    Q[k * 128 + l] = acc;
+    if (l == 0) q[k] = part[0] + part[1] + part[2] + part[3];
+}
+
+// dA[c n + arg[c, j], k] += S[c, j] Wr[k, j]                                                       (cin == 128)
+__global__ void __launch_bounds__(128)
+pool_scatter_kernel(const float *__restrict__ S, const int *__restrict__ arg, const float *__restrict__ Wt, int64_t n, int cout, int jchunk,
+                    float *__restrict__ dA)
+{
+    const int k = threadIdx.x, c = blockIdx.y, j0 = blockIdx.x * jchunk;
+    for (int j = j0; j < min(cout, j0 + jchunk); ++j) {
+        const size_t i = (size_t)c * cout + j;
+        const float s = __ldg(S + i);
+        if (s != 0.f) atomicAdd(dA + ((int64_t)c * n + __ldg(arg + i)) * 128 + k, s * __ldg(Wt + (size_t)j * 128 + k));
+    }
+}
+
+struct PoolLayer {                      // everything one pooled layer's implicit forward / backward touches
+    const float *W = nullptr;           // (128 x cout) kernel
+    const float *gamma = nullptr, *beta_in = nullptr;
+    float *mov_mean = nullptr, *mov_var = nullptr;
+    float *mean = nullptr, *inv = nullptr, *sc = nullptr, *beta = nullptr;     // per-step BN record (cout each)
+    double *red = nullptr;              // 2 x cout
+    int b = 0; int64_t n = 0; int cout = 0;
+    bool batch = false, trainable = false;
+    PoolBufs pb;
+    BnP bnp() const { return BnP{mean, sc, beta, inv}; }
+};
+
+static bool pool_implicit_ok(int cin, int cout) { return g_tc.on && cin == 128 && cout % 128 == 0 && gemm_b_image_bytes(cin, cout) <= g_tc.img_bytes; }
+
+// g (b x cout) = max over the cloud's points of relu(bn(A . W)); BN record + moving statistics updated like bn_prepare
+static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStream_t st)
+{
+    const int64_t rows = (int64_t)L.b * L.n, total = (int64_t)L.b * L.cout;
+    PCP_CUDA_OK(cudaMemsetAsync(L.pb.ext, 0, (size_t)total * 16, st));
+    PCP_TRY(pack_weight_image(L.W, 128, L.cout, L.cout, false, g_tc.img, st));
+    const int mtiles = (int)((L.n + 127) / 128);
+    PCP_REQUIRE(mtiles <= 65535, PCP_ERR_UNSUPPORTED, "pooled_forward: %lld points per cloud exceed one launch", (long long)L.n);
+    const int gmax = 65535 / mtiles;
+    for (int g0 = 0; g0 < L.b; g0 += gmax) {
+        TcGemmParams p;
+        p.A = A + (int64_t)g0 * L.n * 128; p.a_f32 = 1; p.lda = 128; p.a_group_stride = L.n * 128; p.Bimg = g_tc.img;
+        p.Ext_max = L.pb.ext + (size_t)g0 * L.cout; p.Ext_min = L.pb.ext + total + (size_t)g0 * L.cout;
+        p.M = (int)L.n; p.N = L.cout; p.K = 128; p.groups = std::min(gmax, L.b - g0);
+        PCP_TRY(tc_gemm(p, st));
+    }
+    if (L.batch) {
+        PCP_CUDA_OK(cudaMemsetAsync(L.pb.gram, 0, 128 * 128 * 4, st));
+        PCP_CUDA_OK(cudaMemsetAsync(L.pb.asum, 0, 128 * 8, st));
+        PCP_TRY(tc_wgrad(A, 128, rows, 128, A, 128, 128, L.pb.gram, 128, st));
+        pool_colsum_kernel<<<(int)std::min<int64_t>((rows + 1) / 2, (int64_t)sm_count() * 8), 256, 0, st>>>(A, rows, L.pb.asum);
+        PCP_CHECK_LAUNCH();
+        pool_implicit_stats_kernel<<<(L.cout + 3) / 4, 128, 0, st>>>(L.pb.gram, L.pb.asum, L.W, L.cout, L.red, L.red + L.cout);
+        PCP_CHECK_LAUNCH();
+    }
+    bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(L.red, L.red + L.cout, (double)rows, L.cout, L.batch ? 1 : 0, L.gamma, L.beta_in,
+                                                           L.mov_mean, L.mov_var, L.mean, L.inv, L.sc, L.beta, kBnEpsT, kBnMomentum);
+    PCP_CHECK_LAUNCH();
+    pool_select_kernel<<<grid_for(total), 256, 0, st>>>(L.pb.ext, L.pb.ext + total, L.bnp(), total, L.cout, g, L.pb.zsel, L.pb.arg);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+// dg (b x cout) -> dW (+=), dgamma / dbeta (=), dA (rows x 128, =); A must be the forward input again
+static int pooled_backward(const PoolLayer &L, const float *A, const float *g, const float *dg, float *dW, float *dgamma, float *dbeta, float *dA,
+                           cudaStream_t st)
+{
+    const int64_t rows = (int64_t)L.b * L.n;
+    pool_bwd_coef_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(g, dg, L.pb.zsel, L.bnp(), L.b, L.cout, (double)rows, L.batch ? 1 : 0, L.red,
+                                                             L.red + L.cout, L.pb.c0, L.pb.c1, L.pb.S);
+    PCP_CHECK_LAUNCH();
+    if (L.batch && L.trainable && dgamma && dbeta) {
+        store_bn_grads_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(L.red, L.red + L.cout, L.cout, dgamma, dbeta);
+        PCP_CHECK_LAUNCH();
+    }
+    pool_round_transpose_kernel<<<dim3((L.cout + 31) / 32, 4), 256, 0, st>>>(L.W, 128, L.cout, L.pb.Wt);
+    PCP_CHECK_LAUNCH();
+    if (L.trainable && dW) {
+        pool_dw_kernel<<<L.cout / 8, 128, 0, st>>>(L.pb.gram, L.pb.asum, L.pb.Wt, L.pb.c0, L.pb.c1, L.pb.S, L.pb.arg, A, L.b, L.n, L.cout,
+                                                  L.batch ? 1 : 0, dW);
+        PCP_CHECK_LAUNCH();
+    }
+    if (dA) {
+        if (L.batch) {
+            pool_q_kernel<<<128, 128, (size_t)L.cout * 4, st>>>(L.pb.Wt, L.pb.c0, L.pb.c1, L.cout, L.pb.Q, L.pb.q);
+            PCP_CHECK_LAUNCH();
+            PCP_TRY(mm_nn(A, rows, 128, L.pb.Q, 128, 128, dA, L.pb.q, st));
+        } else {
+            PCP_CUDA_OK(cudaMemsetAsync(dA, 0, (size_t)rows * 512, st));
+        }
+        pool_scatter_kernel<<<dim3((L.cout + 63) / 64, L.b), 128, 0, st>>>(L.pb.S, L.pb.arg, L.pb.Wt, L.n, L.cout, 64, dA);
+        PCP_CHECK_LAUNCH();
+    }
+    return PCP_OK;
+}
