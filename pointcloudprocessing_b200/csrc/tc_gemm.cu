@@ -118,46 +118,6 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
         const bool row_ok = row < rows_valid;
         const float *bias = p.bias ? p.bias + (size_t)g * p.bias_group_stride : nullptr;
         const size_t c_off = (size_t)g * p.c_group_stride + (size_t)(row0 + row) * p.ldc;
-        if (p.Ext_max) {
-            // per-group column extrema (training max-pool): warp-level redux over the 32 rows of each column, the four warps
-            // merged through shared memory (the operand stages are idle once acc_full fired), one 64-bit atomicMax per
-            // column and CTA
-            unsigned long long *sx = reinterpret_cast<unsigned long long *>(base);            // [2][4][128]
-            for (int c0 = 0; c0 < bnt; c0 += 32) {
-                uint32_t v[32];
-                tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
-                tmem_ld_wait();
-                unsigned long long kx = 0ull, kn = 0ull;
-#pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                    const uint32_t key = tc_float_key(v[e]);
-                    const uint32_t wmax = __reduce_max_sync(0xffffffffu, row_ok ? key : 0u);
-                    const uint32_t wmin = __reduce_max_sync(0xffffffffu, row_ok ? ~key : 0u);
-                    const uint32_t bx = __ballot_sync(0xffffffffu, row_ok && key == wmax);
-                    const uint32_t bn = __ballot_sync(0xffffffffu, row_ok && ~key == wmin);
-                    if (lane == e) {
-                        if (bx) kx = ((unsigned long long)wmax << 32) | (0xffffffffu - (uint32_t)(row0 + warp * 32 + __ffs(bx) - 1));
-                        if (bn) kn = ((unsigned long long)wmin << 32) | (0xffffffffu - (uint32_t)(row0 + warp * 32 + __ffs(bn) - 1));
-                    }
-                }
-                sx[warp * 128 + c0 + lane] = kx;
-                sx[512 + warp * 128 + c0 + lane] = kn;
-            }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (tid < bnt) {
-                const int n = nt * bnt + tid;
-                if (n < p.N) {
-                    unsigned long long kx = sx[tid], kn = sx[512 + tid];
-#pragma unroll
-                    for (int w = 1; w < 4; ++w) {
-                        kx = max(kx, sx[w * 128 + tid]);
-                        kn = max(kn, sx[512 + w * 128 + tid]);
-                    }
-                    if (kx) atomicMax(p.Ext_max + (size_t)g * p.N + n, kx);
-                    if (kn) atomicMax(p.Ext_min + (size_t)g * p.N + n, kn);
-                }
-            }
-        } else
         for (int c0 = 0; c0 < bnt; c0 += 32) {
             uint32_t v[32];
             tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
@@ -281,7 +241,7 @@ void pack_gemm_b_image(const float *W, int K, int N, std::vector<uint16_t> &img)
 
 int tc_gemm(const TcGemmParams &p, cudaStream_t st)
 {
-    PCP_REQUIRE(p.A && p.Bimg && (p.C32 || p.C16 || p.Csoftmax || (p.Ext_max && p.Ext_min)), PCP_ERR_INVALID, "tc_gemm: null operand");
+    PCP_REQUIRE(p.A && p.Bimg && (p.C32 || p.C16 || p.Csoftmax), PCP_ERR_INVALID, "tc_gemm: null operand");
     PCP_REQUIRE(p.K >= 64 && p.K % 64 == 0, PCP_ERR_UNSUPPORTED, "tc_gemm: K=%d must be a multiple of 64", p.K);
     PCP_REQUIRE(p.N >= 1 && (p.N <= 128 || p.N % 128 == 0), PCP_ERR_UNSUPPORTED, "tc_gemm: N=%d must be <= 128 or a multiple of 128", p.N);
     PCP_REQUIRE(!p.Csoftmax || p.N <= 32, PCP_ERR_UNSUPPORTED, "tc_gemm: softmax epilogue needs N <= 32");

@@ -27,13 +27,10 @@ struct TcGemmParams {
     int groups = 1;
     int relu = 0;
     int accumulate = 0;                 // C32 += result (input-gradient accumulation); no bias / relu / softmax
-    // training max-pool (train_pool.cu): per-group column extrema of the raw accumulator instead of a stored C.
-    // Ext_max / Ext_min: (groups x N) packed keys, zero-initialised by the caller, merged with atomicMax:
-    //   hi 32 bits = order-preserving key of the value (inverted for the minimum), lo 32 bits = ~row (first row wins ties)
-    unsigned long long *Ext_max = nullptr, *Ext_min = nullptr;
 };
 
-// order-preserving uint32 key of a float (larger float <=> larger key) and its inverse
+// order-preserving uint32 key of a float (larger float <=> larger key) and its inverse; packed extrema records of the
+// training max-pool (tc_train.cu tc_pool_extrema): key << 32 | ~row, merged with a 64-bit atomicMax (first row wins ties)
 __host__ __device__ inline uint32_t tc_float_key(uint32_t bits) { return (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u); }
 __host__ __device__ inline uint32_t tc_key_float_bits(uint32_t key) { return (key & 0x80000000u) ? (key ^ 0x80000000u) : ~key; }
 

@@ -237,6 +237,161 @@ int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ
     return PCP_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// per-cloud column extrema of Z = A . W without storing Z (training max-pool, train_pool.inl)
+// ------------------------------------------------------------------------------------------------
+// One CTA per 128-row tile of a cloud.  The tile of A (128 rows x 128 K) is converted to bf16 ONCE and stays in shared
+// memory; the 128-channel tiles of W stream through two stages.  The MMA is issued TRANSPOSED — W tile as the A operand
+// (M = 128 channels), the activation tile as the B operand (N = 128 rows) — so the accumulator has channels on the TMEM
+// lanes and rows along the columns: the epilogue thread that owns a channel reduces over the rows serially in registers
+// (no shuffles), two 64-bit atomicMax per thread and channel tile merge the row tiles of a cloud.  Two accumulator
+// buffers (2 x 128 TMEM columns) overlap the MMA of tile nt + 1 with the epilogue of tile nt.
+constexpr int kPxThreads = 192;                 // warps 0-3 A producer + epilogue, warp 4 MMA issuer, warp 5 W loader
+constexpr uint32_t kPxTile = 32768;             // 128 x 128 bf16: two SW128 k-tiles of 16 KB
+constexpr uint32_t kPxSmem = 3 * kPxTile + 1024;
+
+struct PoolExtParams {
+    const float *A;                      // (b * n) x 128 fp32 row-major
+    const uint8_t *Wimg;                 // pack_weight_image(W, 128, cout): [cout/128][2] tiles of 16 KB
+    unsigned long long *ext_max, *ext_min;   // b x cout packed keys (tc_gemm.cuh), zero-initialised
+    int n, cout, mtiles;
+};
+
+__global__ void __launch_bounds__(kPxThreads, 2)
+tc_pool_extrema_kernel(const PoolExtParams p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t a_full, w_full[2], w_empty[2], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_base;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t *As = base, *Ws = base + kPxTile;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = blockIdx.x / p.mtiles, mt = blockIdx.x % p.mtiles;
+    const int row0 = mt * 128;
+    const int rows_valid = min(128, p.n - row0);
+    const int NT = p.cout >> 7;
+
+    if (tid == 0) {
+        mbar_init(&a_full, 4);
+        for (int i = 0; i < 2; ++i) { mbar_init(&w_full[i], 1); mbar_init(&w_empty[i], 1); mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+        fence_barrier_init();
+    }
+    if (warp == 4) tmem_alloc(&tmem_base, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base;
+
+    if (warp < 4) {
+        // ---------------- A tile: 8 threads per row (32 B fp32 -> 16 B bf16), 16 rows per pass, clamped rows ----------------
+        const int chunk = tid & 7, rsub = tid >> 3;
+        const float *Ag = p.A + ((int64_t)g * p.n + row0) * 128 + chunk * 8;
+#pragma unroll
+        for (int kt = 0; kt < 2; ++kt) {
+            float4 raw[16];
+#pragma unroll
+            for (int pass = 0; pass < 8; ++pass) {
+                const int r = min(pass * 16 + rsub, rows_valid - 1);
+                const float4 *src = reinterpret_cast<const float4 *>(Ag + (int64_t)r * 128 + kt * 64);
+                raw[2 * pass] = __ldg(src); raw[2 * pass + 1] = __ldg(src + 1);
+            }
+#pragma unroll
+            for (int pass = 0; pass < 8; ++pass) {
+                const float4 f0 = raw[2 * pass], f1 = raw[2 * pass + 1];
+                *reinterpret_cast<uint4 *>(As + kt * 16384 + sw128_offset(128, (uint32_t)(pass * 16 + rsub), (uint32_t)chunk * 8)) =
+                    make_uint4(pack_bf16x2(f0.x, f0.y), pack_bf16x2(f0.z, f0.w), pack_bf16x2(f1.x, f1.y), pack_bf16x2(f1.z, f1.w));
+            }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_full);
+        // ---------------- epilogue: thread = channel, serial reduction over the tile's rows ----------------
+        for (int nt = 0; nt < NT; ++nt) {
+            const int buf = nt & 1;
+            mbar_wait(&acc_full[buf], (uint32_t)((nt >> 1) & 1), 61);
+            tc_fence_after();
+            float mx = -INFINITY, mn = INFINITY;
+            int rmx = 0, rmn = 0;
+            for (int c0 = 0; c0 < rows_valid; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(buf * 128 + c0), v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                    const float f = __uint_as_float(v[e]);
+                    const bool ok = c0 + e < rows_valid;
+                    if (ok && f > mx) { mx = f; rmx = c0 + e; }
+                    if (ok && f < mn) { mn = f; rmn = c0 + e; }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+            const size_t o = (size_t)g * p.cout + (size_t)nt * 128 + tid;
+            if (mx > -INFINITY)
+                atomicMax(p.ext_max + o, ((unsigned long long)tc_float_key(__float_as_uint(mx)) << 32) | (0xffffffffu - (uint32_t)(row0 + rmx)));
+            if (mn < INFINITY)
+                atomicMax(p.ext_min + o, ((unsigned long long)(~tc_float_key(__float_as_uint(mn))) << 32) | (0xffffffffu - (uint32_t)(row0 + rmn)));
+        }
+    } else if (warp == 4) {
+        // ---------------- MMA issuer: D[channel, row] = W tile (128 ch x 128 K) . A tile^T ----------------
+        const uint32_t idesc = make_idesc_bf16(128, 128);
+        const uint32_t a_lo = (smem_u32(As) & 0x3FFFFu) >> 4, w_lo = (smem_u32(Ws) & 0x3FFFFu) >> 4;
+        mbar_wait(&a_full, 0, 62);
+        for (int nt = 0; nt < NT; ++nt) {
+            const int s = nt & 1;
+            mbar_wait(&w_full[s], (uint32_t)((nt >> 1) & 1), 63);
+            if (nt >= 2) mbar_wait(&acc_empty[s], (uint32_t)(((nt >> 1) - 1) & 1), 64);
+            tc_fence_after();
+            if (elect_one_sync()) {
+#pragma unroll
+                for (int kt = 0; kt < 2; ++kt)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        mma_bf16_ss(tmem + (uint32_t)(s * 128), sdesc_from_lo(w_lo + (uint32_t)s * (kPxTile >> 4) + kt * 1024 + k * 2),
+                                    sdesc_from_lo(a_lo + kt * 1024 + k * 2), idesc, (kt | k) > 0);
+                mma_commit(&w_empty[s]);
+                mma_commit(&acc_full[s]);
+            }
+            __syncwarp();
+        }
+    } else {
+        // ---------------- W loader ----------------
+        if (lane == 0) {
+            for (int nt = 0; nt < NT; ++nt) {
+                const int s = nt & 1;
+                if (nt >= 2) mbar_wait(&w_empty[s], (uint32_t)(((nt >> 1) - 1) & 1), 65);
+                mbar_arrive_expect_tx(&w_full[s], kPxTile);
+                bulk_g2s(Ws + s * kPxTile, p.Wimg + (size_t)nt * kPxTile, 16384, &w_full[s]);
+                bulk_g2s(Ws + s * kPxTile + 16384, p.Wimg + (size_t)nt * kPxTile + 16384, 16384, &w_full[s]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc(tmem, 256);
+}
+
+int tc_pool_extrema(const float *A, int b, int64_t n, const uint8_t *Wimg, int cout, unsigned long long *ext_max, unsigned long long *ext_min,
+                    cudaStream_t st)
+{
+    PCP_REQUIRE(A && Wimg && ext_max && ext_min, PCP_ERR_INVALID, "tc_pool_extrema: null operand");
+    PCP_REQUIRE(cout >= 128 && cout % 128 == 0 && n >= 1 && n <= 0x7fffffff, PCP_ERR_UNSUPPORTED, "tc_pool_extrema: cout=%d must be a multiple of 128", cout);
+    if (b <= 0) return PCP_OK;
+    PoolExtParams p;
+    p.A = A; p.Wimg = Wimg; p.ext_max = ext_max; p.ext_min = ext_min; p.n = (int)n; p.cout = cout; p.mtiles = (int)((n + 127) / 128);
+    const int64_t grid = (int64_t)b * p.mtiles;
+    PCP_REQUIRE(grid <= 0x7fffffff, PCP_ERR_UNSUPPORTED, "tc_pool_extrema: %lld row tiles exceed one launch", (long long)grid);
+    static bool attr = false;
+    if (!attr) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_pool_extrema_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPxSmem));
+        attr = true;
+    }
+    tc_pool_extrema_kernel<<<(unsigned)grid, kPxThreads, kPxSmem, st>>>(p);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
 }  // namespace pcp
 
 using namespace pcp;

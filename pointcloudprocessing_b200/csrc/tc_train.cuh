@@ -12,4 +12,10 @@ int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, u
 int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ, int64_t ldz, int cout, float *dW, int64_t lddw,
              cudaStream_t st);
 
+// per-cloud column extrema of Z = A . W without storing Z: A (b*n x 128) fp32, Wimg = pack_weight_image(W, 128, cout);
+// ext_max / ext_min (b x cout) hold packed keys (tc_gemm.cuh: value key << 32 | ~row, inverted value key for the minimum),
+// zero-initialised by the caller
+int tc_pool_extrema(const float *A, int b, int64_t n, const uint8_t *Wimg, int cout, unsigned long long *ext_max, unsigned long long *ext_min,
+                    cudaStream_t st);
+
 }  // namespace pcp

@@ -123,7 +123,7 @@ pool_dw_kernel(const float *__restrict__ gram, const double *__restrict__ asum, 
     float acc[8];
 #pragma unroll
     for (int jj = 0; jj < 8; ++jj) acc[jj] = 0.f;
-    if (batch) {
+    if (batch && blockIdx.y == 0) {
         for (int l = 0; l < 128; ++l) {
             const float gv = __ldg(gram + l * 128 + k);
 #pragma unroll
@@ -133,19 +133,18 @@ pool_dw_kernel(const float *__restrict__ gram, const double *__restrict__ asum, 
 #pragma unroll
         for (int jj = 0; jj < 8; ++jj) acc[jj] = acc[jj] * __ldg(c1 + j0 + jj) + as * __ldg(c0 + j0 + jj);
     }
-    for (int c = 0; c < b; ++c) {
+    for (int c = blockIdx.y; c < b; c += gridDim.y) {              // the clouds are split over gridDim.y CTAs
         const size_t i = (size_t)c * cout + j0;
+        float s[8];
+        int r[8];
 #pragma unroll
-        for (int jj = 0; jj < 8; ++jj) {
-            const float s = __ldg(S + i + jj);
-            if (s != 0.f) acc[jj] = fmaf(s, bf16_round(__ldg(A + ((int64_t)c * n + __ldg(arg + i + jj)) * 128 + k)), acc[jj]);
-        }
+        for (int jj = 0; jj < 8; ++jj) { s[jj] = __ldg(S + i + jj); r[jj] = __ldg(arg + i + jj); }
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj)
+            if (s[jj] != 0.f) acc[jj] = fmaf(s[jj], bf16_round(__ldg(A + ((int64_t)c * n + r[jj]) * 128 + k)), acc[jj]);
     }
-    float4 *dst = reinterpret_cast<float4 *>(dW + (size_t)k * cout + j0);
-    float4 a = dst[0], bq = dst[1];
-    a.x += acc[0]; a.y += acc[1]; a.z += acc[2]; a.w += acc[3];
-    bq.x += acc[4]; bq.y += acc[5]; bq.z += acc[6]; bq.w += acc[7];
-    dst[0] = a; dst[1] = bq;
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) atomicAdd(dW + (size_t)k * cout + j0 + jj, acc[jj]);
 }
 
 // Q[k, l] = sum_j Wr[k, j] c1_j Wr[l, j] ; q[k] = sum_j Wr[k, j] c0_j                             (cin == 128; one CTA per k)
@@ -204,16 +203,7 @@ static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStre
     const int64_t rows = (int64_t)L.b * L.n, total = (int64_t)L.b * L.cout;
     PCP_CUDA_OK(cudaMemsetAsync(L.pb.ext, 0, (size_t)total * 16, st));
     PCP_TRY(pack_weight_image(L.W, 128, L.cout, L.cout, false, g_tc.img, st));
-    const int mtiles = (int)((L.n + 127) / 128);
-    PCP_REQUIRE(mtiles <= 65535, PCP_ERR_UNSUPPORTED, "pooled_forward: %lld points per cloud exceed one launch", (long long)L.n);
-    const int gmax = 65535 / mtiles;
-    for (int g0 = 0; g0 < L.b; g0 += gmax) {
-        TcGemmParams p;
-        p.A = A + (int64_t)g0 * L.n * 128; p.a_f32 = 1; p.lda = 128; p.a_group_stride = L.n * 128; p.Bimg = g_tc.img;
-        p.Ext_max = L.pb.ext + (size_t)g0 * L.cout; p.Ext_min = L.pb.ext + total + (size_t)g0 * L.cout;
-        p.M = (int)L.n; p.N = L.cout; p.K = 128; p.groups = std::min(gmax, L.b - g0);
-        PCP_TRY(tc_gemm(p, st));
-    }
+    PCP_TRY(tc_pool_extrema(A, L.b, L.n, g_tc.img, L.cout, L.pb.ext, L.pb.ext + total, st));
     if (L.batch) {
         PCP_CUDA_OK(cudaMemsetAsync(L.pb.gram, 0, 128 * 128 * 4, st));
         PCP_CUDA_OK(cudaMemsetAsync(L.pb.asum, 0, 128 * 8, st));
@@ -246,7 +236,7 @@ static int pooled_backward(const PoolLayer &L, const float *A, const float *g, c
     pool_round_transpose_kernel<<<dim3((L.cout + 31) / 32, 4), 256, 0, st>>>(L.W, 128, L.cout, L.pb.Wt);
     PCP_CHECK_LAUNCH();
     if (L.trainable && dW) {
-        pool_dw_kernel<<<L.cout / 8, 128, 0, st>>>(L.pb.gram, L.pb.asum, L.pb.Wt, L.pb.c0, L.pb.c1, L.pb.S, L.pb.arg, A, L.b, L.n, L.cout,
+        pool_dw_kernel<<<dim3(L.cout / 8, std::min(L.b, 16)), 128, 0, st>>>(L.pb.gram, L.pb.asum, L.pb.Wt, L.pb.c0, L.pb.c1, L.pb.S, L.pb.arg, A, L.b, L.n, L.cout,
                                                   L.batch ? 1 : 0, dW);
         PCP_CHECK_LAUNCH();
     }
