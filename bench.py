@@ -140,7 +140,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--clouds", type=int, default=4096, help="clouds per GPU per step")
-    ap.add_argument("--train-precision", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--train-precision", default="bf16", choices=["fp32", "bf16"], help="C3 training arithmetic (BASELINE config 3 is bf16)")
     ap.add_argument("--skip-extras", action="store_true", help="skip fps / batch32 / all-outputs / cpu baseline (profiling runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -31,7 +31,7 @@ def _sources():
 
 
 def _headers_mtime() -> float:
-    hs = list(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "pcp.h"]
+    hs = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inl")) + [PKG.parent / "include" / "pcp.h"]
     return max(h.stat().st_mtime for h in hs)
 
 

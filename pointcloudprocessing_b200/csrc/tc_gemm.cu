@@ -130,25 +130,38 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
                 if (p.relu) f = f > 0.f ? f : 0.f;
                 o[e] = f;
             }
-            if (row_ok) {
-                const int nbase = nt * bnt + c0;
-                if (p.C32) {
-                    float *dst = p.C32 + c_off + nbase;
-                    if (nbase + 32 <= p.N && (p.ldc & 3) == 0 && (((uintptr_t)dst & 15u) == 0)) {
+            const int nbase = nt * bnt + c0;
+            if (p.C32) {
+                float *Cg = p.C32 + (size_t)g * p.c_group_stride;
+                if (nbase + 32 <= p.N && (p.ldc & 3) == 0 && (((uintptr_t)Cg & 15u) == 0)) {
+                    // warp-uniform fast path: the lane's 32 columns of ITS row go through a warp-private shared tile (the
+                    // operand stages are idle once acc_full fired) so that one store instruction writes four rows x 128
+                    // contiguous bytes instead of 16 bytes in each of 32 rows
+                    float *stage = reinterpret_cast<float *>(base) + warp * (32 * 36);
 #pragma unroll
-                        for (int e = 0; e < 32; e += 4) {
-                            float4 q = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
+                    for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4 *>(stage + lane * 36 + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int rr = warp * 32 + 4 * i + (lane >> 3), c = (lane & 7) * 4;
+                        if (rr < rows_valid) {
+                            float4 q = *reinterpret_cast<const float4 *>(stage + (4 * i + (lane >> 3)) * 36 + c);
+                            float4 *dst = reinterpret_cast<float4 *>(Cg + (size_t)(row0 + rr) * p.ldc + nbase + c);
                             if (p.accumulate) {
-                                const float4 c = *reinterpret_cast<const float4 *>(dst + e);
-                                q.x += c.x; q.y += c.y; q.z += c.z; q.w += c.w;
+                                const float4 cc = *dst;
+                                q.x += cc.x; q.y += cc.y; q.z += cc.z; q.w += cc.w;
                             }
-                            *reinterpret_cast<float4 *>(dst + e) = q;
+                            *dst = q;
                         }
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < 32; ++e) if (nbase + e < p.N) dst[e] = p.accumulate ? dst[e] + o[e] : o[e];
                     }
+                    __syncwarp();
+                } else if (row_ok) {
+                    float *dst = p.C32 + c_off + nbase;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) if (nbase + e < p.N) dst[e] = p.accumulate ? dst[e] + o[e] : o[e];
                 }
+            }
+            if (row_ok) {
                 if (p.C16) {
                     __nv_bfloat16 *dst = p.C16 + c_off + nbase;
                     if (nbase + 32 <= p.N && (p.ldc & 7) == 0 && (((uintptr_t)dst & 15u) == 0)) {

@@ -58,7 +58,7 @@ int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, u
 // wgrad
 // ------------------------------------------------------------------------------------------------
 constexpr int kWgThreads = 288;                 // warps 0-7 producers (+ epilogue on warps 0-3), warp 8 MMA issuer
-constexpr int kWgStages = 3;
+constexpr int kWgStages = 4;
 constexpr uint32_t kWgTile = 16384;             // one operand tile: 128 (MN) x 64 (K = rows) bf16
 constexpr uint32_t kWgStageBytes = 2 * kWgTile;
 constexpr uint32_t kWgSmem = kWgStages * kWgStageBytes + 1024;
@@ -86,7 +86,7 @@ struct WgradParams {
     int64_t rows_per_split;               // multiple of 64
 };
 
-__global__ void __launch_bounds__(kWgThreads, 2)
+__global__ void __launch_bounds__(kWgThreads, 1)
 tc_wgrad_kernel(const WgradParams p)
 {
     extern __shared__ uint8_t smem_raw[];
@@ -133,8 +133,10 @@ tc_wgrad_kernel(const WgradParams p)
             ap[j] = p.A + (a_ok[j] ? ma : 0);            // clamped column: loads stay unconditional, invalid chunks are zeroed
             zp[j] = p.Z + (z_ok[j] ? nz : 0);
         }
-        float4 ra[8], rz[8];
-        auto issue = [&](int kt) {
+        // two k-tiles of loads in flight per thread (2 x 16 float4): the loads of tile kt + 2 are issued before tile kt is
+        // converted, so a tile's loads have two full iterations to land
+        float4 ra0[8], rz0[8], ra1[8], rz1[8];
+        auto issue = [&](int kt, float4 (&ra)[8], float4 (&rz)[8]) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int64_t r = min(r_begin + (int64_t)kt * 64 + krow[j], p.rows - 1);     // clamped row, zeroed below
@@ -144,8 +146,7 @@ tc_wgrad_kernel(const WgradParams p)
                 rz[2 * j] = __ldg(sz); rz[2 * j + 1] = __ldg(sz + 1);
             }
         };
-        issue(0);
-        for (int kt = 0; kt < KT; ++kt) {
+        auto publish = [&](int kt, const float4 (&ra)[8], const float4 (&rz)[8]) {
             const int s = kt % kWgStages;
             uint4 va[4], vz[4];
 #pragma unroll
@@ -157,7 +158,6 @@ tc_wgrad_kernel(const WgradParams p)
                 vz[j] = (row_ok && z_ok[j]) ? make_uint4(pack_bf16x2(z0.x, z0.y), pack_bf16x2(z0.z, z0.w), pack_bf16x2(z1.x, z1.y), pack_bf16x2(z1.z, z1.w))
                                             : make_uint4(0u, 0u, 0u, 0u);
             }
-            if (kt + 1 < KT) issue(kt + 1);
             if (kt >= kWgStages) mbar_wait(&empty[s], (uint32_t)(((kt / kWgStages) - 1) & 1), 50);
             uint8_t *As = base + s * kWgStageBytes, *Zs = As + kWgTile;
 #pragma unroll
@@ -168,22 +168,49 @@ tc_wgrad_kernel(const WgradParams p)
             fence_proxy_async();
             __syncwarp();
             if (lane == 0) mbar_arrive(&full[s]);
+        };
+        issue(0, ra0, rz0);
+        if (KT > 1) issue(1, ra1, rz1);
+        for (int kt = 0; kt < KT; kt += 2) {
+            publish(kt, ra0, rz0);
+            if (kt + 2 < KT) issue(kt + 2, ra0, rz0);
+            if (kt + 1 < KT) {
+                publish(kt + 1, ra1, rz1);
+                if (kt + 3 < KT) issue(kt + 3, ra1, rz1);
+            }
         }
         // ---------------- epilogue (warps 0-3): TMEM lane = input channel m, columns = output channels ----------------
+        // Each lane holds 32 consecutive columns of ITS row; the 32 x 32 block goes through a warp-private shared tile so
+        // that one atomic instruction covers four rows x 128 contiguous bytes (float4 red) instead of 32 rows x 4 bytes.
         if (warp < 4) {
             mbar_wait(&acc_full, 0, 51);
             tc_fence_after();
-            const int m = m0 + tid;
+            float *stage = reinterpret_cast<float *>(base) + warp * (32 * 36);          // operand stages are idle now
+            const bool vec_ok = (p.lddw & 3) == 0 && (((uintptr_t)p.dW & 15u) == 0);
             for (int c0 = 0; c0 < 128; c0 += 32) {
+                if (n0 + c0 >= p.cout) break;
                 uint32_t v[32];
                 tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c0, v);
                 tmem_ld_wait();
-                if (m < p.cin) {
-                    float *dst = p.dW + (int64_t)m * p.lddw + n0 + c0;
 #pragma unroll
-                    for (int e = 0; e < 32; ++e)
-                        if (n0 + c0 + e < p.cout) atomicAdd(dst + e, __uint_as_float(v[e]));
+                for (int e = 0; e < 32; e += 4)
+                    *reinterpret_cast<uint4 *>(stage + lane * 36 + e) = make_uint4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+                __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int r = 4 * i + (lane >> 3), c = (lane & 7) * 4;
+                    const int m = m0 + warp * 32 + r, n = n0 + c0 + c;
+                    const float4 q = *reinterpret_cast<const float4 *>(stage + r * 36 + c);
+                    if (m < p.cin && n < p.cout) {               // cout % 8 == 0: a float4 never straddles the edge
+                        float *dst = p.dW + (int64_t)m * p.lddw + n;
+                        if (vec_ok) {
+                            atomicAdd(reinterpret_cast<float4 *>(dst), q);
+                        } else {
+                            atomicAdd(dst, q.x); atomicAdd(dst + 1, q.y); atomicAdd(dst + 2, q.z); atomicAdd(dst + 3, q.w);
+                        }
+                    }
                 }
+                __syncwarp();
             }
         }
     } else {
@@ -221,7 +248,7 @@ int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ
     p.A = A; p.lda = lda; p.Z = dZ; p.ldz = ldz; p.dW = dW; p.lddw = lddw; p.rows = rows; p.cin = cin; p.cout = cout;
     const int mt = (cin + 127) / 128, nt = (cout + 127) / 128;
     const int64_t ktiles = (rows + 63) / 64;
-    int64_t splits = std::max<int64_t>(1, (2 * (int64_t)sm_count()) / ((int64_t)mt * nt));      // ~2 CTAs per SM in flight
+    int64_t splits = std::max<int64_t>(1, (int64_t)sm_count() / ((int64_t)mt * nt));            // one CTA per SM
     splits = std::min<int64_t>(splits, std::max<int64_t>(1, ktiles / 4));                        // at least 4 k-tiles per split
     splits = std::min<int64_t>(splits, 65535);
     const int64_t kps = (ktiles + splits - 1) / splits;

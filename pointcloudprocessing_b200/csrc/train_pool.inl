@@ -22,14 +22,23 @@
 
 __device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 
-// asum[k] += sum over rows of bf16(A[r, k])          (cin == 128: two row lanes of 128 columns)
+// asum[k] += sum over rows of bf16(A[r, k])          (cin == 128: 32 float4 columns x 8 row lanes, two rows in flight)
 __global__ void __launch_bounds__(256)
 pool_colsum_kernel(const float *__restrict__ A, int64_t rows, double *__restrict__ asum)
 {
-    const int k = threadIdx.x & 127, lane = threadIdx.x >> 7;
-    float acc = 0.f;
-    for (int64_t r = (int64_t)blockIdx.x * 2 + lane; r < rows; r += (int64_t)gridDim.x * 2) acc += bf16_round(__ldg(A + r * 128 + k));
-    atomicAdd(asum + k, (double)acc);
+    const int c4 = threadIdx.x & 31, lane = threadIdx.x >> 5;
+    const float4 *A4 = reinterpret_cast<const float4 *>(A);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto add = [&](const float4 v) { acc.x += bf16_round(v.x); acc.y += bf16_round(v.y); acc.z += bf16_round(v.z); acc.w += bf16_round(v.w); };
+    const int64_t step = (int64_t)gridDim.x * 8;
+    int64_t r = (int64_t)blockIdx.x * 8 + lane;
+    for (; r + step < rows; r += 2 * step) {
+        const float4 v0 = __ldg(A4 + r * 32 + c4), v1 = __ldg(A4 + (r + step) * 32 + c4);
+        add(v0); add(v1);
+    }
+    for (; r < rows; r += step) add(__ldg(A4 + r * 32 + c4));
+    atomicAdd(asum + c4 * 4, (double)acc.x); atomicAdd(asum + c4 * 4 + 1, (double)acc.y);
+    atomicAdd(asum + c4 * 4 + 2, (double)acc.z); atomicAdd(asum + c4 * 4 + 3, (double)acc.w);
 }
 
 // column sums / sums of squares of Z = A.W from the Gram matrix: one warp per output channel
@@ -74,29 +83,38 @@ pool_select_kernel(const unsigned long long *__restrict__ emax, const unsigned l
 }
 
 // BN backward sums over the b selected rows of each channel, the affine coefficients and S = sc * dY
-__global__ void __launch_bounds__(128)
+// (32 channels x 8 cloud lanes per CTA)
+__global__ void __launch_bounds__(256)
 pool_bwd_coef_kernel(const float *__restrict__ g, const float *__restrict__ dg, const float *__restrict__ zsel, BnP p, int b, int cout,
                      double rows, int batch, double *__restrict__ s1o, double *__restrict__ s2o, float *__restrict__ c0, float *__restrict__ c1,
                      float *__restrict__ S)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= cout) return;
-    const float mean = p.mean[j], inv = p.inv[j], sc = p.sc[j];
+    __shared__ double sh1[8][32], sh2[8][32];
+    const int jl = threadIdx.x & 31, cl = threadIdx.x >> 5;
+    const int j = blockIdx.x * 32 + jl;
+    const bool ok = j < cout;
+    const float mean = ok ? p.mean[j] : 0.f, inv = ok ? p.inv[j] : 0.f, sc = ok ? p.sc[j] : 0.f;
     double s1 = 0, s2 = 0;
-    for (int c = 0; c < b; ++c) {
-        const size_t i = (size_t)c * cout + j;
-        const float dy = g[i] > 0.f ? dg[i] : 0.f;
-        s1 += dy;
-        s2 += (double)dy * (double)((zsel[i] - mean) * inv);
-        S[i] = sc * dy;
-    }
-    s1o[j] = s1; s2o[j] = s2;
-    if (batch) {
-        const double k1 = -(double)sc * inv * s2 / rows;
-        c1[j] = (float)k1;
-        c0[j] = (float)(-(double)sc * s1 / rows - k1 * mean);
-    } else {
-        c1[j] = 0.f; c0[j] = 0.f;
+    if (ok)
+        for (int c = cl; c < b; c += 8) {
+            const size_t i = (size_t)c * cout + j;
+            const float dy = g[i] > 0.f ? dg[i] : 0.f;
+            s1 += dy;
+            s2 += (double)dy * (double)((zsel[i] - mean) * inv);
+            S[i] = sc * dy;
+        }
+    sh1[cl][jl] = s1; sh2[cl][jl] = s2;
+    __syncthreads();
+    if (cl == 0 && ok) {
+        for (int l = 1; l < 8; ++l) { s1 += sh1[l][jl]; s2 += sh2[l][jl]; }
+        s1o[j] = s1; s2o[j] = s2;
+        if (batch) {
+            const double k1 = -(double)sc * inv * s2 / rows;
+            c1[j] = (float)k1;
+            c0[j] = (float)(-(double)sc * s1 / rows - k1 * mean);
+        } else {
+            c1[j] = 0.f; c0[j] = 0.f;
+        }
     }
 }
 
@@ -208,7 +226,7 @@ static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStre
         PCP_CUDA_OK(cudaMemsetAsync(L.pb.gram, 0, 128 * 128 * 4, st));
         PCP_CUDA_OK(cudaMemsetAsync(L.pb.asum, 0, 128 * 8, st));
         PCP_TRY(tc_wgrad(A, 128, rows, 128, A, 128, 128, L.pb.gram, 128, st));
-        pool_colsum_kernel<<<(int)std::min<int64_t>((rows + 1) / 2, (int64_t)sm_count() * 8), 256, 0, st>>>(A, rows, L.pb.asum);
+        pool_colsum_kernel<<<(int)std::min<int64_t>((rows + 7) / 8, (int64_t)sm_count() * 4), 256, 0, st>>>(A, rows, L.pb.asum);
         PCP_CHECK_LAUNCH();
         pool_implicit_stats_kernel<<<(L.cout + 3) / 4, 128, 0, st>>>(L.pb.gram, L.pb.asum, L.W, L.cout, L.red, L.red + L.cout);
         PCP_CHECK_LAUNCH();
@@ -226,7 +244,7 @@ static int pooled_backward(const PoolLayer &L, const float *A, const float *g, c
                            cudaStream_t st)
 {
     const int64_t rows = (int64_t)L.b * L.n;
-    pool_bwd_coef_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(g, dg, L.pb.zsel, L.bnp(), L.b, L.cout, (double)rows, L.batch ? 1 : 0, L.red,
+    pool_bwd_coef_kernel<<<(L.cout + 31) / 32, 256, 0, st>>>(g, dg, L.pb.zsel, L.bnp(), L.b, L.cout, (double)rows, L.batch ? 1 : 0, L.red,
                                                              L.red + L.cout, L.pb.c0, L.pb.c1, L.pb.S);
     PCP_CHECK_LAUNCH();
     if (L.batch && L.trainable && dgamma && dbeta) {
