@@ -33,6 +33,17 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
+# stdout carries exactly ONE JSON line: everything else a library writes to fd 1 while the bench runs (NCCL prints its
+# version banner there) is routed to stderr, and the line is written to the saved descriptor at the end.
+_STDOUT_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    sys.stdout.flush()
+    os.write(_STDOUT_FD, (json.dumps(line) + "\n").encode())
+
+
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
@@ -130,7 +141,7 @@ def run_reference(args, rank):
                          "sample": f"{sample} clouds x {N_POINTS} pts per step, oracle/pointnet_torch.py (PyTorch CPU fp32 restatement; TensorFlow not installable here)"},
         "e2e": {"value": rate, "unit": "clouds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -331,7 +342,7 @@ def main():
             "model_tflops": value * flops_per_cloud(N_POINTS) / 1e12,
         }
         line.update(extras)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
