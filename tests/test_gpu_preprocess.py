@@ -157,7 +157,9 @@ def test_gather_points(lib):
     assert np.array_equal(out, np.take_along_axis(x, idx[..., None].astype(np.int64), 1))
 
 
-@pytest.mark.parametrize("b,n,voxel,origin", [(2, 4000, 0.75, None), (3, 20000, 0.5, None), (2, 5000, 1.0, (0.0, -20.0, -10.0)), (1, 131072, 0.35, None)])
+@pytest.mark.parametrize("b,n,voxel,origin", [(2, 4000, 0.75, None), (3, 20000, 0.5, None), (2, 5000, 1.0, (0.0, -20.0, -10.0)), (1, 131072, 0.35, None),
+                                              # bounding grid <= 32 n cells: bitmap-rank fast path; tiny voxels on few points: sort path
+                                              (4, 100000, 0.7, None), (2, 50000, 2.0, (-3.0, 5.0, 1.0)), (2, 300, 0.05, None), (1, 1, 0.5, None)])
 def test_voxel_matches_oracle(lib, b, n, voxel, origin):
     from pointcloudprocessing_b200 import ops
     x = synth.lidar_scans(5005 + n, b, n)
@@ -170,6 +172,19 @@ def test_voxel_matches_oracle(lib, b, n, voxel, origin):
         assert np.array_equal(cnt[c, :v], rn) and (cnt[c, v:] == 0).all()
         assert np.array_equal(cent[c, :v], rc)
     assert cnt.sum(axis=1).tolist() == [n] * b
+
+
+def test_voxel_non_finite_point_flags_the_cloud(lib):
+    """A NaN coordinate makes the cloud's voxel count -1 (oracle: ValueError) on either path; other clouds are unaffected."""
+    from pointcloudprocessing_b200 import ops
+    for n, voxel in ((60000, 0.7), (500, 0.05)):
+        x = synth.lidar_scans(77, 2, n)
+        x[1, n // 3, 1] = np.nan
+        cent, cnt, nv = ops.voxel_downsample(_dev(x), voxel)
+        nv = nv.cpu().numpy()
+        rc, rn, _ = osm.voxel_downsample(x[0], voxel)
+        assert nv[0] == rc.shape[0] and nv[1] == -1
+        assert np.array_equal(cent[0, :nv[0]].cpu().numpy(), rc) and np.array_equal(cnt[0, :nv[0]].cpu().numpy(), rn)
 
 
 def test_golden_sampling_fixture(lib):
