@@ -109,9 +109,9 @@ def voxel_downsample(x: torch.Tensor, voxel: float, origin=None):
     nbytes = C.c_size_t(0)
     _ffi.check(lib.pcp_voxel_workspace_bytes(b, n, C.byref(nbytes)))
     ws = torch.empty((nbytes.value,), device=x.device, dtype=torch.uint8)
-    out = torch.zeros((b, n, 3), device=x.device, dtype=torch.float32)
-    cnt = torch.zeros((b, n), device=x.device, dtype=torch.int32)
-    nv = torch.zeros((b,), device=x.device, dtype=torch.int32)
+    out = torch.empty((b, n, 3), device=x.device, dtype=torch.float32)      # every row is written (zero padded past nvox)
+    cnt = torch.empty((b, n), device=x.device, dtype=torch.int32)
+    nv = torch.empty((b,), device=x.device, dtype=torch.int32)
     org = None if origin is None else np.ascontiguousarray(np.asarray(origin, np.float32).reshape(3))
     _ffi.check(lib.pcp_voxel_f32(_ffi.ptr(x), b, n, _ffi.fptr(org), float(voxel), _ffi.ptr(out), _ffi.ptr(cnt), _ffi.ptr(nv),
                                  _ffi.ptr(ws), nbytes.value, _ffi.stream_ptr()))
