@@ -186,6 +186,34 @@ __device__ __forceinline__ void point_noise(int64_t point, uint64_t seed, uint64
     box_muller3(c, out);
 }
 
+// Warp-cooperative access to runs of xyz points with fully coalesced 16-byte transactions.  A lane that owns 4 points owns
+// 48 contiguous bytes, so per-lane float4 accesses touch every 32-byte sector from two different instructions (half-used
+// sectors, twice the L1 wavefronts and L2 store transactions).  Instead lane l moves float4 l, l+32, l+64 of the warp's
+// 1536-byte run and the lanes pick up / drop off their own 48 bytes in a warp-private shared tile (conflict-free: the
+// quarter-warps of a 16-byte shared access at a 48-byte stride cover all 32 banks).
+struct WarpRun {
+    float4 *tile;                       // 96 float4, private to the warp
+    int lane;
+    __device__ void load(const float4 *src, float4 (&q)[3]) const { q[0] = __ldg(src + lane); q[1] = __ldg(src + 32 + lane); q[2] = __ldg(src + 64 + lane); }
+    __device__ void scatter(const float4 (&q)[3], float (&v)[12]) const
+    {
+        tile[lane] = q[0]; tile[32 + lane] = q[1]; tile[64 + lane] = q[2];
+        __syncwarp();
+        const float4 a = tile[3 * lane], b = tile[3 * lane + 1], c = tile[3 * lane + 2];
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w; v[8] = c.x; v[9] = c.y; v[10] = c.z; v[11] = c.w;
+        __syncwarp();
+    }
+    __device__ void store(const float (&v)[12], float4 *dst) const
+    {
+        tile[3 * lane] = make_float4(v[0], v[1], v[2], v[3]);
+        tile[3 * lane + 1] = make_float4(v[4], v[5], v[6], v[7]);
+        tile[3 * lane + 2] = make_float4(v[8], v[9], v[10], v[11]);
+        __syncwarp();
+        dst[lane] = tile[lane]; dst[32 + lane] = tile[32 + lane]; dst[64 + lane] = tile[64 + lane];
+        __syncwarp();
+    }
+};
+
 __global__ void __launch_bounds__(256)
 philox_normal_kernel(int64_t npoints, uint64_t seed, uint64_t offset, float *__restrict__ out)
 {
@@ -206,8 +234,41 @@ jitter_kernel(const float *__restrict__ x, const float *__restrict__ noise, int6
     const int64_t ngroups = npoints >> 2;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t t0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    __shared__ float4 tiles[8][96];
     if (vec_ok) {
-        for (int64_t g = t0; g < ngroups; g += stride) {
+        // full warp runs (128 points): coalesced through the warp tile, two runs in flight per warp
+        // (the Philox variant is instruction bound — 10 Philox rounds + Box-Muller per point — and keeps the direct path)
+        const WarpRun wr{tiles[threadIdx.x >> 5], (int)(threadIdx.x & 31)};
+        const int64_t nruns = kExplicitNoise ? (ngroups >> 5) : 0, nwarps = stride >> 5, w0 = t0 >> 5;
+        const float4 *x4 = reinterpret_cast<const float4 *>(x), *n4 = reinterpret_cast<const float4 *>(noise);
+        float4 *y4 = reinterpret_cast<float4 *>(y);
+        auto body = [&](int64_t run, const float4 (&q)[3], const float4 (&qn)[3]) {
+            float v[12], z[12];
+            wr.scatter(q, v);
+            if (kExplicitNoise) {
+                wr.scatter(qn, z);
+            } else {
+                const int64_t g = run * 32 + wr.lane;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) point_noise(4 * g + p, seed, offset, z + 3 * p);
+            }
+#pragma unroll
+            for (int j = 0; j < 12; ++j) v[j] = __fadd_rn(v[j], __fmul_rn(z[j], sd[j % 3]));
+            wr.store(v, y4 + run * 96);
+        };
+        for (int64_t run = w0; run < nruns; run += 2 * nwarps) {
+            float4 q0[3], q1[3], m0[3], m1[3];
+            const bool two = run + nwarps < nruns;
+            wr.load(x4 + run * 96, q0);
+            if (kExplicitNoise) wr.load(n4 + run * 96, m0);
+            if (two) {
+                wr.load(x4 + (run + nwarps) * 96, q1);
+                if (kExplicitNoise) wr.load(n4 + (run + nwarps) * 96, m1);
+            }
+            body(run, q0, m0);
+            if (two) body(run + nwarps, q1, m1);
+        }
+        for (int64_t g = (nruns << 5) + t0; g < ngroups; g += stride) {       // the last partial run
             const float4 *xs = reinterpret_cast<const float4 *>(x) + 3 * g;
             float4 a = __ldg(xs), b = __ldg(xs + 1), c = __ldg(xs + 2);
             float v[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
@@ -257,8 +318,28 @@ rotate_kernel(const float *__restrict__ x, int64_t n, const float *__restrict__ 
         for (int j = 0; j < 3; ++j)
             q[j] = __fadd_rn(__fadd_rn(__fmul_rn(p[0], r[3 * j]), __fmul_rn(p[1], r[3 * j + 1])), __fmul_rn(p[2], r[3 * j + 2]));
     };
+    __shared__ float4 tiles[8][96];
     if (vec_ok) {
-        for (int64_t g = t0; g < ngroups; g += stride) {
+        const WarpRun wr{tiles[threadIdx.x >> 5], (int)(threadIdx.x & 31)};
+        const int64_t nruns = ngroups >> 5, nwarps = stride >> 5, w0 = t0 >> 5;
+        const float4 *x4 = reinterpret_cast<const float4 *>(xc);
+        float4 *y4 = reinterpret_cast<float4 *>(yc);
+        auto body = [&](int64_t run, const float4 (&q)[3]) {
+            float v[12], o[12];
+            wr.scatter(q, v);
+#pragma unroll
+            for (int p = 0; p < 4; ++p) rot(v + 3 * p, o + 3 * p);
+            wr.store(o, y4 + run * 96);
+        };
+        for (int64_t run = w0; run < nruns; run += 2 * nwarps) {
+            float4 q0[3], q1[3];
+            const bool two = run + nwarps < nruns;
+            wr.load(x4 + run * 96, q0);
+            if (two) wr.load(x4 + (run + nwarps) * 96, q1);
+            body(run, q0);
+            if (two) body(run + nwarps, q1);
+        }
+        for (int64_t g = (nruns << 5) + t0; g < ngroups; g += stride) {       // the last partial run
             const float4 *xs = reinterpret_cast<const float4 *>(xc) + 3 * g;
             float4 a = __ldg(xs), b = __ldg(xs + 1), c = __ldg(xs + 2);
             float v[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
