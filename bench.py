@@ -312,6 +312,17 @@ def main():
                               "precision": args.train_precision, "loss": last.get("loss"),
                               "config": "C3: PointNet training step (jitter + fwd + bwd + grad all-reduce + Adam), classification_pretrain profile, 1024 pts",
                               "note": "both heads forward like the reference; per-shard BN statistics"}
+        # same step at a FIXED per-GPU batch of 256 (weak scaling of the training path; at N = 1 it is the run above)
+        if world > 1:
+            xw = torch.from_numpy(synth.gaussian_clouds(4004 + rank, 256, N_POINTS)).to(dev)
+            yw = {"classification_output": torch.from_numpy(rng.integers(0, C_CLASSES, 256).astype(np.int32)).to(dev),
+                  "segmentation_output": torch.from_numpy(rng.integers(0, P_PARTS, (256, N_POINTS)).astype(np.int32)).to(dev),
+                  "se3": torch.eye(3, device=dev).repeat(256, 1, 1)}
+            tm._reset_adam_state()
+            ms_tw = timed(lambda i: tm.train_on_batch(ops.jitter(xw, (0.1, 0.1, 0.1), seed=i), yw, global_batch=256 * world, sample_offset=rank * 256), 5, 3)
+            extras["train_c3_weak"] = {"value": world * 256 / (ms_tw * 1e-3), "unit": "clouds/s", "ms_per_step": ms_tw, "global_batch": 256 * world,
+                                       "precision": args.train_precision, "config": "C3 at 256 clouds per GPU (weak scaling)"}
+            del xw, yw
         del tm, xt, yt
 
     if rank == 0:
@@ -319,8 +330,15 @@ def main():
         chain_flops = 2.0 * MAC_TRUNK_PT * N_POINTS * B * K                     # algorithmic FLOPs of all timed chain launches
         achieved = chain_flops / (chain_ms.value * 1e-3) / 1e12 if chain_ms.value > 0 else None
         peak = peaks["bf16_tflops_sustained"] or peaks["bf16_tflops"]
+        # DRAM bytes per chain launch from the committed ncu --set full capture of this command (profiles/, same clouds per step)
+        traffic = None
+        tf = ROOT / "profiles" / "r01_chain2_traffic.json"
+        if tf.exists():
+            rec = json.loads(tf.read_text())
+            if rec.get("clouds_per_launch") == B and rec.get("points") == N_POINTS:
+                traffic = sum(rec["dram_bytes_per_launch"]) / len(rec["dram_bytes_per_launch"])
         roofline = {"bound": "tensor", "kernel": "chain_kernel (tcgen05)", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                    "frac": (achieved / peak) if achieved else None, "traffic": None,
+                    "frac": (achieved / peak) if achieved else None, "traffic": traffic,
                     "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)",
                     "launches": chain_n.value, "kernel_share_of_step": chain_ms.value / (ms_step * K) if ms_step > 0 else None,
                     "algorithmic": f"2*{MAC_TRUNK_PT} FLOP/point x {N_POINTS} pts x {B} clouds per 3 launches"}
