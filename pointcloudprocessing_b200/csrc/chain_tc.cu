@@ -592,39 +592,8 @@ int model_prepare_bf16(pcp_model *m)
     return PCP_OK;
 }
 
-// per-cloud fold: image_b(n, k) = bf16( sum_m R64_b[k][m] * W[m][n] )  —  X_64 . W == X . (R64 . W)  (PointNet.py:228,236)
-__global__ void __launch_bounds__(256)
-fold_r64_kernel(const float *__restrict__ R64, const float *__restrict__ W, uint8_t *__restrict__ img)
-{
-    __shared__ __align__(16) float sW[64 * 64];
-    __shared__ float sR[64 * 65];
-    const int64_t cloud = blockIdx.x;
-    const float *R = R64 + cloud * 4096;
-    for (int i = threadIdx.x; i < 4096; i += 256) { sW[i] = W[i]; sR[(i >> 6) * 65 + (i & 63)] = R[i]; }
-    __syncthreads();
-    uint16_t *out = reinterpret_cast<uint16_t *>(img + cloud * 8192);
-    // thread -> (k, 16 consecutive n): sR reads are conflict-free (stride 65), sW reads broadcast-friendly
-    const int k = threadIdx.x >> 2, n0 = (threadIdx.x & 3) * 16;
-    float acc[16];
-#pragma unroll
-    for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-#pragma unroll 4
-    for (int mm = 0; mm < 64; ++mm) {
-        const float r = sR[k * 65 + mm];
-        const float4 *w4 = reinterpret_cast<const float4 *>(&sW[mm * 64 + n0]);     // 4 x LDS.128 instead of 16 x LDS.32
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const float4 w = w4[q];
-            acc[4 * q] = fmaf(r, w.x, acc[4 * q]); acc[4 * q + 1] = fmaf(r, w.y, acc[4 * q + 1]);
-            acc[4 * q + 2] = fmaf(r, w.z, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(r, w.w, acc[4 * q + 3]);
-        }
-    }
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-        const __nv_bfloat16 h = __float2bfloat16_rn(acc[j]);
-        out[sw128_offset(64, (uint32_t)(n0 + j), (uint32_t)k) / 2] = *reinterpret_cast<const uint16_t *>(&h);
-    }
-}
+// The per-cloud operand images image_b(n, k) = bf16( sum_m R64_b[k][m] * W[m][n] ) — X_64 . W == X . (R64 . W)
+// (PointNet.py:228,236) — come straight out of the feature T-Net's last GEMM (heads_tc.cu: heads_tc_tnet_tail_fold).
 
 static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, int64_t n, const float *R, const uint8_t *wc,
                         float *gmax, cudaStream_t st)
@@ -709,9 +678,8 @@ int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_
         PCP_TRY(launch_chain(ts, ts->A, d_x, b, n, nullptr, nullptr, ws.g1, st));
         PCP_TRY(heads_tc_tnet_tail(m, 0, ws.g1, b, Rout, st));
         PCP_TRY(launch_chain(ts, ts->B, d_x, b, n, Rout, nullptr, ws.g2, st));
-        PCP_TRY(heads_tc_tnet_tail(m, 1, ws.g2, b, ws.R64, st));
-        fold_r64_kernel<<<b, 256, 0, st>>>(ws.R64, m->d_fold + m->layers[L_S2_1].fold_w, ts->wc);
-        PCP_CHECK_LAUNCH();
+        const bool need_r64 = (heads & PCP_HEAD_SEG) && (d_seg || d_seg_logits);       // the seg head folds R64 into its own first layer
+        PCP_TRY(heads_tc_tnet_tail_fold(m, ws.g2, b, ts->wc, need_r64 ? ws.R64 : nullptr, st));
         PCP_TRY(launch_chain(ts, ts->C, d_x, b, n, Rout, ts->wc, ws.g3, st));
     } else {
         if (d_R) PCP_TRY(model_eye3(d_R, b, st));

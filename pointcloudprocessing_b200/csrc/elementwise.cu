@@ -165,6 +165,34 @@ normalize_cluster_kernel(const float *__restrict__ x, int64_t n, float *__restri
     cluster.sync();   // keep part_sum / part_max alive until every peer has read them
 }
 
+// Statistics only (centroid, scale) for batches of SMALL clouds — what the fused model path needs before its first chain
+// kernel.  A cluster launch per 12 KB cloud is all launch / barrier overhead (74 us for 4096 x 1024 points); here a warp
+// owns a cloud: fp64 sums, then the max squared distance on the second (L1-resident) pass.  Same arithmetic as
+// normalize_cluster_kernel.
+__global__ void __launch_bounds__(256)
+normalize_stats_warp_kernel(const float *__restrict__ x, int b, int64_t n, float *__restrict__ centroid_out, float *__restrict__ scale_out)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t cloud = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (cloud >= b) return;
+    const float *xc = x + cloud * n * 3;
+    double sx = 0, sy = 0, sz = 0;
+    for (int64_t i = lane; i < n; i += 32) { sx += (double)xc[3 * i]; sy += (double)xc[3 * i + 1]; sz += (double)xc[3 * i + 2]; }
+    sx = warp_sum(sx); sy = warp_sum(sy); sz = warp_sum(sz);
+    sx = __shfl_sync(0xffffffffu, sx, 0); sy = __shfl_sync(0xffffffffu, sy, 0); sz = __shfl_sync(0xffffffffu, sz, 0);
+    const float cx = (float)(sx / (double)n), cy = (float)(sy / (double)n), cz = (float)(sz / (double)n);
+    float md = 0.f;
+    for (int64_t i = lane; i < n; i += 32) {
+        const float dx = __fsub_rn(xc[3 * i], cx), dy = __fsub_rn(xc[3 * i + 1], cy), dz = __fsub_rn(xc[3 * i + 2], cz);
+        md = fmaxf(md, __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+    }
+    md = warp_max(md);
+    if (lane == 0) {
+        centroid_out[cloud * 3] = cx; centroid_out[cloud * 3 + 1] = cy; centroid_out[cloud * 3 + 2] = cz;
+        scale_out[cloud] = fmaxf(__fsqrt_rn(md), 1e-7f);
+    }
+}
+
 // ---- streaming kernels: 4 points (3 x float4) per thread-iteration ----
 __device__ __forceinline__ void box_muller3(const uint32_t r[4], float out[3]) {
     // u in (0,1]: (r + 1) * 2^-32 ; normals: sqrt(-2 ln u0) * {cos,sin}(2 pi u1), sqrt(-2 ln u2) * cos(2 pi u3)
@@ -420,6 +448,11 @@ extern "C" int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y,
 {
     PCP_REQUIRE(d_x && (d_y || (d_centroid && d_scale)) && b >= 0 && n >= 1, PCP_ERR_INVALID, "pcp_normalize_f32: bad arguments (b=%d n=%lld)", b, (long long)n);
     if (b == 0) return PCP_OK;
+    if (!d_y && n <= 4096 && b >= 64) {
+        normalize_stats_warp_kernel<<<(b + 7) / 8, 256, 0, as_stream(stream)>>>(d_x, b, n, d_centroid, d_scale);
+        PCP_CHECK_LAUNCH();
+        return PCP_OK;
+    }
     // cluster size: slice must fit in shared memory; widen further while the grid under-fills the GPU
     const int64_t max_slice_bytes = 200 * 1024;
     int cs = 1;

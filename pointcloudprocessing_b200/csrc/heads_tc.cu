@@ -7,6 +7,7 @@
 //   h1 = relu(h0 . W[s1_l2_64])              tc_gemm
 //   s1 = relu(h1 . (R64_b . W1[0:64]) + g_b . W1[64:1088] + t1)    per-cloud folded weight image + per-cloud bias
 //   s2..s4, logits, softmax                  tc_gemm chain; activations stay bf16 in HBM between layers
+#include <cmath>
 #include <cstring>
 #include <vector>
 
@@ -26,6 +27,7 @@ struct TcLayerImg {
 
 struct TcHeads {
     TcLayerImg it_d1, it_d2, it_w, ft_d1, ft_d2, ft_w, cls1, cls2, cls3;
+    TcLayerImg ft_fold;                  // 256 -> 4096: feature T-Net output folded into s2_l1_64, columns in image order
     TcLayerImg s1_2, seg1g, seg2, seg3, seg4, seg5;
     float *l0_s1 = nullptr;              // [64][4] folded s1_l1_64 (w0,w1,w2,t)
     const float *wseg1a = nullptr;       // fp32 folded W1[0:64, :] (64 x 512) inside d_fold
@@ -82,6 +84,34 @@ int heads_tc_prepare(pcp_model *m, const std::vector<float> &fold)
         PCP_TRY(make_img(h, h->it_w, fold.data() + m->fold_it_w, m->d_fold + m->fold_it_t, 256, 9));
         PCP_TRY(layer(h->ft_d1, L_FT_D1)); PCP_TRY(layer(h->ft_d2, L_FT_D2));
         PCP_TRY(make_img(h, h->ft_w, fold.data() + m->fold_ft_w, m->d_fold + m->fold_ft_t, 256, 4096));
+        // X_64 = X @ R64 only ever feeds s2_l1_64 in the trunk (PointNet.py:228,236), and R64 = reshape(h . w + b) is linear in
+        // the T-Net's last hidden vector h, so the per-cloud operand image (R64 . W)[n, kk] the third chain kernel reads is
+        // ONE small-M GEMM of h against T[k, (n, kk)] = sum_m w[k, kk*64 + m] W[m, n] with its columns laid out in the image's
+        // SWIZZLE_128B order — no R64 tensor, no per-cloud fold kernel (which was 6.6 % of the forward).
+        {
+            const float *wt = fold.data() + m->fold_ft_w, *bt = fold.data() + m->fold_ft_t, *W = fold.data() + m->layers[L_S2_1].fold_w;
+            std::vector<float> T((size_t)256 * 4096), tb(4096);
+            std::vector<uint32_t> pos(4096);
+            for (int kk = 0; kk < 64; ++kk)
+                for (int n = 0; n < 64; ++n) pos[kk * 64 + n] = sw128_offset(64, (uint32_t)n, (uint32_t)kk) / 2;
+            float row[64];
+            for (int k = 0; k <= 256; ++k) {                              // k == 256: the bias row
+                const float *src = k < 256 ? wt + (size_t)k * 4096 : bt;
+                float *dst = k < 256 ? T.data() + (size_t)k * 4096 : tb.data();
+                for (int kk = 0; kk < 64; ++kk) {
+                    for (int n = 0; n < 64; ++n) row[n] = 0.f;
+                    for (int mm = 0; mm < 64; ++mm) {
+                        const float r = src[kk * 64 + mm];
+                        const float *wr = W + mm * 64;
+                        for (int n = 0; n < 64; ++n) row[n] = fmaf(r, wr[n], row[n]);
+                    }
+                    for (int n = 0; n < 64; ++n) dst[pos[kk * 64 + n]] = row[n];
+                }
+            }
+            float *d_tb = nullptr;
+            PCP_TRY(upload(h, tb.data(), tb.size() * 4, reinterpret_cast<void **>(&d_tb)));
+            PCP_TRY(make_img(h, h->ft_fold, T.data(), d_tb, 256, 4096));
+        }
     }
     PCP_TRY(layer(h->cls1, L_CLS1)); PCP_TRY(layer(h->cls2, L_CLS2)); PCP_TRY(layer(h->cls3, L_CLS3));
     PCP_TRY(layer(h->s1_2, L_S1_2));
@@ -130,6 +160,19 @@ int heads_tc_tnet_tail(pcp_model *m, int which, const float *pooled, int b, floa
     PCP_TRY(gemm_layer(d1, pooled, 1, 1024, b, 1, nullptr, h->d512, nullptr, 512, st));
     PCP_TRY(gemm_layer(d2, h->d512, 0, 512, b, 1, nullptr, h->d256, nullptr, 256, st));
     return gemm_layer(w, h->d256, 0, 256, b, 0, out, nullptr, nullptr, w.N, st);
+}
+
+// feature T-Net tail straight into the per-cloud (R64 . W[s2_l1_64]) operand images of the third chain kernel (b x 8 KB)
+// (r64_out != null: also the plain 64 x 64 matrices, which the segmentation head folds into its own first layer)
+int heads_tc_tnet_tail_fold(pcp_model *m, const float *pooled, int b, uint8_t *wc_img, float *r64_out, cudaStream_t st)
+{
+    TcHeads *h = reinterpret_cast<TcHeads *>(m->tc_heads);
+    PCP_TRY(ensure_small(h, b));
+    PCP_TRY(gemm_layer(h->ft_d1, pooled, 1, 1024, b, 1, nullptr, h->d512, nullptr, 512, st));
+    PCP_TRY(gemm_layer(h->ft_d2, h->d512, 0, 512, b, 1, nullptr, h->d256, nullptr, 256, st));
+    PCP_TRY(gemm_layer(h->ft_fold, h->d256, 0, 256, b, 0, nullptr, reinterpret_cast<__nv_bfloat16 *>(wc_img), nullptr, 4096, st));
+    if (r64_out) PCP_TRY(gemm_layer(h->ft_w, h->d256, 0, 256, b, 0, r64_out, nullptr, nullptr, 4096, st));
+    return PCP_OK;
 }
 
 // classification head (PointNet.py:252-263); Dropout is the identity at inference

@@ -94,6 +94,7 @@ int model_cls_head(pcp_model *m, const float *g3, int b, float *d_cls, float *d_
 int heads_tc_prepare(pcp_model *m, const std::vector<float> &fold);
 void heads_tc_destroy(pcp_model *m);
 int heads_tc_tnet_tail(pcp_model *m, int which, const float *pooled, int b, float *out, cudaStream_t st);
+int heads_tc_tnet_tail_fold(pcp_model *m, const float *pooled, int b, uint8_t *wc_img, float *r64_out, cudaStream_t st);
 int heads_tc_cls(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st);
 int heads_tc_seg(pcp_model *m, const float *d_x, int b, int64_t n, const float *centroid, const float *scale, const float *d_R,
                  const float *d_R64, const float *g3, float *d_seg, float *d_seg_logits, cudaStream_t st);
