@@ -268,6 +268,29 @@ def main():
                          "effective_GBps": 64 * 1024 * 100_000 * 20 / (ms_fps * 1e-3) / 1e9,
                          "effective_frac_of_hbm": 64 * 1024 * 100_000 * 20 / (ms_fps * 1e-3) / 1e9 / peaks["hbm_gbs"],
                          "note": "effective = 20 B per point-distance update (SURVEY §8d); on-chip resident, may exceed 1.0"}
+        if rank == 0:
+            # CPU beside it: the plain-C oracle on one host core, on a bounded sample of the same scans, scaled
+            # linearly to Mpts/s (FPS: 1 of 64 clouds; voxel: 4 of 64) — a reported baseline, not a target
+            try:
+                oc = C.CDLL(str(ROOT / "oracle" / "_build" / "liboracle_sampling.so"))
+                oc.oracle_voxel_f32.restype = C.c_int64
+                sc = scans[:4].cpu().numpy()
+                idx = np.empty((1, 1024), np.int32)
+                t0 = time.perf_counter()
+                oc.oracle_fps_batch_f32(sc.ctypes.data_as(C.c_void_p), 1, C.c_int64(100_000), 1024, 0, idx.ctypes.data_as(C.c_void_p))
+                t_fps = time.perf_counter() - t0
+                oxyz, ocnt = np.empty((100_000, 3), np.float32), np.empty(100_000, np.int32)
+                t0 = time.perf_counter()
+                for c in range(4):
+                    oc.oracle_voxel_f32(sc[c].ctypes.data_as(C.c_void_p), C.c_int64(100_000), None, C.c_float(0.7), oxyz.ctypes.data_as(C.c_void_p),
+                                        ocnt.ctypes.data_as(C.c_void_p))
+                t_vox = time.perf_counter() - t0
+                extras["fps"]["cpu_baseline"] = {"value": 100_000 / t_fps / 1e6, "unit": "Mpts/s", "cores": 1, "kind": "port",
+                                                 "sample": "1 of 64 clouds (100 000 -> 1024), oracle/sampling_c.c"}
+                extras["voxel_cpu_baseline"] = {"value": 4 * 100_000 / t_vox / 1e6, "unit": "Mpts/s", "cores": 1, "kind": "port",
+                                                "sample": "4 of 64 clouds, 0.7 m, oracle/sampling_c.c"}
+            except OSError as e:                                     # the checker library is built by __graft_entry__.build()
+                extras["fps"]["cpu_baseline"] = {"unavailable": str(e)}
         # streaming kernels on the same LiDAR-sized batch (76.8 MB < L2: two alternating batches)
         scans2 = scans.flip(0).contiguous()
         pair = [scans, scans2]
@@ -281,7 +304,7 @@ def main():
         extras["streaming"] = {"config": "64 x 100000 points, 24 B/point algorithmic (12 read + 12 written)", "normalize": stream(ms_norm),
                                "jitter_philox": stream(ms_jit), "rotate": stream(ms_rot),
                                "voxel": {"Mpts_per_s": world * npts / (ms_vox * 1e-3) / 1e6, "ms": ms_vox, "voxel_m": 0.7,
-                                         "note": "key + radix sort + segmented reduce; includes torch allocation of outputs/workspace"}}
+                                         "note": "bitmap-rank fast path (min/max, occupancy bitmap, popcount ranks, fp64 atomic sums); includes the torch allocation of outputs / workspace and the path-dispatch read-back"}}
         del scans, scans2, pair
         # BASELINE config 5: 8 raw scans of 131 072 points -> voxel 0.7 m -> resize 8192 -> normalise -> classify
         from pointcloudprocessing_b200 import pipeline
