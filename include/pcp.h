@@ -185,8 +185,20 @@ int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, 
 int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, const float *h_gamma, const float *h_beta, const float *h_dg, int b,
                               int64_t n, int cout, int batch, float *h_g, float *h_mean, float *h_inv, float *h_dw, float *h_dgamma,
                               float *h_dbeta, float *h_da);
+/* (tests only) the pcp_allreduce_fn callback (declared below) and row scale under which the following
+ * pcp_selftest_pooled_layer calls run: emulates the data-parallel BatchNorm protocol of the pooled layer on one device. */
+int pcp_selftest_set_bn_allreduce(int (*fn)(void *, void *, size_t, int, void *), void *user, double row_scale);
 
 /* ---- training (pointnet_train.py:310-351) ---- */
+/* Data-parallel BatchNorm.  When a callback is set and pcp_model_loss_backward is called with
+ * global_batch > b, every batch-statistics reduction of the step (forward sums and backward sums of each thawed
+ * BatchNormalization layer; the Gram matrix of the implicitly handled pooled layers) is summed over the ranks through it
+ * before it is used, so the data-parallel step computes the single-device step on the concatenated batch (the reference
+ * trains on one device, pointnet_train.py:221-228).  fn must all-reduce(sum) `count` elements of d_buf in place (dtype 0 =
+ * float32, 1 = float64), ordered on `stream`, and return 0; it is called on the thread that runs the step.  Equal shard
+ * sizes are assumed (rows of the concatenated batch = local rows * global_batch / b). */
+typedef int (*pcp_allreduce_fn)(void *user, void *d_buf, size_t count, int dtype, pcp_stream stream);
+int pcp_model_set_bn_allreduce(pcp_model *m, pcp_allreduce_fn fn, void *user);
 #define PCP_GROUP_SHARED 0
 #define PCP_GROUP_INPUT_TRANSFORM 1
 #define PCP_GROUP_CLS_HEAD 2

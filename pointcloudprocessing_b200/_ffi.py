@@ -47,6 +47,9 @@ _vp, _i32, _i64, _u32, _u64, _sz, _f = C.c_void_p, C.c_int, C.c_int64, C.c_uint3
 _fp = C.POINTER(C.c_float)
 
 # name -> (restype, argtypes); every name here must be declared in include/pcp.h (tests check both ways)
+# pcp_allreduce_fn (include/pcp.h): int fn(void *user, void *d_buf, size_t count, int dtype, pcp_stream stream)
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p)
+
 SIGNATURES = {
     "pcp_last_error": (C.c_char_p, []),
     "pcp_version": (_i32, []),
@@ -88,6 +91,8 @@ SIGNATURES = {
     "pcp_selftest_tc_mm": (_i32, [_fp, _fp, _i64, _i32, _i32, _i32, _i32, _fp]),
     "pcp_selftest_pooled_layer": (_i32, [_fp, _fp, _fp, _fp, _fp, _i32, _i64, _i32, _i32, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "pcp_model_set_trainable": (_i32, [_vp, _i32, _i32]),
+    "pcp_model_set_bn_allreduce": (_i32, [_vp, _vp, _vp]),
+    "pcp_selftest_set_bn_allreduce": (_i32, [_vp, _vp, C.c_double]),
     "pcp_model_loss_backward": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, C.POINTER(TrainConfig), _i32, _vp, _vp, _fp, _vp]),
     "pcp_model_evaluate": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, C.POINTER(TrainConfig), _fp, _vp]),
     "pcp_model_grad_buffer": (_i32, [_vp, C.POINTER(_vp), C.POINTER(_sz)]),

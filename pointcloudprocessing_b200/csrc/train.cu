@@ -540,8 +540,10 @@ __global__ void axpy_kernel(float *__restrict__ y, const float *__restrict__ x, 
 // buffers of one implicitly handled max-pooled layer (train_pool.inl)
 struct PoolBufs {
     unsigned long long *ext = nullptr;   // 2 x (b x cout) packed extrema keys (max, then min)
-    float *gram = nullptr;               // cin x cin : A^T A of the bf16-rounded input
+    float *gram = nullptr;               // cin x cin : A^T A of the bf16-rounded input (this rank's rows)
     double *asum = nullptr;              // cin       : 1^T A
+    float *gram_g = nullptr;             // the same summed over the ranks (sync-BN); aliases gram / asum otherwise
+    double *asum_g = nullptr;
     float *zsel = nullptr;               // b x cout  : the selected extremum of z
     int *arg = nullptr;                  // b x cout  : its row inside the cloud
     float *S = nullptr;                  // b x cout  : sc * dY at that row
@@ -589,6 +591,7 @@ struct TrainState {
     uint8_t *tc_img = nullptr;                                     // scratch bf16 weight image of the tensor-core GEMMs (4 MB)
     PoolBufs pool[3];                                              // L_IT_C3, L_FT_C3, L_S2_3 (bf16 mode)
     bool implicit_pool = false;                                    // pooled layers without their (rows x 1024) tensors (train_pool.inl)
+    pcp_allreduce_fn sync_fn = nullptr; void *sync_user = nullptr; // data-parallel BatchNorm (pcp_model_set_bn_allreduce)
 };
 
 static int ensure_train_buffers(pcp_model *m)
@@ -677,6 +680,7 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
     else
         for (PoolBufs &pb : ts->pool) {
             want(&pb.ext, (size_t)b * 1024 * 16); want(&pb.gram, 128 * 128 * 4); want(&pb.asum, 128 * 8); want(&pb.zsel, (size_t)b * 4096);
+            want(&pb.gram_g, 128 * 128 * 4); want(&pb.asum_g, 128 * 8);
             want(&pb.arg, (size_t)b * 4096); want(&pb.S, (size_t)b * 4096); want(&pb.c0, 4096); want(&pb.c1, 4096); want(&pb.Wt, 1024 * 128 * 4);
             want(&pb.Q, 128 * 128 * 4); want(&pb.q, 512);
         }
@@ -708,6 +712,22 @@ struct TcCtx {
     size_t img_bytes = 0;
 };
 static thread_local TcCtx g_tc;
+
+// Data-parallel BatchNorm: every batch-statistics reduction of the step is summed over the ranks through the
+// host's callback before it is used, so a data-parallel step computes the single-device step on the concatenated batch.
+struct SyncCtx {
+    pcp_allreduce_fn fn = nullptr;
+    void *user = nullptr;
+    double scale = 1.0;            // global batch / local batch: rows of the concatenated batch = local rows * scale
+};
+static thread_local SyncCtx g_sync;
+static inline int sync_sum(void *d_buf, size_t count, int dtype, cudaStream_t st)
+{
+    if (!g_sync.fn) return PCP_OK;
+    const int rc = g_sync.fn(g_sync.user, d_buf, count, dtype, reinterpret_cast<pcp_stream>(st));
+    PCP_REQUIRE(rc == 0, PCP_ERR_INVALID, "BatchNorm all-reduce callback failed (%d)", rc);
+    return PCP_OK;
+}
 
 // C (rows x cout) = A (rows x cin) . W  [+ bias]          groups > 1: per-group bias (stride cout), rows per group
 static int mm_nn(const float *A, int64_t rows, int cin, const float *W, int ldw, int cout, float *Cc, const float *bias, cudaStream_t st,
@@ -784,7 +804,8 @@ static int bn_prepare(pcp_model *m, TL &t, cudaStream_t st)
             colstats_kernel<<<grid_for(t.rows, 64, 4), 256, 0, st>>>(t.Z, t.rows, t.cout, t.red, t.red + t.cout);
         PCP_CHECK_LAUNCH();
     }
-    bn_finalize_kernel<<<(t.cout + 127) / 128, 128, 0, st>>>(t.red, t.red + t.cout, (double)t.rows, t.cout, t.batch ? 1 : 0, param(m, S.t_gamma),
+    if (t.batch) PCP_TRY(sync_sum(t.red, (size_t)t.cout * 2, 1, st));
+    bn_finalize_kernel<<<(t.cout + 127) / 128, 128, 0, st>>>(t.red, t.red + t.cout, (double)t.rows * g_sync.scale, t.cout, t.batch ? 1 : 0, param(m, S.t_gamma),
                                                            param(m, S.t_beta), param(m, S.t_mean), param(m, S.t_var), t.mean, t.inv, t.sc,
                                                            t.beta, kBnEpsT, kBnMomentum);
     PCP_CHECK_LAUNCH();
@@ -837,8 +858,9 @@ static int bn_bwd(pcp_model *m, TL &t, float *G, bool relu, cudaStream_t st)
             PCP_CHECK_LAUNCH();
         }
     }
+    if (t.batch) PCP_TRY(sync_sum(t.red, (size_t)t.cout * 2, 1, st));          // after the LOCAL sums became dgamma / dbeta
     bn_bwd_apply_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(G), reinterpret_cast<const float4 *>(t.Z), n4, t.cout / 4, t.bnp(),
-                                                     relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, 1.0f / (float)t.rows);
+                                                     relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, (float)(1.0 / ((double)t.rows * g_sync.scale)));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -946,6 +968,8 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     if (!ts->tc_img) PCP_CUDA_OK(cudaMalloc(&ts->tc_img, kImgBytes));
     g_tc.on = m->desc.precision == PCP_PRECISION_BF16;
     g_tc.img = ts->tc_img; g_tc.img_bytes = kImgBytes;
+    g_sync = SyncCtx();
+    if (ts->sync_fn && global_batch > b) { g_sync.fn = ts->sync_fn; g_sync.user = ts->sync_user; g_sync.scale = (double)global_batch / (double)b; }
     const int64_t M = (int64_t)b * n;
     const int C = m->desc.num_classes, P = m->desc.num_parts;
     const bool full = !m->desc.vanilla;
@@ -1203,6 +1227,16 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
 
 using namespace pcp;
 
+// test hook (tests only): the BatchNorm all-reduce callback + row scale the next pcp_selftest_pooled_layer calls run under
+// (emulates the data-parallel protocol of the pooled layer on one device); fn == null clears it
+static SyncCtx s_selftest_sync;
+extern "C" int pcp_selftest_set_bn_allreduce(pcp_allreduce_fn fn, void *user, double row_scale)
+{
+    s_selftest_sync = SyncCtx();
+    if (fn) { s_selftest_sync.fn = fn; s_selftest_sync.user = user; s_selftest_sync.scale = row_scale; }
+    return PCP_OK;
+}
+
 // test hook (tests only): one implicitly handled max-pooled layer, forward + backward, host in / host out.
 // A (b*n x 128), W (128 x cout), gamma / beta (cout), dg (b x cout) -> g (b x cout), mean / inv (cout), dW (128 x cout),
 // dgamma / dbeta (cout), dA (b*n x 128).  batch != 0: BN uses batch statistics (moving mean 0 / variance 1 otherwise).
@@ -1224,7 +1258,7 @@ extern "C" int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, con
     want(&dg, bc * 4); want(&g, bc * 4); want(&dWg, (size_t)128 * cout * 4); want(&dgam, cout * 4); want(&dbet, cout * 4); want(&dAo, rows * 512);
     want(&img, (size_t)4 << 20);
     want(&L.mean, cout * 4); want(&L.inv, cout * 4); want(&L.sc, cout * 4); want(&L.beta, cout * 4); want(&L.red, (size_t)cout * 16);
-    want(&L.pb.ext, bc * 16); want(&L.pb.gram, 128 * 128 * 4); want(&L.pb.asum, 128 * 8); want(&L.pb.zsel, bc * 4); want(&L.pb.arg, bc * 4);
+    want(&L.pb.ext, bc * 16); want(&L.pb.gram, 128 * 128 * 4); want(&L.pb.asum, 128 * 8); want(&L.pb.gram_g, 128 * 128 * 4); want(&L.pb.asum_g, 128 * 8); want(&L.pb.zsel, bc * 4); want(&L.pb.arg, bc * 4);
     want(&L.pb.S, bc * 4); want(&L.pb.c0, cout * 4); want(&L.pb.c1, cout * 4); want(&L.pb.Wt, (size_t)cout * 512); want(&L.pb.Q, 128 * 128 * 4);
     want(&L.pb.q, 512);
     size_t total = 0;
@@ -1244,6 +1278,8 @@ extern "C" int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, con
         std::vector<float> ones(cout, 1.f);
         PCP_CUDA_OK(cudaMemcpy(mv, ones.data(), cout * 4, cudaMemcpyHostToDevice));
         g_tc.on = true; g_tc.img = img; g_tc.img_bytes = (size_t)4 << 20;
+        g_sync = SyncCtx();
+        if (s_selftest_sync.fn) g_sync = s_selftest_sync;
         L.W = dW_in; L.gamma = gam; L.beta_in = bet; L.mov_mean = mm; L.mov_var = mv; L.b = b; L.n = n; L.cout = cout;
         L.batch = batch != 0; L.trainable = true;
         PCP_TRY(pooled_forward(L, dA_in, g, nullptr));
@@ -1260,8 +1296,18 @@ extern "C" int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, con
     };
     rc = run();
     g_tc = TcCtx();
+    g_sync = SyncCtx();
     PCP_RELEASE(cudaFree(arena));
     return rc;
+}
+
+extern "C" int pcp_model_set_bn_allreduce(pcp_model *m, pcp_allreduce_fn fn, void *user)
+{
+    PCP_REQUIRE(m, PCP_ERR_INVALID, "pcp_model_set_bn_allreduce: null model");
+    PCP_TRY(ensure_train_buffers(m));
+    TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
+    ts->sync_fn = fn; ts->sync_user = user;
+    return PCP_OK;
 }
 
 extern "C" int pcp_model_grad_buffer(pcp_model *m, float **d_grads, size_t *count)

@@ -82,12 +82,11 @@ pool_select_kernel(const unsigned long long *__restrict__ emax, const unsigned l
     }
 }
 
-// BN backward sums over the b selected rows of each channel, the affine coefficients and S = sc * dY
+// BN backward sums over the b selected rows of each channel and S = sc * dY
 // (32 channels x 8 cloud lanes per CTA)
 __global__ void __launch_bounds__(256)
 pool_bwd_coef_kernel(const float *__restrict__ g, const float *__restrict__ dg, const float *__restrict__ zsel, BnP p, int b, int cout,
-                     double rows, int batch, double *__restrict__ s1o, double *__restrict__ s2o, float *__restrict__ c0, float *__restrict__ c1,
-                     float *__restrict__ S)
+                     double *__restrict__ s1o, double *__restrict__ s2o, float *__restrict__ S)
 {
     __shared__ double sh1[8][32], sh2[8][32];
     const int jl = threadIdx.x & 31, cl = threadIdx.x >> 5;
@@ -108,13 +107,22 @@ pool_bwd_coef_kernel(const float *__restrict__ g, const float *__restrict__ dg, 
     if (cl == 0 && ok) {
         for (int l = 1; l < 8; ++l) { s1 += sh1[l][jl]; s2 += sh2[l][jl]; }
         s1o[j] = s1; s2o[j] = s2;
-        if (batch) {
-            const double k1 = -(double)sc * inv * s2 / rows;
-            c1[j] = (float)k1;
-            c0[j] = (float)(-(double)sc * s1 / rows - k1 * mean);
-        } else {
-            c1[j] = 0.f; c0[j] = 0.f;
-        }
+    }
+}
+
+// c1 = -sc inv s2 / M , c0 = -sc s1 / M - c1 mean from the (all-reduced) sums; zero for a frozen BatchNorm
+__global__ void __launch_bounds__(128)
+pool_coef_kernel(const double *__restrict__ s1, const double *__restrict__ s2, BnP p, int cout, double rows, int batch, float *__restrict__ c0,
+                 float *__restrict__ c1)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= cout) return;
+    if (batch) {
+        const double sc = p.sc[j], k1 = -sc * (double)p.inv[j] * s2[j] / rows;
+        c1[j] = (float)k1;
+        c0[j] = (float)(-sc * s1[j] / rows - k1 * (double)p.mean[j]);
+    } else {
+        c1[j] = 0.f; c0[j] = 0.f;
     }
 }
 
@@ -228,10 +236,20 @@ static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStre
         PCP_TRY(tc_wgrad(A, 128, rows, 128, A, 128, 128, L.pb.gram, 128, st));
         pool_colsum_kernel<<<(int)std::min<int64_t>((rows + 7) / 8, (int64_t)sm_count() * 4), 256, 0, st>>>(A, rows, L.pb.asum);
         PCP_CHECK_LAUNCH();
-        pool_implicit_stats_kernel<<<(L.cout + 3) / 4, 128, 0, st>>>(L.pb.gram, L.pb.asum, L.W, L.cout, L.red, L.red + L.cout);
+        // statistics use the Gram matrix / column sums of the CONCATENATED batch (sync-BN); dW below keeps this rank's
+        const float *gram_s = L.pb.gram;
+        const double *asum_s = L.pb.asum;
+        if (g_sync.fn) {
+            PCP_CUDA_OK(cudaMemcpyAsync(L.pb.gram_g, L.pb.gram, 128 * 128 * 4, cudaMemcpyDeviceToDevice, st));
+            PCP_CUDA_OK(cudaMemcpyAsync(L.pb.asum_g, L.pb.asum, 128 * 8, cudaMemcpyDeviceToDevice, st));
+            PCP_TRY(sync_sum(L.pb.gram_g, 128 * 128, 0, st));
+            PCP_TRY(sync_sum(L.pb.asum_g, 128, 1, st));
+            gram_s = L.pb.gram_g; asum_s = L.pb.asum_g;
+        }
+        pool_implicit_stats_kernel<<<(L.cout + 3) / 4, 128, 0, st>>>(gram_s, asum_s, L.W, L.cout, L.red, L.red + L.cout);
         PCP_CHECK_LAUNCH();
     }
-    bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(L.red, L.red + L.cout, (double)rows, L.cout, L.batch ? 1 : 0, L.gamma, L.beta_in,
+    bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(L.red, L.red + L.cout, (double)rows * g_sync.scale, L.cout, L.batch ? 1 : 0, L.gamma, L.beta_in,
                                                            L.mov_mean, L.mov_var, L.mean, L.inv, L.sc, L.beta, kBnEpsT, kBnMomentum);
     PCP_CHECK_LAUNCH();
     pool_select_kernel<<<grid_for(total), 256, 0, st>>>(L.pb.ext, L.pb.ext + total, L.bnp(), total, L.cout, g, L.pb.zsel, L.pb.arg);
@@ -244,13 +262,16 @@ static int pooled_backward(const PoolLayer &L, const float *A, const float *g, c
                            cudaStream_t st)
 {
     const int64_t rows = (int64_t)L.b * L.n;
-    pool_bwd_coef_kernel<<<(L.cout + 31) / 32, 256, 0, st>>>(g, dg, L.pb.zsel, L.bnp(), L.b, L.cout, (double)rows, L.batch ? 1 : 0, L.red,
-                                                             L.red + L.cout, L.pb.c0, L.pb.c1, L.pb.S);
+    pool_bwd_coef_kernel<<<(L.cout + 31) / 32, 256, 0, st>>>(g, dg, L.pb.zsel, L.bnp(), L.b, L.cout, L.red, L.red + L.cout, L.pb.S);
     PCP_CHECK_LAUNCH();
-    if (L.batch && L.trainable && dgamma && dbeta) {
+    if (L.batch && L.trainable && dgamma && dbeta) {          // this rank's sums: the gradient bucket is summed over the ranks later
         store_bn_grads_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(L.red, L.red + L.cout, L.cout, dgamma, dbeta);
         PCP_CHECK_LAUNCH();
     }
+    if (L.batch) PCP_TRY(sync_sum(L.red, (size_t)L.cout * 2, 1, st));
+    pool_coef_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(L.red, L.red + L.cout, L.bnp(), L.cout, (double)rows * g_sync.scale, L.batch ? 1 : 0, L.pb.c0,
+                                                         L.pb.c1);
+    PCP_CHECK_LAUNCH();
     pool_round_transpose_kernel<<<dim3((L.cout + 31) / 32, 4), 256, 0, st>>>(L.W, 128, L.cout, L.pb.Wt);
     PCP_CHECK_LAUNCH();
     if (L.trainable && dW) {

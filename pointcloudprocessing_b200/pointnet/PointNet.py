@@ -397,10 +397,12 @@ class PointNet:
         return [np.concatenate(o, 0) for o in outs]
 
     # ------------------------------------------------------------------ training (pointnet_train.py:221-228, :310-351)
-    def compile(self, optimizer=None, loss=None, loss_weights=None, metrics=None, **kwargs):
+    def compile(self, optimizer=None, loss=None, loss_weights=None, metrics=None, sync_bn=False, **kwargs):
         """keras Model.compile as the reference driver calls it (pointnet_train.py:334-351): Adam (+ ExponentialDecay),
         SCCE on the two softmax outputs, MSE on `se3`, per-output loss weights.  Resets the optimizer state (a fresh
-        optimizer is compiled for every training profile, pointnet_train.py:310-319)."""
+        optimizer is compiled for every training profile, pointnet_train.py:310-319).
+        sync_bn=True (data parallel only): BatchNorm batch statistics are all-reduced over the ranks inside the step, so
+        N ranks x b/N clouds compute exactly the reference's single-device step on b clouds."""
         from . import keras_compat as K
         opt = optimizer if optimizer is not None else K.Adam()
         if not isinstance(opt, K.Adam):
@@ -408,10 +410,34 @@ class PointNet:
         lw = {"classification_output": 1.0, "segmentation_output": 1.0, "se3": 1.0}
         lw.update(loss_weights or {})
         self._compiled = {"optimizer": opt, "loss_weights": lw}
+        self._set_sync_bn(bool(sync_bn))
         self._step = 0
         self._dropout_seed = (self._random_seed if isinstance(self._random_seed, int) else 0) * 7919 + 12345
         self._adam_reset = True
         return self
+
+    def _set_sync_bn(self, on: bool):
+        """Register / clear the BatchNorm all-reduce callback of the training step (pcp_model_set_bn_allreduce)."""
+        import torch.distributed as dist
+        if not on or not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+            if getattr(self, "_sync_cb", None) is not None:
+                _ffi.check(self._lib.pcp_model_set_bn_allreduce(self._handle, None, None))
+            self._sync_cb = None
+            return
+        dev = torch.cuda.current_device()
+
+        def _allreduce(user, ptr, count, dtype, stream):          # called by the library on this thread, mid-step
+            try:
+                class _Dev:
+                    __cuda_array_interface__ = {"shape": (int(count),), "typestr": "<f8" if dtype == 1 else "<f4", "data": (int(ptr), False), "version": 2}
+                dist.all_reduce(torch.as_tensor(_Dev(), device=torch.device("cuda", dev)), op=dist.ReduceOp.SUM)
+                return 0
+            except Exception:                                      # never let an exception cross the C boundary
+                import traceback
+                traceback.print_exc()
+                return 1
+        self._sync_cb = _ffi.ALLREDUCE_FN(_allreduce)              # keep the thunk alive as long as it is registered
+        _ffi.check(self._lib.pcp_model_set_bn_allreduce(self._handle, C.cast(self._sync_cb, C.c_void_p), None))
 
     def _train_config(self, explicit_masks=False, sample_offset=0, skip_unweighted_heads=False):
         if self._compiled is None:

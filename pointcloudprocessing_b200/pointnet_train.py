@@ -54,11 +54,12 @@ class CtrlC_InterruptHandler(Callback):
 
 
 class TrainProfile:
-    def __init__(self, config_file, device: str = "cuda", precision: str = "fp32"):
+    def __init__(self, config_file, device: str = "cuda", precision: str = "fp32", sync_bn: bool = True):
         with open(config_file, 'r') as cf:
             config = json.load(cf)
         self._config_file = config_file
         self._device, self._precision = device, precision
+        self._sync_bn = sync_bn          # data parallel: BatchNorm statistics over the global batch, like the reference's single device
         info, params, fs = config['info'], config['params'], config['file_system']
         self._name: str = info['name']                                                       # pointnet_train.py:83-87
         self._class_labels: list = list(info['class_labels'].values())
@@ -166,6 +167,7 @@ class TrainProfile:
                       loss={'classification_output': keras.SparseCategoricalCrossentropy(),
                             'segmentation_output': keras.SparseCategoricalCrossentropy(), 'se3': keras.MeanSquaredError()},
                       loss_weights={'classification_output': lw['classification'], 'segmentation_output': lw['segmentation'], 'se3': lw['rotation']},
+                      sync_bn=self._sync_bn,
                       metrics={'classification_output': [keras.SparseCategoricalAccuracy()],
                                'segmentation_output': [keras.SparseCategoricalAccuracy()], 'se3': [keras.RootMeanSquaredError()]})
         return model

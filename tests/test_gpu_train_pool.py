@@ -71,3 +71,73 @@ def test_pooled_layer_implicit(lib, b, n, cout, batch, neg):
     assert err(out["dw"], dW) <= 1e-3
     # dA: the BN-correction term A . (W diag(c1) W^T) runs on tensor cores with the 128 x 128 matrix rounded to bf16
     assert err(out["da"], dA) <= 6e-3
+
+
+def test_pooled_layer_data_parallel_protocol(lib):
+    """sync-BN inside the implicit pooled layer, emulated on one device: two shards A, B of a batch are run separately, the
+    all-reduce callback adds the OTHER shard's recorded sums (Gram matrix / column sums in the forward pass, BN backward sums
+    in the backward pass).  Shard outputs must equal the corresponding rows of the single run on the concatenated batch and
+    the weight gradients must add up to it."""
+    from pointcloudprocessing_b200 import _ffi
+    b, n, cout = 3, 256, 512                                   # per shard
+    rng = np.random.default_rng(99)
+    rows = b * n
+    A = [np.maximum(rng.standard_normal((rows, 128)), 0).astype(np.float32) for _ in range(2)]
+    w = (0.1 * rng.standard_normal((128, cout))).astype(np.float32)
+    gamma = (1.0 + 0.2 * rng.standard_normal(cout)).astype(np.float32)
+    gamma[::5] *= -1.0
+    beta = (0.3 * rng.standard_normal(cout)).astype(np.float32)
+    dg = [rng.standard_normal((b, cout)).astype(np.float32) for _ in range(2)]
+    fp = lambda x: x.ctypes.data_as(C.POINTER(C.c_float))
+
+    def run(a, d, bb):
+        out = {k: np.zeros(s, np.float32) for k, s in dict(g=(bb, cout), mean=(cout,), inv=(cout,), dw=(128, cout), dgamma=(cout,), dbeta=(cout,),
+                                                            da=(bb * n, 128)).items()}
+        st = lib.pcp_selftest_pooled_layer(fp(a), fp(w), fp(gamma), fp(beta), fp(d), bb, n, cout, 1, fp(out["g"]), fp(out["mean"]), fp(out["inv"]),
+                                           fp(out["dw"]), fp(out["dgamma"]), fp(out["dbeta"]), fp(out["da"]))
+        assert st == 0, lib.pcp_last_error()
+        return out
+
+    rec = {}                                                   # per shard: the LOCAL buffers handed to each callback call
+    state = {"shard": 0, "call": 0, "add_from": None}
+
+    def cb(user, ptr, count, dtype, stream):
+        class _Dev:
+            __cuda_array_interface__ = {"shape": (int(count),), "typestr": "<f8" if dtype == 1 else "<f4", "data": (int(ptr), False), "version": 2}
+        t = torch.as_tensor(_Dev(), device="cuda")
+        torch.cuda.synchronize()
+        rec.setdefault(state["shard"], {})[state["call"]] = t.clone()
+        other = state["add_from"]
+        if other is not None and state["call"] in rec.get(other, {}):
+            t += rec[other][state["call"]]
+        torch.cuda.synchronize()
+        state["call"] += 1
+        return 0
+    thunk = _ffi.ALLREDUCE_FN(cb)
+    try:
+        lib.pcp_selftest_set_bn_allreduce(C.cast(thunk, C.c_void_p), None, 2.0)
+        # pass 1: forward sums of both shards do not depend on the other shard — record them (backward sums recorded here are stale)
+        for s in (0, 1):
+            state.update(shard=s, call=0, add_from=None)
+            run(A[s], dg[s], b)
+        fwd = {s: {c: rec[s][c] for c in (0, 1)} for s in (0, 1)}
+        # pass 2: shard B under the global statistics -> its true backward sums; then shard A complete; then shard B complete
+        rec.clear(); rec.update({0: dict(fwd[0]), 1: dict(fwd[1])})
+        state.update(shard=1, call=0, add_from=0); run(A[1], dg[1], b)
+        keep_b = dict(rec[1])
+        state.update(shard=0, call=0, add_from=1); out_a = run(A[0], dg[0], b)
+        rec[1] = keep_b
+        rec[0] = {c: v for c, v in rec[0].items()}
+        state.update(shard=1, call=0, add_from=0); out_b = run(A[1], dg[1], b)
+    finally:
+        lib.pcp_selftest_set_bn_allreduce(None, None, 1.0)
+    ref = run(np.concatenate(A), np.concatenate(dg), 2 * b)
+
+    def err(x, r):
+        return float(np.abs(x - r).max() / max(np.abs(r).max(), 1e-30))
+    assert err(out_a["mean"], ref["mean"]) <= 1e-5 and err(out_a["inv"], ref["inv"]) <= 1e-5
+    assert err(np.concatenate([out_a["g"], out_b["g"]]), ref["g"]) <= 1e-5
+    assert err(np.concatenate([out_a["da"], out_b["da"]]), ref["da"]) <= 1e-3
+    assert err(out_a["dw"] + out_b["dw"], ref["dw"]) <= 1e-3
+    assert err(out_a["dgamma"] + out_b["dgamma"], ref["dgamma"]) <= 1e-4
+    assert err(out_a["dbeta"] + out_b["dbeta"], ref["dbeta"]) <= 1e-4
