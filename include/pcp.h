@@ -189,6 +189,19 @@ int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, const float *h
  * pcp_selftest_pooled_layer calls run: emulates the data-parallel BatchNorm protocol of the pooled layer on one device. */
 int pcp_selftest_set_bn_allreduce(int (*fn)(void *, void *, size_t, int, void *), void *user, double row_scale);
 
+/* ---- pose post-processing, batched: the reference's host NumPy float64 helpers on the device;
+ * fp32 in / out, fp64 arithmetic inside; 3x3 matrices row-major, angles in degrees as (roll, pitch, yaw) ---- */
+/* get_dcm (PCA/utils/mat_ops.py:6-39): R = (roll . pitch . yaw)^T; d_rpy_deg (b x 3) -> d_R (b x 9) */
+int pcp_dcm_from_rpy_f32(const float *d_rpy_deg, int b, float *d_R, pcp_stream stream);
+/* get_roll_pitch_yaw_deg (mat_ops.py:30-36) */
+int pcp_rpy_from_dcm_f32(const float *d_R, int b, float *d_rpy_deg, pcp_stream stream);
+/* reorthogonalize (mat_ops.py:63-65): U V^T of the SVD; like the reference, a reflection stays a reflection */
+int pcp_reorthogonalize_f32(const float *d_R, int b, float *d_out, pcp_stream stream);
+/* solve_kabsch (PCT/utils/calibration.py:3-31): b pairs of (n x 3) point sets -> R (b x 9), t (b x 3) with
+ * aligned = R . measured + t, and the rmse (b; may be null) */
+int pcp_kabsch_f32(const float *d_truth, const float *d_measured, int b, int64_t n, float *d_R, float *d_t, float *d_rmse,
+                   pcp_stream stream);
+
 /* ---- training (pointnet_train.py:310-351) ---- */
 /* Data-parallel BatchNorm.  When a callback is set and pcp_model_loss_backward is called with
  * global_batch > b, every batch-statistics reduction of the step (forward sums and backward sums of each thawed

@@ -90,6 +90,10 @@ SIGNATURES = {
     "pcp_selftest_wgrad": (_i32, [_fp, _fp, _i64, _i32, _i32, _fp]),
     "pcp_selftest_tc_mm": (_i32, [_fp, _fp, _i64, _i32, _i32, _i32, _i32, _fp]),
     "pcp_selftest_pooled_layer": (_i32, [_fp, _fp, _fp, _fp, _fp, _i32, _i64, _i32, _i32, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "pcp_dcm_from_rpy_f32": (_i32, [_vp, _i32, _vp, _vp]),
+    "pcp_rpy_from_dcm_f32": (_i32, [_vp, _i32, _vp, _vp]),
+    "pcp_reorthogonalize_f32": (_i32, [_vp, _i32, _vp, _vp]),
+    "pcp_kabsch_f32": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp]),
     "pcp_model_set_trainable": (_i32, [_vp, _i32, _i32]),
     "pcp_model_set_bn_allreduce": (_i32, [_vp, _vp, _vp]),
     "pcp_selftest_set_bn_allreduce": (_i32, [_vp, _vp, C.c_double]),

@@ -116,3 +116,51 @@ def voxel_downsample(x: torch.Tensor, voxel: float, origin=None):
     _ffi.check(lib.pcp_voxel_f32(_ffi.ptr(x), b, n, _ffi.fptr(org), float(voxel), _ffi.ptr(out), _ffi.ptr(cnt), _ffi.ptr(nv),
                                  _ffi.ptr(ws), nbytes.value, _ffi.stream_ptr()))
     return out, cnt, nv
+
+
+# ---- pose post-processing (PCA/utils/mat_ops.py, PCT/utils/calibration.py), batched on the device ----
+def _f32_cuda(a, shape_tail):
+    t = a if isinstance(a, torch.Tensor) else torch.as_tensor(np.asarray(a, np.float32))
+    t = t.to(device="cuda", dtype=torch.float32).contiguous()
+    assert tuple(t.shape[1:]) == tuple(shape_tail), t.shape
+    return t
+
+
+def get_dcm(rpy_deg) -> torch.Tensor:
+    """mat_ops.get_dcm for a batch: (b, 3) [roll, pitch, yaw] degrees -> (b, 3, 3)."""
+    r = _f32_cuda(rpy_deg, (3,))
+    out = torch.empty((r.shape[0], 3, 3), device=r.device, dtype=torch.float32)
+    _ffi.check(_ffi.load().pcp_dcm_from_rpy_f32(_ffi.ptr(r), r.shape[0], _ffi.ptr(out), _ffi.stream_ptr()))
+    return out
+
+
+def get_roll_pitch_yaw_deg(dcm) -> torch.Tensor:
+    """mat_ops.get_roll_pitch_yaw_deg for a batch: (b, 3, 3) -> (b, 3) [roll, pitch, yaw] degrees."""
+    R = _f32_cuda(dcm, (3, 3))
+    out = torch.empty((R.shape[0], 3), device=R.device, dtype=torch.float32)
+    _ffi.check(_ffi.load().pcp_rpy_from_dcm_f32(_ffi.ptr(R), R.shape[0], _ffi.ptr(out), _ffi.stream_ptr()))
+    return out
+
+
+def reorthogonalize(dcm) -> torch.Tensor:
+    """mat_ops.reorthogonalize for a batch (e.g. the model's predicted `se3`): nearest orthogonal matrix U V^T."""
+    R = _f32_cuda(dcm, (3, 3))
+    out = torch.empty_like(R)
+    _ffi.check(_ffi.load().pcp_reorthogonalize_f32(_ffi.ptr(R), R.shape[0], _ffi.ptr(out), _ffi.stream_ptr()))
+    return out
+
+
+def solve_kabsch(truth_vecs, measured_vecs):
+    """calibration.solve_kabsch for a batch of point-set pairs (b, n, 3): returns R (b,3,3), t (b,3), rmse (b,) with
+    aligned = R @ measured + t."""
+    T = truth_vecs if isinstance(truth_vecs, torch.Tensor) else torch.as_tensor(np.asarray(truth_vecs, np.float32))
+    M = measured_vecs if isinstance(measured_vecs, torch.Tensor) else torch.as_tensor(np.asarray(measured_vecs, np.float32))
+    T = T.to(device="cuda", dtype=torch.float32).contiguous()
+    M = M.to(device="cuda", dtype=torch.float32).contiguous()
+    assert T.dim() == 3 and T.shape == M.shape and T.shape[2] == 3
+    b, n, _ = T.shape
+    R = torch.empty((b, 3, 3), device=T.device, dtype=torch.float32)
+    t = torch.empty((b, 3), device=T.device, dtype=torch.float32)
+    rmse = torch.empty((b,), device=T.device, dtype=torch.float32)
+    _ffi.check(_ffi.load().pcp_kabsch_f32(_ffi.ptr(T), _ffi.ptr(M), b, n, _ffi.ptr(R), _ffi.ptr(t), _ffi.ptr(rmse), _ffi.stream_ptr()))
+    return R, t, rmse
