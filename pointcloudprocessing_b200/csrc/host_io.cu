@@ -287,14 +287,21 @@ extern "C" int pcp_parse_aftr_frame(const char *h_text, size_t bytes, const char
         if (np != 3) { set_error("frame line has %d coordinates, expected 3", np); return PCP_ERR_INVALID; }
         // labels: split on ' ', keep tokens longer than one character
         const char *tok[3]; size_t tlen[3]; int nt = 0;
+        char shown[192]; size_t ns = 0;                                   // the token list as Python prints it, for the message below
         q = rp + 1;
         while (q <= le) {
             const char *c = q;
             while (c < le && *c != ' ') ++c;
-            if (c - q > 1) { if (nt < 3) { tok[nt] = q; tlen[nt] = (size_t)(c - q); } ++nt; }
+            if (c - q > 1) {
+                if (nt < 3) { tok[nt] = q; tlen[nt] = (size_t)(c - q); }
+                const int w = snprintf(shown + ns, sizeof(shown) - ns, "%s'%.*s'", nt ? ", " : "", (int)(c - q), q);
+                if (w > 0) ns = ns + (size_t)w < sizeof(shown) ? ns + (size_t)w : sizeof(shown) - 1;
+                ++nt;
+            }
             q = c + 1;
         }
-        if (nt != 2) { set_error("Dataset must contain both a class label and part label. (%d label tokens)", nt); return PCP_ERR_INVALID; }
+        shown[ns] = 0;
+        if (nt != 2) { set_error("Dataset must contain both a class label and part label. [%s] is not correct.", shown); return PCP_ERR_INVALID; }
         const int ci = lookup(class_labels_nl, tok[0], tlen[0]);
         if (ci < 0) { set_error("Class label %.*s not known", (int)tlen[0], tok[0]); return PCP_ERR_INVALID; }
         const int pi = lookup(part_labels_nl, tok[1], tlen[1]);
