@@ -4,11 +4,14 @@ This file is the checker, never the product: only `tests/`, `__graft_entry__.smo
 `cpu_baseline` / `--impl reference` legs of `bench.py` may import it.  Nothing under
 `pointcloudprocessing_b200/` imports `oracle/`.
 
-PARITY UNPINNED: the reference (MAPieschl/PointCloudProcessing) ships no golden vectors, no
-known-answer tests and no weights, and its arithmetic lives in
-TensorFlow 2.20.0 / Keras 3.10.0 (`point_cloud_analysis/requirements.txt:46,113`), which cannot
-be imported in this environment.  This restatement follows the reference source op by op and the
-published Keras semantics (BN eps 1e-3, biased variance, Glorot-uniform, SCCE clip 1e-7).
+PARITY: GRAPH PINNED, KERAS PRIMITIVES UNPINNED.  The reference (MAPieschl/PointCloudProcessing) ships no golden
+vectors, no known-answer tests and no weights, and TensorFlow 2.20.0 / Keras 3.10.0
+(`point_cloud_analysis/requirements.txt:46,113`) cannot be imported in this environment.  The reference's own model
+code (pointnet/PointNet.py, unmodified) IS executed here on a minimal Keras stand-in by
+tests/golden/make_network_golden.py, and tests/test_network_reference.py holds this restatement to its outputs
+(inference, training-mode step with gradients, frozen-network forward): layer table, names, dataflow, T-Net algebra,
+regulariser and freeze semantics are pinned.  What stays restated from the published Keras semantics on both sides:
+BN eps 1e-3 / biased variance / `training and trainable`, Glorot-uniform, SCCE clip 1e-7, Adam eps, dropout scaling.
 
 All citations are `path:line` under /root/reference/point_cloud_analysis/ (PCA/).
 Everything is explicit float32.
