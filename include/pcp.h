@@ -177,6 +177,13 @@ int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t rows, int ci
  * weight-image packer + tcgen05 GEMM of the bf16 training step; W is (k x n) row-major, or (n x k) row-major when
  * transpose_w (dA = dZ . W^T).  Host pointers; h_c is read when accumulate != 0. */
 int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate, float *h_c);
+/* test hook: C[g] (m x n) = act(bf16(A[g]) . bf16(W) + bias[g]) with bf16 activations in HBM (large shapes run the persistent TMA
+ * kernel, small ones the per-tile kernel); out_kind 0 fp32, 1 bf16, 2 softmax (n <= 32); h_c is fp32; h_bias (groups x n) or NULL */
+int pcp_selftest_tc_gemm_bf16(const float *h_a, const float *h_w, const float *h_bias, int64_t m, int groups, int k, int n,
+                              int out_kind, int relu, float *h_c);
+/* development: average milliseconds of one generic tensor-core GEMM launch on device-resident synthetic operands
+ * (out_kind 0 fp32, 1 bf16, 2 softmax; dbg 1 skips output stores, 2 skips activation loads) */
+int pcp_bench_tc_gemm(int64_t rows, int k, int n, int out_kind, int a_f32, int relu, int iters, int dbg, float *h_ms);
 /* max-pooled layer self-test (tests only): conv 128 -> cout, BN (batch statistics when batch != 0, else moving mean 0 /
  * variance 1), ReLU, reduce_max over the n points of each of the b clouds, and its backward pass, through the implicit
  * path of the bf16 training step (no rows x cout tensor; train_pool.inl).  Host pointers:

@@ -89,6 +89,8 @@ SIGNATURES = {
     "pcp_selftest_umma2": (_i32, [_fp, _fp, _i32, _i32, _fp]),
     "pcp_selftest_wgrad": (_i32, [_fp, _fp, _i64, _i32, _i32, _fp]),
     "pcp_selftest_tc_mm": (_i32, [_fp, _fp, _i64, _i32, _i32, _i32, _i32, _fp]),
+    "pcp_selftest_tc_gemm_bf16": (_i32, [_fp, _fp, _fp, _i64, _i32, _i32, _i32, _i32, _i32, _fp]),
+    "pcp_bench_tc_gemm": (_i32, [_i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _fp]),
     "pcp_selftest_pooled_layer": (_i32, [_fp, _fp, _fp, _fp, _fp, _i32, _i64, _i32, _i32, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),
     "pcp_dcm_from_rpy_f32": (_i32, [_vp, _i32, _vp, _vp]),
     "pcp_rpy_from_dcm_f32": (_i32, [_vp, _i32, _vp, _vp]),

@@ -100,14 +100,15 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
 #pragma unroll
                 for (int pass = 0; pass < 8; ++pass) dst[pass] = __ldg(reinterpret_cast<const uint4 *>(rowp[pass] + (size_t)kt * 128));
             };
-            issue(0, r0);
-            if (KT > 1) issue(1, r1);
+            const bool ld = !(p.dbg & 2);
+            if (ld) issue(0, r0);
+            if (ld && KT > 1) issue(1, r1);
             for (int kt = 0; kt < KT; kt += 2) {
                 publish(kt, r0);
-                if (kt + 2 < KT) issue(kt + 2, r0);
+                if (ld && kt + 2 < KT) issue(kt + 2, r0);
                 if (kt + 1 < KT) {
                     publish(kt + 1, r1);
-                    if (kt + 3 < KT) issue(kt + 3, r1);
+                    if (ld && kt + 3 < KT) issue(kt + 3, r1);
                 }
             }
         }
@@ -115,7 +116,7 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
         mbar_wait(&acc_full, 0, 41);
         tc_fence_after();
         const int row = tid;
-        const bool row_ok = row < rows_valid;
+        const bool row_ok = row < rows_valid && !(p.dbg & 1);
         const float *bias = p.bias ? p.bias + (size_t)g * p.bias_group_stride : nullptr;
         const size_t c_off = (size_t)g * p.c_group_stride + (size_t)(row0 + row) * p.ldc;
         for (int c0 = 0; c0 < bnt; c0 += 32) {
@@ -133,7 +134,8 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
             const int nbase = nt * bnt + c0;
             if (p.C32) {
                 float *Cg = p.C32 + (size_t)g * p.c_group_stride;
-                if (nbase + 32 <= p.N && (p.ldc & 3) == 0 && (((uintptr_t)Cg & 15u) == 0)) {
+                if (p.dbg & 1) {
+                } else if (nbase + 32 <= p.N && (p.ldc & 3) == 0 && (((uintptr_t)Cg & 15u) == 0)) {
                     // warp-uniform fast path: the lane's 32 columns of ITS row go through a warp-private shared tile (the
                     // operand stages are idle once acc_full fired) so that one store instruction writes four rows x 128
                     // contiguous bytes instead of 16 bytes in each of 32 rows
@@ -252,6 +254,8 @@ void pack_gemm_b_image(const float *W, int K, int N, std::vector<uint16_t> &img)
         }
 }
 
+bool tc_gemm_persist_try(const TcGemmParams &p, cudaStream_t st, int *rc);   // tc_gemm_tma.cu
+
 int tc_gemm(const TcGemmParams &p, cudaStream_t st)
 {
     PCP_REQUIRE(p.A && p.Bimg && (p.C32 || p.C16 || p.Csoftmax), PCP_ERR_INVALID, "tc_gemm: null operand");
@@ -260,6 +264,10 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
     PCP_REQUIRE(!p.Csoftmax || p.N <= 32, PCP_ERR_UNSUPPORTED, "tc_gemm: softmax epilogue needs N <= 32");
     PCP_REQUIRE((p.lda % (p.a_f32 ? 4 : 8)) == 0, PCP_ERR_UNSUPPORTED, "tc_gemm: lda must keep 16-byte row chunks aligned");
     if (p.M <= 0 || p.groups <= 0) return PCP_OK;
+    {
+        int rc = PCP_OK;
+        if (tc_gemm_persist_try(p, st, &rc)) return rc;
+    }
     const int bnt_img = tc_gemm_bn_tile(p.N);   // MMA N (multiple of 16); the epilogue reads 32-column TMEM chunks and masks n >= N
     const int ntiles = (p.N + bnt_img - 1) / bnt_img;
     const int mtiles = (p.M + 127) / 128;
@@ -276,3 +284,47 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
 }
 
 }  // namespace pcp
+
+// test hook: C[g] (m x n) = act(bf16(A[g]) (m x k) . bf16(W) (k x n) + bias[g]) through tc_gemm with bf16 activations in HBM
+// (large shapes take the persistent TMA kernel, small ones the per-tile kernel).  out_kind 0 fp32, 1 bf16, 2 softmax (n <= 32);
+// host in / host out (h_c always fp32), synchronous.  h_bias is (groups x n) or null.
+extern "C" int pcp_selftest_tc_gemm_bf16(const float *h_a, const float *h_w, const float *h_bias, int64_t m, int groups, int k, int n,
+                                         int out_kind, int relu, float *h_c)
+{
+    using namespace pcp;
+    PCP_REQUIRE(h_a && h_w && h_c && m >= 1 && groups >= 1 && k >= 64 && n >= 1, PCP_ERR_INVALID, "pcp_selftest_tc_gemm_bf16: bad arguments");
+    const size_t rows = (size_t)m * groups;
+    std::vector<uint16_t> a16(rows * k), img;
+    for (size_t i = 0; i < a16.size(); ++i) a16[i] = f2bf_host(h_a[i]);
+    pack_gemm_b_image(h_w, k, n, img);
+    uint16_t *da = nullptr; uint8_t *dimg = nullptr; float *dbias = nullptr; void *dc = nullptr;
+    const size_t c_bytes = rows * n * (out_kind == 1 ? 2 : 4);
+    PCP_CUDA_OK(cudaMalloc(&da, a16.size() * 2)); PCP_CUDA_OK(cudaMalloc(&dimg, img.size() * 2)); PCP_CUDA_OK(cudaMalloc(&dc, c_bytes));
+    PCP_CUDA_OK(cudaMemcpy(da, a16.data(), a16.size() * 2, cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemcpy(dimg, img.data(), img.size() * 2, cudaMemcpyHostToDevice));
+    PCP_CUDA_OK(cudaMemset(dc, 0xff, c_bytes));
+    if (h_bias) {
+        PCP_CUDA_OK(cudaMalloc(&dbias, (size_t)groups * n * 4));
+        PCP_CUDA_OK(cudaMemcpy(dbias, h_bias, (size_t)groups * n * 4, cudaMemcpyHostToDevice));
+    }
+    TcGemmParams p;
+    p.A = da; p.a_f32 = 0; p.lda = k; p.a_group_stride = (int64_t)m * k; p.Bimg = dimg; p.bias = dbias; p.bias_group_stride = n;
+    p.ldc = n; p.c_group_stride = (int64_t)m * n; p.M = (int)m; p.N = n; p.K = k; p.groups = groups; p.relu = relu;
+    if (out_kind == 0) p.C32 = static_cast<float *>(dc);
+    else if (out_kind == 1) p.C16 = static_cast<__nv_bfloat16 *>(dc);
+    else p.Csoftmax = static_cast<float *>(dc);
+    int rc = tc_gemm(p, nullptr);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (rc == PCP_OK && e != cudaSuccess) { set_error("pcp_selftest_tc_gemm_bf16: %s", cudaGetErrorString(e)); rc = PCP_ERR_CUDA; }
+    if (rc == PCP_OK) {
+        if (out_kind == 1) {
+            std::vector<uint16_t> c16(rows * n);
+            cudaMemcpy(c16.data(), dc, c_bytes, cudaMemcpyDeviceToHost);
+            for (size_t i = 0; i < c16.size(); ++i) { const uint32_t u = (uint32_t)c16[i] << 16; memcpy(&h_c[i], &u, 4); }
+        } else {
+            cudaMemcpy(h_c, dc, c_bytes, cudaMemcpyDeviceToHost);
+        }
+    }
+    cudaFree(da); cudaFree(dimg); cudaFree(dc); cudaFree(dbias);
+    return rc;
+}

@@ -27,6 +27,7 @@ struct TcGemmParams {
     int groups = 1;
     int relu = 0;
     int accumulate = 0;                 // C32 += result (input-gradient accumulation); no bias / relu / softmax
+    int dbg = 0;                        // development (pcp_bench_tc_gemm): 1 = skip output stores, 2 = skip activation loads
 };
 
 // order-preserving uint32 key of a float (larger float <=> larger key) and its inverse; packed extrema records of the

@@ -475,3 +475,39 @@ extern "C" int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t ro
     cudaFree(da); cudaFree(dw); cudaFree(dc); cudaFree(img);
     return rc;
 }
+
+// development hook: time tc_gemm alone on device-resident synthetic operands (bf16 or fp32 activations, zero weights are fine:
+// the kernel is memory-bound).  Buffers rotate through enough copies to exceed the 126 MB L2.  out_kind: 0 fp32, 1 bf16, 2 softmax.
+extern "C" int pcp_bench_tc_gemm(int64_t rows, int k, int n, int out_kind, int a_f32, int relu, int iters, int dbg, float *h_ms)
+{
+    PCP_REQUIRE(h_ms && rows >= 1 && k >= 64 && n >= 1 && iters >= 1, PCP_ERR_INVALID, "pcp_bench_tc_gemm: bad arguments");
+    const size_t a_bytes = (size_t)rows * k * (a_f32 ? 4 : 2), c_bytes = (size_t)rows * n * (out_kind == 1 ? 2 : 4);
+    const int nbuf = (int)std::max<size_t>(2, (size_t)400e6 / (a_bytes + c_bytes) + 1);
+    uint8_t *a = nullptr, *c = nullptr, *img = nullptr;
+    float *bias = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&a, a_bytes * nbuf)); PCP_CUDA_OK(cudaMalloc(&c, c_bytes * nbuf));
+    PCP_CUDA_OK(cudaMalloc(&img, gemm_b_image_bytes(k, n))); PCP_CUDA_OK(cudaMalloc(&bias, (size_t)n * 4));
+    PCP_CUDA_OK(cudaMemset(a, 0, a_bytes * nbuf)); PCP_CUDA_OK(cudaMemset(img, 0, gemm_b_image_bytes(k, n))); PCP_CUDA_OK(cudaMemset(bias, 0, (size_t)n * 4));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    int rc = PCP_OK;
+    for (int it = -3; it < iters && rc == PCP_OK; ++it) {
+        if (it == 0) cudaEventRecord(e0, nullptr);
+        const int bsel = ((it % nbuf) + nbuf) % nbuf;
+        TcGemmParams p;
+        p.A = a + a_bytes * bsel; p.a_f32 = a_f32; p.lda = k; p.Bimg = img; p.bias = bias; p.ldc = n; p.M = (int)rows; p.N = n; p.K = k;
+        p.relu = relu; p.dbg = dbg;
+        if (out_kind == 0) p.C32 = reinterpret_cast<float *>(c + c_bytes * bsel);
+        else if (out_kind == 1) p.C16 = reinterpret_cast<__nv_bfloat16 *>(c + c_bytes * bsel);
+        else p.Csoftmax = reinterpret_cast<float *>(c + c_bytes * bsel);
+        rc = tc_gemm(p, nullptr);
+    }
+    cudaEventRecord(e1, nullptr);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (rc == PCP_OK && e != cudaSuccess) { set_error("pcp_bench_tc_gemm: %s", cudaGetErrorString(e)); rc = PCP_ERR_CUDA; }
+    float ms = 0.f;
+    if (rc == PCP_OK) { cudaEventElapsedTime(&ms, e0, e1); *h_ms = ms / iters; }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(a); cudaFree(c); cudaFree(img); cudaFree(bias);
+    return rc;
+}

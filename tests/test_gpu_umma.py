@@ -82,3 +82,32 @@ def test_training_gemm_device_packed_image(lib, rows, k, n, transpose, acc):
     ref = _bf16_round(a).astype(np.float64) @ (wr.T if transpose else wr) + (c0 if acc else 0.0)
     err = np.abs(c - ref).max() / np.abs(ref).max()
     assert err < 2e-5, err
+
+
+@pytest.mark.parametrize("m,groups,k,n,kind,relu", [
+    (1024, 40, 64, 512, 1, 1),        # seg_l1: per-cloud bias, 4 column tiles            (persistent TMA kernel: 1280 tiles)
+    (40000, 1, 512, 256, 1, 1),       # ragged M (40000 = 312 * 128 + 64), 8 k-tiles, 2 column tiles
+    (1000, 41, 128, 128, 0, 0),       # ragged per-group M: tiles straddle groups, rows past rows_valid must not be stored
+    (50000, 1, 128, 12, 2, 0),        # soft-max epilogue, 16-row weight tile
+    (50000, 1, 256, 72, 1, 1),        # N not a multiple of 32: slow store path
+    (300, 3, 128, 128, 1, 1),         # small: per-tile kernel
+])
+def test_tc_gemm_bf16_activations(lib, m, groups, k, n, kind, relu):
+    """The bf16-activation GEMM of the per-point layers against a float64 product of the bf16-rounded operands."""
+    from pointcloudprocessing_b200 import _ffi
+    rng = np.random.default_rng(m + k + n)
+    a = rng.standard_normal((groups, m, k)).astype(np.float32)
+    w = (rng.standard_normal((k, n)) / np.sqrt(k)).astype(np.float32)
+    bias = rng.standard_normal((groups, n)).astype(np.float32)
+    c = np.full((groups, m, n), np.nan, np.float32)
+    _ffi.check(lib.pcp_selftest_tc_gemm_bf16(_ffi.fptr(a), _ffi.fptr(w), _ffi.fptr(bias), m, groups, k, n, kind, relu, _ffi.fptr(c)))
+    r16 = lambda x: torch.from_numpy(x).bfloat16().double().numpy()
+    ref = r16(a) @ r16(w) + bias[:, None, :].astype(np.float64)
+    if relu:
+        ref = np.maximum(ref, 0)
+    if kind == 2:
+        ex = np.exp(ref - ref.max(-1, keepdims=True))
+        ref = ex / ex.sum(-1, keepdims=True)
+    tol = 1e-2 if kind == 1 else 2e-4                       # bf16 output rounding vs fp32 accumulate
+    assert np.isfinite(c).all()
+    assert np.abs(c - ref).max() <= tol * max(1.0, np.abs(ref).max()), float(np.abs(c - ref).max())
