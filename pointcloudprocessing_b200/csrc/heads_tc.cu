@@ -232,36 +232,51 @@ seg_l0_kernel(const float *__restrict__ x, int64_t n, int64_t npts, const float 
 __global__ void __launch_bounds__(256)
 fold_seg1_kernel(const float *__restrict__ R64, const float *__restrict__ W, uint8_t *__restrict__ img)
 {
-    __shared__ float sR[64 * 65];
+    __shared__ __align__(16) float sRt[64 * 68];            // R64 transposed: sRt[m][k], rows padded to 68 floats (16-byte aligned)
     __shared__ __align__(16) float sW[64 * 64];
     const int64_t cloud = blockIdx.y;
     const int c0 = blockIdx.x * 64;               // 64-column slice of the 512 outputs
-    for (int i = threadIdx.x; i < 4096; i += 256) {
-        sR[(i >> 6) * 65 + (i & 63)] = R64 ? R64[cloud * 4096 + i] : ((i >> 6) == (i & 63) ? 1.f : 0.f);
-        sW[i] = __ldg(W + (size_t)(i >> 6) * 512 + c0 + (i & 63));
+    {
+        // all 32 loads of a thread are issued before the first shared store: one memory round trip, not sixteen
+        float rr[16], ww[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int i = threadIdx.x + j * 256;
+            rr[j] = R64 ? __ldg(R64 + cloud * 4096 + i) : ((i >> 6) == (i & 63) ? 1.f : 0.f);
+            ww[j] = __ldg(W + (size_t)(i >> 6) * 512 + c0 + (i & 63));
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int i = threadIdx.x + j * 256;
+            sRt[(i & 63) * 68 + (i >> 6)] = rr[j];
+            sW[i] = ww[j];
+        }
     }
     __syncthreads();
-    uint16_t *out = reinterpret_cast<uint16_t *>(img + cloud * 65536 + (size_t)(c0 >> 7) * 16384);
-    const int k = threadIdx.x >> 2, n0 = (threadIdx.x & 3) * 16;      // thread -> (k, 16 consecutive n)
+    uint8_t *out = img + cloud * 65536 + (size_t)(c0 >> 7) * 16384;
+    // thread -> (output column n, 16 consecutive k): the image row of column n holds its 64 k-values contiguously (128 B), so a
+    // thread's results leave as two 16-byte stores (the first version scattered 2-byte stores: 73 us for 128 clouds)
+    const int nl = threadIdx.x & 63, k0 = (threadIdx.x >> 6) * 16;
     float acc[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) acc[j] = 0.f;
 #pragma unroll 4
     for (int mm = 0; mm < 64; ++mm) {
-        const float r = sR[k * 65 + mm];
-        const float4 *w4 = reinterpret_cast<const float4 *>(&sW[mm * 64 + n0]);
+        const float w = sW[mm * 64 + nl];
+        const float4 *r4 = reinterpret_cast<const float4 *>(&sRt[mm * 68 + k0]);       // warp-uniform address: broadcast
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const float4 w = w4[q];
-            acc[4 * q] = fmaf(r, w.x, acc[4 * q]); acc[4 * q + 1] = fmaf(r, w.y, acc[4 * q + 1]);
-            acc[4 * q + 2] = fmaf(r, w.z, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(r, w.w, acc[4 * q + 3]);
+            const float4 r = r4[q];
+            acc[4 * q] = fmaf(r.x, w, acc[4 * q]); acc[4 * q + 1] = fmaf(r.y, w, acc[4 * q + 1]);
+            acc[4 * q + 2] = fmaf(r.z, w, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(r.w, w, acc[4 * q + 3]);
         }
     }
+    const uint32_t row = (uint32_t)((c0 & 127) + nl);
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-        const __nv_bfloat16 hb = __float2bfloat16_rn(acc[j]);
-        out[sw128_offset(128, (uint32_t)((c0 & 127) + n0 + j), (uint32_t)k) / 2] = *reinterpret_cast<const uint16_t *>(&hb);
-    }
+    for (int h8 = 0; h8 < 2; ++h8)
+        *reinterpret_cast<uint4 *>(out + sw128_offset(128, row, (uint32_t)(k0 + 8 * h8))) =
+            make_uint4(pack_bf16x2(acc[8 * h8], acc[8 * h8 + 1]), pack_bf16x2(acc[8 * h8 + 2], acc[8 * h8 + 3]),
+                       pack_bf16x2(acc[8 * h8 + 4], acc[8 * h8 + 5]), pack_bf16x2(acc[8 * h8 + 6], acc[8 * h8 + 7]));
 }
 
 static int ensure_seg(TcHeads *h, int clouds, int64_t pts)
