@@ -165,6 +165,11 @@ chain2_kernel(const ChainParams p)
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem = sh.tmem_base;
+    // programmatic dependent launch (the launch opts in): everything above — and the loader's resident weight copies below —
+    // touches only weights, so it overlaps the tail of the preceding kernel; centroid / scale / R / per-cloud weight images /
+    // the pooled-feature buffer are the predecessor's output and are read or written only after this wait
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (warp != 9) asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp < 4) {
         // =========================== front (both CTAs): L0 + mid-layer epilogues ===========================
@@ -395,6 +400,7 @@ chain2_kernel(const ChainParams p)
             for (int l = 0; l < p.nmid; ++l)
                 if (p.mid_cloud_stride[l] == 0)
                     bulk_g2s(WM + wm2_slot(p.mid_slot[l]), p.mid_w[l] + (size_t)rank * p.mid_n[l] * 64u, (uint32_t)p.mid_n[l] * 64u, &sh.wres_full);
+            asm volatile("griddepcontrol.wait;" ::: "memory");
             mbar_wait(&sh.wres_full, 0, 15);
             mbar_arrive_cluster(&sh.wready, 0);
             int pc_layer = -1;
@@ -633,7 +639,16 @@ static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, 
         PCP_CUDA_OK(cudaMemsetAsync(d_trace, 0, trace_bytes, st));
         p.trace = d_trace;
     }
-    chain2_kernel<<<2 * ncl, kChainThreads, kChain2Smem, st>>>(p);
+    {
+        static const bool no_pdl = getenv("PCP_TC_GEMM_NO_PDL") != nullptr;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(2 * ncl); cfg.blockDim = dim3(kChainThreads); cfg.dynamicSmemBytes = kChain2Smem; cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = no_pdl ? 0 : 1;
+        PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, chain2_kernel, p));
+    }
     if (trace_path) {
         std::vector<unsigned long long> h(trace_bytes / 8);
         PCP_CUDA_OK(cudaStreamSynchronize(st));

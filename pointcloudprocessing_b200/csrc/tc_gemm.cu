@@ -43,6 +43,11 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base;
+    // programmatic dependent launch: the skinny head GEMMs run back to back in grids of 1-32 CTAs, so the next launch's
+    // scheduling + prologue (barrier init, TMEM allocation) is let loose now and overlaps this kernel's body; nothing of the
+    // predecessor's output is touched before the wait (no-ops when the launch did not opt in)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp < 4) {
         // ---------------- A producer: 8 threads per row (16 B chunks), 16 rows per pass ----------------
@@ -278,7 +283,14 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
         attr = true;
     }
     PCP_REQUIRE(gy <= 65535, PCP_ERR_UNSUPPORTED, "tc_gemm: %lld row tiles exceed one launch", (long long)gy);
-    tc_gemm_kernel<<<dim3(ntiles, (unsigned)gy), kGemmThreads, kGemmSmem, st>>>(p, bnt_img, mtiles);
+    static const bool no_pdl = getenv("PCP_TC_GEMM_NO_PDL") != nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ntiles, (unsigned)gy); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = kGemmSmem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = no_pdl ? 0 : 1;
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel, p, bnt_img, mtiles));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
