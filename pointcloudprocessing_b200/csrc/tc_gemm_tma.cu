@@ -95,6 +95,7 @@ tc_gemm_persist_kernel(const __grid_constant__ CUtensorMap tmA, const TcGemmPara
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // programmatic dependent launch: see tc_gemm.cu
     // tile walk.  streaming: t = blockIdx.x, += gridDim.x over (gm, nt) with nt fastest.  resident: this CTA keeps column block
     // nt_fix = blockIdx.x % ntiles and walks gm = blockIdx.x / ntiles, += gridDim.x / ntiles (the host makes gridDim.x a multiple
     // of ntiles); neighbouring CTAs read the same activation tile at the same time, so HBM sees it once.
@@ -112,6 +113,7 @@ tc_gemm_persist_kernel(const __grid_constant__ CUtensorMap tmA, const TcGemmPara
                 for (int kt = 0; kt < KT; ++kt) bulk_g2s(base + pl.b_off0 + kt * pl.b_stride, img + (size_t)kt * b_tile_bytes, b_tile_bytes, &b_full);
             }
             const bool lda = !(p.dbg & 2);
+            asm volatile("griddepcontrol.wait;" ::: "memory");       // activations are the predecessor's output; the weights above are not
             for (int t = t_first; t < total_tiles; t += t_step) {
                 const int nt = t % ntiles, gm = t / ntiles;
                 const int g = gm / mtiles, mt = gm % mtiles;
@@ -155,6 +157,7 @@ tc_gemm_persist_kernel(const __grid_constant__ CUtensorMap tmA, const TcGemmPara
     } else {
         // ---------------- epilogue groups: group e (warps 4e..4e+3) takes the tiles with local index i % 2 == e ----------------
         // (all eight warps on every tile was measured slower: one group's arithmetic and stores overlap the other's TMEM reads)
+        asm volatile("griddepcontrol.wait;" ::: "memory");           // bias may be the predecessor's output; C may still be read by it
         const int e = warp >> 2, wq = warp & 3, gt = tid & 127;
         uint8_t *stage = base + kPOffStage + warp * kPStageTile;
         float *bias_buf = reinterpret_cast<float *>(base + kPOffBias + e * 1024);     // two 128-float tiles per group
@@ -372,8 +375,15 @@ bool tc_gemm_persist_try(const TcGemmParams &p, cudaStream_t st, int *rc)
         pl.a_off0 = 0; pl.a_stride = 32768; pl.b_off0 = 16384; pl.b_stride = 32768;
         pl.stages = (int)(kPOperandBytes / 32768u);
     }
-    tc_gemm_persist_kernel<<<grid, kPThreads, kPSmem, st>>>(tm, p, pl, bnt, mtiles, ntiles, (int)total);
-    cudaError_t e = cudaGetLastError();
+    static const bool no_pdl = getenv("PCP_TC_GEMM_NO_PDL") != nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kPThreads); cfg.dynamicSmemBytes = kPSmem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = no_pdl ? 0 : 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, tc_gemm_persist_kernel, tm, p, pl, bnt, mtiles, ntiles, (int)total);
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) { set_error("tc_gemm_persist: %s", cudaGetErrorString(e)); *rc = PCP_ERR_CUDA; }
     else *rc = PCP_OK;
     return true;
