@@ -5,6 +5,8 @@
 //   pcp_resize_to_width_f32<- _adjust_to_input_width         (pointcloud/PointCloudSet.py:443-470)
 //   pcp_rotate_f32         <- new (DCM convention utils/mat_ops.py:6-39)
 #include <cooperative_groups.h>
+#include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "umma.cuh"
@@ -242,6 +244,184 @@ struct WarpRun {
     }
 };
 
+// ---- normalisation of LiDAR-sized clouds (n >= kNormPartsMin): persistent CTAs, slices resident across the phases ----
+// normalize_cluster_kernel keeps a cloud on chip too, but a cluster needs eight free SMs of one GPC at once and holds one
+// CTA per SM that cannot do anything before its 150-200 KB load has landed: 27 % of the HBM roofline at 64 x 100 000.
+// Here a cloud is cut into k slices of <= 48 KB; four CTAs per SM take (cloud, slice) tickets in order, keep their slice
+// in shared memory (one bulk async copy = the only HBM read) and meet the cloud's other slices through two counters in
+// global memory: fp64 component sums -> arrive -> centroid; max squared distance -> arrive -> scale; write.  Tickets are
+// issued in increasing order, so every slice a CTA can wait for is already held by a running CTA or is the next ticket
+// (needs k resident CTAs, nothing about dispatch order).  Same arithmetic as normalize_cluster_kernel, so the same bits.
+// What bounds it (scripts/norm_tune.py, PCP_NORM_DBG): a slice lives ~15 us in shared memory (load ~5, two arrive / poll /
+// read-back chains of ~2.5 us of L2 round trips each, compute ~2, write ~2), so throughput = shared memory per SM / slice
+// lifetime ~ 2.2 TB/s of input whatever the slice size; a second buffer per CTA or a static slice order did not help.
+struct NormScratch { double sum[3]; unsigned maxd2, arrive1, arrive2, pad[3]; };   // 48 B per cloud, zeroed by the launcher
+constexpr int64_t kNormPartsMin = 16384;
+constexpr int kNormSliceBytes = 48 * 1024;       // four 256-thread CTAs per SM
+constexpr int kNormPartThreads = 256;
+
+__device__ __forceinline__ void norm_spin(const unsigned *flag, unsigned target)
+{
+    const long long t0 = clock64();
+    unsigned v;
+    do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if (v >= target) break;
+        __nanosleep(64);
+        if (clock64() - t0 > 4000000000ll) __trap();        // a lost arrival must not hang the device
+    } while (true);
+}
+
+// (x - c) / s correctly rounded without the MUFU.RCP + Newton sequence per element: with r = RN(1 / s), q0 = RN(a r),
+// e = a - s q0 (exact, one FMA), q = RN(q0 + e r) is the correctly rounded quotient (Markstein) unless s has an all-ones
+// significand or an intermediate leaves the normal range — those take the IEEE divide.
+struct NormDiv {
+    float s, r;
+    bool fast;
+    __device__ __forceinline__ explicit NormDiv(float scale)
+    {
+        s = scale;
+        r = __frcp_rn(scale);
+        const unsigned u = __float_as_uint(scale);
+        fast = (u & 0x007fffffu) != 0x007fffffu && scale > 1e-30f && scale < 1e30f;
+    }
+    __device__ __forceinline__ float operator()(float a) const
+    {
+        const float q0 = __fmul_rn(a, r);
+        const float q = __fmaf_rn(__fmaf_rn(-q0, s, a), r, q0);
+        return (fast && fabsf(q0) > 1e-30f && fabsf(q0) < 1e30f) ? q : __fdiv_rn(a, s);
+    }
+};
+
+__global__ void __launch_bounds__(kNormPartThreads)
+normalize_parts_kernel(const float *__restrict__ x, int b, int64_t n, int k, int64_t ppc, float *__restrict__ y,
+                       float *__restrict__ centroid_out, float *__restrict__ scale_out, NormScratch *__restrict__ scr,
+                       unsigned *__restrict__ ticket, unsigned dbg)
+{   // (dbg: timing-experiment bits, see scripts/norm_tune.py; 0 in production)
+    constexpr int T = kNormPartThreads;                    // T % 3 == 1: float4 tid + it T of the slice starts at axis (tid + it) % 3
+    static_assert(T % 3 == 1, "axis rotation below assumes T = 1 (mod 3)");
+    extern __shared__ float4 smem4[];
+    __shared__ double red_d[T / 32][3];
+    __shared__ float red_f[T / 32];
+    __shared__ uint64_t load_bar;
+    __shared__ unsigned item_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, r0 = tid % 3;
+    const unsigned total = (unsigned)b * (unsigned)k;
+    if (tid == 0) { mbar_init(&load_bar, 1); fence_barrier_init(); }
+    uint32_t parity = 0;
+    while (true) {
+        __syncthreads();                                   // the previous slice is dead (and load_bar is initialised)
+        if (tid == 0) item_s = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const unsigned item = item_s;
+        if (item >= total) break;
+        const int64_t cloud = item / (unsigned)k;
+        const int64_t p0 = min(n, (int64_t)(item % (unsigned)k) * ppc);
+        const int np = (int)(min(n, p0 + ppc) - p0);       // np % 4 == 0
+        const int nvec = (np * 3) >> 2;
+        NormScratch *sc = scr + cloud;
+        if (np > 0) {
+            if (tid == 0) {
+                const uint32_t bytes = (uint32_t)np * 12u;
+                const char *src = reinterpret_cast<const char *>(x + (cloud * n + p0) * 3);
+                mbar_arrive_expect_tx(&load_bar, bytes);
+                for (uint32_t o = 0; o < bytes; o += 32768u)
+                    bulk_g2s(reinterpret_cast<char *>(smem4) + o, src + o, min(32768u, bytes - o), &load_bar);
+            }
+            mbar_wait(&load_bar, parity, 71);
+            parity ^= 1u;
+        }
+        // ---- fp64 component sums: 16-byte reads, accumulator [u][j] holds axis (r0 + u + j) % 3 ----
+        double acc[3][4];
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[u][j] = 0.0;
+        for (int v0 = tid; v0 < ((dbg & 2) ? 0 : nvec); v0 += 3 * T) {
+#pragma unroll
+            for (int u = 0; u < 3; ++u) {
+                if (v0 + u * T < nvec) {
+                    const float4 q = smem4[v0 + u * T];
+                    acc[u][0] += (double)q.x; acc[u][1] += (double)q.y; acc[u][2] += (double)q.z; acc[u][3] += (double)q.w;
+                }
+            }
+        }
+        double s3[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int axis = (r0 + u + j) % 3;
+                s3[0] += axis == 0 ? acc[u][j] : 0.0; s3[1] += axis == 1 ? acc[u][j] : 0.0; s3[2] += axis == 2 ? acc[u][j] : 0.0;
+            }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { s3[a] = warp_sum(s3[a]); if (lane == 0) red_d[warp][a] = s3[a]; }
+        __syncthreads();
+        if (tid < 3) {
+            double t = 0;
+            for (int w = 0; w < T / 32; ++w) t += red_d[w][tid];
+            atomicAdd(&sc->sum[tid], t);
+            __threadfence();
+        }
+        __syncthreads();
+        if (tid == 0) { atomicAdd(&sc->arrive1, 1u); if (!(dbg & 1)) norm_spin(&sc->arrive1, (unsigned)k); }
+        __syncthreads();
+        const float cx = (float)(__ldcg(&sc->sum[0]) / (double)n), cy = (float)(__ldcg(&sc->sum[1]) / (double)n),
+                    cz = (float)(__ldcg(&sc->sum[2]) / (double)n);
+        // ---- max squared distance: (dx*dx + dy*dy) + dz*dz, separate roundings; four points = three 16-byte reads ----
+        float md = 0.f;
+        auto dist = [&](float px, float py, float pz) {
+            const float dx = __fsub_rn(px, cx), dy = __fsub_rn(py, cy), dz = __fsub_rn(pz, cz);
+            md = fmaxf(md, __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+        };
+        for (int g = tid; g < ((dbg & 2) ? 0 : (np >> 2)); g += T) {
+            const float4 q0 = smem4[3 * g], q1 = smem4[3 * g + 1], q2 = smem4[3 * g + 2];
+            dist(q0.x, q0.y, q0.z); dist(q0.w, q1.x, q1.y); dist(q1.z, q1.w, q2.x); dist(q2.y, q2.z, q2.w);
+        }
+        md = warp_max(md);
+        if (lane == 0) red_f[warp] = md;
+        __syncthreads();
+        if (tid == 0) {
+            float m = 0.f;
+            for (int w = 0; w < T / 32; ++w) m = fmaxf(m, red_f[w]);
+            atomicMax(&sc->maxd2, __float_as_uint(m));      // non-negative floats order as integers
+            __threadfence();
+            atomicAdd(&sc->arrive2, 1u);
+            if (!(dbg & 1)) norm_spin(&sc->arrive2, (unsigned)k);
+        }
+        __syncthreads();
+        const float scale = fmaxf(__fsqrt_rn(__uint_as_float(__ldcg(&sc->maxd2))), 1e-7f);
+        if (p0 == 0 && tid == 0) {
+            if (centroid_out) { centroid_out[cloud * 3] = cx; centroid_out[cloud * 3 + 1] = cy; centroid_out[cloud * 3 + 2] = cz; }
+            if (scale_out) scale_out[cloud] = scale;
+        }
+        // ---- write back: (x - c) / scale, true divide ----
+        if (y) {
+            float4 *dst = reinterpret_cast<float4 *>(y + (cloud * n + p0) * 3);
+            const NormDiv div(scale);
+            const float c3[3] = {cx, cy, cz};
+            float cu[3][3];                                 // centroid components in the order float4 (tid + (3 m + u) T) sees them
+#pragma unroll
+            for (int u = 0; u < 3; ++u)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const int axis = (r0 + u + j) % 3;
+                    cu[u][j] = axis == 0 ? c3[0] : axis == 1 ? c3[1] : c3[2];
+                }
+            for (int v0 = tid; v0 < ((dbg & 4) ? 0 : nvec); v0 += 3 * T) {
+#pragma unroll
+                for (int u = 0; u < 3; ++u) {
+                    if (v0 + u * T < nvec) {
+                        const float4 q = smem4[v0 + u * T];
+                        dst[v0 + u * T] = make_float4(div(__fsub_rn(q.x, cu[u][0])), div(__fsub_rn(q.y, cu[u][1])), div(__fsub_rn(q.z, cu[u][2])),
+                                                      div(__fsub_rn(q.w, cu[u][0])));
+                    }
+                }
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 philox_normal_kernel(int64_t npoints, uint64_t seed, uint64_t offset, float *__restrict__ out)
 {
@@ -450,6 +630,46 @@ extern "C" int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y,
     if (b == 0) return PCP_OK;
     if (!d_y && n <= 4096 && b >= 64) {
         normalize_stats_warp_kernel<<<(b + 7) / 8, 256, 0, as_stream(stream)>>>(d_x, b, n, d_centroid, d_scale);
+        PCP_CHECK_LAUNCH();
+        return PCP_OK;
+    }
+    const bool aligned = (((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y)) & 15u) == 0) && (n % 4 == 0);
+    if (n >= kNormPartsMin && aligned && b <= 65535) {
+        // per-device scratch ring (48 B per cloud + the ticket): eight calls may be in flight on different streams
+        static char *scratch[64] = {};
+        static int64_t cap[64] = {};
+        static unsigned turn[64] = {};
+        static bool attr_parts = false;
+        int dev = 0;
+        PCP_CUDA_OK(cudaGetDevice(&dev));
+        PCP_REQUIRE(dev >= 0 && dev < 64, PCP_ERR_UNSUPPORTED, "pcp_normalize_f32: device ordinal %d", dev);
+        if (cap[dev] < b) {
+            if (scratch[dev]) PCP_CUDA_OK(cudaFree(scratch[dev]));
+            cap[dev] = std::max<int64_t>(b, 1024);
+            PCP_CUDA_OK(cudaMalloc(&scratch[dev], (size_t)(cap[dev] * sizeof(NormScratch) + 64) * 8));
+        }
+        static int slice_bytes = 0, ctas_per_sm = 0, dbg = 0;
+        if (!attr_parts) {
+            slice_bytes = kNormSliceBytes;
+            if (const char *e = getenv("PCP_NORM_SLICE_KB")) slice_bytes = std::max(4, std::min(200, atoi(e))) * 1024;   // tuning knob
+            PCP_CUDA_OK(cudaFuncSetAttribute(normalize_parts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, slice_bytes + 384));   // two buffers (+ rounding of ppc to 4 points)
+            PCP_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, normalize_parts_kernel, kNormPartThreads, slice_bytes + 384));
+            PCP_REQUIRE(ctas_per_sm >= 1, PCP_ERR_CUDA, "pcp_normalize_f32: slice kernel does not fit an SM");
+            if (const char *e = getenv("PCP_NORM_DBG")) dbg = atoi(e) & 7;
+            attr_parts = true;
+        }
+        const size_t slot_bytes = (size_t)cap[dev] * sizeof(NormScratch) + 64;
+        char *slot = scratch[dev] + (size_t)(turn[dev]++ & 7u) * slot_bytes;
+        unsigned *ticket = reinterpret_cast<unsigned *>(slot);
+        NormScratch *scr = reinterpret_cast<NormScratch *>(slot + 64);
+        cudaStream_t st = as_stream(stream);
+        PCP_CUDA_OK(cudaMemsetAsync(slot, 0, 64 + (size_t)b * sizeof(NormScratch), st));
+        const int k = (int)((n * 12 + slice_bytes - 1) / slice_bytes);
+        // slices start on 128-byte lines when the cloud does (32 points = 384 B): bulk copies of misaligned slices split sectors
+        const int64_t ppc = (((n + k - 1) / k) + 31) & ~(int64_t)31;
+        const int grid = (int)std::min<int64_t>((int64_t)b * k, (int64_t)sm_count() * ctas_per_sm);
+        PCP_REQUIRE(k <= grid, PCP_ERR_UNSUPPORTED, "pcp_normalize_f32: n=%lld needs %d resident slices", (long long)n, k);
+        normalize_parts_kernel<<<grid, kNormPartThreads, (size_t)ppc * 12, st>>>(d_x, b, n, k, ppc, d_y, d_centroid, d_scale, scr, ticket, (unsigned)dbg);
         PCP_CHECK_LAUNCH();
         return PCP_OK;
     }

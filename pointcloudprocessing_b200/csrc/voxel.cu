@@ -235,16 +235,48 @@ struct VoxelGrid {                 // per cloud
 };
 
 __global__ void __launch_bounds__(256)
-voxel_minmax_kernel(const float *__restrict__ x, int64_t n, unsigned *__restrict__ min_enc, unsigned *__restrict__ max_enc)
+voxel_minmax_kernel(const float *__restrict__ x, int64_t n, unsigned *__restrict__ min_enc, unsigned *__restrict__ max_enc, int vec_ok)
 {
     const int64_t cloud = blockIdx.y;
     const float *xc = x + cloud * n * 3;
     const float inf = __int_as_float(0x7f800000);
     float lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (vec_ok) {
+        // lane-contiguous float4 loads; load slot u's component j is axis (u T + gt + j) % 3 on every iteration (stride 3 T)
+        const float4 *x4 = reinterpret_cast<const float4 *>(xc);
+        const int64_t nvec = (n * 3) >> 2, T = (int64_t)gridDim.x * 256, gt = (int64_t)blockIdx.x * 256 + threadIdx.x;
+        float l[3][4], h[3][4];
 #pragma unroll
-        for (int a = 0; a < 3; ++a) { const float v = xc[3 * i + a]; lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v); }
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { l[u][j] = inf; h[u][j] = -inf; }
+        for (int64_t v0 = gt; v0 < nvec; v0 += 3 * T) {
+            float4 q[3];
+#pragma unroll
+            for (int u = 0; u < 3; ++u) q[u] = (v0 + u * T < nvec) ? __ldg(x4 + v0 + u * T) : make_float4(inf, inf, inf, inf);
+#pragma unroll
+            for (int u = 0; u < 3; ++u) {
+                const bool ok = v0 + u * T < nvec;
+                l[u][0] = fminf(l[u][0], q[u].x); l[u][1] = fminf(l[u][1], q[u].y); l[u][2] = fminf(l[u][2], q[u].z); l[u][3] = fminf(l[u][3], q[u].w);
+                if (ok) { h[u][0] = fmaxf(h[u][0], q[u].x); h[u][1] = fmaxf(h[u][1], q[u].y); h[u][2] = fmaxf(h[u][2], q[u].z); h[u][3] = fmaxf(h[u][3], q[u].w); }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int axis = (int)((u * T + gt + j) % 3);
+#pragma unroll
+                for (int a = 0; a < 3; ++a)
+                    if (axis == a) { lo[a] = fminf(lo[a], l[u][j]); hi[a] = fmaxf(hi[a], h[u][j]); }
+            }
+    } else {
+        for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { const float v = xc[3 * i + a]; lo[a] = fminf(lo[a], v); hi[a] = fmaxf(hi[a], v); }
+        }
     }
+    __shared__ float red[2][8][3];
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
 #pragma unroll
@@ -252,10 +284,14 @@ voxel_minmax_kernel(const float *__restrict__ x, int64_t n, unsigned *__restrict
             lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
             hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
         }
-        if ((threadIdx.x & 31) == 0) {
-            atomicMin(min_enc + cloud * 3 + a, enc_f32(lo[a]));
-            atomicMax(max_enc + cloud * 3 + a, enc_f32(hi[a]));
-        }
+        if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5][a] = lo[a]; red[1][threadIdx.x >> 5][a] = hi[a]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        float l = inf, h = -inf;
+        for (int w = 0; w < 8; ++w) { l = fminf(l, red[0][w][threadIdx.x]); h = fmaxf(h, red[1][w][threadIdx.x]); }
+        atomicMin(min_enc + cloud * 3 + threadIdx.x, enc_f32(l));
+        atomicMax(max_enc + cloud * 3 + threadIdx.x, enc_f32(h));
     }
 }
 
@@ -294,52 +330,109 @@ __device__ __forceinline__ long long voxel_cell(const float *p, const VoxelGrid 
     return ((long long)((int)kx - g.kmin[0]) * g.ny + ((int)ky - g.kmin[1])) * g.nz + ((int)kz - g.kmin[2]);
 }
 
+// The fast-path kernels are enqueued right behind voxel_grid_kernel and return at once when it raised *need_sort: the host
+// reads the flag only after everything is queued, so the decision costs no bubble on the device.
+
+// zero the bitmap words the cloud's grid actually uses (the capacity is 32 n cells per cloud)
 __global__ void __launch_bounds__(256)
-voxel_mark_kernel(const float *__restrict__ x, int64_t n, const VoxelGrid *__restrict__ grid, float voxel, long long cap_cells,
-                  unsigned *__restrict__ bitmap, int *__restrict__ bad)
+voxel_clear_kernel(const VoxelGrid *__restrict__ grid, long long cap_cells, unsigned *__restrict__ bitmap, const int *__restrict__ need_sort)
 {
+    if (*need_sort) return;
     const int64_t cloud = blockIdx.y;
-    const VoxelGrid g = grid[cloud];
-    const float *xc = x + cloud * n * 3;
-    unsigned *bm = bitmap + cloud * (cap_cells >> 5);
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const long long vec = (((grid[cloud].cells + 31) >> 5) + 3) >> 2;          // capacity is a multiple of 32 words
+    uint4 *bm = reinterpret_cast<uint4 *>(bitmap + cloud * (cap_cells >> 5));
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < vec; i += (long long)gridDim.x * blockDim.x)
+        bm[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
+// four points per thread from three 16-byte loads when the cloud is 16-byte aligned (n % 4 == 0)
+template <typename F>
+__device__ __forceinline__ void voxel_for_points(const float *__restrict__ xc, int64_t n, int vec_ok, F &&f)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, t0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t ngroups = vec_ok ? (n >> 2) : 0;
+    const float4 *x4 = reinterpret_cast<const float4 *>(xc);
+    for (int64_t g = t0; g < ngroups; g += stride) {
+        const float4 a = __ldg(x4 + 3 * g), b = __ldg(x4 + 3 * g + 1), c = __ldg(x4 + 3 * g + 2);
+        const float p0[3] = {a.x, a.y, a.z}, p1[3] = {a.w, b.x, b.y}, p2[3] = {b.z, b.w, c.x}, p3[3] = {c.y, c.z, c.w};
+        f(4 * g, p0); f(4 * g + 1, p1); f(4 * g + 2, p2); f(4 * g + 3, p3);
+    }
+    for (int64_t i = (ngroups << 2) + t0; i < n; i += stride) {
         const float p[3] = {xc[3 * i], xc[3 * i + 1], xc[3 * i + 2]};
-        bool finite;
-        const long long cell = voxel_cell(p, g, voxel, finite);
-        if (!finite) { bad[cloud] = 1; continue; }
-        atomicOr(bm + (cell >> 5), 1u << (cell & 31));
+        f(i, p);
     }
 }
 
+__global__ void __launch_bounds__(256)
+voxel_mark_kernel(const float *__restrict__ x, int64_t n, const VoxelGrid *__restrict__ grid, float voxel, long long cap_cells,
+                  unsigned *__restrict__ bitmap, int *__restrict__ bad, const int *__restrict__ need_sort, int vec_ok)
+{
+    if (*need_sort) return;
+    const int64_t cloud = blockIdx.y;
+    const VoxelGrid g = grid[cloud];
+    unsigned *bm = bitmap + cloud * (cap_cells >> 5);
+    voxel_for_points(x + cloud * n * 3, n, vec_ok, [&](int64_t, const float *p) {
+        bool finite;
+        const long long cell = voxel_cell(p, g, voxel, finite);
+        if (!finite) { bad[cloud] = 1; return; }
+        // ~8 points share a voxel and ~50 a word: look before the read-modify-write (L2 read, the line may be stale in L1)
+        const unsigned bit = 1u << (cell & 31);
+        if (!(__ldcg(bm + (cell >> 5)) & bit)) atomicOr(bm + (cell >> 5), bit);
+    });
+}
+
 // one CTA per cloud: exclusive popcount scan over the bitmap words -> rank of the first cell of every word; voxel count;
-// accumulators of the occupied voxels zeroed
+// accumulators of the occupied voxels zeroed.  A thread owns eight consecutive words (two 16-byte loads), so one block
+// scan covers 8192 words.
 __global__ void __launch_bounds__(1024)
 voxel_rank_kernel(const unsigned *__restrict__ bitmap, const VoxelGrid *__restrict__ grid, long long cap_cells, int64_t n,
                   unsigned *__restrict__ word_rank, int32_t *__restrict__ nvox, const int *__restrict__ bad, double *__restrict__ sums,
-                  int *__restrict__ cnt)
+                  int *__restrict__ cnt, const int *__restrict__ need_sort)
 {
-    __shared__ unsigned part[1024];
+    if (*need_sort) return;
+    __shared__ unsigned wtot[32];
+    __shared__ unsigned carry_s;
     const int64_t cloud = blockIdx.x;
-    const long long words = (grid[cloud].cells + 31) >> 5;
-    const unsigned *bm = bitmap + cloud * (cap_cells >> 5);
-    unsigned *wr = word_rank + cloud * (cap_cells >> 5);
-    const long long per = (words + 1023) / 1024;
-    const long long beg = threadIdx.x * per, end = min(words, beg + per);
-    unsigned s = 0;
-    for (long long w = beg; w < end; ++w) s += __popc(bm[w]);
-    part[threadIdx.x] = s;
-    __syncthreads();
-    for (int o = 1; o < 1024; o <<= 1) {
-        unsigned v = threadIdx.x >= o ? part[threadIdx.x - o] : 0;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long vec = (((grid[cloud].cells + 31) >> 5) + 3) >> 2;          // uint4 count
+    const uint4 *bm = reinterpret_cast<const uint4 *>(bitmap + cloud * (cap_cells >> 5));
+    uint4 *wr = reinterpret_cast<uint4 *>(word_rank + cloud * (cap_cells >> 5));
+    unsigned carry = 0;
+    for (long long base = 0; base < vec; base += 2048) {
+        const long long i0 = base + 2 * tid;
+        uint4 q0 = make_uint4(0u, 0u, 0u, 0u), q1 = q0;
+        if (i0 < vec) q0 = bm[i0];
+        if (i0 + 1 < vec) q1 = bm[i0 + 1];
+        const unsigned c[8] = {(unsigned)__popc(q0.x), (unsigned)__popc(q0.y), (unsigned)__popc(q0.z), (unsigned)__popc(q0.w),
+                               (unsigned)__popc(q1.x), (unsigned)__popc(q1.y), (unsigned)__popc(q1.z), (unsigned)__popc(q1.w)};
+        unsigned tsum = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) tsum += c[k];
+        unsigned incl = tsum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        if (lane == 31) wtot[warp] = incl;
         __syncthreads();
-        part[threadIdx.x] += v;
+        if (warp == 0) {
+            unsigned w = wtot[lane], wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += v; }
+            wtot[lane] = wi - w;
+            if (lane == 31) carry_s = wi;
+        }
+        __syncthreads();
+        unsigned r = carry + wtot[warp] + incl - tsum;
+        carry += carry_s;
+        unsigned e[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { e[k] = r; r += c[k]; }
+        if (i0 < vec) wr[i0] = make_uint4(e[0], e[1], e[2], e[3]);
+        if (i0 + 1 < vec) wr[i0 + 1] = make_uint4(e[4], e[5], e[6], e[7]);
         __syncthreads();
     }
-    unsigned r = part[threadIdx.x] - s;
-    for (long long w = beg; w < end; ++w) { wr[w] = r; r += __popc(bm[w]); }
-    const unsigned total = part[1023];
-    if (threadIdx.x == 0) nvox[cloud] = bad[cloud] ? -1 : (int32_t)total;
-    for (unsigned v = threadIdx.x; v < total; v += 1024) {
+    const unsigned total = carry;
+    if (tid == 0) nvox[cloud] = bad[cloud] ? -1 : (int32_t)total;
+    for (unsigned v = tid; v < total; v += 1024) {
         double *sp = sums + (cloud * n + v) * 3;
         sp[0] = 0.0; sp[1] = 0.0; sp[2] = 0.0;
         cnt[cloud * n + v] = 0;
@@ -348,28 +441,29 @@ voxel_rank_kernel(const unsigned *__restrict__ bitmap, const VoxelGrid *__restri
 
 __global__ void __launch_bounds__(256)
 voxel_accum_kernel(const float *__restrict__ x, int64_t n, const VoxelGrid *__restrict__ grid, float voxel, long long cap_cells,
-                   const unsigned *__restrict__ bitmap, const unsigned *__restrict__ word_rank, double *__restrict__ sums, int *__restrict__ cnt)
+                   const unsigned *__restrict__ bitmap, const unsigned *__restrict__ word_rank, double *__restrict__ sums, int *__restrict__ cnt,
+                   const int *__restrict__ need_sort, int vec_ok)
 {
+    if (*need_sort) return;
     const int64_t cloud = blockIdx.y;
     const VoxelGrid g = grid[cloud];
-    const float *xc = x + cloud * n * 3;
     const unsigned *bm = bitmap + cloud * (cap_cells >> 5), *wr = word_rank + cloud * (cap_cells >> 5);
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        const float p[3] = {xc[3 * i], xc[3 * i + 1], xc[3 * i + 2]};
+    voxel_for_points(x + cloud * n * 3, n, vec_ok, [&](int64_t, const float *p) {
         bool finite;
         const long long cell = voxel_cell(p, g, voxel, finite);
-        if (!finite) continue;
+        if (!finite) return;
         const unsigned w = __ldg(bm + (cell >> 5));
         const int64_t v = cloud * n + __ldg(wr + (cell >> 5)) + __popc(w & ((1u << (cell & 31)) - 1u));
         atomicAdd(sums + v * 3, (double)p[0]); atomicAdd(sums + v * 3 + 1, (double)p[1]); atomicAdd(sums + v * 3 + 2, (double)p[2]);
         atomicAdd(cnt + v, 1);
-    }
+    });
 }
 
 __global__ void __launch_bounds__(256)
 voxel_finalize_kernel(int64_t n, const int32_t *__restrict__ nvox, const double *__restrict__ sums, const int *__restrict__ cnt,
-                      float *__restrict__ out_xyz, int32_t *__restrict__ out_count)
+                      float *__restrict__ out_xyz, int32_t *__restrict__ out_count, const int *__restrict__ need_sort)
 {
+    if (*need_sort) return;
     const int64_t cloud = blockIdx.y;
     const int nv = max(nvox[cloud], 0);
     for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < n; v += (int64_t)gridDim.x * blockDim.x) {
@@ -456,26 +550,27 @@ extern "C" int pcp_voxel_f32(const float *d_x, int b, int64_t n, const float *h_
         PCP_CUDA_OK(cudaMemsetAsync(w.origin_enc, 0xFF, (size_t)b * 12, st));
         PCP_CUDA_OK(cudaMemsetAsync(w.max_enc, 0, (size_t)b * 12, st));
         PCP_CUDA_OK(cudaMemsetAsync(w.need_sort, 0, 4, st));
-        voxel_minmax_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.origin_enc, w.max_enc);
+        const int vec_ok = ((reinterpret_cast<uintptr_t>(d_x) & 15u) == 0) && (n % 4 == 0);
+        voxel_minmax_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.origin_enc, w.max_enc, vec_ok);
         PCP_CHECK_LAUNCH();
         voxel_grid_kernel<<<(b + 127) / 128, 128, 0, st>>>(w.origin_enc, w.max_enc, b, ox, oy, oz, h_origin ? 0 : 1, voxel, w.cap_cells, w.grid,
                                                           w.need_sort);
         PCP_CHECK_LAUNCH();
+        voxel_clear_kernel<<<dim3(gx, b), 256, 0, st>>>(w.grid, w.cap_cells, w.bitmap, w.need_sort);
+        PCP_CHECK_LAUNCH();
+        voxel_mark_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.bad, w.need_sort, vec_ok);
+        PCP_CHECK_LAUNCH();
+        voxel_rank_kernel<<<b, 1024, 0, st>>>(w.bitmap, w.grid, w.cap_cells, n, w.word_rank, d_nvox, w.bad, w.sums, w.cnt, w.need_sort);
+        PCP_CHECK_LAUNCH();
+        voxel_accum_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.word_rank, w.sums, w.cnt, w.need_sort, vec_ok);
+        PCP_CHECK_LAUNCH();
+        voxel_finalize_kernel<<<dim3(gx, b), 256, 0, st>>>(n, d_nvox, w.sums, w.cnt, d_out_xyz, d_out_count, w.need_sort);
+        PCP_CHECK_LAUNCH();
+        // the flag is read once everything is queued: the wait overlaps the kernels instead of stalling the stream mid-way
         int need_sort = 0;
         PCP_CUDA_OK(cudaMemcpyAsync(&need_sort, w.need_sort, 4, cudaMemcpyDeviceToHost, st));
         PCP_CUDA_OK(cudaStreamSynchronize(st));
-        if (!need_sort) {
-            PCP_CUDA_OK(cudaMemsetAsync(w.bitmap, 0, (size_t)b * (size_t)(w.cap_cells >> 3), st));
-            voxel_mark_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.bad);
-            PCP_CHECK_LAUNCH();
-            voxel_rank_kernel<<<b, 1024, 0, st>>>(w.bitmap, w.grid, w.cap_cells, n, w.word_rank, d_nvox, w.bad, w.sums, w.cnt);
-            PCP_CHECK_LAUNCH();
-            voxel_accum_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.word_rank, w.sums, w.cnt);
-            PCP_CHECK_LAUNCH();
-            voxel_finalize_kernel<<<dim3(gx, b), 256, 0, st>>>(n, d_nvox, w.sums, w.cnt, d_out_xyz, d_out_count);
-            PCP_CHECK_LAUNCH();
-            return PCP_OK;
-        }
+        if (!need_sort) return PCP_OK;
     }
     // ---- general path: sort ----
     if (!h_origin) {

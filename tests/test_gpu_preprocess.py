@@ -18,7 +18,8 @@ def _ulp_err(a, ref, scale):
     return np.abs(a.astype(np.float64) - ref.astype(np.float64)).max() / (np.finfo(np.float32).eps * scale)
 
 
-@pytest.mark.parametrize("b,n", [(32, 1024), (8, 8192), (3, 1000), (5, 37), (2, 100000), (1, 1), (64, 2048)])
+# (2, 100000), (160, 16384), (3, 40000): the ticketed slice kernel (one round / more tickets than resident CTAs / uneven last slice)
+@pytest.mark.parametrize("b,n", [(32, 1024), (8, 8192), (3, 1000), (5, 37), (2, 100000), (1, 1), (64, 2048), (160, 16384), (3, 40000), (2, 16386)])
 def test_normalize_matches_oracle(lib, b, n):
     from pointcloudprocessing_b200 import ops
     x = synth.gaussian_clouds(1001 + n, b, n)
@@ -32,6 +33,19 @@ def test_normalize_matches_oracle(lib, b, n):
     assert _ulp_err(y.cpu().numpy(), ry, 1.0) <= max(tol_ulps, 4.0)
     if n > 1:
         assert np.array_equal(y.cpu().numpy(), ry) or _ulp_err(y.cpu().numpy(), ry, 1.0) <= max(tol_ulps, 4.0)
+
+
+@pytest.mark.parametrize("b,n", [(2, 100000), (24, 16384), (4, 8192)])
+def test_normalize_write_is_the_true_divide_of_its_own_statistics(lib, b, n):
+    """PointNet.py:703-704: (x - centroid) / scale with IEEE subtract and divide — bit for bit given the kernel's own centroid
+    and scale (the slice kernel divides through a corrected reciprocal; this pins it to the correctly rounded quotient)."""
+    from pointcloudprocessing_b200 import ops
+    x = synth.gaussian_clouds(99 + n, b, n)
+    x[0, :64] = x[0, 0]                                       # exact zeros after centring are fine; tiny quotients too
+    x[-1, 5] *= np.float32(1e-6)
+    y, (c, s) = ops.normalize(_dev(x), return_stats=True)
+    c, s = c.cpu().numpy().reshape(b, 1, 3), s.cpu().numpy().reshape(b, 1, 1)
+    assert np.array_equal(y.cpu().numpy(), (x - c) / s)
 
 
 def test_normalize_degenerate(lib):
