@@ -9,6 +9,8 @@
 // peer, one cluster barrier.  Ties resolve to the lowest index (np.argmax).
 #include <cooperative_groups.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace cg = cooperative_groups;
@@ -20,9 +22,9 @@ constexpr int kFpsWarps = kFpsThreads / 32;
 constexpr int kFpsMaxCluster = 16;
 
 struct __align__(16) FpsRec {
+    float x, y, z, pad;       // one 16-byte read for the winner's coordinates
     unsigned long long key;   // (float bits of min-distance << 32) | (0xFFFFFFFF - point index)
-    float x, y, z;
-    float pad;
+    unsigned long long pad2;
 };
 
 __device__ __forceinline__ float sqdist_nofma(float px, float py, float pz, float cx, float cy, float cz) {
@@ -30,11 +32,15 @@ __device__ __forceinline__ float sqdist_nofma(float px, float py, float pz, floa
     return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
 }
 
-template <int PPT>
+// phase cycle totals of block 0 / thread 0 (development aid, read through pcp_fps_phase_cycles)
+__device__ unsigned long long g_fps_phase[8];
+#define FPS_STAMP(i) do { if (kProf && blockIdx.x == 0 && tid == 0) { const long long t_ = clock64(); ph[i] += t_ - tprev; tprev = t_; } } while (0)
+
+template <int PPT, bool kProf>
 __global__ void __launch_bounds__(kFpsThreads, 1)
 fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int32_t *__restrict__ idx_out, int cs, int64_t ppc)
 {
-    __shared__ FpsRec warp_rec[kFpsWarps];
+    __shared__ unsigned long long warp_key[kFpsWarps];
     __shared__ FpsRec slots[2][kFpsMaxCluster];
 
     cg::cluster_group cluster = cg::this_cluster();
@@ -60,58 +66,68 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
     float cx = __ldg(xc + 3 * (int64_t)start), cy = __ldg(xc + 3 * (int64_t)start + 1), cz = __ldg(xc + 3 * (int64_t)start + 2);
     if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
 
+    long long ph[6] = {0, 0, 0, 0, 0, 0}, tprev = clock64();
     for (int it = 1; it < s; ++it) {
-        float best = 0.f;
+        // distance update with the thread's arg-max carried along (strict > keeps the lowest k = lowest index; padding sits at
+        // the highest k with d = 0, so it only "wins" a thread that holds no real point)
+        float best = -1.f;
+        int bk = 0;
 #pragma unroll
         for (int k = 0; k < PPT; ++k) {
             const float dd = sqdist_nofma(px[k], py[k], pz[k], cx, cy, cz);
             d[k] = fminf(d[k], dd);
-            best = fmaxf(best, d[k]);
+            if (d[k] > best) { best = d[k]; bk = k; }
         }
+        FPS_STAMP(0);
         const unsigned bb = __float_as_uint(best);
         const unsigned wmax = __reduce_max_sync(0xffffffffu, bb);
-        unsigned cand = 0xFFFFFFFFu;
-        float qx = 0.f, qy = 0.f, qz = 0.f;
-        if (bb == wmax) {
-#pragma unroll
-            for (int k = PPT - 1; k >= 0; --k) {
-                const int64_t gi = p0 + (int64_t)k * kFpsThreads + tid;
-                if (__float_as_uint(d[k]) == wmax && gi < lim) { cand = (unsigned)gi; qx = px[k]; qy = py[k]; qz = pz[k]; }
-            }
-        }
+        const int64_t gi = p0 + (int64_t)bk * kFpsThreads + tid;
+        const unsigned cand = (bb == wmax && gi < lim) ? (unsigned)gi : 0xFFFFFFFFu;
         const unsigned wmin = __reduce_min_sync(0xffffffffu, cand);
-        if (wmin == 0xFFFFFFFFu) {
-            if (lane == 0) { FpsRec r; r.key = ((unsigned long long)wmax << 32); r.x = r.y = r.z = r.pad = 0.f; warp_rec[warp] = r; }
-        } else if (cand == wmin) {
-            FpsRec r; r.key = ((unsigned long long)wmax << 32) | (unsigned long long)(0xFFFFFFFFu - wmin);
-            r.x = qx; r.y = qy; r.z = qz; r.pad = 0.f;
-            warp_rec[warp] = r;
-        }
+        if (lane == 0) warp_key[warp] = ((unsigned long long)wmax << 32) | (unsigned long long)(0xFFFFFFFFu - wmin);   // low word 0: no real point
+        FPS_STAMP(1);
         __syncthreads();
+        FPS_STAMP(2);
         const int par = it & 1;
-        if (warp == 0) {
-            const unsigned long long key = lane < kFpsWarps ? warp_rec[lane].key : 0ull;
+        {
+            // every warp reduces the 16 warp keys itself (no second barrier); the one thread that owns the block's winner
+            // fetches its coordinates and pushes the record into every CTA of the cluster
+            const unsigned long long key = lane < kFpsWarps ? warp_key[lane] : 0ull;
             const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
             const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
             const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
-            const unsigned win = __ballot_sync(0xffffffffu, lane < kFpsWarps && hi == mhi && lo == mlo);
-            if (lane == __ffs(win) - 1) {
-                const FpsRec r = warp_rec[lane];
+            const bool mine = mlo != 0u && cand == 0xFFFFFFFFu - mlo;
+            if (mine || (mlo == 0u && tid == 0)) {
+                FpsRec r;
+                r.key = ((unsigned long long)mhi << 32) | mlo;
+                r.x = r.y = r.z = r.pad = 0.f;
+                if (mine) {
+#pragma unroll
+                    for (int k = 0; k < PPT; ++k)
+                        if (k == bk) { r.x = px[k]; r.y = py[k]; r.z = pz[k]; }
+                }
                 if (cs == 1) slots[par][0] = r;
                 else
                     for (int t = 0; t < cs; ++t) *cluster.map_shared_rank(&slots[par][rank], t) = r;
             }
         }
+        FPS_STAMP(3);
         if (cs == 1) __syncthreads(); else cluster.sync();
-        unsigned long long bk = slots[par][0].key;
-        int br = 0;
-        for (int t = 1; t < cs; ++t) {
-            const unsigned long long k2 = slots[par][t].key;
-            if (k2 > bk) { bk = k2; br = t; }
+        FPS_STAMP(4);
+        {
+            const unsigned long long key = lane < cs ? slots[par][lane].key : 0ull;
+            const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+            const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+            const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
+            const int br = __ffs(__ballot_sync(0xffffffffu, lane < cs && hi == mhi && lo == mlo)) - 1;
+            const float4 w = *reinterpret_cast<const float4 *>(&slots[par][br].x);
+            cx = w.x; cy = w.y; cz = w.z;
+            if (rank == 0 && tid == 0) idx_out[cloud * s + it] = (int32_t)(0xFFFFFFFFu - mlo);
         }
-        cx = slots[par][br].x; cy = slots[par][br].y; cz = slots[par][br].z;
-        if (rank == 0 && tid == 0) idx_out[cloud * s + it] = (int32_t)(0xFFFFFFFFu - (unsigned)bk);
+        FPS_STAMP(5);
     }
+    if (kProf && blockIdx.x == 0 && tid == 0)
+        for (int i = 0; i < 6; ++i) g_fps_phase[i] = (unsigned long long)ph[i];
     if (cs > 1) cluster.sync();    // no CTA may exit while a peer can still write into its slots
 }
 
@@ -163,12 +179,12 @@ fps_stream_kernel(const float *__restrict__ x, int64_t n, int s, int start, int3
     }
 }
 
-template <int PPT>
+template <int PPT, bool kProf = false>
 static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, int cs, int64_t ppc, cudaStream_t st)
 {
     static bool attr_set = false;
     if (!attr_set) {
-        PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
@@ -180,7 +196,7 @@ static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int3
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, fps_cluster_kernel<PPT>, d_x, n, s, start, d_idx, cs, ppc));
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, fps_cluster_kernel<PPT, kProf>, d_x, n, s, start, d_idx, cs, ppc));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -227,5 +243,16 @@ extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start,
     if (ppt <= 13) return launch_fps<13>(d_x, b, n, s, start, d_idx, cs, ppc, st);
     if (ppt <= 16) return launch_fps<16>(d_x, b, n, s, start, d_idx, cs, ppc, st);
     if (ppt <= 20) return launch_fps<20>(d_x, b, n, s, start, d_idx, cs, ppc, st);
+    static const bool prof = getenv("PCP_FPS_PROF") != nullptr;
+    if (prof) return launch_fps<25, true>(d_x, b, n, s, start, d_idx, cs, ppc, st);
     return launch_fps<25>(d_x, b, n, s, start, d_idx, cs, ppc, st);
+}
+
+/* development aid: cycles block 0 / thread 0 of the last PCP_FPS_PROF=1 launch (PPT = 25) spent in: distance loop, candidate
+ * search + record, __syncthreads, warp-0 stage + DSMEM pushes, cluster barrier, slot read-back */
+extern "C" int pcp_fps_phase_cycles(unsigned long long out[6])
+{
+    PCP_CUDA_OK(cudaDeviceSynchronize());
+    PCP_CUDA_OK(cudaMemcpyFromSymbol(out, g_fps_phase, 6 * sizeof(unsigned long long)));
+    return PCP_OK;
 }

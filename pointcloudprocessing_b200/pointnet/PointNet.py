@@ -318,6 +318,13 @@ class PointNet:
         p = Path(path)
         np.savez(p.with_suffix(".npz") if p.suffix != ".npz" else p, __config__=json.dumps(self.get_config()), **self.get_weights_dict())
 
+    def export_onnx(self, path: str, input_width: int) -> str:
+        """The opset-13 inference graph `tf2onnx.convert.from_keras(model, [(None, input_width, 3) f32], opset=13)` would
+        give (pointnet_train.py:237-247), written without onnx / tf2onnx — see pointnet/onnx_export.py."""
+        from . import onnx_export
+        return onnx_export.export_onnx(path, self.get_weights_dict(), self._classification_output_width, self._segmentation_output_width,
+                                       int(input_width), vanilla=self._vanilla)
+
     @classmethod
     def load(cls, path: str, **overrides):
         z = np.load(path, allow_pickle=False)

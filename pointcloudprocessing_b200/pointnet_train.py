@@ -8,8 +8,7 @@ copy, the best checkpoint) — driving the sm_100a kernels of libpcp_b200.so ins
 
 Positions on the reference's quirks: q3 `params.vanilla` defaults to false when absent; q11 a named logger
 and a portable log-file timestamp; checkpoints are this package's `.npz` container (the reference's `.keras` zip needs
-h5py, absent here) and the ONNX export (pointnet_train.py:238-248) is out of scope — both are logged, not silently
-skipped.  Under torchrun every rank trains on its own shard of each batch and rank 0 writes the artefacts.
+h5py, absent here); the ONNX export (:237-247) is written by pointnet/onnx_export.py without onnx / tf2onnx.  Under torchrun every rank trains on its own shard of each batch and rank 0 writes the artefacts.
 """
 from __future__ import annotations
 
@@ -204,7 +203,9 @@ class TrainProfile:
                     json.dump(history.history, j)
                 if not os.path.isfile(ckpt):
                     model.save(ckpt)
-                self._log.info("ONNX export (pointnet_train.py:238-248) is out of scope of this build; weights are in the .npz checkpoint")
+                onnx_path = f"{self._model_path}{P['path']}{self._name}_{prof}.onnx"                # :237-247, opset 13, (None, n, 3) f32
+                model.export_onnx(onnx_path, self._input_width)
+                self._log.info(f"ONNX model written to {onnx_path}")
                 shutil.copy(self._config_file, f"{self._model_path}{P['path']}")
             self._pretrained_model = f"{P['path']}{self._name}_{prof}.npz"                   # the next profile continues from this one (:257)
 

@@ -53,6 +53,13 @@ def test_train_pointnet_driver_two_profiles(lib, tmp_path):
     m = PointNet.load(str(base / "final" / "unit_lidar_final.npz"))
     cls, seg, R = m(np.zeros((2, 128, 3), np.float32) + rng.standard_normal((2, 128, 3)).astype(np.float32))
     assert cls.shape == (2, 3) and seg.shape == (2, 128, 4) and np.allclose(seg.sum(-1), 1, atol=1e-4)
+    # the ONNX artefact (pointnet_train.py:237-247) holds the same network: executed by the independent reader it gives the model's outputs
+    from oracle import onnx_eval
+    xs = rng.standard_normal((2, 128, 3)).astype(np.float32)
+    got = onnx_eval.run(onnx_eval.load((base / "final" / "unit_lidar_final.onnx").read_bytes()), {"pointnet_input": xs})
+    cls, seg, R = m(xs)
+    for a_, b_ in ((got["classification_output"], cls), (got["segmentation_output"], seg), (got["se3"], R)):
+        assert np.abs(a_ - np.asarray(b_)).max() <= 2e-2 * max(1.0, np.abs(a_).max())
     # a second run reuses the existing PointCloudSets (pointnet_train.py:146-150)
     tp = pointnet_train.TrainProfile(str(cf))
     assert tp._training_profiles["final"]["pc"]._data_size["train"]["count"] == 30
