@@ -12,6 +12,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "umma.cuh"
 
 namespace cg = cooperative_groups;
 
@@ -32,13 +33,91 @@ __device__ __forceinline__ float sqdist_nofma(float px, float py, float pz, floa
     return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
 }
 
+// Cluster barrier halves.  Only the warp that pushed records has anything to release; a release fence in the other fifteen
+// warps of every CTA costs ~1000 cycles per iteration for nothing.
+__device__ __forceinline__ void fps_arrive(bool pushed)
+{
+    if (pushed) asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    else asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void fps_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
+// 16 bytes into CTA `cta`'s copy of a shared location, completing 16 bytes of the transaction count of its copy of `bar`
+__device__ __forceinline__ void fps_st_async16(const void *local_dst, const uint64_t *local_bar, uint32_t cta, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+{
+    asm volatile("{\n\t.reg .b32 ra, rb;\n\tmapa.shared::cluster.u32 ra, %0, %2;\n\tmapa.shared::cluster.u32 rb, %1, %2;\n\t"
+                 "st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [ra], {%3, %4, %5, %6}, [rb];\n\t}"
+                 ::"r"(umma::smem_u32(local_dst)), "r"(umma::smem_u32(local_bar)), "r"(cta), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+struct FpsSide {                       // block-level exchange state of a cloud
+    uint64_t *xbar;                    // [2] one transaction barrier per slot parity (nullptr: hardware cluster barrier)
+    unsigned long long *warp_key;      // [kFpsWarps]
+    FpsRec (*slots)[kFpsMaxCluster];   // [2][kFpsMaxCluster]
+};
+
+// after the thread's (best, cand) is known: warp keys -> (caller syncs the block) -> push of the block's winner
+__device__ __forceinline__ void fps_warp_key(const FpsSide &S, unsigned bb, bool real, unsigned gi, unsigned &cand, int lane, int warp)
+{
+    const unsigned wmax = __reduce_max_sync(0xffffffffu, bb);
+    cand = (bb == wmax && real) ? gi : 0xFFFFFFFFu;
+    const unsigned wmin = __reduce_min_sync(0xffffffffu, cand);
+    if (lane == 0) S.warp_key[warp] = ((unsigned long long)wmax << 32) | (unsigned long long)(0xFFFFFFFFu - wmin);
+}
+
+template <typename Coord>
+__device__ __forceinline__ bool fps_push(const FpsSide &S, cg::cluster_group &cluster, int par, int rank, int cs, unsigned cand, int tid, int lane,
+                                         Coord &&coord)
+{
+    const unsigned long long key = lane < kFpsWarps ? S.warp_key[lane] : 0ull;
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
+    const bool mine = mlo != 0u && cand == 0xFFFFFFFFu - mlo;
+    // the warp that holds the winner (warp 0 when the slice has no real point) pushes: lane t writes CTA t's slot
+    const unsigned owner = __ballot_sync(0xffffffffu, mine || (mlo == 0u && tid == 0));
+    if (owner) {
+        FpsRec r;
+        r.key = ((unsigned long long)mhi << 32) | mlo;
+        r.x = r.y = r.z = r.pad = 0.f;
+        r.pad2 = 0ull;
+        if (mine) coord(r);
+        const int src = __ffs(owner) - 1;
+        r.x = __shfl_sync(0xffffffffu, r.x, src); r.y = __shfl_sync(0xffffffffu, r.y, src); r.z = __shfl_sync(0xffffffffu, r.z, src);
+        if (cs == 1) { if (lane == 0) S.slots[par][0] = r; }
+        else if (lane < cs) {
+            if (S.xbar) {
+                // data and its arrival in one remote operation: the receiver's barrier completes when all cs records are in
+                FpsRec *dst = &S.slots[par][rank];
+                fps_st_async16(&dst->x, &S.xbar[par], (uint32_t)lane, __float_as_uint(r.x), __float_as_uint(r.y), __float_as_uint(r.z), 0u);
+                fps_st_async16(&dst->key, &S.xbar[par], (uint32_t)lane, mlo, mhi, 0u, 0u);
+            } else {
+                *cluster.map_shared_rank(&S.slots[par][rank], lane) = r;
+            }
+        }
+    }
+    return owner != 0u;
+}
+
+__device__ __forceinline__ unsigned fps_winner(const FpsSide &S, int par, int cs, int lane, float &cx, float &cy, float &cz)
+{
+    const unsigned long long key = lane < cs ? S.slots[par][lane].key : 0ull;
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
+    const int br = __ffs(__ballot_sync(0xffffffffu, lane < cs && hi == mhi && lo == mlo)) - 1;
+    const float4 w = *reinterpret_cast<const float4 *>(&S.slots[par][br].x);
+    cx = w.x; cy = w.y; cz = w.z;
+    return 0xFFFFFFFFu - mlo;
+}
+
 // phase cycle totals of block 0 / thread 0 (development aid, read through pcp_fps_phase_cycles)
 __device__ unsigned long long g_fps_phase[8];
 #define FPS_STAMP(i) do { if (kProf && blockIdx.x == 0 && tid == 0) { const long long t_ = clock64(); ph[i] += t_ - tprev; tprev = t_; } } while (0)
 
 template <int PPT, bool kProf>
 __global__ void __launch_bounds__(kFpsThreads, 1)
-fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int32_t *__restrict__ idx_out, int cs, int64_t ppc)
+fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int32_t *__restrict__ idx_out, int cs, int64_t ppc, int hw_barrier)
 {
     __shared__ unsigned long long warp_key[kFpsWarps];
     __shared__ FpsRec slots[2][kFpsMaxCluster];
@@ -66,6 +145,18 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
     float cx = __ldg(xc + 3 * (int64_t)start), cy = __ldg(xc + 3 * (int64_t)start + 1), cz = __ldg(xc + 3 * (int64_t)start + 2);
     if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
 
+    // exchange: records travel as st.async with the arrival attached (one DSMEM trip + a local mbarrier wake-up) instead of
+    // remote stores + the hardware cluster barrier (~1300 cycles per iteration, profiles/r01_fps_phases.txt)
+    __shared__ uint64_t xbar[2];
+    const bool use_xbar = cs > 1 && !hw_barrier;
+    const FpsSide SS{use_xbar ? xbar : nullptr, warp_key, slots};
+    uint32_t xph[2] = {0u, 0u};
+    if (use_xbar) {
+        if (tid == 0) { umma::mbar_init(&xbar[0], 1); umma::mbar_init(&xbar[1], 1); umma::fence_barrier_init(); }
+        __syncthreads();
+        if (tid == 0) { umma::mbar_arrive_expect_tx(&xbar[0], cs * 32u); umma::mbar_arrive_expect_tx(&xbar[1], cs * 32u); }
+        cluster.sync();                                     // every CTA is armed before anybody pushes
+    }
     long long ph[6] = {0, 0, 0, 0, 0, 0}, tprev = clock64();
     for (int it = 1; it < s; ++it) {
         // distance update with the thread's arg-max carried along (strict > keeps the lowest k = lowest index; padding sits at
@@ -89,30 +180,21 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
         __syncthreads();
         FPS_STAMP(2);
         const int par = it & 1;
-        {
-            // every warp reduces the 16 warp keys itself (no second barrier); the one thread that owns the block's winner
-            // fetches its coordinates and pushes the record into every CTA of the cluster
-            const unsigned long long key = lane < kFpsWarps ? warp_key[lane] : 0ull;
-            const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
-            const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
-            const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
-            const bool mine = mlo != 0u && cand == 0xFFFFFFFFu - mlo;
-            if (mine || (mlo == 0u && tid == 0)) {
-                FpsRec r;
-                r.key = ((unsigned long long)mhi << 32) | mlo;
-                r.x = r.y = r.z = r.pad = 0.f;
-                if (mine) {
+        // every warp reduces the 16 warp keys itself (no second barrier); the warp that owns the block's winner fetches its
+        // coordinates and pushes the record into every CTA of the cluster (lane t -> CTA t)
+        const bool pushed = fps_push(SS, cluster, par, rank, cs, cand, tid, lane, [&](FpsRec &r) {
 #pragma unroll
-                    for (int k = 0; k < PPT; ++k)
-                        if (k == bk) { r.x = px[k]; r.y = py[k]; r.z = pz[k]; }
-                }
-                if (cs == 1) slots[par][0] = r;
-                else
-                    for (int t = 0; t < cs; ++t) *cluster.map_shared_rank(&slots[par][rank], t) = r;
-            }
-        }
+            for (int k = 0; k < PPT; ++k)
+                if (k == bk) { r.x = px[k]; r.y = py[k]; r.z = pz[k]; }
+        });
         FPS_STAMP(3);
-        if (cs == 1) __syncthreads(); else cluster.sync();
+        if (cs == 1) __syncthreads();
+        else if (use_xbar) {
+            umma::mbar_wait_cluster(&xbar[par], xph[par], 72);
+            xph[par] ^= 1u;
+            // re-arm for iteration it + 2: no peer can push that early (it needs our it + 1 push, which follows this)
+            if (tid == 0 && it + 2 < s) umma::mbar_arrive_expect_tx(&xbar[par], cs * 32u);
+        } else { fps_arrive(pushed); fps_wait(); }
         FPS_STAMP(4);
         {
             const unsigned long long key = lane < cs ? slots[par][lane].key : 0ull;
@@ -196,7 +278,8 @@ static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int3
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, fps_cluster_kernel<PPT, kProf>, d_x, n, s, start, d_idx, cs, ppc));
+    static const int hw_barrier = getenv("PCP_FPS_HW_BARRIER") != nullptr;          // the previous exchange, kept for comparison
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, fps_cluster_kernel<PPT, kProf>, d_x, n, s, start, d_idx, cs, ppc, hw_barrier));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -250,9 +333,9 @@ extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start,
 
 /* development aid: cycles block 0 / thread 0 of the last PCP_FPS_PROF=1 launch (PPT = 25) spent in: distance loop, candidate
  * search + record, __syncthreads, warp-0 stage + DSMEM pushes, cluster barrier, slot read-back */
-extern "C" int pcp_fps_phase_cycles(unsigned long long out[6])
+extern "C" int pcp_fps_phase_cycles(unsigned long long out[8])
 {
     PCP_CUDA_OK(cudaDeviceSynchronize());
-    PCP_CUDA_OK(cudaMemcpyFromSymbol(out, g_fps_phase, 6 * sizeof(unsigned long long)));
+    PCP_CUDA_OK(cudaMemcpyFromSymbol(out, g_fps_phase, 8 * sizeof(unsigned long long)));
     return PCP_OK;
 }

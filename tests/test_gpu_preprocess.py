@@ -123,7 +123,8 @@ def test_resize_to_width(lib):
             assert idx.min() >= 0 and idx.max() < N and len(np.unique(idx)) > min(N, 500 - N) // 4
 
 
-@pytest.mark.parametrize("b,n,s", [(4, 1000, 64), (2, 20000, 128), (3, 4096, 256), (1, 7, 7), (2, 70000, 32)])
+# (75, 20000, 24) / (76, 20000, 1): more clusters than SMs -> two clouds per cluster (registers + shared memory), odd / even batch
+@pytest.mark.parametrize("b,n,s", [(4, 1000, 64), (2, 20000, 128), (3, 4096, 256), (1, 7, 7), (2, 70000, 32), (75, 20000, 24), (76, 20000, 1)])
 def test_fps_bit_exact(lib, b, n, s):
     from pointcloudprocessing_b200 import ops
     x = synth.lidar_scans(2002 + n, b, n, dup_frac=0.02)
