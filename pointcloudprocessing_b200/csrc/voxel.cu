@@ -371,14 +371,38 @@ voxel_mark_kernel(const float *__restrict__ x, int64_t n, const VoxelGrid *__res
     const int64_t cloud = blockIdx.y;
     const VoxelGrid g = grid[cloud];
     unsigned *bm = bitmap + cloud * (cap_cells >> 5);
-    voxel_for_points(x + cloud * n * 3, n, vec_ok, [&](int64_t, const float *p) {
+    // ~8 points share a voxel and ~50 a word: look before the read-modify-write (L2 read, the line may be stale in L1).  The
+    // four look-ups of a thread's points are issued together — behind each other's atomics they would be four serial L2
+    // round trips (long-scoreboard stalls were 27 of 40 issue slots, profiles/r01_preproc_ncu_v10.txt).
+    const float *xc = x + cloud * n * 3;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, t0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t ngroups = vec_ok ? (n >> 2) : 0;
+    const float4 *x4 = reinterpret_cast<const float4 *>(xc);
+    for (int64_t gq = t0; gq < ngroups; gq += stride) {
+        const float4 a = __ldg(x4 + 3 * gq), b4 = __ldg(x4 + 3 * gq + 1), c = __ldg(x4 + 3 * gq + 2);
+        const float p[4][3] = {{a.x, a.y, a.z}, {a.w, b4.x, b4.y}, {b4.z, b4.w, c.x}, {c.y, c.z, c.w}};
+        long long cell[4];
+        bool fin[4];
+        unsigned w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) cell[j] = voxel_cell(p[j], g, voxel, fin[j]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w[j] = fin[j] ? __ldcg(bm + (cell[j] >> 5)) : 0xFFFFFFFFu;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (!fin[j]) { bad[cloud] = 1; continue; }
+            const unsigned bit = 1u << (cell[j] & 31);
+            if (!(w[j] & bit)) atomicOr(bm + (cell[j] >> 5), bit);
+        }
+    }
+    for (int64_t i = (ngroups << 2) + t0; i < n; i += stride) {
+        const float p[3] = {xc[3 * i], xc[3 * i + 1], xc[3 * i + 2]};
         bool finite;
         const long long cell = voxel_cell(p, g, voxel, finite);
-        if (!finite) { bad[cloud] = 1; return; }
-        // ~8 points share a voxel and ~50 a word: look before the read-modify-write (L2 read, the line may be stale in L1)
+        if (!finite) { bad[cloud] = 1; continue; }
         const unsigned bit = 1u << (cell & 31);
         if (!(__ldcg(bm + (cell >> 5)) & bit)) atomicOr(bm + (cell >> 5), bit);
-    });
+    }
 }
 
 // one CTA per cloud: exclusive popcount scan over the bitmap words -> rank of the first cell of every word; voxel count;
@@ -433,30 +457,70 @@ voxel_rank_kernel(const unsigned *__restrict__ bitmap, const VoxelGrid *__restri
     const unsigned total = carry;
     if (tid == 0) nvox[cloud] = bad[cloud] ? -1 : (int32_t)total;
     for (unsigned v = tid; v < total; v += 1024) {
-        double *sp = sums + (cloud * n + v) * 3;
-        sp[0] = 0.0; sp[1] = 0.0; sp[2] = 0.0;
-        cnt[cloud * n + v] = 0;
+        double4 *sp = reinterpret_cast<double4 *>(sums) + (cloud * n + v);          // {sum x, sum y, sum z, count}: one 32-byte sector
+        *sp = make_double4(0.0, 0.0, 0.0, 0.0);
     }
 }
 
+// A voxel's accumulators {sum x, sum y, sum z, count} fill one 32-byte sector, and the four reductions of a point are
+// issued by four neighbouring lanes of ONE instruction: the L2 sees a quarter of the sector operations that per-thread
+// atomicAdds (one instruction per component, 32 sectors each) generate — the kernel was bound by exactly that
+// (lts__throughput 66 %, lg_throttle + long_scoreboard 75 of 80 stalled slots, profiles/r01_preproc_ncu_v10.txt).
 __global__ void __launch_bounds__(256)
 voxel_accum_kernel(const float *__restrict__ x, int64_t n, const VoxelGrid *__restrict__ grid, float voxel, long long cap_cells,
                    const unsigned *__restrict__ bitmap, const unsigned *__restrict__ word_rank, double *__restrict__ sums, int *__restrict__ cnt,
                    const int *__restrict__ need_sort, int vec_ok)
 {
     if (*need_sort) return;
+    (void)cnt;
+    __shared__ float4 tile[8][128];                         // per warp: {x, y, z, voxel rank bits} of 128 points
     const int64_t cloud = blockIdx.y;
     const VoxelGrid g = grid[cloud];
     const unsigned *bm = bitmap + cloud * (cap_cells >> 5), *wr = word_rank + cloud * (cap_cells >> 5);
-    voxel_for_points(x + cloud * n * 3, n, vec_ok, [&](int64_t, const float *p) {
+    const float *xc = x + cloud * n * 3;
+    double *acc = sums + cloud * n * 4;
+    const int lane = threadIdx.x & 31;
+    float4 *tw = tile[threadIdx.x >> 5];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x, t0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t ngroups = vec_ok ? (n >> 2) : 0, nfull = (ngroups + 31) & ~(int64_t)31;      // whole warps stay in the loop together
+    const float4 *x4 = reinterpret_cast<const float4 *>(xc);
+    auto rank_of = [&](const float *p) -> unsigned {
         bool finite;
         const long long cell = voxel_cell(p, g, voxel, finite);
-        if (!finite) return;
+        if (!finite) return 0xFFFFFFFFu;
         const unsigned w = __ldg(bm + (cell >> 5));
-        const int64_t v = cloud * n + __ldg(wr + (cell >> 5)) + __popc(w & ((1u << (cell & 31)) - 1u));
-        atomicAdd(sums + v * 3, (double)p[0]); atomicAdd(sums + v * 3 + 1, (double)p[1]); atomicAdd(sums + v * 3 + 2, (double)p[2]);
-        atomicAdd(cnt + v, 1);
-    });
+        return __ldg(wr + (cell >> 5)) + __popc(w & ((1u << (cell & 31)) - 1u));
+    };
+    for (int64_t gq = t0; gq < nfull; gq += stride) {
+        float p[4][3] = {};
+        unsigned v[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
+        if (gq < ngroups) {
+            const float4 a = __ldg(x4 + 3 * gq), b4 = __ldg(x4 + 3 * gq + 1), c = __ldg(x4 + 3 * gq + 2);
+            p[0][0] = a.x; p[0][1] = a.y; p[0][2] = a.z; p[1][0] = a.w; p[1][1] = b4.x; p[1][2] = b4.y;
+            p[2][0] = b4.z; p[2][1] = b4.w; p[2][2] = c.x; p[3][0] = c.y; p[3][1] = c.z; p[3][2] = c.w;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = rank_of(p[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tw[j * 32 + lane] = make_float4(p[j][0], p[j][1], p[j][2], __uint_as_float(v[j]));
+        __syncwarp();
+        const int comp = lane & 3;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+            const float4 e = tw[q * 8 + (lane >> 2)];
+            const unsigned vv = __float_as_uint(e.w);
+            const double val = comp == 0 ? (double)e.x : comp == 1 ? (double)e.y : comp == 2 ? (double)e.z : 1.0;
+            if (vv != 0xFFFFFFFFu) atomicAdd(acc + (int64_t)vv * 4 + comp, val);
+        }
+        __syncwarp();
+    }
+    for (int64_t i = (ngroups << 2) + t0; i < n; i += stride) {
+        const float p[3] = {xc[3 * i], xc[3 * i + 1], xc[3 * i + 2]};
+        const unsigned vv = rank_of(p);
+        if (vv == 0xFFFFFFFFu) continue;
+        atomicAdd(acc + (int64_t)vv * 4, (double)p[0]); atomicAdd(acc + (int64_t)vv * 4 + 1, (double)p[1]);
+        atomicAdd(acc + (int64_t)vv * 4 + 2, (double)p[2]); atomicAdd(acc + (int64_t)vv * 4 + 3, 1.0);
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -470,9 +534,9 @@ voxel_finalize_kernel(int64_t n, const int32_t *__restrict__ nvox, const double 
         float cx = 0.f, cy = 0.f, cz = 0.f;
         int c = 0;
         if (v < nv) {
-            const double *sp = sums + (cloud * n + v) * 3;
-            c = cnt[cloud * n + v];
-            cx = (float)(sp[0] / (double)c); cy = (float)(sp[1] / (double)c); cz = (float)(sp[2] / (double)c);
+            const double4 sp = reinterpret_cast<const double4 *>(sums)[cloud * n + v];
+            c = (int)sp.w;                                   // counts are exact in a double
+            cx = (float)(sp.x / sp.w); cy = (float)(sp.y / sp.w); cz = (float)(sp.z / sp.w);
         }
         float *o = out_xyz + (cloud * n + v) * 3;
         o[0] = cx; o[1] = cy; o[2] = cz;
@@ -513,7 +577,7 @@ static VoxelWs carve(void *base, int b, int64_t n)
     w.bitmap = reinterpret_cast<unsigned *>(take((size_t)b * (size_t)(w.cap_cells >> 3)));
     w.word_rank = reinterpret_cast<unsigned *>(take((size_t)b * (size_t)(w.cap_cells >> 3)));
     w.grid = reinterpret_cast<VoxelGrid *>(take((size_t)b * sizeof(VoxelGrid)));
-    w.sums = reinterpret_cast<double *>(take(bn * 24));
+    w.sums = reinterpret_cast<double *>(take(bn * 32));
     w.cnt = reinterpret_cast<int *>(take(bn * 4));
     w.need_sort = reinterpret_cast<int *>(take(4));
     w.bytes = (size_t)(p - reinterpret_cast<char *>(base));
