@@ -63,7 +63,10 @@ int pcp_stream_sync(pcp_stream stream);
 /* PointCloudNormalization.call (pointnet/PointNet.py:691-706): per cloud centroid, centre,
  * max distance, scale = max(maxdist, 1e-7), divide.  x,y: (b, n, 3) f32 contiguous.
  * d_centroid (b*3) and d_scale (b) may be NULL; d_y may be NULL when both statistics are
- * requested (statistics-only pass).  One HBM read + one write (24 B/point). */
+ * requested (statistics-only pass).  One HBM read + one write (24 B/point).  Clouds of n >= 16384 points
+ * (16-byte aligned, n % 4 == 0) run as shared-memory-resident slices that meet through per-cloud counters in a
+ * library-owned scratch ring (8 calls may be in flight per device); there is no upper limit on n on that path.
+ * Smaller or unaligned clouds: one thread-block cluster per cloud (n <= 273 066). */
 int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale,
                       pcp_stream stream);
 
@@ -94,6 +97,10 @@ int pcp_resize_to_width_f32(const float *d_x, const int32_t *d_labels, int b, in
 /* Farthest-point sampling: x (b, n, 3) -> idx (b, s) int32; first index = start; fp32
  * ((dx*dx + dy*dy) + dz*dz) without FMA, lowest index wins ties. */
 int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, pcp_stream stream);
+/* Development aid: cycles block 0 / thread 0 of the last pcp_fps_f32 launch made under PCP_FPS_PROF=1 (25 points per
+ * thread) spent in: distance loop, warp keys, __syncthreads, push, exchange wait, read-back (scripts/fps_phases.py). */
+int pcp_fps_phase_cycles(unsigned long long out[8]);
+
 /* out[c, j, :] = x[c, idx[c, j], :] ; labels likewise when non-NULL */
 int pcp_gather_points_f32(const float *d_x, const int32_t *d_labels, int b, int64_t n, const int32_t *d_idx, int s,
                           float *d_out, int32_t *d_labels_out, pcp_stream stream);

@@ -69,6 +69,7 @@ SIGNATURES = {
     "pcp_rotate_f32": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp]),
     "pcp_resize_to_width_f32": (_i32, [_vp, _vp, _i32, _i64, _vp, _i64, _u64, _vp, _vp, _vp]),
     "pcp_fps_f32": (_i32, [_vp, _i32, _i64, _i32, _i32, _vp, _vp]),
+    "pcp_fps_phase_cycles": (_i32, [C.POINTER(C.c_ulonglong)]),
     "pcp_gather_points_f32": (_i32, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
     "pcp_voxel_workspace_bytes": (_i32, [_i32, _i64, C.POINTER(_sz)]),
     "pcp_voxel_f32": (_i32, [_vp, _i32, _i64, _fp, _f, _vp, _vp, _vp, _vp, _sz, _vp]),

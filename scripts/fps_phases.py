@@ -12,7 +12,6 @@ e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=Tr
 e0.record(); ops.farthest_point_sample(x, 1024); e1.record(); torch.cuda.synchronize()
 out = (C.c_ulonglong * 8)()
 lib = _ffi.load()
-lib.pcp_fps_phase_cycles.argtypes = [C.POINTER(C.c_ulonglong)]
 _ffi.check(lib.pcp_fps_phase_cycles(out))
 names = ["distance loop", "candidate search + record", "__syncthreads", "warp-0 stage + pushes", "cluster barrier", "slot read-back", "-", "-"]
 if not os.environ.get("PCP_FPS_NO_PAIR"):
