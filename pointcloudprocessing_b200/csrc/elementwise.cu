@@ -718,7 +718,13 @@ extern "C" int pcp_jitter_f32(const float *d_x, int64_t npoints, const float h_s
     if (npoints == 0) return PCP_OK;
     const int vec_ok = ((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y) |
                          reinterpret_cast<uintptr_t>(d_noise)) & 15u) == 0;
-    const int grid = stream_grid((npoints + 3) / 4, 256);
+    // one resident wave (grid-stride beyond): sm_count * 8 CTAs on a kernel that fits three or four per SM ends in a partial wave
+    static int occ_explicit = 0, occ_philox = 0;
+    if (!occ_explicit) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_explicit, jitter_kernel<true>, 256, 0) != cudaSuccess || occ_explicit < 1) occ_explicit = 4;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_philox, jitter_kernel<false>, 256, 0) != cudaSuccess || occ_philox < 1) occ_philox = 4;
+    }
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(((npoints + 3) / 4 + 255) / 256, (int64_t)sm_count() * (d_noise ? occ_explicit : occ_philox)));
     if (d_noise)
         jitter_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(d_x, d_noise, npoints, h_stdev[0], h_stdev[1], h_stdev[2], seed, offset, d_y, vec_ok);
     else

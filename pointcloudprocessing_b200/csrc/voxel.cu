@@ -584,6 +584,20 @@ static VoxelWs carve(void *base, int b, int64_t n)
     return w;
 }
 
+// grid.x of a (gx, b) grid-stride launch that is resident in ONE wave: a grid of sm_count * 8 CTAs on a kernel that fits five
+// or seven per SM runs a second, mostly empty wave (1152 CTAs on 740-1036 slots at 64 clouds)
+template <typename K>
+static int wave_gx(K kernel, int b, int64_t items_per_cloud, int *cache)
+{
+    if (*cache == 0) {
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 256, 0) != cudaSuccess || occ < 1) occ = 4;
+        *cache = occ;
+    }
+    const int64_t want = std::max<int64_t>(1, (int64_t)sm_count() * *cache / b);
+    return (int)std::max<int64_t>(1, std::min<int64_t>((items_per_cloud + 255) / 256, want));
+}
+
 }  // namespace pcp
 
 using namespace pcp;
@@ -615,20 +629,22 @@ extern "C" int pcp_voxel_f32(const float *d_x, int b, int64_t n, const float *h_
         PCP_CUDA_OK(cudaMemsetAsync(w.max_enc, 0, (size_t)b * 12, st));
         PCP_CUDA_OK(cudaMemsetAsync(w.need_sort, 0, 4, st));
         const int vec_ok = ((reinterpret_cast<uintptr_t>(d_x) & 15u) == 0) && (n % 4 == 0);
-        voxel_minmax_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.origin_enc, w.max_enc, vec_ok);
+        static int occ_minmax = 0, occ_clear = 0, occ_mark = 0, occ_accum = 0, occ_fin = 0;
+        const int64_t groups = vec_ok ? (n + 3) / 4 : n;
+        voxel_minmax_kernel<<<dim3(wave_gx(voxel_minmax_kernel, b, vec_ok ? (n * 3 / 4 + 2) / 3 : n, &occ_minmax), b), 256, 0, st>>>(d_x, n, w.origin_enc, w.max_enc, vec_ok);
         PCP_CHECK_LAUNCH();
         voxel_grid_kernel<<<(b + 127) / 128, 128, 0, st>>>(w.origin_enc, w.max_enc, b, ox, oy, oz, h_origin ? 0 : 1, voxel, w.cap_cells, w.grid,
                                                           w.need_sort);
         PCP_CHECK_LAUNCH();
-        voxel_clear_kernel<<<dim3(gx, b), 256, 0, st>>>(w.grid, w.cap_cells, w.bitmap, w.need_sort);
+        voxel_clear_kernel<<<dim3(wave_gx(voxel_clear_kernel, b, (w.cap_cells >> 7) + 1, &occ_clear), b), 256, 0, st>>>(w.grid, w.cap_cells, w.bitmap, w.need_sort);
         PCP_CHECK_LAUNCH();
-        voxel_mark_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.bad, w.need_sort, vec_ok);
+        voxel_mark_kernel<<<dim3(wave_gx(voxel_mark_kernel, b, groups, &occ_mark), b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.bad, w.need_sort, vec_ok);
         PCP_CHECK_LAUNCH();
         voxel_rank_kernel<<<b, 1024, 0, st>>>(w.bitmap, w.grid, w.cap_cells, n, w.word_rank, d_nvox, w.bad, w.sums, w.cnt, w.need_sort);
         PCP_CHECK_LAUNCH();
-        voxel_accum_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.word_rank, w.sums, w.cnt, w.need_sort, vec_ok);
+        voxel_accum_kernel<<<dim3(wave_gx(voxel_accum_kernel, b, groups, &occ_accum), b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.word_rank, w.sums, w.cnt, w.need_sort, vec_ok);
         PCP_CHECK_LAUNCH();
-        voxel_finalize_kernel<<<dim3(gx, b), 256, 0, st>>>(n, d_nvox, w.sums, w.cnt, d_out_xyz, d_out_count, w.need_sort);
+        voxel_finalize_kernel<<<dim3(wave_gx(voxel_finalize_kernel, b, n, &occ_fin), b), 256, 0, st>>>(n, d_nvox, w.sums, w.cnt, d_out_xyz, d_out_count, w.need_sort);
         PCP_CHECK_LAUNCH();
         // the flag is read once everything is queued: the wait overlaps the kernels instead of stalling the stream mid-way
         int need_sort = 0;
