@@ -18,15 +18,19 @@ constexpr uint32_t kGemmStageBytes = 32768;   // 16 KB A + up to 16 KB B
 constexpr uint32_t kGemmSmem = kGemmStages * kGemmStageBytes + 1024;
 
 __global__ void __launch_bounds__(kGemmThreads, 2)
-tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
-{
+tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nsplit)
+{   // bnt: MMA N of this CTA; img_rows: rows of a weight-image tile; nsplit = img_rows / bnt column blocks per image tile
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t full[kGemmStages], empty[kGemmStages], acc_full;
     __shared__ uint32_t tmem_base;
     uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nt = blockIdx.x;
+    // A (img_rows x 64) SWIZZLE_128B tile is a stack of 1024-byte 8-row atoms, so rows [j bnt, (j + 1) bnt) of it are a
+    // contiguous, valid bnt-row operand: skinny GEMMs (M = one row tile) split their 128-column tiles over several CTAs, each
+    // streaming its share of the weights (4 CTAs pulling a 1 MB image had been the whole cost of a 1024 -> 512 head layer)
+    const int ntile = blockIdx.x / nsplit, nsub = blockIdx.x % nsplit;
+    const int ncol0 = ntile * img_rows + nsub * bnt;
     const int g = blockIdx.y / mtiles, mt = blockIdx.y % mtiles;
     const int row0 = mt * 128;
     const int rows_valid = min(128, p.M - row0);
@@ -131,12 +135,12 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
             float o[32];
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
-                const int n = nt * bnt + c0 + e;
+                const int n = ncol0 + c0 + e;
                 float f = __uint_as_float(v[e]) + ((bias && n < p.N) ? __ldg(bias + n) : 0.f);
                 if (p.relu) f = f > 0.f ? f : 0.f;
                 o[e] = f;
             }
-            const int nbase = nt * bnt + c0;
+            const int nbase = ncol0 + c0;
             if (p.C32) {
                 float *Cg = p.C32 + (size_t)g * p.c_group_stride;
                 if (p.dbg & 1) {
@@ -215,12 +219,13 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles)
     } else {
         // ---------------- weight-tile loader ----------------
         if (lane == 0) {
-            const uint8_t *img = p.Bimg + (size_t)g * p.b_group_stride + (size_t)nt * KT * b_tile_bytes;
+            const size_t img_tile_bytes = (size_t)img_rows * 128u;
+            const uint8_t *img = p.Bimg + (size_t)g * p.b_group_stride + (size_t)ntile * KT * img_tile_bytes + (size_t)nsub * b_tile_bytes;
             for (int kt = 0; kt < KT; ++kt) {
                 const int s = kt % kGemmStages;
                 if (kt >= kGemmStages) mbar_wait(&empty[s], (uint32_t)(((kt / kGemmStages) - 1) & 1), 43);
                 mbar_arrive_expect_tx(&full[s], b_tile_bytes);
-                bulk_g2s(base + s * kGemmStageBytes + 16384, img + (size_t)kt * b_tile_bytes, b_tile_bytes, &full[s]);
+                bulk_g2s(base + s * kGemmStageBytes + 16384, img + (size_t)kt * img_tile_bytes, b_tile_bytes, &full[s]);
             }
         }
     }
@@ -285,12 +290,15 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
     PCP_REQUIRE(gy <= 65535, PCP_ERR_UNSUPPORTED, "tc_gemm: %lld row tiles exceed one launch", (long long)gy);
     static const bool no_pdl = getenv("PCP_TC_GEMM_NO_PDL") != nullptr;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(ntiles, (unsigned)gy); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = kGemmSmem; cfg.stream = st;
+    // few CTAs and full-width tiles: 32-column blocks (see the kernel)
+    static const bool no_split = getenv("PCP_TC_GEMM_NO_NSPLIT") != nullptr;
+    const int nsplit = (!no_split && bnt_img == 128 && (int64_t)ntiles * gy * 4 <= 2 * (int64_t)sm_count()) ? 4 : 1;
+    cfg.gridDim = dim3(ntiles * nsplit, (unsigned)gy); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = kGemmSmem; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = no_pdl ? 0 : 1;
-    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel, p, bnt_img, mtiles));
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }

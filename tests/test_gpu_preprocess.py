@@ -19,7 +19,7 @@ def _ulp_err(a, ref, scale):
 
 
 # (2, 100000), (160, 16384), (3, 40000): the ticketed slice kernel (one round / more tickets than resident CTAs / uneven last slice)
-@pytest.mark.parametrize("b,n", [(32, 1024), (8, 8192), (3, 1000), (5, 37), (2, 100000), (1, 1), (64, 2048), (160, 16384), (3, 40000), (2, 16386)])
+@pytest.mark.parametrize("b,n", [(32, 1024), (8, 8192), (3, 1000), (5, 37), (2, 100000), (1, 1), (64, 2048), (160, 16384), (3, 40000), (2, 16386), (1, 300000)])
 def test_normalize_matches_oracle(lib, b, n):
     from pointcloudprocessing_b200 import ops
     x = synth.gaussian_clouds(1001 + n, b, n)
@@ -173,6 +173,8 @@ def test_gather_points(lib):
 
 
 @pytest.mark.parametrize("b,n,voxel,origin", [(2, 4000, 0.75, None), (3, 20000, 0.5, None), (2, 5000, 1.0, (0.0, -20.0, -10.0)), (1, 131072, 0.35, None),
+                                              (3, 4001, 0.75, None), (2, 130, 2.0, None),   # n % 4 != 0: scalar loads on the fast path; fewer than one warp run
+
                                               # bounding grid <= 32 n cells: bitmap-rank fast path; tiny voxels on few points: sort path
                                               (4, 100000, 0.7, None), (2, 50000, 2.0, (-3.0, 5.0, 1.0)), (2, 300, 0.05, None), (1, 1, 0.5, None)])
 def test_voxel_matches_oracle(lib, b, n, voxel, origin):
