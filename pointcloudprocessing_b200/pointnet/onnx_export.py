@@ -67,8 +67,8 @@ def messages():
                 f = m.field.add(name=fname, number=num, type=ftype, label=label)
                 if tname:
                     f.type_name = f".{_PKG}.{tname}"
-                if label == 3 and ftype in (_F.TYPE_INT64, _F.TYPE_FLOAT):
-                    f.options.packed = True                  # onnx.proto marks the repeated scalars [packed = true]
+                if label == 3 and fname.endswith("_data"):
+                    f.options.packed = True                  # onnx.proto: float_data / int64_data are [packed = true]; dims, ints, floats are not
         pool = descriptor_pool.DescriptorPool()
         pool.Add(fd)
         _classes = {n: message_factory.GetMessageClass(pool.FindMessageTypeByName(f"{_PKG}.{n}")) for n in _SCHEMA}
