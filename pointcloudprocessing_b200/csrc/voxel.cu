@@ -456,10 +456,18 @@ voxel_rank_kernel(const unsigned *__restrict__ bitmap, const VoxelGrid *__restri
     }
     const unsigned total = carry;
     if (tid == 0) nvox[cloud] = bad[cloud] ? -1 : (int32_t)total;
-    for (unsigned v = tid; v < total; v += 1024) {
-        double4 *sp = reinterpret_cast<double4 *>(sums) + (cloud * n + v);          // {sum x, sum y, sum z, count}: one 32-byte sector
-        *sp = make_double4(0.0, 0.0, 0.0, 0.0);
-    }
+}
+
+// accumulators of the occupied voxels zeroed by the whole GPU (one CTA per cloud took as long over it as the scan itself)
+__global__ void __launch_bounds__(256)
+voxel_zero_kernel(int64_t n, const int32_t *__restrict__ nvox, double *__restrict__ sums, const int *__restrict__ need_sort)
+{
+    if (*need_sort) return;
+    const int64_t cloud = blockIdx.y;
+    const int64_t nv = max(nvox[cloud], 0);
+    double4 *sp = reinterpret_cast<double4 *>(sums) + cloud * n;                // {sum x, sum y, sum z, count}: one 32-byte sector
+    for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nv; v += (int64_t)gridDim.x * blockDim.x)
+        sp[v] = make_double4(0.0, 0.0, 0.0, 0.0);
 }
 
 // A voxel's accumulators {sum x, sum y, sum z, count} fill one 32-byte sector, and the four reductions of a point are
@@ -629,7 +637,7 @@ extern "C" int pcp_voxel_f32(const float *d_x, int b, int64_t n, const float *h_
         PCP_CUDA_OK(cudaMemsetAsync(w.max_enc, 0, (size_t)b * 12, st));
         PCP_CUDA_OK(cudaMemsetAsync(w.need_sort, 0, 4, st));
         const int vec_ok = ((reinterpret_cast<uintptr_t>(d_x) & 15u) == 0) && (n % 4 == 0);
-        static int occ_minmax = 0, occ_clear = 0, occ_mark = 0, occ_accum = 0, occ_fin = 0;
+        static int occ_minmax = 0, occ_clear = 0, occ_mark = 0, occ_accum = 0, occ_fin = 0, occ_zero = 0;
         const int64_t groups = vec_ok ? (n + 3) / 4 : n;
         voxel_minmax_kernel<<<dim3(wave_gx(voxel_minmax_kernel, b, vec_ok ? (n * 3 / 4 + 2) / 3 : n, &occ_minmax), b), 256, 0, st>>>(d_x, n, w.origin_enc, w.max_enc, vec_ok);
         PCP_CHECK_LAUNCH();
@@ -641,6 +649,8 @@ extern "C" int pcp_voxel_f32(const float *d_x, int b, int64_t n, const float *h_
         voxel_mark_kernel<<<dim3(wave_gx(voxel_mark_kernel, b, groups, &occ_mark), b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.bad, w.need_sort, vec_ok);
         PCP_CHECK_LAUNCH();
         voxel_rank_kernel<<<b, 1024, 0, st>>>(w.bitmap, w.grid, w.cap_cells, n, w.word_rank, d_nvox, w.bad, w.sums, w.cnt, w.need_sort);
+        PCP_CHECK_LAUNCH();
+        voxel_zero_kernel<<<dim3(wave_gx(voxel_zero_kernel, b, n, &occ_zero), b), 256, 0, st>>>(n, d_nvox, w.sums, w.need_sort);
         PCP_CHECK_LAUNCH();
         voxel_accum_kernel<<<dim3(wave_gx(voxel_accum_kernel, b, groups, &occ_accum), b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.word_rank, w.sums, w.cnt, w.need_sort, vec_ok);
         PCP_CHECK_LAUNCH();
