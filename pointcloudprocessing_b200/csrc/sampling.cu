@@ -21,6 +21,7 @@ namespace pcp {
 constexpr int kFpsThreads = 512;
 constexpr int kFpsWarps = kFpsThreads / 32;
 constexpr int kFpsMaxCluster = 16;
+constexpr int kFpsMaxSmemRows = 27;               // 27 * 512 points * 16 B = 221 184 B of dynamic shared memory
 
 struct __align__(16) FpsRec {
     float x, y, z, pad;       // one 16-byte read for the winner's coordinates
@@ -117,8 +118,10 @@ __device__ unsigned long long g_fps_phase[8];
 
 template <int PPT, bool kProf>
 __global__ void __launch_bounds__(kFpsThreads, 1)
-fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int32_t *__restrict__ idx_out, int cs, int64_t ppc, int hw_barrier)
-{
+fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int32_t *__restrict__ idx_out, int cs, int64_t ppc, int hw_barrier,
+                   int srows)
+{   // srows: rows of 512 points the thread block keeps in SHARED memory on top of the PPT rows in registers (0: none)
+    extern __shared__ float fps_dyn[];                     // SoA x | y | z | d, srows * 512 floats each
     __shared__ unsigned long long warp_key[kFpsWarps];
     __shared__ FpsRec slots[2][kFpsMaxCluster];
 
@@ -141,6 +144,14 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
             px[k] = py[k] = pz[k] = 0.f;
             d[k] = 0.f;      // padding never wins: ties go to the lowest (real) index
         }
+    }
+    float *sx = fps_dyn, *sy = sx + srows * kFpsThreads, *sz = sy + srows * kFpsThreads, *sd = sz + srows * kFpsThreads;
+    for (int k = 0; k < srows; ++k) {
+        const int64_t gi = p0 + (int64_t)(PPT + k) * kFpsThreads + tid;
+        const bool real = gi < lim;
+        const int i = k * kFpsThreads + tid;
+        sx[i] = real ? __ldg(xc + 3 * gi) : 0.f; sy[i] = real ? __ldg(xc + 3 * gi + 1) : 0.f; sz[i] = real ? __ldg(xc + 3 * gi + 2) : 0.f;
+        sd[i] = real ? __int_as_float(0x7f800000) : 0.f;
     }
     float cx = __ldg(xc + 3 * (int64_t)start), cy = __ldg(xc + 3 * (int64_t)start + 1), cz = __ldg(xc + 3 * (int64_t)start + 2);
     if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
@@ -169,6 +180,14 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
             d[k] = fminf(d[k], dd);
             if (d[k] > best) { best = d[k]; bk = k; }
         }
+        // the rows in shared memory (each thread only ever touches its own column: no barrier); conflict-free 4-byte accesses
+#pragma unroll 4
+        for (int k = 0; k < srows; ++k) {
+            const int i = k * kFpsThreads + tid;
+            const float m = fminf(sd[i], sqdist_nofma(sx[i], sy[i], sz[i], cx, cy, cz));
+            sd[i] = m;
+            if (m > best) { best = m; bk = PPT + k; }
+        }
         FPS_STAMP(0);
         const unsigned bb = __float_as_uint(best);
         const unsigned wmax = __reduce_max_sync(0xffffffffu, bb);
@@ -183,9 +202,14 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
         // every warp reduces the 16 warp keys itself (no second barrier); the warp that owns the block's winner fetches its
         // coordinates and pushes the record into every CTA of the cluster (lane t -> CTA t)
         const bool pushed = fps_push(SS, cluster, par, rank, cs, cand, tid, lane, [&](FpsRec &r) {
+            if (bk >= PPT) {
+                const int i = (bk - PPT) * kFpsThreads + tid;
+                r.x = sx[i]; r.y = sy[i]; r.z = sz[i];
+            } else {
 #pragma unroll
-            for (int k = 0; k < PPT; ++k)
-                if (k == bk) { r.x = px[k]; r.y = py[k]; r.z = pz[k]; }
+                for (int k = 0; k < PPT; ++k)
+                    if (k == bk) { r.x = px[k]; r.y = py[k]; r.z = pz[k]; }
+            }
         });
         FPS_STAMP(3);
         if (cs == 1) __syncthreads();
@@ -262,24 +286,25 @@ fps_stream_kernel(const float *__restrict__ x, int64_t n, int s, int start, int3
 }
 
 template <int PPT, bool kProf = false>
-static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, int cs, int64_t ppc, cudaStream_t st)
+static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, int cs, int64_t ppc, cudaStream_t st, int srows = 0)
 {
     static bool attr_set = false;
     if (!attr_set) {
         PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpsMaxSmemRows * kFpsThreads * 16));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((int64_t)b * cs));
     cfg.blockDim = dim3(kFpsThreads);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = (size_t)srows * kFpsThreads * 16;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     static const int hw_barrier = getenv("PCP_FPS_HW_BARRIER") != nullptr;          // the previous exchange, kept for comparison
-    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, fps_cluster_kernel<PPT, kProf>, d_x, n, s, start, d_idx, cs, ppc, hw_barrier));
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, fps_cluster_kernel<PPT, kProf>, d_x, n, s, start, d_idx, cs, ppc, hw_barrier, srows));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -316,6 +341,20 @@ extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start,
         fps_stream_kernel<<<b, 1024, 0, st>>>(d_x, n, s, start, d_idx, g_fps_scratch);
         PCP_CHECK_LAUNCH();
         return PCP_OK;
+    }
+    // More clusters than the GPU holds at once (64 clouds x 8 CTAs on 148 SMs = four waves): halve the cluster and keep the
+    // second half of every CTA's slice in shared memory (SoA, 16 B per point) beside the 25 rows in registers — half the
+    // waves for a longer iteration.
+    static const bool no_hybrid = getenv("PCP_FPS_NO_HYBRID") != nullptr;
+    if (!no_hybrid && cs >= 2 && (int64_t)b * cs > sm_count()) {
+        const int csh = cs / 2;
+        const int64_t ppch = (n + csh - 1) / csh;
+        const int rows = (int)((ppch + kFpsThreads - 1) / kFpsThreads);
+        if (rows > kMaxPPT && rows - kMaxPPT <= kFpsMaxSmemRows) {
+            static const bool prof_h = getenv("PCP_FPS_PROF") != nullptr;
+            if (prof_h) return launch_fps<25, true>(d_x, b, n, s, start, d_idx, csh, ppch, st, rows - kMaxPPT);
+            return launch_fps<25>(d_x, b, n, s, start, d_idx, csh, ppch, st, rows - kMaxPPT);
+        }
     }
     const int64_t ppc = (n + cs - 1) / cs;
     const int ppt = (int)((ppc + kFpsThreads - 1) / kFpsThreads);
