@@ -21,6 +21,7 @@ namespace pcp {
 constexpr int kFpsThreads = 512;
 constexpr int kFpsWarps = kFpsThreads / 32;
 constexpr int kFpsMaxCluster = 16;
+constexpr int kFpsRegRows = 17, kFpsRegDist = 32;  // hybrid split: rows fully in registers / rows with only the distance there
 constexpr int kFpsMaxSmemRows = 27;               // 27 * 512 points * 16 B = 221 184 B of dynamic shared memory
 
 struct __align__(16) FpsRec {
@@ -112,16 +113,24 @@ __device__ __forceinline__ unsigned fps_winner(const FpsSide &S, int par, int cs
     return 0xFFFFFFFFu - mlo;
 }
 
+// SD > 0 hybrid rows: shared-memory element of a thread's k-th point (one row of 512 points per k).  The element index is
+// also the point's offset behind the register rows of the slice.
+__device__ __forceinline__ int fps_selem(int k, int tid) { return k * kFpsThreads + tid; }
+
 // phase cycle totals of block 0 / thread 0 (development aid, read through pcp_fps_phase_cycles)
 __device__ unsigned long long g_fps_phase[8];
 #define FPS_STAMP(i) do { if (kProf && blockIdx.x == 0 && tid == 0) { const long long t_ = clock64(); ph[i] += t_ - tprev; tprev = t_; } } while (0)
 
-template <int PPT, bool kProf>
+template <int PPT, bool kProf, int SD = 0>
 __global__ void __launch_bounds__(kFpsThreads, 1)
 fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int32_t *__restrict__ idx_out, int cs, int64_t ppc, int hw_barrier,
                    int srows)
 {   // srows: rows of 512 points the thread block keeps in SHARED memory on top of the PPT rows in registers (0: none)
-    extern __shared__ float fps_dyn[];                     // SoA x | y | z | d, srows * 512 floats each
+    // SD == 0: shared rows hold x | y | z | d.  SD > 0: shared rows hold the coordinates only and their running distances stay
+    // in SD registers per thread (srows <= SD, rows allocated in groups of four) — 12 B instead of 20 B of shared-memory
+    // traffic per point and iteration.
+    extern __shared__ __align__(16) float fps_dyn[];                     // SoA, arows * 512 floats each
+    const int arows = SD > 0 ? (srows + 3) & ~3 : srows;
     __shared__ unsigned long long warp_key[kFpsWarps];
     __shared__ FpsRec slots[2][kFpsMaxCluster];
 
@@ -145,13 +154,18 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
             d[k] = 0.f;      // padding never wins: ties go to the lowest (real) index
         }
     }
-    float *sx = fps_dyn, *sy = sx + srows * kFpsThreads, *sz = sy + srows * kFpsThreads, *sd = sz + srows * kFpsThreads;
-    for (int k = 0; k < srows; ++k) {
+    float *sx = fps_dyn, *sy = sx + arows * kFpsThreads, *sz = sy + arows * kFpsThreads, *sd = sz + arows * kFpsThreads;
+    float ds[SD > 0 ? SD : 1];
+    for (int k = 0; k < arows; ++k) {
         const int64_t gi = p0 + (int64_t)(PPT + k) * kFpsThreads + tid;
         const bool real = gi < lim;
         const int i = k * kFpsThreads + tid;
         sx[i] = real ? __ldg(xc + 3 * gi) : 0.f; sy[i] = real ? __ldg(xc + 3 * gi + 1) : 0.f; sz[i] = real ? __ldg(xc + 3 * gi + 2) : 0.f;
-        sd[i] = real ? __int_as_float(0x7f800000) : 0.f;
+        if (SD == 0) sd[i] = real ? __int_as_float(0x7f800000) : 0.f;
+    }
+    if (SD > 0) {
+#pragma unroll
+        for (int k = 0; k < SD; ++k) ds[k] = (p0 + (int64_t)PPT * kFpsThreads + fps_selem(k, tid) < lim) ? __int_as_float(0x7f800000) : 0.f;
     }
     float cx = __ldg(xc + 3 * (int64_t)start), cy = __ldg(xc + 3 * (int64_t)start + 1), cz = __ldg(xc + 3 * (int64_t)start + 2);
     if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
@@ -181,17 +195,32 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
             if (d[k] > best) { best = d[k]; bk = k; }
         }
         // the rows in shared memory (each thread only ever touches its own column: no barrier); conflict-free 4-byte accesses
+        if (SD > 0) {
+#pragma unroll
+            for (int k4 = 0; k4 < SD; k4 += 4) {
+                if (k4 < arows) {
+#pragma unroll
+                    for (int k = k4; k < k4 + 4 && k < SD; ++k) {
+                        const int i = fps_selem(k, tid);
+                        const float m = fminf(ds[k], sqdist_nofma(sx[i], sy[i], sz[i], cx, cy, cz));
+                        ds[k] = m;
+                        if (m > best) { best = m; bk = PPT + k; }
+                    }
+                }
+            }
+        } else {
 #pragma unroll 4
-        for (int k = 0; k < srows; ++k) {
-            const int i = k * kFpsThreads + tid;
-            const float m = fminf(sd[i], sqdist_nofma(sx[i], sy[i], sz[i], cx, cy, cz));
-            sd[i] = m;
-            if (m > best) { best = m; bk = PPT + k; }
+            for (int k = 0; k < srows; ++k) {
+                const int i = k * kFpsThreads + tid;
+                const float m = fminf(sd[i], sqdist_nofma(sx[i], sy[i], sz[i], cx, cy, cz));
+                sd[i] = m;
+                if (m > best) { best = m; bk = PPT + k; }
+            }
         }
         FPS_STAMP(0);
         const unsigned bb = __float_as_uint(best);
         const unsigned wmax = __reduce_max_sync(0xffffffffu, bb);
-        const int64_t gi = p0 + (int64_t)bk * kFpsThreads + tid;
+        const int64_t gi = (SD > 0 && bk >= PPT) ? p0 + (int64_t)PPT * kFpsThreads + fps_selem(bk - PPT, tid) : p0 + (int64_t)bk * kFpsThreads + tid;
         const unsigned cand = (bb == wmax && gi < lim) ? (unsigned)gi : 0xFFFFFFFFu;
         const unsigned wmin = __reduce_min_sync(0xffffffffu, cand);
         if (lane == 0) warp_key[warp] = ((unsigned long long)wmax << 32) | (unsigned long long)(0xFFFFFFFFu - wmin);   // low word 0: no real point
@@ -203,7 +232,7 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
         // coordinates and pushes the record into every CTA of the cluster (lane t -> CTA t)
         const bool pushed = fps_push(SS, cluster, par, rank, cs, cand, tid, lane, [&](FpsRec &r) {
             if (bk >= PPT) {
-                const int i = (bk - PPT) * kFpsThreads + tid;
+                const int i = SD > 0 ? fps_selem(bk - PPT, tid) : (bk - PPT) * kFpsThreads + tid;
                 r.x = sx[i]; r.y = sy[i]; r.z = sz[i];
             } else {
 #pragma unroll
@@ -285,26 +314,26 @@ fps_stream_kernel(const float *__restrict__ x, int64_t n, int s, int start, int3
     }
 }
 
-template <int PPT, bool kProf = false>
+template <int PPT, bool kProf = false, int SD = 0>
 static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, int cs, int64_t ppc, cudaStream_t st, int srows = 0)
 {
     static bool attr_set = false;
     if (!attr_set) {
-        PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-        PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpsMaxSmemRows * kFpsThreads * 16));
+        PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf, SD>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf, SD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpsMaxSmemRows * kFpsThreads * 16));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((int64_t)b * cs));
     cfg.blockDim = dim3(kFpsThreads);
-    cfg.dynamicSmemBytes = (size_t)srows * kFpsThreads * 16;
+    cfg.dynamicSmemBytes = SD > 0 ? (size_t)((srows + 3) & ~3) * kFpsThreads * 12 : (size_t)srows * kFpsThreads * 16;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     static const int hw_barrier = getenv("PCP_FPS_HW_BARRIER") != nullptr;          // the previous exchange, kept for comparison
-    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, fps_cluster_kernel<PPT, kProf>, d_x, n, s, start, d_idx, cs, ppc, hw_barrier, srows));
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, fps_cluster_kernel<PPT, kProf, SD>, d_x, n, s, start, d_idx, cs, ppc, hw_barrier, srows));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -350,6 +379,14 @@ extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start,
         const int csh = cs / 2;
         const int64_t ppch = (n + csh - 1) / csh;
         const int rows = (int)((ppch + kFpsThreads - 1) / kFpsThreads);
+        // 17 rows with everything in registers + up to 32 rows whose coordinates sit in shared memory and whose distances stay in
+        // registers (17 * 4 + 32 = 100 data registers, 32 * 512 * 12 B = 192 KB)
+        static const bool no_regd = getenv("PCP_FPS_NO_REGD") != nullptr;
+        if (!no_regd && rows > kFpsRegRows && rows - kFpsRegRows <= kFpsRegDist) {
+            static const bool prof_r = getenv("PCP_FPS_PROF") != nullptr;
+            if (prof_r) return launch_fps<kFpsRegRows, true, kFpsRegDist>(d_x, b, n, s, start, d_idx, csh, ppch, st, rows - kFpsRegRows);
+            return launch_fps<kFpsRegRows, false, kFpsRegDist>(d_x, b, n, s, start, d_idx, csh, ppch, st, rows - kFpsRegRows);
+        }
         if (rows > kMaxPPT && rows - kMaxPPT <= kFpsMaxSmemRows) {
             static const bool prof_h = getenv("PCP_FPS_PROF") != nullptr;
             if (prof_h) return launch_fps<25, true>(d_x, b, n, s, start, d_idx, csh, ppch, st, rows - kMaxPPT);

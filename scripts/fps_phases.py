@@ -10,12 +10,12 @@ x = torch.from_numpy(synth.lidar_scans(2002, 64, 100000)).cuda()
 ops.farthest_point_sample(x, 1024); torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record(); ops.farthest_point_sample(x, 1024); e1.record(); torch.cuda.synchronize()
+if os.environ.get("PCP_FPS_TIME_ONLY"):
+    print("total %.2f ms (profiling stamps on)" % e0.elapsed_time(e1)); sys.exit(0)
 out = (C.c_ulonglong * 8)()
 lib = _ffi.load()
 _ffi.check(lib.pcp_fps_phase_cycles(out))
 names = ["distance loop", "candidate search + record", "__syncthreads", "warp-0 stage + pushes", "cluster barrier", "slot read-back", "-", "-"]
-if not os.environ.get("PCP_FPS_NO_PAIR"):
-    names = ["A distances", "A warp keys", "wait B + B winner", "sync + push A + arrive", "B distances (smem)", "B warp keys", "wait A", "A winner + sync + push B + arrive"]
 print("total %.2f ms" % e0.elapsed_time(e1))
 for nm, v in zip(names, out):
     print(f"{nm:28s} {v / 1023:8.0f} cycles / iteration")
