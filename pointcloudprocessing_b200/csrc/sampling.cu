@@ -165,7 +165,7 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
     }
     if (SD > 0) {
 #pragma unroll
-        for (int k = 0; k < SD; ++k) ds[k] = (p0 + (int64_t)PPT * kFpsThreads + fps_selem(k, tid) < lim) ? __int_as_float(0x7f800000) : 0.f;
+        for (int k = 0; k < SD; ++k) ds[k] = (p0 + (int64_t)(PPT + k) * kFpsThreads + tid < lim) ? __int_as_float(0x7f800000) : 0.f;
     }
     float cx = __ldg(xc + 3 * (int64_t)start), cy = __ldg(xc + 3 * (int64_t)start + 1), cz = __ldg(xc + 3 * (int64_t)start + 2);
     if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
@@ -201,7 +201,7 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
                 if (k4 < arows) {
 #pragma unroll
                     for (int k = k4; k < k4 + 4 && k < SD; ++k) {
-                        const int i = fps_selem(k, tid);
+                        const int i = k * kFpsThreads + tid;
                         const float m = fminf(ds[k], sqdist_nofma(sx[i], sy[i], sz[i], cx, cy, cz));
                         ds[k] = m;
                         if (m > best) { best = m; bk = PPT + k; }
@@ -220,7 +220,7 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
         FPS_STAMP(0);
         const unsigned bb = __float_as_uint(best);
         const unsigned wmax = __reduce_max_sync(0xffffffffu, bb);
-        const int64_t gi = (SD > 0 && bk >= PPT) ? p0 + (int64_t)PPT * kFpsThreads + fps_selem(bk - PPT, tid) : p0 + (int64_t)bk * kFpsThreads + tid;
+        const int64_t gi = p0 + (int64_t)bk * kFpsThreads + tid;
         const unsigned cand = (bb == wmax && gi < lim) ? (unsigned)gi : 0xFFFFFFFFu;
         const unsigned wmin = __reduce_min_sync(0xffffffffu, cand);
         if (lane == 0) warp_key[warp] = ((unsigned long long)wmax << 32) | (unsigned long long)(0xFFFFFFFFu - wmin);   // low word 0: no real point
@@ -232,7 +232,7 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
         // coordinates and pushes the record into every CTA of the cluster (lane t -> CTA t)
         const bool pushed = fps_push(SS, cluster, par, rank, cs, cand, tid, lane, [&](FpsRec &r) {
             if (bk >= PPT) {
-                const int i = SD > 0 ? fps_selem(bk - PPT, tid) : (bk - PPT) * kFpsThreads + tid;
+                const int i = (bk - PPT) * kFpsThreads + tid;
                 r.x = sx[i]; r.y = sy[i]; r.z = sz[i];
             } else {
 #pragma unroll
