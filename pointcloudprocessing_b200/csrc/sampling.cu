@@ -113,10 +113,6 @@ __device__ __forceinline__ unsigned fps_winner(const FpsSide &S, int par, int cs
     return 0xFFFFFFFFu - mlo;
 }
 
-// SD > 0 hybrid rows: shared-memory element of a thread's k-th point (one row of 512 points per k).  The element index is
-// also the point's offset behind the register rows of the slice.
-__device__ __forceinline__ int fps_selem(int k, int tid) { return k * kFpsThreads + tid; }
-
 // phase cycle totals of block 0 / thread 0 (development aid, read through pcp_fps_phase_cycles)
 __device__ unsigned long long g_fps_phase[8];
 #define FPS_STAMP(i) do { if (kProf && blockIdx.x == 0 && tid == 0) { const long long t_ = clock64(); ph[i] += t_ - tprev; tprev = t_; } } while (0)
