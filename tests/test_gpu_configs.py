@@ -1,0 +1,100 @@
+"""GPU parity at the FULL sizes of BASELINE.json's configs (VERDICT r01 "configs untested at their size"):
+  C2  FPS 64 x 100 000 -> 1024: every cloud bit-exact against the plain-C oracle (oracle/sampling_c.c);
+  C3  one bf16 training step at 256 x 1024 (classification_pretrain profile, pointnet_train.py:310-351) against the
+      bf16-rounding autograd oracle: loss, outputs, BN moving statistics and every gradient tensor;
+  C4  segmentation inference 128 x 2048, all three outputs, both precisions (the bf16 model takes the persistent TMA GEMM
+      for the per-point segmentation layers at this size);
+  C5  8 scans x 131 072 points -> voxel grid -> resize to 8192 -> normalise -> classify, vanilla and full.
+C1 (32 x 1024) is tests/test_gpu_model.py::test_forward_matches_oracle[False-32-1024-*]."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pointnet_numpy as onp
+from oracle import pointnet_torch as opt
+from oracle import sampling as osm
+from tests import synth
+from tests.test_gpu_train import PRETRAIN, build as build_train, check_bf16_step_against_noise_floor, make_batch
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_err(a, ref):
+    return float(np.abs(a.astype(np.float64) - ref.astype(np.float64)).max() / max(np.abs(ref).max(), 1e-30))
+
+
+def test_c2_fps_all_64_clouds_bit_exact(lib, oracle_c):
+    from pointcloudprocessing_b200 import ops
+    b, n, s = 64, 100_000, 1024
+    x = synth.lidar_scans(2002, b, n)
+    idx = ops.farthest_point_sample(torch.from_numpy(x).cuda(), s).cpu().numpy()
+    ref = np.empty((b, s), np.int32)
+    oracle_c.oracle_fps_batch_f32(x.ctypes.data_as(ctypes.c_void_p), b, ctypes.c_int64(n), s, 0, ref.ctypes.data_as(ctypes.c_void_p))
+    assert np.array_equal(idx, ref)
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("bf16", 2e-2)])
+def test_c4_segmentation_128x2048_all_outputs(lib, precision, tol):
+    from pointcloudprocessing_b200.pointnet import PointNet
+    b, n, C, P = 128, 2048, 23, 12
+    p = onp.make_params(C, P, seed=7)
+    m = PointNet(C, P, 0.3, 42, precision=precision)
+    m.set_weights_dict(p)
+    x = synth.gaussian_clouds(4004, b, n)
+    out = m.forward_with_logits(torch.from_numpy(x).cuda())
+    got = {k: v.cpu().numpy() for k, v in out.items()}
+    with torch.no_grad():
+        ref = {k: v.numpy() for k, v in opt.forward(torch.from_numpy(x), opt.to_torch(p)).items()}
+    for k in ("R", "cls_logits", "seg_logits", "cls", "seg"):
+        assert got[k].shape == ref[k].shape
+        assert rel_err(got[k], ref[k]) <= tol, (k, rel_err(got[k], ref[k]))
+    assert (got["cls_logits"].argmax(-1) == ref["cls_logits"].argmax(-1)).all()
+    # per-point arg-max: identical wherever the oracle's top-2 gap exceeds what the tolerance can move
+    rl = ref["seg_logits"].reshape(-1, P).astype(np.float64)
+    srt = np.sort(rl, -1)
+    decided = (srt[:, -1] - srt[:, -2]) > 2 * tol * np.abs(rl).max()
+    same = got["seg_logits"].reshape(-1, P).argmax(-1) == rl.argmax(-1)
+    assert same[decided].all() and same.mean() > (0.999 if precision == "fp32" else 0.97), (decided.mean(), same.mean())
+    # the host path returns the same bits (D2H of b x n x P inside the library)
+    c2, s2, r2 = m(x)
+    assert np.array_equal(s2, got["seg"]) and np.array_equal(c2, got["cls"]) and np.array_equal(r2, got["R"])
+
+
+@pytest.mark.parametrize("vanilla", [True, False])
+def test_c5_voxel_resize_classify_8x131072(lib, vanilla):
+    from pointcloudprocessing_b200 import pipeline
+    from pointcloudprocessing_b200.pointnet import PointNet
+    b, nraw, width, voxel = 8, 131072, 8192, 0.7
+    scans = synth.lidar_scans(5005, b, nraw)
+    p = onp.make_params(23, 12, seed=7, vanilla=vanilla)
+    xd = torch.from_numpy(scans).cuda()
+    got_x = pipeline.voxel_resize(xd, voxel, width).cpu().numpy()
+    ref_x = np.empty((b, width, 3), np.float32)
+    for c in range(b):
+        cen, cnt, keys = osm.voxel_downsample(scans[c], voxel)
+        assert 8192 <= cen.shape[0] <= 16384, cen.shape          # voxel chosen so V in [8192, 16384]
+        ref_x[c] = cen[:width]                                   # truncate branch (PointCloudSet.py:455-456)
+    assert np.array_equal(got_x, ref_x)
+    for precision, tol in (("fp32", 1e-3), ("bf16", 2e-2)):
+        m = PointNet(23, 12, 0.3, 42, vanilla=vanilla, precision=precision)
+        m.set_weights_dict(p)
+        cls, _, R = pipeline.classify_scans(m, xd, voxel, width)
+        with torch.no_grad():
+            ref = opt.forward(torch.from_numpy(ref_x), opt.to_torch(p), vanilla=vanilla, heads=("cls",))
+        assert rel_err(cls.cpu().numpy(), ref["cls"].numpy()) <= tol, (precision, rel_err(cls.cpu().numpy(), ref["cls"].numpy()))
+        assert rel_err(R.cpu().numpy(), ref["R"].numpy()) <= tol
+        assert (cls.cpu().numpy().argmax(-1) == ref["cls"].numpy().argmax(-1)).all()
+
+
+@pytest.mark.parametrize("smooth", [False, True])
+def test_c3_training_step_256x1024_bf16(lib, smooth):
+    """BASELINE config 3's arithmetic at its size: one bf16 step of the classification_pretrain profile
+    (kc46_lidar_config.json:44-68) on 256 x 1024 points against the bf16-rounding autograd oracle — loss within 2e-2,
+    outputs, BN moving statistics and every gradient tensor within the oracle's own measured conditioning (see
+    tests/test_gpu_train.py::test_bf16_tensor_core_training_step for why that, and not a flat 2e-2, is the tight bound)."""
+    C, P, b, n = 23, 12, 256, 1024
+    m, p = build_train(C, P, False, PRETRAIN, (1.0, 0.0, 0.0), (False, False), precision="bf16", lr=1e-4, smooth=smooth)
+    x, y, masks = make_batch(3003, b, n, C, P)
+    check_bf16_step_against_noise_floor(m, p, x, y, masks, False, PRETRAIN, (1.0, 0.0, 0.0), (False, False), f"C3 256x1024 smooth={smooth}")
