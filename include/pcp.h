@@ -70,6 +70,19 @@ int pcp_stream_sync(pcp_stream stream);
 int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale,
                       pcp_stream stream);
 
+/* Allocation-free variant of pcp_normalize_f32 for the sliced kernel (n >= 16384, n % 4 == 0, 16-byte aligned x / y).
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic and the same kernel as
+ * pcp_normalize_f32; the per-cloud scratch (48 B per cloud + a 64-byte ticket block) is a static device array of
+ * 64 + 4096 * 48 = 196 672 bytes that every GPU which loads the library holds until exit, so b is limited to
+ * pcp_normalize_noalloc_max_clouds() = 4096 clouds per call (larger b, smaller or unaligned clouds: PCP_ERR_UNSUPPORTED
+ * with a message; nothing is launched).  The call performs no cudaMalloc / cudaFree and calls no allocating library
+ * routine; it clears the part of the array it uses on `stream` before the launch.  EVERY call on a device shares that one
+ * array: two calls that overlap on the GPU (different streams, or graphs replayed concurrently) race — serialise them. */
+int pcp_normalize_noalloc_max_clouds(void);
+int pcp_normalize_noalloc_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale,
+                              pcp_stream stream);
+
 /* PointCloudSet._parse_function jitter (pointcloud/PointCloudSet.py:335-337):
  * y = x + noise * stdev_axis.  d_noise != NULL: explicit noise tensor (parity tests).
  * d_noise == NULL: noise = Philox4x32-10 + Box-Muller, one Philox block per point, counter =

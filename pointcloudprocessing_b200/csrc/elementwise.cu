@@ -774,3 +774,63 @@ extern "C" int pcp_gather_points_f32(const float *d_x, const int32_t *d_labels, 
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
+
+// ---- allocation-free variant of the sliced normalisation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops) ----
+// Its scratch — the ticket word and one NormScratch per cloud — lives in a file-scope device array that every GPU which loads
+// the library holds until exit.  The name `g_norm_noalloc_scratch` is only a host-side stand-in in host code: the device
+// address is taken once per device with cudaGetSymbolAddress and that pointer is what the kernel receives.
+#define PCP_NORMALIZE_NOALLOC_MAX_CLOUDS 4096
+namespace pcp {
+constexpr size_t kNormNoAllocBytes = 64 + (size_t)PCP_NORMALIZE_NOALLOC_MAX_CLOUDS * sizeof(NormScratch);      // 196 672 B
+static __device__ __align__(256) unsigned char g_norm_noalloc_scratch[kNormNoAllocBytes];
+}  // namespace pcp
+
+extern "C" int pcp_normalize_noalloc_max_clouds(void) { return PCP_NORMALIZE_NOALLOC_MAX_CLOUDS; }
+
+extern "C" int pcp_normalize_noalloc_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale, pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && (d_y || (d_centroid && d_scale)) && b >= 0 && n >= 1, PCP_ERR_INVALID, "pcp_normalize_noalloc_f32: bad arguments (b=%d n=%lld)", b,
+                (long long)n);
+    if (b == 0) return PCP_OK;
+    PCP_REQUIRE(b <= PCP_NORMALIZE_NOALLOC_MAX_CLOUDS, PCP_ERR_UNSUPPORTED,
+                "pcp_normalize_noalloc_f32: b=%d exceeds the static scratch (%d clouds); use pcp_normalize_f32", b, PCP_NORMALIZE_NOALLOC_MAX_CLOUDS);
+    const bool aligned = (((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y)) & 15u) == 0) && (n % 4 == 0);
+    PCP_REQUIRE(n >= kNormPartsMin && aligned, PCP_ERR_UNSUPPORTED,
+                "pcp_normalize_noalloc_f32: only the sliced kernel uses scratch: n >= %lld, n %% 4 == 0 and 16-byte aligned x / y are required "
+                "(smaller clouds need no scratch: pcp_normalize_f32 allocates nothing for them)", (long long)kNormPartsMin);
+    // once per device, with that device current: the scratch's device address, the kernel's shared-memory opt-in and occupancy
+    static unsigned char *scratch_ptr[64] = {};
+    static int ctas_per_sm[64] = {};
+    int dev = 0;
+    PCP_CUDA_OK(cudaGetDevice(&dev));
+    PCP_REQUIRE(dev >= 0 && dev < 64, PCP_ERR_UNSUPPORTED, "pcp_normalize_noalloc_f32: device ordinal %d", dev);
+    const int smem_max = kNormSliceBytes + 384;
+    if (!scratch_ptr[dev]) {
+        void *p = nullptr;
+        PCP_CUDA_OK(cudaGetSymbolAddress(&p, g_norm_noalloc_scratch));
+        PCP_REQUIRE(p != nullptr, PCP_ERR_CUDA, "pcp_normalize_noalloc_f32: cudaGetSymbolAddress returned a null address");
+        cudaFuncAttributes fa;
+        PCP_CUDA_OK(cudaFuncGetAttributes(&fa, normalize_parts_kernel));
+        if (fa.maxDynamicSharedSizeBytes < smem_max)          // never lower what pcp_normalize_f32 may have opted into
+            PCP_CUDA_OK(cudaFuncSetAttribute(normalize_parts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+        int occ = 0;
+        PCP_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, normalize_parts_kernel, kNormPartThreads, smem_max));
+        PCP_REQUIRE(occ >= 1, PCP_ERR_CUDA, "pcp_normalize_noalloc_f32: slice kernel does not fit an SM");
+        ctas_per_sm[dev] = occ;
+        scratch_ptr[dev] = static_cast<unsigned char *>(p);
+    }
+    unsigned char *slot = scratch_ptr[dev];
+    unsigned *ticket = reinterpret_cast<unsigned *>(slot);
+    NormScratch *scr = reinterpret_cast<NormScratch *>(slot + 64);
+    cudaStream_t st = as_stream(stream);
+    // the array keeps the previous call's contents: the ticket and this call's b records must start at zero
+    PCP_CUDA_OK(cudaMemsetAsync(slot, 0, 64 + (size_t)b * sizeof(NormScratch), st));
+    const int k = (int)((n * 12 + kNormSliceBytes - 1) / kNormSliceBytes);
+    const int64_t ppc = (((n + k - 1) / k) + 31) & ~(int64_t)31;
+    const int grid = (int)std::min<int64_t>((int64_t)b * k, (int64_t)sm_count() * ctas_per_sm[dev]);
+    PCP_REQUIRE(k <= grid, PCP_ERR_UNSUPPORTED, "pcp_normalize_noalloc_f32: n=%lld needs %d resident slices", (long long)n, k);
+    normalize_parts_kernel<<<grid, kNormPartThreads, (size_t)ppc * 12, st>>>(d_x, b, n, k, ppc, d_y, d_centroid, d_scale, scr, ticket, 0u);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
