@@ -19,6 +19,12 @@ def world():
     return 0, 1
 
 
+def barrier():
+    """dist.barrier() when a process group is up; nothing otherwise (single-process runs)."""
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+
+
 def init_from_env(backend: str | None = None):
     """Initialise the default process group from torchrun's RANK / WORLD_SIZE / MASTER_* environment."""
     ws = int(os.environ.get("WORLD_SIZE", "1"))

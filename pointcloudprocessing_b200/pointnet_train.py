@@ -107,21 +107,33 @@ class TrainProfile:
             self._log.addHandler(ch)
             self._log.addHandler(fh)
 
+        # Data-parallel runs (torchrun): the PointCloudSet directory, pc_set.joblib and the TFRecord files are written by
+        # rank 0 alone; the other ranks wait at a barrier and then load the finished set (all ranks writing the same files at
+        # once could hand a half-written pc_set.joblib or a truncated TFRecord to a slower rank).
+        from . import parallel
+        rank, world = parallel.world()
         for prof in self._training_profiles:                                                 # :144-172
             P = self._training_profiles[prof]
-            if os.path.isdir(f"{self._data_path}{self._name}_{prof}"):
-                self._log.info(f"Training profile {self._name}_{prof} already exists. Using existing profile...")
-                with open(f"{self._data_path}{self._name}_{prof}/pc_set.joblib", "rb") as jl:
+            set_dir = f"{self._data_path}{self._name}_{prof}"
+            if rank == 0:
+                if os.path.isdir(set_dir):
+                    self._log.info(f"Training profile {self._name}_{prof} already exists. Using existing profile...")
+                    with open(f"{set_dir}/pc_set.joblib", "rb") as jl:
+                        P['pc'] = joblib.load(jl)
+                    P['pc']._print = self._log.info
+                else:
+                    noise = P['noise']
+                    P['pc'] = PointCloudSet(name=f"{self._name}_{prof}", class_labels=self._class_labels,
+                                                                part_labels=self._part_labels, network_input_width=self._input_width,
+                                                                jitter_stdev_m=np.array([noise['x_stdev_m'], noise['y_stdev_m'], noise['z_stdev_m']]),
+                                                                batch_size=self._batch_size, rand_seed=42, description=prof,
+                                                                print_func=self._log.info, data_path=self._data_path)
+                self._profile_datasets(prof)
+            parallel.barrier()
+            if rank != 0:
+                with open(f"{set_dir}/pc_set.joblib", "rb") as jl:
                     P['pc'] = joblib.load(jl)
                 P['pc']._print = self._log.info
-            else:
-                noise = P['noise']
-                P['pc'] = PointCloudSet(name=f"{self._name}_{prof}", class_labels=self._class_labels,
-                                                            part_labels=self._part_labels, network_input_width=self._input_width,
-                                                            jitter_stdev_m=np.array([noise['x_stdev_m'], noise['y_stdev_m'], noise['z_stdev_m']]),
-                                                            batch_size=self._batch_size, rand_seed=42, description=prof,
-                                                            print_func=self._log.info, data_path=self._data_path)
-            self._profile_datasets(prof)
             P['path'] = f"{self._specific_model_path}{prof}/"
             os.makedirs(f"{self._model_path}{P['path']}", exist_ok=True)
 
@@ -207,6 +219,8 @@ class TrainProfile:
                 model.export_onnx(onnx_path, self._input_width)
                 self._log.info(f"ONNX model written to {onnx_path}")
                 shutil.copy(self._config_file, f"{self._model_path}{P['path']}")
+            # only rank 0 wrote the checkpoint / ONNX file: nobody loads it (or enters the next profile's collectives) before it is complete
+            parallel.barrier()
             self._pretrained_model = f"{P['path']}{self._name}_{prof}.npz"                   # the next profile continues from this one (:257)
 
 
