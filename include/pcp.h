@@ -127,6 +127,16 @@ int pcp_voxel_f32(const float *d_x, int b, int64_t n, const float *h_origin, flo
                   int32_t *d_out_count, int32_t *d_nvox, void *d_workspace, size_t workspace_bytes,
                   pcp_stream stream);
 
+/* The same operator with caller-owned, capacity-bounded outputs, fully asynchronous: d_out_xyz (b, capacity, 3),
+ * d_out_count (b, capacity); rows [0, min(nvox, capacity)) of a cloud are written, the others are left untouched (no
+ * zero padding).  Nothing is allocated, nothing is read back and the call does not synchronise (workspace from
+ * pcp_voxel_workspace_bytes).  d_nvox[c] = number of voxels of cloud c (may exceed capacity: the caller sees the
+ * truncation), -1 for a cloud the contract rejects (non-finite coordinate), -2 for EVERY cloud when one cloud's bounding
+ * grid exceeds 32 n cells (the bitmap path does not cover the batch): hand the batch to pcp_voxel_f32. */
+int pcp_voxel_compact_f32(const float *d_x, int b, int64_t n, const float *h_origin, float voxel, int64_t capacity,
+                          float *d_out_xyz, int32_t *d_out_count, int32_t *d_nvox, void *d_workspace,
+                          size_t workspace_bytes, pcp_stream stream);
+
 /* ---- model: PointNet (pointnet/PointNet.py:84-292) ---- */
 
 typedef struct pcp_model pcp_model;

@@ -75,6 +75,7 @@ SIGNATURES = {
     "pcp_gather_points_f32": (_i32, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
     "pcp_voxel_workspace_bytes": (_i32, [_i32, _i64, C.POINTER(_sz)]),
     "pcp_voxel_f32": (_i32, [_vp, _i32, _i64, _fp, _f, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "pcp_voxel_compact_f32": (_i32, [_vp, _i32, _i64, _fp, _f, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "pcp_model_create": (_i32, [C.POINTER(ModelDesc), C.POINTER(_vp)]),
     "pcp_model_destroy": (_i32, [_vp]),
     "pcp_model_num_tensors": (_i32, [_vp]),

@@ -552,6 +552,23 @@ voxel_finalize_kernel(int64_t n, const int32_t *__restrict__ nvox, const double 
     }
 }
 
+// compact form of the finalize pass: rows [0, min(nvox, capacity)) only — no zero padding (at 64 x 100 000 points the padded
+// b x n rows were 102 MB of writes for 12 MB of voxels); a batch the bitmap path does not cover reports nvox = -2
+__global__ void __launch_bounds__(256)
+voxel_finalize_compact_kernel(int64_t n, int64_t capacity, int32_t *__restrict__ nvox, const double *__restrict__ sums, float *__restrict__ out_xyz,
+                              int32_t *__restrict__ out_count, const int *__restrict__ need_sort)
+{
+    const int64_t cloud = blockIdx.y;
+    if (*need_sort) { if (blockIdx.x == 0 && threadIdx.x == 0) nvox[cloud] = -2; return; }
+    const int64_t nv = min((int64_t)max(nvox[cloud], 0), capacity);
+    for (int64_t v = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; v < nv; v += (int64_t)gridDim.x * blockDim.x) {
+        const double4 sp = reinterpret_cast<const double4 *>(sums)[cloud * n + v];
+        float *o = out_xyz + (cloud * capacity + v) * 3;
+        o[0] = (float)(sp.x / sp.w); o[1] = (float)(sp.y / sp.w); o[2] = (float)(sp.z / sp.w);
+        out_count[cloud * capacity + v] = (int)sp.w;                 // counts are exact in a double
+    }
+}
+
 struct VoxelWs {
     unsigned long long *keys_a, *keys_b;
     unsigned *vals_a, *vals_b, *hist, *starts, *origin_enc;
@@ -685,6 +702,45 @@ extern "C" int pcp_voxel_f32(const float *d_x, int b, int64_t n, const float *h_
     voxel_heads_kernel<<<b, 1024, 0, st>>>(ka, n, w.starts, d_nvox, w.bad);
     PCP_CHECK_LAUNCH();
     voxel_reduce_kernel<<<dim3(gx, b), 256, 0, st>>>(d_x, n, va, w.starts, d_nvox, d_out_xyz, d_out_count);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+extern "C" int pcp_voxel_compact_f32(const float *d_x, int b, int64_t n, const float *h_origin, float voxel, int64_t capacity, float *d_out_xyz,
+                                     int32_t *d_out_count, int32_t *d_nvox, void *d_workspace, size_t workspace_bytes, pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && d_out_xyz && d_out_count && d_nvox && d_workspace && b >= 0 && n >= 1 && capacity >= 1, PCP_ERR_INVALID,
+                "pcp_voxel_compact_f32: bad arguments");
+    PCP_REQUIRE(voxel > 0.f, PCP_ERR_INVALID, "pcp_voxel_compact_f32: voxel size must be > 0");
+    PCP_REQUIRE(n < 0xFFFFFFFFll && b <= 65535, PCP_ERR_UNSUPPORTED, "pcp_voxel_compact_f32: n or b too large");
+    if (b == 0) return PCP_OK;
+    VoxelWs w = carve(d_workspace, b, n);
+    PCP_REQUIRE(w.bytes <= workspace_bytes, PCP_ERR_INVALID, "pcp_voxel_compact_f32: workspace too small (%zu < %zu)", workspace_bytes, w.bytes);
+    cudaStream_t st = as_stream(stream);
+    const float ox = h_origin ? h_origin[0] : 0.f, oy = h_origin ? h_origin[1] : 0.f, oz = h_origin ? h_origin[2] : 0.f;
+    PCP_CUDA_OK(cudaMemsetAsync(w.bad, 0, (size_t)b * 4, st));
+    PCP_CUDA_OK(cudaMemsetAsync(w.origin_enc, 0xFF, (size_t)b * 12, st));
+    PCP_CUDA_OK(cudaMemsetAsync(w.max_enc, 0, (size_t)b * 12, st));
+    PCP_CUDA_OK(cudaMemsetAsync(w.need_sort, 0, 4, st));
+    const int vec_ok = ((reinterpret_cast<uintptr_t>(d_x) & 15u) == 0) && (n % 4 == 0);
+    static int occ_minmax = 0, occ_clear = 0, occ_mark = 0, occ_accum = 0, occ_fin = 0, occ_zero = 0;
+    const int64_t groups = vec_ok ? (n + 3) / 4 : n;
+    voxel_minmax_kernel<<<dim3(wave_gx(voxel_minmax_kernel, b, vec_ok ? (n * 3 / 4 + 2) / 3 : n, &occ_minmax), b), 256, 0, st>>>(d_x, n, w.origin_enc, w.max_enc, vec_ok);
+    PCP_CHECK_LAUNCH();
+    voxel_grid_kernel<<<(b + 127) / 128, 128, 0, st>>>(w.origin_enc, w.max_enc, b, ox, oy, oz, h_origin ? 0 : 1, voxel, w.cap_cells, w.grid, w.need_sort);
+    PCP_CHECK_LAUNCH();
+    voxel_clear_kernel<<<dim3(wave_gx(voxel_clear_kernel, b, (w.cap_cells >> 7) + 1, &occ_clear), b), 256, 0, st>>>(w.grid, w.cap_cells, w.bitmap, w.need_sort);
+    PCP_CHECK_LAUNCH();
+    voxel_mark_kernel<<<dim3(wave_gx(voxel_mark_kernel, b, groups, &occ_mark), b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.bad, w.need_sort, vec_ok);
+    PCP_CHECK_LAUNCH();
+    voxel_rank_kernel<<<b, 1024, 0, st>>>(w.bitmap, w.grid, w.cap_cells, n, w.word_rank, d_nvox, w.bad, w.sums, w.cnt, w.need_sort);
+    PCP_CHECK_LAUNCH();
+    voxel_zero_kernel<<<dim3(wave_gx(voxel_zero_kernel, b, n, &occ_zero), b), 256, 0, st>>>(n, d_nvox, w.sums, w.need_sort);
+    PCP_CHECK_LAUNCH();
+    voxel_accum_kernel<<<dim3(wave_gx(voxel_accum_kernel, b, groups, &occ_accum), b), 256, 0, st>>>(d_x, n, w.grid, voxel, w.cap_cells, w.bitmap, w.word_rank, w.sums, w.cnt, w.need_sort, vec_ok);
+    PCP_CHECK_LAUNCH();
+    voxel_finalize_compact_kernel<<<dim3(wave_gx(voxel_finalize_compact_kernel, b, std::min<int64_t>(n, capacity), &occ_fin), b), 256, 0, st>>>(
+        n, capacity, d_nvox, w.sums, d_out_xyz, d_out_count, w.need_sort);
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }

@@ -101,9 +101,53 @@ def resize_to_width(x: torch.Tensor, n_valid: torch.Tensor, width: int, seed: in
     return (y, lo) if labels is not None else y
 
 
-def voxel_downsample(x: torch.Tensor, voxel: float, origin=None):
-    """Voxel-grid downsample: returns (centroids (b, n, 3) padded, counts (b, n) int32, nvox (b,) int32)."""
+class VoxelGrid:
+    """Voxel-grid downsampler with caller-owned buffers (workspace, capacity-bounded outputs): every call is asynchronous on
+    the current stream, allocates nothing and reads nothing back (pcp_voxel_compact_f32).  `nvox` reports per cloud the
+    voxel count, -1 (cloud rejected: non-finite coordinate) or -2 (batch not covered by the bitmap path: use
+    voxel_downsample, which falls back to the general path)."""
+
+    def __init__(self, b: int, n: int, capacity: int | None = None, device="cuda", zero_fill: bool = False):
+        self.b, self.n, self.capacity = int(b), int(n), int(capacity if capacity is not None else n)
+        lib = _ffi.load()
+        nbytes = C.c_size_t(0)
+        _ffi.check(lib.pcp_voxel_workspace_bytes(self.b, self.n, C.byref(nbytes)))
+        self._ws_bytes = nbytes.value
+        self._ws = torch.empty((self._ws_bytes,), device=device, dtype=torch.uint8)
+        alloc = torch.zeros if zero_fill else torch.empty
+        self.centroids = alloc((self.b, self.capacity, 3), device=device, dtype=torch.float32)
+        self.counts = alloc((self.b, self.capacity), device=device, dtype=torch.int32)
+        self.nvox = torch.empty((self.b,), device=device, dtype=torch.int32)
+
+    def __call__(self, x: torch.Tensor, voxel: float, origin=None):
+        x = _chk_cloud(x)
+        assert tuple(x.shape[:2]) == (self.b, self.n), (x.shape, self.b, self.n)
+        org = None if origin is None else np.ascontiguousarray(np.asarray(origin, np.float32).reshape(3))
+        _ffi.check(_ffi.load().pcp_voxel_compact_f32(_ffi.ptr(x), self.b, self.n, _ffi.fptr(org), float(voxel), self.capacity, _ffi.ptr(self.centroids),
+                                                    _ffi.ptr(self.counts), _ffi.ptr(self.nvox), _ffi.ptr(self._ws), self._ws_bytes, _ffi.stream_ptr()))
+        return self.centroids, self.counts, self.nvox
+
+
+def voxel_downsample(x: torch.Tensor, voxel: float, origin=None, capacity: int | None = None):
+    """Voxel-grid downsample: returns (centroids (b, capacity, 3), counts (b, capacity) int32, nvox (b,) int32); rows past
+    nvox are zero; capacity defaults to n (a cloud cannot have more voxels than points).  Runs the bitmap path
+    (pcp_voxel_compact_f32) and, for grids it does not cover, the general sort path (pcp_voxel_f32) — that decision reads
+    nvox back, so this convenience form synchronises; VoxelGrid is the asynchronous form."""
     x = _chk_cloud(x)
+    b, n, _ = x.shape
+    cap = int(capacity if capacity is not None else n)
+    if b == 0 or n == 0:
+        return (torch.zeros((b, cap, 3), device=x.device), torch.zeros((b, cap), device=x.device, dtype=torch.int32),
+                torch.zeros((b,), device=x.device, dtype=torch.int32))
+    vg = VoxelGrid(b, n, cap, device=x.device, zero_fill=True)
+    out, cnt, nv = vg(x, voxel, origin)
+    if bool((nv == -2).any()):
+        return _voxel_general(x, voxel, origin, cap)
+    return out, cnt, nv
+
+
+def _voxel_general(x: torch.Tensor, voxel: float, origin, cap: int):
+    """pcp_voxel_f32: bitmap-rank path / radix-sort path, outputs padded to n rows per cloud."""
     b, n, _ = x.shape
     lib = _ffi.load()
     nbytes = C.c_size_t(0)
@@ -115,6 +159,11 @@ def voxel_downsample(x: torch.Tensor, voxel: float, origin=None):
     org = None if origin is None else np.ascontiguousarray(np.asarray(origin, np.float32).reshape(3))
     _ffi.check(lib.pcp_voxel_f32(_ffi.ptr(x), b, n, _ffi.fptr(org), float(voxel), _ffi.ptr(out), _ffi.ptr(cnt), _ffi.ptr(nv),
                                  _ffi.ptr(ws), nbytes.value, _ffi.stream_ptr()))
+    if cap < n:
+        out, cnt = out[:, :cap].contiguous(), cnt[:, :cap].contiguous()
+    elif cap > n:
+        out = torch.nn.functional.pad(out, (0, 0, 0, cap - n))
+        cnt = torch.nn.functional.pad(cnt, (0, cap - n))
     return out, cnt, nv
 
 

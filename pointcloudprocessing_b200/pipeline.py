@@ -11,7 +11,7 @@ from . import ops
 
 def voxel_resize(scans: torch.Tensor, voxel: float, width: int, seed: int = 0) -> torch.Tensor:
     """(b, N_raw, 3) CUDA scans -> (b, width, 3) voxel centroids, truncated / duplicate-padded per cloud."""
-    cen, _cnt, nvox = ops.voxel_downsample(scans, voxel)
+    cen, _cnt, nvox = ops.voxel_downsample(scans, voxel, capacity=width)          # only the first `width` voxels are ever read
     return ops.resize_to_width(cen, nvox, width, seed=seed)
 
 

@@ -191,6 +191,42 @@ def test_voxel_matches_oracle(lib, b, n, voxel, origin):
     assert cnt.sum(axis=1).tolist() == [n] * b
 
 
+def test_voxel_grid_caller_owned_capacity_bounded(lib):
+    """pcp_voxel_compact_f32 through ops.VoxelGrid: asynchronous, caller-owned workspace and outputs, rows past
+    min(nvox, capacity) untouched, buffers reusable across calls, truncation visible through nvox > capacity, -2 for a batch
+    the bitmap path does not cover (then pcp_voxel_f32 takes it)."""
+    from pointcloudprocessing_b200 import ops
+    b, n, cap = 5, 30000, 6000
+    vg = ops.VoxelGrid(b, n, cap)
+    truncated = covered = 0
+    for seed, voxel, origin in ((11, 0.7, None), (12, 0.9, (-2.0, -40.0, -12.0)), (13, 0.6, None), (14, 0.35, None)):
+        x = synth.lidar_scans(seed, b, n)
+        vg.centroids.fill_(-7.0); vg.counts.fill_(-7)
+        cent, cnt, nv = vg(_dev(x), voxel, origin)
+        cent, cnt, nv = cent.cpu().numpy(), cnt.cpu().numpy(), nv.cpu().numpy()
+        if (nv == -2).any():                          # bounding grid above 32 n cells: the whole batch is handed back untouched
+            assert (nv == -2).all() and (cent == -7.0).all() and (cnt == -7).all()
+            continue
+        covered += 1
+        for c in range(b):
+            rc, rn, _ = osm.voxel_downsample(x[c], voxel, origin)
+            v = rc.shape[0]
+            assert nv[c] == v
+            k = min(v, cap)
+            truncated += v > cap
+            assert np.array_equal(cent[c, :k], rc[:k]) and np.array_equal(cnt[c, :k], rn[:k])
+            assert (cent[c, k:] == -7.0).all() and (cnt[c, k:] == -7).all()
+    assert covered >= 3 and truncated > 0             # the capacity really was exceeded somewhere
+    # a grid outside the bitmap path (more than 32 n cells): 1 cm voxels on a 300-point cloud
+    vg2 = ops.VoxelGrid(2, 300, 300)
+    x = synth.lidar_scans(5, 2, 300)
+    _, _, nv = vg2(_dev(x), 0.01)
+    assert nv.cpu().numpy().tolist() == [-2, -2]
+    cent, cnt, nv = ops.voxel_downsample(_dev(x), 0.01)
+    rc, rn, _ = osm.voxel_downsample(x[1], 0.01)
+    assert int(nv[1]) == rc.shape[0] and np.array_equal(cent[1, :rc.shape[0]].cpu().numpy(), rc)
+
+
 def test_voxel_non_finite_point_flags_the_cloud(lib):
     """A NaN coordinate makes the cloud's voxel count -1 (oracle: ValueError) on either path; other clouds are unaffected."""
     from pointcloudprocessing_b200 import ops
