@@ -404,6 +404,32 @@ def main():
             del xw, yw
         del tm, xt, yt
 
+    if rank == 0 and not args.skip_extras:
+        # host-side ingest either side of the path: AftrBurner frame text of 8192 labelled points
+        from pointcloudprocessing_b200.pointcloud import aftr
+        rngf = np.random.default_rng(8192)
+        classes, parts = ["kc46", "f15"], ["wing", "fuselage", "engine", "boom", "tail", "stabilizer"]
+        fp = np.round(rngf.normal(0, 40, (8192, 3)), 3)
+        fl = np.stack([np.array(["kc46"] * 8192), np.array(parts)[rngf.integers(0, len(parts), 8192)]], 1)
+        text = aftr.format_aftr_frame(fp, fl)
+        t0 = time.perf_counter()
+        for _ in range(50):
+            aftr.parse_aftr_frame(text, classes, parts)
+        t_parse = (time.perf_counter() - t0) / 50
+        t0 = time.perf_counter()
+        for _ in range(20):
+            aftr.format_aftr_frame(fp, fl)
+        t_write = (time.perf_counter() - t0) / 20
+        t0 = time.perf_counter()
+        for _ in range(3):
+            onp.parse_aftr_frame_lines(text.decode(), {k: i for i, k in enumerate(classes)}, {k: i for i, k in enumerate(parts)})
+        t_ref = (time.perf_counter() - t0) / 3
+        extras["aftr_ingest"] = {"parse_frames_per_s": 1.0 / t_parse, "write_frames_per_s": 1.0 / t_write, "points_per_frame": 8192,
+                                 "frame_bytes": len(text), "threads": 1,
+                                 "cpu_baseline": {"value": 1.0 / t_ref, "unit": "frames/s", "cores": 1, "kind": "port",
+                                                  "sample": "3 frames, per-line Python loop of PointCloudSet.add_from_aftr_output (oracle/pointnet_numpy.py:parse_aftr_frame_lines)"},
+                                 "published_reference": {"value": 47.25, "unit": "frames/s", "source": "examples/pointnet_train.ipynb cell 6 (tqdm, other hardware, includes file I/O)"},
+                                 "note": "pcp_parse_aftr_frame / pcp_format_aftr_frame (csrc/host_io.cu), one host thread, text in memory"}
     if rank == 0:
         # roofline of the dominant kernel (chain_kernel: 3 launches per forward)
         chain_flops = 2.0 * MAC_TRUNK_PT * N_POINTS * B * K                     # algorithmic FLOPs of all timed chain launches

@@ -313,6 +313,14 @@ int pcp_parse_aftr_frame(const char *h_text, size_t bytes, const char *class_lab
                          double *h_xyz, int32_t *h_part, size_t capacity, size_t *count, int32_t *class_label,
                          size_t *h_nonfinite);
 
+/* Provizio.to_aftr_frame (point_cloud_toolkit/utils/Provizio.py:126-145): the AftrBurner frame text, one line
+ * "(x, y, z) label label ..." per point, every coordinate formatted like the reference's f-string (shortest round-trip
+ * digits, Python's positional / scientific rules).  h_points: n x 3 float32 (is_f64 == 0) or float64; h_label_ids:
+ * (n x labels_per_point) int32 indices into the '\n'-separated label_table_nl (labels_per_point == 0: no labels).  The text
+ * goes to h_out (capacity bytes), its length to *len; PCP_ERR_NOMEM with the size needed in *len when capacity is too small. */
+int pcp_format_aftr_frame(const void *h_points, int is_f64, size_t n, const int32_t *h_label_ids, int labels_per_point,
+                          const char *label_table_nl, char *h_out, size_t capacity, size_t *len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -325,3 +325,27 @@ def rotate(x, R):
         c = (x[..., 2] * R[:, None, j, 2]).astype(F32)
         out[..., j] = ((a + bb).astype(F32) + c).astype(F32)
     return out
+
+
+def parse_aftr_frame_lines(text: str, class_labels: dict, part_labels: dict):
+    """ORACLE (timed CPU baseline of the ingest path): the per-line loop of PointCloudSet.add_from_aftr_output
+    (PCA/pointcloud/PointCloudSet.py:161-198) restated for one frame's text: strip, split the "(x, y, z)" part on ',',
+    float() each value, split the labels on ' ', np.isfinite per point.  Returns (obs (N,3) float64, class index, part (N,))."""
+    obs, cl, pl = [], None, []
+    for line in text.splitlines():
+        line = line.strip()
+        a, b = line.find('('), line.find(')')
+        pos = [float(v) for v in line[a + 1:b].split(',')]
+        labels = [l for l in line[b + 1:].split(" ") if len(l) > 1]
+        if len(labels) == 2:
+            if labels[0] not in class_labels:
+                raise Exception(f"Class label {labels[0]} not known")
+            if labels[1] not in part_labels:
+                raise Exception(f"Part label {labels[1]} not known")
+        else:
+            raise Exception(f"Dataset must contain both a class label and part label. {labels} is not correct.")
+        if np.isfinite(np.array(pos)).all():
+            obs.append(np.array(pos))
+            cl = class_labels.get(labels[0], -1)
+            pl.append(part_labels.get(labels[1], -1))
+    return np.array(obs), cl, np.array(pl)

@@ -7,7 +7,10 @@
 //       pointcloud/PointCloudSet.py:161-198 (~47 frames/s in the reference's pure-Python loop)
 #include <cmath>
 #include <cstdlib>
+#include <algorithm>
+#include <charconv>
 #include <cstring>
+#include <vector>
 
 #include "common.cuh"
 
@@ -271,14 +274,25 @@ extern "C" int pcp_parse_aftr_frame(const char *h_text, size_t bytes, const char
         while (q <= rp) {
             const char *c = q;
             while (c < rp && *c != ',') ++c;
-            char buf[64];
-            size_t l = (size_t)(c - q);
-            if (l >= sizeof(buf)) { set_error("coordinate token too long"); return PCP_ERR_INVALID; }
-            memcpy(buf, q, l); buf[l] = 0;
-            char *ep = nullptr;
-            const double v = strtod(buf, &ep);
-            while (ep && (*ep == ' ' || *ep == '\t')) ++ep;
-            if (ep == buf || (ep && *ep)) { set_error("could not convert string to float: '%s'", buf); return PCP_ERR_INVALID; }
+            double v;
+            {
+                // fast path: plain decimal / scientific digits (std::from_chars, no locale); everything else float() accepts
+                // (sign '+', inf / nan spellings, surrounding blanks) goes through strtod below
+                const char *a = q, *z = c;
+                while (a < z && *a == ' ') ++a;
+                while (z > a && z[-1] == ' ') --z;
+                auto fr = std::from_chars(a, z, v);
+                if (fr.ec != std::errc() || fr.ptr != z || a == z) {
+                    char buf[64];
+                    size_t l = (size_t)(c - q);
+                    if (l >= sizeof(buf)) { set_error("coordinate token too long"); return PCP_ERR_INVALID; }
+                    memcpy(buf, q, l); buf[l] = 0;
+                    char *ep = nullptr;
+                    v = strtod(buf, &ep);
+                    while (ep && (*ep == ' ' || *ep == '\t')) ++ep;
+                    if (ep == buf || (ep && *ep)) { set_error("could not convert string to float: '%s'", buf); return PCP_ERR_INVALID; }
+                }
+            }
             if (np < 3) pos[np] = v;
             ++np;
             q = c + 1;
@@ -287,21 +301,33 @@ extern "C" int pcp_parse_aftr_frame(const char *h_text, size_t bytes, const char
         if (np != 3) { set_error("frame line has %d coordinates, expected 3", np); return PCP_ERR_INVALID; }
         // labels: split on ' ', keep tokens longer than one character
         const char *tok[3]; size_t tlen[3]; int nt = 0;
-        char shown[192]; size_t ns = 0;                                   // the token list as Python prints it, for the message below
         q = rp + 1;
         while (q <= le) {
             const char *c = q;
             while (c < le && *c != ' ') ++c;
             if (c - q > 1) {
                 if (nt < 3) { tok[nt] = q; tlen[nt] = (size_t)(c - q); }
-                const int w = snprintf(shown + ns, sizeof(shown) - ns, "%s'%.*s'", nt ? ", " : "", (int)(c - q), q);
-                if (w > 0) ns = ns + (size_t)w < sizeof(shown) ? ns + (size_t)w : sizeof(shown) - 1;
                 ++nt;
             }
             q = c + 1;
         }
-        shown[ns] = 0;
-        if (nt != 2) { set_error("Dataset must contain both a class label and part label. [%s] is not correct.", shown); return PCP_ERR_INVALID; }
+        if (nt != 2) {
+            char shown[192]; size_t ns = 0; int k = 0;                    // the token list as Python prints it (error path only)
+            q = rp + 1;
+            while (q <= le) {
+                const char *c = q;
+                while (c < le && *c != ' ') ++c;
+                if (c - q > 1) {
+                    const int w = snprintf(shown + ns, sizeof(shown) - ns, "%s'%.*s'", k ? ", " : "", (int)(c - q), q);
+                    if (w > 0) ns = ns + (size_t)w < sizeof(shown) ? ns + (size_t)w : sizeof(shown) - 1;
+                    ++k;
+                }
+                q = c + 1;
+            }
+            shown[ns] = 0;
+            set_error("Dataset must contain both a class label and part label. [%s] is not correct.", shown);
+            return PCP_ERR_INVALID;
+        }
         const int ci = lookup(class_labels_nl, tok[0], tlen[0]);
         if (ci < 0) { set_error("Class label %.*s not known", (int)tlen[0], tok[0]); return PCP_ERR_INVALID; }
         const int pi = lookup(part_labels_nl, tok[1], tlen[1]);
@@ -319,5 +345,105 @@ extern "C" int pcp_parse_aftr_frame(const char *h_text, size_t bytes, const char
     *count = n;
     *class_label = cls;
     if (h_nonfinite) *h_nonfinite = bad;
+    return PCP_OK;
+}
+
+// ---- AftrBurner frame writer: Provizio.to_aftr_frame (point_cloud_toolkit/utils/Provizio.py:126-145) ----
+// One line per point: "(x, y, z)" followed by " label" for each of the point's labels.  The reference formats every
+// coordinate with an f-string, i.e. repr of a Python float — for float32 points too: numpy's scalar __format__ hands the
+// value to float.__format__, so a float32 prints with the digits of its DOUBLE value (9.999999747378752e-05 for
+// np.float32(1e-4); pinned by tests/golden/aftr_frames.npz, written by the reference's own function).  repr: shortest digits
+// that read back to the same double, positional notation for 1e-4 <= |v| < 1e16 (with a trailing ".0" on integers),
+// scientific otherwise (mantissa, 'e', sign, at least two exponent digits), "nan" / "inf".
+namespace pcp {
+
+template <typename T>
+static char *fmt_py_float(char *out, T v)
+{
+    if (std::isnan(v)) { memcpy(out, "nan", 3); return out + 3; }
+    if (std::isinf(v)) { if (v < 0) *out++ = '-'; memcpy(out, "inf", 3); return out + 3; }
+    if (v == 0) { if (std::signbit(v)) *out++ = '-'; memcpy(out, "0.0", 3); return out + 3; }
+    char sci[64];
+    auto r = std::to_chars(sci, sci + sizeof(sci) - 1, v, std::chars_format::scientific);     // shortest round trip: d[.ddd]e[+-]XX
+    *r.ptr = 0;
+    char *e = sci;
+    while (e < r.ptr && *e != 'e') ++e;
+    const int exp10 = atoi(e + 1);
+    const char *s = sci;
+    if (*s == '-') { *out++ = '-'; ++s; }
+    char digits[40];
+    int nd = 0;
+    for (const char *q = s; q < e; ++q) if (*q != '.') digits[nd++] = *q;
+    if (exp10 >= -4 && exp10 < 16) {
+        if (exp10 < 0) {
+            *out++ = '0'; *out++ = '.';
+            for (int i = 0; i < -exp10 - 1; ++i) *out++ = '0';
+            memcpy(out, digits, nd); out += nd;
+        } else {
+            for (int i = 0; i <= exp10; ++i) *out++ = i < nd ? digits[i] : '0';
+            *out++ = '.';
+            if (nd > exp10 + 1) { memcpy(out, digits + exp10 + 1, nd - exp10 - 1); out += nd - exp10 - 1; }
+            else *out++ = '0';
+        }
+    } else {
+        *out++ = digits[0];
+        if (nd > 1) { *out++ = '.'; memcpy(out, digits + 1, nd - 1); out += nd - 1; }
+        *out++ = 'e';
+        *out++ = exp10 < 0 ? '-' : '+';
+        const int a = exp10 < 0 ? -exp10 : exp10;
+        if (a < 10) *out++ = '0';
+        auto r2 = std::to_chars(out, out + 8, a);
+        out = r2.ptr;
+    }
+    return out;
+}
+
+}  // namespace pcp
+
+// h_points: n x 3, float32 (is_f64 == 0) or float64.  Labels: h_label_ids (n x labels_per_point) int32 indices into the
+// '\n'-separated label_table_nl (labels_per_point == 0: none).  Writes the text into h_out (capacity bytes) and its length
+// into *len; when the buffer is too small nothing useful is written, *len is the size needed and PCP_ERR_NOMEM is returned.
+extern "C" int pcp_format_aftr_frame(const void *h_points, int is_f64, size_t n, const int32_t *h_label_ids, int labels_per_point,
+                                     const char *label_table_nl, char *h_out, size_t capacity, size_t *len)
+{
+    PCP_REQUIRE(len && (n == 0 || h_points) && labels_per_point >= 0 && (labels_per_point == 0 || (h_label_ids && label_table_nl)), PCP_ERR_INVALID,
+                "pcp_format_aftr_frame: bad arguments");
+    std::vector<std::pair<const char *, size_t>> table;
+    size_t longest = 0;
+    if (labels_per_point > 0) {
+        const char *s = label_table_nl;
+        for (;;) {
+            const char *e = strchr(s, '\n');
+            const size_t l = e ? (size_t)(e - s) : strlen(s);
+            table.emplace_back(s, l);
+            longest = std::max(longest, l);
+            if (!e) break;
+            s = e + 1;
+        }
+    }
+    const size_t per_line = 3 * 32 + 8 + (size_t)labels_per_point * (longest + 1);
+    const size_t need = n * per_line + 1;
+    *len = need;
+    if (!h_out || capacity < need) { set_error("pcp_format_aftr_frame: buffer of %zu bytes needed", need); return PCP_ERR_NOMEM; }
+    char *o = h_out;
+    const float *pf = reinterpret_cast<const float *>(h_points);
+    const double *pd = reinterpret_cast<const double *>(h_points);
+    for (size_t i = 0; i < n; ++i) {
+        *o++ = '(';
+        for (int a = 0; a < 3; ++a) {
+            o = fmt_py_float(o, is_f64 ? pd[3 * i + a] : (double)pf[3 * i + a]);
+            if (a < 2) { *o++ = ','; *o++ = ' '; }
+        }
+        *o++ = ')';
+        for (int k = 0; k < labels_per_point; ++k) {
+            const int32_t id = h_label_ids[i * (size_t)labels_per_point + k];
+            PCP_REQUIRE(id >= 0 && (size_t)id < table.size(), PCP_ERR_INVALID, "pcp_format_aftr_frame: label id %d out of range at point %zu", id, i);
+            *o++ = ' ';
+            memcpy(o, table[id].first, table[id].second);
+            o += table[id].second;
+        }
+        *o++ = '\n';
+    }
+    *len = (size_t)(o - h_out);
     return PCP_OK;
 }

@@ -111,9 +111,26 @@ class PointCloudSet:
         else:
             raise Exception(f"No state info found in {dir_path}")
         self._print(f"Parsing frames in {dir_path}...")
-        for i in range(len(lidar_contents)):
+        # frames are parsed natively on a small thread pool (ctypes releases the GIL), 64 at a time, and consumed in frame
+        # order, so the accepted frames, the messages and their order are those of the reference's sequential loop
+        from concurrent.futures import ThreadPoolExecutor
+
+        def _try_parse(i):
             try:
-                obs, cl, pl, _bad = self._parse_frame_file(f'{dir_path}/Lidar/frame_{i}.txt')
+                return self._parse_frame_file(f'{dir_path}/Lidar/frame_{i}.txt')
+            except Exception as e:                                                       # re-raised in order below
+                return e
+        n_frames = len(lidar_contents)
+        pool = ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1))
+        parsed = {}
+        for i in range(n_frames):
+            if i % 64 == 0:
+                parsed = dict(zip(range(i, min(i + 64, n_frames)), pool.map(_try_parse, range(i, min(i + 64, n_frames)))))
+            try:
+                res = parsed.pop(i)
+                if isinstance(res, Exception):
+                    raise res
+                obs, cl, pl, _bad = res
                 if len(obs) != 0:
                     se = state_info[i]['tanker_in_sensor_frame'][:3, :3]
                     obs, pl = self._adjust_to_input_width(obs, pl)
@@ -125,6 +142,7 @@ class PointCloudSet:
                 if frames_searched == 0:
                     frames_searched = i
                 self._print(f"Failed to add file {dir_path}/Lidar/frame_{i}.txt:\n\t{type(e).__name__} : {e}")
+        pool.shutdown()
         self.add_data(dir_path.rstrip("/").split("/")[-1], np.array(observations), np.array(class_labels), np.array(part_labels), np.array(se3),
                       shuffle_points)
         return True
