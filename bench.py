@@ -430,6 +430,31 @@ def main():
                                                   "sample": "3 frames, per-line Python loop of PointCloudSet.add_from_aftr_output (oracle/pointnet_numpy.py:parse_aftr_frame_lines)"},
                                  "published_reference": {"value": 47.25, "unit": "frames/s", "source": "examples/pointnet_train.ipynb cell 6 (tqdm, other hardware, includes file I/O)"},
                                  "note": "pcp_parse_aftr_frame / pcp_format_aftr_frame (csrc/host_io.cu), one host thread, text in memory"}
+    if rank == 0 and not args.skip_extras:
+        # input pipeline of the training step: records/s of PointCloudSet.get_train_set(device=...) at C3's shape
+        import tempfile
+        from pointcloudprocessing_b200.pointcloud.PointCloudSet import PointCloudSet
+        with tempfile.TemporaryDirectory() as dtmp:
+            pcs = PointCloudSet("bench", {f"c{i}": i for i in range(C_CLASSES)}, {f"p{i}": i for i in range(P_PARTS)}, N_POINTS,
+                                jitter_stdev_m=np.array([0.1, 0.1, 0.1]), val=0.1, test=0.05, batch_size=256, rand_seed=5,
+                                print_func=lambda *a, **k: None, data_path=dtmp + "/")
+            rngd = np.random.default_rng(0)
+            for sidx in range(2):
+                pcs.add_data(f"set{sidx}", rngd.normal(0, 30, (1024, N_POINTS, 3)), rngd.integers(0, C_CLASSES, 1024), rngd.integers(0, P_PARTS, (1024, N_POINTS)),
+                             np.tile(np.eye(3), (1024, 1, 1)), shuffle_points=False)
+            itd = pcs.get_train_set(device=dev)
+            for _ in range(3):
+                next(itd)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(30):
+                next(itd)
+            torch.cuda.synchronize()
+            dt_it = (time.perf_counter() - t0) / 30
+            itd.close()
+        extras["input_pipeline"] = {"value": 256 / dt_it, "unit": "clouds/s", "ms_per_batch": dt_it * 1e3, "batch": 256, "points": N_POINTS,
+                                    "consumed_by_train_c3": extras["train_c3"]["value"] / world,
+                                    "note": "TFRecord (mmap) -> reference record order -> native batch decode on host threads -> pinned ring -> H2D on a copy stream -> jitter on the device"}
     if rank == 0:
         # roofline of the dominant kernel (chain_kernel: 3 launches per forward)
         chain_flops = 2.0 * MAC_TRUNK_PT * N_POINTS * B * K                     # algorithmic FLOPs of all timed chain launches

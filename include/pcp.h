@@ -307,6 +307,12 @@ int pcp_tfrecord_scan(const uint8_t *h_buf, size_t bytes, int verify_crc, uint64
  * observations float[width*3], class_label int64, part_labels int64[width] (written as int32), se3 float[9]. */
 int pcp_example_decode(const uint8_t *h_rec, size_t bytes, int64_t width, float *h_obs, int64_t *h_class_label,
                        int32_t *h_part_labels, float *h_se3);
+/* `count` records decoded by `threads` host threads straight into one batch — the map(parse, AUTOTUNE) + batch() stage of
+ * the reference's tf.data pipeline (pointcloud/PointCloudSet.py:347-363): h_obs (count, width, 3) f32, h_class_labels
+ * (count) i32, h_part_labels (count, width) i32, h_se3 (count, 3, 3) f32; h_recs / h_lengths: payload pointer and length of
+ * every record (e.g. into memory-mapped TFRecord files indexed by pcp_tfrecord_scan). */
+int pcp_example_decode_batch(const uint8_t *const *h_recs, const uint64_t *h_lengths, int count, int64_t width, float *h_obs,
+                             int32_t *h_class_labels, int32_t *h_part_labels, float *h_se3, int threads);
 /* Parse one AftrBurner frame text ("(x, y, z) class part" per line) with the semantics of
  * PointCloudSet.add_from_aftr_output (pointcloud/PointCloudSet.py:161-198).  Label lists are '\n'-separated. */
 int pcp_parse_aftr_frame(const char *h_text, size_t bytes, const char *class_labels_nl, const char *part_labels_nl,

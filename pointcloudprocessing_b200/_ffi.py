@@ -112,6 +112,7 @@ SIGNATURES = {
     "pcp_crc32c_masked": (_u32, [_vp, _sz]),
     "pcp_tfrecord_scan": (_i32, [_vp, _sz, _i32, _vp, _vp, _sz, C.POINTER(_sz)]),
     "pcp_example_decode": (_i32, [_vp, _sz, _i64, _vp, C.POINTER(_i64), _vp, _vp]),
+    "pcp_example_decode_batch": (_i32, [_vp, _vp, _i32, _i64, _vp, _vp, _vp, _vp, _i32]),
     "pcp_parse_aftr_frame": (_i32, [C.c_char_p, _sz, C.c_char_p, C.c_char_p, _vp, _vp, _sz, C.POINTER(_sz), C.POINTER(_i32), C.POINTER(_sz)]),
     "pcp_format_aftr_frame": (_i32, [_vp, _i32, _sz, _vp, _i32, C.c_char_p, _vp, _sz, C.POINTER(_sz)]),
     "pcp_model_get_grad": (_i32, [_vp, C.c_char_p, _fp, _sz]),

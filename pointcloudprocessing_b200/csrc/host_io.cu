@@ -447,3 +447,44 @@ extern "C" int pcp_format_aftr_frame(const void *h_points, int is_f64, size_t n,
     *len = (size_t)(o - h_out);
     return PCP_OK;
 }
+
+// ---- batch decode: the map(parse, num_parallel_calls = AUTOTUNE) + batch() stage of the reference's tf.data pipeline
+// (pointcloud/PointCloudSet.py:347-363) — `count` records decoded by `threads` host threads straight into one batch ----
+#include <atomic>
+#include <thread>
+
+extern "C" int pcp_example_decode_batch(const uint8_t *const *h_recs, const uint64_t *h_lengths, int count, int64_t width, float *h_obs,
+                                        int32_t *h_class_labels, int32_t *h_part_labels, float *h_se3, int threads)
+{
+    PCP_REQUIRE(count >= 0 && width >= 1 && (count == 0 || (h_recs && h_lengths && h_obs && h_class_labels && h_part_labels && h_se3)), PCP_ERR_INVALID,
+                "pcp_example_decode_batch: bad arguments");
+    if (count == 0) return PCP_OK;
+    const int nt = std::max(1, std::min(threads, count));
+    std::atomic<int> next{0}, failed{-1};
+    std::string first_error;
+    std::atomic_flag err_lock = ATOMIC_FLAG_INIT;
+    auto work = [&]() {
+        for (;;) {
+            const int i = next.fetch_add(1);
+            if (i >= count || failed.load() >= 0) return;
+            int64_t cl = 0;
+            const int rc = pcp_example_decode(h_recs[i], (size_t)h_lengths[i], width, h_obs + (size_t)i * width * 3, &cl, h_part_labels + (size_t)i * width,
+                                              h_se3 + (size_t)i * 9);
+            h_class_labels[i] = (int32_t)cl;
+            if (rc != PCP_OK) {
+                while (err_lock.test_and_set()) {}
+                if (failed.load() < 0) { failed.store(i); first_error = pcp_last_error(); }      // the message is thread-local: carry it over
+                err_lock.clear();
+            }
+        }
+    };
+    if (nt == 1) work();
+    else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nt - 1; ++t) pool.emplace_back(work);
+        work();
+        for (auto &t : pool) t.join();
+    }
+    if (failed.load() >= 0) { set_error("record %d of the batch: %s", failed.load(), first_error.c_str()); return PCP_ERR_INVALID; }
+    return PCP_OK;
+}

@@ -182,67 +182,179 @@ class PointCloudSet:
         files = sorted(glob.glob(f"{self._data_path}{self._name}/*/{split}_*.tfrecord"))
         return [tfrecord.TFRecordFile(f) for f in files]
 
-    def _dataset(self, split: str, device=None, seed=None, jitter: bool = True, repeat: bool = True, shuffle_buffer: int = 2048):
-        """shuffle(2048) -> repeat -> parse (+ jitter) -> batch, as PointCloudSet.py:347-363.  Yields
-        (x (b,n,3) float32, {'classification_output' (b,), 'segmentation_output' (b,n), 'se3' (b,3,3)})."""
+    def _record_stream(self, split: str, recs, rng, repeat: bool, shuffle_buffer: int):
+        """(file index, record index) in the order the reference's pipeline hands records to batch() (PointCloudSet.py:341-391):
+        list_files (file order reshuffled on every pass) -> train: interleave(cycle_length=2), one record from each of two
+        open files in turn, the next file taking the place of an exhausted one; val / test: files read one after another
+        -> shuffle(2048) -> repeat (the shuffle buffer drains at the end of a pass: every record exactly once per pass)."""
+        def one_pass():
+            files = [fi for fi in range(len(recs)) if len(recs[fi])]
+            rng.shuffle(files)
+            if split != 'train':
+                for fi in files:
+                    for ri in range(len(recs[fi])):
+                        yield fi, ri
+                return
+            pending = list(files)
+            slots = [[pending.pop(0), 0] for _ in range(min(2, len(pending)))]
+            while slots:
+                for sl in list(slots):
+                    fi, ri = sl
+                    yield fi, ri
+                    sl[1] += 1
+                    if sl[1] >= len(recs[fi]):
+                        if pending:
+                            sl[0], sl[1] = pending.pop(0), 0
+                        else:
+                            slots.remove(sl)
+        while True:
+            buf = []
+            for item in one_pass():
+                buf.append(item)
+                if len(buf) >= shuffle_buffer:
+                    j = int(rng.integers(len(buf)))
+                    buf[j], buf[-1] = buf[-1], buf[j]
+                    yield buf.pop()
+            while buf:
+                j = int(rng.integers(len(buf)))
+                buf[j], buf[-1] = buf[-1], buf[j]
+                yield buf.pop()
+            if not repeat:
+                return
+
+    def _dataset(self, split: str, device=None, seed=None, jitter: bool = True, repeat: bool = True, shuffle_buffer: int = 2048,
+                 prefetch: int = 3, decode_threads: int | None = None):
+        """list_files -> [interleave] -> shuffle(2048) -> repeat -> map(parse + jitter, AUTOTUNE) -> batch -> prefetch(AUTOTUNE),
+        as PointCloudSet.py:341-391.  Yields (x (b,n,3) float32, {'classification_output' (b,), 'segmentation_output' (b,n),
+        'se3' (b,3,3)}).  Records are decoded a batch at a time by native host threads (pcp_example_decode_batch) out of the
+        memory-mapped TFRecord files.  With a device, a producer thread decodes into a ring of `prefetch` PINNED host slots and
+        issues the host-to-device copies on its own stream, so decoding and copying batch k + 1 overlap the training step on
+        batch k; the Gaussian jitter of _parse_function (:335-337) runs on the device (pcp_jitter_f32)."""
         recs = self._records(split)
-        order = [(fi, ri) for fi, r in enumerate(recs) for ri in range(len(r))]
-        if not order:
+        if not any(len(r) for r in recs):
             return
         w, bs = self._network_input_width, self._batch_size
         rng = np.random.default_rng(self._random_seed if seed is None else seed)
         use_jitter = jitter and bool(np.any(self._jitter_stdev_m != 0))
         if use_jitter and device is None:
             raise RuntimeError("jitter runs on the GPU (pcp_jitter_f32): pass device='cuda' (there is no CPU compute path)")
+        nthreads = decode_threads if decode_threads is not None else max(1, min(8, (os.cpu_count() or 2) // 2))
+        lib = _ffi.load()
+        stream_it = self._record_stream(split, recs, rng, repeat, shuffle_buffer)
+        ptrs = np.empty(bs, np.uint64)
+        lens = np.empty(bs, np.uint64)
 
-        def shuffled():
-            # dataset.shuffle(2048).repeat(): the shuffle buffer is drained at the end of every pass, so each pass sees
-            # every record exactly once (PointCloudSet.py:356-357)
-            while True:
-                buf = []
-                for item in order:
-                    buf.append(item)
-                    if len(buf) >= shuffle_buffer:
-                        j = int(rng.integers(len(buf)))
-                        buf[j], buf[-1] = buf[-1], buf[j]
-                        yield buf.pop()
-                while buf:
-                    j = int(rng.integers(len(buf)))
-                    buf[j], buf[-1] = buf[-1], buf[j]
-                    yield buf.pop()
-                if not repeat:
-                    return
-
-        step = 0
-        it = shuffled()
-        while True:
-            x = np.empty((bs, w, 3), np.float32)
-            ycls = np.empty((bs,), np.int32)
-            yseg = np.empty((bs, w), np.int32)
-            yse3 = np.empty((bs, 3, 3), np.float32)
+        def fill(x, ycls, yseg, yse3) -> int:
+            """next batch of records decoded into the given (bs, ...) host arrays; returns the number of records"""
             k = 0
-            for fi, ri in it:
-                ycls[k] = recs[fi].decode_into(ri, w, x[k], yseg[k], yse3[k])
+            for fi, ri in stream_it:
+                ptrs[k], lens[k] = recs[fi].record_ptr(ri)
                 k += 1
                 if k == bs:
                     break
-            if k == 0:
-                return
-            x, ycls, yseg, yse3 = x[:k], ycls[:k], yseg[:k], yse3[:k]
-            labels = {'classification_output': ycls, 'segmentation_output': yseg, 'se3': yse3}
-            if device is not None:
-                import torch
-                from .. import ops
-                xd = torch.from_numpy(x).to(device, non_blocking=True)
-                if use_jitter:
-                    xd = ops.jitter(xd, self._jitter_stdev_m, seed=(self._random_seed or 0) + 1, offset=step * bs * w)
-                labels = {kk: torch.from_numpy(v).to(device, non_blocking=True) for kk, v in labels.items()}
+            if k:
+                _ffi.check(lib.pcp_example_decode_batch(_ffi.ptr(ptrs), _ffi.ptr(lens), k, w, _ffi.ptr(x), _ffi.ptr(ycls), _ffi.ptr(yseg), _ffi.ptr(yse3), nthreads))
+            return k
+
+        if device is None:
+            while True:
+                x = np.empty((bs, w, 3), np.float32)
+                ycls = np.empty((bs,), np.int32)
+                yseg = np.empty((bs, w), np.int32)
+                yse3 = np.empty((bs, 3, 3), np.float32)
+                k = fill(x, ycls, yseg, yse3)
+                if k == 0:
+                    return
+                yield x[:k], {'classification_output': ycls[:k], 'segmentation_output': yseg[:k], 'se3': yse3[:k]}
+                if k < bs:
+                    return
+        yield from self._device_batches(fill, device, use_jitter, max(2, int(prefetch)), split)
+
+    def _device_batches(self, fill, device, use_jitter: bool, depth: int, split: str):
+        """prefetch(AUTOTUNE) onto the GPU: see _dataset."""
+        import queue
+        import threading
+
+        import torch
+        from .. import ops
+        w, bs = self._network_input_width, self._batch_size
+        dev = torch.device(device)
+        if dev.type == "cuda" and dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        copy_stream = torch.cuda.Stream(device=dev)
+
+        class Slot:
+            pass
+        slots = []
+        for _ in range(depth):
+            sl = Slot()
+            sl.h = (torch.empty((bs, w, 3), dtype=torch.float32).pin_memory(), torch.empty((bs,), dtype=torch.int32).pin_memory(),
+                    torch.empty((bs, w), dtype=torch.int32).pin_memory(), torch.empty((bs, 3, 3), dtype=torch.float32).pin_memory())
+            sl.d = tuple(torch.empty_like(t, device=dev) for t in sl.h)
+            sl.copied = torch.cuda.Event()
+            sl.released = None                     # event on the consumer's stream: the device buffers may be overwritten after it
+            slots.append(sl)
+        free_q, ready_q = queue.Queue(), queue.Queue(maxsize=depth)
+        for sl in slots:
+            free_q.put(sl)
+        stop = threading.Event()
+
+        def producer():
+            try:
+                torch.cuda.set_device(dev)
+                while not stop.is_set():
+                    sl = free_q.get()
+                    if sl is None:
+                        return
+                    k = fill(*(t.numpy() for t in sl.h))
+                    if k == 0:
+                        ready_q.put((None, 0))
+                        return
+                    with torch.cuda.stream(copy_stream):
+                        if sl.released is not None:
+                            copy_stream.wait_event(sl.released)
+                        for hd, dd in zip(sl.h, sl.d):
+                            dd[:k].copy_(hd[:k], non_blocking=True)
+                        sl.copied.record(copy_stream)
+                    sl.copied.synchronize()        # the pinned slot is refilled next time round: its copy must have left the host
+                    ready_q.put((sl, k))
+                    if k < bs:
+                        ready_q.put((None, 0))
+                        return
+            except BaseException as e:             # surfaced to the consumer
+                ready_q.put((e, -1))
+
+        th = threading.Thread(target=producer, name=f"pcs-prefetch-{split}", daemon=True)
+        th.start()
+        # jitter stream: keyed by the set's seed, the split and — for an unseeded set, where the reference draws fresh
+        # tf.random.normal noise on every run — a nonce from the OS; the counter is the global point index of the iterator
+        base = self._random_seed if isinstance(self._random_seed, int) else int.from_bytes(os.urandom(6), "little")
+        seed_base = base + 1 + {"train": 0, "val": 1_000_003, "test": 2_000_003}.get(split, 0)
+        step = 0
+        prev = None
+        try:
+            while True:
+                sl, k = ready_q.get()
+                if prev is not None:               # the consumer has moved on: everything it enqueued on `prev` precedes this event
+                    prev.released = torch.cuda.Event()
+                    prev.released.record(torch.cuda.current_stream(dev))
+                    free_q.put(prev)
+                    prev = None
+                if k < 0:
+                    raise sl
+                if sl is None:
+                    return
+                torch.cuda.current_stream(dev).wait_event(sl.copied)
+                xd, ycls, yseg, yse3 = (t[:k] for t in sl.d)
+                # the caller gets tensors of its own (like tf.data): the ring's device buffers are recycled behind its back
+                xd = ops.jitter(xd, self._jitter_stdev_m, seed=seed_base, offset=step * bs * w) if use_jitter else xd.clone()
+                labels = {'classification_output': ycls.clone(), 'segmentation_output': yseg.clone(), 'se3': yse3.clone()}
+                prev = sl
+                step += 1
                 yield xd, labels
-            else:
-                yield x, labels
-            step += 1
-            if k < bs:
-                return
+        finally:
+            stop.set()
+            free_q.put(None)
 
     def get_train_set(self, device=None, **kw):
         return self._dataset('train', device=device, **kw)

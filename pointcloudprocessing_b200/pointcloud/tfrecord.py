@@ -11,6 +11,8 @@ from __future__ import annotations
 import ctypes as C
 import struct
 
+import os
+
 import numpy as np
 
 from .. import _ffi
@@ -89,7 +91,8 @@ class TFRecordFile:
     def __init__(self, path: str, verify_crc: int = 2):
         self._lib = _ffi.load()
         self.path = path
-        self.buf = np.fromfile(path, np.uint8)
+        # mapped, not read: a kc46-sized split is ~1.5 GB per process, and every rank opens every file
+        self.buf = np.memmap(path, np.uint8, 'r') if os.path.getsize(path) > 0 else np.empty(0, np.uint8)
         cnt = C.c_size_t()
         _ffi.check(self._lib.pcp_tfrecord_scan(_ffi.ptr(self.buf), self.buf.size, 0, None, None, 0, C.byref(cnt)))
         self.offsets = np.empty(cnt.value, np.uint64)
@@ -111,6 +114,10 @@ class TFRecordFile:
         o, l = int(self.offsets[i]), int(self.lengths[i])
         _ffi.check(self._lib.pcp_example_decode(C.c_void_p(self.buf.ctypes.data + o), l, width, _ffi.ptr(obs), C.byref(cl), _ffi.ptr(part), _ffi.ptr(se3)))
         return int(cl.value)
+
+    def record_ptr(self, i: int):
+        """(address, length) of record i's payload inside the mapped file (for pcp_example_decode_batch)."""
+        return self.buf.ctypes.data + int(self.offsets[i]), int(self.lengths[i])
 
     def decode(self, i: int, width: int):
         obs = np.empty((width, 3), np.float32)
