@@ -143,6 +143,10 @@ typedef struct pcp_model pcp_model;
 
 #define PCP_PRECISION_FP32 0   /* CUDA-core fp32 FMA path: the 1e-3 contract */
 #define PCP_PRECISION_BF16 1   /* tcgen05 kind::f16, bf16 operands, fp32 accumulate in TMEM: the 2e-2 contract */
+#define PCP_PRECISION_FP32_TC 2 /* the 1e-3 contract ON the tensor cores: every layer product evaluated as three bf16 tcgen05 products
+                                  hi(A) hi(W) + hi(A) lo(W) + lo(A) hi(W) (hi = bf16(x), lo = bf16(x - hi): ~16 mantissa bits — more than
+                                  TF32's 10), fp32 accumulation in TMEM, fp32 activations between layers.  Inference only: training
+                                  steps of such a model run the fp32 CUDA-core path. */
 
 #define PCP_HEAD_CLS 1u        /* classification_output */
 #define PCP_HEAD_SEG 2u        /* segmentation_output   */

@@ -14,6 +14,7 @@ _lib = None
 
 PRECISION_FP32 = 0
 PRECISION_BF16 = 1
+PRECISION_FP32_TC = 2
 HEAD_CLS = 1
 HEAD_SEG = 2
 GROUP_SHARED, GROUP_INPUT_TRANSFORM, GROUP_CLS_HEAD, GROUP_SEG_HEAD = 0, 1, 2, 3

@@ -5,6 +5,8 @@
 
 #include "gemm_simt.cuh"
 #include "model.cuh"
+#include "tc_gemm.cuh"
+#include "tc_train.cuh"
 
 namespace pcp {
 
@@ -164,11 +166,90 @@ int softmax_rows(const float *d_logits, float *d_prob, int64_t rows, int cols, c
     return PCP_OK;
 }
 
+// ---- PCP_PRECISION_FP32_TC: the fp32 forward with its layer products on the bf16 tensor cores (hi / lo split) ----
+struct Tc3Images {
+    uint8_t *split[L_COUNT] = {};        // [hi(W'); lo(W'); hi(W')] image of every layer with cin % 64 == 0 (tc_gemm a_split3)
+    uint8_t *pool_hi[L_COUNT] = {}, *pool_lo[L_COUNT] = {};   // the max-pooled 128 -> 1024 layers: hi / lo images for tc_pool_max3
+    uint8_t *seg1_local = nullptr;       // seg_l1 rows [0, 64): the X_64 part of the hoisted 1088 -> 512 layer
+    std::vector<void *> owned;
+};
+
+static void tc3_destroy(pcp_model *m)
+{
+    if (!m->tc3) return;
+    Tc3Images *t = reinterpret_cast<Tc3Images *>(m->tc3);
+    for (void *p : t->owned) PCP_RELEASE(cudaFree(p));
+    delete t;
+    m->tc3 = nullptr;
+}
+
+static int tc3_upload(Tc3Images *t, const std::vector<uint16_t> &img, uint8_t **out)
+{
+    void *d = nullptr;
+    PCP_CUDA_OK(cudaMalloc(&d, img.size() * 2));
+    PCP_CUDA_OK(cudaMemcpy(d, img.data(), img.size() * 2, cudaMemcpyHostToDevice));
+    t->owned.push_back(d);
+    *out = reinterpret_cast<uint8_t *>(d);
+    return PCP_OK;
+}
+
+static int tc3_prepare(pcp_model *m, const std::vector<float> &fold)
+{
+    tc3_destroy(m);
+    Tc3Images *t = new Tc3Images();
+    m->tc3 = t;
+    std::vector<uint16_t> img;
+    for (int i = 0; i < L_COUNT; ++i) {
+        const LayerSpec &L = m->layers[i];
+        if (!L.present || L.cin % 64 != 0 || !(L.cout <= 128 || L.cout % 128 == 0)) continue;
+        const float *W = fold.data() + L.fold_w;
+        if (i == L_IT_C3 || i == L_FT_C3 || i == L_S2_3) {
+            std::vector<float> hi((size_t)L.cin * L.cout), lo(hi.size());
+            for (size_t k = 0; k < hi.size(); ++k) {
+                uint32_t u; memcpy(&u, &W[k], 4);
+                uint32_t r = u + 0x7FFFu + ((u >> 16) & 1u);            // bf16 round-to-nearest-even (finite weights)
+                r &= 0xFFFF0000u;
+                memcpy(&hi[k], &r, 4);
+                lo[k] = W[k] - hi[k];
+            }
+            pack_gemm_b_image(hi.data(), L.cin, L.cout, img);
+            PCP_TRY(tc3_upload(t, img, &t->pool_hi[i]));
+            pack_gemm_b_image(lo.data(), L.cin, L.cout, img);
+            PCP_TRY(tc3_upload(t, img, &t->pool_lo[i]));
+        } else if (i == L_SEG1) {
+            pack_gemm_b_image_split3(W, 64, L.cout, img);                // rows [0, 64) of the (1088 x 512) kernel
+            PCP_TRY(tc3_upload(t, img, &t->seg1_local));
+        } else {
+            pack_gemm_b_image_split3(W, L.cin, L.cout, img);
+            PCP_TRY(tc3_upload(t, img, &t->split[i]));
+        }
+    }
+    return PCP_OK;
+}
+
+// C[g] (M x N) = act(A[g] . W' + bias[g]) through tc_gemm with the hi / lo split
+static int tc3_gemm(const float *A, int64_t rows, int cin, const uint8_t *img, int cout, float *Cc, const float *bias, bool relu, cudaStream_t st,
+                    int groups = 1, int64_t bias_stride = 0)
+{
+    TcGemmParams p;
+    const int64_t rpg = rows / groups;
+    p.A = A; p.a_f32 = 1; p.a_split3 = 1; p.lda = cin; p.a_group_stride = rpg * cin; p.Bimg = img; p.bias = bias; p.bias_group_stride = bias_stride;
+    p.C32 = Cc; p.ldc = cout; p.c_group_stride = rpg * cout; p.M = (int)rpg; p.N = cout; p.K = 3 * cin; p.groups = groups; p.relu = relu ? 1 : 0;
+    return tc_gemm(p, st);
+}
+
 // C = act(A . Wfold + t): one ConvLayer / DenseLayer in inference form (PointNet.py:554-566, :642-654)
 static int layer_fwd(pcp_model *m, int id, const float *A, int64_t M, float *C, bool relu, cudaStream_t st,
                      float *colmax = nullptr, int groups = 1, int64_t rows_per_group = 0)
 {
     const LayerSpec &L = m->layers[id];
+    if (m->desc.precision == PCP_PRECISION_FP32_TC && m->tc3) {
+        const Tc3Images *t3 = reinterpret_cast<const Tc3Images *>(m->tc3);
+        if (colmax && t3->pool_hi[id] && L.cin == 128)
+            return tc_pool_max3(A, groups, rows_per_group, t3->pool_hi[id], t3->pool_lo[id], m->d_fold + L.fold_t, L.cout, colmax, st);
+        if (!colmax && t3->split[id] && (((uintptr_t)A) & 15u) == 0 && M < 0x7fffffff && (M + 127) / 128 <= 65535)
+            return tc3_gemm(A, M, L.cin, t3->split[id], L.cout, C, m->d_fold + L.fold_t, relu, st);
+    }
     GemmArgs g;
     g.A = A; g.lda = L.cin; g.B = m->d_fold + L.fold_w; g.ldb = L.cout; g.C = C; g.ldc = L.cout;
     g.bias = m->d_fold + L.fold_t; g.N = L.cout; g.K = L.cin; g.relu = relu ? 1 : 0;
@@ -209,11 +290,16 @@ static int seg_from_x64(pcp_model *m, const float *X64, const float *g3, int bc,
     gv.A = g3; gv.lda = 1024; gv.B = m->d_fold + S1.fold_w + (size_t)64 * 512; gv.ldb = 512;
     gv.C = ws.gvec; gv.ldc = 512; gv.bias = m->d_fold + S1.fold_t; gv.M = bc; gv.N = 512; gv.K = 1024;
     PCP_TRY(gemm_f32(gv, st));
-    GemmArgs g;
-    g.A = X64; g.lda = 64; g.strideA = n * 64; g.B = m->d_fold + S1.fold_w; g.ldb = 512; g.strideB = 0;
-    g.C = ws.s512; g.ldc = 512; g.strideC = n * 512; g.bias = ws.gvec; g.strideBias = 512;
-    g.M = (int)n; g.N = 512; g.K = 64; g.groups = bc; g.relu = 1;
-    PCP_TRY(gemm_f32(g, st));
+    const Tc3Images *t3 = (m->desc.precision == PCP_PRECISION_FP32_TC) ? reinterpret_cast<const Tc3Images *>(m->tc3) : nullptr;
+    if (t3 && t3->seg1_local && (int64_t)bc * ((n + 127) / 128) <= 65535) {
+        PCP_TRY(tc3_gemm(X64, M, 64, t3->seg1_local, 512, ws.s512, ws.gvec, true, st, bc, 512));
+    } else {
+        GemmArgs g;
+        g.A = X64; g.lda = 64; g.strideA = n * 64; g.B = m->d_fold + S1.fold_w; g.ldb = 512; g.strideB = 0;
+        g.C = ws.s512; g.ldc = 512; g.strideC = n * 512; g.bias = ws.gvec; g.strideBias = 512;
+        g.M = (int)n; g.N = 512; g.K = 64; g.groups = bc; g.relu = 1;
+        PCP_TRY(gemm_f32(g, st));
+    }
     PCP_TRY(layer_fwd(m, L_SEG2, ws.s512, M, ws.s256, true, st));
     PCP_TRY(layer_fwd(m, L_SEG3, ws.s256, M, ws.s128a, true, st));
     PCP_TRY(layer_fwd(m, L_SEG4, ws.s128a, M, ws.s128b, true, st));
@@ -386,7 +472,7 @@ extern "C" int pcp_model_create(const pcp_model_desc *desc, pcp_model **out)
 {
     PCP_REQUIRE(desc && out, PCP_ERR_INVALID, "pcp_model_create: null argument");
     PCP_REQUIRE(desc->num_classes >= 1 && desc->num_parts >= 1, PCP_ERR_INVALID, "pcp_model_create: widths must be >= 1");
-    PCP_REQUIRE(desc->precision == PCP_PRECISION_FP32 || desc->precision == PCP_PRECISION_BF16, PCP_ERR_INVALID,
+    PCP_REQUIRE(desc->precision == PCP_PRECISION_FP32 || desc->precision == PCP_PRECISION_BF16 || desc->precision == PCP_PRECISION_FP32_TC, PCP_ERR_INVALID,
                 "pcp_model_create: unknown precision %d", desc->precision);
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -414,6 +500,7 @@ extern "C" int pcp_model_destroy(pcp_model *m)
     if (!m) return PCP_OK;
     ws_free(m->ws);
     model_destroy_bf16(m);
+    tc3_destroy(m);
     train_destroy(m);
     PCP_RELEASE(cudaFree(m->d_params)); PCP_RELEASE(cudaFree(m->d_fold));
     PCP_RELEASE(cudaFree(m->d_grads)); PCP_RELEASE(cudaFree(m->d_adam_m)); PCP_RELEASE(cudaFree(m->d_adam_v));
@@ -493,6 +580,7 @@ extern "C" int pcp_model_prepare(pcp_model *m)
     PCP_CUDA_OK(cudaMemcpy(m->d_fold, fold.data(), m->n_fold * sizeof(float), cudaMemcpyHostToDevice));
     PCP_CUDA_OK(cudaMemcpy(m->d_params, m->h_params.data(), m->n_params * sizeof(float), cudaMemcpyHostToDevice));
     if (m->desc.precision == PCP_PRECISION_BF16) PCP_TRY(model_prepare_bf16(m));
+    if (m->desc.precision == PCP_PRECISION_FP32_TC) PCP_TRY(tc3_prepare(m, fold));
     m->prepared = true;
     return PCP_OK;
 }
@@ -504,7 +592,7 @@ extern "C" int pcp_model_reserve(pcp_model *m, int b, int64_t n)
     if (ws.total_b >= b && ws.cap_n == n) return PCP_OK;
     ws_free(ws);
     const int C = m->desc.num_classes, P = m->desc.num_parts;
-    const bool fp32 = m->desc.precision == PCP_PRECISION_FP32;
+    const bool fp32 = m->desc.precision != PCP_PRECISION_BF16;
     // fp32 path materialises per-point activations: bound a chunk to ~192k points
     const int64_t max_pts = 196608;
     int cap_b = (int)std::max<int64_t>(1, std::min<int64_t>(b, max_pts / n));

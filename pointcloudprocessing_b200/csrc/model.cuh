@@ -81,6 +81,7 @@ struct pcp_model {
     // bf16 tensor-core images (chain_tc.cu)
     void *tc = nullptr;
     void *tc_heads = nullptr;   // heads_tc.cu
+    void *tc3 = nullptr;        // PCP_PRECISION_FP32_TC: split weight images (model.cu)
 };
 
 namespace pcp {

@@ -17,6 +17,8 @@ constexpr int kGemmStages = 3;
 constexpr uint32_t kGemmStageBytes = 32768;   // 16 KB A + up to 16 KB B
 constexpr uint32_t kGemmSmem = kGemmStages * kGemmStageBytes + 1024;
 
+__device__ __forceinline__ float bf16_trunc_rn(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+
 __global__ void __launch_bounds__(kGemmThreads, 2)
 tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nsplit)
 {   // bnt: MMA N of this CTA; img_rows: rows of a weight-image tile; nsplit = img_rows / bnt column blocks per image tile
@@ -83,10 +85,12 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
         if (p.a_f32) {
             // fp32 activations (pooled features): one k-tile (16 x float4) in flight, converted to bf16 on arrival
             float4 raw[16];
+            const int KTs = p.a_split3 ? KT / 3 : KT;          // k-tiles of the source matrix (split3: every tile is read three times)
             auto issue = [&](int kt) {
+                const int ks = p.a_split3 ? kt % KTs : kt;
 #pragma unroll
                 for (int pass = 0; pass < 8; ++pass) {
-                    const float4 *src = reinterpret_cast<const float4 *>(rowp[pass] + (size_t)kt * 256);
+                    const float4 *src = reinterpret_cast<const float4 *>(rowp[pass] + (size_t)ks * 256);
                     raw[2 * pass] = __ldg(src);
                     raw[2 * pass + 1] = __ldg(src + 1);
                 }
@@ -94,9 +98,14 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
             issue(0);
             for (int kt = 0; kt < KT; ++kt) {
                 uint4 v[8];
+                const bool lo_part = p.a_split3 && kt >= 2 * KTs;
 #pragma unroll
                 for (int pass = 0; pass < 8; ++pass) {
-                    const float4 f0 = raw[2 * pass], f1 = raw[2 * pass + 1];
+                    float4 f0 = raw[2 * pass], f1 = raw[2 * pass + 1];
+                    if (lo_part) {                             // lo(A) = bf16(A - float(bf16(A))): exact difference, then rounded
+                        f0.x -= bf16_trunc_rn(f0.x); f0.y -= bf16_trunc_rn(f0.y); f0.z -= bf16_trunc_rn(f0.z); f0.w -= bf16_trunc_rn(f0.w);
+                        f1.x -= bf16_trunc_rn(f1.x); f1.y -= bf16_trunc_rn(f1.y); f1.z -= bf16_trunc_rn(f1.z); f1.w -= bf16_trunc_rn(f1.w);
+                    }
                     v[pass] = make_uint4(pack_bf16x2(f0.x, f0.y), pack_bf16x2(f0.z, f0.w), pack_bf16x2(f1.x, f1.y), pack_bf16x2(f1.z, f1.w));
                 }
                 if (kt + 1 < KT) issue(kt + 1);
@@ -264,6 +273,20 @@ void pack_gemm_b_image(const float *W, int K, int N, std::vector<uint16_t> &img)
         }
 }
 
+static inline float bf2f_host(uint16_t h) { uint32_t u = (uint32_t)h << 16; float f; memcpy(&f, &u, 4); return f; }
+
+void pack_gemm_b_image_split3(const float *W, int K, int N, std::vector<uint16_t> &img)
+{
+    std::vector<float> W3((size_t)3 * K * N);
+    for (size_t i = 0; i < (size_t)K * N; ++i) {
+        const float hi = bf2f_host(f2bf_host(W[i]));
+        W3[i] = hi;                                   // rows [0, K): hi(W)    x hi(A)
+        W3[(size_t)K * N + i] = W[i] - hi;            // rows [K, 2K): lo(W)   x hi(A)   (rounded to bf16 by the packer)
+        W3[(size_t)2 * K * N + i] = hi;               // rows [2K, 3K): hi(W)  x lo(A)
+    }
+    pack_gemm_b_image(W3.data(), 3 * K, N, img);
+}
+
 bool tc_gemm_persist_try(const TcGemmParams &p, cudaStream_t st, int *rc);   // tc_gemm_tma.cu
 
 int tc_gemm(const TcGemmParams &p, cudaStream_t st)
@@ -273,6 +296,7 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
     PCP_REQUIRE(p.N >= 1 && (p.N <= 128 || p.N % 128 == 0), PCP_ERR_UNSUPPORTED, "tc_gemm: N=%d must be <= 128 or a multiple of 128", p.N);
     PCP_REQUIRE(!p.Csoftmax || p.N <= 32, PCP_ERR_UNSUPPORTED, "tc_gemm: softmax epilogue needs N <= 32");
     PCP_REQUIRE((p.lda % (p.a_f32 ? 4 : 8)) == 0, PCP_ERR_UNSUPPORTED, "tc_gemm: lda must keep 16-byte row chunks aligned");
+    PCP_REQUIRE(!p.a_split3 || (p.a_f32 && p.K % 192 == 0), PCP_ERR_UNSUPPORTED, "tc_gemm: a_split3 needs fp32 activations and K = 3 x a multiple of 64");
     if (p.M <= 0 || p.groups <= 0) return PCP_OK;
     {
         int rc = PCP_OK;

@@ -12,6 +12,9 @@ namespace pcp {
 struct TcGemmParams {
     const void *A = nullptr;            // (groups * M) x K row-major; fp32 if a_f32 else bf16
     int a_f32 = 0;
+    int a_split3 = 0;                   // fp32 contract on bf16 tensor cores: K = 3 * Ksrc, the k-tiles are [hi(A) | hi(A) | lo(A)] of the
+                                        // SAME fp32 A (lda columns Ksrc), against a weight image of [hi(W); lo(W); hi(W)] (pack_gemm_b_image_split3):
+                                        // A.W ~ hi.hi + hi.lo + lo.hi, 16 mantissa bits instead of 8 (a_f32 must be set)
     int64_t lda = 0;                    // elements
     int64_t a_group_stride = 0;         // elements between groups
     const uint8_t *Bimg = nullptr;      // weight image from pack_gemm_b_image: tiles [nt][kt] of (BNt rows x 64 K) bf16 SW128
@@ -40,6 +43,8 @@ inline int tc_gemm_bn_tile(int N) { return N >= 128 ? 128 : ((N + 15) / 16) * 16
 // W: (K x N) row-major fp32 -> bf16 image (K % 64 == 0; N % 128 == 0 when N > 128)
 void pack_gemm_b_image(const float *W, int K, int N, std::vector<uint16_t> &img);
 size_t gemm_b_image_bytes(int K, int N);
+// W: (K x N) row-major fp32 -> bf16 image of the (3K x N) matrix [hi(W); lo(W); hi(W)], hi = bf16(W), lo = bf16(W - hi)
+void pack_gemm_b_image_split3(const float *W, int K, int N, std::vector<uint16_t> &img);
 
 int tc_gemm(const TcGemmParams &p, cudaStream_t st);
 

@@ -419,6 +419,160 @@ int tc_pool_extrema(const float *A, int b, int64_t n, const uint8_t *Wimg, int c
     return PCP_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// fp32-contract inference on the bf16 tensor cores (PCP_PRECISION_FP32_TC): g[cloud, ch] = max over the cloud's rows of
+// relu(A . W' + t) for the three max-pooled 128 -> 1024 layers (PointNet.py:425-429, :242-248), with the product evaluated as
+// hi(W) hi(A) + lo(W) hi(A) + hi(W) lo(A)  (hi = bf16(x), lo = bf16(x - hi): ~16 mantissa bits, fp32 accumulation in TMEM).
+// Same structure as tc_pool_extrema_kernel (transposed MMA: channels on the TMEM lanes, rows along the columns, the owning
+// thread reduces over the rows in registers); BN is folded into W' / t, so relu(max z + t) is the pooled value whatever the
+// sign of gamma; clouds' row tiles merge through atomicMax on the float bits (non-negative floats order like integers).
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kP3Smem = 6 * kPxTile + 1024;     // A hi | A lo | 2 stages x (W hi | W lo)
+
+struct PoolMax3Params {
+    const float *A;                      // (b * n) x 128 fp32 row-major
+    const uint8_t *Whi, *Wlo;            // pack_gemm_b_image(hi(W') / lo(W'), 128, cout): [cout/128][2] tiles of 16 KB
+    const float *t;                      // cout: folded shift
+    float *g;                            // b x cout, zero-initialised
+    int n, cout, mtiles;
+};
+
+__global__ void __launch_bounds__(kPxThreads, 1)
+tc_pool_max3_kernel(const PoolMax3Params p)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t a_full, w_full[2], w_empty[2], acc_full[2], acc_empty[2];
+    __shared__ uint32_t tmem_base;
+    uint8_t *base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t *Ahi = base, *Alo = base + kPxTile, *Ws = base + 2 * kPxTile;      // stage s: Ws + s * 2 * kPxTile = hi | lo
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = blockIdx.x / p.mtiles, mt = blockIdx.x % p.mtiles;
+    const int row0 = mt * 128;
+    const int rows_valid = min(128, p.n - row0);
+    const int NT = p.cout >> 7;
+
+    if (tid == 0) {
+        mbar_init(&a_full, 4);
+        for (int i = 0; i < 2; ++i) { mbar_init(&w_full[i], 1); mbar_init(&w_empty[i], 1); mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+        fence_barrier_init();
+    }
+    if (warp == 4) tmem_alloc(&tmem_base, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base;
+
+    if (warp < 4) {
+        const int chunk = tid & 7, rsub = tid >> 3;
+        const float *Ag = p.A + ((int64_t)g * p.n + row0) * 128 + chunk * 8;
+#pragma unroll
+        for (int kt = 0; kt < 2; ++kt) {
+            float4 raw[16];
+#pragma unroll
+            for (int pass = 0; pass < 8; ++pass) {
+                const int r = min(pass * 16 + rsub, rows_valid - 1);
+                const float4 *src = reinterpret_cast<const float4 *>(Ag + (int64_t)r * 128 + kt * 64);
+                raw[2 * pass] = __ldg(src); raw[2 * pass + 1] = __ldg(src + 1);
+            }
+#pragma unroll
+            for (int pass = 0; pass < 8; ++pass) {
+                const float f[8] = {raw[2 * pass].x, raw[2 * pass].y, raw[2 * pass].z, raw[2 * pass].w,
+                                    raw[2 * pass + 1].x, raw[2 * pass + 1].y, raw[2 * pass + 1].z, raw[2 * pass + 1].w};
+                float l[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) l[e] = f[e] - __bfloat162float(__float2bfloat16_rn(f[e]));
+                const uint32_t off = kt * 16384 + sw128_offset(128, (uint32_t)(pass * 16 + rsub), (uint32_t)chunk * 8);
+                *reinterpret_cast<uint4 *>(Ahi + off) = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+                *reinterpret_cast<uint4 *>(Alo + off) = make_uint4(pack_bf16x2(l[0], l[1]), pack_bf16x2(l[2], l[3]), pack_bf16x2(l[4], l[5]), pack_bf16x2(l[6], l[7]));
+            }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_full);
+        for (int nt = 0; nt < NT; ++nt) {
+            const int buf = nt & 1;
+            mbar_wait(&acc_full[buf], (uint32_t)((nt >> 1) & 1), 66);
+            tc_fence_after();
+            float mx = -INFINITY;
+            for (int c0 = 0; c0 < rows_valid; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(buf * 128 + c0), v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; ++e)
+                    if (c0 + e < rows_valid) mx = fmaxf(mx, __uint_as_float(v[e]));
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[buf]);
+            const int ch = nt * 128 + tid;
+            const float y = fmaxf(mx + __ldg(p.t + ch), 0.f);
+            if (y > 0.f) atomicMax(reinterpret_cast<unsigned *>(p.g + (size_t)g * p.cout + ch), __float_as_uint(y));
+        }
+    } else if (warp == 4) {
+        const uint32_t idesc = make_idesc_bf16(128, 128);
+        const uint32_t ahi = (smem_u32(Ahi) & 0x3FFFFu) >> 4, alo = (smem_u32(Alo) & 0x3FFFFu) >> 4, w0 = (smem_u32(Ws) & 0x3FFFFu) >> 4;
+        mbar_wait(&a_full, 0, 67);
+        for (int nt = 0; nt < NT; ++nt) {
+            const int s = nt & 1;
+            mbar_wait(&w_full[s], (uint32_t)((nt >> 1) & 1), 68);
+            if (nt >= 2) mbar_wait(&acc_empty[s], (uint32_t)(((nt >> 1) - 1) & 1), 69);
+            tc_fence_after();
+            if (elect_one_sync()) {
+                const uint32_t whi = w0 + (uint32_t)s * (2 * kPxTile >> 4), wlo = whi + (kPxTile >> 4);
+                const uint32_t wsel[3] = {whi, wlo, whi}, asel[3] = {ahi, ahi, alo};
+#pragma unroll
+                for (int part = 0; part < 3; ++part)
+#pragma unroll
+                    for (int kt = 0; kt < 2; ++kt)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            mma_bf16_ss(tmem + (uint32_t)(s * 128), sdesc_from_lo(wsel[part] + kt * 1024 + k * 2), sdesc_from_lo(asel[part] + kt * 1024 + k * 2),
+                                        idesc, (part | kt | k) > 0);
+                mma_commit(&w_empty[s]);
+                mma_commit(&acc_full[s]);
+            }
+            __syncwarp();
+        }
+    } else {
+        if (lane == 0) {
+            for (int nt = 0; nt < NT; ++nt) {
+                const int s = nt & 1;
+                if (nt >= 2) mbar_wait(&w_empty[s], (uint32_t)(((nt >> 1) - 1) & 1), 70);
+                mbar_arrive_expect_tx(&w_full[s], 2 * kPxTile);
+                uint8_t *dst = Ws + (size_t)s * 2 * kPxTile;
+                bulk_g2s(dst, p.Whi + (size_t)nt * kPxTile, 16384, &w_full[s]);
+                bulk_g2s(dst + 16384, p.Whi + (size_t)nt * kPxTile + 16384, 16384, &w_full[s]);
+                bulk_g2s(dst + kPxTile, p.Wlo + (size_t)nt * kPxTile, 16384, &w_full[s]);
+                bulk_g2s(dst + kPxTile + 16384, p.Wlo + (size_t)nt * kPxTile + 16384, 16384, &w_full[s]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc(tmem, 256);
+}
+
+int tc_pool_max3(const float *A, int b, int64_t n, const uint8_t *Whi, const uint8_t *Wlo, const float *t, int cout, float *g, cudaStream_t st)
+{
+    PCP_REQUIRE(A && Whi && Wlo && t && g, PCP_ERR_INVALID, "tc_pool_max3: null operand");
+    PCP_REQUIRE(cout >= 128 && cout % 128 == 0 && n >= 1 && n <= 0x7fffffff, PCP_ERR_UNSUPPORTED, "tc_pool_max3: cout=%d must be a multiple of 128", cout);
+    if (b <= 0) return PCP_OK;
+    PoolMax3Params p;
+    p.A = A; p.Whi = Whi; p.Wlo = Wlo; p.t = t; p.g = g; p.n = (int)n; p.cout = cout; p.mtiles = (int)((n + 127) / 128);
+    const int64_t grid = (int64_t)b * p.mtiles;
+    PCP_REQUIRE(grid <= 0x7fffffff, PCP_ERR_UNSUPPORTED, "tc_pool_max3: %lld row tiles exceed one launch", (long long)grid);
+    static bool attr = false;
+    if (!attr) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_pool_max3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kP3Smem));
+        attr = true;
+    }
+    tc_pool_max3_kernel<<<(unsigned)grid, kPxThreads, kP3Smem, st>>>(p);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
 }  // namespace pcp
 
 using namespace pcp;

@@ -18,4 +18,8 @@ int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ
 int tc_pool_extrema(const float *A, int b, int64_t n, const uint8_t *Wimg, int cout, unsigned long long *ext_max, unsigned long long *ext_min,
                     cudaStream_t st);
 
+// fp32-contract inference of a max-pooled 128 -> cout layer on the bf16 tensor cores (hi/lo split, see tc_train.cu):
+// g (b x cout, zero-initialised) = max over each cloud's n rows of relu(A . W' + t); Whi / Wlo = pack_gemm_b_image of hi(W') / lo(W')
+int tc_pool_max3(const float *A, int b, int64_t n, const uint8_t *Whi, const uint8_t *Wlo, const float *t, int cout, float *g, cudaStream_t st);
+
 }  // namespace pcp

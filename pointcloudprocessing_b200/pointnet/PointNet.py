@@ -158,7 +158,9 @@ class PointNet:
     """PointNet classification + part segmentation + input-transform output (PointNet.py:84-376).
 
     model(pc, training=False) -> [classification (b,C) probabilities, segmentation (b,n,P) probabilities, R (b,3,3)].
-    `precision`: 'bf16' (tcgen05 tensor cores, 2e-2 contract) or 'fp32' (CUDA-core FMA, 1e-3 contract).
+    `precision`: 'bf16' (tcgen05 tensor cores, 2e-2 contract), 'fp32' (CUDA-core FMA, 1e-3 contract) or 'fp32_tc' (the 1e-3
+    contract on the tensor cores: every layer product as three bf16 products of hi / lo halves, ~16 mantissa bits; inference —
+    its training steps run the fp32 path).
     """
 
     def __init__(self, classification_output_width: int, segmentation_output_width: int, dropout_rate: float,
@@ -211,7 +213,7 @@ class PointNet:
 
     # ------------------------------------------------------------------ lifecycle
     def _create_handle(self):
-        prec = {"fp32": _ffi.PRECISION_FP32, "bf16": _ffi.PRECISION_BF16}[self._precision]
+        prec = {"fp32": _ffi.PRECISION_FP32, "bf16": _ffi.PRECISION_BF16, "fp32_tc": _ffi.PRECISION_FP32_TC}[self._precision]
         desc = _ffi.ModelDesc(self._classification_output_width, self._segmentation_output_width, int(self._vanilla),
                               int(self._regularize_input_transform), int(self._regularize_feature_transform),
                               self._dropout_rate, prec)

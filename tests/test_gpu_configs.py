@@ -35,7 +35,7 @@ def test_c2_fps_all_64_clouds_bit_exact(lib, oracle_c):
     assert np.array_equal(idx, ref)
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("bf16", 2e-2)])
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("bf16", 2e-2), ("fp32_tc", 1e-3)])
 def test_c4_segmentation_128x2048_all_outputs(lib, precision, tol):
     from pointcloudprocessing_b200.pointnet import PointNet
     b, n, C, P = 128, 2048, 23, 12
@@ -56,7 +56,7 @@ def test_c4_segmentation_128x2048_all_outputs(lib, precision, tol):
     srt = np.sort(rl, -1)
     decided = (srt[:, -1] - srt[:, -2]) > 2 * tol * np.abs(rl).max()
     same = got["seg_logits"].reshape(-1, P).argmax(-1) == rl.argmax(-1)
-    assert same[decided].all() and same.mean() > (0.999 if precision == "fp32" else 0.97), (decided.mean(), same.mean())
+    assert same[decided].all() and same.mean() > (0.97 if precision == "bf16" else 0.999), (decided.mean(), same.mean())
     # the host path returns the same bits (D2H of b x n x P inside the library)
     c2, s2, r2 = m(x)
     assert np.array_equal(s2, got["seg"]) and np.array_equal(c2, got["cls"]) and np.array_equal(r2, got["R"])

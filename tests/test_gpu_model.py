@@ -10,7 +10,7 @@ from tests import synth
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp32": 1e-3, "bf16": 2e-2}
+TOL = {"fp32": 1e-3, "bf16": 2e-2, "fp32_tc": 1e-3}
 
 
 def rel_err(a, ref):
@@ -43,7 +43,7 @@ def oracle_forward(x, p, vanilla):
     return {k: v.numpy() for k, v in o.items()}
 
 
-@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16", "fp32_tc"])
 @pytest.mark.parametrize("vanilla,b,n", [(False, 4, 256), (True, 4, 256), (False, 32, 1024), (False, 3, 2048), (False, 2, 200)])
 def test_forward_matches_oracle(lib, precision, vanilla, b, n):
     m, p = build(precision, vanilla)
@@ -61,7 +61,7 @@ def test_forward_matches_oracle(lib, precision, vanilla, b, n):
     assert np.allclose(got["cls"].sum(-1), 1.0, atol=1e-5) and np.allclose(got["seg"].sum(-1), 1.0, atol=1e-5)
 
 
-@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("precision", ["fp32", "bf16", "fp32_tc"])
 def test_pooled_features_and_golden(lib, precision):
     from pathlib import Path
     g = np.load(Path(__file__).parent / "golden" / "pointnet_small.npz")
