@@ -18,7 +18,12 @@
  *   - launches are asynchronous on the cudaStream_t passed as `stream` (void*, 0 = default stream);
  *     the *_host entry points copy H2D/D2H themselves and synchronise before returning;
  *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with
- *     PCP_ERR_CUDA.
+ *     PCP_ERR_CUDA;
+ *   - EXCLUSIVE USE OF THE DEVICE is assumed by the kernels whose CTAs wait for each other inside one launch
+ *     (pcp_normalize_f32 on LiDAR-sized clouds, pcp_fps_f32, the fused chain kernel of pcp_model_forward in bf16 mode):
+ *     they size their grids to be fully resident, so under MPS / co-tenancy with another process's kernels a
+ *     waited-for CTA may not be scheduled; every such wait is bounded and traps after ~2 s instead of hanging;
+ *   - test / development hooks (pcp_selftest_*, pcp_bench_*, ...) are declared in pcp_dev.h, not here.
  */
 #ifndef PCP_H_
 #define PCP_H_
@@ -110,10 +115,6 @@ int pcp_resize_to_width_f32(const float *d_x, const int32_t *d_labels, int b, in
 /* Farthest-point sampling: x (b, n, 3) -> idx (b, s) int32; first index = start; fp32
  * ((dx*dx + dy*dy) + dz*dz) without FMA, lowest index wins ties. */
 int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, pcp_stream stream);
-/* Development aid: cycles block 0 / thread 0 of the last pcp_fps_f32 launch made under PCP_FPS_PROF=1 (25 points per
- * thread) spent in: distance loop, warp keys, __syncthreads, push, exchange wait, read-back (scripts/fps_phases.py). */
-int pcp_fps_phase_cycles(unsigned long long out[8]);
-
 /* out[c, j, :] = x[c, idx[c, j], :] ; labels likewise when non-NULL */
 int pcp_gather_points_f32(const float *d_x, const int32_t *d_labels, int b, int64_t n, const int32_t *d_idx, int s,
                           float *d_out, int32_t *d_labels_out, pcp_stream stream);
@@ -196,39 +197,6 @@ int pcp_model_get_pooled(pcp_model *m, int which, int b, float *h_out);
  * summed device time and the launch count since the last call. */
 int pcp_model_enable_timing(pcp_model *m, int flag);
 int pcp_model_chain_time(pcp_model *m, float *ms_total, int *launches);
-
-/* Tensor-core self-test (used by tests only): D (128 x N) = A (128 x K) . B (N x K)^T through one
- * tcgen05.mma chain with bf16-rounded operands; validates the shared-memory operand image, the
- * descriptors and the TMEM read-back in isolation.  Host pointers, synchronous. */
-int pcp_selftest_umma(const float *h_a, const float *h_b, int N, int K, float *h_d);
-/* same with a CTA pair (cluster of 2, cta_group::2): D (256 x N) = A (256 x K) . B (N x K)^T */
-int pcp_selftest_umma2(const float *h_a, const float *h_b, int N, int K, float *h_d);
-
-/* weight-gradient self-test (tests only): dW (cin x cout) = A^T (cin x rows) . dZ (rows x cout) through the MN-major
- * tcgen05 split-K kernel of the bf16 training step; operands rounded to bf16, fp32 accumulate.  Host pointers. */
-int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t rows, int cin, int cout, float *h_dw);
-/* forward / input-gradient GEMM self-test (tests only): C (rows x n) (+)= A (rows x k) . W through the device-side
- * weight-image packer + tcgen05 GEMM of the bf16 training step; W is (k x n) row-major, or (n x k) row-major when
- * transpose_w (dA = dZ . W^T).  Host pointers; h_c is read when accumulate != 0. */
-int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate, float *h_c);
-/* test hook: C[g] (m x n) = act(bf16(A[g]) . bf16(W) + bias[g]) with bf16 activations in HBM (large shapes run the persistent TMA
- * kernel, small ones the per-tile kernel); out_kind 0 fp32, 1 bf16, 2 softmax (n <= 32); h_c is fp32; h_bias (groups x n) or NULL */
-int pcp_selftest_tc_gemm_bf16(const float *h_a, const float *h_w, const float *h_bias, int64_t m, int groups, int k, int n,
-                              int out_kind, int relu, float *h_c);
-/* development: average milliseconds of one generic tensor-core GEMM launch on device-resident synthetic operands
- * (out_kind 0 fp32, 1 bf16, 2 softmax; dbg 1 skips output stores, 2 skips activation loads) */
-int pcp_bench_tc_gemm(int64_t rows, int k, int n, int out_kind, int a_f32, int relu, int iters, int dbg, float *h_ms);
-/* max-pooled layer self-test (tests only): conv 128 -> cout, BN (batch statistics when batch != 0, else moving mean 0 /
- * variance 1), ReLU, reduce_max over the n points of each of the b clouds, and its backward pass, through the implicit
- * path of the bf16 training step (no rows x cout tensor; train_pool.inl).  Host pointers:
- * A (b*n x 128), W (128 x cout), gamma / beta (cout), dg (b x cout) -> g (b x cout), mean / inv (cout: batch mean and
- * 1/sqrt(var + 1e-3)), dW (128 x cout), dgamma / dbeta (cout), dA (b*n x 128). */
-int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, const float *h_gamma, const float *h_beta, const float *h_dg, int b,
-                              int64_t n, int cout, int batch, float *h_g, float *h_mean, float *h_inv, float *h_dw, float *h_dgamma,
-                              float *h_dbeta, float *h_da);
-/* (tests only) the pcp_allreduce_fn callback (declared below) and row scale under which the following
- * pcp_selftest_pooled_layer calls run: emulates the data-parallel BatchNorm protocol of the pooled layer on one device. */
-int pcp_selftest_set_bn_allreduce(int (*fn)(void *, void *, size_t, int, void *), void *user, double row_scale);
 
 /* ---- pose post-processing, batched: the reference's host NumPy float64 helpers on the device;
  * fp32 in / out, fp64 arithmetic inside; 3x3 matrices row-major, angles in degrees as (roll, pitch, yaw) ---- */

@@ -31,7 +31,7 @@ def _sources():
 
 
 def _headers_mtime() -> float:
-    hs = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inl")) + [PKG.parent / "include" / "pcp.h"]
+    hs = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inl")) + [PKG.parent / "include" / "pcp.h", PKG.parent / "include" / "pcp_dev.h"]
     return max(h.stat().st_mtime for h in hs)
 
 

@@ -8,6 +8,7 @@
 #include <string>
 
 #include "../../include/pcp.h"
+#include "../../include/pcp_dev.h"
 
 namespace pcp {
 

@@ -2,11 +2,14 @@
 // contract is oracle/sampling.py:fps — SURVEY.md §8 a9).
 //
 // Design: FPS is a serial chain of S global arg-max steps, so the working set must never leave the
-// chip.  One thread-block CLUSTER per cloud; every thread keeps PPT points (x,y,z) and their running
-// min-distance in REGISTERS for the whole kernel (the cloud is read from HBM exactly once).  Per
-// iteration: register-only distance update (3 sub, 3 mul, 2 add, min — no FMA, bit-exact with the
-// oracle), REDUX warp arg-max, one __syncthreads, one 32-byte DSMEM record per CTA pushed to every
-// peer, one cluster barrier.  Ties resolve to the lowest index (np.argmax).
+// chip.  One thread-block CLUSTER per cloud; every thread keeps its points (x,y,z) and their running
+// min-distance in REGISTERS for the whole kernel — or, when the batch needs more than one wave of clusters, the larger part of
+// its slice's coordinates in shared memory with the distances still in registers (hybrid residency) — so the cloud is read
+// from HBM exactly once.  Per iteration: distance update (3 sub, 3 mul, 2 add, min — no FMA, bit-exact with the oracle),
+// REDUX warp arg-max, one __syncthreads, then the warp that owns the block's winner pushes one 32-byte record into every CTA
+// of the cluster as st.async with the arrival attached (mbarrier complete_tx); every CTA waits on its own transaction
+// barrier — no hardware cluster barrier in the loop.  Ties resolve to the lowest index (np.argmax).
+// Exclusive use of the device is assumed: CTAs of a cluster wait for their peers' records (bounded: a lost arrival traps).
 #include <cooperative_groups.h>
 
 #include <cstdlib>

@@ -11,8 +11,11 @@ ROOT = Path(__file__).resolve().parents[1]
 
 def test_header_and_binding_agree(lib):
     from pointcloudprocessing_b200 import _ffi
-    hdr = (ROOT / "include" / "pcp.h").read_text()
+    # pcp.h: the drop-in boundary; pcp_dev.h: test / development hooks (kept out of the boundary header)
+    hdr = (ROOT / "include" / "pcp.h").read_text() + (ROOT / "include" / "pcp_dev.h").read_text()
     declared = set(re.findall(r"\b(pcp_[a-z0-9_]+)\s*\(", hdr))
+    product = set(re.findall(r"\b(pcp_[a-z0-9_]+)\s*\(", (ROOT / "include" / "pcp.h").read_text()))
+    assert not [n for n in product if "selftest" in n or "bench" in n or "phase_cycles" in n], "test hooks belong in pcp_dev.h"
     assert declared == set(_ffi.SIGNATURES), (declared ^ set(_ffi.SIGNATURES))
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in pcp.h but not exported"
