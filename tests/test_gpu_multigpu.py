@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 ROOT = Path(__file__).resolve().parents[1]
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs: NOT verified on this box — the all-reduced gradient bucket over NCCL, identical weights on every rank after Adam, sharded inference == whole-batch inference, sync-BN step == single-device step (verified on 2 x B200 by the builder: profiles/r02_multigpu_2gpu.txt; host logic on CPU: tests/test_parallel_gloo.py)")
 def test_data_parallel_step_two_ranks(lib):
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
