@@ -473,7 +473,9 @@ def main():
         peak = peaks["bf16_tflops"]
         # DRAM bytes per chain launch from the committed ncu --set full capture of this command (profiles/, same clouds per step)
         traffic = None
-        tf = ROOT / "profiles" / "r01_chain2_traffic.json"
+        tf = ROOT / "profiles" / "r02_chain2_traffic.json"
+        if not tf.exists():
+            tf = ROOT / "profiles" / "r01_chain2_traffic.json"
         if tf.exists():
             rec = json.loads(tf.read_text())
             if rec.get("clouds_per_launch") == B and rec.get("points") == N_POINTS:
