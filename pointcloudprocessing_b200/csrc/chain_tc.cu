@@ -23,7 +23,7 @@ namespace pcp {
 using namespace umma;
 
 constexpr int kTP = 128;            // points per tile
-constexpr int kChainThreads = 352;   // 11 warps: 4 front, 4 final-epilogue, mid issuer, loader, final issuer
+constexpr int kChainThreads = 512;   // 16 warps: front group 0 (0-3), final epilogue (4-7), mid issuer 0 (8), loader (9), final issuer (10), mid issuer 1 (11), front group 1 (12-15)
 constexpr uint32_t kW3Tile = 16384;  // one W3 operand tile: 128 channels x 64 K, bf16
 
 struct ChainParams {
@@ -124,8 +124,8 @@ __device__ __forceinline__ void trace_ev(const ChainParams &p, uint32_t rank, in
 }
 
 struct Chain2Shared {
-    uint64_t a_full, mid_full, wready, wres_full;
-    uint64_t h2_full[2], h2_empty[2], acc_full[3], acc_empty[3], wc_full[2], wc_ready[2], wc_empty[2];
+    uint64_t a_full[2], mid_full[2], wready, wres_full;     // [front group]
+    uint64_t h2_full[2], h2_empty[2][2], acc_full[3], acc_empty[3], wc_full[2], wc_ready[2], wc_empty[2];   // h2_empty[step parity][half]
     uint32_t tmem_base;
     alignas(16) float l0[64 * 4];
     alignas(16) float mid_t[3][128];
@@ -148,9 +148,10 @@ chain2_kernel(const ChainParams p)
     const int64_t nsteps = s_end - s_begin;
 
     if (tid == 0) {
-        mbar_init(&sh.a_full, 8); mbar_init(&sh.mid_full, 1); mbar_init(&sh.wready, 2); mbar_init(&sh.wres_full, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(&sh.a_full[i], 8); mbar_init(&sh.mid_full[i], 1); }
+        mbar_init(&sh.wready, 2); mbar_init(&sh.wres_full, 1);
         for (int i = 0; i < 2; ++i) {
-            mbar_init(&sh.h2_full[i], 4); mbar_init(&sh.h2_empty[i], 1);
+            mbar_init(&sh.h2_full[i], 4); mbar_init(&sh.h2_empty[0][i], 1); mbar_init(&sh.h2_empty[1][i], 1);
             mbar_init(&sh.wc_full[i], 1); mbar_init(&sh.wc_ready[i], 2); mbar_init(&sh.wc_empty[i], 1);
         }
         for (int i = 0; i < 3; ++i) { mbar_init(&sh.acc_full[i], 1); mbar_init(&sh.acc_empty[i], 8); }
@@ -171,50 +172,45 @@ chain2_kernel(const ChainParams p)
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (warp != 9) asm volatile("griddepcontrol.wait;" ::: "memory");
 
-    if (warp < 4) {
+    if (warp < 4 || warp >= 12) {
         // =========================== front (both CTAs): L0 + mid-layer epilogues ===========================
-        const int row = tid;
-        const int half = warp >> 1;
+        // TWO front groups (round 2), each with its own operand buffer (A0 / A1, written IN PLACE by every epilogue: mid_full says
+        // the MMA that read the buffer is complete), its own mid accumulator in TMEM and its own barriers: group g takes the
+        // pair-steps it = g, g + 2, ...  A tile still crosses seven serial hand-offs of ~650 ns, but two tiles are in flight, so
+        // the final layer is fed twice as often (the traced single front chain took 5.5 us per step against 2.3 us of final MMAs).
+        const int fgp = warp >= 12 ? 1 : 0, fw = warp & 3;
+        const int row = fw * 32 + lane;
+        const int half = fw >> 1;
+        uint8_t *Ag = fgp ? A1 : A0;
         uint32_t mid_phase = 0;
         uint32_t tcnt = 0;
-        const bool tr = (tid == 0);
+        const bool tr = (tid == 0);                        // (trace: group 0 only)
         // normalised (and R-rotated) coordinates of this thread's point for pair-step `it`; evaluated one step
         // ahead so the global-load + divide latency hides behind the wait for the first mid-layer MMA
-        // A point is fetched in two halves so that nothing waits on HBM: raw loads two steps ahead (coordinates, centroid, scale
-        // and R of its cloud into registers, no dependent arithmetic), normalisation / rotation one hand-off later.
-        struct RawPoint { float x, y, z, cx, cy, cz, sc, r[9]; };
-        auto fetch_point = [&](int64_t it, RawPoint &w) {
+        auto load_point = [&](int64_t it, float &q0, float &q1, float &q2) {
             const int64_t st = s_begin + it;
             const int64_t cloud = st / ppc;
             const int64_t tile = 2 * (st % ppc) + rank;
             const int64_t pi = min(tile * (int64_t)kTP + row, p.n - 1);      // clamp: duplicates do not change a max
             const float *px = p.x + (cloud * p.n + pi) * 3;
-            w.x = __ldg(px); w.y = __ldg(px + 1); w.z = __ldg(px + 2);
-            w.cx = __ldg(p.centroid + cloud * 3); w.cy = __ldg(p.centroid + cloud * 3 + 1); w.cz = __ldg(p.centroid + cloud * 3 + 2);
-            w.sc = __ldg(p.scale + cloud);
-            if (p.R) {
-#pragma unroll
-                for (int i = 0; i < 9; ++i) w.r[i] = __ldg(p.R + cloud * 9 + i);
-            }
-        };
-        auto finish_point = [&](const RawPoint &w, float &q0, float &q1, float &q2) {
-            q0 = __fdiv_rn(__fsub_rn(w.x, w.cx), w.sc);                      // PointNet.py:691-706
-            q1 = __fdiv_rn(__fsub_rn(w.y, w.cy), w.sc);
-            q2 = __fdiv_rn(__fsub_rn(w.z, w.cz), w.sc);
+            const float cx = __ldg(p.centroid + cloud * 3), cy = __ldg(p.centroid + cloud * 3 + 1), cz = __ldg(p.centroid + cloud * 3 + 2);
+            const float sc = __ldg(p.scale + cloud);
+            q0 = __fdiv_rn(__fsub_rn(__ldg(px), cx), sc);                    // PointNet.py:691-706
+            q1 = __fdiv_rn(__fsub_rn(__ldg(px + 1), cy), sc);
+            q2 = __fdiv_rn(__fsub_rn(__ldg(px + 2), cz), sc);
             if (p.R) {                                                       // X = pc @ R (PointNet.py:207)
-                const float r0 = q0 * w.r[0] + q1 * w.r[3] + q2 * w.r[6];
-                const float r1 = q0 * w.r[1] + q1 * w.r[4] + q2 * w.r[7];
-                const float r2 = q0 * w.r[2] + q1 * w.r[5] + q2 * w.r[8];
+                const float *R = p.R + cloud * 9;
+                const float r0 = q0 * __ldg(R) + q1 * __ldg(R + 3) + q2 * __ldg(R + 6);
+                const float r1 = q0 * __ldg(R + 1) + q1 * __ldg(R + 4) + q2 * __ldg(R + 7);
+                const float r2 = q0 * __ldg(R + 2) + q1 * __ldg(R + 5) + q2 * __ldg(R + 8);
                 q0 = r0; q1 = r1; q2 = r2;
             }
         };
-        auto load_point = [&](int64_t it, float &q0, float &q1, float &q2) { RawPoint w; fetch_point(it, w); finish_point(w, q0, q1, q2); };
-        // L0 (3 -> 64, FMA) of a tile is computed into REGISTERS one step ahead — inside the wait for a mid-layer MMA, where the
-        // front warps would otherwise sleep — and only its eight 16-byte stores stay on the critical path (round 2: the traced
-        // front chain was 5.5 us per step, 0.77 us of it L0, against 4.1 us for the final layer it feeds).
-        float nq0 = 0.f, nq1 = 0.f, nq2 = 0.f;
-        uint32_t l0r[32];                                                    // relu(L0) of this thread's point, 64 bf16 values
-        auto l0_compute = [&](float q0, float q1, float q2) {
+        float q0 = 0.f, q1 = 0.f, q2 = 0.f, nq0 = 0.f, nq1 = 0.f, nq2 = 0.f;
+        if (nsteps > fgp) load_point(fgp, nq0, nq1, nq2);
+        for (int64_t it = fgp; it < nsteps; it += 2) {
+            if (tr) trace_ev(p, rank, 0, tcnt, 0x100);
+            q0 = nq0; q1 = nq1; q2 = nq2;
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
                 float o[8];
@@ -224,20 +220,9 @@ chain2_kernel(const ChainParams p)
                     const float v = fmaf(q2, w.z, fmaf(q1, w.y, fmaf(q0, w.x, w.w)));
                     o[e] = v > 0.f ? v : 0.f;
                 }
-                l0r[c * 4] = pack_bf16x2(o[0], o[1]); l0r[c * 4 + 1] = pack_bf16x2(o[2], o[3]);
-                l0r[c * 4 + 2] = pack_bf16x2(o[4], o[5]); l0r[c * 4 + 3] = pack_bf16x2(o[6], o[7]);
+                *reinterpret_cast<uint4 *>(Ag + sw128_offset(128, row, c * 8)) =
+                    make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
             }
-        };
-        if (nsteps > 0) {
-            load_point(0, nq0, nq1, nq2);
-            l0_compute(nq0, nq1, nq2);
-            if (nsteps > 1) load_point(1, nq0, nq1, nq2);
-        }
-        for (int64_t it = 0; it < nsteps; ++it) {
-            if (tr) trace_ev(p, rank, 0, tcnt, 0x100);
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-                *reinterpret_cast<uint4 *>(A0 + sw128_offset(128, row, c * 8)) = make_uint4(l0r[c * 4], l0r[c * 4 + 1], l0r[c * 4 + 2], l0r[c * 4 + 3]);
             // one arrival per WARP (8 per pair), not per thread: 256 serialized smem atomics per hand-off
             // were the dominant latency of the whole pipeline
             fence_proxy_async();
@@ -245,28 +230,25 @@ chain2_kernel(const ChainParams p)
             // Follower CTA -> leader barrier: relaxed cluster-scope arrive.  The payload (this CTA's smem) was made
             // visible to the async proxy by fence.proxy.async above, in program order before the arrive; a
             // release.cluster here costs ~0.5 us of MEMBAR on the critical path of every layer.
-            if (lane == 0) { if (rank == 0) mbar_arrive(&sh.a_full); else mbar_arrive_cluster_relaxed(&sh.a_full, 0); }
+            if (lane == 0) { if (rank == 0) mbar_arrive(&sh.a_full[fgp]); else mbar_arrive_cluster_relaxed(&sh.a_full[fgp], 0); }
             if (tr) trace_ev(p, rank, 0, tcnt, 0x101);
-            // next tile's L0 while the first mid-layer MMA runs (its point was loaded one step ago), then the loads of the tile after
-            // (the raw loads of the tile after next go out first: their HBM latency runs under the FMA work and the MMA wait)
-            RawPoint raw;
-            const bool have_raw = it + 2 < nsteps;
-            if (have_raw) fetch_point(it + 2, raw);
-            if (it + 1 < nsteps) l0_compute(nq0, nq1, nq2);
+            if (it + 2 < nsteps) load_point(it + 2, nq0, nq1, nq2);
             for (int l = 0; l < p.nmid; ++l) {
-                if (l == (p.nmid > 1 ? 1 : 0) && have_raw) finish_point(raw, nq0, nq1, nq2);    // after the first epilogue (when there is one): the loads have long landed
-                mbar_wait(&sh.mid_full, mid_phase, 11);
+                mbar_wait(&sh.mid_full[fgp], mid_phase, 11);
                 if (tr) trace_ev(p, rank, 0, tcnt, 0x110 + l);
                 mid_phase ^= 1;
                 tc_fence_after();
                 const bool last = (l == p.nmid - 1);
-                uint8_t *out = last ? H2 : ((l & 1) ? A0 : A1);
-                if (last && it >= 1) mbar_wait(&sh.h2_empty[half], (uint32_t)((it - 1) & 1), 12);
+                uint8_t *out = last ? H2 : Ag;
+                // H2 is written by the two groups in turn: step it may be written once step it - 1 has been consumed.  One barrier per
+                // step parity, so that a waiter is never more than one phase behind (a single barrier would skip phases per group
+                // and a parity wait would alias): completion k of h2_empty[q] = step 2 k + q consumed.
+                if (last && it >= 1) mbar_wait(&sh.h2_empty[(it - 1) & 1][half], (uint32_t)(((it - 1) >> 1) & 1), 12);
                 if (tr && last) trace_ev(p, rank, 0, tcnt, 0x120);
                 const int N = p.mid_n[l];
                 for (int c0 = 0; c0 < N; c0 += 64) {
                     uint32_t va[32], vb[32];
-                    const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16) + c0;
+                    const uint32_t taddr = tmem + ((uint32_t)(fw * 32) << 16) + (uint32_t)(fgp * 128) + c0;
                     tmem_ld32(taddr, va); tmem_ld32(taddr + 32, vb);
                     tmem_ld_wait();
 #pragma unroll
@@ -286,7 +268,7 @@ chain2_kernel(const ChainParams p)
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) {
-                    uint64_t *bar = last ? &sh.h2_full[half] : &sh.a_full;
+                    uint64_t *bar = last ? &sh.h2_full[half] : &sh.a_full[fgp];
                     if (rank == 0) mbar_arrive(bar); else mbar_arrive_cluster_relaxed(bar, 0);
                 }
                 if (tr) trace_ev(p, rank, 0, tcnt, 0x130 + l);
@@ -321,26 +303,36 @@ chain2_kernel(const ChainParams p)
 #pragma unroll
             for (int hj = 0; hj < 8; ++hj) {
                 const int j = hj & 3;
-                const uint32_t buf = (uint32_t)(g % 3);      // three TMEM accumulator buffers (TMEM: 128 mid + 3 x 128)
-                mbar_wait(&sh.acc_full[buf], (uint32_t)((g / 3) & 1), 13);
+                const uint32_t buf = (uint32_t)(g & 1);      // two TMEM accumulator buffers (TMEM: 2 x 128 mid + 2 x 128 final)
+                mbar_wait(&sh.acc_full[buf], (uint32_t)((g >> 1) & 1), 13);
                 if (tid == 128) trace_ev(p, rank, 1, tcnt, 0x200 + hj);
                 tc_fence_after();
-                // all 128 columns in flight at once, TMEM buffer released before the arithmetic
-                uint32_t v0[32], v1[32], v2[32], v3[32];
-                const uint32_t taddr = tmem + lane_base + 128 + buf * 128;
-                tmem_ld32(taddr, v0); tmem_ld32(taddr + 32, v1); tmem_ld32(taddr + 64, v2); tmem_ld32(taddr + 96, v3);
-                tmem_ld_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive_cluster_relaxed(&sh.acc_empty[buf], 0);
-                if (tid == 128) trace_ev(p, rank, 1, tcnt, 0x210 + hj);
-                float m0 = mx[j], m1 = -3.0e38f, m2 = -3.0e38f, m3 = -3.0e38f;      // 4 independent chains (FMNMX3)
+                // two passes of 64 columns (512 threads: 128 registers each); the buffer is released after the second load
+                const uint32_t taddr = tmem + lane_base + 256 + buf * 128;
+                float m0 = mx[j], m1 = -3.0e38f, m2 = -3.0e38f, m3 = -3.0e38f;      // independent chains (FMNMX3)
+                {
+                    uint32_t v0[32], v1[32];
+                    tmem_ld32(taddr, v0); tmem_ld32(taddr + 32, v1);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int e = 0; e < 32; e += 2) {
-                    m0 = fmaxf(fmaxf(m0, __uint_as_float(v0[e])), __uint_as_float(v0[e + 1]));
-                    m1 = fmaxf(fmaxf(m1, __uint_as_float(v1[e])), __uint_as_float(v1[e + 1]));
-                    m2 = fmaxf(fmaxf(m2, __uint_as_float(v2[e])), __uint_as_float(v2[e + 1]));
-                    m3 = fmaxf(fmaxf(m3, __uint_as_float(v3[e])), __uint_as_float(v3[e + 1]));
+                    for (int e = 0; e < 32; e += 2) {
+                        m0 = fmaxf(fmaxf(m0, __uint_as_float(v0[e])), __uint_as_float(v0[e + 1]));
+                        m1 = fmaxf(fmaxf(m1, __uint_as_float(v1[e])), __uint_as_float(v1[e + 1]));
+                    }
+                }
+                {
+                    uint32_t v2[32], v3[32];
+                    tmem_ld32(taddr + 64, v2); tmem_ld32(taddr + 96, v3);
+                    tmem_ld_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster_relaxed(&sh.acc_empty[buf], 0);
+                    if (tid == 128) trace_ev(p, rank, 1, tcnt, 0x210 + hj);
+#pragma unroll
+                    for (int e = 0; e < 32; e += 2) {
+                        m2 = fmaxf(fmaxf(m2, __uint_as_float(v2[e])), __uint_as_float(v2[e + 1]));
+                        m3 = fmaxf(fmaxf(m3, __uint_as_float(v3[e])), __uint_as_float(v3[e + 1]));
+                    }
                 }
                 const float m = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
                 mx[j] = m;
@@ -348,32 +340,33 @@ chain2_kernel(const ChainParams p)
             }
         }
         if (cur_cloud >= 0) flush(cur_cloud);
-    } else if (warp == 8) {
+    } else if (warp == 8 || warp == 11) {
         // =========================== mid-layer MMA issuer (leader CTA only) ===========================
         // Two independent issuing warps (mid layers here, final layer in warp 10) replace a single polling
         // state machine: every hand-off is a hardware-suspended mbarrier wait (wake-up ~100 cycles) instead of
         // a ~150-cycle test_wait poll per barrier per iteration, which had made the issuer the bottleneck.
-        if (rank == 0 && nsteps > 0) {
+        const int ig = warp == 11 ? 1 : 0;                 // one issuing warp per front group
+        if (rank == 0 && nsteps > ig) {
             mbar_wait_cluster(&sh.wready, 0, 14);
             const uint32_t lo_a0 = (smem_u32(A0) & 0x3FFFFu) >> 4, lo_a1 = (smem_u32(A1) & 0x3FFFFu) >> 4;
             const uint32_t lo_wm = (smem_u32(WM) & 0x3FFFFu) >> 4, lo_wc = (smem_u32(WC) & 0x3FFFFu) >> 4;
             uint32_t a_cnt = 0, tcnt = 0;
-            for (int64_t it = 0; it < nsteps; ++it) {
+            for (int64_t it = ig; it < nsteps; it += 2) {
                 for (int l = 0; l < p.nmid; ++l) {
-                    mbar_wait(&sh.a_full, a_cnt & 1, 24);
+                    mbar_wait(&sh.a_full[ig], a_cnt & 1, 24);
                     ++a_cnt;
                     const bool percloud = p.mid_cloud_stride[l] != 0;
                     if (percloud) mbar_wait(&sh.wc_ready[it & 1], (uint32_t)((it >> 1) & 1), 25);
                     tc_fence_after();
-                    const uint32_t a_lo = (l & 1) ? lo_a1 : lo_a0;
+                    const uint32_t a_lo = ig ? lo_a1 : lo_a0;
                     const uint32_t b_lo = percloud ? lo_wc + (uint32_t)(it & 1) * (4096u >> 4) : lo_wm + (wm2_slot(p.mid_slot[l]) >> 4);
                     const uint32_t idesc = make_idesc_bf16(256, (uint32_t)p.mid_n[l]);
                     if (elect_one_sync()) {
-                        trace_ev(p, rank, 2, tcnt, 0x300 + l);
+                        if (ig == 0) trace_ev(p, rank, 2, tcnt, 0x300 + l);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            mma2_bf16_ss(tmem, sdesc_from_lo(a_lo + k * 2), sdesc_from_lo(b_lo + k * 2), idesc, k > 0);
-                        mma2_commit_mc(&sh.mid_full, 3);
+                            mma2_bf16_ss(tmem + (uint32_t)(ig * 128), sdesc_from_lo(a_lo + k * 2), sdesc_from_lo(b_lo + k * 2), idesc, k > 0);
+                        mma2_commit_mc(&sh.mid_full[ig], 3);
                         if (percloud) mma2_commit_mc(&sh.wc_empty[it & 1], 3);
                     }
                     __syncwarp();
@@ -392,16 +385,16 @@ chain2_kernel(const ChainParams p)
                 for (int hf = 0; hf < 2; ++hf) {
                     mbar_wait(&sh.h2_full[hf], (uint32_t)(it & 1), 27);
                     for (int j = 0; j < 4; ++j, ++g) {
-                        const uint32_t buf = (uint32_t)(g % 3);
-                        if (g >= 3) mbar_wait(&sh.acc_empty[buf], (uint32_t)(((g / 3) - 1) & 1), 28);
+                        const uint32_t buf = (uint32_t)(g & 1);
+                        if (g >= 2) mbar_wait(&sh.acc_empty[buf], (uint32_t)(((g >> 1) - 1) & 1), 28);
                         // keep at most kFinalInFlight granules queued so a mid-layer MMA (critical path of the
                         // next tile, issued by warp 8 into the same tensor FIFO) never waits long
                         if (g >= kFinalInFlight)
-                            mbar_wait(&sh.acc_full[(g - kFinalInFlight) % 3], (uint32_t)(((g - kFinalInFlight) / 3) & 1), 29);
+                            mbar_wait(&sh.acc_full[(g - kFinalInFlight) & 1], (uint32_t)(((g - kFinalInFlight) >> 1) & 1), 29);
                         tc_fence_after();
                         const uint32_t a_lo = lo_w3 + (uint32_t)j * (32768u >> 4);
                         const uint32_t b_lo = lo_h2 + (uint32_t)hf * (8192u >> 4);
-                        const uint32_t d = tmem + 128 + buf * 128;
+                        const uint32_t d = tmem + 256 + buf * 128;
                         if (elect_one_sync()) {
                             trace_ev(p, rank, 3, tcnt, 0x400 + hf * 16 + j * 2);
 #pragma unroll
@@ -409,7 +402,7 @@ chain2_kernel(const ChainParams p)
                                 mma2_bf16_ss(d, sdesc_from_lo(a_lo + (kk >> 2) * (16384u >> 4) + (kk & 3) * 2),
                                              sdesc_from_lo(b_lo + (kk >> 2) * (16384u >> 4) + (kk & 3) * 2), idesc_fin, kk > 0);
                             mma2_commit_mc(&sh.acc_full[buf], 3);
-                            if (j == 3) mma2_commit_mc(&sh.h2_empty[hf], 3);
+                            if (j == 3) mma2_commit_mc(&sh.h2_empty[it & 1][hf], 3);
                         }
                         __syncwarp();
                     }
