@@ -314,10 +314,15 @@ class PointNet:
     def get_weights_dict(self) -> dict:
         return {name: self.get_tensor(name, cnt) for name, cnt in self.tensor_table()}
 
-    def save(self, path: str):
-        """Own weight container (.npz keyed by the reference's variable names + config JSON).
-        The reference's `.keras` zip needs h5py, which this environment lacks."""
+    def save(self, path: str, input_width=None):
+        """`*.keras`: the reference's archive format (pointnet_train.py:207-214, :280-295) — zip of config.json / metadata.json /
+        model.weights.h5 written without Keras or h5py (pointnet/keras_io.py, pointnet/hdf5_min.py).  Anything else: our own
+        container, `.npz` keyed by the reference's variable names + the config JSON."""
         p = Path(path)
+        if p.suffix == ".keras":
+            from . import keras_io
+            keras_io.save_keras(str(p), self.get_weights_dict(), self.get_config(), input_width)
+            return
         np.savez(p.with_suffix(".npz") if p.suffix != ".npz" else p, __config__=json.dumps(self.get_config()), **self.get_weights_dict())
 
     def export_onnx(self, path: str, input_width: int) -> str:
@@ -329,6 +334,13 @@ class PointNet:
 
     @classmethod
     def load(cls, path: str, **overrides):
+        if str(path).endswith(".keras"):                          # tf.keras.models.load_model(path, custom_objects=...) (pointnet_train.py:280-295)
+            from . import keras_io
+            weights, cfg = keras_io.load_keras(str(path))
+            cfg.update(overrides)
+            m = cls.from_config(cfg)
+            m.set_weights_dict(weights)
+            return m
         z = np.load(path, allow_pickle=False)
         cfg = json.loads(str(z["__config__"]))
         cfg.update(overrides)

@@ -63,3 +63,24 @@ def test_train_pointnet_driver_two_profiles(lib, tmp_path):
     # a second run reuses the existing PointCloudSets (pointnet_train.py:146-150)
     tp = pointnet_train.TrainProfile(str(cf))
     assert tp._training_profiles["final"]["pc"]._data_size["train"]["count"] == 30
+
+
+def test_keras_archive_save_load_identical_outputs(lib, tmp_path):
+    """PointNet.save('*.keras') / PointNet.load('*.keras') (pointnet_train.py:207-214, :280-295): the archive round trip
+    reproduces every weight and therefore the outputs, bit for bit."""
+    import torch
+    from oracle import pointnet_numpy as onp
+    from pointcloudprocessing_b200.pointnet import PointNet
+    from tests import synth
+    for vanilla in (False, True):
+        m = PointNet(23, 12, 0.3, 42, vanilla=vanilla, precision="bf16")
+        m.set_weights_dict(onp.make_params(23, 12, seed=7, vanilla=vanilla))
+        path = str(tmp_path / f"model_{int(vanilla)}.keras")
+        m.save(path, input_width=256)
+        m2 = PointNet.load(path, precision="bf16")
+        assert m2._vanilla == vanilla
+        w1, w2 = m.get_weights_dict(), m2.get_weights_dict()
+        assert set(w1) == set(w2) and all(np.array_equal(w1[k], w2[k]) for k in w1)
+        x = torch.from_numpy(synth.gaussian_clouds(3, 4, 256)).cuda()
+        for a, b in zip(m(x), m2(x)):
+            assert torch.equal(a, b)
