@@ -60,8 +60,10 @@ def weights_to_h5_tree(weights: dict, vanilla: bool):
     for prefix, kind, layer in _layer_entries(vanilla):
         inner = "conv" if kind == "conv" else "dense"
         k = np.asarray(weights[f"{layer}/kernel"], np.float32)
-        if kind == "conv":
-            k = k.reshape(1, 1, k.shape[-2], k.shape[-1])
+        if k.ndim < 2:                               # flat (PointNet.get_weights_dict): Cout is the length of the layer's BN gamma / bias
+            cout = np.asarray(weights[f"{layer}/bn/gamma"] if f"{layer}/bn/gamma" in weights else weights[f"{layer}/bias"]).size
+            k = k.reshape(-1, cout)
+        k = k.reshape((1, 1, k.shape[-2], k.shape[-1]) if kind == "conv" else (k.shape[-2], k.shape[-1]))
         groups += [f"{prefix}/vars", f"{prefix}/{inner}/vars"]
         ds[f"{prefix}/{inner}/vars/0"] = k
         if f"{layer}/bias" in weights:

@@ -215,6 +215,8 @@ class TrainProfile:
                     json.dump(history.history, j)
                 if not os.path.isfile(ckpt):
                     model.save(ckpt)
+                # the reference's artefact name and format (ModelCheckpoint(...*.keras), pointnet_train.py:207-214): same weights as the .npz
+                PointNet.load(ckpt, precision=self._precision).save(ckpt[:-4] + ".keras", input_width=self._input_width)
                 onnx_path = f"{self._model_path}{P['path']}{self._name}_{prof}.onnx"                # :237-247, opset 13, (None, n, 3) f32
                 model.export_onnx(onnx_path, self._input_width)
                 self._log.info(f"ONNX model written to {onnx_path}")

@@ -51,6 +51,8 @@ def test_train_pointnet_driver_two_profiles(lib, tmp_path):
     assert np.array_equal(a["s2_l3_1024_convolution_layer/kernel"], b["s2_l3_1024_convolution_layer/kernel"])
     assert not np.array_equal(a["seg_l1_512_convolution_layer/kernel"], b["seg_l1_512_convolution_layer/kernel"])
     m = PointNet.load(str(base / "final" / "unit_lidar_final.npz"))
+    mk = PointNet.load(str(base / "final" / "unit_lidar_final.keras"))          # the reference's artefact format, same weights
+    assert all(np.array_equal(v, mk.get_weights_dict()[k]) for k, v in m.get_weights_dict().items())
     cls, seg, R = m(np.zeros((2, 128, 3), np.float32) + rng.standard_normal((2, 128, 3)).astype(np.float32))
     assert cls.shape == (2, 3) and seg.shape == (2, 128, 4) and np.allclose(seg.sum(-1), 1, atol=1e-4)
     # the ONNX artefact (pointnet_train.py:237-247) holds the same network: executed by the independent reader it gives the model's outputs

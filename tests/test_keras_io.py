@@ -52,7 +52,8 @@ def test_keras_archive_round_trip(tmp_path, vanilla):
     cfg = {"classification_output_width": 23, "segmentation_output_width": 12, "dropout_rate": 0.3, "random_seed": 42, "debugging": False,
            "vanilla": vanilla, "regularize_input_transform": False, "regularize_feature_transform": True, "precision": "bf16"}
     path = tmp_path / "m.keras"
-    keras_io.save_keras(str(path), p, cfg, input_width=8192)
+    flat = {k: np.asarray(v).reshape(-1) for k, v in p.items()}            # what PointNet.get_weights_dict() hands over
+    keras_io.save_keras(str(path), flat, cfg, input_width=8192)
     with zipfile.ZipFile(path) as z:
         assert sorted(z.namelist()) == ["config.json", "metadata.json", "model.weights.h5"]
     w, c = keras_io.load_keras(str(path))
