@@ -115,6 +115,13 @@ int pcp_resize_to_width_f32(const float *d_x, const int32_t *d_labels, int b, in
 /* Farthest-point sampling: x (b, n, 3) -> idx (b, s) int32; first index = start; fp32
  * ((dx*dx + dy*dy) + dz*dz) without FMA, lowest index wins ties. */
 int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, pcp_stream stream);
+/* The same samples (bit-identical) with caller-owned scratch: with a workspace the library first puts every cloud in Morton order
+ * of a coarse grid and then skips, per iteration, the groups of points whose bounding sphere is farther from the new sample than
+ * their largest running distance — 2-3x faster on LiDAR-sized batches.  pcp_fps_workspace_bytes reports 0 where the plain kernel
+ * is the better choice (few or small clouds); pcp_fps_ws_f32 then ignores the workspace and runs pcp_fps_f32. */
+int pcp_fps_workspace_bytes(int b, int64_t n, int s, size_t *bytes);
+int pcp_fps_ws_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, void *d_workspace, size_t workspace_bytes,
+                   pcp_stream stream);
 /* out[c, j, :] = x[c, idx[c, j], :] ; labels likewise when non-NULL */
 int pcp_gather_points_f32(const float *d_x, const int32_t *d_labels, int b, int64_t n, const int32_t *d_idx, int s,
                           float *d_out, int32_t *d_labels_out, pcp_stream stream);

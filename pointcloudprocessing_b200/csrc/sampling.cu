@@ -12,6 +12,7 @@
 // Exclusive use of the device is assumed: CTAs of a cluster wait for their peers' records (bounded: a lost arrival traps).
 #include <cooperative_groups.h>
 
+#include <algorithm>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -118,6 +119,10 @@ __device__ __forceinline__ unsigned fps_winner(const FpsSide &S, int par, int cs
 
 // phase cycle totals of block 0 / thread 0 (development aid, read through pcp_fps_phase_cycles)
 __device__ unsigned long long g_fps_phase[8];
+// per-warp timeline of block 0, iterations [kFpsTraceIt0, kFpsTraceIt0 + 16): [it][warp][stamp] clock64 (PCP_FPS_PROF builds)
+constexpr int kFpsTraceIt0 = 600;
+__device__ long long g_fps_trace[16][kFpsWarps][6];
+#define FPS_TRACE(i) do { if (kProf && blockIdx.x == 0 && lane == 0 && it >= kFpsTraceIt0 && it < kFpsTraceIt0 + 16) g_fps_trace[it - kFpsTraceIt0][warp][i] = clock64(); } while (0)
 #define FPS_STAMP(i) do { if (kProf && blockIdx.x == 0 && tid == 0) { const long long t_ = clock64(); ph[i] += t_ - tprev; tprev = t_; } } while (0)
 
 template <int PPT, bool kProf, int SD = 0>
@@ -265,6 +270,463 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
     if (cs > 1) cluster.sync();    // no CTA may exit while a peer can still write into its slots
 }
 
+// ------------------------------------------------------------------------------------------------------------------------------
+// PRUNED variant (round 2).  The distance update of an iteration only changes points closer to the new sample than their running
+// minimum; late in the chain that is a small neighbourhood.  The cloud is first put in Morton order of a coarse grid (a counting
+// sort, fps_sort_* below) and every warp keeps a CONTIGUOUS run of the sorted cloud: rowsT rows of 32 points, split in groups of
+// kFpsGroupRows rows (224 points).  Per group the block keeps a bounding sphere and the group's largest running distance; a group
+// (and, one level up, a whole warp) whose sphere is farther from the new sample than sqrt(that distance) cannot change and is
+// skipped by a warp-uniform branch.  Skipping is conservative (1e-4 relative slack against fp32 rounding of the test itself) and
+// an updated group runs exactly the arithmetic of the unpruned kernel, so the samples stay bit-identical with the oracle; ties go to
+// the lowest ORIGINAL index, looked up in the sort's permutation only for the points that attain a group's maximum.
+constexpr int kFpsGroupRows = 7, kFpsGroups = 7;      // 7 x 7 = 49 rows = kFpsPruneReg + kFpsPruneSm
+constexpr int kFpsPruneReg = 13, kFpsPruneSm = 36;    // rows with the coordinates in registers / in shared memory (36 * 512 * 12 B = 216 KB)
+constexpr int kFpsSortBits = 5;                       // grid of 32^3 cells over the cloud's bounding cube
+constexpr int kFpsSortBins = 1 << (3 * kFpsSortBits);
+
+__device__ __forceinline__ unsigned fps_fenc(float f) { const unsigned b = __float_as_uint(f); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
+__device__ __forceinline__ float fps_fdec(unsigned k) { return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k); }
+__device__ __forceinline__ unsigned fps_part1by2(unsigned v)
+{
+    v &= 0x3ffu; v = (v | (v << 16)) & 0x30000ffu; v = (v | (v << 8)) & 0x300f00fu; v = (v | (v << 4)) & 0x30c30c3u; v = (v | (v << 2)) & 0x9249249u;
+    return v;
+}
+__device__ __forceinline__ unsigned fps_cell(float px, float py, float pz, const unsigned *bb)
+{
+    const float lx = fps_fdec(bb[0]), ly = fps_fdec(bb[1]), lz = fps_fdec(bb[2]);
+    const float ext = fmaxf(fmaxf(fps_fdec(bb[3]) - lx, fps_fdec(bb[4]) - ly), fps_fdec(bb[5]) - lz);
+    const float inv = ext > 0.f ? (float)(1 << kFpsSortBits) / ext : 0.f;
+    const float top = (float)((1 << kFpsSortBits) - 1);
+    const unsigned ix = (unsigned)fminf(fmaxf((px - lx) * inv, 0.f), top), iy = (unsigned)fminf(fmaxf((py - ly) * inv, 0.f), top),
+                   iz = (unsigned)fminf(fmaxf((pz - lz) * inv, 0.f), top);
+    return fps_part1by2(ix) | (fps_part1by2(iy) << 1) | (fps_part1by2(iz) << 2);
+}
+
+__global__ void fps_sort_init_kernel(unsigned *__restrict__ bbox, int b, int *__restrict__ hist, int64_t nh)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < (int64_t)b * 6) bbox[i] = (i % 6) < 3 ? 0xFFFFFFFFu : 0u;
+    for (int64_t j = i; j < nh; j += (int64_t)gridDim.x * blockDim.x) hist[j] = 0;
+}
+
+__global__ void __launch_bounds__(256)
+fps_sort_bbox_kernel(const float *__restrict__ x, int64_t n, unsigned *__restrict__ bbox)
+{
+    const int cloud = blockIdx.y;
+    const float *xc = x + (int64_t)cloud * n * 3;
+    unsigned lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256)
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { const unsigned k = fps_fenc(__ldg(xc + 3 * i + a)); lo[a] = min(lo[a], k); hi[a] = max(hi[a], k); }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const unsigned l = __reduce_min_sync(0xffffffffu, lo[a]), h = __reduce_max_sync(0xffffffffu, hi[a]);
+        if ((threadIdx.x & 31) == 0) { atomicMin(&bbox[cloud * 6 + a], l); atomicMax(&bbox[cloud * 6 + 3 + a], h); }
+    }
+}
+
+template <bool kScatter>
+__global__ void __launch_bounds__(256)
+fps_sort_pass_kernel(const float *__restrict__ x, int64_t n, const unsigned *__restrict__ bbox, int *__restrict__ hist, float *__restrict__ xs,
+                     int32_t *__restrict__ perm)
+{
+    const int cloud = blockIdx.y;
+    const float *xc = x + (int64_t)cloud * n * 3;
+    int *h = hist + (int64_t)cloud * kFpsSortBins;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+        const float px = __ldg(xc + 3 * i), py = __ldg(xc + 3 * i + 1), pz = __ldg(xc + 3 * i + 2);
+        const unsigned c = fps_cell(px, py, pz, bbox + cloud * 6);
+        if (!kScatter) atomicAdd(&h[c], 1);
+        else {
+            const int64_t pos = (int64_t)cloud * n + atomicAdd(&h[c], 1);
+            xs[3 * pos] = px; xs[3 * pos + 1] = py; xs[3 * pos + 2] = pz;
+            perm[pos] = (int32_t)i;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+fps_sort_scan_kernel(int *__restrict__ hist)
+{   // exclusive scan of one cloud's kFpsSortBins counters, in place
+    __shared__ int wsum[32];
+    int *h = hist + (int64_t)blockIdx.x * kFpsSortBins;
+    constexpr int per = kFpsSortBins / 1024;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int v[per], tot = 0;
+#pragma unroll
+    for (int j = 0; j < per; ++j) { v[j] = h[tid * per + j]; tot += v[j]; }
+    int inc = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = wsum[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+        wsum[lane] = wi - w;
+    }
+    __syncthreads();
+    int run = wsum[warp] + inc - tot;
+#pragma unroll
+    for (int j = 0; j < per; ++j) { h[tid * per + j] = run; run += v[j]; }
+}
+
+// low word of a key inside a block: bit 31 = a real point stands behind it, bit 30 = more than one point attains the value,
+// then warp | group | row | lane of the (first) point.  Uniqueness across the cluster is what the high word decides; whenever it does
+// not (two keys with the same distance, or bit 30), the iteration falls back to the original indices (np.argmax: lowest wins).
+__device__ __forceinline__ unsigned fps_local_id(bool multi, int warp, int g, int row, int lane)
+{
+    return 0x80000000u | (multi ? 0x40000000u : 0u) | ((unsigned)warp << 14) | ((unsigned)g << 11) | ((unsigned)row << 5) | (unsigned)lane;
+}
+
+__device__ __forceinline__ float fps_skip_threshold(float rad_inflated, float dmax)
+{   // skip when |q - c|^2 (fp32, any rounding) > thr: then every point of the sphere is farther from q than sqrt(dmax).
+    // sqrt.approx is within a few ulp — far inside the 1e-4 slack
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(dmax));
+    const float t = rad_inflated + r * 1.0001f;
+    return t * t * 1.0002f;
+}
+
+// the arg-max of the keys held by the lanes (low word 0: no key): its high word, the lane that holds the first of them, and whether it
+// is shared
+__device__ __forceinline__ unsigned fps_key_max(unsigned hi, unsigned lo, int &sel, bool &multi)
+{
+    const unsigned mhi = __reduce_max_sync(0xffffffffu, lo ? hi : 0u);
+    const unsigned eq = __ballot_sync(0xffffffffu, lo != 0u && hi == mhi);
+    sel = eq ? __ffs(eq) - 1 : -1;
+    const unsigned slo = __shfl_sync(0xffffffffu, lo, sel < 0 ? 0 : sel);
+    multi = __popc(eq) > 1 || (sel >= 0 && (slo & 0x40000000u));
+    return mhi;
+}
+
+// The hot loop must stay small and shallow: the instruction caches hold ~6 KB (L0) / 32 KB (L1.5), sixteen warps walk different
+// parts of it, and with ~100 of the 128 registers holding points there is nothing left to keep many loads in flight.  So
+//  - the per-group state lives in REGISTERS of lane g (sphere, threshold, key): the seven skip tests are one compare and a ballot;
+//  - the coordinates in shared memory are laid out per THREAD, row-major (x y z x y z ...) in 16-byte chunks [chunk][tid], so a group
+//    of 7 rows is 6-7 conflict-free LDS.128 from one base register instead of 21 scalar loads;
+//  - exchange: no block stage.  Every WARP pushes ONE 16-byte record (x, y, z, code) into every block of the cluster (st.async onto the
+//    receiver's transaction barrier) and every warp reduces the cs * 16 records itself; warps of a block only meet in the tie path.
+//    code = 0: the warp holds no point; else (float bits of its largest running distance + 1) | bit 31 when several of its points
+//    attain it.
+constexpr int kFpsPruneMaxCluster = 8;
+// try_wait with a suspend-time hint: the waiter sleeps in hardware instead of coming back every few hundred cycles to spin
+__device__ __forceinline__ void fps_wait_records(uint64_t *bar, uint32_t parity)
+{
+    uint32_t ok = 0u;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(umma::smem_u32(bar)), "r"(parity), "r"(20000u) : "memory");
+        if (ok) return;
+        if (clock64() - t0 > 4000000000ll) __trap();       // a lost record must fail the launch, not hang the device
+    }
+}
+
+template <int PPT, int SD, int CS, bool kProf>
+__global__ void __launch_bounds__(kFpsThreads, 1)
+fps_pruned_kernel(const float *__restrict__ xs, const int32_t *__restrict__ perm, const float *__restrict__ xorig, int64_t n, int s, int start,
+                  int32_t *__restrict__ idx_out, int ngroups, int dbg)
+{
+    constexpr int cs = CS;
+    static_assert(PPT + SD == kFpsGroupRows * kFpsGroups, "row groups must tile the thread's rows");
+    extern __shared__ __align__(16) float4 fps_dyn4[];
+    const int rowsT = ngroups * kFpsGroupRows;
+    const int arows = rowsT > PPT ? rowsT - PPT : 0;
+    __shared__ float4 slots[2][(CS * kFpsWarps < 32 ? 32 : CS * kFpsWarps)];
+    __shared__ unsigned tie_key[kFpsWarps];          // tie resolution: lowest original index per warp
+    __shared__ float4 tslots[CS];   // tie resolution: per block x, y, z, original index
+    __shared__ uint64_t xbar[2];
+
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank();
+    const int64_t cloud = blockIdx.x / cs;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float *xc = xs + cloud * n * 3;
+    const int32_t *pc = perm + cloud * n;
+    // groups of 224 consecutive sorted points are dealt round-robin over the blocks of the cluster and their warps, so the
+    // neighbourhood of a sample spreads over all of them: sorted position of (group g, row j of it, this lane)
+    auto gpos = [&](int r) -> int64_t {
+        const int g = r / kFpsGroupRows, j = r - g * kFpsGroupRows;
+        return ((int64_t)((g * kFpsWarps + warp) * cs + rank) * kFpsGroupRows + j) * 32 + lane;
+    };
+    const float4 *sb = fps_dyn4 + tid;                // chunk k of this thread: sb[k * 512]
+    auto srow = [&](int r, float &x, float &y, float &z) {      // a shared-memory row by run-time index (start-up / rare paths)
+        const float *f = reinterpret_cast<const float *>(fps_dyn4);
+        const int f0 = 3 * (r - PPT);
+        x = f[(((f0) >> 2) * kFpsThreads + tid) * 4 + ((f0) & 3)];
+        y = f[(((f0 + 1) >> 2) * kFpsThreads + tid) * 4 + ((f0 + 1) & 3)];
+        z = f[(((f0 + 2) >> 2) * kFpsThreads + tid) * 4 + ((f0 + 2) & 3)];
+    };
+
+    float px[PPT], py[PPT], pz[PPT], d[PPT], ds[SD];
+    unsigned long long realmask = 0ull;          // bit r: row r of this thread is a point of the cloud
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+        const int64_t gi = gpos(k);
+        const bool real = k < rowsT && gi < n;
+        if (real) realmask |= 1ull << k;
+        px[k] = real ? __ldg(xc + 3 * gi) : 0.f; py[k] = real ? __ldg(xc + 3 * gi + 1) : 0.f; pz[k] = real ? __ldg(xc + 3 * gi + 2) : 0.f;
+        d[k] = real ? __int_as_float(0x7f800000) : 0.f;      // padding is never "real" when keys are built
+    }
+#pragma unroll
+    for (int k = 0; k < SD; ++k) {
+        const bool real = k < arows && gpos(PPT + k) < n;
+        if (real) realmask |= 1ull << (PPT + k);
+        ds[k] = real ? __int_as_float(0x7f800000) : 0.f;
+    }
+    {
+        const int nch = (3 * arows + 3) / 4;
+        for (int k = 0; k < nch; ++k) {
+            float v[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int f = 4 * k + e, r = PPT + f / 3, c = f - 3 * (f / 3);
+                const int64_t gi = gpos(r);
+                v[e] = (r < rowsT && gi < n) ? __ldg(xc + 3 * gi + c) : 0.f;
+            }
+            fps_dyn4[k * kFpsThreads + tid] = make_float4(v[0], v[1], v[2], v[3]);
+        }
+    }
+    // bounding spheres: centre = mean of the group's real points, radius = farthest of them (fp32, inflated); lane g keeps group g's
+    float scx = 0.f, scy = 0.f, scz = 0.f, srad = 0.f, sthr = -1.f;      // thr -1: always skipped (lanes >= 7, empty groups)
+    unsigned khi = 0u, klo = 0u;                                          // lane g: key of group g (klo: fps_local_id, 0 = no point)
+    for (int g = 0; g < kFpsGroups; ++g) {       // (not unrolled: start-up code, the register rows are read through a select chain)
+        float ax = 0.f, ay = 0.f, az = 0.f, cnt = 0.f, qx[kFpsGroupRows], qy[kFpsGroupRows], qz[kFpsGroupRows];
+#pragma unroll
+        for (int j = 0; j < kFpsGroupRows; ++j) {
+            const int r = g * kFpsGroupRows + j;
+            qx[j] = qy[j] = qz[j] = 0.f;
+            if (r < PPT) {
+#pragma unroll
+                for (int k = 0; k < PPT; ++k)
+                    if (k == r) { qx[j] = px[k]; qy[j] = py[k]; qz[j] = pz[k]; }
+            } else if (r - PPT < arows) srow(r, qx[j], qy[j], qz[j]);
+            if ((realmask >> r) & 1ull) { ax += qx[j]; ay += qy[j]; az += qz[j]; cnt += 1.f; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            ax += __shfl_xor_sync(0xffffffffu, ax, o); ay += __shfl_xor_sync(0xffffffffu, ay, o);
+            az += __shfl_xor_sync(0xffffffffu, az, o); cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        }
+        const float ic = cnt > 0.f ? 1.f / cnt : 0.f;
+        const float mx = ax * ic, my = ay * ic, mz = az * ic;
+        float r2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < kFpsGroupRows; ++j)
+            if ((realmask >> (g * kFpsGroupRows + j)) & 1ull)
+                r2 = fmaxf(r2, (qx[j] - mx) * (qx[j] - mx) + (qy[j] - my) * (qy[j] - my) + (qz[j] - mz) * (qz[j] - mz));
+        r2 = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(r2)));
+        if (lane == g) {
+            // a populated group is never skipped before its first update; an empty one always is
+            scx = mx; scy = my; scz = mz;
+            srad = sqrtf(r2) * 1.0001f + 1e-30f;
+            sthr = cnt > 0.f ? __int_as_float(0x7f800000) : -1.f;
+        }
+    }
+    const float *xo = xorig + cloud * n * 3;
+    float cx = __ldg(xo + 3 * (int64_t)start), cy = __ldg(xo + 3 * (int64_t)start + 1), cz = __ldg(xo + 3 * (int64_t)start + 2);
+    if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
+
+    constexpr int nrec = CS * kFpsWarps;         // records per iteration
+    if (nrec < 32 && tid < 32) { slots[0][tid] = make_float4(0.f, 0.f, 0.f, 0.f); slots[1][tid] = make_float4(0.f, 0.f, 0.f, 0.f); }   // unused slots read as "no point"
+    if (tid == 0) { umma::mbar_init(&xbar[0], 1); umma::mbar_init(&xbar[1], 1); umma::fence_barrier_init(); }
+    __syncthreads();
+    if (tid == 0) { umma::mbar_arrive_expect_tx(&xbar[0], nrec * 16u); umma::mbar_arrive_expect_tx(&xbar[1], nrec * 16u); }
+    cluster.sync();                              // every block is armed before anybody pushes
+    long long ph[6] = {0, 0, 0, 0, 0, 0}, tprev = clock64();
+    unsigned long long nact = 0, nties = 0;
+    unsigned wcode = 0u, wlo = 0u;               // this warp's record (warp-uniform): code, local id and coordinates of its best point
+    float wx = 0.f, wy = 0.f, wz = 0.f;
+    for (int it = 1; it < s; ++it) {
+        FPS_TRACE(0);
+        const float tdx = cx - scx, tdy = cy - scy, tdz = cz - scz;
+        unsigned act = __ballot_sync(0xffffffffu, !(tdx * tdx + tdy * tdy + tdz * tdz > sthr));
+        if (dbg == 1 && it > 1) act = 0u;            // development: exchange only (results wrong)
+        if (act) {
+#pragma unroll
+            for (int g = 0; g < kFpsGroups; ++g) {
+                if (!((act >> g) & 1u)) continue;
+                if (kProf) ++nact;
+                // the shared-memory part of the group: floats [f_lo, f_hi) of this thread, in chunks [k_lo, k_hi]
+                constexpr int kNone = 0;
+                const int r_lo = g * kFpsGroupRows < PPT ? PPT : g * kFpsGroupRows, r_hi = (g + 1) * kFpsGroupRows;      // rows [r_lo, r_hi) in smem
+                const int k_lo = r_lo < r_hi ? (3 * (r_lo - PPT)) / 4 : kNone, k_hi = r_lo < r_hi ? (3 * (r_hi - PPT) - 1) / 4 : kNone - 1;
+                float4 ch[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (k_lo + k <= k_hi) ch[k] = sb[(k_lo + k) * kFpsThreads];
+                auto sf = [&](int f) -> float {      // float f of this thread's shared rows (compile-time f after unrolling)
+                    const float4 &c = ch[(f >> 2) - k_lo < 8 && (f >> 2) >= k_lo ? (f >> 2) - k_lo : 0];
+                    return (f & 3) == 0 ? c.x : (f & 3) == 1 ? c.y : (f & 3) == 2 ? c.z : c.w;
+                };
+                float lbv = -1.f;
+#pragma unroll
+                for (int j = 0; j < kFpsGroupRows; ++j) {
+                    const int r = g * kFpsGroupRows + j;
+                    if (r < PPT) {
+                        const int k = r < PPT ? r : 0;
+                        d[k] = fminf(d[k], sqdist_nofma(px[k], py[k], pz[k], cx, cy, cz));
+                        lbv = fmaxf(lbv, d[k]);
+                    } else {
+                        const int k = r >= PPT ? r - PPT : 0;
+                        ds[k] = fminf(ds[k], sqdist_nofma(sf(3 * k), sf(3 * k + 1), sf(3 * k + 2), cx, cy, cz));
+                        lbv = fmaxf(lbv, ds[k]);
+                    }
+                }
+                // the group's maximum over its REAL points (padding rows hold 0 and never raise it), the first point that attains
+                // it and whether it is alone
+                const unsigned mine = (unsigned)(realmask >> (g * kFpsGroupRows)) & ((1u << kFpsGroupRows) - 1u);
+                const unsigned gm = __reduce_max_sync(0xffffffffu, mine ? __float_as_uint(lbv) : 0u);
+                unsigned at = 0u;            // real rows of this lane at the maximum
+#pragma unroll
+                for (int j = 0; j < kFpsGroupRows; ++j) {
+                    const int r = g * kFpsGroupRows + j;
+                    const float dv = r < PPT ? d[r < PPT ? r : 0] : ds[r >= PPT ? r - PPT : 0];
+                    if (__float_as_uint(dv) == gm) at |= 1u << j;
+                }
+                at &= mine;
+                const unsigned lanes_at = __ballot_sync(0xffffffffu, at != 0u);
+                const unsigned multi_l = __ballot_sync(0xffffffffu, (at & (at - 1u)) != 0u);
+                const int ol = __ffs(lanes_at) - 1;
+                const unsigned oat = __shfl_sync(0xffffffffu, at, ol < 0 ? 0 : ol);
+                if (lane == g) {
+                    khi = gm;
+                    klo = lanes_at ? fps_local_id((lanes_at & (lanes_at - 1u)) != 0u || multi_l != 0u, warp, g, g * kFpsGroupRows + __ffs(oat) - 1, ol) : 0u;
+                    sthr = lanes_at ? fps_skip_threshold(srad, __uint_as_float(gm)) : -1.f;
+                }
+            }
+            // the warp's record: its best group's key and that point's coordinates
+            int sel; bool multi;
+            const unsigned whi = fps_key_max(khi, klo, sel, multi);
+            wlo = sel < 0 ? 0u : __shfl_sync(0xffffffffu, klo, sel);
+            wcode = sel < 0 ? 0u : (whi + 1u) | (multi ? 0x80000000u : 0u);
+            const int ol = (int)(wlo & 31u), orow = (int)((wlo >> 5) & 63u);
+            float rx = 0.f, ry = 0.f, rz = 0.f;
+            if (sel >= 0 && lane == ol) {
+                if (orow >= PPT) srow(orow, rx, ry, rz);
+                else {
+#pragma unroll
+                    for (int k = 0; k < PPT; ++k)
+                        if (k == orow) { rx = px[k]; ry = py[k]; rz = pz[k]; }
+                }
+            }
+            wx = __shfl_sync(0xffffffffu, rx, ol); wy = __shfl_sync(0xffffffffu, ry, ol); wz = __shfl_sync(0xffffffffu, rz, ol);
+        }
+        FPS_STAMP(0);
+        FPS_TRACE(1);
+        const int par = it & 1;
+        if (lane < cs)       // lane t -> block t of the cluster: data and its arrival in one remote operation
+            fps_st_async16(&slots[par][rank * kFpsWarps + warp], &xbar[par], (uint32_t)lane, __float_as_uint(wx), __float_as_uint(wy),
+                           __float_as_uint(wz), wcode);
+        FPS_STAMP(3);
+        FPS_TRACE(2);
+        // CTA-scope wait: the records land in THIS block's shared memory through the async proxy, ordered by the barrier's transaction
+        // count (each barrier completes every second iteration)
+        fps_wait_records(&xbar[par], ((unsigned)(it - 1) >> 1) & 1u);
+        // re-arm for iteration it + 2: nobody pushes that early (it takes this block's it + 1 records, which follow this in tid 0's
+        // program order)
+        if (tid == 0 && it + 2 < s) umma::mbar_arrive_expect_tx(&xbar[par], nrec * 16u);
+        FPS_STAMP(4);
+        FPS_TRACE(3);
+        // every warp reduces the records itself: per lane the first best of its records, then across lanes
+        constexpr int kPerLane = nrec <= 32 ? 1 : nrec / 32;
+        float4 rc[kPerLane];
+#pragma unroll
+        for (int e = 0; e < kPerLane; ++e) rc[e] = slots[par][lane + 32 * e];
+        float4 brec = rc[0];
+        unsigned bcode = __float_as_uint(rc[0].w), bi = (unsigned)lane;
+#pragma unroll
+        for (int e = 1; e < kPerLane; ++e) {
+            const unsigned c = __float_as_uint(rc[e].w);
+            if ((c & 0x7FFFFFFFu) > (bcode & 0x7FFFFFFFu)) { brec = rc[e]; bcode = c; bi = (unsigned)(lane + 32 * e); }
+            else if (c != 0u && (c & 0x7FFFFFFFu) == (bcode & 0x7FFFFFFFu)) bcode |= 0x80000000u;
+        }
+        const unsigned cmax = __reduce_max_sync(0xffffffffu, bcode & 0x7FFFFFFFu);       // > 0: the cloud has points
+        const unsigned eq = __ballot_sync(0xffffffffu, (bcode & 0x7FFFFFFFu) == cmax && bcode != 0u);
+        const int sl = __ffs(eq) - 1;
+        const bool tie = (eq & (eq - 1u)) != 0u || (__shfl_sync(0xffffffffu, bcode, sl) & 0x80000000u) != 0u;
+        const unsigned dmax = cmax - 1u;
+        FPS_TRACE(4);
+        if (!tie) {
+            cx = __shfl_sync(0xffffffffu, brec.x, sl); cy = __shfl_sync(0xffffffffu, brec.y, sl); cz = __shfl_sync(0xffffffffu, brec.z, sl);
+            const int wi = (int)__shfl_sync(0xffffffffu, bi, sl);
+            // the one thread that holds the winner translates its sorted position (a load that nothing in the loop waits for)
+            if (wi == rank * kFpsWarps + warp && lane == (int)(wlo & 31u))
+                idx_out[cloud * s + it] = __ldg(pc + gpos((int)((wlo >> 5) & 63u)));
+        } else {
+            // several points share the largest distance: np.argmax takes the lowest original index.  Every warp of the cluster sees
+            // the same records and takes this branch.
+            if (kProf) ++nties;
+            unsigned cand = 0xFFFFFFFFu;
+            int crow = 0;
+            const unsigned gat = __ballot_sync(0xffffffffu, klo != 0u && khi == dmax);      // groups of this warp at the maximum
+            for (int g = 0; g < kFpsGroups; ++g) {      // (not unrolled: rare path, keep it out of the instruction cache's way)
+                if (!((gat >> g) & 1u)) continue;
+#pragma unroll
+                for (int j = 0; j < kFpsGroupRows; ++j) {
+                    const int r = g * kFpsGroupRows + j;
+                    float dv = 0.f;
+                    if (r < PPT) {
+#pragma unroll
+                        for (int k = 0; k < PPT; ++k)
+                            if (k == r) dv = d[k];
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < SD; ++k)
+                            if (k == r - PPT) dv = ds[k];
+                    }
+                    if (__float_as_uint(dv) == dmax && ((realmask >> r) & 1ull)) {
+                        const unsigned o = (unsigned)__ldg(pc + gpos(r));
+                        if (o < cand) { cand = o; crow = r; }
+                    }
+                }
+            }
+            const unsigned wmin = __reduce_min_sync(0xffffffffu, cand);
+            if (lane == 0) tie_key[warp] = wmin;
+            __syncthreads();
+            const unsigned bmin = __reduce_min_sync(0xffffffffu, lane < kFpsWarps ? tie_key[lane] : 0xFFFFFFFFu);
+            const bool own_w = bmin != 0xFFFFFFFFu ? tie_key[warp] == bmin : warp == 0;
+            if (own_w) {
+                float rx = 0.f, ry = 0.f, rz = 0.f;
+                const unsigned who = __ballot_sync(0xffffffffu, bmin != 0xFFFFFFFFu && cand == bmin);
+                const int ol = who ? __ffs(who) - 1 : 0;
+                if (who && lane == ol) {
+                    if (crow >= PPT) srow(crow, rx, ry, rz);
+                    else {
+#pragma unroll
+                        for (int k = 0; k < PPT; ++k)
+                            if (k == crow) { rx = px[k]; ry = py[k]; rz = pz[k]; }
+                    }
+                }
+                rx = __shfl_sync(0xffffffffu, rx, ol); ry = __shfl_sync(0xffffffffu, ry, ol); rz = __shfl_sync(0xffffffffu, rz, ol);
+                const float4 rec = make_float4(rx, ry, rz, __uint_as_float(bmin));
+                if (lane < cs) *cluster.map_shared_rank(&tslots[rank], lane) = rec;
+            }
+            asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+            fps_wait();
+            const float4 t = tslots[lane < cs ? lane : 0];
+            const unsigned ti = lane < cs ? __float_as_uint(t.w) : 0xFFFFFFFFu;
+            const unsigned tmin = __reduce_min_sync(0xffffffffu, ti);
+            const int tb = __ffs(__ballot_sync(0xffffffffu, ti == tmin)) - 1;
+            cx = __shfl_sync(0xffffffffu, t.x, tb); cy = __shfl_sync(0xffffffffu, t.y, tb); cz = __shfl_sync(0xffffffffu, t.z, tb);
+            if (rank == 0 && tid == 0) idx_out[cloud * s + it] = (int32_t)tmin;
+        }
+        FPS_STAMP(5);
+        FPS_TRACE(5);
+    }
+    if (kProf) {
+        // groups updated by block 0's warps over the whole chain (of 16 warps x 7 groups x (s - 1)), and the tie iterations
+        if (blockIdx.x == 0 && lane == 0) atomicAdd(&g_fps_phase[6], nact);
+        if (blockIdx.x == 0 && tid == 0) {
+            for (int i = 0; i < 6; ++i) g_fps_phase[i] = (unsigned long long)ph[i];
+            g_fps_phase[7] = nties;
+        }
+    }
+    cluster.sync();     // no block may exit while a peer can still write into its slots
+}
+
 // Fallback for clouds too large to stay register-resident: one CTA per cloud, running distances in
 // a global scratch array (L2-resident for realistic sizes).  Same arithmetic and tie-break.
 __global__ void __launch_bounds__(1024, 1)
@@ -340,9 +802,129 @@ static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int3
 static float *g_fps_scratch = nullptr;
 static size_t g_fps_scratch_bytes = 0;
 
+// ---- pruned path: geometry, workspace layout and launch
+struct FpsPrunePlan {
+    int cs = 0, ngroups = 0;
+    size_t off_xs = 0, off_perm = 0, off_hist = 0, off_bbox = 0, bytes = 0;
+};
+
+static bool fps_prune_plan(int b, int64_t n, int s, FpsPrunePlan &pl)
+{
+    static const bool off = getenv("PCP_FPS_NO_PRUNE") != nullptr;
+    if (off || s < 32 || n >= 0x7FFFFFFFll) return false;
+    // the cluster that keeps a cloud on chip with 49 rows of 512 points per block (13 rows in registers, 36 with the coordinates in
+    // shared memory): the pruned kernel is built for that shape only
+    constexpr int rows_max = kFpsPruneReg + kFpsPruneSm;
+    int cs = 1;
+    while (cs <= kFpsPruneMaxCluster && n > (int64_t)cs * kFpsThreads * rows_max) cs *= 2;
+    if (cs > kFpsPruneMaxCluster) return false;
+    // only where the register-resident clusters (25 rows per block) would not all be resident at once — the batch sizes the
+    // hybrid kernel was built for; a few clouds are faster spread over wide clusters
+    int cs_reg = 1;
+    while (cs_reg < kFpsMaxCluster && n > (int64_t)cs_reg * kFpsThreads * 25) cs_reg *= 2;
+    static const bool force = getenv("PCP_FPS_FORCE_PRUNE") != nullptr;
+    if (!force && (int64_t)b * cs_reg <= sm_count()) return false;
+    const int64_t per_group = (int64_t)cs * kFpsWarps * kFpsGroupRows * 32;      // points one group slot holds across the cluster
+    const int ngroups = (int)((n + per_group - 1) / per_group);
+    if (ngroups < 3) return false;                               // small clouds: the register-only kernel, nothing to prune at 1-2 ms
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    pl.cs = cs; pl.ngroups = ngroups;
+    pl.off_xs = 0;
+    pl.off_perm = up((size_t)b * n * 3 * sizeof(float));
+    pl.off_hist = pl.off_perm + up((size_t)b * n * sizeof(int32_t));
+    pl.off_bbox = pl.off_hist + up((size_t)b * kFpsSortBins * sizeof(int));
+    pl.bytes = pl.off_bbox + up((size_t)b * 6 * sizeof(unsigned));
+    return true;
+}
+
+template <int CS, bool kProf>
+static int launch_fps_pruned_cs(const float *xs, const int32_t *perm, const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx,
+                                const FpsPrunePlan &pl, int dbg, cudaStream_t st)
+{
+    auto kern = fps_pruned_kernel<kFpsPruneReg, kFpsPruneSm, CS, kProf>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        PCP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ((3 * kFpsPruneSm + 3) / 4) * kFpsThreads * 16));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((int64_t)b * CS));
+    cfg.blockDim = dim3(kFpsThreads);
+    cfg.dynamicSmemBytes = (size_t)((3 * (pl.ngroups * kFpsGroupRows - kFpsPruneReg) + 3) / 4) * kFpsThreads * 16;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, xs, perm, d_x, n, s, start, d_idx, pl.ngroups, dbg));
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+template <bool kProf>
+static int launch_fps_pruned(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, const FpsPrunePlan &pl, void *ws, cudaStream_t st)
+{
+    auto *base = static_cast<unsigned char *>(ws);
+    float *xs = reinterpret_cast<float *>(base + pl.off_xs);
+    int32_t *perm = reinterpret_cast<int32_t *>(base + pl.off_perm);
+    int *hist = reinterpret_cast<int *>(base + pl.off_hist);
+    unsigned *bbox = reinterpret_cast<unsigned *>(base + pl.off_bbox);
+    const int64_t nh = (int64_t)b * kFpsSortBins;
+    fps_sort_init_kernel<<<(unsigned)std::min<int64_t>((nh + 255) / 256, 4096), 256, 0, st>>>(bbox, b, hist, nh);
+    PCP_CHECK_LAUNCH();
+    const dim3 grid((unsigned)std::min<int64_t>((n + 2047) / 2048, 1024), (unsigned)b);
+    fps_sort_bbox_kernel<<<grid, 256, 0, st>>>(d_x, n, bbox);
+    PCP_CHECK_LAUNCH();
+    fps_sort_pass_kernel<false><<<grid, 256, 0, st>>>(d_x, n, bbox, hist, nullptr, nullptr);
+    PCP_CHECK_LAUNCH();
+    fps_sort_scan_kernel<<<b, 1024, 0, st>>>(hist);
+    PCP_CHECK_LAUNCH();
+    fps_sort_pass_kernel<true><<<grid, 256, 0, st>>>(d_x, n, bbox, hist, xs, perm);
+    PCP_CHECK_LAUNCH();
+
+    static const int dbg = getenv("PCP_FPS_PRUNE_DBG") ? atoi(getenv("PCP_FPS_PRUNE_DBG")) : 0;      // development (see the kernel)
+    switch (pl.cs) {
+    case 1: return launch_fps_pruned_cs<1, kProf>(xs, perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    case 2: return launch_fps_pruned_cs<2, kProf>(xs, perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    case 4: return launch_fps_pruned_cs<4, kProf>(xs, perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    default: return launch_fps_pruned_cs<8, kProf>(xs, perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    }
+}
+
 }  // namespace pcp
 
 using namespace pcp;
+
+extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, pcp_stream stream);
+
+extern "C" int pcp_fps_workspace_bytes(int b, int64_t n, int s, size_t *bytes)
+{
+    PCP_REQUIRE(bytes && b >= 0 && n >= 1 && s >= 1, PCP_ERR_INVALID, "pcp_fps_workspace_bytes: bad arguments");
+    FpsPrunePlan pl;
+    *bytes = (b > 0 && fps_prune_plan(b, n, s, pl)) ? pl.bytes : 0;
+    return PCP_OK;
+}
+
+extern "C" int pcp_fps_ws_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, void *d_workspace, size_t workspace_bytes,
+                              pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && d_idx && b >= 0 && n >= 1 && s >= 1 && start >= 0 && start < n, PCP_ERR_INVALID,
+                "pcp_fps_ws_f32: bad arguments (b=%d n=%lld s=%d start=%d)", b, (long long)n, s, start);
+    if (b == 0) return PCP_OK;
+    FpsPrunePlan pl;
+    if (!fps_prune_plan(b, n, s, pl)) return pcp_fps_f32(d_x, b, n, s, start, d_idx, stream);
+    PCP_REQUIRE(d_workspace && workspace_bytes >= pl.bytes && (reinterpret_cast<uintptr_t>(d_workspace) & 255) == 0, PCP_ERR_INVALID,
+                "pcp_fps_ws_f32: workspace of %zu bytes (256-byte aligned) needed, %zu given — size it with pcp_fps_workspace_bytes", pl.bytes,
+                workspace_bytes);
+    static const bool prof = getenv("PCP_FPS_PROF") != nullptr;
+    if (prof) {
+        unsigned long long zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        PCP_CUDA_OK(cudaMemcpyToSymbol(g_fps_phase, zero, sizeof(zero)));
+        return launch_fps_pruned<true>(d_x, b, n, s, start, d_idx, pl, d_workspace, as_stream(stream));
+    }
+    return launch_fps_pruned<false>(d_x, b, n, s, start, d_idx, pl, d_workspace, as_stream(stream));
+}
 
 extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, pcp_stream stream)
 {
@@ -408,6 +990,14 @@ extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start,
 
 /* development aid: cycles block 0 / thread 0 of the last PCP_FPS_PROF=1 launch (PPT = 25) spent in: distance loop, candidate
  * search + record, __syncthreads, warp-0 stage + DSMEM pushes, cluster barrier, slot read-back */
+extern "C" int pcp_fps_trace(long long *out, int count)
+{
+    PCP_REQUIRE(out && count == 16 * kFpsWarps * 6, PCP_ERR_INVALID, "pcp_fps_trace: count must be %d", 16 * kFpsWarps * 6);
+    PCP_CUDA_OK(cudaDeviceSynchronize());
+    PCP_CUDA_OK(cudaMemcpyFromSymbol(out, g_fps_trace, sizeof(long long) * count));
+    return PCP_OK;
+}
+
 extern "C" int pcp_fps_phase_cycles(unsigned long long out[8])
 {
     PCP_CUDA_OK(cudaDeviceSynchronize());

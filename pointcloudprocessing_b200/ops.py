@@ -62,13 +62,28 @@ def rotate(x: torch.Tensor, R: torch.Tensor) -> torch.Tensor:
     return y
 
 
-def farthest_point_sample(x: torch.Tensor, s: int, start: int = 0) -> torch.Tensor:
-    """(b, n, 3) -> (b, s) int32 indices, bit-exact with oracle/sampling.py:fps."""
+def farthest_point_sample(x: torch.Tensor, s: int, start: int = 0, workspace: torch.Tensor | None = None) -> torch.Tensor:
+    """(b, n, 3) -> (b, s) int32 indices, bit-exact with oracle/sampling.py:fps.  `workspace`: optional caller-owned uint8 scratch of
+    fps_workspace_bytes(b, n, s) bytes for the pruned kernel (allocated here when omitted)."""
     x = _chk_cloud(x)
     b, n, _ = x.shape
     idx = torch.empty((b, s), device=x.device, dtype=torch.int32)
-    _ffi.check(_ffi.load().pcp_fps_f32(_ffi.ptr(x), b, n, s, start, _ffi.ptr(idx), _ffi.stream_ptr()))
+    lib = _ffi.load()
+    need = C.c_size_t(0)
+    _ffi.check(lib.pcp_fps_workspace_bytes(b, n, s, C.byref(need)))
+    if workspace is None and need.value:
+        workspace = torch.empty(need.value, device=x.device, dtype=torch.uint8)   # caching allocator: no cudaMalloc in the steady state
+    if need.value and (workspace.numel() * workspace.element_size() < need.value or workspace.device != x.device):
+        raise ValueError(f"farthest_point_sample: workspace of {need.value} bytes on {x.device} needed")
+    _ffi.check(lib.pcp_fps_ws_f32(_ffi.ptr(x), b, n, s, start, _ffi.ptr(idx), _ffi.ptr(workspace) if need.value else None,
+                                  need.value, _ffi.stream_ptr()))
     return idx
+
+
+def fps_workspace_bytes(b: int, n: int, s: int) -> int:
+    need = C.c_size_t(0)
+    _ffi.check(_ffi.load().pcp_fps_workspace_bytes(b, n, s, C.byref(need)))
+    return need.value
 
 
 def gather_points(x: torch.Tensor, idx: torch.Tensor, labels: torch.Tensor | None = None):
