@@ -6,11 +6,17 @@
 // FMNMX over TMEM columns -> per-cloud atomicMax.  No per-point activation ever reaches HBM: the chain
 // reads 12 B/point and writes 4 KB/cloud.
 //
-// Warp roles (320 threads, 1 CTA/SM, persistent over a contiguous range of 128-point tiles):
-//   warps 0-3  front: normalise + L0 + mid-layer epilogues (TMEM -> regs -> bf16 -> smem)
-//   warps 4-7  final epilogue: TMEM -> running per-channel max -> atomicMax
-//   warp  8    MMA issuer (one thread): interleaves mid-layer MMAs of tile i+1 with the final layer of tile i
-//   warp  9    loader (one thread): weight images via cp.async.bulk (TMA engine) + TMEM allocation
+// Warp roles (512 threads, one CTA per SM, CTA pairs (cta_group::2), persistent over a contiguous range of pair-steps of
+// 2 x 128 points, TWO pair-steps in flight — even steps belong to front group 0, odd steps to front group 1):
+//   warps 0-3   front group 0: normalise + L0 + mid-layer epilogues (TMEM -> regs -> bf16 -> smem, IN PLACE into the operand
+//               buffer A0 its own MMA has finished reading; the last layer's epilogue writes the shared H2 halves)
+//   warps 12-15 front group 1: the same on buffer A1 / the second mid accumulator (same TMEM lane quarters as warps 0-3)
+//   warps 4-7   final epilogue: TMEM (two 64-column passes) -> running per-channel max -> atomicMax
+//   warp  8/11  mid-layer MMA issuer of group 0 / 1 (one elected thread each)
+//   warp  10    final-layer MMA issuer (two granules in flight)
+//   warp  9     loader (one thread): weight images via cp.async.bulk (TMA engine) + TMEM allocation
+// TMEM: 2 x 128 columns mid accumulators + 2 x 128 columns final accumulators.  Barriers: a_full[g] / mid_full[g] per group,
+// h2_full[half], h2_empty[step parity][half] (a parity wait is only alias-free when the waiter is at most one phase behind).
 #include <cstring>
 #include <vector>
 

@@ -10,6 +10,9 @@
 // of the cluster as st.async with the arrival attached (mbarrier complete_tx); every CTA waits on its own transaction
 // barrier — no hardware cluster barrier in the loop.  Ties resolve to the lowest index (np.argmax).
 // Exclusive use of the device is assumed: CTAs of a cluster wait for their peers' records (bounded: a lost arrival traps).
+//
+// Round 2 adds the PRUNED variant behind pcp_fps_ws_f32 (caller-owned workspace): the same samples with ~90 % of the distance
+// updates skipped — Morton-ordered cloud, per-group bounding spheres, warp-uniform skip; see the comment above fps_pruned_kernel.
 #include <cooperative_groups.h>
 
 #include <algorithm>
