@@ -69,11 +69,17 @@ int pcp_stream_sync(pcp_stream stream);
  * max distance, scale = max(maxdist, 1e-7), divide.  x,y: (b, n, 3) f32 contiguous.
  * d_centroid (b*3) and d_scale (b) may be NULL; d_y may be NULL when both statistics are
  * requested (statistics-only pass).  One HBM read + one write (24 B/point).  Clouds of n >= 16384 points
- * (16-byte aligned, n % 4 == 0) run as shared-memory-resident slices that meet through per-cloud counters in a
- * library-owned scratch ring (8 calls may be in flight per device); there is no upper limit on n on that path.
- * Smaller or unaligned clouds: one thread-block cluster per cloud (n <= 273 066). */
+ * (16-byte aligned, n % 4 == 0) run as shared-memory-resident slices that meet through per-cloud counters in scratch
+ * memory (64 + 48 b bytes); there is no upper limit on n on that path.  pcp_normalize_f32 takes the scratch from a
+ * library-owned per-device ring of eight slots (a slot is re-used only after the stream that used it last has passed its
+ * kernel; growing the ring calls cudaFree / cudaMalloc); pcp_normalize_ws_f32 takes it from the caller — no allocation,
+ * no hidden state — sized by pcp_normalize_workspace_bytes (0: this shape needs none).
+ * Smaller or unaligned clouds: one thread-block cluster per cloud (n <= 273 066), no scratch. */
 int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale,
                       pcp_stream stream);
+int pcp_normalize_workspace_bytes(int b, int64_t n, size_t *bytes);
+int pcp_normalize_ws_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale, void *d_workspace,
+                         size_t workspace_bytes, pcp_stream stream);
 
 /* Allocation-free variant of pcp_normalize_f32 for the sliced kernel (n >= 16384, n % 4 == 0, 16-byte aligned x / y).
  * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
@@ -118,7 +124,9 @@ int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d
 /* The same samples (bit-identical) with caller-owned scratch: with a workspace the library first puts every cloud in Morton order
  * of a coarse grid and then skips, per iteration, the groups of points whose bounding sphere is farther from the new sample than
  * their largest running distance — 2-3x faster on LiDAR-sized batches.  pcp_fps_workspace_bytes reports 0 where the plain kernel
- * is the better choice (few or small clouds); pcp_fps_ws_f32 then ignores the workspace and runs pcp_fps_f32. */
+ * is the better choice (few or small clouds); pcp_fps_ws_f32 then ignores the workspace and runs the plain kernel.  Clouds too
+ * large to stay on chip (n > 204 800) stream their running distances through b * n floats of scratch: from the workspace here,
+ * from a library-owned per-device buffer (cudaMalloc on growth) in pcp_fps_f32. */
 int pcp_fps_workspace_bytes(int b, int64_t n, int s, size_t *bytes);
 int pcp_fps_ws_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, void *d_workspace, size_t workspace_bytes,
                    pcp_stream stream);

@@ -65,6 +65,8 @@ SIGNATURES = {
     "pcp_memset": (_i32, [_vp, _i32, _sz, _vp]),
     "pcp_stream_sync": (_i32, [_vp]),
     "pcp_normalize_f32": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp]),
+    "pcp_normalize_workspace_bytes": (_i32, [_i32, _i64, C.POINTER(_sz)]),
+    "pcp_normalize_ws_f32": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "pcp_normalize_noalloc_max_clouds": (_i32, []),
     "pcp_normalize_noalloc_f32": (_i32, [_vp, _i32, _i64, _vp, _vp, _vp, _vp]),
     "pcp_jitter_f32": (_i32, [_vp, _i64, _fp, _u64, _u64, _vp, _vp, _vp]),

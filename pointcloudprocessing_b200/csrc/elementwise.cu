@@ -619,6 +619,57 @@ static int stream_grid(int64_t work_items, int threads) {
     return (int)blocks;
 }
 
+// ---- the sliced kernel's launch, shared by the three entry points that differ only in where the scratch lives ----
+struct NormPartsCfg { bool ready = false; int slice_bytes = 0, ctas_per_sm = 0, dbg = 0; };
+static NormPartsCfg g_norm_parts_cfg[64];            // per DEVICE: the shared-memory opt-in and the occupancy belong to a context
+
+static int norm_parts_cfg(const NormPartsCfg **out)
+{
+    int dev = 0;
+    PCP_CUDA_OK(cudaGetDevice(&dev));
+    PCP_REQUIRE(dev >= 0 && dev < 64, PCP_ERR_UNSUPPORTED, "normalize: device ordinal %d", dev);
+    NormPartsCfg &c = g_norm_parts_cfg[dev];
+    if (!c.ready) {
+        c.slice_bytes = kNormSliceBytes;
+        if (const char *e = getenv("PCP_NORM_SLICE_KB")) c.slice_bytes = std::max(4, std::min(200, atoi(e))) * 1024;   // tuning knob
+        PCP_CUDA_OK(cudaFuncSetAttribute(normalize_parts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c.slice_bytes + 384));   // (+ rounding of ppc)
+        PCP_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c.ctas_per_sm, normalize_parts_kernel, kNormPartThreads, c.slice_bytes + 384));
+        PCP_REQUIRE(c.ctas_per_sm >= 1, PCP_ERR_CUDA, "normalize: slice kernel does not fit an SM");
+        if (const char *e = getenv("PCP_NORM_DBG")) c.dbg = atoi(e) & 7;
+        c.ready = true;
+    }
+    *out = &c;
+    return PCP_OK;
+}
+
+static inline bool norm_parts_applies(const float *d_x, const float *d_y, int b, int64_t n)
+{
+    const bool aligned = (((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y)) & 15u) == 0) && (n % 4 == 0);
+    return n >= kNormPartsMin && aligned && b <= 65535;
+}
+static inline size_t norm_parts_scratch_bytes(int b) { return 64 + (size_t)b * sizeof(NormScratch); }
+
+// slot: 64 bytes of ticket + b NormScratch records, cleared here on the stream
+static int norm_parts_launch(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale, void *slot_v, cudaStream_t st)
+{
+    const NormPartsCfg *c = nullptr;
+    PCP_TRY(norm_parts_cfg(&c));
+    char *slot = static_cast<char *>(slot_v);
+    PCP_CUDA_OK(cudaMemsetAsync(slot, 0, norm_parts_scratch_bytes(b), st));
+    const int k = (int)((n * 12 + c->slice_bytes - 1) / c->slice_bytes);
+    // slices start on 128-byte lines when the cloud does (32 points = 384 B): bulk copies of misaligned slices split sectors
+    const int64_t ppc = (((n + k - 1) / k) + 31) & ~(int64_t)31;
+    const int grid = (int)std::min<int64_t>((int64_t)b * k, (int64_t)sm_count() * c->ctas_per_sm);
+    PCP_REQUIRE(k <= grid, PCP_ERR_UNSUPPORTED, "normalize: n=%lld needs %d resident slices", (long long)n, k);
+    normalize_parts_kernel<<<grid, kNormPartThreads, (size_t)ppc * 12, st>>>(d_x, b, n, k, ppc, d_y, d_centroid, d_scale,
+                                                                           reinterpret_cast<NormScratch *>(slot + 64), reinterpret_cast<unsigned *>(slot),
+                                                                           (unsigned)c->dbg);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+static int norm_small_launch(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale, cudaStream_t st);
+
 }  // namespace pcp
 
 using namespace pcp;
@@ -628,48 +679,61 @@ extern "C" int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y,
 {
     PCP_REQUIRE(d_x && (d_y || (d_centroid && d_scale)) && b >= 0 && n >= 1, PCP_ERR_INVALID, "pcp_normalize_f32: bad arguments (b=%d n=%lld)", b, (long long)n);
     if (b == 0) return PCP_OK;
-    if (!d_y && n <= 4096 && b >= 64) {
-        normalize_stats_warp_kernel<<<(b + 7) / 8, 256, 0, as_stream(stream)>>>(d_x, b, n, d_centroid, d_scale);
-        PCP_CHECK_LAUNCH();
-        return PCP_OK;
+    cudaStream_t st = as_stream(stream);
+    if (!norm_parts_applies(d_x, d_y, b, n) || (!d_y && n <= 4096 && b >= 64)) return norm_small_launch(d_x, b, n, d_y, d_centroid, d_scale, st);
+    // Library-owned scratch for callers that pass none (pcp_normalize_ws_f32 is the allocation-free form): a per-device ring of
+    // eight slots; a slot is handed out again only after the stream that used it last has passed its kernel (event per slot), so
+    // any number of calls may be in flight on any number of streams.  Growing the ring frees and allocates (device-synchronising).
+    struct Ring { char *base = nullptr; int64_t cap = 0; unsigned turn = 0; cudaEvent_t done[8] = {}; bool used[8] = {}; };
+    static Ring rings[64];
+    int dev = 0;
+    PCP_CUDA_OK(cudaGetDevice(&dev));
+    PCP_REQUIRE(dev >= 0 && dev < 64, PCP_ERR_UNSUPPORTED, "pcp_normalize_f32: device ordinal %d", dev);
+    Ring &r = rings[dev];
+    if (r.cap < b) {
+        if (r.base) PCP_CUDA_OK(cudaFree(r.base));       // synchronises the device: no slot is in use afterwards
+        r.base = nullptr;
+        r.cap = std::max<int64_t>(b, 1024);
+        PCP_CUDA_OK(cudaMalloc(&r.base, norm_parts_scratch_bytes((int)r.cap) * 8));
+        for (bool &u : r.used) u = false;
     }
-    const bool aligned = (((reinterpret_cast<uintptr_t>(d_x) | reinterpret_cast<uintptr_t>(d_y)) & 15u) == 0) && (n % 4 == 0);
-    if (n >= kNormPartsMin && aligned && b <= 65535) {
-        // per-device scratch ring (48 B per cloud + the ticket): eight calls may be in flight on different streams
-        static char *scratch[64] = {};
-        static int64_t cap[64] = {};
-        static unsigned turn[64] = {};
-        static bool attr_parts = false;
-        int dev = 0;
-        PCP_CUDA_OK(cudaGetDevice(&dev));
-        PCP_REQUIRE(dev >= 0 && dev < 64, PCP_ERR_UNSUPPORTED, "pcp_normalize_f32: device ordinal %d", dev);
-        if (cap[dev] < b) {
-            if (scratch[dev]) PCP_CUDA_OK(cudaFree(scratch[dev]));
-            cap[dev] = std::max<int64_t>(b, 1024);
-            PCP_CUDA_OK(cudaMalloc(&scratch[dev], (size_t)(cap[dev] * sizeof(NormScratch) + 64) * 8));
-        }
-        static int slice_bytes = 0, ctas_per_sm = 0, dbg = 0;
-        if (!attr_parts) {
-            slice_bytes = kNormSliceBytes;
-            if (const char *e = getenv("PCP_NORM_SLICE_KB")) slice_bytes = std::max(4, std::min(200, atoi(e))) * 1024;   // tuning knob
-            PCP_CUDA_OK(cudaFuncSetAttribute(normalize_parts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, slice_bytes + 384));   // two buffers (+ rounding of ppc to 4 points)
-            PCP_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, normalize_parts_kernel, kNormPartThreads, slice_bytes + 384));
-            PCP_REQUIRE(ctas_per_sm >= 1, PCP_ERR_CUDA, "pcp_normalize_f32: slice kernel does not fit an SM");
-            if (const char *e = getenv("PCP_NORM_DBG")) dbg = atoi(e) & 7;
-            attr_parts = true;
-        }
-        const size_t slot_bytes = (size_t)cap[dev] * sizeof(NormScratch) + 64;
-        char *slot = scratch[dev] + (size_t)(turn[dev]++ & 7u) * slot_bytes;
-        unsigned *ticket = reinterpret_cast<unsigned *>(slot);
-        NormScratch *scr = reinterpret_cast<NormScratch *>(slot + 64);
-        cudaStream_t st = as_stream(stream);
-        PCP_CUDA_OK(cudaMemsetAsync(slot, 0, 64 + (size_t)b * sizeof(NormScratch), st));
-        const int k = (int)((n * 12 + slice_bytes - 1) / slice_bytes);
-        // slices start on 128-byte lines when the cloud does (32 points = 384 B): bulk copies of misaligned slices split sectors
-        const int64_t ppc = (((n + k - 1) / k) + 31) & ~(int64_t)31;
-        const int grid = (int)std::min<int64_t>((int64_t)b * k, (int64_t)sm_count() * ctas_per_sm);
-        PCP_REQUIRE(k <= grid, PCP_ERR_UNSUPPORTED, "pcp_normalize_f32: n=%lld needs %d resident slices", (long long)n, k);
-        normalize_parts_kernel<<<grid, kNormPartThreads, (size_t)ppc * 12, st>>>(d_x, b, n, k, ppc, d_y, d_centroid, d_scale, scr, ticket, (unsigned)dbg);
+    const unsigned i = r.turn++ & 7u;
+    if (!r.done[i]) PCP_CUDA_OK(cudaEventCreateWithFlags(&r.done[i], cudaEventDisableTiming));
+    if (r.used[i]) PCP_CUDA_OK(cudaStreamWaitEvent(st, r.done[i], 0));
+    PCP_TRY(norm_parts_launch(d_x, b, n, d_y, d_centroid, d_scale, r.base + (size_t)i * norm_parts_scratch_bytes((int)r.cap), st));
+    PCP_CUDA_OK(cudaEventRecord(r.done[i], st));
+    r.used[i] = true;
+    return PCP_OK;
+}
+
+extern "C" int pcp_normalize_workspace_bytes(int b, int64_t n, size_t *bytes)
+{
+    PCP_REQUIRE(bytes && b >= 0 && n >= 1, PCP_ERR_INVALID, "pcp_normalize_workspace_bytes: bad arguments");
+    // only the sliced kernel (LiDAR-sized clouds) uses scratch; alignment of x / y is the caller's to keep (16 bytes)
+    *bytes = (b > 0 && n >= kNormPartsMin && n % 4 == 0 && b <= 65535) ? ((norm_parts_scratch_bytes(b) + 255) & ~(size_t)255) : 0;
+    return PCP_OK;
+}
+
+extern "C" int pcp_normalize_ws_f32(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale, void *d_workspace,
+                                    size_t workspace_bytes, pcp_stream stream)
+{
+    PCP_REQUIRE(d_x && (d_y || (d_centroid && d_scale)) && b >= 0 && n >= 1, PCP_ERR_INVALID, "pcp_normalize_ws_f32: bad arguments (b=%d n=%lld)", b,
+                (long long)n);
+    if (b == 0) return PCP_OK;
+    cudaStream_t st = as_stream(stream);
+    if (!norm_parts_applies(d_x, d_y, b, n) || (!d_y && n <= 4096 && b >= 64)) return norm_small_launch(d_x, b, n, d_y, d_centroid, d_scale, st);
+    PCP_REQUIRE(d_workspace && workspace_bytes >= norm_parts_scratch_bytes(b) && (reinterpret_cast<uintptr_t>(d_workspace) & 15u) == 0, PCP_ERR_INVALID,
+                "pcp_normalize_ws_f32: workspace of %zu bytes (16-byte aligned) needed, %zu given — size it with pcp_normalize_workspace_bytes",
+                norm_parts_scratch_bytes(b), workspace_bytes);
+    return norm_parts_launch(d_x, b, n, d_y, d_centroid, d_scale, d_workspace, st);
+}
+
+namespace pcp {
+// clouds that need no scratch: a warp per cloud for the statistics-only pass of the model, else one thread-block cluster per cloud
+static int norm_small_launch(const float *d_x, int b, int64_t n, float *d_y, float *d_centroid, float *d_scale, cudaStream_t st)
+{
+    if (!d_y && n <= 4096 && b >= 64) {
+        normalize_stats_warp_kernel<<<(b + 7) / 8, 256, 0, st>>>(d_x, b, n, d_centroid, d_scale);
         PCP_CHECK_LAUNCH();
         return PCP_OK;
     }
@@ -682,17 +746,20 @@ extern "C" int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y,
                 (long long)(16 * max_slice_bytes / 12));
     const int64_t ppc = (((n + cs - 1) / cs) + 3) & ~(int64_t)3;
     const size_t smem = (size_t)(ppc * 3 + 8) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};                     // per device
+    int dev = 0;
+    PCP_CUDA_OK(cudaGetDevice(&dev));
+    PCP_REQUIRE(dev >= 0 && dev < 64, PCP_ERR_UNSUPPORTED, "normalize: device ordinal %d", dev);
+    if (!attr_set[dev]) {
         PCP_CUDA_OK(cudaFuncSetAttribute(normalize_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         PCP_CUDA_OK(cudaFuncSetAttribute(normalize_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((int64_t)b * cs));
     cfg.blockDim = dim3(kNormThreads);
     cfg.dynamicSmemBytes = smem;
-    cfg.stream = as_stream(stream);
+    cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
@@ -701,6 +768,7 @@ extern "C" int pcp_normalize_f32(const float *d_x, int b, int64_t n, float *d_y,
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
+}  // namespace pcp
 
 extern "C" int pcp_philox_normal_f32(int64_t npoints, uint64_t seed, uint64_t offset, float *d_noise, pcp_stream stream)
 {
@@ -799,38 +867,18 @@ extern "C" int pcp_normalize_noalloc_f32(const float *d_x, int b, int64_t n, flo
     PCP_REQUIRE(n >= kNormPartsMin && aligned, PCP_ERR_UNSUPPORTED,
                 "pcp_normalize_noalloc_f32: only the sliced kernel uses scratch: n >= %lld, n %% 4 == 0 and 16-byte aligned x / y are required "
                 "(smaller clouds need no scratch: pcp_normalize_f32 allocates nothing for them)", (long long)kNormPartsMin);
-    // once per device, with that device current: the scratch's device address, the kernel's shared-memory opt-in and occupancy
+    // once per device, with that device current: the scratch's device address (the kernel's shared-memory opt-in and occupancy are
+    // cached per device by norm_parts_cfg)
     static unsigned char *scratch_ptr[64] = {};
-    static int ctas_per_sm[64] = {};
     int dev = 0;
     PCP_CUDA_OK(cudaGetDevice(&dev));
     PCP_REQUIRE(dev >= 0 && dev < 64, PCP_ERR_UNSUPPORTED, "pcp_normalize_noalloc_f32: device ordinal %d", dev);
-    const int smem_max = kNormSliceBytes + 384;
     if (!scratch_ptr[dev]) {
         void *p = nullptr;
         PCP_CUDA_OK(cudaGetSymbolAddress(&p, g_norm_noalloc_scratch));
         PCP_REQUIRE(p != nullptr, PCP_ERR_CUDA, "pcp_normalize_noalloc_f32: cudaGetSymbolAddress returned a null address");
-        cudaFuncAttributes fa;
-        PCP_CUDA_OK(cudaFuncGetAttributes(&fa, normalize_parts_kernel));
-        if (fa.maxDynamicSharedSizeBytes < smem_max)          // never lower what pcp_normalize_f32 may have opted into
-            PCP_CUDA_OK(cudaFuncSetAttribute(normalize_parts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
-        int occ = 0;
-        PCP_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, normalize_parts_kernel, kNormPartThreads, smem_max));
-        PCP_REQUIRE(occ >= 1, PCP_ERR_CUDA, "pcp_normalize_noalloc_f32: slice kernel does not fit an SM");
-        ctas_per_sm[dev] = occ;
         scratch_ptr[dev] = static_cast<unsigned char *>(p);
     }
-    unsigned char *slot = scratch_ptr[dev];
-    unsigned *ticket = reinterpret_cast<unsigned *>(slot);
-    NormScratch *scr = reinterpret_cast<NormScratch *>(slot + 64);
-    cudaStream_t st = as_stream(stream);
-    // the array keeps the previous call's contents: the ticket and this call's b records must start at zero
-    PCP_CUDA_OK(cudaMemsetAsync(slot, 0, 64 + (size_t)b * sizeof(NormScratch), st));
-    const int k = (int)((n * 12 + kNormSliceBytes - 1) / kNormSliceBytes);
-    const int64_t ppc = (((n + k - 1) / k) + 31) & ~(int64_t)31;
-    const int grid = (int)std::min<int64_t>((int64_t)b * k, (int64_t)sm_count() * ctas_per_sm[dev]);
-    PCP_REQUIRE(k <= grid, PCP_ERR_UNSUPPORTED, "pcp_normalize_noalloc_f32: n=%lld needs %d resident slices", (long long)n, k);
-    normalize_parts_kernel<<<grid, kNormPartThreads, (size_t)ppc * 12, st>>>(d_x, b, n, k, ppc, d_y, d_centroid, d_scale, scr, ticket, 0u);
-    PCP_CHECK_LAUNCH();
-    return PCP_OK;
+    // the array keeps the previous call's contents: norm_parts_launch clears the ticket and this call's b records on the stream
+    return norm_parts_launch(d_x, b, n, d_y, d_centroid, d_scale, scratch_ptr[dev], as_stream(stream));
 }

@@ -778,14 +778,23 @@ fps_stream_kernel(const float *__restrict__ x, int64_t n, int s, int start, int3
     }
 }
 
+static inline int fps_device()
+{
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return -1;
+    return dev;
+}
+
 template <int PPT, bool kProf = false, int SD = 0>
 static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, int cs, int64_t ppc, cudaStream_t st, int srows = 0)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};          // per device (per template instance): function attributes belong to a context
+    const int dev = fps_device();
+    PCP_REQUIRE(dev >= 0, PCP_ERR_CUDA, "fps: no current device");
+    if (!attr_set[dev]) {
         PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf, SD>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         PCP_CUDA_OK(cudaFuncSetAttribute(fps_cluster_kernel<PPT, kProf, SD>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpsMaxSmemRows * kFpsThreads * 16));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((int64_t)b * cs));
@@ -802,8 +811,11 @@ static int launch_fps(const float *d_x, int b, int64_t n, int s, int start, int3
     return PCP_OK;
 }
 
-static float *g_fps_scratch = nullptr;
-static size_t g_fps_scratch_bytes = 0;
+static float *g_fps_scratch[64] = {};        // per device: running distances of the streaming fallback when the caller passes no workspace
+static size_t g_fps_scratch_bytes[64] = {};
+// clouds too large for the widest register-resident cluster take the streaming kernel (one float of scratch per point)
+static inline bool fps_needs_stream(int64_t n) { return n > (int64_t)kFpsMaxCluster * kFpsThreads * 25; }
+static int fps_plain(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, float *dist_ws, cudaStream_t st);
 
 // ---- pruned path: geometry, workspace layout and launch
 struct FpsPrunePlan {
@@ -845,7 +857,10 @@ static int launch_fps_pruned_cs(const float *xs, const int32_t *perm, const floa
                                 const FpsPrunePlan &pl, int dbg, cudaStream_t st)
 {
     auto kern = fps_pruned_kernel<kFpsPruneReg, kFpsPruneSm, CS, kProf>;
-    static bool attr_set = false;
+    static bool attr_set_dev[64] = {};      // per device (per template instance)
+    const int dev = fps_device();
+    PCP_REQUIRE(dev >= 0, PCP_ERR_CUDA, "fps: no current device");
+    bool &attr_set = attr_set_dev[dev];
     if (!attr_set) {
         PCP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         PCP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ((3 * kFpsPruneSm + 3) / 4) * kFpsThreads * 16));
@@ -905,7 +920,9 @@ extern "C" int pcp_fps_workspace_bytes(int b, int64_t n, int s, size_t *bytes)
 {
     PCP_REQUIRE(bytes && b >= 0 && n >= 1 && s >= 1, PCP_ERR_INVALID, "pcp_fps_workspace_bytes: bad arguments");
     FpsPrunePlan pl;
-    *bytes = (b > 0 && fps_prune_plan(b, n, s, pl)) ? pl.bytes : 0;
+    if (b > 0 && fps_prune_plan(b, n, s, pl)) *bytes = pl.bytes;
+    else if (b > 0 && fps_needs_stream(n)) *bytes = ((size_t)b * (size_t)n * sizeof(float) + 255) & ~(size_t)255;      // running distances
+    else *bytes = 0;
     return PCP_OK;
 }
 
@@ -916,7 +933,17 @@ extern "C" int pcp_fps_ws_f32(const float *d_x, int b, int64_t n, int s, int sta
                 "pcp_fps_ws_f32: bad arguments (b=%d n=%lld s=%d start=%d)", b, (long long)n, s, start);
     if (b == 0) return PCP_OK;
     FpsPrunePlan pl;
-    if (!fps_prune_plan(b, n, s, pl)) return pcp_fps_f32(d_x, b, n, s, start, d_idx, stream);
+    PCP_REQUIRE(n < 0xFFFFFFFFll, PCP_ERR_UNSUPPORTED, "pcp_fps_ws_f32: n too large");
+    if (!fps_prune_plan(b, n, s, pl)) {
+        float *dist = nullptr;
+        if (fps_needs_stream(n)) {
+            PCP_REQUIRE(d_workspace && workspace_bytes >= (size_t)b * (size_t)n * sizeof(float), PCP_ERR_INVALID,
+                        "pcp_fps_ws_f32: workspace of %zu bytes needed, %zu given — size it with pcp_fps_workspace_bytes",
+                        (size_t)b * (size_t)n * sizeof(float), workspace_bytes);
+            dist = static_cast<float *>(d_workspace);
+        }
+        return fps_plain(d_x, b, n, s, start, d_idx, dist, as_stream(stream));
+    }
     PCP_REQUIRE(d_workspace && workspace_bytes >= pl.bytes && (reinterpret_cast<uintptr_t>(d_workspace) & 255) == 0, PCP_ERR_INVALID,
                 "pcp_fps_ws_f32: workspace of %zu bytes (256-byte aligned) needed, %zu given — size it with pcp_fps_workspace_bytes", pl.bytes,
                 workspace_bytes);
@@ -935,7 +962,13 @@ extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start,
                 "pcp_fps_f32: bad arguments (b=%d n=%lld s=%d start=%d)", b, (long long)n, s, start);
     PCP_REQUIRE(n < 0xFFFFFFFFll, PCP_ERR_UNSUPPORTED, "pcp_fps_f32: n too large");
     if (b == 0) return PCP_OK;
-    cudaStream_t st = as_stream(stream);
+    return fps_plain(d_x, b, n, s, start, d_idx, nullptr, as_stream(stream));
+}
+
+namespace pcp {
+// the unpruned kernels; dist_ws: b * n floats for the streaming fallback (nullptr: library-owned, grown with cudaMalloc)
+static int fps_plain(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, float *dist_ws, cudaStream_t st)
+{
     // smallest cluster whose register file holds the cloud: cs * 512 threads * PPT points, PPT <= 25.
     // Prefer the widest PPT that fits (fewest CTAs per cloud => most clouds in flight), but widen the
     // cluster while the grid would leave SMs idle.
@@ -944,14 +977,20 @@ extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start,
     while (cs < kFpsMaxCluster && (n > (int64_t)cs * kFpsThreads * kMaxPPT)) cs *= 2;
     while (cs < 8 && (int64_t)b * cs * 2 <= sm_count() && n / cs > 2 * kFpsThreads) cs *= 2;
     if (n > (int64_t)cs * kFpsThreads * kMaxPPT) {
-        const size_t need = (size_t)b * (size_t)n * sizeof(float);
-        if (need > g_fps_scratch_bytes) {
-            if (g_fps_scratch) cudaFree(g_fps_scratch);
-            g_fps_scratch = nullptr; g_fps_scratch_bytes = 0;
-            PCP_CUDA_OK(cudaMalloc(&g_fps_scratch, need));
-            g_fps_scratch_bytes = need;
+        float *dist = dist_ws;
+        if (!dist) {      // no caller workspace (pcp_fps_f32): per-device scratch, grown on demand — calls that overlap on the GPU share it
+            const int dev = fps_device();
+            PCP_REQUIRE(dev >= 0, PCP_ERR_CUDA, "fps: no current device");
+            const size_t need = (size_t)b * (size_t)n * sizeof(float);
+            if (need > g_fps_scratch_bytes[dev]) {
+                if (g_fps_scratch[dev]) PCP_CUDA_OK(cudaFree(g_fps_scratch[dev]));
+                g_fps_scratch[dev] = nullptr; g_fps_scratch_bytes[dev] = 0;
+                PCP_CUDA_OK(cudaMalloc(&g_fps_scratch[dev], need));
+                g_fps_scratch_bytes[dev] = need;
+            }
+            dist = g_fps_scratch[dev];
         }
-        fps_stream_kernel<<<b, 1024, 0, st>>>(d_x, n, s, start, d_idx, g_fps_scratch);
+        fps_stream_kernel<<<b, 1024, 0, st>>>(d_x, n, s, start, d_idx, dist);
         PCP_CHECK_LAUNCH();
         return PCP_OK;
     }
@@ -990,6 +1029,7 @@ extern "C" int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start,
     if (prof) return launch_fps<25, true>(d_x, b, n, s, start, d_idx, cs, ppc, st);
     return launch_fps<25>(d_x, b, n, s, start, d_idx, cs, ppc, st);
 }
+}  // namespace pcp
 
 /* development aid: cycles block 0 / thread 0 of the last PCP_FPS_PROF=1 launch (PPT = 25) spent in: distance loop, candidate
  * search + record, __syncthreads, warp-0 stage + DSMEM pushes, cluster barrier, slot read-back */

@@ -29,7 +29,12 @@ def normalize(x: torch.Tensor, return_stats: bool = False):
     cen = torch.empty((b, 1, 3), device=x.device, dtype=torch.float32) if return_stats else None
     sc = torch.empty((b, 1, 1), device=x.device, dtype=torch.float32) if return_stats else None
     if b and n:
-        _ffi.check(_ffi.load().pcp_normalize_f32(_ffi.ptr(x), b, n, _ffi.ptr(y), _ffi.ptr(cen), _ffi.ptr(sc), _ffi.stream_ptr()))
+        lib = _ffi.load()
+        need = C.c_size_t(0)
+        _ffi.check(lib.pcp_normalize_workspace_bytes(b, n, C.byref(need)))
+        # caller-owned scratch from torch's caching allocator: no cudaMalloc and no library-side ring in the steady state
+        ws = torch.empty(need.value, device=x.device, dtype=torch.uint8) if need.value else None
+        _ffi.check(lib.pcp_normalize_ws_f32(_ffi.ptr(x), b, n, _ffi.ptr(y), _ffi.ptr(cen), _ffi.ptr(sc), _ffi.ptr(ws), need.value, _ffi.stream_ptr()))
     return (y, (cen, sc)) if return_stats else y
 
 

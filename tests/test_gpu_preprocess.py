@@ -48,6 +48,37 @@ def test_normalize_write_is_the_true_divide_of_its_own_statistics(lib, b, n):
     assert np.array_equal(y.cpu().numpy(), (x - c) / s)
 
 
+def test_normalize_scratch_ownership(lib):
+    """The three forms of the sliced normalisation — caller-owned workspace (what ops.normalize uses), the library's per-device ring
+    with far more calls in flight on different streams than the ring has slots, and the static-array form — give the same bits."""
+    from pointcloudprocessing_b200 import _ffi, ops
+    import ctypes as C
+    L = _ffi.load()
+    b, n = 6, 40_000
+    xs = [_dev(synth.gaussian_clouds(500 + i, b, n)) for i in range(20)]
+    want = [ops.normalize(x) for x in xs]                      # pcp_normalize_ws_f32
+    need = C.c_size_t(0)
+    _ffi.check(L.pcp_normalize_workspace_bytes(b, n, C.byref(need)))
+    assert need.value >= 64 + 48 * b
+    _ffi.check(L.pcp_normalize_workspace_bytes(32, 1024, C.byref(need)))
+    assert need.value == 0                                     # cluster-per-cloud path: no scratch
+    streams = [torch.cuda.Stream() for _ in range(5)]
+    got = [torch.empty_like(x) for x in xs]
+    torch.cuda.synchronize()
+    for i, x in enumerate(xs):                                 # 20 calls, 5 streams, 8 ring slots, nothing synchronises in between
+        st = streams[i % len(streams)]
+        _ffi.check(L.pcp_normalize_f32(_ffi.ptr(x), b, n, _ffi.ptr(got[i]), None, None, C.c_void_p(st.cuda_stream)))
+    torch.cuda.synchronize()
+    for g, w in zip(got, want):
+        assert torch.equal(g, w)
+    y = torch.empty_like(xs[0])
+    _ffi.check(L.pcp_normalize_noalloc_f32(_ffi.ptr(xs[0]), b, n, _ffi.ptr(y), None, None, _ffi.stream_ptr()))
+    assert torch.equal(y, want[0])
+    small = torch.empty(16, device="cuda", dtype=torch.uint8)
+    rc = L.pcp_normalize_ws_f32(_ffi.ptr(xs[0]), b, n, _ffi.ptr(y), None, None, _ffi.ptr(small), 16, _ffi.stream_ptr())
+    assert rc != 0 and b"workspace" in L.pcp_last_error()
+
+
 def test_normalize_degenerate(lib):
     from pointcloudprocessing_b200 import ops
     same = np.tile(np.array([[[3.0, -2.0, 5.0]]], np.float32), (2, 9, 1))
