@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "model.cuh"
+#include "tail_fused.cuh"
 #include "tc_gemm.cuh"
 #include "umma.cuh"
 
@@ -21,6 +22,7 @@ using namespace umma;
 
 struct TcLayerImg {
     uint8_t *img = nullptr;
+    const uint4 *frag = nullptr;         // the same weights in mma.sync fragment order (tail_fused.cu), dense tails only
     const float *bias = nullptr;
     int K = 0, N = 0;
 };
@@ -49,13 +51,36 @@ static int upload(TcHeads *h, const void *src, size_t bytes, void **dst)
     return PCP_OK;
 }
 
-static int make_img(TcHeads *h, TcLayerImg &L, const float *W, const float *d_bias, int K, int N)
+static int make_img(TcHeads *h, TcLayerImg &L, const float *W, const float *d_bias, int K, int N, bool tail = false)
 {
     std::vector<uint16_t> img;
     pack_gemm_b_image(W, K, N, img);
     PCP_TRY(upload(h, img.data(), img.size() * 2, reinterpret_cast<void **>(&L.img)));
+    if (tail) {          // dense tails also run fused at small batch
+        std::vector<uint32_t> fr;
+        pack_tail_weights(W, K, N, fr);
+        void *d = nullptr;
+        PCP_TRY(upload(h, fr.data(), fr.size() * 4, &d));
+        L.frag = static_cast<const uint4 *>(d);
+    }
     L.bias = d_bias; L.K = K; L.N = N;
     return PCP_OK;
+}
+
+// the three dense layers behind a pooled feature in one launch (b <= 32); PCP_NO_FUSED_TAIL keeps the three tc_gemm launches
+static bool fused_tail_ok(int b, const TcLayerImg &l1, const TcLayerImg &l2, const TcLayerImg &l3)
+{
+    static const bool off = getenv("PCP_NO_FUSED_TAIL") != nullptr;
+    return !off && b <= kTailMaxRows && l1.frag && l2.frag && l3.frag && l1.K == 1024 && l1.N == 512 && l2.K == 512 && l2.N == 256 && l3.K == 256 &&
+           (l3.N <= 32 || l3.N % 2 == 0);
+}
+static int fused_tail(const float *pooled, int b, const TcLayerImg &l1, const TcLayerImg &l2, const TcLayerImg &l3, float *out32, __nv_bfloat16 *out16,
+                      float *out_softmax, cudaStream_t st)
+{
+    TailFusedParams p;
+    p.A0 = pooled; p.b = b; p.w1 = l1.frag; p.w2 = l2.frag; p.w3 = l3.frag; p.t1 = l1.bias; p.t2 = l2.bias; p.t3 = l3.bias; p.n3 = l3.N;
+    p.out32 = out32; p.out16 = out16; p.out_softmax = out_softmax;
+    return tail_fused(p, st);
 }
 
 void heads_tc_destroy(pcp_model *m)
@@ -75,15 +100,15 @@ int heads_tc_prepare(pcp_model *m, const std::vector<float> &fold)
     heads_tc_destroy(m);
     TcHeads *h = new TcHeads();
     m->tc_heads = h;
-    auto layer = [&](TcLayerImg &L, int id) {
+    auto layer = [&](TcLayerImg &L, int id, bool tail = false) {
         const LayerSpec &S = m->layers[id];
-        return make_img(h, L, fold.data() + S.fold_w, m->d_fold + S.fold_t, S.cin, S.cout);
+        return make_img(h, L, fold.data() + S.fold_w, m->d_fold + S.fold_t, S.cin, S.cout, tail);
     };
     if (!m->desc.vanilla) {
-        PCP_TRY(layer(h->it_d1, L_IT_D1)); PCP_TRY(layer(h->it_d2, L_IT_D2));
-        PCP_TRY(make_img(h, h->it_w, fold.data() + m->fold_it_w, m->d_fold + m->fold_it_t, 256, 9));
-        PCP_TRY(layer(h->ft_d1, L_FT_D1)); PCP_TRY(layer(h->ft_d2, L_FT_D2));
-        PCP_TRY(make_img(h, h->ft_w, fold.data() + m->fold_ft_w, m->d_fold + m->fold_ft_t, 256, 4096));
+        PCP_TRY(layer(h->it_d1, L_IT_D1, true)); PCP_TRY(layer(h->it_d2, L_IT_D2, true));
+        PCP_TRY(make_img(h, h->it_w, fold.data() + m->fold_it_w, m->d_fold + m->fold_it_t, 256, 9, true));
+        PCP_TRY(layer(h->ft_d1, L_FT_D1, true)); PCP_TRY(layer(h->ft_d2, L_FT_D2, true));
+        PCP_TRY(make_img(h, h->ft_w, fold.data() + m->fold_ft_w, m->d_fold + m->fold_ft_t, 256, 4096, true));
         // X_64 = X @ R64 only ever feeds s2_l1_64 in the trunk (PointNet.py:228,236), and R64 = reshape(h . w + b) is linear in
         // the T-Net's last hidden vector h, so the per-cloud operand image (R64 . W)[n, kk] the third chain kernel reads is
         // ONE small-M GEMM of h against T[k, (n, kk)] = sum_m w[k, kk*64 + m] W[m, n] with its columns laid out in the image's
@@ -110,10 +135,10 @@ int heads_tc_prepare(pcp_model *m, const std::vector<float> &fold)
             }
             float *d_tb = nullptr;
             PCP_TRY(upload(h, tb.data(), tb.size() * 4, reinterpret_cast<void **>(&d_tb)));
-            PCP_TRY(make_img(h, h->ft_fold, T.data(), d_tb, 256, 4096));
+            PCP_TRY(make_img(h, h->ft_fold, T.data(), d_tb, 256, 4096, true));
         }
     }
-    PCP_TRY(layer(h->cls1, L_CLS1)); PCP_TRY(layer(h->cls2, L_CLS2)); PCP_TRY(layer(h->cls3, L_CLS3));
+    PCP_TRY(layer(h->cls1, L_CLS1, true)); PCP_TRY(layer(h->cls2, L_CLS2, true)); PCP_TRY(layer(h->cls3, L_CLS3, true));
     PCP_TRY(layer(h->s1_2, L_S1_2));
     const LayerSpec &S1 = m->layers[L_SEG1];
     // global half of seg_l1_512: rows 64..1087 of the folded kernel (1024 x 512)
@@ -157,6 +182,7 @@ int heads_tc_tnet_tail(pcp_model *m, int which, const float *pooled, int b, floa
     TcHeads *h = reinterpret_cast<TcHeads *>(m->tc_heads);
     PCP_TRY(ensure_small(h, b));
     const TcLayerImg &d1 = which == 0 ? h->it_d1 : h->ft_d1, &d2 = which == 0 ? h->it_d2 : h->ft_d2, &w = which == 0 ? h->it_w : h->ft_w;
+    if (fused_tail_ok(b, d1, d2, w)) return fused_tail(pooled, b, d1, d2, w, out, nullptr, nullptr, st);
     PCP_TRY(gemm_layer(d1, pooled, 1, 1024, b, 1, nullptr, h->d512, nullptr, 512, st));
     PCP_TRY(gemm_layer(d2, h->d512, 0, 512, b, 1, nullptr, h->d256, nullptr, 256, st));
     return gemm_layer(w, h->d256, 0, 256, b, 0, out, nullptr, nullptr, w.N, st);
@@ -168,6 +194,8 @@ int heads_tc_tnet_tail_fold(pcp_model *m, const float *pooled, int b, uint8_t *w
 {
     TcHeads *h = reinterpret_cast<TcHeads *>(m->tc_heads);
     PCP_TRY(ensure_small(h, b));
+    if (!r64_out && fused_tail_ok(b, h->ft_d1, h->ft_d2, h->ft_fold))
+        return fused_tail(pooled, b, h->ft_d1, h->ft_d2, h->ft_fold, nullptr, reinterpret_cast<__nv_bfloat16 *>(wc_img), nullptr, st);
     PCP_TRY(gemm_layer(h->ft_d1, pooled, 1, 1024, b, 1, nullptr, h->d512, nullptr, 512, st));
     PCP_TRY(gemm_layer(h->ft_d2, h->d512, 0, 512, b, 1, nullptr, h->d256, nullptr, 256, st));
     PCP_TRY(gemm_layer(h->ft_fold, h->d256, 0, 256, b, 0, nullptr, reinterpret_cast<__nv_bfloat16 *>(wc_img), nullptr, 4096, st));
@@ -181,6 +209,7 @@ int heads_tc_cls(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cl
     TcHeads *h = reinterpret_cast<TcHeads *>(m->tc_heads);
     PCP_TRY(ensure_small(h, b));
     const int C = m->desc.num_classes;
+    if (C <= 32 && fused_tail_ok(b, h->cls1, h->cls2, h->cls3)) return fused_tail(g3, b, h->cls1, h->cls2, h->cls3, d_cls_logits, nullptr, d_cls, st);
     PCP_TRY(gemm_layer(h->cls1, g3, 1, 1024, b, 1, nullptr, h->d512, nullptr, 512, st));
     PCP_TRY(gemm_layer(h->cls2, h->d512, 0, 512, b, 1, nullptr, h->d256, nullptr, 256, st));
     if (C <= 32)

@@ -294,11 +294,8 @@ __device__ __forceinline__ unsigned fps_part1by2(unsigned v)
     v &= 0x3ffu; v = (v | (v << 16)) & 0x30000ffu; v = (v | (v << 8)) & 0x300f00fu; v = (v | (v << 4)) & 0x30c30c3u; v = (v | (v << 2)) & 0x9249249u;
     return v;
 }
-__device__ __forceinline__ unsigned fps_cell(float px, float py, float pz, const unsigned *bb)
-{
-    const float lx = fps_fdec(bb[0]), ly = fps_fdec(bb[1]), lz = fps_fdec(bb[2]);
-    const float ext = fmaxf(fmaxf(fps_fdec(bb[3]) - lx, fps_fdec(bb[4]) - ly), fps_fdec(bb[5]) - lz);
-    const float inv = ext > 0.f ? (float)(1 << kFpsSortBits) / ext : 0.f;
+__device__ __forceinline__ unsigned fps_cell_of(float px, float py, float pz, float lx, float ly, float lz, float inv)
+{   // NaN / Inf coordinates clamp into the grid (fmaxf drops a NaN): any cell is correct, the order only steers the pruning
     const float top = (float)((1 << kFpsSortBits) - 1);
     const unsigned ix = (unsigned)fminf(fmaxf((px - lx) * inv, 0.f), top), iy = (unsigned)fminf(fmaxf((py - ly) * inv, 0.f), top),
                    iz = (unsigned)fminf(fmaxf((pz - lz) * inv, 0.f), top);
@@ -312,67 +309,130 @@ __global__ void fps_sort_init_kernel(unsigned *__restrict__ bbox, int b, int *__
     for (int64_t j = i; j < nh; j += (int64_t)gridDim.x * blockDim.x) hist[j] = 0;
 }
 
-__global__ void __launch_bounds__(256)
+// All global atomics of the sort go to a handful of words per cloud; issued per warp or per point they serialise in the L2 (bounding
+// box: 447 k atomics on 384 words = 106 us; histogram / scatter: 7 M atomics on a very uneven cell population = 158 + 196 us).
+// So: the bounding box is reduced per BLOCK first, and the histogram of a block's part of the cloud is built in SHARED memory
+// (all 32 768 cells: 128 KB) — only per-bin totals / base claims go to global memory.
+__global__ void __launch_bounds__(1024)
 fps_sort_bbox_kernel(const float *__restrict__ x, int64_t n, unsigned *__restrict__ bbox)
 {
+    __shared__ unsigned slo[3][32], shi[3][32];
     const int cloud = blockIdx.y;
     const float *xc = x + (int64_t)cloud * n * 3;
-    unsigned lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256)
+    const int64_t nf = 3 * n;
+    // flat, coalesced float loads; element e of a trip sits at i + 1024 e, its axis is (i + 1024 e) % 3 = (a0 + e) % 3
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned lo[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, hi[3] = {0u, 0u, 0u};       // by (axis - a0) mod 3
+    for (int64_t i = (int64_t)blockIdx.x * 3072 + tid; i < nf; i += (int64_t)gridDim.x * 3072) {
 #pragma unroll
-        for (int a = 0; a < 3; ++a) { const unsigned k = fps_fenc(__ldg(xc + 3 * i + a)); lo[a] = min(lo[a], k); hi[a] = max(hi[a], k); }
+        for (int e = 0; e < 3; ++e) {
+            const int64_t j = i + 1024 * e;
+            if (j < nf) { const unsigned k = fps_fenc(__ldg(xc + j)); lo[e] = min(lo[e], k); hi[e] = max(hi[e], k); }
+        }
+    }
+    // (the stride 3072 * gridDim.x is a multiple of 3, so a thread's slot e always holds axis (tid + 1024 e + 3072 blockIdx.x) % 3
+    //  = (tid + e) % 3)
+    const int a0 = tid % 3;
+    unsigned alo[3], ahi[3];
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
-        const unsigned l = __reduce_min_sync(0xffffffffu, lo[a]), h = __reduce_max_sync(0xffffffffu, hi[a]);
-        if ((threadIdx.x & 31) == 0) { atomicMin(&bbox[cloud * 6 + a], l); atomicMax(&bbox[cloud * 6 + 3 + a], h); }
+        const int e = (a - a0 + 3) % 3;
+        alo[a] = e == 0 ? lo[0] : e == 1 ? lo[1] : lo[2];
+        ahi[a] = e == 0 ? hi[0] : e == 1 ? hi[1] : hi[2];
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const unsigned l = __reduce_min_sync(0xffffffffu, alo[a]), h = __reduce_max_sync(0xffffffffu, ahi[a]);
+        if (lane == 0) { slo[a][warp] = l; shi[a][warp] = h; }
+    }
+    __syncthreads();
+    if (warp < 3) {
+        const unsigned l = __reduce_min_sync(0xffffffffu, slo[warp][lane]), h = __reduce_max_sync(0xffffffffu, shi[warp][lane]);
+        if (lane == 0) { atomicMin(&bbox[cloud * 6 + warp], l); atomicMax(&bbox[cloud * 6 + 3 + warp], h); }
     }
 }
 
+// blockIdx.x = part of the cloud (gridDim.x parts of `per` points), blockIdx.y = cloud; dynamic shared memory: kFpsSortBins ints.
+// kScatter = false: hist[cell] += this part's count.  kScatter = true (hist holds the exclusive scan): claim a base per cell for
+// this part (one global atomic per occupied cell), then place the part's points behind it with shared-memory cursors.
 template <bool kScatter>
-__global__ void __launch_bounds__(256)
-fps_sort_pass_kernel(const float *__restrict__ x, int64_t n, const unsigned *__restrict__ bbox, int *__restrict__ hist, float *__restrict__ xs,
+__global__ void __launch_bounds__(1024)
+fps_sort_pass_kernel(const float *__restrict__ x, int64_t n, int64_t per, const unsigned *__restrict__ bbox, int *__restrict__ hist,
                      int32_t *__restrict__ perm)
 {
-    const int cloud = blockIdx.y;
+    extern __shared__ int fps_cnt[];
+    const int cloud = blockIdx.y, tid = threadIdx.x;
     const float *xc = x + (int64_t)cloud * n * 3;
     int *h = hist + (int64_t)cloud * kFpsSortBins;
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
-        const float px = __ldg(xc + 3 * i), py = __ldg(xc + 3 * i + 1), pz = __ldg(xc + 3 * i + 2);
-        const unsigned c = fps_cell(px, py, pz, bbox + cloud * 6);
-        if (!kScatter) atomicAdd(&h[c], 1);
-        else {
-            const int64_t pos = (int64_t)cloud * n + atomicAdd(&h[c], 1);
-            xs[3 * pos] = px; xs[3 * pos + 1] = py; xs[3 * pos + 2] = pz;
-            perm[pos] = (int32_t)i;
+    const int64_t p0 = (int64_t)blockIdx.x * per, p1 = min(n, p0 + per);
+    const unsigned *bb = bbox + cloud * 6;
+    const float lx = fps_fdec(bb[0]), ly = fps_fdec(bb[1]), lz = fps_fdec(bb[2]);
+    const float ext = fmaxf(fmaxf(fps_fdec(bb[3]) - lx, fps_fdec(bb[4]) - ly), fps_fdec(bb[5]) - lz);
+    const float inv = ext > 0.f ? (float)(1 << kFpsSortBits) / ext : 0.f;
+    for (int i = tid; i < kFpsSortBins; i += 1024) fps_cnt[i] = 0;
+    __syncthreads();
+    for (int64_t i0 = p0 + tid; i0 < p1; i0 += 4096) {
+        unsigned c[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int64_t i = i0 + 1024 * e;
+            c[e] = i < p1 ? fps_cell_of(__ldg(xc + 3 * i), __ldg(xc + 3 * i + 1), __ldg(xc + 3 * i + 2), lx, ly, lz, inv) : 0xFFFFFFFFu;
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+            if (c[e] != 0xFFFFFFFFu) atomicAdd(&fps_cnt[c[e]], 1);
+    }
+    __syncthreads();
+    if constexpr (!kScatter) {
+        for (int i = tid; i < kFpsSortBins; i += 1024) { const int v = fps_cnt[i]; if (v) atomicAdd(&h[i], v); }
+    } else {
+        for (int i = tid; i < kFpsSortBins; i += 1024) { const int v = fps_cnt[i]; fps_cnt[i] = v ? atomicAdd(&h[i], v) : 0; }
+        __syncthreads();
+        int32_t *pc = perm + (int64_t)cloud * n;
+        for (int64_t i0 = p0 + tid; i0 < p1; i0 += 4096) {
+            unsigned c[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int64_t i = i0 + 1024 * e;
+                c[e] = i < p1 ? fps_cell_of(__ldg(xc + 3 * i), __ldg(xc + 3 * i + 1), __ldg(xc + 3 * i + 2), lx, ly, lz, inv) : 0xFFFFFFFFu;
+            }
+            // only the permutation is written: a sorted COPY would be 12-byte writes at random positions (partial sectors); the
+            // sampler gathers its points through the permutation instead
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (c[e] != 0xFFFFFFFFu) pc[atomicAdd(&fps_cnt[c[e]], 1)] = (int32_t)(i0 + 1024 * e);
         }
     }
 }
 
 __global__ void __launch_bounds__(1024)
 fps_sort_scan_kernel(int *__restrict__ hist)
-{   // exclusive scan of one cloud's kFpsSortBins counters, in place
+{   // exclusive scan of one cloud's kFpsSortBins counters, in place; 1024 bins per round, coalesced
     __shared__ int wsum[32];
+    __shared__ int carry_s;
     int *h = hist + (int64_t)blockIdx.x * kFpsSortBins;
-    constexpr int per = kFpsSortBins / 1024;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int v[per], tot = 0;
+    int carry = 0;
+    for (int base = 0; base < kFpsSortBins; base += 1024) {
+        const int v = h[base + tid];
+        int inc = v;
 #pragma unroll
-    for (int j = 0; j < per; ++j) { v[j] = h[tid * per + j]; tot += v[j]; }
-    int inc = tot;
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            const int w = wsum[lane];
+            int wi = w;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-    if (lane == 31) wsum[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-        int w = wsum[lane], wi = w;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
-        wsum[lane] = wi - w;
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+            wsum[lane] = wi - w;
+            if (lane == 31) carry_s = wi;
+        }
+        __syncthreads();
+        h[base + tid] = carry + wsum[warp] + inc - v;
+        carry += carry_s;
+        __syncthreads();
     }
-    __syncthreads();
-    int run = wsum[warp] + inc - tot;
-#pragma unroll
-    for (int j = 0; j < per; ++j) { h[tid * per + j] = run; run += v[j]; }
 }
 
 // low word of a key inside a block: bit 31 = a real point stands behind it, bit 30 = more than one point attains the value,
@@ -429,7 +489,7 @@ __device__ __forceinline__ void fps_wait_records(uint64_t *bar, uint32_t parity)
 
 template <int PPT, int SD, int CS, bool kProf>
 __global__ void __launch_bounds__(kFpsThreads, 1)
-fps_pruned_kernel(const float *__restrict__ xs, const int32_t *__restrict__ perm, const float *__restrict__ xorig, int64_t n, int s, int start,
+fps_pruned_kernel(const int32_t *__restrict__ perm, const float *__restrict__ xorig, int64_t n, int s, int start,
                   int32_t *__restrict__ idx_out, int ngroups, int dbg)
 {
     constexpr int cs = CS;
@@ -446,7 +506,7 @@ fps_pruned_kernel(const float *__restrict__ xs, const int32_t *__restrict__ perm
     const int rank = (int)cluster.block_rank();
     const int64_t cloud = blockIdx.x / cs;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const float *xc = xs + cloud * n * 3;
+    const float *xo = xorig + cloud * n * 3;
     const int32_t *pc = perm + cloud * n;
     // groups of 224 consecutive sorted points are dealt round-robin over the blocks of the cluster and their warps, so the
     // neighbourhood of a sample spreads over all of them: sorted position of (group g, row j of it, this lane)
@@ -470,7 +530,10 @@ fps_pruned_kernel(const float *__restrict__ xs, const int32_t *__restrict__ perm
         const int64_t gi = gpos(k);
         const bool real = k < rowsT && gi < n;
         if (real) realmask |= 1ull << k;
-        px[k] = real ? __ldg(xc + 3 * gi) : 0.f; py[k] = real ? __ldg(xc + 3 * gi + 1) : 0.f; pz[k] = real ? __ldg(xc + 3 * gi + 2) : 0.f;
+        // the sorted cloud is never materialised: the point is gathered through the permutation (the input is L2 resident after the
+        // sort's passes over it)
+        const int64_t o = real ? (int64_t)__ldg(pc + gi) : 0;
+        px[k] = real ? __ldg(xo + 3 * o) : 0.f; py[k] = real ? __ldg(xo + 3 * o + 1) : 0.f; pz[k] = real ? __ldg(xo + 3 * o + 2) : 0.f;
         d[k] = real ? __int_as_float(0x7f800000) : 0.f;      // padding is never "real" when keys are built
     }
 #pragma unroll
@@ -487,7 +550,7 @@ fps_pruned_kernel(const float *__restrict__ xs, const int32_t *__restrict__ perm
             for (int e = 0; e < 4; ++e) {
                 const int f = 4 * k + e, r = PPT + f / 3, c = f - 3 * (f / 3);
                 const int64_t gi = gpos(r);
-                v[e] = (r < rowsT && gi < n) ? __ldg(xc + 3 * gi + c) : 0.f;
+                v[e] = (r < rowsT && gi < n) ? __ldg(xo + 3 * (int64_t)__ldg(pc + gi) + c) : 0.f;
             }
             fps_dyn4[k * kFpsThreads + tid] = make_float4(v[0], v[1], v[2], v[3]);
         }
@@ -528,7 +591,6 @@ fps_pruned_kernel(const float *__restrict__ xs, const int32_t *__restrict__ perm
             sthr = cnt > 0.f ? __int_as_float(0x7f800000) : -1.f;
         }
     }
-    const float *xo = xorig + cloud * n * 3;
     float cx = __ldg(xo + 3 * (int64_t)start), cy = __ldg(xo + 3 * (int64_t)start + 1), cz = __ldg(xo + 3 * (int64_t)start + 2);
     if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
 
@@ -820,7 +882,7 @@ static int fps_plain(const float *d_x, int b, int64_t n, int s, int start, int32
 // ---- pruned path: geometry, workspace layout and launch
 struct FpsPrunePlan {
     int cs = 0, ngroups = 0;
-    size_t off_xs = 0, off_perm = 0, off_hist = 0, off_bbox = 0, bytes = 0;
+    size_t off_perm = 0, off_hist = 0, off_bbox = 0, bytes = 0;
 };
 
 static bool fps_prune_plan(int b, int64_t n, int s, FpsPrunePlan &pl)
@@ -844,8 +906,7 @@ static bool fps_prune_plan(int b, int64_t n, int s, FpsPrunePlan &pl)
     if (ngroups < 3) return false;                               // small clouds: the register-only kernel, nothing to prune at 1-2 ms
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
     pl.cs = cs; pl.ngroups = ngroups;
-    pl.off_xs = 0;
-    pl.off_perm = up((size_t)b * n * 3 * sizeof(float));
+    pl.off_perm = 0;
     pl.off_hist = pl.off_perm + up((size_t)b * n * sizeof(int32_t));
     pl.off_bbox = pl.off_hist + up((size_t)b * kFpsSortBins * sizeof(int));
     pl.bytes = pl.off_bbox + up((size_t)b * 6 * sizeof(unsigned));
@@ -853,7 +914,7 @@ static bool fps_prune_plan(int b, int64_t n, int s, FpsPrunePlan &pl)
 }
 
 template <int CS, bool kProf>
-static int launch_fps_pruned_cs(const float *xs, const int32_t *perm, const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx,
+static int launch_fps_pruned_cs(const int32_t *perm, const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx,
                                 const FpsPrunePlan &pl, int dbg, cudaStream_t st)
 {
     auto kern = fps_pruned_kernel<kFpsPruneReg, kFpsPruneSm, CS, kProf>;
@@ -875,7 +936,7 @@ static int launch_fps_pruned_cs(const float *xs, const int32_t *perm, const floa
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, xs, perm, d_x, n, s, start, d_idx, pl.ngroups, dbg));
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, perm, d_x, n, s, start, d_idx, pl.ngroups, dbg));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -884,29 +945,41 @@ template <bool kProf>
 static int launch_fps_pruned(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, const FpsPrunePlan &pl, void *ws, cudaStream_t st)
 {
     auto *base = static_cast<unsigned char *>(ws);
-    float *xs = reinterpret_cast<float *>(base + pl.off_xs);
     int32_t *perm = reinterpret_cast<int32_t *>(base + pl.off_perm);
     int *hist = reinterpret_cast<int *>(base + pl.off_hist);
     unsigned *bbox = reinterpret_cast<unsigned *>(base + pl.off_bbox);
     const int64_t nh = (int64_t)b * kFpsSortBins;
     fps_sort_init_kernel<<<(unsigned)std::min<int64_t>((nh + 255) / 256, 4096), 256, 0, st>>>(bbox, b, hist, nh);
     PCP_CHECK_LAUNCH();
-    const dim3 grid((unsigned)std::min<int64_t>((n + 2047) / 2048, 1024), (unsigned)b);
-    fps_sort_bbox_kernel<<<grid, 256, 0, st>>>(d_x, n, bbox);
+    // parts per cloud: one resident wave of blocks (a block holds the whole 128 KB histogram: one per SM)
+    const int parts = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)16, (int64_t)sm_count() / b, (n + 8191) / 8192}));
+    const int64_t per = (((n + parts - 1) / parts) + 3) & ~(int64_t)3;
+    const dim3 grid((unsigned)parts, (unsigned)b);
+    static bool attr_set[64] = {};
+    const int sdev = fps_device();
+    PCP_REQUIRE(sdev >= 0, PCP_ERR_CUDA, "fps: no current device");
+    if (!attr_set[sdev]) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(fps_sort_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpsSortBins * 4));
+        PCP_CUDA_OK(cudaFuncSetAttribute(fps_sort_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFpsSortBins * 4));
+        attr_set[sdev] = true;
+    }
+    const int bparts = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)32, (int64_t)4 * sm_count() / b, (3 * n + 3071) / 3072}));
+    fps_sort_bbox_kernel<<<dim3((unsigned)bparts, (unsigned)b), 1024, 0, st>>>(d_x, n, bbox);
     PCP_CHECK_LAUNCH();
-    fps_sort_pass_kernel<false><<<grid, 256, 0, st>>>(d_x, n, bbox, hist, nullptr, nullptr);
+    fps_sort_pass_kernel<false><<<grid, 1024, kFpsSortBins * 4, st>>>(d_x, n, per, bbox, hist, nullptr);
     PCP_CHECK_LAUNCH();
     fps_sort_scan_kernel<<<b, 1024, 0, st>>>(hist);
     PCP_CHECK_LAUNCH();
-    fps_sort_pass_kernel<true><<<grid, 256, 0, st>>>(d_x, n, bbox, hist, xs, perm);
+    fps_sort_pass_kernel<true><<<grid, 1024, kFpsSortBins * 4, st>>>(d_x, n, per, bbox, hist, perm);
     PCP_CHECK_LAUNCH();
 
     static const int dbg = getenv("PCP_FPS_PRUNE_DBG") ? atoi(getenv("PCP_FPS_PRUNE_DBG")) : 0;      // development (see the kernel)
+    if (dbg == 2) return PCP_OK;                     // development: the sort alone
     switch (pl.cs) {
-    case 1: return launch_fps_pruned_cs<1, kProf>(xs, perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
-    case 2: return launch_fps_pruned_cs<2, kProf>(xs, perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
-    case 4: return launch_fps_pruned_cs<4, kProf>(xs, perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
-    default: return launch_fps_pruned_cs<8, kProf>(xs, perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    case 1: return launch_fps_pruned_cs<1, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    case 2: return launch_fps_pruned_cs<2, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    case 4: return launch_fps_pruned_cs<4, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    default: return launch_fps_pruned_cs<8, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
     }
 }
 
