@@ -58,14 +58,17 @@ __device__ __forceinline__ void mma_bf16(float (&c)[4], uint32_t a0, uint32_t a1
                  : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// acc[mt] += A[32 rows, k-pairs kp0 .. kp0 + NKP) . W[n-tile]; A in shared memory (row stride LD bf16), w = this n-tile's first
-// uint4 of k-pair 0 for lane 0.  All the weight loads of the range are issued before the first mma.
-template <int LD, int NKP>
-__device__ __forceinline__ void tail_mma_range(const __nv_bfloat16 *A, const uint4 *w, int kp0, float (&acc)[2][4], int lane)
+// the weights of k-pairs kp0 .. kp0 + NKP of one n-tile (w = the tile's first uint4 for lane 0), issued together
+template <int NKP>
+__device__ __forceinline__ void tail_load(uint4 (&bw)[NKP], const uint4 *w, int kp0, int lane)
 {
-    uint4 bw[NKP];
 #pragma unroll
     for (int i = 0; i < NKP; ++i) bw[i] = __ldg(w + (size_t)(kp0 + i) * 32 + lane);
+}
+// acc[mt] += A[32 rows, those k-pairs] . W[n-tile]; A in shared memory (row stride LD bf16)
+template <int LD, int NKP>
+__device__ __forceinline__ void tail_mma(const __nv_bfloat16 *A, const uint4 (&bw)[NKP], int kp0, float (&acc)[2][4], int lane)
+{
     const uint32_t a_base = (uint32_t)__cvta_generic_to_shared(A) + (uint32_t)(((lane & 15) * LD + (lane >> 4) * 8) * 2);
 #pragma unroll
     for (int i = 0; i < NKP; ++i) {
@@ -114,7 +117,21 @@ tail_fused_kernel(TailFusedParams p)
     const int c = (int)cluster.block_rank();
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
 
+    // programmatic dependent launch: the successor may start its own prologue now; this kernel's weights do not depend on the
+    // predecessor, its activations do
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const int nt1 = w & 3, kh1 = w >> 2;            // layer 1: this CTA's 32 columns = 4 n-tiles x 2 K halves over the 8 warps
+    const int nt2 = w & 1, kq2 = w >> 1;            // layer 2: 16 columns = 2 n-tiles x 4 K quarters
+    const int NT3 = (p.n3 + 7) / 8;
+    const int t3 = NT3 <= 4 ? w : w * kTailCluster + c;      // layer 3: first n-tile of this warp (narrow: CTA 0 only)
+    uint4 bw1[16], bw2[4], bw3[8];
+    tail_load<16>(bw1, p.w1 + (size_t)(4 * c + nt1) * (1024 / 32) * 32, kh1 * 16, lane);
+    tail_load<4>(bw2, p.w2 + (size_t)(2 * c + nt2) * (512 / 32) * 32, kq2 * 4, lane);
+    if (t3 < NT3) tail_load<8>(bw3, p.w3 + (size_t)t3 * (256 / 32) * 32, 0, lane);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
     // ---- A1 = bf16(pooled), rows >= b zero
+#pragma unroll 8
     for (int idx = tid; idx < kTailMaxRows * 256; idx += kTailThreads) {
         const int row = idx >> 8, c4 = idx & 255;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -126,13 +143,11 @@ tail_fused_kernel(TailFusedParams p)
     }
     cluster.sync();               // A1 complete, and every CTA of the cluster is running before anybody writes into a peer
 
-    // ---- layer 1: 1024 -> 512; this CTA's 32 columns = 4 n-tiles x 2 K halves over the 8 warps
+    // ---- layer 1: 1024 -> 512
     {
-        const int nt = w & 3, kh = w >> 2;
+        const int nt = nt1, kh = kh1;
         float acc[2][4] = {};
-        const uint4 *wt = p.w1 + (size_t)(4 * c + nt) * (1024 / 32) * 32;
-#pragma unroll
-        for (int part = 0; part < 2; ++part) tail_mma_range<kLd1, 8>(S.A1, wt, kh * 16 + part * 8, acc, lane);
+        tail_mma<kLd1, 16>(S.A1, bw1, kh * 16, acc, lane);
         if (kh == 1) {
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
@@ -156,12 +171,11 @@ tail_fused_kernel(TailFusedParams p)
         }
         cluster.sync();
     }
-    // ---- layer 2: 512 -> 256; 16 columns = 2 n-tiles x 4 K quarters
+    // ---- layer 2: 512 -> 256
     {
-        const int nt = w & 1, kq = w >> 1;
+        const int nt = nt2, kq = kq2;
         float acc[2][4] = {};
-        const uint4 *wt = p.w2 + (size_t)(2 * c + nt) * (512 / 32) * 32;
-        tail_mma_range<kLd2, 4>(S.A2, wt, kq * 4, acc, lane);
+        tail_mma<kLd2, 4>(S.A2, bw2, kq * 4, acc, lane);
         if (kq > 0) {
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
@@ -187,14 +201,13 @@ tail_fused_kernel(TailFusedParams p)
         cluster.sync();           // the last remote access to any peer's shared memory
     }
     // ---- layer 3: 256 -> n3 (no ReLU)
-    const int NT3 = (p.n3 + 7) / 8;
     const int g = lane >> 2, q = (lane & 3) * 2;
     if (NT3 <= 4) {
         // narrow output (R, logits): CTA 0 alone, one warp per n-tile, then the row softmax if asked for
         if (c != 0) return;
         if (w < NT3) {
             float acc[2][4] = {};
-            tail_mma_range<kLd3, 8>(S.A3, p.w3 + (size_t)w * (256 / 32) * 32, 0, acc, lane);
+            tail_mma<kLd3, 8>(S.A3, bw3, 0, acc, lane);
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
@@ -221,10 +234,14 @@ tail_fused_kernel(TailFusedParams p)
         }
         return;
     }
-    // wide output (the folded per-cloud operand image, 4096 columns): n-tiles dealt over CTAs and warps, results straight to HBM
-    for (int t = w * kTailCluster + c; t < NT3; t += 8 * kTailCluster) {
+    // wide output (the folded per-cloud operand image, 4096 columns): n-tiles dealt over CTAs and warps, results straight to HBM;
+    // the next tile's weights are in flight while this one is multiplied
+    for (int t = t3; t < NT3; t += 8 * kTailCluster) {
+        uint4 nx[8];
+        const int tn = t + 8 * kTailCluster;
+        if (tn < NT3) tail_load<8>(nx, p.w3 + (size_t)tn * (256 / 32) * 32, 0, lane);
         float acc[2][4] = {};
-        tail_mma_range<kLd3, 8>(S.A3, p.w3 + (size_t)t * (256 / 32) * 32, 0, acc, lane);
+        tail_mma<kLd3, 8>(S.A3, bw3, 0, acc, lane);
         const int col = t * 8 + q;
         const float t0 = col < p.n3 ? __ldg(p.t3 + col) : 0.f, t1 = col + 1 < p.n3 ? __ldg(p.t3 + col + 1) : 0.f;
 #pragma unroll
@@ -242,6 +259,10 @@ tail_fused_kernel(TailFusedParams p)
                     if (p.out16) p.out16[(size_t)row * p.n3 + col] = __float2bfloat16_rn(v0);
                 }
             }
+        if (tn < NT3) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) bw3[i] = nx[i];
+        }
     }
 }
 
@@ -260,7 +281,16 @@ int tail_fused(const TailFusedParams &p, cudaStream_t st)
         PCP_CUDA_OK(cudaFuncSetAttribute(tail_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TailShared)));
         attr_set[dev] = true;
     }
-    tail_fused_kernel<<<kTailCluster, kTailThreads, sizeof(TailShared), st>>>(p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(kTailCluster);
+    cfg.blockDim = dim3(kTailThreads);
+    cfg.dynamicSmemBytes = sizeof(TailShared);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;      // starts while the producer of A0 drains; see griddepcontrol.wait
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tail_fused_kernel, p));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
