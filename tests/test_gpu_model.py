@@ -44,7 +44,9 @@ def oracle_forward(x, p, vanilla):
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16", "fp32_tc"])
-@pytest.mark.parametrize("vanilla,b,n", [(False, 4, 256), (True, 4, 256), (False, 32, 1024), (False, 3, 2048), (False, 2, 200)])
+# b = 1 / 17 / 32: the fused small-batch dense tails (tail_fused.cu, b <= 32) with one row, a ragged row tile and a full one; b = 33: just past them
+@pytest.mark.parametrize("vanilla,b,n", [(False, 4, 256), (True, 4, 256), (False, 32, 1024), (False, 3, 2048), (False, 2, 200), (False, 1, 300), (False, 17, 128),
+                                         (False, 33, 128)])
 def test_forward_matches_oracle(lib, precision, vanilla, b, n):
     m, p = build(precision, vanilla)
     x = synth.gaussian_clouds(1001, b, n)
