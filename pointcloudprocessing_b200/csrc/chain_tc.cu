@@ -628,12 +628,13 @@ int model_prepare_bf16(pcp_model *m)
 // The per-cloud operand images image_b(n, k) = bf16( sum_m R64_b[k][m] * W[m][n] ) — X_64 . W == X . (R64 . W)
 // (PointNet.py:228,236) — come straight out of the feature T-Net's last GEMM (heads_tc.cu: heads_tc_tnet_tail_fold).
 
+// d_x / gmax (/ R / wc) point at the first cloud of the launch; cloud0 is its index in the batch the statistics were taken over
 static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, int64_t n, const float *R, const uint8_t *wc,
-                        float *gmax, cudaStream_t st)
+                        float *gmax, cudaStream_t st, int cloud0 = 0)
 {
     ChainParams p;
     memset(&p, 0, sizeof(p));
-    p.x = d_x; p.n = n; p.b = b; p.centroid = ts->centroid; p.scale = ts->scale; p.R = R; p.l0 = c.l0;
+    p.x = d_x; p.n = n; p.b = b; p.centroid = ts->centroid + (size_t)cloud0 * 3; p.scale = ts->scale + cloud0; p.R = R; p.l0 = c.l0;
     p.nmid = c.nmid;
     for (int i = 0; i < c.nmid; ++i) {
         p.mid_n[i] = c.mid_n[i];
@@ -694,14 +695,16 @@ static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, 
     return PCP_OK;
 }
 
-int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
-                       float *d_R, float *d_cls_logits, float *d_seg_logits, cudaStream_t st)
+// The bf16 forward in three parts, so that a caller whose points are still arriving from the host can run the part that only
+// needs the points (statistics + the first chain) on each chunk as it lands and everything behind it once, on the whole batch:
+//   begin(b)              buffers for b clouds, pooled features cleared
+//   stage1(x, c0, bc)     clouds [c0, c0 + bc): centroid / scale, then chain A (full net) or the whole trunk (vanilla) -> pooled rows
+//   finish(x, b, ...)     T-Net tails, chains B and C, heads
+int model_forward_bf16_begin(pcp_model *m, int b, cudaStream_t st)
 {
     TcState *ts = reinterpret_cast<TcState *>(m->tc);
     PCP_REQUIRE(ts, PCP_ERR_STATE, "bf16 path: model not prepared");
     Workspace &ws = m->ws;
-    const bool full = !m->desc.vanilla;
-    const int C = m->desc.num_classes;
     if (ts->stat_clouds < (size_t)b) {
         cudaFree(ts->centroid); cudaFree(ts->scale); cudaFree(ts->wc);
         ts->centroid = ts->scale = nullptr; ts->wc = nullptr; ts->stat_clouds = 0;
@@ -710,28 +713,52 @@ int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_
         PCP_CUDA_OK(cudaMalloc(&ts->wc, (size_t)b * 8192));
         ts->stat_clouds = (size_t)b;
     }
-    // per-cloud centroid / scale only (the chains normalise on the fly; nothing per-point is written)
-    PCP_TRY(pcp_normalize_f32(d_x, b, n, nullptr, ts->centroid, ts->scale, st));
-    float *Rout = d_R ? d_R : ws.R;
     PCP_CUDA_OK(cudaMemsetAsync(ws.g3, 0, (size_t)b * 1024 * sizeof(float), st));
-    if (full) {
+    if (!m->desc.vanilla) {
         PCP_CUDA_OK(cudaMemsetAsync(ws.g1, 0, (size_t)b * 1024 * sizeof(float), st));
         PCP_CUDA_OK(cudaMemsetAsync(ws.g2, 0, (size_t)b * 1024 * sizeof(float), st));
-        PCP_TRY(launch_chain(ts, ts->A, d_x, b, n, nullptr, nullptr, ws.g1, st));
+    }
+    return PCP_OK;
+}
+
+int model_forward_bf16_stage1(pcp_model *m, const float *d_x_chunk, int c0, int bc, int64_t n, cudaStream_t st)
+{
+    TcState *ts = reinterpret_cast<TcState *>(m->tc);
+    Workspace &ws = m->ws;
+    // per-cloud centroid / scale only (the chains normalise on the fly; nothing per-point is written)
+    PCP_TRY(pcp_normalize_f32(d_x_chunk, bc, n, nullptr, ts->centroid + (size_t)c0 * 3, ts->scale + c0, st));
+    if (!m->desc.vanilla) return launch_chain(ts, ts->A, d_x_chunk, bc, n, nullptr, nullptr, ws.g1 + (size_t)c0 * 1024, st, c0);
+    return launch_chain(ts, ts->C, d_x_chunk, bc, n, nullptr, nullptr, ws.g3 + (size_t)c0 * 1024, st, c0);
+}
+
+int model_forward_bf16_finish(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg, float *d_R,
+                              float *d_cls_logits, float *d_seg_logits, cudaStream_t st)
+{
+    TcState *ts = reinterpret_cast<TcState *>(m->tc);
+    Workspace &ws = m->ws;
+    const bool full = !m->desc.vanilla;
+    float *Rout = d_R ? d_R : ws.R;
+    if (full) {
         PCP_TRY(heads_tc_tnet_tail(m, 0, ws.g1, b, Rout, st));
         PCP_TRY(launch_chain(ts, ts->B, d_x, b, n, Rout, nullptr, ws.g2, st));
         const bool need_r64 = (heads & PCP_HEAD_SEG) && (d_seg || d_seg_logits);       // the seg head folds R64 into its own first layer
         PCP_TRY(heads_tc_tnet_tail_fold(m, ws.g2, b, ts->wc, need_r64 ? ws.R64 : nullptr, st));
         PCP_TRY(launch_chain(ts, ts->C, d_x, b, n, Rout, ts->wc, ws.g3, st));
-    } else {
-        if (d_R) PCP_TRY(model_eye3(d_R, b, st));
-        PCP_TRY(launch_chain(ts, ts->C, d_x, b, n, nullptr, nullptr, ws.g3, st));
+    } else if (d_R) {
+        PCP_TRY(model_eye3(d_R, b, st));
     }
     if ((heads & PCP_HEAD_CLS) && (d_cls || d_cls_logits)) PCP_TRY(heads_tc_cls(m, ws.g3, b, d_cls, d_cls_logits, st));
     if ((heads & PCP_HEAD_SEG) && (d_seg || d_seg_logits))
         PCP_TRY(heads_tc_seg(m, d_x, b, n, ts->centroid, ts->scale, full ? Rout : nullptr, full ? ws.R64 : nullptr, ws.g3, d_seg, d_seg_logits, st));
-    (void)C;
     return PCP_OK;
+}
+
+int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
+                       float *d_R, float *d_cls_logits, float *d_seg_logits, cudaStream_t st)
+{
+    PCP_TRY(model_forward_bf16_begin(m, b, st));
+    PCP_TRY(model_forward_bf16_stage1(m, d_x, 0, b, n, st));
+    return model_forward_bf16_finish(m, d_x, b, n, heads, d_cls, d_seg, d_R, d_cls_logits, d_seg_logits, st);
 }
 
 }  // namespace pcp

@@ -444,6 +444,10 @@ int model_forward_fp32(pcp_model *m, const float *d_x, int b, int64_t n, uint32_
 
 int model_forward_bf16(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg,
                        float *d_R, float *d_cls_logits, float *d_seg_logits, cudaStream_t st);
+int model_forward_bf16_begin(pcp_model *m, int b, cudaStream_t st);
+int model_forward_bf16_stage1(pcp_model *m, const float *d_x_chunk, int c0, int bc, int64_t n, cudaStream_t st);
+int model_forward_bf16_finish(pcp_model *m, const float *d_x, int b, int64_t n, uint32_t heads, float *d_cls, float *d_seg, float *d_R,
+                              float *d_cls_logits, float *d_seg_logits, cudaStream_t st);
 int model_prepare_bf16(pcp_model *m);
 void model_destroy_bf16(pcp_model *m);
 
@@ -642,6 +646,45 @@ extern "C" int pcp_model_predict_host(pcp_model *m, const float *h_x, int b, int
         PCP_CUDA_OK(cudaStreamCreateWithFlags(&ws.copy_stream, cudaStreamNonBlocking));
         PCP_CUDA_OK(cudaEventCreateWithFlags(&ws.ev_start, cudaEventDisableTiming));
     }
+    // bf16 model, no per-point output: only the part of the forward that needs nothing but the points (statistics + first chain)
+    // runs per chunk, behind the chunk's copy; the T-Net tails, the other two chains and the heads run ONCE on the whole batch
+    // (a full forward per chunk pays the dependent-launch latency of the tails and short chain launches three times over).
+    // 1/8 of the batch per chunk (measured at 4096 x 1024: 4 / 6 / 8 / 12 / 16 / 24 chunks -> 3.40 / 3.35 / 3.35 / 3.39 / 3.42 / 3.64 ms):
+    // the first chain consumes points about as fast as PCIe delivers them, so what stays exposed is the last chunk's chain, while
+    // short chain launches lose efficiency.
+    static const bool no_staged = getenv("PCP_PREDICT_NO_STAGED") != nullptr;
+    if (!no_staged && m->desc.precision == PCP_PRECISION_BF16 && !h_seg) {
+        if (!m->prepared) PCP_TRY(pcp_model_prepare(m));
+        static const int parts = getenv("PCP_PREDICT_CHUNKS") ? std::max(1, atoi(getenv("PCP_PREDICT_CHUNKS"))) : 8;      // tuning knob
+        const int cb = std::max(1, std::max((int)(((int64_t)1 << 17) / n), (b + parts - 1) / parts));
+        const int nchunks = (b + cb - 1) / cb;
+        while ((int)ws.ev_copied.size() < nchunks) {
+            cudaEvent_t e;
+            PCP_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            ws.ev_copied.push_back(e);
+        }
+        PCP_CUDA_OK(cudaEventRecord(ws.ev_start, st));
+        PCP_CUDA_OK(cudaStreamWaitEvent(ws.copy_stream, ws.ev_start, 0));
+        for (int i = 0; i < nchunks; ++i) {
+            const int c0 = i * cb, bc = std::min(cb, b - c0);
+            PCP_CUDA_OK(cudaMemcpyAsync(ws.stage_x + (size_t)c0 * n * 3, h_x + (size_t)c0 * n * 3, (size_t)bc * n * 3 * sizeof(float),
+                                        cudaMemcpyHostToDevice, ws.copy_stream));
+            PCP_CUDA_OK(cudaEventRecord(ws.ev_copied[i], ws.copy_stream));
+        }
+        PCP_TRY(model_forward_bf16_begin(m, b, st));
+        for (int i = 0; i < nchunks; ++i) {
+            const int c0 = i * cb, bc = std::min(cb, b - c0);
+            PCP_CUDA_OK(cudaStreamWaitEvent(st, ws.ev_copied[i], 0));
+            PCP_TRY(model_forward_bf16_stage1(m, ws.stage_x + (size_t)c0 * n * 3, c0, bc, n, st));
+        }
+        PCP_TRY(model_forward_bf16_finish(m, ws.stage_x, b, n, heads, h_cls ? ws.stage_cls : nullptr, nullptr, h_R ? ws.stage_R : nullptr, nullptr,
+                                          nullptr, st));
+        if (h_cls) PCP_CUDA_OK(cudaMemcpyAsync(h_cls, ws.stage_cls, cls_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+        if (h_R) PCP_CUDA_OK(cudaMemcpyAsync(h_R, ws.stage_R, r_cnt * sizeof(float), cudaMemcpyDeviceToHost, st));
+        PCP_CUDA_OK(cudaStreamSynchronize(st));
+        return PCP_OK;
+    }
+    // Otherwise the batch is cut into chunks that each run a whole forward.
     // Chunk sizes grow geometrically (256 K points, then x3): the first copy is short, so compute starts early, and every
     // later copy hides behind the forward of the chunk before it while the per-forward fixed cost is paid only ~4 times.
     std::vector<int> bounds(1, 0);
