@@ -498,9 +498,8 @@ fps_pruned_kernel(const int32_t *__restrict__ perm, const float *__restrict__ xo
     const int rowsT = ngroups * kFpsGroupRows;
     const int arows = rowsT > PPT ? rowsT - PPT : 0;
     __shared__ float4 slots[2][(CS * kFpsWarps < 32 ? 32 : CS * kFpsWarps)];
-    __shared__ unsigned tie_key[kFpsWarps];          // tie resolution: lowest original index per warp
-    __shared__ float4 tslots[CS];   // tie resolution: per block x, y, z, original index
-    __shared__ uint64_t xbar[2];
+    __shared__ float4 tslots[2][(CS * kFpsWarps < 32 ? 32 : CS * kFpsWarps)];      // tie resolution: per warp x, y, z, original index
+    __shared__ uint64_t xbar[2], tbar[2];
 
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
@@ -595,13 +594,23 @@ fps_pruned_kernel(const int32_t *__restrict__ perm, const float *__restrict__ xo
     if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
 
     constexpr int nrec = CS * kFpsWarps;         // records per iteration
-    if (nrec < 32 && tid < 32) { slots[0][tid] = make_float4(0.f, 0.f, 0.f, 0.f); slots[1][tid] = make_float4(0.f, 0.f, 0.f, 0.f); }   // unused slots read as "no point"
-    if (tid == 0) { umma::mbar_init(&xbar[0], 1); umma::mbar_init(&xbar[1], 1); umma::fence_barrier_init(); }
+    if (nrec < 32 && tid < 32) {         // unused slots read as "no point"
+        slots[0][tid] = make_float4(0.f, 0.f, 0.f, 0.f); slots[1][tid] = make_float4(0.f, 0.f, 0.f, 0.f);
+        tslots[0][tid] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0xFFFFFFFFu)); tslots[1][tid] = tslots[0][tid];
+    }
+    if (tid == 0) {
+        umma::mbar_init(&xbar[0], 1); umma::mbar_init(&xbar[1], 1); umma::mbar_init(&tbar[0], 1); umma::mbar_init(&tbar[1], 1);
+        umma::fence_barrier_init();
+    }
     __syncthreads();
-    if (tid == 0) { umma::mbar_arrive_expect_tx(&xbar[0], nrec * 16u); umma::mbar_arrive_expect_tx(&xbar[1], nrec * 16u); }
+    if (tid == 0) {
+        umma::mbar_arrive_expect_tx(&xbar[0], nrec * 16u); umma::mbar_arrive_expect_tx(&xbar[1], nrec * 16u);
+        umma::mbar_arrive_expect_tx(&tbar[0], nrec * 16u); umma::mbar_arrive_expect_tx(&tbar[1], nrec * 16u);
+    }
     cluster.sync();                              // every block is armed before anybody pushes
     long long ph[6] = {0, 0, 0, 0, 0, 0}, tprev = clock64();
     unsigned long long nact = 0, nties = 0;
+    unsigned ntie = 0u;                          // tie iterations so far (identical in every warp of the cluster)
     unsigned wcode = 0u, wlo = 0u;               // this warp's record (warp-uniform): code, local id and coordinates of its best point
     float wx = 0.f, wy = 0.f, wz = 0.f;
     for (int it = 1; it < s; ++it) {
@@ -748,34 +757,38 @@ fps_pruned_kernel(const int32_t *__restrict__ perm, const float *__restrict__ xo
                     }
                 }
             }
+            // every warp pushes (x, y, z, lowest original index among ITS tied points) into every block, on a second pair of
+            // transaction barriers that advances with the number of tie iterations (all warps count them alike)
             const unsigned wmin = __reduce_min_sync(0xffffffffu, cand);
-            if (lane == 0) tie_key[warp] = wmin;
-            __syncthreads();
-            const unsigned bmin = __reduce_min_sync(0xffffffffu, lane < kFpsWarps ? tie_key[lane] : 0xFFFFFFFFu);
-            const bool own_w = bmin != 0xFFFFFFFFu ? tie_key[warp] == bmin : warp == 0;
-            if (own_w) {
-                float rx = 0.f, ry = 0.f, rz = 0.f;
-                const unsigned who = __ballot_sync(0xffffffffu, bmin != 0xFFFFFFFFu && cand == bmin);
-                const int ol = who ? __ffs(who) - 1 : 0;
-                if (who && lane == ol) {
-                    if (crow >= PPT) srow(crow, rx, ry, rz);
-                    else {
+            float rx = 0.f, ry = 0.f, rz = 0.f;
+            const unsigned who = __ballot_sync(0xffffffffu, wmin != 0xFFFFFFFFu && cand == wmin);
+            const int ol = who ? __ffs(who) - 1 : 0;
+            if (who && lane == ol) {
+                if (crow >= PPT) srow(crow, rx, ry, rz);
+                else {
 #pragma unroll
-                        for (int k = 0; k < PPT; ++k)
-                            if (k == crow) { rx = px[k]; ry = py[k]; rz = pz[k]; }
-                    }
+                    for (int k = 0; k < PPT; ++k)
+                        if (k == crow) { rx = px[k]; ry = py[k]; rz = pz[k]; }
                 }
-                rx = __shfl_sync(0xffffffffu, rx, ol); ry = __shfl_sync(0xffffffffu, ry, ol); rz = __shfl_sync(0xffffffffu, rz, ol);
-                const float4 rec = make_float4(rx, ry, rz, __uint_as_float(bmin));
-                if (lane < cs) *cluster.map_shared_rank(&tslots[rank], lane) = rec;
             }
-            asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-            fps_wait();
-            const float4 t = tslots[lane < cs ? lane : 0];
-            const unsigned ti = lane < cs ? __float_as_uint(t.w) : 0xFFFFFFFFu;
-            const unsigned tmin = __reduce_min_sync(0xffffffffu, ti);
-            const int tb = __ffs(__ballot_sync(0xffffffffu, ti == tmin)) - 1;
-            cx = __shfl_sync(0xffffffffu, t.x, tb); cy = __shfl_sync(0xffffffffu, t.y, tb); cz = __shfl_sync(0xffffffffu, t.z, tb);
+            rx = __shfl_sync(0xffffffffu, rx, ol); ry = __shfl_sync(0xffffffffu, ry, ol); rz = __shfl_sync(0xffffffffu, rz, ol);
+            const int tpar = (int)(ntie & 1u);
+            if (lane < cs)
+                fps_st_async16(&tslots[tpar][rank * kFpsWarps + warp], &tbar[tpar], (uint32_t)lane, __float_as_uint(rx), __float_as_uint(ry),
+                               __float_as_uint(rz), wmin);
+            fps_wait_records(&tbar[tpar], (ntie >> 1) & 1u);
+            if (tid == 0) umma::mbar_arrive_expect_tx(&tbar[tpar], nrec * 16u);        // for tie iteration ntie + 2 (same argument as xbar)
+            ++ntie;
+            float4 tr[kPerLane];
+#pragma unroll
+            for (int e = 0; e < kPerLane; ++e) tr[e] = tslots[tpar][lane + 32 * e];
+            float4 tb4 = tr[0];
+#pragma unroll
+            for (int e = 1; e < kPerLane; ++e)
+                if (__float_as_uint(tr[e].w) < __float_as_uint(tb4.w)) tb4 = tr[e];
+            const unsigned tmin = __reduce_min_sync(0xffffffffu, __float_as_uint(tb4.w));
+            const int tb = __ffs(__ballot_sync(0xffffffffu, __float_as_uint(tb4.w) == tmin)) - 1;
+            cx = __shfl_sync(0xffffffffu, tb4.x, tb); cy = __shfl_sync(0xffffffffu, tb4.y, tb); cz = __shfl_sync(0xffffffffu, tb4.z, tb);
             if (rank == 0 && tid == 0) idx_out[cloud * s + it] = (int32_t)tmin;
         }
         FPS_STAMP(5);
