@@ -46,18 +46,30 @@ def check_sync_bn(x, y, gb, C, P, world, precision, tol):
     cos = float((g_dp * g_1).sum() / (g_dp.norm() * g_1.norm()))
     if os.environ.get("PCP_MG_REPORT") and dist.get_rank() == 0:
         print(f"[report] {precision}: max-norm err {err:.3e} rel-L2 {float((g_dp - g_1).norm() / g_1.norm()):.3e} cosine {cos:.5f}", flush=True)
+    loss = torch.tensor([met_d["classification_output_loss"] * len(xs) / gb], dtype=torch.float64, device="cuda")
+    dist.all_reduce(loss)          # the per-rank loss is this shard's share of the global mean: summed over the ranks it is the single-device loss
+    loss_1 = met_s["classification_output_loss"]
     if precision == "fp32":
         assert err < tol, (precision, err)
+        assert abs(float(loss) - loss_1) <= 1e-4 * max(1.0, loss_1)
     else:
-        # bf16 with the implicit pooled layers: the fp32 Gram matrix differs at 1e-6 between one device and two (summation
-        # order), and a bf16-rounded network amplifies that (test_gpu_train.py docstring); with PCP_TRAIN_EXPLICIT_POOL=1 the
-        # same comparison agrees to 3e-7.  The pooled layer's protocol itself is pinned exactly on one device
-        # (test_gpu_train_pool.py::test_pooled_layer_data_parallel_protocol); here only direction and scale are bounded.
-        assert cos > 0.9 and 0.5 < float(g_dp.norm() / g_1.norm()) < 2.0, (precision, err, cos)
-    # the per-rank loss is this shard's share of the global mean: summed over the ranks it is the single-device loss
-    loss = torch.tensor([met_d["classification_output_loss"] * len(xs) / gb], dtype=torch.float64, device="cuda")
-    dist.all_reduce(loss)
-    assert abs(float(loss) - met_s["classification_output_loss"]) <= 1e-4 * max(1.0, met_s["classification_output_loss"]) * (1 if precision == "fp32" else 50)
+        # bf16 with the implicit pooled layers: the fp32 Gram matrix is accumulated with float atomics, so it differs at 1e-6 between
+        # two RUNS of the same single-device step, and a bf16-rounded network amplifies that (test_gpu_train.py docstring): measured
+        # on 2 x B200, the single-device loss of this very batch varies by 1 % from run to run (8.424 ... 8.506) and its gradient
+        # against itself has cosine 0.92 - 0.97.  With PCP_TRAIN_EXPLICIT_POOL=1 the data-parallel comparison agrees to 3e-7, and the
+        # pooled layer's protocol is pinned exactly on one device (test_gpu_train_pool.py::test_pooled_layer_data_parallel_protocol)
+        # and end to end in fp32 above.  So the bound here is the step's OWN nondeterminism: the data-parallel step may differ from
+        # the single-device step by no more than a few times what the single-device step differs from itself.
+        ms2 = make_model(C, P, precision, sync_bn=False, smooth=True)
+        met_s2 = ms2.train_on_batch(x, y, global_batch=gb, sample_offset=0, apply=False, allreduce=False)
+        g_1b = ms2._grad_tensor().clone()
+        self_cos = float((g_1b * g_1).sum() / (g_1b.norm() * g_1.norm()))
+        self_loss = abs(met_s2["classification_output_loss"] - loss_1) / max(1.0, loss_1)
+        if os.environ.get("PCP_MG_REPORT") and dist.get_rank() == 0:
+            print(f"[report] {precision}: single-device step against itself: cosine {self_cos:.5f} loss rel diff {self_loss:.3e}; "
+                  f"data-parallel loss {float(loss):.6f} single {loss_1:.6f}", flush=True)
+        assert cos > min(0.9, self_cos) - 0.15 and 0.5 < float(g_dp.norm() / g_1.norm()) < 2.0, (precision, err, cos, self_cos)
+        assert abs(float(loss) - loss_1) / max(1.0, loss_1) <= max(2e-2, 4.0 * self_loss), (float(loss), loss_1, self_loss)
     wd, w1 = md.get_weights_dict(), ms.get_weights_dict()
     for k in wd:
         if "moving_" in k and precision == "fp32":
