@@ -84,6 +84,7 @@ struct WgradParams {
     int64_t rows;
     int cin, cout;
     int64_t rows_per_split;               // multiple of 64
+    int64_t split_stride;                 // 0: every split accumulates into dW with atomics; else split z STORES its partial at dW + z * stride
 };
 
 __global__ void __launch_bounds__(kWgThreads, 1)
@@ -202,8 +203,10 @@ tc_wgrad_kernel(const WgradParams p)
                     const int m = m0 + warp * 32 + r, n = n0 + c0 + c;
                     const float4 q = *reinterpret_cast<const float4 *>(stage + r * 36 + c);
                     if (m < p.cin && n < p.cout) {               // cout % 8 == 0: a float4 never straddles the edge
-                        float *dst = p.dW + (int64_t)m * p.lddw + n;
-                        if (vec_ok) {
+                        float *dst = p.dW + (int64_t)blockIdx.z * p.split_stride + (int64_t)m * p.lddw + n;
+                        if (p.split_stride) {                    // deterministic mode: this CTA is the only writer of its slice
+                            dst[0] = q.x; dst[1] = q.y; dst[2] = q.z; dst[3] = q.w;
+                        } else if (vec_ok) {
                             atomicAdd(reinterpret_cast<float4 *>(dst), q);
                         } else {
                             atomicAdd(dst, q.x); atomicAdd(dst + 1, q.y); atomicAdd(dst + 2, q.z); atomicAdd(dst + 3, q.w);
@@ -236,16 +239,18 @@ tc_wgrad_kernel(const WgradParams p)
     if (warp == 8) tmem_dealloc(tmem, 128);
 }
 
-int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ, int64_t ldz, int cout, float *dW, int64_t lddw,
-             cudaStream_t st)
+// parts != nullptr: deterministic form — split z stores its partial product at parts + z * cin * lddw (nothing is accumulated with
+// atomics) and *nparts receives the number of splits; the caller sums the slices in a fixed order
+static int tc_wgrad_impl(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ, int64_t ldz, int cout, float *dW, int64_t lddw,
+                         float *parts, size_t parts_floats, int *nparts, cudaStream_t st)
 {
-    PCP_REQUIRE(A && dZ && dW, PCP_ERR_INVALID, "tc_wgrad: null operand");
+    PCP_REQUIRE(A && dZ && (dW || parts), PCP_ERR_INVALID, "tc_wgrad: null operand");
     PCP_REQUIRE(cin % 8 == 0 && cout % 8 == 0 && lda % 4 == 0 && ldz % 4 == 0, PCP_ERR_UNSUPPORTED,
                 "tc_wgrad: cin=%d / cout=%d must be multiples of 8 and the leading dimensions multiples of 4", cin, cout);
     PCP_REQUIRE((((uintptr_t)A | (uintptr_t)dZ) & 15u) == 0, PCP_ERR_UNSUPPORTED, "tc_wgrad: operands must be 16-byte aligned");
-    if (rows <= 0) return PCP_OK;
+    if (rows <= 0) { if (nparts) *nparts = 0; return PCP_OK; }
     WgradParams p;
-    p.A = A; p.lda = lda; p.Z = dZ; p.ldz = ldz; p.dW = dW; p.lddw = lddw; p.rows = rows; p.cin = cin; p.cout = cout;
+    p.A = A; p.lda = lda; p.Z = dZ; p.ldz = ldz; p.dW = dW; p.lddw = lddw; p.rows = rows; p.cin = cin; p.cout = cout; p.split_stride = 0;
     const int mt = (cin + 127) / 128, nt = (cout + 127) / 128;
     const int64_t ktiles = (rows + 63) / 64;
     int64_t splits = std::max<int64_t>(1, (int64_t)sm_count() / ((int64_t)mt * nt));            // one CTA per SM
@@ -254,12 +259,52 @@ int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ
     const int64_t kps = (ktiles + splits - 1) / splits;
     p.rows_per_split = kps * 64;
     splits = (ktiles + kps - 1) / kps;
-    static bool attr = false;
-    if (!attr) {
+    if (parts) {
+        p.split_stride = (int64_t)cin * lddw;
+        PCP_REQUIRE((size_t)splits * (size_t)p.split_stride <= parts_floats, PCP_ERR_INVALID, "tc_wgrad: partial-product scratch too small");
+        p.dW = parts;
+        *nparts = (int)splits;
+    }
+    static bool attr[64] = {};
+    int dev = 0;
+    PCP_CUDA_OK(cudaGetDevice(&dev));
+    PCP_REQUIRE(dev >= 0 && dev < 64, PCP_ERR_UNSUPPORTED, "tc_wgrad: device ordinal %d", dev);
+    if (!attr[dev]) {
         PCP_CUDA_OK(cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWgSmem));
-        attr = true;
+        attr[dev] = true;
     }
     tc_wgrad_kernel<<<dim3(nt, mt, (unsigned)splits), kWgThreads, kWgSmem, st>>>(p);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ, int64_t ldz, int cout, float *dW, int64_t lddw,
+             cudaStream_t st)
+{
+    return tc_wgrad_impl(A, lda, rows, cin, dZ, ldz, cout, dW, lddw, nullptr, 0, nullptr, st);
+}
+
+__global__ void __launch_bounds__(256)
+sum_parts_kernel(const float *__restrict__ parts, int nparts, int64_t stride, int64_t count, float *__restrict__ out)
+{
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    double acc = 0.0;
+    for (int z = 0; z < nparts; ++z) acc += (double)parts[(int64_t)z * stride + i];      // fixed order: the result does not depend on scheduling
+    out[i] = (float)acc;
+}
+
+size_t tc_gram_scratch_floats(int cin) { return (size_t)sm_count() * cin * cin; }
+
+// G (cin x cin) = A^T A of the bf16-rounded A, DETERMINISTIC: run to run the same bits (the atomics of tc_wgrad's split-K make the
+// plain form differ at 1e-6, which a bf16-rounded network amplifies into a 1 % loss difference between two runs of the same step)
+int tc_gram_det(const float *A, int64_t lda, int64_t rows, int cin, float *G, float *scratch, size_t scratch_floats, cudaStream_t st)
+{
+    int nparts = 0;
+    PCP_TRY(tc_wgrad_impl(A, lda, rows, cin, A, lda, cin, nullptr, cin, scratch, scratch_floats, &nparts, st));
+    const int64_t count = (int64_t)cin * cin;
+    if (nparts == 0) { PCP_CUDA_OK(cudaMemsetAsync(G, 0, (size_t)count * 4, st)); return PCP_OK; }
+    sum_parts_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(scratch, nparts, count, count, G);
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }

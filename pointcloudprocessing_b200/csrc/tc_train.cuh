@@ -11,6 +11,9 @@ int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, u
 // dW (cin x cout, leading dimension lddw) += A^T (cin x rows) . dZ (rows x cout): split-K over the rows, fp32 atomics
 int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ, int64_t ldz, int cout, float *dW, int64_t lddw,
              cudaStream_t st);
+// deterministic Gram matrix G = A^T A (cin x cin) through per-split partial products summed in a fixed order
+size_t tc_gram_scratch_floats(int cin);
+int tc_gram_det(const float *A, int64_t lda, int64_t rows, int cin, float *G, float *scratch, size_t scratch_floats, cudaStream_t st);
 
 // per-cloud column extrema of Z = A . W without storing Z: A (b*n x 128) fp32, Wimg = pack_weight_image(W, 128, cout);
 // ext_max / ext_min (b x cout) hold packed keys (tc_gemm.cuh: value key << 32 | ~row, inverted value key for the minimum),

@@ -541,6 +541,7 @@ __global__ void axpy_kernel(float *__restrict__ y, const float *__restrict__ x, 
 struct PoolBufs {
     unsigned long long *ext = nullptr;   // 2 x (b x cout) packed extrema keys (max, then min)
     float *gram = nullptr;               // cin x cin : A^T A of the bf16-rounded input (this rank's rows)
+    float *gram_parts = nullptr;         // per-split partial Gram matrices (tc_gram_det)
     double *asum = nullptr;              // cin       : 1^T A
     float *gram_g = nullptr;             // the same summed over the ranks (sync-BN); aliases gram / asum otherwise
     double *asum_g = nullptr;
@@ -680,6 +681,7 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
     else
         for (PoolBufs &pb : ts->pool) {
             want(&pb.ext, (size_t)b * 1024 * 16); want(&pb.gram, 128 * 128 * 4); want(&pb.asum, 128 * 8); want(&pb.zsel, (size_t)b * 4096);
+            want(&pb.gram_parts, tc_gram_scratch_floats(128) * 4);
             want(&pb.gram_g, 128 * 128 * 4); want(&pb.asum_g, 128 * 8);
             want(&pb.arg, (size_t)b * 4096); want(&pb.S, (size_t)b * 4096); want(&pb.c0, 4096); want(&pb.c1, 4096); want(&pb.Wt, 1024 * 128 * 4);
             want(&pb.Q, 128 * 128 * 4); want(&pb.q, 512);
@@ -1258,6 +1260,7 @@ extern "C" int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, con
     want(&dg, bc * 4); want(&g, bc * 4); want(&dWg, (size_t)128 * cout * 4); want(&dgam, cout * 4); want(&dbet, cout * 4); want(&dAo, rows * 512);
     want(&img, (size_t)4 << 20);
     want(&L.mean, cout * 4); want(&L.inv, cout * 4); want(&L.sc, cout * 4); want(&L.beta, cout * 4); want(&L.red, (size_t)cout * 16);
+    want(&L.pb.gram_parts, tc_gram_scratch_floats(128) * 4);
     want(&L.pb.ext, bc * 16); want(&L.pb.gram, 128 * 128 * 4); want(&L.pb.asum, 128 * 8); want(&L.pb.gram_g, 128 * 128 * 4); want(&L.pb.asum_g, 128 * 8); want(&L.pb.zsel, bc * 4); want(&L.pb.arg, bc * 4);
     want(&L.pb.S, bc * 4); want(&L.pb.c0, cout * 4); want(&L.pb.c1, cout * 4); want(&L.pb.Wt, (size_t)cout * 512); want(&L.pb.Q, 128 * 128 * 4);
     want(&L.pb.q, 512);

@@ -231,9 +231,9 @@ static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStre
     PCP_TRY(pack_weight_image(L.W, 128, L.cout, L.cout, false, g_tc.img, st));
     PCP_TRY(tc_pool_extrema(A, L.b, L.n, g_tc.img, L.cout, L.pb.ext, L.pb.ext + total, st));
     if (L.batch) {
-        PCP_CUDA_OK(cudaMemsetAsync(L.pb.gram, 0, 128 * 128 * 4, st));
         PCP_CUDA_OK(cudaMemsetAsync(L.pb.asum, 0, 128 * 8, st));
-        PCP_TRY(tc_wgrad(A, 128, rows, 128, A, 128, 128, L.pb.gram, 128, st));
+        // the Gram matrix feeds the layer's batch statistics, i.e. the FORWARD: it has to be the same bits on every run
+        PCP_TRY(tc_gram_det(A, 128, rows, 128, L.pb.gram, L.pb.gram_parts, tc_gram_scratch_floats(128), st));
         pool_colsum_kernel<<<(int)std::min<int64_t>((rows + 7) / 8, (int64_t)sm_count() * 4), 256, 0, st>>>(A, rows, L.pb.asum);
         PCP_CHECK_LAUNCH();
         // statistics use the Gram matrix / column sums of the CONCATENATED batch (sync-BN); dW below keeps this rank's

@@ -53,13 +53,14 @@ def check_sync_bn(x, y, gb, C, P, world, precision, tol):
         assert err < tol, (precision, err)
         assert abs(float(loss) - loss_1) <= 1e-4 * max(1.0, loss_1)
     else:
-        # bf16 with the implicit pooled layers: the fp32 Gram matrix is accumulated with float atomics, so it differs at 1e-6 between
-        # two RUNS of the same single-device step, and a bf16-rounded network amplifies that (test_gpu_train.py docstring): measured
-        # on 2 x B200, the single-device loss of this very batch varies by 1 % from run to run (8.424 ... 8.506) and its gradient
-        # against itself has cosine 0.92 - 0.97.  With PCP_TRAIN_EXPLICIT_POOL=1 the data-parallel comparison agrees to 3e-7, and the
-        # pooled layer's protocol is pinned exactly on one device (test_gpu_train_pool.py::test_pooled_layer_data_parallel_protocol)
-        # and end to end in fp32 above.  So the bound here is the step's OWN nondeterminism: the data-parallel step may differ from
-        # the single-device step by no more than a few times what the single-device step differs from itself.
+        # bf16: the pooled layers take their batch statistics from the Gram matrix of their input, and one device sums it in a
+        # different order than two (per-rank sums, then the all-reduce) — a 1e-7 difference that a bf16-rounded network amplifies
+        # (test_gpu_train.py docstring): on 2 x B200 the two losses of this batch are 8.414 and 8.509, the gradients' cosine 0.95.
+        # With PCP_TRAIN_EXPLICIT_POOL=1 the comparison agrees to 3e-7, the pooled layer's protocol is pinned exactly on one device
+        # (test_gpu_train_pool.py::test_pooled_layer_data_parallel_protocol) and end to end in fp32 above; here direction, scale and
+        # the loss are bounded.  Each side is reproducible by itself: the Gram matrix is summed in a fixed order (tc_gram_det), so
+        # the single-device step run twice gives the same loss bit for bit — checked below (before round 2's fix it varied by 1 %
+        # from run to run and this test failed two times in five).
         ms2 = make_model(C, P, precision, sync_bn=False, smooth=True)
         met_s2 = ms2.train_on_batch(x, y, global_batch=gb, sample_offset=0, apply=False, allreduce=False)
         g_1b = ms2._grad_tensor().clone()
@@ -68,8 +69,9 @@ def check_sync_bn(x, y, gb, C, P, world, precision, tol):
         if os.environ.get("PCP_MG_REPORT") and dist.get_rank() == 0:
             print(f"[report] {precision}: single-device step against itself: cosine {self_cos:.5f} loss rel diff {self_loss:.3e}; "
                   f"data-parallel loss {float(loss):.6f} single {loss_1:.6f}", flush=True)
-        assert cos > min(0.9, self_cos) - 0.15 and 0.5 < float(g_dp.norm() / g_1.norm()) < 2.0, (precision, err, cos, self_cos)
-        assert abs(float(loss) - loss_1) / max(1.0, loss_1) <= max(2e-2, 4.0 * self_loss), (float(loss), loss_1, self_loss)
+        assert self_loss <= 1e-6 and self_cos > 0.999, ("the bf16 step is not reproducible run to run", self_loss, self_cos)
+        assert cos > 0.8 and 0.5 < float(g_dp.norm() / g_1.norm()) < 2.0, (precision, err, cos, self_cos)
+        assert abs(float(loss) - loss_1) / max(1.0, loss_1) <= 3e-2, (float(loss), loss_1, self_loss)
     wd, w1 = md.get_weights_dict(), ms.get_weights_dict()
     for k in wd:
         if "moving_" in k and precision == "fp32":
