@@ -49,6 +49,7 @@ struct ChainParams {
     int tiles_per_cloud;
     int64_t total_tiles;
     unsigned long long *trace;            // development only (PCP_CHAIN_TRACE): per-role event timestamps of cluster 0
+    int trace_tid;                        // the front-group thread that records role 0 (PCP_CHAIN_TRACE_TID, default 0)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -190,7 +191,7 @@ chain2_kernel(const ChainParams p)
         uint8_t *Ag = fgp ? A1 : A0;
         uint32_t mid_phase = 0;
         uint32_t tcnt = 0;
-        const bool tr = (tid == 0);                        // (trace: group 0 only)
+        const bool tr = (tid == p.trace_tid);              // (trace: one thread, by default of group 0)
         // normalised (and R-rotated) coordinates of this thread's point for pair-step `it`; evaluated one step
         // ahead so the global-load + divide latency hides behind the wait for the first mid-layer MMA
         auto load_point = [&](int64_t it, float &q0, float &q1, float &q2) {
@@ -666,6 +667,7 @@ static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, 
         PCP_CUDA_OK(cudaMalloc(&d_trace, trace_bytes));
         PCP_CUDA_OK(cudaMemsetAsync(d_trace, 0, trace_bytes, st));
         p.trace = d_trace;
+        if (const char *e = getenv("PCP_CHAIN_TRACE_TID")) p.trace_tid = atoi(e);
     }
     {
         static const bool no_pdl = getenv("PCP_TC_GEMM_NO_PDL") != nullptr;

@@ -20,7 +20,8 @@ for f in glob.glob("/tmp/chain_trace*"):
     os.remove(f)
 m(x, heads=("cls",))
 torch.cuda.synchronize()
-f = sorted(glob.glob("/tmp/chain_trace*"))[-1]
+which = int(sys.argv[1]) if len(sys.argv) > 1 else -1          # launch of the forward: 0 / 1 / 2 = chain A / B / C (default C)
+f = sorted(glob.glob("/tmp/chain_trace*"))[which]
 a = np.fromfile(f, dtype=np.uint64).reshape(8, 2048, 2)
 
 
