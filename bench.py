@@ -179,6 +179,9 @@ def main():
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # host threads (and therefore the first-touch pinned buffers of the e2e leg) next to this rank's GPU; a no-op on single-node boxes
+    from pointcloudprocessing_b200 import parallel as _par
+    numa = _par.bind_to_gpu_numa(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -529,7 +532,7 @@ def main():
             "metric": "pointnet_clouds_per_sec_1024pts", "value": value, "unit": "clouds/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": workload_config(B, world),
-            "clocks": clocks, "gpu_launches": launches,
+            "clocks": clocks, "gpu_launches": launches, "host_binding": numa,
             "e2e": {"value": e2e_value, "unit": "clouds/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
             "roofline": roofline, "rooflines": rooflines, "cpu_baseline": cpu, "gflop_per_cloud": flops_per_cloud(N_POINTS) / 1e9,
             "model_tflops": value * flops_per_cloud(N_POINTS) / 1e12,

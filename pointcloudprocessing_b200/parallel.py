@@ -25,6 +25,50 @@ def barrier():
         dist.barrier()
 
 
+def bind_to_gpu_numa(device_index: int | None = None) -> dict:
+    """Pin this process to the CPU cores NVML reports as local to its GPU (the GPU's NUMA node), BEFORE any pinned host buffer is
+    allocated: pinned pages are first-touch, so the end-to-end path's H2D copies then start from the memory controller next to the
+    GPU's PCIe root instead of wherever the launcher happened to start the rank (eight ranks pulling 50 MB per
+    step through one node).  Returns what was done — {"bound": bool, "cpus": n, "reason": ...} — and never raises: on a box whose
+    GPUs all report the same CPU set (one NUMA node) there is nothing to gain and the mask is left alone."""
+    info = {"bound": False, "cpus": 0, "reason": ""}
+    try:
+        import pynvml
+        if device_index is None:
+            device_index = torch.cuda.current_device() if torch.cuda.is_available() else 0
+        pynvml.nvmlInit()
+        n_dev = pynvml.nvmlDeviceGetCount()
+        words = (os.cpu_count() + 63) // 64
+
+        def cpus_of(i):
+            # honour CUDA_VISIBLE_DEVICES: torch's ordinal i is the i-th visible device
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = i
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if i < len(ids) and ids[i].isdigit():
+                    phys = int(ids[i])
+            h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+            return {w * 64 + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        mine = cpus_of(device_index)
+        allowed = os.sched_getaffinity(0)
+        target = mine & allowed
+        info["cpus"] = len(target)
+        if not target:
+            info["reason"] = "no overlap between the GPU's CPU set and this process's allowed CPUs"
+        elif all(cpus_of(i) == mine for i in range(n_dev)) and n_dev > 1:
+            info["reason"] = "every GPU reports the same CPU set (single NUMA node): nothing to bind"
+        elif target == allowed:
+            info["reason"] = "already confined to the GPU's CPU set"
+        else:
+            os.sched_setaffinity(0, target)
+            info["bound"] = True
+    except Exception as e:                      # NVML missing, permission denied, exotic topology: keep running unbound
+        info["reason"] = f"{type(e).__name__}: {e}"
+    return info
+
+
 def init_from_env(backend: str | None = None):
     """Initialise the default process group from torchrun's RANK / WORLD_SIZE / MASTER_* environment."""
     ws = int(os.environ.get("WORLD_SIZE", "1"))
@@ -36,6 +80,7 @@ def init_from_env(backend: str | None = None):
     if backend == "nccl":
         lr = int(os.environ.get("LOCAL_RANK", "0"))
         torch.cuda.set_device(lr)
+        bind_to_gpu_numa(lr)
         dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     else:
         dist.init_process_group(backend)

@@ -78,3 +78,16 @@ def test_single_process_defaults():
     x = np.arange(10)
     xs, ys, off = parallel.shard_batch(x, None, rank=1, world_size=4)
     assert list(xs) == [3, 4, 5] and ys is None and off == 3
+
+
+def test_bind_to_gpu_numa_never_raises():
+    """Host-side placement helper: without NVML / a GPU it reports why it did nothing and leaves the CPU mask alone."""
+    import os
+    from pointcloudprocessing_b200 import parallel
+    before = os.sched_getaffinity(0)
+    info = parallel.bind_to_gpu_numa(0)
+    assert set(info) == {"bound", "cpus", "reason"}
+    if not info["bound"]:
+        assert os.sched_getaffinity(0) == before
+    else:
+        os.sched_setaffinity(0, before)
