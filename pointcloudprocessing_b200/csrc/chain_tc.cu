@@ -743,8 +743,10 @@ int model_forward_bf16_finish(pcp_model *m, const float *d_x, int b, int64_t n, 
     if (full) {
         PCP_TRY(heads_tc_tnet_tail(m, 0, ws.g1, b, Rout, st));
         PCP_TRY(launch_chain(ts, ts->B, d_x, b, n, Rout, nullptr, ws.g2, st));
-        const bool need_r64 = (heads & PCP_HEAD_SEG) && (d_seg || d_seg_logits);       // the seg head folds R64 into its own first layer
+        // the seg head folds R64 into its own first layer; pcp_model_evaluate wants its orthogonality regulariser
+        const bool need_r64 = ((heads & PCP_HEAD_SEG) && (d_seg || d_seg_logits)) || m->eval_reg_acc;
         PCP_TRY(heads_tc_tnet_tail_fold(m, ws.g2, b, ts->wc, need_r64 ? ws.R64 : nullptr, st));
+        if (m->eval_reg_acc) PCP_TRY(tnet_reg_accumulate(ws.R64, b, 64, m->eval_reg_acc, st));
         PCP_TRY(launch_chain(ts, ts->C, d_x, b, n, Rout, ts->wc, ws.g3, st));
     } else if (d_R) {
         PCP_TRY(model_eye3(d_R, b, st));

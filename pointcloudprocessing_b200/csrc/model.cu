@@ -421,6 +421,7 @@ int model_forward_fp32(pcp_model *m, const float *d_x, int b, int64_t n, uint32_
             PCP_TRY(layer_fwd(m, L_FT_C2, ws.h64a, M, ws.h128, true, st));
             PCP_TRY(layer_fwd(m, L_FT_C3, ws.h128, M, nullptr, true, st, g2, bc, n));
             PCP_TRY(tnet_tail(m, L_FT_C1, m->fold_ft_w, m->fold_ft_t, 64, g2, bc, ws.R64, st));     // :227
+            if (m->eval_reg_acc) PCP_TRY(tnet_reg_accumulate(ws.R64, bc, 64, m->eval_reg_acc, st));
             GemmArgs g;                                                                            // X_64 = X @ R_64 :228
             g.A = ws.h64b; g.lda = 64; g.strideA = n * 64; g.B = ws.R64; g.ldb = 64; g.strideB = 4096;
             g.C = ws.x64; g.ldc = 64; g.strideC = n * 64; g.M = (int)n; g.N = 64; g.K = 64; g.groups = bc;

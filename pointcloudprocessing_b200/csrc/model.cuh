@@ -72,6 +72,8 @@ struct pcp_model {
     float *d_fold = nullptr;
     size_t n_fold = 0;
     bool prepared = false;
+    double *eval_reg_acc = nullptr;      // pcp_model_evaluate: device accumulator the inference forward adds the feature T-Net's
+                                         // orthogonality regulariser to (per chunk, since R64 only exists chunk by chunk); null otherwise
     bool dev_newer = false;    // d_params was updated on the device (Adam) after the last host sync
     bool trainable[4] = {true, true, true, true};
     pcp::Workspace ws;
@@ -94,6 +96,8 @@ int model_eye3(float *d_R, int b, cudaStream_t st);
 int model_cls_head(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st);
 int heads_tc_prepare(pcp_model *m, const std::vector<float> &fold);
 void heads_tc_destroy(pcp_model *m);
+// 1e-3 * sum_b 1/2 ||I - M_b M_b^T||_F^2 of b (k x k) matrices added to *acc (train.cu; PointNet.py:447-451)
+int tnet_reg_accumulate(const float *M, int b, int k, double *acc, cudaStream_t st);
 int heads_tc_tnet_tail(pcp_model *m, int which, const float *pooled, int b, float *out, cudaStream_t st);
 int heads_tc_tnet_tail_fold(pcp_model *m, const float *pooled, int b, uint8_t *wc_img, float *r64_out, cudaStream_t st);
 int heads_tc_cls(pcp_model *m, const float *g3, int b, float *d_cls, float *d_cls_logits, cudaStream_t st);

@@ -529,6 +529,14 @@ tnet_reg_kernel(const float *__restrict__ Mx, int k, float *__restrict__ dM, dou
     }
 }
 
+int tnet_reg_accumulate(const float *M, int b, int k, double *acc, cudaStream_t st)
+{
+    if (b <= 0) return PCP_OK;
+    tnet_reg_kernel<<<b, k <= 8 ? 32 : 256, 2 * (size_t)k * k * sizeof(float), st>>>(M, k, nullptr, acc);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
 __global__ void axpy_kernel(float *__restrict__ y, const float *__restrict__ x, int64_t n, float a)
 {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] += a * x[i];
@@ -1406,8 +1414,13 @@ extern "C" int pcp_model_evaluate(pcp_model *m, const float *d_x, int b, int64_t
     float *seg_logits = R + (((size_t)b * 9 + 63) & ~(size_t)63);
     const bool want_seg = d_y_seg != nullptr;
     PCP_CUDA_OK(cudaMemsetAsync(met, 0, 64, st));
-    PCP_TRY(pcp_model_forward(m, d_x, b, n, PCP_HEAD_CLS | (want_seg ? PCP_HEAD_SEG : 0u), nullptr, nullptr, R, cls_logits,
-                              want_seg ? seg_logits : nullptr, stream));
+    // Keras' test_step runs the same forward as training, so the feature T-Net's add_loss is part of val_loss too: the
+    // inference forward adds it to met[3] wherever it has R64 in hand
+    m->eval_reg_acc = (!m->desc.vanilla && m->desc.regularize_feature_transform) ? met + 3 : nullptr;
+    const int frc = pcp_model_forward(m, d_x, b, n, PCP_HEAD_CLS | (want_seg ? PCP_HEAD_SEG : 0u), nullptr, nullptr, R, cls_logits,
+                                      want_seg ? seg_logits : nullptr, stream);
+    m->eval_reg_acc = nullptr;
+    if (frc != PCP_OK) return frc;
     if (d_y_cls) {
         softmax_ce_kernel<<<grid_for(b, 256, 1), 256, 0, st>>>(cls_logits, b, C, d_y_cls, 0.f, nullptr, nullptr, met + 0, met + 4);
         PCP_CHECK_LAUNCH();
