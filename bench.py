@@ -419,6 +419,18 @@ def main():
             extras["train_c3_weak"] = {"value": world * 256 / (ms_tw * 1e-3), "unit": "clouds/s", "ms_per_step": ms_tw, "global_batch": 256 * world,
                                        "precision": args.train_precision, "config": "C3 at 256 clouds per GPU (weak scaling)"}
             del xw, yw
+            # the same global-batch-256 step with sync-BN: every BatchNorm reduction summed over the ranks inside the step, i.e. the
+            # reference's single-device batch-256 step computed by N ranks (per-shard statistics above are the torch-DDP default)
+            tms = PointNet(C_CLASSES, P_PARTS, 0.3, 42, precision=args.train_precision)
+            tms.set_weights_dict(onp.make_params(C_CLASSES, P_PARTS, seed=7, trained_like=False))
+            tms.thaw_shared_network(); tms.thaw_input_transform(); tms.thaw_classification_head(); tms.freeze_segmentation_head()
+            tms.compile(optimizer=Kc.Adam(learning_rate=Kc.ExponentialDecay(1e-4, 7000, 0.7)),
+                        loss_weights={"classification_output": 1.0, "segmentation_output": 0.0, "se3": 0.0}, sync_bn=True)
+            ms_ts = timed(lambda i: tms.train_on_batch(ops.jitter(xt, (0.1, 0.1, 0.1), seed=i), yt, global_batch=tb * world, sample_offset=rank * tb), 5, 3)
+            extras["train_c3_syncbn"] = {"value": world * tb / (ms_ts * 1e-3), "unit": "clouds/s", "ms_per_step": ms_ts, "global_batch": tb * world,
+                                         "precision": args.train_precision,
+                                         "config": "C3 with sync-BN: BatchNorm sums all-reduced inside the step (one NCCL call per reduction, issued through a host callback)"}
+            del tms
         del tm, xt, yt
 
     if rank == 0 and not args.skip_extras:
