@@ -37,8 +37,17 @@ pool_colsum_kernel(const float *__restrict__ A, int64_t rows, double *__restrict
         add(v0); add(v1);
     }
     for (; r < rows; r += step) add(__ldg(A4 + r * 32 + c4));
-    atomicAdd(asum + c4 * 4, (double)acc.x); atomicAdd(asum + c4 * 4 + 1, (double)acc.y);
-    atomicAdd(asum + c4 * 4 + 2, (double)acc.z); atomicAdd(asum + c4 * 4 + 3, (double)acc.w);
+    // the eight row lanes of the block first (shared memory), then 128 atomics per block: 1024 per block on the same 128 words
+    // serialised in the L2 (0.17 ms per layer)
+    __shared__ float4 part[8][32];
+    part[lane][c4] = acc;
+    __syncthreads();
+    if (lane == 0) {
+        double sx = 0, sy = 0, sz = 0, sw = 0;
+#pragma unroll
+        for (int l = 0; l < 8; ++l) { const float4 v = part[l][c4]; sx += v.x; sy += v.y; sz += v.z; sw += v.w; }
+        atomicAdd(asum + c4 * 4, sx); atomicAdd(asum + c4 * 4 + 1, sy); atomicAdd(asum + c4 * 4 + 2, sz); atomicAdd(asum + c4 * 4 + 3, sw);
+    }
 }
 
 // column sums / sums of squares of Z = A.W from the Gram matrix: one warp per output channel
@@ -83,7 +92,8 @@ pool_select_kernel(const unsigned long long *__restrict__ emax, const unsigned l
 }
 
 // BN backward sums over the b selected rows of each channel and S = sc * dY
-// (32 channels x 8 cloud lanes per CTA)
+// (32 channels x 8 cloud lanes per CTA; the clouds are split over gridDim.y CTAs that add into the zeroed sums — as one CTA per 32
+//  channels the 32 dependent trips of three loads each took 100 us per layer)
 __global__ void __launch_bounds__(256)
 pool_bwd_coef_kernel(const float *__restrict__ g, const float *__restrict__ dg, const float *__restrict__ zsel, BnP p, int b, int cout,
                      double *__restrict__ s1o, double *__restrict__ s2o, float *__restrict__ S)
@@ -95,7 +105,7 @@ pool_bwd_coef_kernel(const float *__restrict__ g, const float *__restrict__ dg, 
     const float mean = ok ? p.mean[j] : 0.f, inv = ok ? p.inv[j] : 0.f, sc = ok ? p.sc[j] : 0.f;
     double s1 = 0, s2 = 0;
     if (ok)
-        for (int c = cl; c < b; c += 8) {
+        for (int c = blockIdx.y * 8 + cl; c < b; c += 8 * gridDim.y) {
             const size_t i = (size_t)c * cout + j;
             const float dy = g[i] > 0.f ? dg[i] : 0.f;
             s1 += dy;
@@ -106,7 +116,7 @@ pool_bwd_coef_kernel(const float *__restrict__ g, const float *__restrict__ dg, 
     __syncthreads();
     if (cl == 0 && ok) {
         for (int l = 1; l < 8; ++l) { s1 += sh1[l][jl]; s2 += sh2[l][jl]; }
-        s1o[j] = s1; s2o[j] = s2;
+        atomicAdd(s1o + j, s1); atomicAdd(s2o + j, s2);
     }
 }
 
@@ -190,9 +200,15 @@ pool_q_kernel(const float *__restrict__ Wt, const float *__restrict__ c0, const 
     for (int o = 16; o; o >>= 1) qk += __shfl_xor_sync(0xffffffffu, qk, o);
     if ((l & 31) == 0) part[l >> 5] = qk;
     __syncthreads();
-    float acc = 0.f;
-    for (int j = 0; j < cout; ++j) acc = fmaf(sk[j], __ldg(Wt + (size_t)j * 128 + l), acc);
-    Q[k * 128 + l] = acc;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;          // independent chains: the loop is load-latency bound
+    int j = 0;
+#pragma unroll 2
+    for (; j + 3 < cout; j += 4) {
+        a0 = fmaf(sk[j], __ldg(Wt + (size_t)j * 128 + l), a0); a1 = fmaf(sk[j + 1], __ldg(Wt + (size_t)(j + 1) * 128 + l), a1);
+        a2 = fmaf(sk[j + 2], __ldg(Wt + (size_t)(j + 2) * 128 + l), a2); a3 = fmaf(sk[j + 3], __ldg(Wt + (size_t)(j + 3) * 128 + l), a3);
+    }
+    for (; j < cout; ++j) a0 = fmaf(sk[j], __ldg(Wt + (size_t)j * 128 + l), a0);
+    Q[k * 128 + l] = (a0 + a1) + (a2 + a3);
     if (l == 0) q[k] = part[0] + part[1] + part[2] + part[3];
 }
 
@@ -201,11 +217,21 @@ __global__ void __launch_bounds__(128)
 pool_scatter_kernel(const float *__restrict__ S, const int *__restrict__ arg, const float *__restrict__ Wt, int64_t n, int cout, int jchunk,
                     float *__restrict__ dA)
 {
-    const int k = threadIdx.x, c = blockIdx.y, j0 = blockIdx.x * jchunk;
-    for (int j = j0; j < min(cout, j0 + jchunk); ++j) {
-        const size_t i = (size_t)c * cout + j;
-        const float s = __ldg(S + i);
-        if (s != 0.f) atomicAdd(dA + ((int64_t)c * n + __ldg(arg + i)) * 128 + k, s * __ldg(Wt + (size_t)j * 128 + k));
+    const int k = threadIdx.x, c = blockIdx.y, j0 = blockIdx.x * jchunk, j1 = min(cout, j0 + jchunk);
+    for (int j = j0; j < j1; j += 8) {               // eight channels' loads in flight: one dependent S -> arg -> Wt chain per channel was 46 us per layer
+        float s[8], w[8];
+        int r[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const bool in = j + e < j1;
+            const size_t i = (size_t)c * cout + j + e;
+            s[e] = in ? __ldg(S + i) : 0.f;
+            r[e] = in ? __ldg(arg + i) : 0;
+            w[e] = in ? __ldg(Wt + (size_t)(j + e) * 128 + k) : 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+            if (s[e] != 0.f) atomicAdd(dA + ((int64_t)c * n + r[e]) * 128 + k, s[e] * w[e]);
     }
 }
 
@@ -262,7 +288,9 @@ static int pooled_backward(const PoolLayer &L, const float *A, const float *g, c
                            cudaStream_t st)
 {
     const int64_t rows = (int64_t)L.b * L.n;
-    pool_bwd_coef_kernel<<<(L.cout + 31) / 32, 256, 0, st>>>(g, dg, L.pb.zsel, L.bnp(), L.b, L.cout, L.red, L.red + L.cout, L.pb.S);
+    PCP_CUDA_OK(cudaMemsetAsync(L.red, 0, (size_t)L.cout * 16, st));
+    pool_bwd_coef_kernel<<<dim3((L.cout + 31) / 32, (unsigned)std::max(1, std::min(32, (L.b + 7) / 8))), 256, 0, st>>>(g, dg, L.pb.zsel, L.bnp(), L.b, L.cout,
+                                                                                                                  L.red, L.red + L.cout, L.pb.S);
     PCP_CHECK_LAUNCH();
     if (L.batch && L.trainable && dgamma && dbeta) {          // this rank's sums: the gradient bucket is summed over the ranks later
         store_bn_grads_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(L.red, L.red + L.cout, L.cout, dgamma, dbeta);
