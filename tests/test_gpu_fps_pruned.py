@@ -51,6 +51,7 @@ def make(kind, b, n):
 @pytest.mark.parametrize("kind,b,n,s,start", [
     ("lidar", 40, 100_000, 256, 0), ("lidar", 64, 70_001, 128, 77), ("lidar", 150, 13_000, 128, 5), ("dup", 40, 90_001, 200, 3),
     ("lattice", 40, 60_000, 300, 0), ("same", 40, 52_000, 40, 5), ("offset", 40, 100_000, 128, 0), ("line", 40, 75_000, 128, 1),
+    ("dup", 40, 40_000, 64, 0), ("lidar", 10, 120_000, 64, 2),          # clusters of 2 and of 8 blocks (the others: 1 and 4)
 ])
 def test_pruned_fps_matches_plain_kernel_and_oracle(lib, oracle_c, kind, b, n, s, start):
     from pointcloudprocessing_b200 import ops
