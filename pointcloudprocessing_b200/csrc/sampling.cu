@@ -805,6 +805,267 @@ fps_pruned_kernel(const int32_t *__restrict__ perm, const float *__restrict__ xo
     cluster.sync();     // no block may exit while a peer can still write into its slots
 }
 
+// ------------------------------------------------------------------------------------------------------------------------------
+// LEAN pruned variant: only the running DISTANCES stay on chip.  With pruning ~9 % of the groups need their coordinates in an
+// iteration, so the coordinates can live in an L2-resident copy (per thread row-major in 16-byte chunks [group][chunk][tid]: a group
+// is six coalesced LDG.128) and a block only has to hold 4 bytes per point — 98 rows of 512 distances in shared memory = 50 176
+// points per block.  A 100 000-point cloud then fits in a cluster of TWO, 64 clouds are 128 blocks = ONE wave on 148 SMs instead of
+// the two waves of the register / shared-memory resident kernels, and the whole kernel is generic code (no register-resident rows
+// to unroll over): the loop body is a few KB.  Same skip test, same keys, same exchange and tie path as fps_pruned_kernel.
+constexpr int kLeanMaxGroups = 14;                    // 14 x 7 rows x 512 x 4 B = 200 704 B of distances
+constexpr int kLeanChunks = 6;                        // 7 rows x 3 floats = 21 (+ 3 padding) floats = 6 float4 per thread and group
+
+__device__ __forceinline__ unsigned fps_lean_id(bool multi, int warp, int g, int j, int lane)
+{
+    return 0x80000000u | (multi ? 0x40000000u : 0u) | ((unsigned)warp << 12) | ((unsigned)g << 8) | ((unsigned)j << 5) | (unsigned)lane;
+}
+
+template <int CS, bool kProf>
+__global__ void __launch_bounds__(kFpsThreads, 1)
+fps_lean_kernel(const int32_t *__restrict__ perm, const float *__restrict__ xorig, float4 *__restrict__ coords, int64_t n, int s, int start,
+                int32_t *__restrict__ idx_out, int ngroups, int dbg)
+{
+    constexpr int cs = CS;
+    constexpr int nrec = CS * kFpsWarps;
+    constexpr int kSlots = nrec < 32 ? 32 : nrec;
+    constexpr int kPerLane = nrec <= 32 ? 1 : nrec / 32;
+    extern __shared__ __align__(16) float fps_dsm[];              // running distances [ngroups * 7][512]
+    __shared__ float4 slots[2][kSlots], tslots[2][kSlots];
+    __shared__ uint64_t xbar[2], tbar[2];
+
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank();
+    const int64_t cloud = blockIdx.x / cs;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float *xo = xorig + cloud * n * 3;
+    const int32_t *pc = perm + cloud * n;
+    float4 *cb = coords + (size_t)blockIdx.x * ngroups * kLeanChunks * kFpsThreads + tid;      // this thread's chunk c of group g: cb[(g * 6 + c) * 512]
+    // group slot g of this warp holds sorted group ((g * 16 + warp) * cs + rank): 224 consecutive sorted points, dealt round-robin
+    auto gpos = [&](int g, int j) -> int64_t { return ((int64_t)((g * kFpsWarps + warp) * cs + rank) * kFpsGroupRows + j) * 32 + lane; };
+    auto real_rows = [&](int g) -> unsigned {      // bit j: row j of group g is a point of the cloud (rows fill up in order)
+        const int64_t left = n - gpos(g, 0);
+        const int cnt = left <= 0 ? 0 : (int)min((int64_t)kFpsGroupRows, (left + 31) / 32);
+        return (1u << cnt) - 1u;
+    };
+
+    // ---- set-up: gather the points through the permutation, write the coordinate copy, clear the distances, bounding spheres
+    float scx = 0.f, scy = 0.f, scz = 0.f, srad = 0.f, sthr = -1.f;      // lane g: sphere of group g; thr -1: always skipped
+    float gx = 0.f, gy = 0.f, gz = 0.f;                                   // lane g: coordinates of the point behind the group's key
+    unsigned khi = 0u, klo = 0u;                                          // lane g: key of group g (klo: fps_lean_id, 0 = no point)
+    for (int g = 0; g < ngroups; ++g) {
+        const unsigned mine = real_rows(g);
+        float f[24];
+#pragma unroll
+        for (int j = 0; j < kFpsGroupRows; ++j) {
+            const bool real = (mine >> j) & 1u;
+            const int64_t o = real ? (int64_t)__ldg(pc + gpos(g, j)) : 0;
+            f[3 * j] = real ? __ldg(xo + 3 * o) : 0.f; f[3 * j + 1] = real ? __ldg(xo + 3 * o + 1) : 0.f; f[3 * j + 2] = real ? __ldg(xo + 3 * o + 2) : 0.f;
+            fps_dsm[(g * kFpsGroupRows + j) * kFpsThreads + tid] = real ? __int_as_float(0x7f800000) : 0.f;
+        }
+        f[21] = f[22] = f[23] = 0.f;
+#pragma unroll
+        for (int c = 0; c < kLeanChunks; ++c) cb[(size_t)(g * kLeanChunks + c) * kFpsThreads] = make_float4(f[4 * c], f[4 * c + 1], f[4 * c + 2], f[4 * c + 3]);
+        float ax = 0.f, ay = 0.f, az = 0.f, cnt = 0.f;
+#pragma unroll
+        for (int j = 0; j < kFpsGroupRows; ++j)
+            if ((mine >> j) & 1u) { ax += f[3 * j]; ay += f[3 * j + 1]; az += f[3 * j + 2]; cnt += 1.f; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            ax += __shfl_xor_sync(0xffffffffu, ax, o); ay += __shfl_xor_sync(0xffffffffu, ay, o);
+            az += __shfl_xor_sync(0xffffffffu, az, o); cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        }
+        const float ic = cnt > 0.f ? 1.f / cnt : 0.f;
+        const float mx = ax * ic, my = ay * ic, mz = az * ic;
+        float r2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < kFpsGroupRows; ++j)
+            if ((mine >> j) & 1u)
+                r2 = fmaxf(r2, (f[3 * j] - mx) * (f[3 * j] - mx) + (f[3 * j + 1] - my) * (f[3 * j + 1] - my) + (f[3 * j + 2] - mz) * (f[3 * j + 2] - mz));
+        r2 = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(r2)));
+        if (lane == g) {
+            scx = mx; scy = my; scz = mz;
+            srad = sqrtf(r2) * 1.0001f + 1e-30f;
+            sthr = cnt > 0.f ? __int_as_float(0x7f800000) : -1.f;      // a populated group is never skipped before its first update
+        }
+    }
+    float cx = __ldg(xo + 3 * (int64_t)start), cy = __ldg(xo + 3 * (int64_t)start + 1), cz = __ldg(xo + 3 * (int64_t)start + 2);
+    if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
+    if (tid < kSlots) {
+        slots[0][tid] = make_float4(0.f, 0.f, 0.f, 0.f); slots[1][tid] = slots[0][tid];
+        tslots[0][tid] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0xFFFFFFFFu)); tslots[1][tid] = tslots[0][tid];
+    }
+    if (tid == 0) {
+        umma::mbar_init(&xbar[0], 1); umma::mbar_init(&xbar[1], 1); umma::mbar_init(&tbar[0], 1); umma::mbar_init(&tbar[1], 1);
+        umma::fence_barrier_init();
+    }
+    __syncthreads();       // (also: this thread's coordinate copy is only ever read back by itself)
+    if (tid == 0) {
+        umma::mbar_arrive_expect_tx(&xbar[0], nrec * 16u); umma::mbar_arrive_expect_tx(&xbar[1], nrec * 16u);
+        umma::mbar_arrive_expect_tx(&tbar[0], nrec * 16u); umma::mbar_arrive_expect_tx(&tbar[1], nrec * 16u);
+    }
+    cluster.sync();                              // every block is armed before anybody pushes
+    long long ph[6] = {0, 0, 0, 0, 0, 0}, tprev = clock64();
+    unsigned long long nact = 0, nties = 0;
+    unsigned ntie = 0u;                          // tie iterations so far (identical in every warp of the cluster)
+    unsigned wcode = 0u, wlo = 0u;               // this warp's record (warp-uniform)
+    float wx = 0.f, wy = 0.f, wz = 0.f;
+    auto load_group = [&](float4 (&c)[kLeanChunks], int g) {      // plain loads: the copy was written by this kernel
+#pragma unroll
+        for (int k = 0; k < kLeanChunks; ++k) c[k] = cb[(size_t)(g * kLeanChunks + k) * kFpsThreads];
+    };
+    for (int it = 1; it < s; ++it) {
+        const float tdx = cx - scx, tdy = cy - scy, tdz = cz - scz;
+        unsigned act = __ballot_sync(0xffffffffu, !(tdx * tdx + tdy * tdy + tdz * tdz > sthr));
+        if (dbg == 1 && it > 1) act = 0u;            // development: exchange only (results wrong)
+        if (act) {
+            unsigned rem = act;
+            int g = __ffs(rem) - 1;
+            rem &= rem - 1u;
+            float4 c[kLeanChunks];
+            load_group(c, g);
+            while (true) {
+                // the next active group's coordinates are in flight while this one is updated
+                const int gn = rem ? __ffs(rem) - 1 : -1;
+                float4 cn[kLeanChunks];
+                if (gn >= 0) { rem &= rem - 1u; load_group(cn, gn); }
+                if (kProf) ++nact;
+                const float f[24] = {c[0].x, c[0].y, c[0].z, c[0].w, c[1].x, c[1].y, c[1].z, c[1].w, c[2].x, c[2].y, c[2].z, c[2].w,
+                                     c[3].x, c[3].y, c[3].z, c[3].w, c[4].x, c[4].y, c[4].z, c[4].w, c[5].x, c[5].y, c[5].z, c[5].w};
+                float *dg = fps_dsm + (size_t)g * kFpsGroupRows * kFpsThreads + tid;
+                float m[kFpsGroupRows], lbv = -1.f;
+#pragma unroll
+                for (int j = 0; j < kFpsGroupRows; ++j) {
+                    m[j] = fminf(dg[j * kFpsThreads], sqdist_nofma(f[3 * j], f[3 * j + 1], f[3 * j + 2], cx, cy, cz));
+                    dg[j * kFpsThreads] = m[j];
+                    lbv = fmaxf(lbv, m[j]);
+                }
+                // the group's maximum over its REAL points (padding rows hold 0 and never raise it), the first point that attains it,
+                // whether it is alone, and that point's coordinates (kept with the key: a later record needs no fetch)
+                const unsigned mine = real_rows(g);
+                const unsigned gm = __reduce_max_sync(0xffffffffu, mine ? __float_as_uint(lbv) : 0u);
+                unsigned at = 0u;
+#pragma unroll
+                for (int j = 0; j < kFpsGroupRows; ++j)
+                    if (__float_as_uint(m[j]) == gm) at |= 1u << j;
+                at &= mine;
+                const unsigned lanes_at = __ballot_sync(0xffffffffu, at != 0u);
+                const unsigned multi_l = __ballot_sync(0xffffffffu, (at & (at - 1u)) != 0u);
+                const int ol = lanes_at ? __ffs(lanes_at) - 1 : 0;
+                const unsigned oat = __shfl_sync(0xffffffffu, at, ol);
+                const int oj = oat ? __ffs(oat) - 1 : 0;
+                float ox = 0.f, oy = 0.f, oz = 0.f;
+#pragma unroll
+                for (int j = 0; j < kFpsGroupRows; ++j)
+                    if (j == oj) { ox = f[3 * j]; oy = f[3 * j + 1]; oz = f[3 * j + 2]; }
+                ox = __shfl_sync(0xffffffffu, ox, ol); oy = __shfl_sync(0xffffffffu, oy, ol); oz = __shfl_sync(0xffffffffu, oz, ol);
+                if (lane == g) {
+                    khi = gm;
+                    klo = lanes_at ? fps_lean_id((lanes_at & (lanes_at - 1u)) != 0u || multi_l != 0u, warp, g, oj, ol) : 0u;
+                    sthr = lanes_at ? fps_skip_threshold(srad, __uint_as_float(gm)) : -1.f;
+                    gx = ox; gy = oy; gz = oz;
+                }
+                if (gn < 0) break;
+                g = gn;
+#pragma unroll
+                for (int k = 0; k < kLeanChunks; ++k) c[k] = cn[k];
+            }
+            // the warp's record: its best group's key and that point's coordinates
+            int sel; bool multi;
+            const unsigned whi = fps_key_max(khi, klo, sel, multi);
+            wlo = sel < 0 ? 0u : __shfl_sync(0xffffffffu, klo, sel);
+            wcode = sel < 0 ? 0u : (whi + 1u) | (multi ? 0x80000000u : 0u);
+            const int ss = sel < 0 ? 0 : sel;
+            wx = __shfl_sync(0xffffffffu, gx, ss); wy = __shfl_sync(0xffffffffu, gy, ss); wz = __shfl_sync(0xffffffffu, gz, ss);
+        }
+        FPS_STAMP(0);
+        const int par = it & 1;
+        if (lane < cs)       // lane t -> block t of the cluster: data and its arrival in one remote operation
+            fps_st_async16(&slots[par][rank * kFpsWarps + warp], &xbar[par], (uint32_t)lane, __float_as_uint(wx), __float_as_uint(wy),
+                           __float_as_uint(wz), wcode);
+        FPS_STAMP(3);
+        fps_wait_records(&xbar[par], ((unsigned)(it - 1) >> 1) & 1u);
+        if (tid == 0 && it + 2 < s) umma::mbar_arrive_expect_tx(&xbar[par], nrec * 16u);      // re-arm for iteration it + 2
+        FPS_STAMP(4);
+        // every warp reduces the records itself
+        float4 rc[kPerLane];
+#pragma unroll
+        for (int e = 0; e < kPerLane; ++e) rc[e] = slots[par][lane + 32 * e];
+        float4 brec = rc[0];
+        unsigned bcode = __float_as_uint(rc[0].w), bi = (unsigned)lane;
+#pragma unroll
+        for (int e = 1; e < kPerLane; ++e) {
+            const unsigned cc = __float_as_uint(rc[e].w);
+            if ((cc & 0x7FFFFFFFu) > (bcode & 0x7FFFFFFFu)) { brec = rc[e]; bcode = cc; bi = (unsigned)(lane + 32 * e); }
+            else if (cc != 0u && (cc & 0x7FFFFFFFu) == (bcode & 0x7FFFFFFFu)) bcode |= 0x80000000u;
+        }
+        const unsigned cmax = __reduce_max_sync(0xffffffffu, bcode & 0x7FFFFFFFu);       // > 0: the cloud has points
+        const unsigned eq = __ballot_sync(0xffffffffu, (bcode & 0x7FFFFFFFu) == cmax && bcode != 0u);
+        const int sl = __ffs(eq) - 1;
+        const bool tie = (eq & (eq - 1u)) != 0u || (__shfl_sync(0xffffffffu, bcode, sl) & 0x80000000u) != 0u;
+        const unsigned dmax = cmax - 1u;
+        if (!tie) {
+            cx = __shfl_sync(0xffffffffu, brec.x, sl); cy = __shfl_sync(0xffffffffu, brec.y, sl); cz = __shfl_sync(0xffffffffu, brec.z, sl);
+            const int wi = (int)__shfl_sync(0xffffffffu, bi, sl);
+            // the one thread that holds the winner translates its sorted position (a load that nothing in the loop waits for)
+            if (wi == rank * kFpsWarps + warp && lane == (int)(wlo & 31u))
+                idx_out[cloud * s + it] = __ldg(pc + gpos((int)((wlo >> 8) & 15u), (int)((wlo >> 5) & 7u)));
+        } else {
+            // several points share the largest distance: np.argmax takes the lowest original index
+            if (kProf) ++nties;
+            unsigned cand = 0xFFFFFFFFu;
+            int cg_ = 0, cj = 0;
+            unsigned gat = __ballot_sync(0xffffffffu, klo != 0u && khi == dmax);      // groups of this warp at the maximum
+            while (gat) {
+                const int g = __ffs(gat) - 1;
+                gat &= gat - 1u;
+                const unsigned mine = real_rows(g);
+                for (int j = 0; j < kFpsGroupRows; ++j)
+                    if (((mine >> j) & 1u) && __float_as_uint(fps_dsm[(size_t)(g * kFpsGroupRows + j) * kFpsThreads + tid]) == dmax) {
+                        const unsigned o = (unsigned)__ldg(pc + gpos(g, j));
+                        if (o < cand) { cand = o; cg_ = g; cj = j; }
+                    }
+            }
+            const unsigned wmin = __reduce_min_sync(0xffffffffu, cand);
+            float rx = 0.f, ry = 0.f, rz = 0.f;
+            const unsigned who = __ballot_sync(0xffffffffu, wmin != 0xFFFFFFFFu && cand == wmin);
+            const int ol = who ? __ffs(who) - 1 : 0;
+            if (who && lane == ol) {
+                const float *fb = reinterpret_cast<const float *>(cb);
+                auto comp = [&](int q) { return fb[((size_t)(cg_ * kLeanChunks + (q >> 2)) * kFpsThreads) * 4 + (q & 3)]; };
+                rx = comp(3 * cj); ry = comp(3 * cj + 1); rz = comp(3 * cj + 2);
+            }
+            rx = __shfl_sync(0xffffffffu, rx, ol); ry = __shfl_sync(0xffffffffu, ry, ol); rz = __shfl_sync(0xffffffffu, rz, ol);
+            const int tpar = (int)(ntie & 1u);
+            if (lane < cs)
+                fps_st_async16(&tslots[tpar][rank * kFpsWarps + warp], &tbar[tpar], (uint32_t)lane, __float_as_uint(rx), __float_as_uint(ry),
+                               __float_as_uint(rz), wmin);
+            fps_wait_records(&tbar[tpar], (ntie >> 1) & 1u);
+            if (tid == 0) umma::mbar_arrive_expect_tx(&tbar[tpar], nrec * 16u);
+            ++ntie;
+            float4 tr[kPerLane];
+#pragma unroll
+            for (int e = 0; e < kPerLane; ++e) tr[e] = tslots[tpar][lane + 32 * e];
+            float4 tb4 = tr[0];
+#pragma unroll
+            for (int e = 1; e < kPerLane; ++e)
+                if (__float_as_uint(tr[e].w) < __float_as_uint(tb4.w)) tb4 = tr[e];
+            const unsigned tmin = __reduce_min_sync(0xffffffffu, __float_as_uint(tb4.w));
+            const int tb = __ffs(__ballot_sync(0xffffffffu, __float_as_uint(tb4.w) == tmin)) - 1;
+            cx = __shfl_sync(0xffffffffu, tb4.x, tb); cy = __shfl_sync(0xffffffffu, tb4.y, tb); cz = __shfl_sync(0xffffffffu, tb4.z, tb);
+            if (rank == 0 && tid == 0) idx_out[cloud * s + it] = (int32_t)tmin;
+        }
+        FPS_STAMP(5);
+    }
+    if (kProf) {
+        if (blockIdx.x == 0 && lane == 0) atomicAdd(&g_fps_phase[6], nact);
+        if (blockIdx.x == 0 && tid == 0) {
+            for (int i = 0; i < 6; ++i) g_fps_phase[i] = (unsigned long long)ph[i];
+            g_fps_phase[7] = nties;
+        }
+    }
+    cluster.sync();     // no block may exit while a peer can still write into its slots
+}
+
 // Fallback for clouds too large to stay register-resident: one CTA per cloud, running distances in
 // a global scratch array (L2-resident for realistic sizes).  Same arithmetic and tie-break.
 __global__ void __launch_bounds__(1024, 1)
@@ -895,7 +1156,8 @@ static int fps_plain(const float *d_x, int b, int64_t n, int s, int start, int32
 // ---- pruned path: geometry, workspace layout and launch
 struct FpsPrunePlan {
     int cs = 0, ngroups = 0;
-    size_t off_perm = 0, off_hist = 0, off_bbox = 0, bytes = 0;
+    bool lean = false;                   // fps_lean_kernel (distances only on chip) instead of fps_pruned_kernel
+    size_t off_perm = 0, off_hist = 0, off_bbox = 0, off_coords = 0, bytes = 0;
 };
 
 static bool fps_prune_plan(int b, int64_t n, int s, FpsPrunePlan &pl)
@@ -907,22 +1169,30 @@ static bool fps_prune_plan(int b, int64_t n, int s, FpsPrunePlan &pl)
     constexpr int rows_max = kFpsPruneReg + kFpsPruneSm;
     int cs = 1;
     while (cs <= kFpsPruneMaxCluster && n > (int64_t)cs * kFpsThreads * rows_max) cs *= 2;
-    if (cs > kFpsPruneMaxCluster) return false;
+    // the lean kernel wherever the cloud's distances fit a cluster of <= 8 blocks (50 176 points per block); PCP_FPS_PRUNE_V1 keeps
+    // the coordinate-resident kernel for comparison
+    static const bool v1 = getenv("PCP_FPS_PRUNE_V1") != nullptr;
+    int csl = 1;
+    while (csl <= kFpsPruneMaxCluster && n > (int64_t)csl * kLeanMaxGroups * kFpsWarps * kFpsGroupRows * 32) csl *= 2;
+    pl.lean = !v1 && csl <= kFpsPruneMaxCluster;
+    if (!pl.lean && cs > kFpsPruneMaxCluster) return false;
     // only where the register-resident clusters (25 rows per block) would not all be resident at once — the batch sizes the
     // hybrid kernel was built for; a few clouds are faster spread over wide clusters
     int cs_reg = 1;
     while (cs_reg < kFpsMaxCluster && n > (int64_t)cs_reg * kFpsThreads * 25) cs_reg *= 2;
     static const bool force = getenv("PCP_FPS_FORCE_PRUNE") != nullptr;
     if (!force && (int64_t)b * cs_reg <= sm_count()) return false;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    if (pl.lean) cs = csl;
     const int64_t per_group = (int64_t)cs * kFpsWarps * kFpsGroupRows * 32;      // points one group slot holds across the cluster
     const int ngroups = (int)((n + per_group - 1) / per_group);
-    if (ngroups < 3) return false;                               // small clouds: the register-only kernel, nothing to prune at 1-2 ms
-    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    if (!pl.lean && ngroups < 3) return false;                   // small clouds: the register-only kernel, nothing to prune at 1-2 ms
     pl.cs = cs; pl.ngroups = ngroups;
     pl.off_perm = 0;
     pl.off_hist = pl.off_perm + up((size_t)b * n * sizeof(int32_t));
     pl.off_bbox = pl.off_hist + up((size_t)b * kFpsSortBins * sizeof(int));
-    pl.bytes = pl.off_bbox + up((size_t)b * 6 * sizeof(unsigned));
+    pl.off_coords = pl.off_bbox + up((size_t)b * 6 * sizeof(unsigned));
+    pl.bytes = pl.off_coords + (pl.lean ? up((size_t)b * cs * ngroups * kLeanChunks * kFpsThreads * sizeof(float4)) : 0);
     return true;
 }
 
@@ -950,6 +1220,33 @@ static int launch_fps_pruned_cs(const int32_t *perm, const float *d_x, int b, in
     attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, perm, d_x, n, s, start, d_idx, pl.ngroups, dbg));
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+template <int CS, bool kProf>
+static int launch_fps_lean_cs(const int32_t *perm, const float *d_x, float4 *coords, int b, int64_t n, int s, int start, int32_t *d_idx,
+                              const FpsPrunePlan &pl, int dbg, cudaStream_t st)
+{
+    auto kern = fps_lean_kernel<CS, kProf>;
+    static bool attr_set_dev[64] = {};      // per device (per template instance)
+    const int dev = fps_device();
+    PCP_REQUIRE(dev >= 0, PCP_ERR_CUDA, "fps: no current device");
+    if (!attr_set_dev[dev]) {
+        PCP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        PCP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kLeanMaxGroups * kFpsGroupRows * kFpsThreads * 4));
+        attr_set_dev[dev] = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((int64_t)b * CS));
+    cfg.blockDim = dim3(kFpsThreads);
+    cfg.dynamicSmemBytes = (size_t)pl.ngroups * kFpsGroupRows * kFpsThreads * 4;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, perm, d_x, coords, n, s, start, d_idx, pl.ngroups, dbg));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -988,6 +1285,15 @@ static int launch_fps_pruned(const float *d_x, int b, int64_t n, int s, int star
 
     static const int dbg = getenv("PCP_FPS_PRUNE_DBG") ? atoi(getenv("PCP_FPS_PRUNE_DBG")) : 0;      // development (see the kernel)
     if (dbg == 2) return PCP_OK;                     // development: the sort alone
+    if (pl.lean) {
+        float4 *coords = reinterpret_cast<float4 *>(base + pl.off_coords);
+        switch (pl.cs) {
+        case 1: return launch_fps_lean_cs<1, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
+        case 2: return launch_fps_lean_cs<2, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
+        case 4: return launch_fps_lean_cs<4, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
+        default: return launch_fps_lean_cs<8, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
+        }
+    }
     switch (pl.cs) {
     case 1: return launch_fps_pruned_cs<1, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
     case 2: return launch_fps_pruned_cs<2, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
