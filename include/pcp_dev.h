@@ -13,8 +13,6 @@ extern "C" {
 /* Development aid: cycles block 0 / thread 0 of the last pcp_fps_f32 launch made under PCP_FPS_PROF=1 (25 points per
  * thread) spent in: distance loop, warp keys, __syncthreads, push, exchange wait, read-back (scripts/fps_phases.py). */
 int pcp_fps_phase_cycles(unsigned long long out[8]);
-/* per-warp clock64 timeline of block 0 over 16 iterations of the last PCP_FPS_PROF=1 pruned launch: [16][16 warps][6 stamps] */
-int pcp_fps_trace(long long *out, int count);
 
 /* Tensor-core self-test (used by tests only): D (128 x N) = A (128 x K) . B (N x K)^T through one
  * tcgen05.mma chain with bf16-rounded operands; validates the shared-memory operand image, the

@@ -76,7 +76,6 @@ SIGNATURES = {
     "pcp_fps_f32": (_i32, [_vp, _i32, _i64, _i32, _i32, _vp, _vp]),
     "pcp_fps_workspace_bytes": (_i32, [_i32, _i64, _i32, C.POINTER(_sz)]),
     "pcp_fps_ws_f32": (_i32, [_vp, _i32, _i64, _i32, _i32, _vp, _vp, _sz, _vp]),
-    "pcp_fps_trace": (_i32, [C.POINTER(C.c_longlong), _i32]),
     "pcp_fps_phase_cycles": (_i32, [C.POINTER(C.c_ulonglong)]),
     "pcp_gather_points_f32": (_i32, [_vp, _vp, _i32, _i64, _vp, _i32, _vp, _vp, _vp]),
     "pcp_voxel_workspace_bytes": (_i32, [_i32, _i64, C.POINTER(_sz)]),

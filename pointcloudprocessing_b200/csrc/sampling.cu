@@ -12,7 +12,7 @@
 // Exclusive use of the device is assumed: CTAs of a cluster wait for their peers' records (bounded: a lost arrival traps).
 //
 // Round 2 adds the PRUNED variant behind pcp_fps_ws_f32 (caller-owned workspace): the same samples with ~90 % of the distance
-// updates skipped — Morton-ordered cloud, per-group bounding spheres, warp-uniform skip; see the comment above fps_pruned_kernel.
+// updates skipped — Morton-ordered cloud, per-group bounding spheres, warp-uniform skip; see the comment above fps_lean_kernel.
 #include <cooperative_groups.h>
 
 #include <algorithm>
@@ -122,10 +122,6 @@ __device__ __forceinline__ unsigned fps_winner(const FpsSide &S, int par, int cs
 
 // phase cycle totals of block 0 / thread 0 (development aid, read through pcp_fps_phase_cycles)
 __device__ unsigned long long g_fps_phase[8];
-// per-warp timeline of block 0, iterations [kFpsTraceIt0, kFpsTraceIt0 + 16): [it][warp][stamp] clock64 (PCP_FPS_PROF builds)
-constexpr int kFpsTraceIt0 = 600;
-__device__ long long g_fps_trace[16][kFpsWarps][6];
-#define FPS_TRACE(i) do { if (kProf && blockIdx.x == 0 && lane == 0 && it >= kFpsTraceIt0 && it < kFpsTraceIt0 + 16) g_fps_trace[it - kFpsTraceIt0][warp][i] = clock64(); } while (0)
 #define FPS_STAMP(i) do { if (kProf && blockIdx.x == 0 && tid == 0) { const long long t_ = clock64(); ph[i] += t_ - tprev; tprev = t_; } } while (0)
 
 template <int PPT, bool kProf, int SD = 0>
@@ -274,16 +270,18 @@ fps_cluster_kernel(const float *__restrict__ x, int64_t n, int s, int start, int
 }
 
 // ------------------------------------------------------------------------------------------------------------------------------
-// PRUNED variant (round 2).  The distance update of an iteration only changes points closer to the new sample than their running
-// minimum; late in the chain that is a small neighbourhood.  The cloud is first put in Morton order of a coarse grid (a counting
-// sort, fps_sort_* below) and every warp keeps a CONTIGUOUS run of the sorted cloud: rowsT rows of 32 points, split in groups of
-// kFpsGroupRows rows (224 points).  Per group the block keeps a bounding sphere and the group's largest running distance; a group
-// (and, one level up, a whole warp) whose sphere is farther from the new sample than sqrt(that distance) cannot change and is
-// skipped by a warp-uniform branch.  Skipping is conservative (1e-4 relative slack against fp32 rounding of the test itself) and
-// an updated group runs exactly the arithmetic of the unpruned kernel, so the samples stay bit-identical with the oracle; ties go to
-// the lowest ORIGINAL index, looked up in the sort's permutation only for the points that attain a group's maximum.
-constexpr int kFpsGroupRows = 7, kFpsGroups = 7;      // 7 x 7 = 49 rows = kFpsPruneReg + kFpsPruneSm
-constexpr int kFpsPruneReg = 13, kFpsPruneSm = 36;    // rows with the coordinates in registers / in shared memory (36 * 512 * 12 B = 216 KB)
+// PRUNED sampler (round 2; fps_lean_kernel below).  The distance update of an iteration only changes points closer to the new
+// sample than their running minimum; late in the chain that is a small neighbourhood.  The cloud is first put in Morton order of a
+// coarse grid (a counting sort, fps_sort_* below, which only produces the permutation) and cut into groups of kFpsGroupRows rows of 32
+// = 224 consecutive sorted points, dealt round-robin over the blocks of the cluster and their warps.  Per group: a bounding sphere
+// and the group's largest running distance; a group whose sphere is farther from the new sample than sqrt(that distance) cannot
+// change and is skipped by a warp-uniform branch.  Skipping is conservative (1e-4 relative slack against fp32 rounding of the test
+// itself) and an updated group runs exactly the arithmetic of the unpruned kernel, so the samples stay bit-identical with the oracle;
+// keys inside the kernel carry a block-local id and an exact "several points attain this maximum" flag, and only when the
+// cluster-wide maximum is shared does an iteration fall back to the lowest ORIGINAL index through the permutation.
+// (History: a first version kept the coordinates on chip — 13 rows in registers, 36 in shared memory, clusters of four, two waves
+//  for 64 clouds: 3.26 ms; measurements of every step in profiles/r02_fps_pruned.txt.)
+constexpr int kFpsGroupRows = 7;                      // rows of 32 points per group
 constexpr int kFpsSortBits = 5;                       // grid of 32^3 cells over the cloud's bounding cube
 constexpr int kFpsSortBins = 1 << (3 * kFpsSortBits);
 
@@ -435,14 +433,6 @@ fps_sort_scan_kernel(int *__restrict__ hist)
     }
 }
 
-// low word of a key inside a block: bit 31 = a real point stands behind it, bit 30 = more than one point attains the value,
-// then warp | group | row | lane of the (first) point.  Uniqueness across the cluster is what the high word decides; whenever it does
-// not (two keys with the same distance, or bit 30), the iteration falls back to the original indices (np.argmax: lowest wins).
-__device__ __forceinline__ unsigned fps_local_id(bool multi, int warp, int g, int row, int lane)
-{
-    return 0x80000000u | (multi ? 0x40000000u : 0u) | ((unsigned)warp << 14) | ((unsigned)g << 11) | ((unsigned)row << 5) | (unsigned)lane;
-}
-
 __device__ __forceinline__ float fps_skip_threshold(float rad_inflated, float dmax)
 {   // skip when |q - c|^2 (fp32, any rounding) > thr: then every point of the sphere is farther from q than sqrt(dmax).
     // sqrt.approx is within a few ulp — far inside the 1e-4 slack
@@ -464,15 +454,11 @@ __device__ __forceinline__ unsigned fps_key_max(unsigned hi, unsigned lo, int &s
     return mhi;
 }
 
-// The hot loop must stay small and shallow: the instruction caches hold ~6 KB (L0) / 32 KB (L1.5), sixteen warps walk different
-// parts of it, and with ~100 of the 128 registers holding points there is nothing left to keep many loads in flight.  So
-//  - the per-group state lives in REGISTERS of lane g (sphere, threshold, key): the seven skip tests are one compare and a ballot;
-//  - the coordinates in shared memory are laid out per THREAD, row-major (x y z x y z ...) in 16-byte chunks [chunk][tid], so a group
-//    of 7 rows is 6-7 conflict-free LDS.128 from one base register instead of 21 scalar loads;
-//  - exchange: no block stage.  Every WARP pushes ONE 16-byte record (x, y, z, code) into every block of the cluster (st.async onto the
-//    receiver's transaction barrier) and every warp reduces the cs * 16 records itself; warps of a block only meet in the tie path.
-//    code = 0: the warp holds no point; else (float bits of its largest running distance + 1) | bit 31 when several of its points
-//    attain it.
+// Exchange of the pruned sampler: there is no block stage.  Every WARP pushes ONE 16-byte record (x, y, z, code) into every block of
+// the cluster (st.async onto the receiver's transaction barrier) and every warp reduces the cs * 16 records itself; warps of a block
+// never meet.  code = 0: the warp holds no point; else (float bits of its largest running distance + 1) | bit 31 when several of its
+// points attain it.  The per-group state (sphere, threshold, key, coordinates of the point behind the key) lives in REGISTERS of
+// lane g: the skip tests of all groups of a warp are one compare and a ballot.
 constexpr int kFpsPruneMaxCluster = 8;
 // try_wait with a suspend-time hint: the waiter sleeps in hardware instead of coming back every few hundred cycles to spin
 __device__ __forceinline__ void fps_wait_records(uint64_t *bar, uint32_t parity)
@@ -487,331 +473,13 @@ __device__ __forceinline__ void fps_wait_records(uint64_t *bar, uint32_t parity)
     }
 }
 
-template <int PPT, int SD, int CS, bool kProf>
-__global__ void __launch_bounds__(kFpsThreads, 1)
-fps_pruned_kernel(const int32_t *__restrict__ perm, const float *__restrict__ xorig, int64_t n, int s, int start,
-                  int32_t *__restrict__ idx_out, int ngroups, int dbg)
-{
-    constexpr int cs = CS;
-    static_assert(PPT + SD == kFpsGroupRows * kFpsGroups, "row groups must tile the thread's rows");
-    extern __shared__ __align__(16) float4 fps_dyn4[];
-    const int rowsT = ngroups * kFpsGroupRows;
-    const int arows = rowsT > PPT ? rowsT - PPT : 0;
-    __shared__ float4 slots[2][(CS * kFpsWarps < 32 ? 32 : CS * kFpsWarps)];
-    __shared__ float4 tslots[2][(CS * kFpsWarps < 32 ? 32 : CS * kFpsWarps)];      // tie resolution: per warp x, y, z, original index
-    __shared__ uint64_t xbar[2], tbar[2];
-
-    cg::cluster_group cluster = cg::this_cluster();
-    const int rank = (int)cluster.block_rank();
-    const int64_t cloud = blockIdx.x / cs;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const float *xo = xorig + cloud * n * 3;
-    const int32_t *pc = perm + cloud * n;
-    // groups of 224 consecutive sorted points are dealt round-robin over the blocks of the cluster and their warps, so the
-    // neighbourhood of a sample spreads over all of them: sorted position of (group g, row j of it, this lane)
-    auto gpos = [&](int r) -> int64_t {
-        const int g = r / kFpsGroupRows, j = r - g * kFpsGroupRows;
-        return ((int64_t)((g * kFpsWarps + warp) * cs + rank) * kFpsGroupRows + j) * 32 + lane;
-    };
-    const float4 *sb = fps_dyn4 + tid;                // chunk k of this thread: sb[k * 512]
-    auto srow = [&](int r, float &x, float &y, float &z) {      // a shared-memory row by run-time index (start-up / rare paths)
-        const float *f = reinterpret_cast<const float *>(fps_dyn4);
-        const int f0 = 3 * (r - PPT);
-        x = f[(((f0) >> 2) * kFpsThreads + tid) * 4 + ((f0) & 3)];
-        y = f[(((f0 + 1) >> 2) * kFpsThreads + tid) * 4 + ((f0 + 1) & 3)];
-        z = f[(((f0 + 2) >> 2) * kFpsThreads + tid) * 4 + ((f0 + 2) & 3)];
-    };
-
-    float px[PPT], py[PPT], pz[PPT], d[PPT], ds[SD];
-    unsigned long long realmask = 0ull;          // bit r: row r of this thread is a point of the cloud
-#pragma unroll
-    for (int k = 0; k < PPT; ++k) {
-        const int64_t gi = gpos(k);
-        const bool real = k < rowsT && gi < n;
-        if (real) realmask |= 1ull << k;
-        // the sorted cloud is never materialised: the point is gathered through the permutation (the input is L2 resident after the
-        // sort's passes over it)
-        const int64_t o = real ? (int64_t)__ldg(pc + gi) : 0;
-        px[k] = real ? __ldg(xo + 3 * o) : 0.f; py[k] = real ? __ldg(xo + 3 * o + 1) : 0.f; pz[k] = real ? __ldg(xo + 3 * o + 2) : 0.f;
-        d[k] = real ? __int_as_float(0x7f800000) : 0.f;      // padding is never "real" when keys are built
-    }
-#pragma unroll
-    for (int k = 0; k < SD; ++k) {
-        const bool real = k < arows && gpos(PPT + k) < n;
-        if (real) realmask |= 1ull << (PPT + k);
-        ds[k] = real ? __int_as_float(0x7f800000) : 0.f;
-    }
-    {
-        const int nch = (3 * arows + 3) / 4;
-        for (int k = 0; k < nch; ++k) {
-            float v[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const int f = 4 * k + e, r = PPT + f / 3, c = f - 3 * (f / 3);
-                const int64_t gi = gpos(r);
-                v[e] = (r < rowsT && gi < n) ? __ldg(xo + 3 * (int64_t)__ldg(pc + gi) + c) : 0.f;
-            }
-            fps_dyn4[k * kFpsThreads + tid] = make_float4(v[0], v[1], v[2], v[3]);
-        }
-    }
-    // bounding spheres: centre = mean of the group's real points, radius = farthest of them (fp32, inflated); lane g keeps group g's
-    float scx = 0.f, scy = 0.f, scz = 0.f, srad = 0.f, sthr = -1.f;      // thr -1: always skipped (lanes >= 7, empty groups)
-    unsigned khi = 0u, klo = 0u;                                          // lane g: key of group g (klo: fps_local_id, 0 = no point)
-    for (int g = 0; g < kFpsGroups; ++g) {       // (not unrolled: start-up code, the register rows are read through a select chain)
-        float ax = 0.f, ay = 0.f, az = 0.f, cnt = 0.f, qx[kFpsGroupRows], qy[kFpsGroupRows], qz[kFpsGroupRows];
-#pragma unroll
-        for (int j = 0; j < kFpsGroupRows; ++j) {
-            const int r = g * kFpsGroupRows + j;
-            qx[j] = qy[j] = qz[j] = 0.f;
-            if (r < PPT) {
-#pragma unroll
-                for (int k = 0; k < PPT; ++k)
-                    if (k == r) { qx[j] = px[k]; qy[j] = py[k]; qz[j] = pz[k]; }
-            } else if (r - PPT < arows) srow(r, qx[j], qy[j], qz[j]);
-            if ((realmask >> r) & 1ull) { ax += qx[j]; ay += qy[j]; az += qz[j]; cnt += 1.f; }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            ax += __shfl_xor_sync(0xffffffffu, ax, o); ay += __shfl_xor_sync(0xffffffffu, ay, o);
-            az += __shfl_xor_sync(0xffffffffu, az, o); cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-        }
-        const float ic = cnt > 0.f ? 1.f / cnt : 0.f;
-        const float mx = ax * ic, my = ay * ic, mz = az * ic;
-        float r2 = 0.f;
-#pragma unroll
-        for (int j = 0; j < kFpsGroupRows; ++j)
-            if ((realmask >> (g * kFpsGroupRows + j)) & 1ull)
-                r2 = fmaxf(r2, (qx[j] - mx) * (qx[j] - mx) + (qy[j] - my) * (qy[j] - my) + (qz[j] - mz) * (qz[j] - mz));
-        r2 = __uint_as_float(__reduce_max_sync(0xffffffffu, __float_as_uint(r2)));
-        if (lane == g) {
-            // a populated group is never skipped before its first update; an empty one always is
-            scx = mx; scy = my; scz = mz;
-            srad = sqrtf(r2) * 1.0001f + 1e-30f;
-            sthr = cnt > 0.f ? __int_as_float(0x7f800000) : -1.f;
-        }
-    }
-    float cx = __ldg(xo + 3 * (int64_t)start), cy = __ldg(xo + 3 * (int64_t)start + 1), cz = __ldg(xo + 3 * (int64_t)start + 2);
-    if (rank == 0 && tid == 0) idx_out[cloud * s] = start;
-
-    constexpr int nrec = CS * kFpsWarps;         // records per iteration
-    if (nrec < 32 && tid < 32) {         // unused slots read as "no point"
-        slots[0][tid] = make_float4(0.f, 0.f, 0.f, 0.f); slots[1][tid] = make_float4(0.f, 0.f, 0.f, 0.f);
-        tslots[0][tid] = make_float4(0.f, 0.f, 0.f, __uint_as_float(0xFFFFFFFFu)); tslots[1][tid] = tslots[0][tid];
-    }
-    if (tid == 0) {
-        umma::mbar_init(&xbar[0], 1); umma::mbar_init(&xbar[1], 1); umma::mbar_init(&tbar[0], 1); umma::mbar_init(&tbar[1], 1);
-        umma::fence_barrier_init();
-    }
-    __syncthreads();
-    if (tid == 0) {
-        umma::mbar_arrive_expect_tx(&xbar[0], nrec * 16u); umma::mbar_arrive_expect_tx(&xbar[1], nrec * 16u);
-        umma::mbar_arrive_expect_tx(&tbar[0], nrec * 16u); umma::mbar_arrive_expect_tx(&tbar[1], nrec * 16u);
-    }
-    cluster.sync();                              // every block is armed before anybody pushes
-    long long ph[6] = {0, 0, 0, 0, 0, 0}, tprev = clock64();
-    unsigned long long nact = 0, nties = 0;
-    unsigned ntie = 0u;                          // tie iterations so far (identical in every warp of the cluster)
-    unsigned wcode = 0u, wlo = 0u;               // this warp's record (warp-uniform): code, local id and coordinates of its best point
-    float wx = 0.f, wy = 0.f, wz = 0.f;
-    for (int it = 1; it < s; ++it) {
-        FPS_TRACE(0);
-        const float tdx = cx - scx, tdy = cy - scy, tdz = cz - scz;
-        unsigned act = __ballot_sync(0xffffffffu, !(tdx * tdx + tdy * tdy + tdz * tdz > sthr));
-        if (dbg == 1 && it > 1) act = 0u;            // development: exchange only (results wrong)
-        if (act) {
-#pragma unroll
-            for (int g = 0; g < kFpsGroups; ++g) {
-                if (!((act >> g) & 1u)) continue;
-                if (kProf) ++nact;
-                // the shared-memory part of the group: floats [f_lo, f_hi) of this thread, in chunks [k_lo, k_hi]
-                constexpr int kNone = 0;
-                const int r_lo = g * kFpsGroupRows < PPT ? PPT : g * kFpsGroupRows, r_hi = (g + 1) * kFpsGroupRows;      // rows [r_lo, r_hi) in smem
-                const int k_lo = r_lo < r_hi ? (3 * (r_lo - PPT)) / 4 : kNone, k_hi = r_lo < r_hi ? (3 * (r_hi - PPT) - 1) / 4 : kNone - 1;
-                float4 ch[8];
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    if (k_lo + k <= k_hi) ch[k] = sb[(k_lo + k) * kFpsThreads];
-                auto sf = [&](int f) -> float {      // float f of this thread's shared rows (compile-time f after unrolling)
-                    const float4 &c = ch[(f >> 2) - k_lo < 8 && (f >> 2) >= k_lo ? (f >> 2) - k_lo : 0];
-                    return (f & 3) == 0 ? c.x : (f & 3) == 1 ? c.y : (f & 3) == 2 ? c.z : c.w;
-                };
-                float lbv = -1.f;
-#pragma unroll
-                for (int j = 0; j < kFpsGroupRows; ++j) {
-                    const int r = g * kFpsGroupRows + j;
-                    if (r < PPT) {
-                        const int k = r < PPT ? r : 0;
-                        d[k] = fminf(d[k], sqdist_nofma(px[k], py[k], pz[k], cx, cy, cz));
-                        lbv = fmaxf(lbv, d[k]);
-                    } else {
-                        const int k = r >= PPT ? r - PPT : 0;
-                        ds[k] = fminf(ds[k], sqdist_nofma(sf(3 * k), sf(3 * k + 1), sf(3 * k + 2), cx, cy, cz));
-                        lbv = fmaxf(lbv, ds[k]);
-                    }
-                }
-                // the group's maximum over its REAL points (padding rows hold 0 and never raise it), the first point that attains
-                // it and whether it is alone
-                const unsigned mine = (unsigned)(realmask >> (g * kFpsGroupRows)) & ((1u << kFpsGroupRows) - 1u);
-                const unsigned gm = __reduce_max_sync(0xffffffffu, mine ? __float_as_uint(lbv) : 0u);
-                unsigned at = 0u;            // real rows of this lane at the maximum
-#pragma unroll
-                for (int j = 0; j < kFpsGroupRows; ++j) {
-                    const int r = g * kFpsGroupRows + j;
-                    const float dv = r < PPT ? d[r < PPT ? r : 0] : ds[r >= PPT ? r - PPT : 0];
-                    if (__float_as_uint(dv) == gm) at |= 1u << j;
-                }
-                at &= mine;
-                const unsigned lanes_at = __ballot_sync(0xffffffffu, at != 0u);
-                const unsigned multi_l = __ballot_sync(0xffffffffu, (at & (at - 1u)) != 0u);
-                const int ol = __ffs(lanes_at) - 1;
-                const unsigned oat = __shfl_sync(0xffffffffu, at, ol < 0 ? 0 : ol);
-                if (lane == g) {
-                    khi = gm;
-                    klo = lanes_at ? fps_local_id((lanes_at & (lanes_at - 1u)) != 0u || multi_l != 0u, warp, g, g * kFpsGroupRows + __ffs(oat) - 1, ol) : 0u;
-                    sthr = lanes_at ? fps_skip_threshold(srad, __uint_as_float(gm)) : -1.f;
-                }
-            }
-            // the warp's record: its best group's key and that point's coordinates
-            int sel; bool multi;
-            const unsigned whi = fps_key_max(khi, klo, sel, multi);
-            wlo = sel < 0 ? 0u : __shfl_sync(0xffffffffu, klo, sel);
-            wcode = sel < 0 ? 0u : (whi + 1u) | (multi ? 0x80000000u : 0u);
-            const int ol = (int)(wlo & 31u), orow = (int)((wlo >> 5) & 63u);
-            float rx = 0.f, ry = 0.f, rz = 0.f;
-            if (sel >= 0 && lane == ol) {
-                if (orow >= PPT) srow(orow, rx, ry, rz);
-                else {
-#pragma unroll
-                    for (int k = 0; k < PPT; ++k)
-                        if (k == orow) { rx = px[k]; ry = py[k]; rz = pz[k]; }
-                }
-            }
-            wx = __shfl_sync(0xffffffffu, rx, ol); wy = __shfl_sync(0xffffffffu, ry, ol); wz = __shfl_sync(0xffffffffu, rz, ol);
-        }
-        FPS_STAMP(0);
-        FPS_TRACE(1);
-        const int par = it & 1;
-        if (lane < cs)       // lane t -> block t of the cluster: data and its arrival in one remote operation
-            fps_st_async16(&slots[par][rank * kFpsWarps + warp], &xbar[par], (uint32_t)lane, __float_as_uint(wx), __float_as_uint(wy),
-                           __float_as_uint(wz), wcode);
-        FPS_STAMP(3);
-        FPS_TRACE(2);
-        // CTA-scope wait: the records land in THIS block's shared memory through the async proxy, ordered by the barrier's transaction
-        // count (each barrier completes every second iteration)
-        fps_wait_records(&xbar[par], ((unsigned)(it - 1) >> 1) & 1u);
-        // re-arm for iteration it + 2: nobody pushes that early (it takes this block's it + 1 records, which follow this in tid 0's
-        // program order)
-        if (tid == 0 && it + 2 < s) umma::mbar_arrive_expect_tx(&xbar[par], nrec * 16u);
-        FPS_STAMP(4);
-        FPS_TRACE(3);
-        // every warp reduces the records itself: per lane the first best of its records, then across lanes
-        constexpr int kPerLane = nrec <= 32 ? 1 : nrec / 32;
-        float4 rc[kPerLane];
-#pragma unroll
-        for (int e = 0; e < kPerLane; ++e) rc[e] = slots[par][lane + 32 * e];
-        float4 brec = rc[0];
-        unsigned bcode = __float_as_uint(rc[0].w), bi = (unsigned)lane;
-#pragma unroll
-        for (int e = 1; e < kPerLane; ++e) {
-            const unsigned c = __float_as_uint(rc[e].w);
-            if ((c & 0x7FFFFFFFu) > (bcode & 0x7FFFFFFFu)) { brec = rc[e]; bcode = c; bi = (unsigned)(lane + 32 * e); }
-            else if (c != 0u && (c & 0x7FFFFFFFu) == (bcode & 0x7FFFFFFFu)) bcode |= 0x80000000u;
-        }
-        const unsigned cmax = __reduce_max_sync(0xffffffffu, bcode & 0x7FFFFFFFu);       // > 0: the cloud has points
-        const unsigned eq = __ballot_sync(0xffffffffu, (bcode & 0x7FFFFFFFu) == cmax && bcode != 0u);
-        const int sl = __ffs(eq) - 1;
-        const bool tie = (eq & (eq - 1u)) != 0u || (__shfl_sync(0xffffffffu, bcode, sl) & 0x80000000u) != 0u;
-        const unsigned dmax = cmax - 1u;
-        FPS_TRACE(4);
-        if (!tie) {
-            cx = __shfl_sync(0xffffffffu, brec.x, sl); cy = __shfl_sync(0xffffffffu, brec.y, sl); cz = __shfl_sync(0xffffffffu, brec.z, sl);
-            const int wi = (int)__shfl_sync(0xffffffffu, bi, sl);
-            // the one thread that holds the winner translates its sorted position (a load that nothing in the loop waits for)
-            if (wi == rank * kFpsWarps + warp && lane == (int)(wlo & 31u))
-                idx_out[cloud * s + it] = __ldg(pc + gpos((int)((wlo >> 5) & 63u)));
-        } else {
-            // several points share the largest distance: np.argmax takes the lowest original index.  Every warp of the cluster sees
-            // the same records and takes this branch.
-            if (kProf) ++nties;
-            unsigned cand = 0xFFFFFFFFu;
-            int crow = 0;
-            const unsigned gat = __ballot_sync(0xffffffffu, klo != 0u && khi == dmax);      // groups of this warp at the maximum
-            for (int g = 0; g < kFpsGroups; ++g) {      // (not unrolled: rare path, keep it out of the instruction cache's way)
-                if (!((gat >> g) & 1u)) continue;
-#pragma unroll
-                for (int j = 0; j < kFpsGroupRows; ++j) {
-                    const int r = g * kFpsGroupRows + j;
-                    float dv = 0.f;
-                    if (r < PPT) {
-#pragma unroll
-                        for (int k = 0; k < PPT; ++k)
-                            if (k == r) dv = d[k];
-                    } else {
-#pragma unroll
-                        for (int k = 0; k < SD; ++k)
-                            if (k == r - PPT) dv = ds[k];
-                    }
-                    if (__float_as_uint(dv) == dmax && ((realmask >> r) & 1ull)) {
-                        const unsigned o = (unsigned)__ldg(pc + gpos(r));
-                        if (o < cand) { cand = o; crow = r; }
-                    }
-                }
-            }
-            // every warp pushes (x, y, z, lowest original index among ITS tied points) into every block, on a second pair of
-            // transaction barriers that advances with the number of tie iterations (all warps count them alike)
-            const unsigned wmin = __reduce_min_sync(0xffffffffu, cand);
-            float rx = 0.f, ry = 0.f, rz = 0.f;
-            const unsigned who = __ballot_sync(0xffffffffu, wmin != 0xFFFFFFFFu && cand == wmin);
-            const int ol = who ? __ffs(who) - 1 : 0;
-            if (who && lane == ol) {
-                if (crow >= PPT) srow(crow, rx, ry, rz);
-                else {
-#pragma unroll
-                    for (int k = 0; k < PPT; ++k)
-                        if (k == crow) { rx = px[k]; ry = py[k]; rz = pz[k]; }
-                }
-            }
-            rx = __shfl_sync(0xffffffffu, rx, ol); ry = __shfl_sync(0xffffffffu, ry, ol); rz = __shfl_sync(0xffffffffu, rz, ol);
-            const int tpar = (int)(ntie & 1u);
-            if (lane < cs)
-                fps_st_async16(&tslots[tpar][rank * kFpsWarps + warp], &tbar[tpar], (uint32_t)lane, __float_as_uint(rx), __float_as_uint(ry),
-                               __float_as_uint(rz), wmin);
-            fps_wait_records(&tbar[tpar], (ntie >> 1) & 1u);
-            if (tid == 0) umma::mbar_arrive_expect_tx(&tbar[tpar], nrec * 16u);        // for tie iteration ntie + 2 (same argument as xbar)
-            ++ntie;
-            float4 tr[kPerLane];
-#pragma unroll
-            for (int e = 0; e < kPerLane; ++e) tr[e] = tslots[tpar][lane + 32 * e];
-            float4 tb4 = tr[0];
-#pragma unroll
-            for (int e = 1; e < kPerLane; ++e)
-                if (__float_as_uint(tr[e].w) < __float_as_uint(tb4.w)) tb4 = tr[e];
-            const unsigned tmin = __reduce_min_sync(0xffffffffu, __float_as_uint(tb4.w));
-            const int tb = __ffs(__ballot_sync(0xffffffffu, __float_as_uint(tb4.w) == tmin)) - 1;
-            cx = __shfl_sync(0xffffffffu, tb4.x, tb); cy = __shfl_sync(0xffffffffu, tb4.y, tb); cz = __shfl_sync(0xffffffffu, tb4.z, tb);
-            if (rank == 0 && tid == 0) idx_out[cloud * s + it] = (int32_t)tmin;
-        }
-        FPS_STAMP(5);
-        FPS_TRACE(5);
-    }
-    if (kProf) {
-        // groups updated by block 0's warps over the whole chain (of 16 warps x 7 groups x (s - 1)), and the tie iterations
-        if (blockIdx.x == 0 && lane == 0) atomicAdd(&g_fps_phase[6], nact);
-        if (blockIdx.x == 0 && tid == 0) {
-            for (int i = 0; i < 6; ++i) g_fps_phase[i] = (unsigned long long)ph[i];
-            g_fps_phase[7] = nties;
-        }
-    }
-    cluster.sync();     // no block may exit while a peer can still write into its slots
-}
-
 // ------------------------------------------------------------------------------------------------------------------------------
 // LEAN pruned variant: only the running DISTANCES stay on chip.  With pruning ~9 % of the groups need their coordinates in an
 // iteration, so the coordinates can live in an L2-resident copy (per thread row-major in 16-byte chunks [group][chunk][tid]: a group
 // is six coalesced LDG.128) and a block only has to hold 4 bytes per point — 98 rows of 512 distances in shared memory = 50 176
 // points per block.  A 100 000-point cloud then fits in a cluster of TWO, 64 clouds are 128 blocks = ONE wave on 148 SMs instead of
 // the two waves of the register / shared-memory resident kernels, and the whole kernel is generic code (no register-resident rows
-// to unroll over): the loop body is a few KB.  Same skip test, same keys, same exchange and tie path as fps_pruned_kernel.
+// to unroll over): the loop body is a few KB.
 constexpr int kLeanMaxGroups = 14;                    // 14 x 7 rows x 512 x 4 B = 200 704 B of distances
 constexpr int kLeanChunks = 6;                        // 7 rows x 3 floats = 21 (+ 3 padding) floats = 6 float4 per thread and group
 
@@ -1156,7 +824,6 @@ static int fps_plain(const float *d_x, int b, int64_t n, int s, int start, int32
 // ---- pruned path: geometry, workspace layout and launch
 struct FpsPrunePlan {
     int cs = 0, ngroups = 0;
-    bool lean = false;                   // fps_lean_kernel (distances only on chip) instead of fps_pruned_kernel
     size_t off_perm = 0, off_hist = 0, off_bbox = 0, off_coords = 0, bytes = 0;
 };
 
@@ -1164,18 +831,10 @@ static bool fps_prune_plan(int b, int64_t n, int s, FpsPrunePlan &pl)
 {
     static const bool off = getenv("PCP_FPS_NO_PRUNE") != nullptr;
     if (off || s < 32 || n >= 0x7FFFFFFFll) return false;
-    // the cluster that keeps a cloud on chip with 49 rows of 512 points per block (13 rows in registers, 36 with the coordinates in
-    // shared memory): the pruned kernel is built for that shape only
-    constexpr int rows_max = kFpsPruneReg + kFpsPruneSm;
+    // the cluster whose blocks hold the cloud's running distances (50 176 points per block)
     int cs = 1;
-    while (cs <= kFpsPruneMaxCluster && n > (int64_t)cs * kFpsThreads * rows_max) cs *= 2;
-    // the lean kernel wherever the cloud's distances fit a cluster of <= 8 blocks (50 176 points per block); PCP_FPS_PRUNE_V1 keeps
-    // the coordinate-resident kernel for comparison
-    static const bool v1 = getenv("PCP_FPS_PRUNE_V1") != nullptr;
-    int csl = 1;
-    while (csl <= kFpsPruneMaxCluster && n > (int64_t)csl * kLeanMaxGroups * kFpsWarps * kFpsGroupRows * 32) csl *= 2;
-    pl.lean = !v1 && csl <= kFpsPruneMaxCluster;
-    if (!pl.lean && cs > kFpsPruneMaxCluster) return false;
+    while (cs <= kFpsPruneMaxCluster && n > (int64_t)cs * kLeanMaxGroups * kFpsWarps * kFpsGroupRows * 32) cs *= 2;
+    if (cs > kFpsPruneMaxCluster) return false;
     // only where the register-resident clusters (25 rows per block) would not all be resident at once — the batch sizes the
     // hybrid kernel was built for; a few clouds are faster spread over wide clusters
     int cs_reg = 1;
@@ -1183,45 +842,15 @@ static bool fps_prune_plan(int b, int64_t n, int s, FpsPrunePlan &pl)
     static const bool force = getenv("PCP_FPS_FORCE_PRUNE") != nullptr;
     if (!force && (int64_t)b * cs_reg <= sm_count()) return false;
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    if (pl.lean) cs = csl;
     const int64_t per_group = (int64_t)cs * kFpsWarps * kFpsGroupRows * 32;      // points one group slot holds across the cluster
     const int ngroups = (int)((n + per_group - 1) / per_group);
-    if (!pl.lean && ngroups < 3) return false;                   // small clouds: the register-only kernel, nothing to prune at 1-2 ms
     pl.cs = cs; pl.ngroups = ngroups;
     pl.off_perm = 0;
     pl.off_hist = pl.off_perm + up((size_t)b * n * sizeof(int32_t));
     pl.off_bbox = pl.off_hist + up((size_t)b * kFpsSortBins * sizeof(int));
     pl.off_coords = pl.off_bbox + up((size_t)b * 6 * sizeof(unsigned));
-    pl.bytes = pl.off_coords + (pl.lean ? up((size_t)b * cs * ngroups * kLeanChunks * kFpsThreads * sizeof(float4)) : 0);
+    pl.bytes = pl.off_coords + up((size_t)b * cs * ngroups * kLeanChunks * kFpsThreads * sizeof(float4));
     return true;
-}
-
-template <int CS, bool kProf>
-static int launch_fps_pruned_cs(const int32_t *perm, const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx,
-                                const FpsPrunePlan &pl, int dbg, cudaStream_t st)
-{
-    auto kern = fps_pruned_kernel<kFpsPruneReg, kFpsPruneSm, CS, kProf>;
-    static bool attr_set_dev[64] = {};      // per device (per template instance)
-    const int dev = fps_device();
-    PCP_REQUIRE(dev >= 0, PCP_ERR_CUDA, "fps: no current device");
-    bool &attr_set = attr_set_dev[dev];
-    if (!attr_set) {
-        PCP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-        PCP_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ((3 * kFpsPruneSm + 3) / 4) * kFpsThreads * 16));
-        attr_set = true;
-    }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((int64_t)b * CS));
-    cfg.blockDim = dim3(kFpsThreads);
-    cfg.dynamicSmemBytes = (size_t)((3 * (pl.ngroups * kFpsGroupRows - kFpsPruneReg) + 3) / 4) * kFpsThreads * 16;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, perm, d_x, n, s, start, d_idx, pl.ngroups, dbg));
-    PCP_CHECK_LAUNCH();
-    return PCP_OK;
 }
 
 template <int CS, bool kProf>
@@ -1285,20 +914,12 @@ static int launch_fps_pruned(const float *d_x, int b, int64_t n, int s, int star
 
     static const int dbg = getenv("PCP_FPS_PRUNE_DBG") ? atoi(getenv("PCP_FPS_PRUNE_DBG")) : 0;      // development (see the kernel)
     if (dbg == 2) return PCP_OK;                     // development: the sort alone
-    if (pl.lean) {
-        float4 *coords = reinterpret_cast<float4 *>(base + pl.off_coords);
-        switch (pl.cs) {
-        case 1: return launch_fps_lean_cs<1, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
-        case 2: return launch_fps_lean_cs<2, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
-        case 4: return launch_fps_lean_cs<4, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
-        default: return launch_fps_lean_cs<8, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
-        }
-    }
+    float4 *coords = reinterpret_cast<float4 *>(base + pl.off_coords);
     switch (pl.cs) {
-    case 1: return launch_fps_pruned_cs<1, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
-    case 2: return launch_fps_pruned_cs<2, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
-    case 4: return launch_fps_pruned_cs<4, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
-    default: return launch_fps_pruned_cs<8, kProf>(perm, d_x, b, n, s, start, d_idx, pl, dbg, st);
+    case 1: return launch_fps_lean_cs<1, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
+    case 2: return launch_fps_lean_cs<2, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
+    case 4: return launch_fps_lean_cs<4, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
+    default: return launch_fps_lean_cs<8, kProf>(perm, d_x, coords, b, n, s, start, d_idx, pl, dbg, st);
     }
 }
 
@@ -1425,14 +1046,6 @@ static int fps_plain(const float *d_x, int b, int64_t n, int s, int start, int32
 
 /* development aid: cycles block 0 / thread 0 of the last PCP_FPS_PROF=1 launch (PPT = 25) spent in: distance loop, candidate
  * search + record, __syncthreads, warp-0 stage + DSMEM pushes, cluster barrier, slot read-back */
-extern "C" int pcp_fps_trace(long long *out, int count)
-{
-    PCP_REQUIRE(out && count == 16 * kFpsWarps * 6, PCP_ERR_INVALID, "pcp_fps_trace: count must be %d", 16 * kFpsWarps * 6);
-    PCP_CUDA_OK(cudaDeviceSynchronize());
-    PCP_CUDA_OK(cudaMemcpyFromSymbol(out, g_fps_trace, sizeof(long long) * count));
-    return PCP_OK;
-}
-
 extern "C" int pcp_fps_phase_cycles(unsigned long long out[8])
 {
     PCP_CUDA_OK(cudaDeviceSynchronize());
