@@ -332,8 +332,8 @@ def main():
         ms_fps_plain = timed(lambda i: _ffi.check(_ffi.load().pcp_fps_f32(_ffi.ptr(scans), 64, 100_000, 1024, 0, _ffi.ptr(fps_idx), _ffi.stream_ptr())), 3, 1)
         extras["fps"] = {"metric": "fps_downsampling_mpts_per_sec", "value": world * 64 * 100_000 / (ms_fps * 1e-3) / 1e6, "unit": "Mpts/s",
                          "ms_per_step": ms_fps, "ms_per_step_unpruned_kernel": ms_fps_plain,
-                         "config": "C2: 64 x 100000 -> 1024, cluster per cloud, register + shared-memory resident; Morton-ordered cloud with "
-                                   "bounding-sphere skipping (pcp_fps_ws_f32), sort included in the time",
+                         "config": "C2: 64 x 100000 -> 1024, cluster of two blocks per cloud (one wave), running distances in shared memory; Morton-ordered "
+                                   "cloud with bounding-sphere skipping, coordinates of active groups from an L2-resident copy (pcp_fps_ws_f32); sort included",
                          "effective_GBps": 64 * 1024 * 100_000 * 20 / (ms_fps * 1e-3) / 1e9,
                          "effective_frac_of_hbm": 64 * 1024 * 100_000 * 20 / (ms_fps * 1e-3) / 1e9 / peaks["hbm_gbs"],
                          "note": "effective = 20 B per point-distance update (SURVEY §8d); on-chip resident, may exceed 1.0"}
@@ -520,9 +520,9 @@ def main():
             fp = extras["fps"]
             fps_prof = ROOT / "profiles" / "r02_fps_ncu.json"
             fps_ncu = json.loads(fps_prof.read_text()) if fps_prof.exists() else {}
-            rooflines["fps"] = {"bound": "hbm", "kernel": "fps_pruned_kernel (+ fps_sort_*)", "achieved": fp["effective_GBps"], "peak": hbm, "unit": "GB/s",
+            rooflines["fps"] = {"bound": "hbm", "kernel": "fps_lean_kernel (+ fps_sort_*)", "achieved": fp["effective_GBps"], "peak": hbm, "unit": "GB/s",
                                 "frac": fp["effective_frac_of_hbm"], "traffic": fps_ncu.get("dram_bytes"),
-                                "algorithmic": "20 B per point-distance update x 64 x 1024 x 100 000 (effective: the cloud is on-chip resident and ~90 % of the "
+                                "algorithmic": "20 B per point-distance update x 64 x 1024 x 100 000 (effective: the running distances are on-chip resident and ~92 % of the "
                                                "updates are proven unnecessary and skipped)",
                                 "real_bound": "per-iteration latency chain (exchange + the busiest warp's updates)", "issue_slot_frac_of_elapsed": fps_ncu.get("issue_slot_frac_of_elapsed"),
                                 "thread_instr_per_update": fps_ncu.get("thread_instr_per_update"), "profile": fps_ncu.get("file")}

@@ -123,10 +123,12 @@ int pcp_resize_to_width_f32(const float *d_x, const int32_t *d_labels, int b, in
 int pcp_fps_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, pcp_stream stream);
 /* The same samples (bit-identical) with caller-owned scratch: with a workspace the library first puts every cloud in Morton order
  * of a coarse grid and then skips, per iteration, the groups of points whose bounding sphere is farther from the new sample than
- * their largest running distance — 2-3x faster on LiDAR-sized batches.  pcp_fps_workspace_bytes reports 0 where the plain kernel
- * is the better choice (few or small clouds); pcp_fps_ws_f32 then ignores the workspace and runs the plain kernel.  Clouds too
- * large to stay on chip (n > 204 800) stream their running distances through b * n floats of scratch: from the workspace here,
- * from a library-owned per-device buffer (cudaMalloc on growth) in pcp_fps_f32. */
+ * their largest running distance; only the running distances stay on chip, so a 100 000-point cloud needs two thread blocks
+ * instead of four — 1.9x faster on LiDAR-sized batches (64 x 100 000 -> 1024: 2.7 ms against 5.1 ms).
+ * pcp_fps_workspace_bytes reports 0 where the plain kernel is the better choice (few or small clouds); pcp_fps_ws_f32 then
+ * ignores the workspace and runs the plain kernel.  Clouds the plain kernel cannot keep on chip (n > 204 800) and that are too
+ * few to be pruned stream their running distances through b * n floats of scratch: from the workspace here, from a
+ * library-owned per-device buffer (cudaMalloc on growth) in pcp_fps_f32. */
 int pcp_fps_workspace_bytes(int b, int64_t n, int s, size_t *bytes);
 int pcp_fps_ws_f32(const float *d_x, int b, int64_t n, int s, int start, int32_t *d_idx, void *d_workspace, size_t workspace_bytes,
                    pcp_stream stream);
