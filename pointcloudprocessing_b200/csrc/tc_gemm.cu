@@ -19,7 +19,11 @@ constexpr uint32_t kGemmSmem = kGemmStages * kGemmStageBytes + 1024;
 
 __device__ __forceinline__ float bf16_trunc_rn(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 
-__global__ void __launch_bounds__(kGemmThreads, 2)
+// kMinBlocks = 3: the K <= 128 per-point layers of the training step.  One k-tile or two means one or two ring stages
+// (33 / 65 KB of shared memory), and at 96 registers three CTAs fit an SM: each CTA is one dependent chain (weights and
+// activations in, one MMA group, TMEM out), so the tiles in flight per SM are what hides its latency.
+template <int kMinBlocks>
+__global__ void __launch_bounds__(kGemmThreads, kMinBlocks)
 tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nsplit)
 {   // bnt: MMA N of this CTA; img_rows: rows of a weight-image tile; nsplit = img_rows / bnt column blocks per image tile
     extern __shared__ uint8_t smem_raw[];
@@ -36,7 +40,8 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
     const int g = blockIdx.y / mtiles, mt = blockIdx.y % mtiles;
     const int row0 = mt * 128;
     const int rows_valid = min(128, p.M - row0);
-    const int KT = p.K >> 6;
+    const int KT = (p.K >> 6) / (int)gridDim.z;          // this CTA's k-tiles: [kt0, kt0 + KT) of the matrix (split-K over grid.z)
+    const int kt0 = (int)blockIdx.z * KT;
     const uint32_t b_tile_bytes = (uint32_t)bnt * 128u;
 
     if (tid == 0) {
@@ -60,7 +65,7 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
         const int chunk = tid & 7, rsub = tid >> 3;
         const char *Abase = reinterpret_cast<const char *>(p.A);
         const size_t esz = p.a_f32 ? 4 : 2;
-        const size_t a_off = ((size_t)g * p.a_group_stride + (size_t)row0 * p.lda) * esz;
+        const size_t a_off = ((size_t)g * p.a_group_stride + (size_t)row0 * p.lda + (size_t)kt0 * 64) * esz;
         // Rows past the end of the matrix are clamped to the last valid row instead of predicated: every load is
         // unconditional, so the compiler issues all loads of a k-tile back to back (ONE memory round trip per tile —
         // predicated loads had been serialised into eight dependent round trips, 3.7 us per k-tile); the duplicated
@@ -85,7 +90,7 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
         if (p.a_f32) {
             // fp32 activations (pooled features): one k-tile (16 x float4) in flight, converted to bf16 on arrival
             float4 raw[16];
-            const int KTs = p.a_split3 ? KT / 3 : KT;          // k-tiles of the source matrix (split3: every tile is read three times)
+            const int KTs = p.a_split3 ? KT / 3 : KT;          // k-tiles of the source matrix (split3: every tile is read three times; never split-K)
             auto issue = [&](int kt) {
                 const int ks = p.a_split3 ? kt % KTs : kt;
 #pragma unroll
@@ -153,6 +158,12 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
             if (p.C32) {
                 float *Cg = p.C32 + (size_t)g * p.c_group_stride;
                 if (p.dbg & 1) {
+                } else if (gridDim.z > 1) {
+                    if (row_ok) {
+                        float *dst = p.C32 + c_off + nbase;
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) if (nbase + e < p.N) atomicAdd(dst + e, o[e]);
+                    }
                 } else if (nbase + 32 <= p.N && (p.ldc & 3) == 0 && (((uintptr_t)Cg & 15u) == 0)) {
                     // warp-uniform fast path: the lane's 32 columns of ITS row go through a warp-private shared tile (the
                     // operand stages are idle once acc_full fired) so that one store instruction writes four rows x 128
@@ -229,7 +240,7 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
         // ---------------- weight-tile loader ----------------
         if (lane == 0) {
             const size_t img_tile_bytes = (size_t)img_rows * 128u;
-            const uint8_t *img = p.Bimg + (size_t)g * p.b_group_stride + (size_t)ntile * KT * img_tile_bytes + (size_t)nsub * b_tile_bytes;
+            const uint8_t *img = p.Bimg + (size_t)g * p.b_group_stride + ((size_t)ntile * (p.K >> 6) + kt0) * img_tile_bytes + (size_t)nsub * b_tile_bytes;
             for (int kt = 0; kt < KT; ++kt) {
                 const int s = kt % kGemmStages;
                 if (kt >= kGemmStages) mbar_wait(&empty[s], (uint32_t)(((kt / kGemmStages) - 1) & 1), 43);
@@ -297,8 +308,11 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
     PCP_REQUIRE(!p.Csoftmax || p.N <= 32, PCP_ERR_UNSUPPORTED, "tc_gemm: softmax epilogue needs N <= 32");
     PCP_REQUIRE((p.lda % (p.a_f32 ? 4 : 8)) == 0, PCP_ERR_UNSUPPORTED, "tc_gemm: lda must keep 16-byte row chunks aligned");
     PCP_REQUIRE(!p.a_split3 || (p.a_f32 && p.K % 192 == 0), PCP_ERR_UNSUPPORTED, "tc_gemm: a_split3 needs fp32 activations and K = 3 x a multiple of 64");
+    PCP_REQUIRE(p.ksplit >= 1 && (p.K / 64) % p.ksplit == 0, PCP_ERR_UNSUPPORTED, "tc_gemm: K / 64 = %d is not a multiple of ksplit = %d", p.K / 64, p.ksplit);
+    PCP_REQUIRE(p.ksplit == 1 || (p.C32 && !p.C16 && !p.Csoftmax && !p.bias && !p.relu && !p.a_split3), PCP_ERR_INVALID,
+                "tc_gemm: split-K adds plain fp32 products");
     if (p.M <= 0 || p.groups <= 0) return PCP_OK;
-    {
+    if (p.ksplit == 1) {
         int rc = PCP_OK;
         if (tc_gemm_persist_try(p, st, &rc)) return rc;
     }
@@ -308,7 +322,8 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
     const int64_t gy = (int64_t)mtiles * p.groups;
     static bool attr = false;
     if (!attr) {
-        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
         attr = true;
     }
     PCP_REQUIRE(gy <= 65535, PCP_ERR_UNSUPPORTED, "tc_gemm: %lld row tiles exceed one launch", (long long)gy);
@@ -317,12 +332,18 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
     // few CTAs and full-width tiles: 32-column blocks (see the kernel)
     static const bool no_split = getenv("PCP_TC_GEMM_NO_NSPLIT") != nullptr;
     const int nsplit = (!no_split && bnt_img == 128 && (int64_t)ntiles * gy * 4 <= 2 * (int64_t)sm_count()) ? 4 : 1;
-    cfg.gridDim = dim3(ntiles * nsplit, (unsigned)gy); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = kGemmSmem; cfg.stream = st;
+    // the ring only uses min(K / 64, stages) stages
+    const int stages_used = std::min(p.K / 64 / p.ksplit, kGemmStages);
+    static const bool no_dense = getenv("PCP_TC_GEMM_NO_DENSE") != nullptr;
+    const bool dense = !no_dense && stages_used <= 2 && (int64_t)ntiles * nsplit * gy >= 3 * (int64_t)sm_count();
+    cfg.gridDim = dim3(ntiles * nsplit, (unsigned)gy, (unsigned)p.ksplit); cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = (size_t)stages_used * kGemmStageBytes + 1024; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = no_pdl ? 0 : 1;
-    PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
+    if (dense) PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel<3>, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
+    else PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel<2>, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }

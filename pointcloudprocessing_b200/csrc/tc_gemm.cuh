@@ -30,6 +30,9 @@ struct TcGemmParams {
     int groups = 1;
     int relu = 0;
     int accumulate = 0;                 // C32 += result (input-gradient accumulation); no bias / relu / softmax
+    int ksplit = 1;                     // > 1: the K / 64 k-tiles are dealt over ksplit CTAs (grid.z) that ADD their products into C32 with
+                                        // fp32 atomics — skinny, long-K products (a 256 x 4096 . 4096 x 256 gradient walked 64 dependent
+                                        // k-tiles on 16 CTAs: 61 us); C32 only, no bias / relu; K / 64 must be a multiple of ksplit
     int dbg = 0;                        // development (pcp_bench_tc_gemm): 1 = skip output stores, 2 = skip activation loads
 };
 

@@ -22,12 +22,12 @@ using namespace umma;
 // weight image packer: element (k, n) of the logical (K x N) matrix is W[k*ldw + n] (transpose = 0) or W[n*ldw + k]
 // (transpose = 1); tiles [nt][kt] of (bnt rows x 64 K) bf16, K-major SWIZZLE_128B (tc_gemm.cu:pack_gemm_b_image)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-pack_weight_image_kernel(const float *__restrict__ W, int K, int N, int ldw, int transpose, int bnt, uint16_t *__restrict__ img)
+__device__ __forceinline__ void pack_weight_image_body(const float *__restrict__ W, int K, int N, int ldw, int transpose, int bnt,
+                                                       const float *__restrict__ colscale, uint16_t *__restrict__ img, int64_t first, int64_t stride)
 {
     const int KT = K >> 6, ntiles = (N + bnt - 1) / bnt;
     const int64_t total = (int64_t)ntiles * KT * bnt * 64;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    for (int64_t i = first; i < total; i += stride) {
         // decode i as (tile, r, k) with k fastest so that global reads of the non-transposed case are strided by ldw but
         // the writes stay inside one 128-byte swizzle row
         const int k = (int)(i & 63);
@@ -38,18 +38,45 @@ pack_weight_image_kernel(const float *__restrict__ W, int K, int N, int ldw, int
         const int n = nt * bnt + r, kk = kt * 64 + k;
         float v = 0.f;
         if (n < N) v = transpose ? __ldg(W + (int64_t)n * ldw + kk) : __ldg(W + (int64_t)kk * ldw + n);
+        if (colscale && n < N) v *= __ldg(colscale + n);
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
         img[tile * (bnt * 64) + sw128_offset((uint32_t)bnt, (uint32_t)r, (uint32_t)k) / 2] = *reinterpret_cast<const uint16_t *>(&h);
     }
 }
 
-int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, uint8_t *d_img, cudaStream_t st)
+__global__ void __launch_bounds__(256)
+pack_weight_image_kernel(const float *__restrict__ W, int K, int N, int ldw, int transpose, int bnt, const float *__restrict__ colscale,
+                         uint16_t *__restrict__ img)
+{
+    pack_weight_image_body(W, K, N, ldw, transpose, bnt, colscale, img, blockIdx.x * (int64_t)blockDim.x + threadIdx.x, (int64_t)gridDim.x * blockDim.x);
+}
+
+// every job of a table in one launch (blockIdx.y = job): the training step re-packs all its weight images once per step
+__global__ void __launch_bounds__(256)
+pack_weight_images_kernel(const PackJob *__restrict__ jobs)
+{
+    const PackJob j = jobs[blockIdx.y];
+    pack_weight_image_body(j.W, j.K, j.N, j.ldw, j.transpose, j.bnt, nullptr, j.img, blockIdx.x * (int64_t)blockDim.x + threadIdx.x,
+                           (int64_t)gridDim.x * blockDim.x);
+}
+
+int pack_weight_images(const PackJob *d_jobs, int njobs, cudaStream_t st)
+{
+    if (njobs <= 0) return PCP_OK;
+    PCP_REQUIRE(njobs <= 65535, PCP_ERR_UNSUPPORTED, "pack_weight_images: too many jobs");
+    // a (256 x 4096) image is 1 M elements: 256 x 256 threads take four each, blocks past a small image's end leave at once
+    pack_weight_images_kernel<<<dim3(256, njobs), 256, 0, st>>>(d_jobs);
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
+}
+
+int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, uint8_t *d_img, cudaStream_t st, const float *d_colscale)
 {
     PCP_REQUIRE(K >= 64 && K % 64 == 0, PCP_ERR_UNSUPPORTED, "pack_weight_image: K=%d must be a multiple of 64", K);
     const int bnt = tc_gemm_bn_tile(N);
     const int64_t total = (int64_t)((N + bnt - 1) / bnt) * (K / 64) * bnt * 64;
     const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)sm_count() * 8);
-    pack_weight_image_kernel<<<grid, 256, 0, st>>>(d_W, K, N, ldw, transpose ? 1 : 0, bnt, reinterpret_cast<uint16_t *>(d_img));
+    pack_weight_image_kernel<<<grid, 256, 0, st>>>(d_W, K, N, ldw, transpose ? 1 : 0, bnt, d_colscale, reinterpret_cast<uint16_t *>(d_img));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -329,7 +356,13 @@ struct PoolExtParams {
     int n, cout, mtiles;
 };
 
-__global__ void __launch_bounds__(kPxThreads, 2)
+constexpr int kPeThreads = 320;                 // warps 0-7: A producer, then two epilogue warpgroups; warp 8 MMA issuer, warp 9 W loader
+
+// The epilogue is a chain of TMEM round trips (tcgen05.ld of 32 columns, wait, 32 compare/selects, four times per 128-channel
+// block) and was the kernel's critical path with one warpgroup: 8 blocks x 4 round trips per CTA behind one another, 165 us.
+// Two warpgroups take the channel blocks alternately (block nt lives in accumulator nt & 1, warpgroup nt & 1 reduces it), so
+// two blocks are being reduced while the MMA of the next one runs; the A tile is converted by all eight warps.
+__global__ void __launch_bounds__(kPeThreads, 2)
 tc_pool_extrema_kernel(const PoolExtParams p)
 {
     extern __shared__ uint8_t smem_raw[];
@@ -344,68 +377,79 @@ tc_pool_extrema_kernel(const PoolExtParams p)
     const int NT = p.cout >> 7;
 
     if (tid == 0) {
-        mbar_init(&a_full, 4);
+        mbar_init(&a_full, 8);
         for (int i = 0; i < 2; ++i) { mbar_init(&w_full[i], 1); mbar_init(&w_empty[i], 1); mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
         fence_barrier_init();
     }
-    if (warp == 4) tmem_alloc(&tmem_base, 256);
+    if (warp == 8) tmem_alloc(&tmem_base, 256);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = tmem_base;
 
-    if (warp < 4) {
-        // ---------------- A tile: 8 threads per row (32 B fp32 -> 16 B bf16), 16 rows per pass, clamped rows ----------------
+    if (warp < 8) {
+        // ---------------- A tile: 8 threads per row (32 B fp32 -> 16 B bf16), 32 rows per pass, clamped rows ----------------
         const int chunk = tid & 7, rsub = tid >> 3;
         const float *Ag = p.A + ((int64_t)g * p.n + row0) * 128 + chunk * 8;
+        float4 raw[16];
 #pragma unroll
-        for (int kt = 0; kt < 2; ++kt) {
-            float4 raw[16];
+        for (int kt = 0; kt < 2; ++kt)
 #pragma unroll
-            for (int pass = 0; pass < 8; ++pass) {
-                const int r = min(pass * 16 + rsub, rows_valid - 1);
+            for (int pass = 0; pass < 4; ++pass) {
+                const int r = min(pass * 32 + rsub, rows_valid - 1);
                 const float4 *src = reinterpret_cast<const float4 *>(Ag + (int64_t)r * 128 + kt * 64);
-                raw[2 * pass] = __ldg(src); raw[2 * pass + 1] = __ldg(src + 1);
+                raw[kt * 8 + 2 * pass] = __ldg(src); raw[kt * 8 + 2 * pass + 1] = __ldg(src + 1);
             }
 #pragma unroll
-            for (int pass = 0; pass < 8; ++pass) {
-                const float4 f0 = raw[2 * pass], f1 = raw[2 * pass + 1];
-                *reinterpret_cast<uint4 *>(As + kt * 16384 + sw128_offset(128, (uint32_t)(pass * 16 + rsub), (uint32_t)chunk * 8)) =
+        for (int kt = 0; kt < 2; ++kt)
+#pragma unroll
+            for (int pass = 0; pass < 4; ++pass) {
+                const float4 f0 = raw[kt * 8 + 2 * pass], f1 = raw[kt * 8 + 2 * pass + 1];
+                *reinterpret_cast<uint4 *>(As + kt * 16384 + sw128_offset(128, (uint32_t)(pass * 32 + rsub), (uint32_t)chunk * 8)) =
                     make_uint4(pack_bf16x2(f0.x, f0.y), pack_bf16x2(f0.z, f0.w), pack_bf16x2(f1.x, f1.y), pack_bf16x2(f1.z, f1.w));
             }
-        }
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(&a_full);
         // ---------------- epilogue: thread = channel, serial reduction over the tile's rows ----------------
-        for (int nt = 0; nt < NT; ++nt) {
-            const int buf = nt & 1;
-            mbar_wait(&acc_full[buf], (uint32_t)((nt >> 1) & 1), 61);
+        const int wg = warp >> 2, ch = (warp & 3) * 32 + lane;         // warpgroup = accumulator buffer; TMEM lane = channel
+        const uint32_t tacc = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(wg * 128);
+        for (int nt = wg; nt < NT; nt += 2) {
+            mbar_wait(&acc_full[wg], (uint32_t)((nt >> 1) & 1), 61);
             tc_fence_after();
             float mx = -INFINITY, mn = INFINITY;
             int rmx = 0, rmn = 0;
             for (int c0 = 0; c0 < rows_valid; c0 += 32) {
                 uint32_t v[32];
-                tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(buf * 128 + c0), v);
+                tmem_ld32(tacc + (uint32_t)c0, v);
                 tmem_ld_wait();
+                if (c0 + 32 <= rows_valid) {
 #pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                    const float f = __uint_as_float(v[e]);
-                    const bool ok = c0 + e < rows_valid;
-                    if (ok && f > mx) { mx = f; rmx = c0 + e; }
-                    if (ok && f < mn) { mn = f; rmn = c0 + e; }
+                    for (int e = 0; e < 32; ++e) {
+                        const float f = __uint_as_float(v[e]);
+                        if (f > mx) { mx = f; rmx = c0 + e; }
+                        if (f < mn) { mn = f; rmn = c0 + e; }
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        const float f = __uint_as_float(v[e]);
+                        const bool ok = c0 + e < rows_valid;
+                        if (ok && f > mx) { mx = f; rmx = c0 + e; }
+                        if (ok && f < mn) { mn = f; rmn = c0 + e; }
+                    }
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[buf]);
-            const size_t o = (size_t)g * p.cout + (size_t)nt * 128 + tid;
+            if (lane == 0) mbar_arrive(&acc_empty[wg]);
+            const size_t o = (size_t)g * p.cout + (size_t)nt * 128 + ch;
             if (mx > -INFINITY)
                 atomicMax(p.ext_max + o, ((unsigned long long)tc_float_key(__float_as_uint(mx)) << 32) | (0xffffffffu - (uint32_t)(row0 + rmx)));
             if (mn < INFINITY)
                 atomicMax(p.ext_min + o, ((unsigned long long)(~tc_float_key(__float_as_uint(mn))) << 32) | (0xffffffffu - (uint32_t)(row0 + rmn)));
         }
-    } else if (warp == 4) {
+    } else if (warp == 8) {
         // ---------------- MMA issuer: D[channel, row] = W tile (128 ch x 128 K) . A tile^T ----------------
         const uint32_t idesc = make_idesc_bf16(128, 128);
         const uint32_t a_lo = (smem_u32(As) & 0x3FFFFu) >> 4, w_lo = (smem_u32(Ws) & 0x3FFFFu) >> 4;
@@ -441,7 +485,7 @@ tc_pool_extrema_kernel(const PoolExtParams p)
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc(tmem, 256);
+    if (warp == 8) tmem_dealloc(tmem, 256);
 }
 
 int tc_pool_extrema(const float *A, int b, int64_t n, const uint8_t *Wimg, int cout, unsigned long long *ext_max, unsigned long long *ext_min,
@@ -459,7 +503,7 @@ int tc_pool_extrema(const float *A, int b, int64_t n, const uint8_t *Wimg, int c
         PCP_CUDA_OK(cudaFuncSetAttribute(tc_pool_extrema_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPxSmem));
         attr = true;
     }
-    tc_pool_extrema_kernel<<<(unsigned)grid, kPxThreads, kPxSmem, st>>>(p);
+    tc_pool_extrema_kernel<<<(unsigned)grid, kPeThreads, kPxSmem, st>>>(p);
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }

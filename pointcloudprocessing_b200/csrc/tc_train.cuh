@@ -5,8 +5,17 @@
 namespace pcp {
 
 // fp32 weights (row-major, leading dimension ldw) -> packed bf16 SWIZZLE_128B image of the logical (K x N) matrix
-// B[k][n] = W[k*ldw + n] (transpose = false) or W[n*ldw + k] (transpose = true); layout of tc_gemm's Bimg
-int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, uint8_t *d_img, cudaStream_t st);
+// B[k][n] = W[k*ldw + n] (transpose = false) or W[n*ldw + k] (transpose = true); layout of tc_gemm's Bimg.
+// d_colscale (N floats, optional): B[k][n] is multiplied by colscale[n] before rounding (a frozen BatchNorm folded into its layer)
+int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, uint8_t *d_img, cudaStream_t st,
+                      const float *d_colscale = nullptr);
+
+// the same for a device table of jobs in ONE launch (no column scale); bnt = tc_gemm_bn_tile(N)
+struct PackJob {
+    const float *W; uint16_t *img;
+    int K, N, ldw, transpose, bnt;
+};
+int pack_weight_images(const PackJob *d_jobs, int njobs, cudaStream_t st);
 
 // dW (cin x cout, leading dimension lddw) += A^T (cin x rows) . dZ (rows x cout): split-K over the rows, fp32 atomics
 int tc_wgrad(const float *A, int64_t lda, int64_t rows, int cin, const float *dZ, int64_t ldz, int cout, float *dW, int64_t lddw,

@@ -84,8 +84,9 @@ __device__ __forceinline__ void lane_reduce(double *sh, const ColMap &cm, int C,
 
 // sum / sum of squares per column (BatchNormalization batch statistics, biased variance)
 __global__ void __launch_bounds__(256)
-colstats_kernel(const float *__restrict__ Z, int64_t rows, int C, double *__restrict__ sum, double *__restrict__ sumsq)
+colstats_kernel(const float *__restrict__ Z, int64_t rows, int C, double *__restrict__ parts)
 {
+    double *sum = parts + (size_t)blockIdx.x * 2 * C, *sumsq = sum + C;
     __shared__ double sh[256];
     const ColMap cm(C);
     const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
@@ -101,10 +102,10 @@ colstats_kernel(const float *__restrict__ Z, int64_t rows, int C, double *__rest
     }
     lane_reduce(sh, cm, C, s);
     lane_reduce(sh, cm, C, q);
-    if (cm.lane == 0 && r1 > r0)
+    if (cm.lane == 0)
         for (int j = 0; j < cm.cpt; ++j) {
-            atomicAdd(sum + cm.col0 + j * 256, s[j]);
-            atomicAdd(sumsq + cm.col0 + j * 256, q[j]);
+            sum[cm.col0 + j * 256] = s[j];
+            sumsq[cm.col0 + j * 256] = q[j];
         }
 }
 
@@ -133,8 +134,9 @@ __device__ __forceinline__ void lane_reduce4(double (*sh)[256], const ColMap4 &c
 }
 
 __global__ void __launch_bounds__(256)
-colstats4_kernel(const float4 *__restrict__ Z, int64_t rows, int C, double *__restrict__ sum, double *__restrict__ sumsq)
+colstats4_kernel(const float4 *__restrict__ Z, int64_t rows, int C, double *__restrict__ parts)
 {
+    double *sum = parts + (size_t)blockIdx.x * 2 * C, *sumsq = sum + C;
     __shared__ double sh[4][256];
     const ColMap4 cm(C);
     const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
@@ -155,18 +157,19 @@ colstats4_kernel(const float4 *__restrict__ Z, int64_t rows, int C, double *__re
     for (; r < r1; r += step) acc(__ldg(Z + r * cm.c4 + cm.col));
     lane_reduce4(sh, cm, s);
     lane_reduce4(sh, cm, q);
-    if (cm.lane == 0 && r1 > r0)
+    if (cm.lane == 0)
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            atomicAdd(sum + cm.col * 4 + e, s[e]);
-            atomicAdd(sumsq + cm.col * 4 + e, q[e]);
+            sum[cm.col * 4 + e] = s[e];
+            sumsq[cm.col * 4 + e] = q[e];
         }
 }
 
 __global__ void __launch_bounds__(256)
 bn_bwd_reduce4_kernel(const float4 *__restrict__ dY, const float4 *__restrict__ Z, int64_t rows, int C, BnP p, int relu,
-                      double *__restrict__ s1, double *__restrict__ s2)
+                      double *__restrict__ parts)
 {
+    double *s1 = parts + (size_t)blockIdx.x * 2 * C, *s2 = s1 + C;
     __shared__ double sh[4][256];
     const ColMap4 cm(C);
     const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
@@ -196,54 +199,111 @@ bn_bwd_reduce4_kernel(const float4 *__restrict__ dY, const float4 *__restrict__ 
     for (; r < r1; r += step) acc(__ldg(Z + r * cm.c4 + cm.col), __ldg(dY + r * cm.c4 + cm.col));
     lane_reduce4(sh, cm, a);
     lane_reduce4(sh, cm, b);
-    if (cm.lane == 0 && r1 > r0)
+    if (cm.lane == 0)
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            atomicAdd(s1 + cm.col * 4 + e, a[e]);
-            atomicAdd(s2 + cm.col * 4 + e, b[e]);
+            s1[cm.col * 4 + e] = a[e];
+            s2[cm.col * 4 + e] = b[e];
         }
 }
 
 // dW (3 x C) += X^T (3 x rows) . dZ (rows x C): the two 3-channel input layers (a 128 x 64 GEMM tile wastes 125 of its rows)
 __global__ void __launch_bounds__(256)
-wgrad3_kernel(const float *__restrict__ X, const float4 *__restrict__ dZ, int64_t rows, int C, float *__restrict__ dW)
+wgrad3_kernel(const float *__restrict__ X, const float4 *__restrict__ dZ, int64_t rows, int C, double *__restrict__ parts)
 {
+    double *dW = parts + (size_t)blockIdx.x * 3 * C;
     __shared__ double sh[4][256];
     const ColMap4 cm(C);
     const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
     const int64_t r0 = (int64_t)blockIdx.x * per, r1 = min(rows, r0 + per);
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0;
-    for (int64_t r = r0 + cm.lane; r < r1; r += cm.lanes) {
-        const float4 d = __ldg(dZ + r * cm.c4 + cm.col);
-        const float x = __ldg(X + r * 3), y = __ldg(X + r * 3 + 1), z = __ldg(X + r * 3 + 2);
+    auto acc3 = [&](const float4 d, float x, float y, float z) {
         a0.x = fmaf(x, d.x, a0.x); a0.y = fmaf(x, d.y, a0.y); a0.z = fmaf(x, d.z, a0.z); a0.w = fmaf(x, d.w, a0.w);
         a1.x = fmaf(y, d.x, a1.x); a1.y = fmaf(y, d.y, a1.y); a1.z = fmaf(y, d.z, a1.z); a1.w = fmaf(y, d.w, a1.w);
         a2.x = fmaf(z, d.x, a2.x); a2.y = fmaf(z, d.y, a2.y); a2.z = fmaf(z, d.z, a2.z); a2.w = fmaf(z, d.w, a2.w);
+    };
+    int64_t r = r0 + cm.lane;
+    const int64_t step = cm.lanes;
+    for (; r + 3 * step < r1; r += 4 * step) {                    // four rows in flight
+        float4 d[4]; float x[4], y[4], z[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t rr = r + u * step;
+            d[u] = __ldg(dZ + rr * cm.c4 + cm.col); x[u] = __ldg(X + rr * 3); y[u] = __ldg(X + rr * 3 + 1); z[u] = __ldg(X + rr * 3 + 2);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) acc3(d[u], x[u], y[u], z[u]);
     }
+    for (; r < r1; r += step) acc3(__ldg(dZ + r * cm.c4 + cm.col), __ldg(X + r * 3), __ldg(X + r * 3 + 1), __ldg(X + r * 3 + 2));
     const float4 acc[3] = {a0, a1, a2};
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         double v[4] = {acc[k].x, acc[k].y, acc[k].z, acc[k].w};
         lane_reduce4(sh, cm, v);
-        if (cm.lane == 0 && r1 > r0)
+        if (cm.lane == 0)
 #pragma unroll
-            for (int e = 0; e < 4; ++e) atomicAdd(dW + (size_t)k * C + cm.col * 4 + e, (float)v[e]);
+            for (int e = 0; e < 4; ++e) dW[(size_t)k * C + cm.col * 4 + e] = v[e];
     }
 }
 
-// batch statistics -> (mean, inv, sc, beta) and the moving-average update; or the moving statistics when the
-// layer is frozen (keras: training and trainable)
-__global__ void bn_finalize_kernel(const double *__restrict__ sum, const double *__restrict__ sumsq, double rows, int C, int batch,
-                                   const float *__restrict__ gamma, const float *__restrict__ beta_in, float *__restrict__ mov_mean,
-                                   float *__restrict__ mov_var, float *__restrict__ mean, float *__restrict__ inv, float *__restrict__ sc,
-                                   float *__restrict__ beta, float eps, float momentum)
+// The column reductions above end in per-block partial sums (parts[block][...]) instead of one atomic per column and
+// block: 592 blocks' double atomics on the same 128 words serialise in the L2 at ~40 ns each, a fixed 25 us per launch
+// that was most of colstats4 (36 us for 67 MB) and bn_bwd_reduce4.  The partials are summed in block order — the same
+// bits on every run — by one warp per element here, or inside bn_finalize_kernel.
+// sum_p col[p * stride] over the block's 256 threads: every thread's (<= 4) loads leave together — ONE L2 round trip for
+// 592 partials where a warp per element walked five dependent ones (7 us) — and the partial sums are added in a fixed
+// order (lanes by shuffle, then the eight warps in turn).  Result valid in thread 0.
+__device__ __forceinline__ double block_parts_sum(const double *__restrict__ col, size_t stride, int nparts, double *sh8)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+    const int tid = threadIdx.x;
+    double v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { const int p = tid + 256 * u; v[u] = p < nparts ? col[(size_t)p * stride] : 0.0; }
+    double s = (v[0] + v[1]) + (v[2] + v[3]);
+    for (int p = tid + 1024; p < nparts; p += 256) s += col[(size_t)p * stride];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    __syncthreads();
+    if ((tid & 31) == 0) sh8[tid >> 5] = s;
+    __syncthreads();
+    return ((sh8[0] + sh8[1]) + (sh8[2] + sh8[3])) + ((sh8[4] + sh8[5]) + (sh8[6] + sh8[7]));
+}
+
+//   out[i] = sum_p parts[p][i];  f_lo / f_hi: float copies of the two halves (dbeta / dgamma);  add_f32[i] += sum.  Block = element.
+__global__ void __launch_bounds__(256)
+reduce_parts_kernel(const double *__restrict__ parts, int nparts, int count, double *__restrict__ out, float *__restrict__ f_lo,
+                    float *__restrict__ f_hi, int half, float *__restrict__ add_f32)
+{
+    __shared__ double sh8[8];
+    const int i = blockIdx.x;
+    const double s = block_parts_sum(parts + i, (size_t)count, nparts, sh8);
+    if (threadIdx.x) return;
+    if (out) out[i] = s;
+    if (f_lo && i < half) f_lo[i] = (float)s;
+    if (f_hi && i >= half) f_hi[i - half] = (float)s;
+    if (add_f32) add_f32[i] += (float)s;
+}
+
+// batch statistics -> (mean, inv, sc, beta) and the moving-average update; or the moving statistics when the
+// layer is frozen (keras: training and trainable).  One block per column; parts[p][0:C] are the partial
+// sums, parts[p][C:2C] the partial sums of squares (nparts = 1: already reduced)
+__global__ void __launch_bounds__(256)
+bn_finalize_kernel(const double *__restrict__ parts, int nparts, double rows, int C, int batch, const float *__restrict__ gamma,
+                   const float *__restrict__ beta_in, float *__restrict__ mov_mean, float *__restrict__ mov_var, float *__restrict__ mean,
+                   float *__restrict__ inv, float *__restrict__ sc, float *__restrict__ beta, float eps, float momentum)
+{
+    __shared__ double sh8[2][8];
+    const int c = blockIdx.x;
+    double sum = 0, sumsq = 0;
+    if (batch) {
+        sum = block_parts_sum(parts + c, (size_t)2 * C, nparts, sh8[0]);
+        sumsq = block_parts_sum(parts + C + c, (size_t)2 * C, nparts, sh8[1]);
+    }
+    if (threadIdx.x) return;
     float mu, var;
     if (batch) {
-        const double m = sum[c] / rows;
-        double v = sumsq[c] / rows - m * m;
+        const double m = sum / rows;
+        double v = sumsq / rows - m * m;
         if (v < 0) v = 0;
         mu = (float)m; var = (float)v;
         mov_mean[c] = momentum * mov_mean[c] + (1.f - momentum) * mu;
@@ -345,8 +405,9 @@ pool_bwd_kernel(const float4 *__restrict__ Z, int64_t n4_per_cloud, int64_t tota
 // BN + ReLU backward, reduction half: s1[c] = sum dyh, s2[c] = sum dyh * xhat, dyh = dY * [pre > 0]
 __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const float *__restrict__ dY, const float *__restrict__ Z, int64_t rows, int C, BnP p, int relu,
-                     double *__restrict__ s1, double *__restrict__ s2)
+                     double *__restrict__ parts)
 {
+    double *s1 = parts + (size_t)blockIdx.x * 2 * C, *s2 = s1 + C;
     __shared__ double sh[256];
     const ColMap cm(C);
     const int64_t per = (rows + gridDim.x - 1) / gridDim.x;
@@ -369,10 +430,10 @@ bn_bwd_reduce_kernel(const float *__restrict__ dY, const float *__restrict__ Z, 
     }
     lane_reduce(sh, cm, C, a);
     lane_reduce(sh, cm, C, b);
-    if (cm.lane == 0 && r1 > r0)
+    if (cm.lane == 0)
         for (int j = 0; j < cm.cpt; ++j) {
-            atomicAdd(s1 + cm.col0 + j * 256, a[j]);
-            atomicAdd(s2 + cm.col0 + j * 256, b[j]);
+            s1[cm.col0 + j * 256] = a[j];
+            s2[cm.col0 + j * 256] = b[j];
         }
 }
 
@@ -398,6 +459,49 @@ bn_bwd_apply_kernel(float4 *__restrict__ dY, const float4 *__restrict__ Z, int64
             dd[j] = p.sc[c + j] * dy;
         }
         dY[i] = make_float4(dd[0], dd[1], dd[2], dd[3]);
+    }
+}
+
+// the same with a thread bound to four adjacent columns (ColMap4): the eight per-column constants live in registers instead
+// of being re-read (24 scalar loads and 8 double -> float conversions per float4 pair before: 3.4 TB/s; the loop is now two
+// 16-byte loads and one store per element group, two rows in flight)
+__global__ void __launch_bounds__(256)
+bn_bwd_apply4_kernel(float4 *__restrict__ dY, const float4 *__restrict__ Z, int64_t rows, int C, BnP p, int relu, int batch,
+                     const double *__restrict__ s1, const double *__restrict__ s2, float inv_rows)
+{
+    const ColMap4 cm(C);
+    const int c = cm.col * 4;
+    float mu[4], sc[4], be[4], iv[4], k1[4], k2[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        mu[j] = p.mean[c + j]; sc[j] = p.sc[c + j]; be[j] = p.beta[c + j]; iv[j] = p.inv[c + j];
+        k1[j] = batch ? (float)s1[c + j] * inv_rows : 0.f;
+        k2[j] = batch ? (float)s2[c + j] * inv_rows : 0.f;
+    }
+    auto apply = [&](const float4 z, const float4 d) {
+        const float zz[4] = {z.x, z.y, z.z, z.w};
+        float dd[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float zc = zz[j] - mu[j];
+            float dy = dd[j];
+            if (relu && !(fmaf(zc, sc[j], be[j]) > 0.f)) dy = 0.f;
+            if (batch) dy = dy - k1[j] - (zc * iv[j]) * k2[j];
+            dd[j] = sc[j] * dy;
+        }
+        return make_float4(dd[0], dd[1], dd[2], dd[3]);
+    };
+    const int64_t L = (int64_t)gridDim.x * cm.lanes;
+    int64_t r = (int64_t)blockIdx.x * cm.lanes + cm.lane;
+    for (; r + L < rows; r += 2 * L) {
+        const int64_t i0 = r * cm.c4 + cm.col, i1 = (r + L) * cm.c4 + cm.col;
+        const float4 z0 = __ldg(Z + i0), d0 = dY[i0], z1 = __ldg(Z + i1), d1 = dY[i1];
+        dY[i0] = apply(z0, d0);
+        dY[i1] = apply(z1, d1);
+    }
+    for (; r < rows; r += L) {
+        const int64_t i0 = r * cm.c4 + cm.col;
+        dY[i0] = apply(__ldg(Z + i0), dY[i0]);
     }
 }
 
@@ -475,6 +579,92 @@ softmax_ce_kernel(const float *__restrict__ logits, int64_t rows, int C, const i
     if ((threadIdx.x & 31) == 0) { atomicAdd(loss_sum, lsum); atomicAdd(correct, csum); }
 }
 
+// The same per 128-row tile staged through shared memory (C <= 96): the thread-per-row kernel above reads and writes rows
+// 4*C bytes apart from neighbouring lanes (113 us for 262 144 x 50, 0.9 TB/s) and ends in one atomic pair per WARP on one
+// line; here the tile moves with coalesced 16-byte accesses, the row arithmetic (identical, in the same order) runs on
+// shared memory, and a block adds its loss / accuracy sums once.
+__global__ void __launch_bounds__(128)
+softmax_ce_tile_kernel(const float *__restrict__ logits, int64_t rows, int C, const int32_t *__restrict__ labels, float gscale,
+                       float *__restrict__ prob, float *__restrict__ dlogits, double *__restrict__ loss_sum, double *__restrict__ correct)
+{
+    extern __shared__ __align__(16) float ce_tile[];
+    __shared__ double red[2][4];
+    double lsum = 0, csum = 0;
+    const int64_t ntiles = (rows + 127) / 128;
+    const bool vec = ((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(prob) | reinterpret_cast<uintptr_t>(dlogits)) & 15u) == 0;
+    auto copy_out = [&](float *dst, int cnt) {
+        const int c4 = vec ? cnt >> 2 : 0;
+        for (int i = threadIdx.x; i < c4; i += 128) reinterpret_cast<float4 *>(dst)[i] = reinterpret_cast<const float4 *>(ce_tile)[i];
+        for (int i = (c4 << 2) + threadIdx.x; i < cnt; i += 128) dst[i] = ce_tile[i];
+    };
+    for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int64_t r0 = t * 128;
+        const int nr = (int)min((int64_t)128, rows - r0), cnt = nr * C;
+        const float *src = logits + r0 * C;                     // 128 * C floats per tile: 16-byte aligned with the base
+        {
+            const int c4 = vec ? cnt >> 2 : 0;
+            for (int i = threadIdx.x; i < c4; i += 128) reinterpret_cast<float4 *>(ce_tile)[i] = __ldg(reinterpret_cast<const float4 *>(src) + i);
+            for (int i = (c4 << 2) + threadIdx.x; i < cnt; i += 128) ce_tile[i] = __ldg(src + i);
+        }
+        __syncthreads();
+        float *z = ce_tile + threadIdx.x * C;
+        bool clipped = false;
+        int y = 0;
+        if ((int)threadIdx.x < nr) {
+            float mx = z[0]; int am = 0;
+            for (int c = 1; c < C; ++c) if (z[c] > mx) { mx = z[c]; am = c; }
+            float s = 0.f;
+            for (int c = 0; c < C; ++c) s += expf(z[c] - mx);
+            const float inv = 1.0f / s;
+            y = labels[r0 + threadIdx.x];
+            const float py = expf(z[y] - mx) * inv;
+            clipped = (py < 1e-7f) || (py > 1.0f - 1e-7f);
+            const float pc = fminf(fmaxf(py, 1e-7f), 1.0f - 1e-7f);
+            lsum += (double)(-logf(pc));
+            csum += (am == y) ? 1.0 : 0.0;
+            for (int c = 0; c < C; ++c) z[c] = expf(z[c] - mx) * inv;
+        }
+        __syncthreads();
+        if (prob) copy_out(prob + r0 * C, cnt);
+        if (dlogits) {
+            __syncthreads();
+            if ((int)threadIdx.x < nr)
+                for (int c = 0; c < C; ++c) z[c] = clipped ? 0.f : gscale * (z[c] - (c == y ? 1.f : 0.f));
+            __syncthreads();
+            copy_out(dlogits + r0 * C, cnt);
+        }
+        __syncthreads();
+    }
+    lsum = warp_sum(lsum); csum = warp_sum(csum);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = lsum; red[1][threadIdx.x >> 5] = csum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        atomicAdd(loss_sum, (red[0][0] + red[0][1]) + (red[0][2] + red[0][3]));
+        atomicAdd(correct, (red[1][0] + red[1][1]) + (red[1][2] + red[1][3]));
+    }
+}
+
+// Z (rows x C) = X (rows x 3) . W (3 x C) [+ bias]: the two 3-channel input layers (a 128 x 64 x 16 GEMM tile spends 13 of its
+// 16 k-steps on padding: 49 us for a 67 MB store).  A thread owns four adjacent columns of one row; fma order of the GEMM.
+__global__ void __launch_bounds__(256)
+mm3_kernel(const float *__restrict__ X, const float *__restrict__ W, int ldw, const float *__restrict__ bias, int64_t rows, int C4,
+           float4 *__restrict__ Z)
+{
+    const int64_t total = rows * C4;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / C4;
+        const int c = (int)(i - r * C4) * 4;
+        const float x0 = __ldg(X + 3 * r), x1 = __ldg(X + 3 * r + 1), x2 = __ldg(X + 3 * r + 2);
+        const float4 w0 = __ldg(reinterpret_cast<const float4 *>(W + c)), w1 = __ldg(reinterpret_cast<const float4 *>(W + ldw + c)),
+                     w2 = __ldg(reinterpret_cast<const float4 *>(W + 2 * ldw + c));
+        float4 z;
+        z.x = fmaf(x2, w2.x, fmaf(x1, w1.x, x0 * w0.x)); z.y = fmaf(x2, w2.y, fmaf(x1, w1.y, x0 * w0.y));
+        z.z = fmaf(x2, w2.z, fmaf(x1, w1.z, x0 * w0.z)); z.w = fmaf(x2, w2.w, fmaf(x1, w1.w, x0 * w0.w));
+        if (bias) { const float4 b = __ldg(reinterpret_cast<const float4 *>(bias + c)); z.x += b.x; z.y += b.y; z.z += b.z; z.w += b.w; }
+        Z[i] = z;
+    }
+}
+
 // MSE(R, y_se3) (pointnet_train.py:339): dR += gscale * 2 (R - y); sq_sum += sum (R - y)^2
 __global__ void mse_kernel(const float *__restrict__ R, const float *__restrict__ y, int64_t count, float gscale, float *__restrict__ dR,
                            double *__restrict__ sq_sum)
@@ -545,12 +735,24 @@ __global__ void axpy_kernel(float *__restrict__ y, const float *__restrict__ x, 
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
+// The packed bf16 images of the step's weight matrices.  The weights only change in the Adam step, so every image the
+// previous step used is re-packed by ONE launch at the start of the step (41 launches of ~4 us each before); a matrix
+// seen for the first time is packed on the spot and joins the table.
+struct ImgCache {
+    uint8_t *pool = nullptr;
+    size_t cap = 0, used = 0;
+    std::vector<PackJob> jobs;
+    PackJob *d_jobs = nullptr;
+    int d_count = 0;              // jobs in the device table
+    int fresh = 0;                // jobs[0 .. fresh) were packed by this step's refresh
+};
 // buffers of one implicitly handled max-pooled layer (train_pool.inl)
 struct PoolBufs {
     unsigned long long *ext = nullptr;   // 2 x (b x cout) packed extrema keys (max, then min)
     float *gram = nullptr;               // cin x cin : A^T A of the bf16-rounded input (this rank's rows)
     float *gram_parts = nullptr;         // per-split partial Gram matrices (tc_gram_det)
     double *asum = nullptr;              // cin       : 1^T A
+    double *colparts = nullptr;          // per-block partial column sums (pool_colsum_kernel), 4 x SMs x 128
     float *gram_g = nullptr;             // the same summed over the ranks (sync-BN); aliases gram / asum otherwise
     double *asum_g = nullptr;
     float *zsel = nullptr;               // b x cout  : the selected extremum of z
@@ -588,6 +790,8 @@ struct TrainState {
     float *H1 = nullptr, *H2 = nullptr;                            // after dropout
     float *cls_logits = nullptr, *cls_prob = nullptr, *seg_logits = nullptr, *seg_prob = nullptr;
     float *gvec = nullptr, *dgvec = nullptr;                       // per-cloud bias of seg_l1 (b x 512) and its gradient
+    double *colparts = nullptr;                                    // per-block partial sums of the column reductions
+    float *fshift = nullptr;                                       // 512 floats: epilogue constant of a frozen layer (seg_head_fwd_frozen)
     float *dg1 = nullptr, *dg2 = nullptr, *dg3 = nullptr;
     float *dsmall[4] = {nullptr};                                  // (b x 512), (b x 256), (b x C) ...
     // per-point scratch
@@ -598,6 +802,7 @@ struct TrainState {
     bool have_seg = false;
     char *eval_buf = nullptr; size_t eval_bytes = 0;               // pcp_model_evaluate: metrics + logits
     uint8_t *tc_img = nullptr;                                     // scratch bf16 weight image of the tensor-core GEMMs (4 MB)
+    ImgCache img_cache;                                            // the step's packed weight images (bf16 mode)
     PoolBufs pool[3];                                              // L_IT_C3, L_FT_C3, L_S2_3 (bf16 mode)
     bool implicit_pool = false;                                    // pooled layers without their (rows x 1024) tensors (train_pool.inl)
     pcp_allreduce_fn sync_fn = nullptr; void *sync_user = nullptr; // data-parallel BatchNorm (pcp_model_set_bn_allreduce)
@@ -639,9 +844,13 @@ void train_destroy(pcp_model *m)
     PCP_RELEASE(cudaFree(ts->arena));
     PCP_RELEASE(cudaFree(ts->eval_buf));
     PCP_RELEASE(cudaFree(ts->tc_img));
+    PCP_RELEASE(cudaFree(ts->img_cache.pool)); PCP_RELEASE(cudaFree(ts->img_cache.d_jobs));
     delete ts;
     m->train_ws = nullptr;
 }
+
+// capacity of the column reductions' partial-sum scratch: blocks (<= 8 per SM) x (2 or 3) x up to 1024 columns
+static inline size_t colparts_doubles() { return (size_t)sm_count() * 8 * 3 * 1024; }
 
 // (re)build the activation arena for b clouds of n points
 static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
@@ -681,7 +890,8 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
     want(&ts->H1, (size_t)b * 2048); want(&ts->H2, (size_t)b * 1024);
     want(&ts->cls_logits, (size_t)b * C * 4); want(&ts->cls_prob, (size_t)b * C * 4);
     want(&ts->seg_logits, (size_t)M * P * 4); want(&ts->seg_prob, (size_t)M * P * 4);
-    want(&ts->gvec, (size_t)b * 2048); want(&ts->dgvec, (size_t)b * 2048);
+    want(&ts->gvec, (size_t)b * 2048); want(&ts->dgvec, (size_t)b * 2048); want(&ts->fshift, 2048);
+    want(&ts->colparts, colparts_doubles() * 8);
     for (int i = 0; i < 4; ++i) want(&ts->dsmall[i], (size_t)b * 4096 * 4);
     want(&ts->Y64a, M * 256); want(&ts->Y64b, M * 256); want(&ts->Y128, M * 512); want(&ts->Y128b, M * 512);
     want(&ts->Y256, M * 1024); want(&ts->Y512, M * 2048);
@@ -689,7 +899,7 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
     else
         for (PoolBufs &pb : ts->pool) {
             want(&pb.ext, (size_t)b * 1024 * 16); want(&pb.gram, 128 * 128 * 4); want(&pb.asum, 128 * 8); want(&pb.zsel, (size_t)b * 4096);
-            want(&pb.gram_parts, tc_gram_scratch_floats(128) * 4);
+            want(&pb.gram_parts, tc_gram_scratch_floats(128) * 4); want(&pb.colparts, (size_t)sm_count() * 4 * 128 * 8);
             want(&pb.gram_g, 128 * 128 * 4); want(&pb.asum_g, 128 * 8);
             want(&pb.arg, (size_t)b * 4096); want(&pb.S, (size_t)b * 4096); want(&pb.c0, 4096); want(&pb.c1, 4096); want(&pb.Wt, 1024 * 128 * 4);
             want(&pb.Q, 128 * 128 * 4); want(&pb.q, 512);
@@ -707,10 +917,30 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
     return PCP_OK;
 }
 
+// blocks per SM of the column reductions whose blocks end in one atomic per column (colstats4, bn_bwd_reduce4, wgrad3)
+static inline int colred_waves()
+{
+    static const int w = [] { const char *e = getenv("PCP_COLRED_WAVES"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 8 ? v : 4; }();
+    return w;
+}
+
 static inline int grid_for(int64_t work, int per_block = 256, int waves = 8)
 {
     const int64_t g = (work + per_block - 1) / per_block;
     return (int)std::max<int64_t>(1, std::min<int64_t>(g, (int64_t)sm_count() * waves));
+}
+
+static int softmax_ce(const float *logits, int64_t rows, int C, const int32_t *labels, float gscale, float *prob, float *dlogits, double *loss_sum,
+                      double *correct, cudaStream_t st)
+{
+    if (C <= 96) {
+        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((rows + 127) / 128, (int64_t)sm_count() * 4));
+        softmax_ce_tile_kernel<<<grid, 128, (size_t)128 * C * sizeof(float), st>>>(logits, rows, C, labels, gscale, prob, dlogits, loss_sum, correct);
+    } else {
+        softmax_ce_kernel<<<grid_for(rows), 256, 0, st>>>(logits, rows, C, labels, gscale, prob, dlogits, loss_sum, correct);
+    }
+    PCP_CHECK_LAUNCH();
+    return PCP_OK;
 }
 
 // ---- GEMM wrappers (row-major fp32 activations; W is (cin x cout) row-major inside the flat parameter buffer) ----
@@ -718,10 +948,66 @@ static inline int grid_for(int64_t work, int per_block = 256, int waves = 8)
 // shapes the tensor-core tiles do not cover (K = 3 inputs, 9 / C / P wide outputs as a contraction) stay on the fp32 path.
 struct TcCtx {
     bool on = false;
-    uint8_t *img = nullptr;       // scratch weight image (re-packed before every GEMM: the weights change every step)
+    uint8_t *img = nullptr;       // scratch weight image (frozen layers with a folded BatchNorm, anything the cache cannot hold)
     size_t img_bytes = 0;
+    ImgCache *cache = nullptr;
 };
 static thread_local TcCtx g_tc;
+constexpr size_t kImgCacheBytes = (size_t)48 << 20;
+constexpr int kImgCacheMaxJobs = 256;
+
+static int img_cache_refresh(ImgCache *c, cudaStream_t st)
+{
+    if (!c->pool) {
+        PCP_CUDA_OK(cudaMalloc(&c->pool, kImgCacheBytes));
+        PCP_CUDA_OK(cudaMalloc(&c->d_jobs, kImgCacheMaxJobs * sizeof(PackJob)));
+        c->cap = kImgCacheBytes;
+    }
+    const int n = (int)c->jobs.size();
+    if (n > c->d_count) {
+        // the table only grows during the first steps; the copy is ordered before the launch on the same stream and
+        // completes (pageable source) before the call returns
+        PCP_CUDA_OK(cudaMemcpyAsync(c->d_jobs + c->d_count, c->jobs.data() + c->d_count, (size_t)(n - c->d_count) * sizeof(PackJob),
+                                    cudaMemcpyHostToDevice, st));
+        c->d_count = n;
+    }
+    PCP_TRY(pack_weight_images(c->d_jobs, n, st));
+    c->fresh = n;
+    return PCP_OK;
+}
+
+// image of the logical (K x N) matrix B[k][n] = W[k*ldw + n] (or W[n*ldw + k], transpose) for tc_gemm
+static int tc_image(const float *W, int K, int N, int ldw, bool transpose, const uint8_t **img, cudaStream_t st)
+{
+    ImgCache *c = g_tc.cache;
+    const size_t bytes = (gemm_b_image_bytes(K, N) + 1023) & ~(size_t)1023;
+    if (c && c->pool) {
+        for (int i = 0; i < (int)c->jobs.size(); ++i) {
+            const PackJob &j = c->jobs[i];
+            if (j.W == W && j.K == K && j.N == N && j.ldw == ldw && j.transpose == (transpose ? 1 : 0)) {
+                if (i >= c->fresh) PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, reinterpret_cast<uint8_t *>(j.img), st));
+                *img = reinterpret_cast<const uint8_t *>(j.img);
+                return PCP_OK;
+            }
+        }
+        if ((int)c->jobs.size() < kImgCacheMaxJobs && c->used + bytes <= c->cap) {
+            PackJob j;
+            j.W = W; j.img = reinterpret_cast<uint16_t *>(c->pool + c->used); j.K = K; j.N = N; j.ldw = ldw; j.transpose = transpose ? 1 : 0;
+            j.bnt = tc_gemm_bn_tile(N);
+            c->used += bytes;
+            c->jobs.push_back(j);
+            PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, reinterpret_cast<uint8_t *>(j.img), st));
+            *img = reinterpret_cast<const uint8_t *>(j.img);
+            return PCP_OK;
+        }
+    }
+    PCP_REQUIRE(bytes <= g_tc.img_bytes, PCP_ERR_UNSUPPORTED, "tc_image: %d x %d does not fit the scratch image", K, N);
+    PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, g_tc.img, st));
+    *img = g_tc.img;
+    return PCP_OK;
+}
+// scratch of the column reductions' per-block partial sums (TrainState::colparts; colparts_doubles() doubles)
+static thread_local double *g_colparts = nullptr;
 
 // Data-parallel BatchNorm: every batch-statistics reduction of the step is summed over the ranks through the
 // host's callback before it is used, so a data-parallel step computes the single-device step on the concatenated batch.
@@ -744,12 +1030,18 @@ static int mm_nn(const float *A, int64_t rows, int cin, const float *W, int ldw,
                  int groups = 1, int64_t bias_stride = 0)
 {
     if (g_tc.on && cin % 64 == 0 && (cout <= 128 || cout % 128 == 0) && gemm_b_image_bytes(cin, cout) <= g_tc.img_bytes) {
-        PCP_TRY(pack_weight_image(W, cin, cout, ldw, false, g_tc.img, st));
         TcGemmParams p;
+        PCP_TRY(tc_image(W, cin, cout, ldw, false, &p.Bimg, st));
         const int64_t rpg = rows / groups;
-        p.A = A; p.a_f32 = 1; p.lda = cin; p.a_group_stride = rpg * cin; p.Bimg = g_tc.img; p.bias = bias; p.bias_group_stride = bias_stride;
+        p.A = A; p.a_f32 = 1; p.lda = cin; p.a_group_stride = rpg * cin; p.bias = bias; p.bias_group_stride = bias_stride;
         p.C32 = Cc; p.ldc = cout; p.c_group_stride = rpg * cout; p.M = (int)rpg; p.N = cout; p.K = cin; p.groups = groups;
         return tc_gemm(p, st);
+    }
+    if (cin == 3 && groups == 1 && cout % 4 == 0 && ldw % 4 == 0 &&
+        (((uintptr_t)W | (uintptr_t)Cc | (uintptr_t)(bias ? bias : W)) & 15u) == 0) {
+        mm3_kernel<<<grid_for(rows * (cout / 4)), 256, 0, st>>>(A, W, ldw, bias, rows, cout / 4, reinterpret_cast<float4 *>(Cc));
+        PCP_CHECK_LAUNCH();
+        return PCP_OK;
     }
     GemmArgs g;
     g.A = A; g.lda = cin; g.B = W; g.ldb = ldw; g.C = Cc; g.ldc = cout; g.bias = bias; g.N = cout; g.K = cin;
@@ -765,10 +1057,20 @@ static int mm_nn(const float *A, int64_t rows, int cin, const float *W, int ldw,
 static int mm_nt(const float *dZ, int64_t rows, int cout, const float *W, int ldw, int cin, float *dA, bool accumulate, cudaStream_t st)
 {
     if (g_tc.on && cout % 64 == 0 && (cin <= 128 || cin % 128 == 0) && gemm_b_image_bytes(cout, cin) <= g_tc.img_bytes) {
-        PCP_TRY(pack_weight_image(W, cout, cin, ldw, true, g_tc.img, st));
         TcGemmParams p;
-        p.A = dZ; p.a_f32 = 1; p.lda = cout; p.Bimg = g_tc.img; p.C32 = dA; p.ldc = cin; p.M = (int)rows; p.N = cin; p.K = cout;
+        PCP_TRY(tc_image(W, cout, cin, ldw, true, &p.Bimg, st));
+        p.A = dZ; p.a_f32 = 1; p.lda = cout; p.C32 = dA; p.ldc = cin; p.M = (int)rows; p.N = cin; p.K = cout;
         p.accumulate = accumulate ? 1 : 0;
+        // few row tiles and a long contraction (the T-Net tails' 4096 -> 256): deal the k-tiles over CTAs
+        const int kt = cout / 64;
+        if (rows <= 512 && kt >= 16) {
+            int ks = 16;
+            while (kt % ks) ks >>= 1;
+            if (ks > 1) {
+                if (!accumulate) PCP_CUDA_OK(cudaMemsetAsync(dA, 0, (size_t)rows * cin * sizeof(float), st));
+                p.ksplit = ks; p.accumulate = 0;
+            }
+        }
         return tc_gemm(p, st);
     }
     GemmArgs g;
@@ -781,8 +1083,11 @@ static int mm_tn(const float *A, int64_t rows, int cin, const float *dZ, int cou
 {
     if (g_tc.on && cin % 8 == 0 && cout % 8 == 0 && ((((uintptr_t)A | (uintptr_t)dZ) & 15u) == 0))
         return tc_wgrad(A, cin, rows, cin, dZ, cout, cout, dW, lddw, st);
-    if (cin == 3 && lddw == cout && colmap4_ok(cout) && (((uintptr_t)dZ & 15u) == 0)) {
-        wgrad3_kernel<<<grid_for(rows, 64, 4), 256, 0, st>>>(A, reinterpret_cast<const float4 *>(dZ), rows, cout, dW);
+    if (cin == 3 && lddw == cout && colmap4_ok(cout) && (((uintptr_t)dZ & 15u) == 0) && g_colparts) {
+        const int np = grid_for(rows, 64, colred_waves());
+        wgrad3_kernel<<<np, 256, 0, st>>>(A, reinterpret_cast<const float4 *>(dZ), rows, cout, g_colparts);
+        PCP_CHECK_LAUNCH();
+        reduce_parts_kernel<<<3 * cout, 256, 0, st>>>(g_colparts, np, 3 * cout, nullptr, nullptr, nullptr, 0, dW);
         PCP_CHECK_LAUNCH();
         return PCP_OK;
     }
@@ -806,18 +1111,26 @@ static inline float *grad(pcp_model *m, int ti) { return m->d_grads + m->tensors
 static int bn_prepare(pcp_model *m, TL &t, cudaStream_t st)
 {
     const LayerSpec &S = m->layers[t.id];
+    const double *parts = t.red;
+    int np = 1;
     if (t.batch) {
-        PCP_CUDA_OK(cudaMemsetAsync(t.red, 0, (size_t)t.cout * 16, st));
+        np = grid_for(t.rows, 64, colred_waves());
         if (colmap4_ok(t.cout))
-            colstats4_kernel<<<grid_for(t.rows, 64, 4), 256, 0, st>>>(reinterpret_cast<const float4 *>(t.Z), t.rows, t.cout, t.red, t.red + t.cout);
+            colstats4_kernel<<<np, 256, 0, st>>>(reinterpret_cast<const float4 *>(t.Z), t.rows, t.cout, g_colparts);
         else
-            colstats_kernel<<<grid_for(t.rows, 64, 4), 256, 0, st>>>(t.Z, t.rows, t.cout, t.red, t.red + t.cout);
+            colstats_kernel<<<np, 256, 0, st>>>(t.Z, t.rows, t.cout, g_colparts);
         PCP_CHECK_LAUNCH();
+        parts = g_colparts;
+        if (g_sync.fn) {             // the ranks exchange the reduced sums
+            reduce_parts_kernel<<<2 * t.cout, 256, 0, st>>>(g_colparts, np, 2 * t.cout, t.red, nullptr, nullptr, 0, nullptr);
+            PCP_CHECK_LAUNCH();
+            PCP_TRY(sync_sum(t.red, (size_t)t.cout * 2, 1, st));
+            parts = t.red; np = 1;
+        }
     }
-    if (t.batch) PCP_TRY(sync_sum(t.red, (size_t)t.cout * 2, 1, st));
-    bn_finalize_kernel<<<(t.cout + 127) / 128, 128, 0, st>>>(t.red, t.red + t.cout, (double)t.rows * g_sync.scale, t.cout, t.batch ? 1 : 0, param(m, S.t_gamma),
-                                                           param(m, S.t_beta), param(m, S.t_mean), param(m, S.t_var), t.mean, t.inv, t.sc,
-                                                           t.beta, kBnEpsT, kBnMomentum);
+    bn_finalize_kernel<<<t.cout, 256, 0, st>>>(parts, np, (double)t.rows * g_sync.scale, t.cout, t.batch ? 1 : 0, param(m, S.t_gamma),
+                                                        param(m, S.t_beta), param(m, S.t_mean), param(m, S.t_var), t.mean, t.inv, t.sc, t.beta,
+                                                        kBnEpsT, kBnMomentum);
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -840,6 +1153,93 @@ static int layer_fwd_train(pcp_model *m, TL &t, const float *A, float *Y, cudaSt
     return PCP_OK;
 }
 
+// X = pc @ R per cloud (PointNet.py:207), 3 x 3: one thread per point, the fma order of the generic GEMM it replaces
+__global__ void __launch_bounds__(256)
+pc_matmul3_kernel(const float *__restrict__ X, const float *__restrict__ R, int64_t n, int64_t total, float *__restrict__ Y)
+{
+    for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < total; p += (int64_t)gridDim.x * blockDim.x) {
+        const float *r = R + (p / n) * 9;
+        const float x0 = __ldg(X + 3 * p), x1 = __ldg(X + 3 * p + 1), x2 = __ldg(X + 3 * p + 2);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) Y[3 * p + j] = fmaf(x2, __ldg(r + 6 + j), fmaf(x1, __ldg(r + 3 + j), x0 * __ldg(r + j)));
+    }
+}
+
+// dR[g] (3 x 3) += X[g]^T (3 x n) . dX[g] (n x 3): one block per cloud (a 128 x 64 GEMM tile per cloud took 146 us for this)
+__global__ void __launch_bounds__(256)
+atb3_kernel(const float *__restrict__ X, const float *__restrict__ dX, int64_t n, float *__restrict__ dR)
+{
+    __shared__ float sh[8][9];
+    const float *x = X + (int64_t)blockIdx.x * n * 3, *d = dX + (int64_t)blockIdx.x * n * 3;
+    float acc[9] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int64_t r = threadIdx.x; r < n; r += 256) {
+        const float xv[3] = {__ldg(x + 3 * r), __ldg(x + 3 * r + 1), __ldg(x + 3 * r + 2)};
+        const float dv[3] = {__ldg(d + 3 * r), __ldg(d + 3 * r + 1), __ldg(d + 3 * r + 2)};
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) acc[i * 3 + j] = fmaf(xv[i], dv[j], acc[i * 3 + j]);
+    }
+#pragma unroll
+    for (int e = 0; e < 9; ++e) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], o);
+        if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5][e] = acc[e];
+    }
+    __syncthreads();
+    if (threadIdx.x < 9) {
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) v += sh[w][threadIdx.x];
+        dR[(int64_t)blockIdx.x * 9 + threadIdx.x] += v;
+    }
+}
+
+// bf16 copy of an fp32 activation (n4 groups of four): lets a GEMM over it take the persistent TMA kernel
+__global__ void __launch_bounds__(256)
+to_bf16_kernel(const float4 *__restrict__ X, int64_t n4, uint2 *__restrict__ Y)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldg(X + i);
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        Y[i] = make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
+    }
+}
+
+// out[g, c] = beta[c] - sc[c] * mean[c] (+ sc[c] * add[g, c]): what a frozen BatchNorm leaves of itself once sc is folded into
+// the layer's weight image — relu(sc * (a . W + add - mean) + beta) = relu(a . (W sc) + out)
+__global__ void __launch_bounds__(256)
+frozen_shift_kernel(BnP p, int C, const float *__restrict__ add, int groups, float *__restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= groups * C) return;
+    const int c = i % C;
+    float v = fmaf(-p.sc[c], p.mean[c], p.beta[c]);
+    if (add) v = fmaf(p.sc[c], add[i], v);
+    out[i] = v;
+}
+
+// Forward of a BN layer that runs on its MOVING statistics (keras: not trainable) when nothing will be differentiated
+// through it: BatchNorm and ReLU ride in the GEMM (scaled weight image, shift + relu epilogue), the output is bf16 — what
+// the next GEMM reads anyway — and the pre-activation Z is never written.  A: rows x cin (fp32 or bf16), W: first cin rows
+// of the layer's kernel; add: optional per-group pre-BN bias (groups x cout), shift: groups x cout floats of scratch.
+static int frozen_layer_fwd16(pcp_model *m, TL &t, const void *A, int a_f32, int cin, const float *add, int groups, float *shift,
+                              __nv_bfloat16 *Y, cudaStream_t st)
+{
+    const LayerSpec &S = m->layers[t.id];
+    PCP_TRY(bn_prepare(m, t, st));
+    frozen_shift_kernel<<<(groups * t.cout + 255) / 256, 256, 0, st>>>(t.bnp(), t.cout, add, groups, shift);
+    PCP_CHECK_LAUNCH();
+    PCP_REQUIRE(gemm_b_image_bytes(cin, t.cout) <= g_tc.img_bytes, PCP_ERR_UNSUPPORTED, "frozen layer: weight image too large");
+    PCP_TRY(pack_weight_image(param(m, S.t_kernel), cin, t.cout, t.cout, false, g_tc.img, st, t.sc));
+    TcGemmParams p;
+    const int64_t rpg = t.rows / groups;
+    p.A = A; p.a_f32 = a_f32; p.lda = cin; p.a_group_stride = rpg * cin; p.Bimg = g_tc.img; p.bias = shift;
+    p.bias_group_stride = groups > 1 ? t.cout : 0; p.C16 = Y; p.ldc = t.cout; p.c_group_stride = rpg * t.cout;
+    p.M = (int)rpg; p.N = t.cout; p.K = cin; p.groups = groups; p.relu = 1;
+    return tc_gemm(p, st);
+}
+
 // reduce_max over the points of each cloud of relu(bn(Z))
 static int pool_fwd(const TL &t, int b, int64_t n, float *g, cudaStream_t st)
 {
@@ -856,21 +1256,26 @@ static int bn_bwd(pcp_model *m, TL &t, float *G, bool relu, cudaStream_t st)
     const LayerSpec &S = m->layers[t.id];
     const int64_t n4 = t.rows * t.cout / 4;
     if (t.batch) {
-        PCP_CUDA_OK(cudaMemsetAsync(t.red, 0, (size_t)t.cout * 16, st));
+        const int np = grid_for(t.rows, 64, colred_waves());
         if (colmap4_ok(t.cout))
-            bn_bwd_reduce4_kernel<<<grid_for(t.rows, 64, 4), 256, 0, st>>>(reinterpret_cast<const float4 *>(G), reinterpret_cast<const float4 *>(t.Z),
-                                                                           t.rows, t.cout, t.bnp(), relu ? 1 : 0, t.red, t.red + t.cout);
+            bn_bwd_reduce4_kernel<<<np, 256, 0, st>>>(reinterpret_cast<const float4 *>(G), reinterpret_cast<const float4 *>(t.Z), t.rows, t.cout, t.bnp(),
+                                                     relu ? 1 : 0, g_colparts);
         else
-            bn_bwd_reduce_kernel<<<grid_for(t.rows, 64, 4), 256, 0, st>>>(G, t.Z, t.rows, t.cout, t.bnp(), relu ? 1 : 0, t.red, t.red + t.cout);
+            bn_bwd_reduce_kernel<<<np, 256, 0, st>>>(G, t.Z, t.rows, t.cout, t.bnp(), relu ? 1 : 0, g_colparts);
         PCP_CHECK_LAUNCH();
-        if (t.trainable) {
-            store_bn_grads_kernel<<<(t.cout + 127) / 128, 128, 0, st>>>(t.red, t.red + t.cout, t.cout, grad(m, S.t_gamma), grad(m, S.t_beta));
-            PCP_CHECK_LAUNCH();
-        }
+        // s1 | s2 into t.red, and this rank's dbeta = s1, dgamma = s2 when the layer trains
+        reduce_parts_kernel<<<2 * t.cout, 256, 0, st>>>(g_colparts, np, 2 * t.cout, t.red, t.trainable ? grad(m, S.t_beta) : nullptr,
+                                                                 t.trainable ? grad(m, S.t_gamma) : nullptr, t.cout, nullptr);
+        PCP_CHECK_LAUNCH();
     }
     if (t.batch) PCP_TRY(sync_sum(t.red, (size_t)t.cout * 2, 1, st));          // after the LOCAL sums became dgamma / dbeta
-    bn_bwd_apply_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(G), reinterpret_cast<const float4 *>(t.Z), n4, t.cout / 4, t.bnp(),
-                                                     relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, (float)(1.0 / ((double)t.rows * g_sync.scale)));
+    const float inv_rows = (float)(1.0 / ((double)t.rows * g_sync.scale));
+    if (colmap4_ok(t.cout))
+        bn_bwd_apply4_kernel<<<grid_for(n4, 512), 256, 0, st>>>(reinterpret_cast<float4 *>(G), reinterpret_cast<const float4 *>(t.Z), t.rows, t.cout, t.bnp(),
+                                                               relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, inv_rows);
+    else
+        bn_bwd_apply_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(G), reinterpret_cast<const float4 *>(t.Z), n4, t.cout / 4, t.bnp(),
+                                                         relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, inv_rows);
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -978,6 +1383,10 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     if (!ts->tc_img) PCP_CUDA_OK(cudaMalloc(&ts->tc_img, kImgBytes));
     g_tc.on = m->desc.precision == PCP_PRECISION_BF16;
     g_tc.img = ts->tc_img; g_tc.img_bytes = kImgBytes;
+    static const bool no_img_cache = getenv("PCP_TRAIN_NO_IMG_CACHE") != nullptr;
+    g_tc.cache = (g_tc.on && !no_img_cache) ? &ts->img_cache : nullptr;
+    if (g_tc.cache) PCP_TRY(img_cache_refresh(g_tc.cache, st));
+    g_colparts = ts->colparts;
     g_sync = SyncCtx();
     if (ts->sync_fn && global_batch > b) { g_sync.fn = ts->sync_fn; g_sync.user = ts->sync_user; g_sync.scale = (double)global_batch / (double)b; }
     const int64_t M = (int64_t)b * n;
@@ -1007,10 +1416,8 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         PCP_TRY(layer_fwd_train(m, L[L_IT_C2], ts->Y64a, ts->Y128, st));                                // :424
         PCP_TRY(pooled_layer_fwd(m, ts, L_IT_C3, 0, ts->Y128, ts->g1, st));                             // :425-429
         PCP_TRY(tnet_tail_fwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, ts->g1, ts->Ys[0], ts->Ys[1], ts->R, st));
-        GemmArgs g;                                                                                     // X = pc @ R  :207
-        g.A = ts->pcn; g.lda = 3; g.strideA = n * 3; g.B = ts->R; g.ldb = 3; g.strideB = 9;
-        g.C = ts->X3; g.ldc = 3; g.strideC = n * 3; g.M = (int)n; g.N = 3; g.K = 3; g.groups = b;
-        PCP_TRY(gemm_f32(g, st));
+        pc_matmul3_kernel<<<grid_for(M), 256, 0, st>>>(ts->pcn, ts->R, n, M, ts->X3);                    // X = pc @ R  :207
+        PCP_CHECK_LAUNCH();
         X3 = ts->X3;
     } else {
         PCP_TRY(model_eye3(ts->R, b, st));
@@ -1058,14 +1465,38 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     float *dlog_cls = ts->dsmall[2];
     PCP_REQUIRE(C <= 4096 && P <= 4096, PCP_ERR_UNSUPPORTED, "training supports up to 4096 classes / parts");
     if (y_cls) {
-        softmax_ce_kernel<<<grid_for(b, 256, 1), 256, 0, st>>>(ts->cls_logits, b, C, y_cls, cfg->w_cls / (float)global_batch, ts->cls_prob, dlog_cls,
-                                                               ts->metrics + 0, ts->metrics + 4);
-        PCP_CHECK_LAUNCH();
+        PCP_TRY(softmax_ce(ts->cls_logits, b, C, y_cls, cfg->w_cls / (float)global_batch, ts->cls_prob, dlog_cls,
+                                                               ts->metrics + 0, ts->metrics + 4, st));
     }
 
     // ---- segmentation head (:268-290): concat([X_64, tile(global)]) . W1 = X_64 . W1[0:64] + global . W1[64:1088] ----
     ts->have_seg = seg_needed;
-    if (seg_needed) {
+    // nothing is differentiated through a frozen head whose loss is not weighted: it runs in its inference form (moving
+    // statistics folded into the GEMMs, bf16 activations, no Z) — the classification_pretrain profile of BASELINE config 3
+    bool seg_frozen_fwd = seg_needed && !do_seg_bwd && g_tc.on && (P <= 128);
+    for (int i = L_SEG1; i <= L_SEG4; ++i) seg_frozen_fwd = seg_frozen_fwd && L[i].has_bn && !L[i].batch;
+    if (seg_frozen_fwd) {
+        const LayerSpec &S1 = m->layers[L_SEG1], &S5 = m->layers[L_SEG5];
+        __nv_bfloat16 *y512 = reinterpret_cast<__nv_bfloat16 *>(ts->Y512), *y256 = reinterpret_cast<__nv_bfloat16 *>(ts->Y256),
+                      *y128a = reinterpret_cast<__nv_bfloat16 *>(ts->Y128), *y128b = reinterpret_cast<__nv_bfloat16 *>(ts->Y128b);
+        PCP_TRY(mm_nn(ts->g3, b, 1024, param(m, S1.t_kernel) + (size_t)64 * 512, 512, 512, ts->gvec, nullptr, st));
+        // X_64 as bf16 first: the 64 -> 512 layer then streams it through TMA instead of converting it once per column block
+        __nv_bfloat16 *x16 = reinterpret_cast<__nv_bfloat16 *>(ts->Y64b);
+        to_bf16_kernel<<<grid_for(M * 16), 256, 0, st>>>(reinterpret_cast<const float4 *>(X64), M * 16, reinterpret_cast<uint2 *>(x16));
+        PCP_CHECK_LAUNCH();
+        PCP_TRY(frozen_layer_fwd16(m, L[L_SEG1], x16, 0, 64, ts->gvec, b, ts->dgvec, y512, st));
+        PCP_TRY(frozen_layer_fwd16(m, L[L_SEG2], y512, 0, 512, nullptr, 1, ts->fshift, y256, st));
+        PCP_TRY(frozen_layer_fwd16(m, L[L_SEG3], y256, 0, 256, nullptr, 1, ts->fshift, y128a, st));
+        PCP_TRY(frozen_layer_fwd16(m, L[L_SEG4], y128a, 0, 128, nullptr, 1, ts->fshift, y128b, st));
+        TcGemmParams p;
+        PCP_TRY(tc_image(param(m, S5.t_kernel), 128, P, P, false, &p.Bimg, st));
+        p.A = y128b; p.a_f32 = 0; p.lda = 128; p.bias = param(m, S5.t_bias); p.C32 = ts->seg_logits; p.ldc = P;
+        p.M = (int)M; p.N = P; p.K = 128;
+        PCP_TRY(tc_gemm(p, st));
+        if (y_seg) {
+            PCP_TRY(softmax_ce(ts->seg_logits, M, P, y_seg, 0.f, ts->seg_prob, nullptr, ts->metrics + 1, ts->metrics + 5, st));
+        }
+    } else if (seg_needed) {
         const LayerSpec &S1 = m->layers[L_SEG1];
         PCP_TRY(mm_nn(ts->g3, b, 1024, param(m, S1.t_kernel) + (size_t)64 * 512, 512, 512, ts->gvec, nullptr, st));
         TL &t1 = L[L_SEG1];
@@ -1078,9 +1509,8 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         const LayerSpec &S5 = m->layers[L_SEG5];
         PCP_TRY(mm_nn(ts->Y128b, M, 128, param(m, S5.t_kernel), P, P, ts->seg_logits, param(m, S5.t_bias), st));
         if (y_seg) {
-            softmax_ce_kernel<<<grid_for(M), 256, 0, st>>>(ts->seg_logits, M, P, y_seg, cfg->w_seg / ((float)global_batch * (float)n), ts->seg_prob,
-                                                           do_seg_bwd ? ts->GP : nullptr, ts->metrics + 1, ts->metrics + 5);
-            PCP_CHECK_LAUNCH();
+            PCP_TRY(softmax_ce(ts->seg_logits, M, P, y_seg, cfg->w_seg / ((float)global_batch * (float)n), ts->seg_prob,
+                                                           do_seg_bwd ? ts->GP : nullptr, ts->metrics + 1, ts->metrics + 5, st));
         }
     }
 
@@ -1174,7 +1604,11 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
             // X_64 = X @ R_64: dR_64 = X^T . dX_64 per cloud ; dX = dX_64 . R_64^T
             GemmArgs g;
             g.A = ts->X2; g.lda = 64; g.strideA = n * 64; g.transA = 1; g.B = ts->dX64; g.ldb = 64; g.strideB = n * 64;
-            g.C = ts->dR64; g.ldc = 64; g.strideC = 4096; g.M = 64; g.N = 64; g.K = (int)n; g.groups = b; g.accumulate = 1;
+            g.C = ts->dR64; g.ldc = 64; g.strideC = 4096; g.M = 64; g.N = 64; g.K = (int)n; g.groups = b;
+            // one 64 x 64 tile per cloud leaves the device idle (173 us at 256 clouds): split the points, atomics into the
+            // zero-initialised (+ regulariser) dR64, like every other weight-gradient reduction of the step
+            g.splitk = (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(n / 128, 65535 / std::max(b, 1)), (8 * (int64_t)sm_count() + b - 1) / b));
+            if (g.splitk == 1) g.accumulate = 1;
             PCP_TRY(gemm_f32(g, st));
             GemmArgs h;
             h.A = ts->dX64; h.lda = 64; h.strideA = n * 64; h.B = ts->R64; h.ldb = 64; h.strideB = 4096; h.transB = 1;
@@ -1198,10 +1632,8 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         PCP_TRY(layer_bwd_mm(m, L[L_S1_1], X3, ts->G64b, (full && tr_it) ? ts->dX3 : nullptr, false, st));
         if (full && tr_it) {
             // X = pc @ R: dR += pc^T . dX per cloud
-            GemmArgs g;
-            g.A = ts->pcn; g.lda = 3; g.strideA = n * 3; g.transA = 1; g.B = ts->dX3; g.ldb = 3; g.strideB = n * 3;
-            g.C = ts->dR; g.ldc = 3; g.strideC = 9; g.M = 3; g.N = 3; g.K = (int)n; g.groups = b; g.accumulate = 1;
-            PCP_TRY(gemm_f32(g, st));
+            atb3_kernel<<<b, 256, 0, st>>>(ts->pcn, ts->dX3, n, ts->dR);
+            PCP_CHECK_LAUNCH();
         }
     }
     if (full && tr_it) {
@@ -1268,7 +1700,7 @@ extern "C" int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, con
     want(&dg, bc * 4); want(&g, bc * 4); want(&dWg, (size_t)128 * cout * 4); want(&dgam, cout * 4); want(&dbet, cout * 4); want(&dAo, rows * 512);
     want(&img, (size_t)4 << 20);
     want(&L.mean, cout * 4); want(&L.inv, cout * 4); want(&L.sc, cout * 4); want(&L.beta, cout * 4); want(&L.red, (size_t)cout * 16);
-    want(&L.pb.gram_parts, tc_gram_scratch_floats(128) * 4);
+    want(&L.pb.gram_parts, tc_gram_scratch_floats(128) * 4); want(&L.pb.colparts, (size_t)sm_count() * 4 * 128 * 8);
     want(&L.pb.ext, bc * 16); want(&L.pb.gram, 128 * 128 * 4); want(&L.pb.asum, 128 * 8); want(&L.pb.gram_g, 128 * 128 * 4); want(&L.pb.asum_g, 128 * 8); want(&L.pb.zsel, bc * 4); want(&L.pb.arg, bc * 4);
     want(&L.pb.S, bc * 4); want(&L.pb.c0, cout * 4); want(&L.pb.c1, cout * 4); want(&L.pb.Wt, (size_t)cout * 512); want(&L.pb.Q, 128 * 128 * 4);
     want(&L.pb.q, 512);
@@ -1288,6 +1720,7 @@ extern "C" int pcp_selftest_pooled_layer(const float *h_a, const float *h_w, con
         PCP_CUDA_OK(cudaMemcpy(dg, h_dg, bc * 4, cudaMemcpyHostToDevice));
         std::vector<float> ones(cout, 1.f);
         PCP_CUDA_OK(cudaMemcpy(mv, ones.data(), cout * 4, cudaMemcpyHostToDevice));
+        g_tc = TcCtx();                    // thread-local: a training step on this thread leaves its own context behind
         g_tc.on = true; g_tc.img = img; g_tc.img_bytes = (size_t)4 << 20;
         g_sync = SyncCtx();
         if (s_selftest_sync.fn) g_sync = s_selftest_sync;
@@ -1422,12 +1855,10 @@ extern "C" int pcp_model_evaluate(pcp_model *m, const float *d_x, int b, int64_t
     m->eval_reg_acc = nullptr;
     if (frc != PCP_OK) return frc;
     if (d_y_cls) {
-        softmax_ce_kernel<<<grid_for(b, 256, 1), 256, 0, st>>>(cls_logits, b, C, d_y_cls, 0.f, nullptr, nullptr, met + 0, met + 4);
-        PCP_CHECK_LAUNCH();
+        PCP_TRY(softmax_ce(cls_logits, b, C, d_y_cls, 0.f, nullptr, nullptr, met + 0, met + 4, st));
     }
     if (want_seg) {
-        softmax_ce_kernel<<<grid_for(M), 256, 0, st>>>(seg_logits, M, P, d_y_seg, 0.f, nullptr, nullptr, met + 1, met + 5);
-        PCP_CHECK_LAUNCH();
+        PCP_TRY(softmax_ce(seg_logits, M, P, d_y_seg, 0.f, nullptr, nullptr, met + 1, met + 5, st));
     }
     if (d_y_se3) {
         mse_kernel<<<grid_for((int64_t)b * 9, 256, 1), 256, 0, st>>>(R, d_y_se3, (int64_t)b * 9, 0.f, nullptr, met + 2);

@@ -24,8 +24,9 @@ __device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(_
 
 // asum[k] += sum over rows of bf16(A[r, k])          (cin == 128: 32 float4 columns x 8 row lanes, two rows in flight)
 __global__ void __launch_bounds__(256)
-pool_colsum_kernel(const float *__restrict__ A, int64_t rows, double *__restrict__ asum)
+pool_colsum_kernel(const float *__restrict__ A, int64_t rows, double *__restrict__ parts)
 {
+    double *asum = parts + (size_t)blockIdx.x * 128;
     const int c4 = threadIdx.x & 31, lane = threadIdx.x >> 5;
     const float4 *A4 = reinterpret_cast<const float4 *>(A);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -37,8 +38,8 @@ pool_colsum_kernel(const float *__restrict__ A, int64_t rows, double *__restrict
         add(v0); add(v1);
     }
     for (; r < rows; r += step) add(__ldg(A4 + r * 32 + c4));
-    // the eight row lanes of the block first (shared memory), then 128 atomics per block: 1024 per block on the same 128 words
-    // serialised in the L2 (0.17 ms per layer)
+    // the eight row lanes of the block first (shared memory), then the block's 128 partial sums (reduce_parts_kernel adds the
+    // blocks up: 1024 atomics per block on the same 128 words serialised in the L2 for 0.17 ms per layer, 128 still for 25 us)
     __shared__ float4 part[8][32];
     part[lane][c4] = acc;
     __syncthreads();
@@ -46,7 +47,7 @@ pool_colsum_kernel(const float *__restrict__ A, int64_t rows, double *__restrict
         double sx = 0, sy = 0, sz = 0, sw = 0;
 #pragma unroll
         for (int l = 0; l < 8; ++l) { const float4 v = part[l][c4]; sx += v.x; sy += v.y; sz += v.z; sw += v.w; }
-        atomicAdd(asum + c4 * 4, sx); atomicAdd(asum + c4 * 4 + 1, sy); atomicAdd(asum + c4 * 4 + 2, sz); atomicAdd(asum + c4 * 4 + 3, sw);
+        asum[c4 * 4] = sx; asum[c4 * 4 + 1] = sy; asum[c4 * 4 + 2] = sz; asum[c4 * 4 + 3] = sw;
     }
 }
 
@@ -254,13 +255,16 @@ static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStre
 {
     const int64_t rows = (int64_t)L.b * L.n, total = (int64_t)L.b * L.cout;
     PCP_CUDA_OK(cudaMemsetAsync(L.pb.ext, 0, (size_t)total * 16, st));
-    PCP_TRY(pack_weight_image(L.W, 128, L.cout, L.cout, false, g_tc.img, st));
-    PCP_TRY(tc_pool_extrema(A, L.b, L.n, g_tc.img, L.cout, L.pb.ext, L.pb.ext + total, st));
+    const uint8_t *wimg = nullptr;
+    PCP_TRY(tc_image(L.W, 128, L.cout, L.cout, false, &wimg, st));
+    PCP_TRY(tc_pool_extrema(A, L.b, L.n, wimg, L.cout, L.pb.ext, L.pb.ext + total, st));
     if (L.batch) {
-        PCP_CUDA_OK(cudaMemsetAsync(L.pb.asum, 0, 128 * 8, st));
         // the Gram matrix feeds the layer's batch statistics, i.e. the FORWARD: it has to be the same bits on every run
         PCP_TRY(tc_gram_det(A, 128, rows, 128, L.pb.gram, L.pb.gram_parts, tc_gram_scratch_floats(128), st));
-        pool_colsum_kernel<<<(int)std::min<int64_t>((rows + 7) / 8, (int64_t)sm_count() * 4), 256, 0, st>>>(A, rows, L.pb.asum);
+        const int np = (int)std::min<int64_t>((rows + 7) / 8, (int64_t)sm_count() * 4);
+        pool_colsum_kernel<<<np, 256, 0, st>>>(A, rows, L.pb.colparts);
+        PCP_CHECK_LAUNCH();
+        reduce_parts_kernel<<<128, 256, 0, st>>>(L.pb.colparts, np, 128, L.pb.asum, nullptr, nullptr, 0, nullptr);
         PCP_CHECK_LAUNCH();
         // statistics use the Gram matrix / column sums of the CONCATENATED batch (sync-BN); dW below keeps this rank's
         const float *gram_s = L.pb.gram;
@@ -275,8 +279,8 @@ static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStre
         pool_implicit_stats_kernel<<<(L.cout + 3) / 4, 128, 0, st>>>(gram_s, asum_s, L.W, L.cout, L.red, L.red + L.cout);
         PCP_CHECK_LAUNCH();
     }
-    bn_finalize_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(L.red, L.red + L.cout, (double)rows * g_sync.scale, L.cout, L.batch ? 1 : 0, L.gamma, L.beta_in,
-                                                           L.mov_mean, L.mov_var, L.mean, L.inv, L.sc, L.beta, kBnEpsT, kBnMomentum);
+    bn_finalize_kernel<<<L.cout, 256, 0, st>>>(L.red, 1, (double)rows * g_sync.scale, L.cout, L.batch ? 1 : 0, L.gamma, L.beta_in, L.mov_mean,
+                                                        L.mov_var, L.mean, L.inv, L.sc, L.beta, kBnEpsT, kBnMomentum);
     PCP_CHECK_LAUNCH();
     pool_select_kernel<<<grid_for(total), 256, 0, st>>>(L.pb.ext, L.pb.ext + total, L.bnp(), total, L.cout, g, L.pb.zsel, L.pb.arg);
     PCP_CHECK_LAUNCH();

@@ -316,8 +316,9 @@ def check_bf16_step_against_noise_floor(m, p, x, y, masks, vanilla, trainable, w
     (out, loss, gref, stats), (out_p, loss_p, gref_p, _) = bf16_oracle_pair(x, y, masks, p, vanilla, trainable, weights, reg)
     assert abs(met["loss"] - loss) <= 2e-2 * max(1.0, abs(loss)), (met["loss"], loss)
     dev = {"cls": m.train_output(0, b * C).reshape(b, C), "R": m.train_output(2, b * 9).reshape(b, 3, 3)}
-    if weights[1] != 0.0 or trainable["seg"]:            # the step may skip a frozen, unweighted segmentation head
-        dev["seg"] = m.train_output(1, b * n * P).reshape(b, n, P)
+    # a frozen, unweighted segmentation head is still evaluated (keras reports its loss): it takes the inference-form
+    # forward of train.cu:seg_head_fwd_frozen, held to the same oracle output
+    dev["seg"] = m.train_output(1, b * n * P).reshape(b, n, P)
     report = {}
     for k, v in dev.items():
         e_dev, e_self = rel_err(v, out[k]), rel_err(out_p[k], out[k])
