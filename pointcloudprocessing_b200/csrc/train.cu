@@ -766,6 +766,7 @@ struct PoolBufs {
 struct TL {                       // one weighted layer's training record
     int id = -1;
     float *Z = nullptr;           // pre-BN output (rows x cout)
+    float *Y = nullptr;           // relu(bn(Z)) kept for the backward pass (trunk layers; 0.7 GB at 256 x 1024 instead of seven recomputations)
     int64_t rows = 0;
     int cin = 0, cout = 0;
     bool has_bn = false, batch = false, trainable = false;
@@ -877,6 +878,8 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
         t.id = i; t.rows = per_point ? M : b; t.cin = S.cin; t.cout = S.cout; t.has_bn = S.has_bn;
         const bool pooled = (i == L_IT_C3 || i == L_FT_C3 || i == L_S2_3);
         if (i != L_SEG5 && i != L_CLS3 && !(pooled && ts->implicit_pool)) want(&t.Z, (size_t)t.rows * S.cout * 4);
+        if (i == L_IT_C1 || i == L_IT_C2 || i == L_S1_1 || i == L_FT_C1 || i == L_FT_C2 || i == L_S2_1 || i == L_S2_2)
+            want(&t.Y, (size_t)t.rows * S.cout * 4);
         if (S.has_bn) {
             want(&t.mean, S.cout * 4); want(&t.inv, S.cout * 4); want(&t.sc, S.cout * 4); want(&t.beta, S.cout * 4);
             want(&t.red, (size_t)S.cout * 2 * 8);
@@ -1143,6 +1146,15 @@ static int bn_act(const TL &t, float *Y, cudaStream_t st)
     return PCP_OK;
 }
 
+// the layer's activation relu(bn(Z)) in the backward pass: the forward pass's own copy, else recomputed into scratch
+static int layer_act(const TL &t, float *scratch, const float **Y, cudaStream_t st)
+{
+    if (t.Y) { *Y = t.Y; return PCP_OK; }
+    PCP_TRY(bn_act(t, scratch, st));
+    *Y = scratch;
+    return PCP_OK;
+}
+
 // forward of one BN layer: Z = A . W ; statistics ; optionally Y = relu(bn(Z))
 static int layer_fwd_train(pcp_model *m, TL &t, const float *A, float *Y, cudaStream_t st)
 {
@@ -1337,13 +1349,14 @@ static int pooled_layer_fwd(pcp_model *m, TrainState *ts, int li, int slot, cons
 static int pooled_layer_bwd(pcp_model *m, TrainState *ts, int li, int slot, int lprev, const float *g, const float *dg, float *dA, cudaStream_t st)
 {
     const LayerSpec &S = m->layers[li];
+    const float *Aprev = nullptr;
     if (ts->implicit_pool) {
-        PCP_TRY(bn_act(ts->L[lprev], ts->Y128, st));
-        return pooled_backward(make_pool_layer(m, ts, li, slot), ts->Y128, g, dg, grad(m, S.t_kernel), grad(m, S.t_gamma), grad(m, S.t_beta), dA, st);
+        PCP_TRY(layer_act(ts->L[lprev], ts->Y128, &Aprev, st));
+        return pooled_backward(make_pool_layer(m, ts, li, slot), Aprev, g, dg, grad(m, S.t_kernel), grad(m, S.t_gamma), grad(m, S.t_beta), dA, st);
     }
     PCP_TRY(pool_bwd(m, ts->L[li], ts->b, ts->n, g, dg, ts->cnt, ts->G1024, st));
-    PCP_TRY(bn_act(ts->L[lprev], ts->Y128, st));
-    return layer_bwd_mm(m, ts->L[li], ts->Y128, ts->G1024, dA, false, st);
+    PCP_TRY(layer_act(ts->L[lprev], ts->Y128, &Aprev, st));
+    return layer_bwd_mm(m, ts->L[li], Aprev, ts->G1024, dA, false, st);
 }
 
 // T-Net tail forward (PointNet.py:431-442): g (b x 1024) -> dense 512 -> 256 -> (256 x k^2) + b
@@ -1412,9 +1425,9 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     PCP_TRY(pcp_normalize_f32(d_x, b, n, ts->pcn, nullptr, nullptr, st));                               // PointNet.py:202
     const float *X3 = ts->pcn;
     if (full) {
-        PCP_TRY(layer_fwd_train(m, L[L_IT_C1], ts->pcn, ts->Y64a, st));                                 // TNet.call :423
-        PCP_TRY(layer_fwd_train(m, L[L_IT_C2], ts->Y64a, ts->Y128, st));                                // :424
-        PCP_TRY(pooled_layer_fwd(m, ts, L_IT_C3, 0, ts->Y128, ts->g1, st));                             // :425-429
+        PCP_TRY(layer_fwd_train(m, L[L_IT_C1], ts->pcn, L[L_IT_C1].Y, st));                                 // TNet.call :423
+        PCP_TRY(layer_fwd_train(m, L[L_IT_C2], L[L_IT_C1].Y, L[L_IT_C2].Y, st));                                // :424
+        PCP_TRY(pooled_layer_fwd(m, ts, L_IT_C3, 0, L[L_IT_C2].Y, ts->g1, st));                             // :425-429
         PCP_TRY(tnet_tail_fwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, ts->g1, ts->Ys[0], ts->Ys[1], ts->R, st));
         pc_matmul3_kernel<<<grid_for(M), 256, 0, st>>>(ts->pcn, ts->R, n, M, ts->X3);                    // X = pc @ R  :207
         PCP_CHECK_LAUNCH();
@@ -1422,13 +1435,13 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     } else {
         PCP_TRY(model_eye3(ts->R, b, st));
     }
-    PCP_TRY(layer_fwd_train(m, L[L_S1_1], X3, ts->Y64a, st));                                           // :217
-    PCP_TRY(layer_fwd_train(m, L[L_S1_2], ts->Y64a, ts->X2, st));                                       // :220
+    PCP_TRY(layer_fwd_train(m, L[L_S1_1], X3, L[L_S1_1].Y, st));                                           // :217
+    PCP_TRY(layer_fwd_train(m, L[L_S1_2], L[L_S1_1].Y, ts->X2, st));                                       // :220
     const float *X64 = ts->X2;
     if (full) {
-        PCP_TRY(layer_fwd_train(m, L[L_FT_C1], ts->X2, ts->Y64a, st));
-        PCP_TRY(layer_fwd_train(m, L[L_FT_C2], ts->Y64a, ts->Y128, st));
-        PCP_TRY(pooled_layer_fwd(m, ts, L_FT_C3, 1, ts->Y128, ts->g2, st));
+        PCP_TRY(layer_fwd_train(m, L[L_FT_C1], ts->X2, L[L_FT_C1].Y, st));
+        PCP_TRY(layer_fwd_train(m, L[L_FT_C2], L[L_FT_C1].Y, L[L_FT_C2].Y, st));
+        PCP_TRY(pooled_layer_fwd(m, ts, L_FT_C3, 1, L[L_FT_C2].Y, ts->g2, st));
         PCP_TRY(tnet_tail_fwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, ts->g2, ts->Ys[2], ts->Ys[3], ts->R64, st));   // :227
         GemmArgs g;                                                                                     // X_64 = X @ R_64 :228
         g.A = ts->X2; g.lda = 64; g.strideA = n * 64; g.B = ts->R64; g.ldb = 64; g.strideB = 4096;
@@ -1436,9 +1449,9 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         PCP_TRY(gemm_f32(g, st));
         X64 = ts->X64;
     }
-    PCP_TRY(layer_fwd_train(m, L[L_S2_1], X64, ts->Y64a, st));                                          // :236
-    PCP_TRY(layer_fwd_train(m, L[L_S2_2], ts->Y64a, ts->Y128, st));                                     // :239
-    PCP_TRY(pooled_layer_fwd(m, ts, L_S2_3, 2, ts->Y128, ts->g3, st));                                  // :242-248
+    PCP_TRY(layer_fwd_train(m, L[L_S2_1], X64, L[L_S2_1].Y, st));                                          // :236
+    PCP_TRY(layer_fwd_train(m, L[L_S2_2], L[L_S2_1].Y, L[L_S2_2].Y, st));                                     // :239
+    PCP_TRY(pooled_layer_fwd(m, ts, L_S2_3, 2, L[L_S2_2].Y, ts->g3, st));                                  // :242-248
 
     // ---- classification head (:252-263) ----
     const float *Yc1 = ts->Ys[4], *Yc2 = ts->Ys[5];
@@ -1595,8 +1608,7 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         // ---- mlp_2 (:234-248) ----
         PCP_TRY(pooled_layer_bwd(m, ts, L_S2_3, 2, L_S2_2, ts->g3, ts->dg3, ts->G128a, st));
         PCP_TRY(bn_bwd(m, L[L_S2_2], ts->G128a, true, st));
-        PCP_TRY(bn_act(L[L_S2_1], ts->Y64a, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_S2_2], ts->Y64a, ts->G128a, ts->G64a, false, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_S2_2], L[L_S2_1].Y, ts->G128a, ts->G64a, false, st));
         PCP_TRY(bn_bwd(m, L[L_S2_1], ts->G64a, true, st));
         PCP_TRY(layer_bwd_mm(m, L[L_S2_1], X64, ts->G64a, ts->dX64, true, st));
         float *dX2 = ts->dX64;                     // vanilla: X_64 is X (:231)
@@ -1619,15 +1631,13 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
             PCP_TRY(tnet_tail_bwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, tr_sh, ts->g2, ts->Ys[2], ts->Ys[3], ts->dR64, ts->dg2, st));
             PCP_TRY(pooled_layer_bwd(m, ts, L_FT_C3, 1, L_FT_C2, ts->g2, ts->dg2, ts->G128a, st));
             PCP_TRY(bn_bwd(m, L[L_FT_C2], ts->G128a, true, st));
-            PCP_TRY(bn_act(L[L_FT_C1], ts->Y64a, st));
-            PCP_TRY(layer_bwd_mm(m, L[L_FT_C2], ts->Y64a, ts->G128a, ts->G64a, false, st));
+            PCP_TRY(layer_bwd_mm(m, L[L_FT_C2], L[L_FT_C1].Y, ts->G128a, ts->G64a, false, st));
             PCP_TRY(bn_bwd(m, L[L_FT_C1], ts->G64a, true, st));
             PCP_TRY(layer_bwd_mm(m, L[L_FT_C1], ts->X2, ts->G64a, dX2, true, st));
         }
         // ---- mlp_1 (:215-223): dX2 holds dY of s1_l2 ----
         PCP_TRY(bn_bwd(m, L[L_S1_2], dX2, true, st));
-        PCP_TRY(bn_act(L[L_S1_1], ts->Y64a, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_S1_2], ts->Y64a, dX2, ts->G64b, false, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_S1_2], L[L_S1_1].Y, dX2, ts->G64b, false, st));
         PCP_TRY(bn_bwd(m, L[L_S1_1], ts->G64b, true, st));
         PCP_TRY(layer_bwd_mm(m, L[L_S1_1], X3, ts->G64b, (full && tr_it) ? ts->dX3 : nullptr, false, st));
         if (full && tr_it) {
@@ -1641,8 +1651,7 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         PCP_TRY(tnet_tail_bwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, true, ts->g1, ts->Ys[0], ts->Ys[1], ts->dR, ts->dg1, st));
         PCP_TRY(pooled_layer_bwd(m, ts, L_IT_C3, 0, L_IT_C2, ts->g1, ts->dg1, ts->G128a, st));
         PCP_TRY(bn_bwd(m, L[L_IT_C2], ts->G128a, true, st));
-        PCP_TRY(bn_act(L[L_IT_C1], ts->Y64a, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_IT_C2], ts->Y64a, ts->G128a, ts->G64a, false, st));
+        PCP_TRY(layer_bwd_mm(m, L[L_IT_C2], L[L_IT_C1].Y, ts->G128a, ts->G64a, false, st));
         PCP_TRY(bn_bwd(m, L[L_IT_C1], ts->G64a, true, st));
         PCP_TRY(layer_bwd_mm(m, L[L_IT_C1], ts->pcn, ts->G64a, nullptr, false, st));
     }

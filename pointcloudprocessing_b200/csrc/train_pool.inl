@@ -65,8 +65,17 @@ pool_implicit_stats_kernel(const float *__restrict__ gram, const double *__restr
     double s = 0, qd = 0;
     for (int i = 0; i < 4; ++i) {
         const int k = lane + 32 * i;
-        double t = 0;
-        for (int l = 0; l < 128; ++l) t += (double)__ldg(gram + l * 128 + k) * ws[warp][l];      // G symmetric: coalesced over k
+        // G symmetric: coalesced over k.  Four independent chains, eight loads in flight: as ONE chain of 128 dependent fp64
+        // multiply-adds behind 128 dependent loads the kernel took 49 us per layer.
+        double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+#pragma unroll 2
+        for (int l = 0; l < 128; l += 4) {
+            const float g0 = __ldg(gram + l * 128 + k), g1 = __ldg(gram + (l + 1) * 128 + k), g2 = __ldg(gram + (l + 2) * 128 + k),
+                        g3 = __ldg(gram + (l + 3) * 128 + k);
+            t0 = fma((double)g0, ws[warp][l], t0); t1 = fma((double)g1, ws[warp][l + 1], t1);
+            t2 = fma((double)g2, ws[warp][l + 2], t2); t3 = fma((double)g3, ws[warp][l + 3], t3);
+        }
+        const double t = (t0 + t1) + (t2 + t3);
         qd += ws[warp][k] * t;
         s += ws[warp][k] * asum[k];
     }
@@ -160,57 +169,92 @@ pool_dw_kernel(const float *__restrict__ gram, const double *__restrict__ asum, 
     float acc[8];
 #pragma unroll
     for (int jj = 0; jj < 8; ++jj) acc[jj] = 0.f;
-    if (batch && blockIdx.y == 0) {
-        for (int l = 0; l < 128; ++l) {
-            const float gv = __ldg(gram + l * 128 + k);
+    // the last row of CTAs (blockIdx.y == gridDim.y - 1) takes the Gram term, the others the clouds: behind one another in the same
+    // CTA the two dependent-load chains added up to 67 us per layer
+    const int ycl = (int)gridDim.y - 1;
+    if ((int)blockIdx.y == ycl) {
+        if (batch) {
+#pragma unroll 4
+            for (int l = 0; l < 128; ++l) {
+                const float gv = __ldg(gram + l * 128 + k);
 #pragma unroll
-            for (int jj = 0; jj < 8; ++jj) acc[jj] = fmaf(gv, __ldg(Wt + (size_t)(j0 + jj) * 128 + l), acc[jj]);
+                for (int jj = 0; jj < 8; ++jj) acc[jj] = fmaf(gv, __ldg(Wt + (size_t)(j0 + jj) * 128 + l), acc[jj]);
+            }
+            const float as = (float)asum[k];
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj) acc[jj] = acc[jj] * __ldg(c1 + j0 + jj) + as * __ldg(c0 + j0 + jj);
         }
-        const float as = (float)asum[k];
+    } else {
+        for (int c = blockIdx.y; c < b; c += 2 * ycl) {            // two clouds per trip: 16 (S, arg) pairs, then 16 row gathers in flight
+            const int c2 = c + ycl;
+            const bool two = c2 < b;
+            const size_t i = (size_t)c * cout + j0, i2 = (size_t)(two ? c2 : c) * cout + j0;
+            float s[16];
+            int r[16];
 #pragma unroll
-        for (int jj = 0; jj < 8; ++jj) acc[jj] = acc[jj] * __ldg(c1 + j0 + jj) + as * __ldg(c0 + j0 + jj);
-    }
-    for (int c = blockIdx.y; c < b; c += gridDim.y) {              // the clouds are split over gridDim.y CTAs
-        const size_t i = (size_t)c * cout + j0;
-        float s[8];
-        int r[8];
+            for (int jj = 0; jj < 8; ++jj) {
+                s[jj] = __ldg(S + i + jj); r[jj] = __ldg(arg + i + jj);
+                s[8 + jj] = two ? __ldg(S + i2 + jj) : 0.f; r[8 + jj] = __ldg(arg + i2 + jj);
+            }
+            float a[16];
 #pragma unroll
-        for (int jj = 0; jj < 8; ++jj) { s[jj] = __ldg(S + i + jj); r[jj] = __ldg(arg + i + jj); }
+            for (int jj = 0; jj < 8; ++jj) {
+                a[jj] = __ldg(A + ((int64_t)c * n + r[jj]) * 128 + k);
+                a[8 + jj] = __ldg(A + ((int64_t)(two ? c2 : c) * n + r[8 + jj]) * 128 + k);
+            }
 #pragma unroll
-        for (int jj = 0; jj < 8; ++jj)
-            if (s[jj] != 0.f) acc[jj] = fmaf(s[jj], bf16_round(__ldg(A + ((int64_t)c * n + r[jj]) * 128 + k)), acc[jj]);
+            for (int jj = 0; jj < 8; ++jj) {
+                if (s[jj] != 0.f) acc[jj] = fmaf(s[jj], bf16_round(a[jj]), acc[jj]);
+                if (s[8 + jj] != 0.f) acc[jj] = fmaf(s[8 + jj], bf16_round(a[8 + jj]), acc[jj]);
+            }
+        }
     }
 #pragma unroll
     for (int jj = 0; jj < 8; ++jj) atomicAdd(dW + (size_t)k * cout + j0 + jj, acc[jj]);
 }
 
-// Q[k, l] = sum_j Wr[k, j] c1_j Wr[l, j] ; q[k] = sum_j Wr[k, j] c0_j                             (cin == 128; one CTA per k)
-__global__ void __launch_bounds__(128)
+// Q[k, l] = sum_j Wr[k, j] c1_j Wr[l, j] ; q[k] = sum_j Wr[k, j] c0_j             (cin == 128; one CTA of 8 x 128 threads per k)
+// Thread (grp, l) sums the grp-th eighth of the channels for column l (128 threads walking all 1024 channels, a handful of loads
+// in flight each, took 47 us per layer); the eight partial sums are added in group order.
+__global__ void __launch_bounds__(1024)
 pool_q_kernel(const float *__restrict__ Wt, const float *__restrict__ c0, const float *__restrict__ c1, int cout, float *__restrict__ Q,
               float *__restrict__ q)
 {
     extern __shared__ float sk[];                 // cout floats: Wr[k, j] c1_j
-    __shared__ float part[4];
-    const int k = blockIdx.x, l = threadIdx.x;
+    __shared__ float part[32];
+    __shared__ float red[8][128];
+    const int k = blockIdx.x, t = threadIdx.x, l = t & 127, grp = t >> 7;
     float qk = 0.f;
-    for (int j = l; j < cout; j += 128) {
+    for (int j = t; j < cout; j += 1024) {
         const float w = __ldg(Wt + (size_t)j * 128 + k);
         sk[j] = w * __ldg(c1 + j);
         qk = fmaf(w, __ldg(c0 + j), qk);
     }
     for (int o = 16; o; o >>= 1) qk += __shfl_xor_sync(0xffffffffu, qk, o);
-    if ((l & 31) == 0) part[l >> 5] = qk;
+    if ((t & 31) == 0) part[t >> 5] = qk;
     __syncthreads();
+    const int per = (cout + 7) / 8, j0 = grp * per, j1 = min(cout, j0 + per);
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;          // independent chains: the loop is load-latency bound
-    int j = 0;
+    int j = j0;
 #pragma unroll 2
-    for (; j + 3 < cout; j += 4) {
+    for (; j + 3 < j1; j += 4) {
         a0 = fmaf(sk[j], __ldg(Wt + (size_t)j * 128 + l), a0); a1 = fmaf(sk[j + 1], __ldg(Wt + (size_t)(j + 1) * 128 + l), a1);
         a2 = fmaf(sk[j + 2], __ldg(Wt + (size_t)(j + 2) * 128 + l), a2); a3 = fmaf(sk[j + 3], __ldg(Wt + (size_t)(j + 3) * 128 + l), a3);
     }
-    for (; j < cout; ++j) a0 = fmaf(sk[j], __ldg(Wt + (size_t)j * 128 + l), a0);
-    Q[k * 128 + l] = (a0 + a1) + (a2 + a3);
-    if (l == 0) q[k] = part[0] + part[1] + part[2] + part[3];
+    for (; j < j1; ++j) a0 = fmaf(sk[j], __ldg(Wt + (size_t)j * 128 + l), a0);
+    red[grp][l] = (a0 + a1) + (a2 + a3);
+    __syncthreads();
+    if (t < 128) {
+        float v = 0.f;
+#pragma unroll
+        for (int gg = 0; gg < 8; ++gg) v += red[gg][t];
+        Q[k * 128 + t] = v;
+    }
+    if (t == 0) {
+        float v = 0.f;
+        for (int w = 0; w < 32; ++w) v += part[w];
+        q[k] = v;
+    }
 }
 
 // dA[c n + arg[c, j], k] += S[c, j] Wr[k, j]                                                       (cin == 128)
@@ -307,13 +351,13 @@ static int pooled_backward(const PoolLayer &L, const float *A, const float *g, c
     pool_round_transpose_kernel<<<dim3((L.cout + 31) / 32, 4), 256, 0, st>>>(L.W, 128, L.cout, L.pb.Wt);
     PCP_CHECK_LAUNCH();
     if (L.trainable && dW) {
-        pool_dw_kernel<<<dim3(L.cout / 8, std::min(L.b, 16)), 128, 0, st>>>(L.pb.gram, L.pb.asum, L.pb.Wt, L.pb.c0, L.pb.c1, L.pb.S, L.pb.arg, A, L.b, L.n, L.cout,
+        pool_dw_kernel<<<dim3(L.cout / 8, std::min(L.b, 16) + 1), 128, 0, st>>>(L.pb.gram, L.pb.asum, L.pb.Wt, L.pb.c0, L.pb.c1, L.pb.S, L.pb.arg, A, L.b, L.n, L.cout,
                                                   L.batch ? 1 : 0, dW);
         PCP_CHECK_LAUNCH();
     }
     if (dA) {
         if (L.batch) {
-            pool_q_kernel<<<128, 128, (size_t)L.cout * 4, st>>>(L.pb.Wt, L.pb.c0, L.pb.c1, L.cout, L.pb.Q, L.pb.q);
+            pool_q_kernel<<<128, 1024, (size_t)L.cout * 4, st>>>(L.pb.Wt, L.pb.c0, L.pb.c1, L.cout, L.pb.Q, L.pb.q);
             PCP_CHECK_LAUNCH();
             PCP_TRY(mm_nn(A, rows, 128, L.pb.Q, 128, 128, dA, L.pb.q, st));
         } else {
