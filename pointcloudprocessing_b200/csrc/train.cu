@@ -317,8 +317,8 @@ bn_finalize_kernel(const double *__restrict__ parts, int nparts, double rows, in
 
 // Y = relu((Z - mean) * sc + beta)
 __global__ void __launch_bounds__(256)
-bn_act_kernel(const float4 *__restrict__ Z, int64_t n4, int C4, BnP p, float4 *__restrict__ Y)
-{
+bn_act_kernel(const float4 *__restrict__ Z, int64_t n4, int C4, BnP p, float4 *__restrict__ Y, uint2 *__restrict__ Y16)
+{   // Y16 (optional): the same activation rounded to bf16 for the GEMM of the next layer (persistent TMA kernel)
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
         const int c = (int)(i % C4) * 4;
         const float4 z = __ldg(Z + i);
@@ -328,6 +328,10 @@ bn_act_kernel(const float4 *__restrict__ Z, int64_t n4, int C4, BnP p, float4 *_
         y.x = fmaxf(bn_pre(z.x, mu.x, s.x, be.x), 0.f); y.y = fmaxf(bn_pre(z.y, mu.y, s.y, be.y), 0.f);
         y.z = fmaxf(bn_pre(z.z, mu.z, s.z, be.z), 0.f); y.w = fmaxf(bn_pre(z.w, mu.w, s.w, be.w), 0.f);
         Y[i] = y;
+        if (Y16) {
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(y.x, y.y), hi = __floats2bfloat162_rn(y.z, y.w);
+            Y16[i] = make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
+        }
     }
 }
 
@@ -467,8 +471,8 @@ bn_bwd_apply_kernel(float4 *__restrict__ dY, const float4 *__restrict__ Z, int64
 // 16-byte loads and one store per element group, two rows in flight)
 __global__ void __launch_bounds__(256)
 bn_bwd_apply4_kernel(float4 *__restrict__ dY, const float4 *__restrict__ Z, int64_t rows, int C, BnP p, int relu, int batch,
-                     const double *__restrict__ s1, const double *__restrict__ s2, float inv_rows)
-{
+                     const double *__restrict__ s1, const double *__restrict__ s2, float inv_rows, uint2 *__restrict__ dZ16)
+{   // dZ16 (optional): the same dZ rounded to bf16 — the input-gradient GEMM that follows then streams it through TMA
     const ColMap4 cm(C);
     const int c = cm.col * 4;
     float mu[4], sc[4], be[4], iv[4], k1[4], k2[4];
@@ -491,17 +495,24 @@ bn_bwd_apply4_kernel(float4 *__restrict__ dY, const float4 *__restrict__ Z, int6
         }
         return make_float4(dd[0], dd[1], dd[2], dd[3]);
     };
+    auto put = [&](int64_t i, const float4 v) {
+        dY[i] = v;
+        if (dZ16) {
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            dZ16[i] = make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
+        }
+    };
     const int64_t L = (int64_t)gridDim.x * cm.lanes;
     int64_t r = (int64_t)blockIdx.x * cm.lanes + cm.lane;
     for (; r + L < rows; r += 2 * L) {
         const int64_t i0 = r * cm.c4 + cm.col, i1 = (r + L) * cm.c4 + cm.col;
         const float4 z0 = __ldg(Z + i0), d0 = dY[i0], z1 = __ldg(Z + i1), d1 = dY[i1];
-        dY[i0] = apply(z0, d0);
-        dY[i1] = apply(z1, d1);
+        put(i0, apply(z0, d0));
+        put(i1, apply(z1, d1));
     }
     for (; r < rows; r += L) {
         const int64_t i0 = r * cm.c4 + cm.col;
-        dY[i0] = apply(__ldg(Z + i0), dY[i0]);
+        put(i0, apply(__ldg(Z + i0), dY[i0]));
     }
 }
 
@@ -665,6 +676,17 @@ mm3_kernel(const float *__restrict__ X, const float *__restrict__ W, int ldw, co
     }
 }
 
+// bf16 copy of an fp32 activation (n4 groups of four): lets a GEMM over it take the persistent TMA kernel
+__global__ void __launch_bounds__(256)
+to_bf16_kernel(const float4 *__restrict__ X, int64_t n4, uint2 *__restrict__ Y)
+{
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldg(X + i);
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        Y[i] = make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
+    }
+}
+
 // MSE(R, y_se3) (pointnet_train.py:339): dR += gscale * 2 (R - y); sq_sum += sum (R - y)^2
 __global__ void mse_kernel(const float *__restrict__ R, const float *__restrict__ y, int64_t count, float gscale, float *__restrict__ dR,
                            double *__restrict__ sq_sum)
@@ -792,6 +814,7 @@ struct TrainState {
     float *cls_logits = nullptr, *cls_prob = nullptr, *seg_logits = nullptr, *seg_prob = nullptr;
     float *gvec = nullptr, *dgvec = nullptr;                       // per-cloud bias of seg_l1 (b x 512) and its gradient
     double *colparts = nullptr;                                    // per-block partial sums of the column reductions
+    __nv_bfloat16 *G16 = nullptr;                                  // bf16 copy of the dZ the next input-gradient GEMM reads (M x 128)
     float *fshift = nullptr;                                       // 512 floats: epilogue constant of a frozen layer (seg_head_fwd_frozen)
     float *dg1 = nullptr, *dg2 = nullptr, *dg3 = nullptr;
     float *dsmall[4] = {nullptr};                                  // (b x 512), (b x 256), (b x C) ...
@@ -895,6 +918,7 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
     want(&ts->seg_logits, (size_t)M * P * 4); want(&ts->seg_prob, (size_t)M * P * 4);
     want(&ts->gvec, (size_t)b * 2048); want(&ts->dgvec, (size_t)b * 2048); want(&ts->fshift, 2048);
     want(&ts->colparts, colparts_doubles() * 8);
+    want(&ts->G16, (size_t)M * 128 * 2);
     for (int i = 0; i < 4; ++i) want(&ts->dsmall[i], (size_t)b * 4096 * 4);
     want(&ts->Y64a, M * 256); want(&ts->Y64b, M * 256); want(&ts->Y128, M * 512); want(&ts->Y128b, M * 512);
     want(&ts->Y256, M * 1024); want(&ts->Y512, M * 2048);
@@ -1030,13 +1054,14 @@ static inline int sync_sum(void *d_buf, size_t count, int dtype, cudaStream_t st
 
 // C (rows x cout) = A (rows x cin) . W  [+ bias]          groups > 1: per-group bias (stride cout), rows per group
 static int mm_nn(const float *A, int64_t rows, int cin, const float *W, int ldw, int cout, float *Cc, const float *bias, cudaStream_t st,
-                 int groups = 1, int64_t bias_stride = 0)
+                 int groups = 1, int64_t bias_stride = 0, const __nv_bfloat16 *A16 = nullptr)
 {
     if (g_tc.on && cin % 64 == 0 && (cout <= 128 || cout % 128 == 0) && gemm_b_image_bytes(cin, cout) <= g_tc.img_bytes) {
         TcGemmParams p;
         PCP_TRY(tc_image(W, cin, cout, ldw, false, &p.Bimg, st));
         const int64_t rpg = rows / groups;
-        p.A = A; p.a_f32 = 1; p.lda = cin; p.a_group_stride = rpg * cin; p.bias = bias; p.bias_group_stride = bias_stride;
+        p.A = A; p.a_f32 = 1; p.lda = cin; p.a_group_stride = rpg * cin;
+        if (A16) { p.A = A16; p.a_f32 = 0; } p.bias = bias; p.bias_group_stride = bias_stride;
         p.C32 = Cc; p.ldc = cout; p.c_group_stride = rpg * cout; p.M = (int)rpg; p.N = cout; p.K = cin; p.groups = groups;
         return tc_gemm(p, st);
     }
@@ -1057,12 +1082,14 @@ static int mm_nn(const float *A, int64_t rows, int cin, const float *W, int ldw,
     return gemm_f32(g, st);
 }
 // dA (rows x cin) (+)= dZ (rows x cout) . W^T
-static int mm_nt(const float *dZ, int64_t rows, int cout, const float *W, int ldw, int cin, float *dA, bool accumulate, cudaStream_t st)
+static int mm_nt(const float *dZ, int64_t rows, int cout, const float *W, int ldw, int cin, float *dA, bool accumulate, cudaStream_t st,
+                 const __nv_bfloat16 *dZ16 = nullptr)
 {
     if (g_tc.on && cout % 64 == 0 && (cin <= 128 || cin % 128 == 0) && gemm_b_image_bytes(cout, cin) <= g_tc.img_bytes) {
         TcGemmParams p;
         PCP_TRY(tc_image(W, cout, cin, ldw, true, &p.Bimg, st));
         p.A = dZ; p.a_f32 = 1; p.lda = cout; p.C32 = dA; p.ldc = cin; p.M = (int)rows; p.N = cin; p.K = cout;
+        if (dZ16) { p.A = dZ16; p.a_f32 = 0; }      // the producer's own bf16 copy (bn_bwd): same rounding, persistent TMA kernel
         p.accumulate = accumulate ? 1 : 0;
         // few row tiles and a long contraction (the T-Net tails' 4096 -> 256): deal the k-tiles over CTAs
         const int kt = cout / 64;
@@ -1138,10 +1165,11 @@ static int bn_prepare(pcp_model *m, TL &t, cudaStream_t st)
     return PCP_OK;
 }
 
-static int bn_act(const TL &t, float *Y, cudaStream_t st)
+static int bn_act(const TL &t, float *Y, cudaStream_t st, __nv_bfloat16 *Y16 = nullptr)
 {
     const int64_t n4 = t.rows * t.cout / 4;
-    bn_act_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<const float4 *>(t.Z), n4, t.cout / 4, t.bnp(), reinterpret_cast<float4 *>(Y));
+    bn_act_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<const float4 *>(t.Z), n4, t.cout / 4, t.bnp(), reinterpret_cast<float4 *>(Y),
+                                                reinterpret_cast<uint2 *>(Y16));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -1156,12 +1184,14 @@ static int layer_act(const TL &t, float *scratch, const float **Y, cudaStream_t 
 }
 
 // forward of one BN layer: Z = A . W ; statistics ; optionally Y = relu(bn(Z))
-static int layer_fwd_train(pcp_model *m, TL &t, const float *A, float *Y, cudaStream_t st)
+// A16 (optional): A already rounded to bf16 by its producer; Y16 (optional): receives bf16(Y) for the next layer
+static int layer_fwd_train(pcp_model *m, TL &t, const float *A, float *Y, cudaStream_t st, const __nv_bfloat16 *A16 = nullptr,
+                           __nv_bfloat16 *Y16 = nullptr)
 {
     const LayerSpec &S = m->layers[t.id];
-    PCP_TRY(mm_nn(A, t.rows, t.cin, param(m, S.t_kernel), t.cout, t.cout, t.Z, nullptr, st));
+    PCP_TRY(mm_nn(A, t.rows, t.cin, param(m, S.t_kernel), t.cout, t.cout, t.Z, nullptr, st, 1, 0, A16));
     PCP_TRY(bn_prepare(m, t, st));
-    if (Y) PCP_TRY(bn_act(t, Y, st));
+    if (Y) PCP_TRY(bn_act(t, Y, st, Y16));
     return PCP_OK;
 }
 
@@ -1204,17 +1234,6 @@ atb3_kernel(const float *__restrict__ X, const float *__restrict__ dX, int64_t n
 #pragma unroll
         for (int w = 0; w < 8; ++w) v += sh[w][threadIdx.x];
         dR[(int64_t)blockIdx.x * 9 + threadIdx.x] += v;
-    }
-}
-
-// bf16 copy of an fp32 activation (n4 groups of four): lets a GEMM over it take the persistent TMA kernel
-__global__ void __launch_bounds__(256)
-to_bf16_kernel(const float4 *__restrict__ X, int64_t n4, uint2 *__restrict__ Y)
-{
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-        const float4 v = __ldg(X + i);
-        const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
-        Y[i] = make_uint2(*reinterpret_cast<const uint32_t *>(&lo), *reinterpret_cast<const uint32_t *>(&hi));
     }
 }
 
@@ -1263,7 +1282,7 @@ static int pool_fwd(const TL &t, int b, int64_t n, float *g, cudaStream_t st)
 }
 
 // G (rows x cout) holds dY on entry, dZ on exit; BN parameter gradients are written when the layer trains
-static int bn_bwd(pcp_model *m, TL &t, float *G, bool relu, cudaStream_t st)
+static int bn_bwd(pcp_model *m, TL &t, float *G, bool relu, cudaStream_t st, __nv_bfloat16 *G16 = nullptr)
 {
     const LayerSpec &S = m->layers[t.id];
     const int64_t n4 = t.rows * t.cout / 4;
@@ -1284,10 +1303,13 @@ static int bn_bwd(pcp_model *m, TL &t, float *G, bool relu, cudaStream_t st)
     const float inv_rows = (float)(1.0 / ((double)t.rows * g_sync.scale));
     if (colmap4_ok(t.cout))
         bn_bwd_apply4_kernel<<<grid_for(n4, 512), 256, 0, st>>>(reinterpret_cast<float4 *>(G), reinterpret_cast<const float4 *>(t.Z), t.rows, t.cout, t.bnp(),
-                                                               relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, inv_rows);
-    else
+                                                               relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, inv_rows,
+                                                               reinterpret_cast<uint2 *>(G16));
+    else {
         bn_bwd_apply_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<float4 *>(G), reinterpret_cast<const float4 *>(t.Z), n4, t.cout / 4, t.bnp(),
                                                          relu ? 1 : 0, t.batch ? 1 : 0, t.red, t.red + t.cout, inv_rows);
+        if (G16) to_bf16_kernel<<<grid_for(n4), 256, 0, st>>>(reinterpret_cast<const float4 *>(G), n4, reinterpret_cast<uint2 *>(G16));
+    }
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -1307,11 +1329,12 @@ static int pool_bwd(pcp_model *m, TL &t, int b, int64_t n, const float *g, const
 }
 
 // weight gradient + input gradient of a layer whose dZ is in G
-static int layer_bwd_mm(pcp_model *m, TL &t, const float *Ain, const float *G, float *dA, bool accumulate, cudaStream_t st)
+static int layer_bwd_mm(pcp_model *m, TL &t, const float *Ain, const float *G, float *dA, bool accumulate, cudaStream_t st,
+                        const __nv_bfloat16 *G16 = nullptr)
 {
     const LayerSpec &S = m->layers[t.id];
     if (t.trainable) PCP_TRY(mm_tn(Ain, t.rows, t.cin, G, t.cout, grad(m, S.t_kernel), t.cout, st));
-    if (dA) PCP_TRY(mm_nt(G, t.rows, t.cout, param(m, S.t_kernel), t.cout, t.cin, dA, accumulate, st));
+    if (dA) PCP_TRY(mm_nt(G, t.rows, t.cout, param(m, S.t_kernel), t.cout, t.cin, dA, accumulate, st, G16));
     return PCP_OK;
 }
 
@@ -1424,9 +1447,12 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     // =========================================== forward ===========================================
     PCP_TRY(pcp_normalize_f32(d_x, b, n, ts->pcn, nullptr, nullptr, st));                               // PointNet.py:202
     const float *X3 = ts->pcn;
+    // tensor-core mode: a 64-wide activation is also written in bf16 by its producer for the GEMM right behind it
+    // (a16: ts->G16, the backward pass's scratch; a16b: ts->Y64b, needed across two layers)
+    __nv_bfloat16 *a16 = g_tc.on ? ts->G16 : nullptr, *a16b = g_tc.on ? reinterpret_cast<__nv_bfloat16 *>(ts->Y64b) : nullptr;
     if (full) {
-        PCP_TRY(layer_fwd_train(m, L[L_IT_C1], ts->pcn, L[L_IT_C1].Y, st));                                 // TNet.call :423
-        PCP_TRY(layer_fwd_train(m, L[L_IT_C2], L[L_IT_C1].Y, L[L_IT_C2].Y, st));                                // :424
+        PCP_TRY(layer_fwd_train(m, L[L_IT_C1], ts->pcn, L[L_IT_C1].Y, st, nullptr, a16));                                 // TNet.call :423
+        PCP_TRY(layer_fwd_train(m, L[L_IT_C2], L[L_IT_C1].Y, L[L_IT_C2].Y, st, a16));                                // :424
         PCP_TRY(pooled_layer_fwd(m, ts, L_IT_C3, 0, L[L_IT_C2].Y, ts->g1, st));                             // :425-429
         PCP_TRY(tnet_tail_fwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, ts->g1, ts->Ys[0], ts->Ys[1], ts->R, st));
         pc_matmul3_kernel<<<grid_for(M), 256, 0, st>>>(ts->pcn, ts->R, n, M, ts->X3);                    // X = pc @ R  :207
@@ -1435,12 +1461,12 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     } else {
         PCP_TRY(model_eye3(ts->R, b, st));
     }
-    PCP_TRY(layer_fwd_train(m, L[L_S1_1], X3, L[L_S1_1].Y, st));                                           // :217
-    PCP_TRY(layer_fwd_train(m, L[L_S1_2], L[L_S1_1].Y, ts->X2, st));                                       // :220
+    PCP_TRY(layer_fwd_train(m, L[L_S1_1], X3, L[L_S1_1].Y, st, nullptr, a16));                                           // :217
+    PCP_TRY(layer_fwd_train(m, L[L_S1_2], L[L_S1_1].Y, ts->X2, st, a16, (full && a16) ? a16b : nullptr));                                       // :220
     const float *X64 = ts->X2;
     if (full) {
-        PCP_TRY(layer_fwd_train(m, L[L_FT_C1], ts->X2, L[L_FT_C1].Y, st));
-        PCP_TRY(layer_fwd_train(m, L[L_FT_C2], L[L_FT_C1].Y, L[L_FT_C2].Y, st));
+        PCP_TRY(layer_fwd_train(m, L[L_FT_C1], ts->X2, L[L_FT_C1].Y, st, a16b, a16));
+        PCP_TRY(layer_fwd_train(m, L[L_FT_C2], L[L_FT_C1].Y, L[L_FT_C2].Y, st, a16));
         PCP_TRY(pooled_layer_fwd(m, ts, L_FT_C3, 1, L[L_FT_C2].Y, ts->g2, st));
         PCP_TRY(tnet_tail_fwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, ts->g2, ts->Ys[2], ts->Ys[3], ts->R64, st));   // :227
         GemmArgs g;                                                                                     // X_64 = X @ R_64 :228
@@ -1449,8 +1475,8 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         PCP_TRY(gemm_f32(g, st));
         X64 = ts->X64;
     }
-    PCP_TRY(layer_fwd_train(m, L[L_S2_1], X64, L[L_S2_1].Y, st));                                          // :236
-    PCP_TRY(layer_fwd_train(m, L[L_S2_2], L[L_S2_1].Y, L[L_S2_2].Y, st));                                     // :239
+    PCP_TRY(layer_fwd_train(m, L[L_S2_1], X64, L[L_S2_1].Y, st, nullptr, a16));                                          // :236
+    PCP_TRY(layer_fwd_train(m, L[L_S2_2], L[L_S2_1].Y, L[L_S2_2].Y, st, a16));                                     // :239
     PCP_TRY(pooled_layer_fwd(m, ts, L_S2_3, 2, L[L_S2_2].Y, ts->g3, st));                                  // :242-248
 
     // ---- classification head (:252-263) ----
@@ -1607,10 +1633,12 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     if (trunk_bwd) {
         // ---- mlp_2 (:234-248) ----
         PCP_TRY(pooled_layer_bwd(m, ts, L_S2_3, 2, L_S2_2, ts->g3, ts->dg3, ts->G128a, st));
-        PCP_TRY(bn_bwd(m, L[L_S2_2], ts->G128a, true, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_S2_2], L[L_S2_1].Y, ts->G128a, ts->G64a, false, st));
-        PCP_TRY(bn_bwd(m, L[L_S2_1], ts->G64a, true, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_S2_1], X64, ts->G64a, ts->dX64, true, st));
+        // g16: bn_bwd also leaves dZ in bf16 for the input-gradient GEMM behind it (tensor-core mode)
+        __nv_bfloat16 *g16 = g_tc.on ? ts->G16 : nullptr;
+        PCP_TRY(bn_bwd(m, L[L_S2_2], ts->G128a, true, st, g16));
+        PCP_TRY(layer_bwd_mm(m, L[L_S2_2], L[L_S2_1].Y, ts->G128a, ts->G64a, false, st, g16));
+        PCP_TRY(bn_bwd(m, L[L_S2_1], ts->G64a, true, st, g16));
+        PCP_TRY(layer_bwd_mm(m, L[L_S2_1], X64, ts->G64a, ts->dX64, true, st, g16));
         float *dX2 = ts->dX64;                     // vanilla: X_64 is X (:231)
         if (full) {
             // X_64 = X @ R_64: dR_64 = X^T . dX_64 per cloud ; dX = dX_64 . R_64^T
@@ -1630,14 +1658,14 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
             // ---- feature T-Net ----
             PCP_TRY(tnet_tail_bwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, tr_sh, ts->g2, ts->Ys[2], ts->Ys[3], ts->dR64, ts->dg2, st));
             PCP_TRY(pooled_layer_bwd(m, ts, L_FT_C3, 1, L_FT_C2, ts->g2, ts->dg2, ts->G128a, st));
-            PCP_TRY(bn_bwd(m, L[L_FT_C2], ts->G128a, true, st));
-            PCP_TRY(layer_bwd_mm(m, L[L_FT_C2], L[L_FT_C1].Y, ts->G128a, ts->G64a, false, st));
-            PCP_TRY(bn_bwd(m, L[L_FT_C1], ts->G64a, true, st));
-            PCP_TRY(layer_bwd_mm(m, L[L_FT_C1], ts->X2, ts->G64a, dX2, true, st));
+            PCP_TRY(bn_bwd(m, L[L_FT_C2], ts->G128a, true, st, g16));
+            PCP_TRY(layer_bwd_mm(m, L[L_FT_C2], L[L_FT_C1].Y, ts->G128a, ts->G64a, false, st, g16));
+            PCP_TRY(bn_bwd(m, L[L_FT_C1], ts->G64a, true, st, g16));
+            PCP_TRY(layer_bwd_mm(m, L[L_FT_C1], ts->X2, ts->G64a, dX2, true, st, g16));
         }
         // ---- mlp_1 (:215-223): dX2 holds dY of s1_l2 ----
-        PCP_TRY(bn_bwd(m, L[L_S1_2], dX2, true, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_S1_2], L[L_S1_1].Y, dX2, ts->G64b, false, st));
+        PCP_TRY(bn_bwd(m, L[L_S1_2], dX2, true, st, g16));
+        PCP_TRY(layer_bwd_mm(m, L[L_S1_2], L[L_S1_1].Y, dX2, ts->G64b, false, st, g16));
         PCP_TRY(bn_bwd(m, L[L_S1_1], ts->G64b, true, st));
         PCP_TRY(layer_bwd_mm(m, L[L_S1_1], X3, ts->G64b, (full && tr_it) ? ts->dX3 : nullptr, false, st));
         if (full && tr_it) {
@@ -1650,8 +1678,9 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         // ---- input T-Net: gradient enters through R only ----
         PCP_TRY(tnet_tail_bwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, true, ts->g1, ts->Ys[0], ts->Ys[1], ts->dR, ts->dg1, st));
         PCP_TRY(pooled_layer_bwd(m, ts, L_IT_C3, 0, L_IT_C2, ts->g1, ts->dg1, ts->G128a, st));
-        PCP_TRY(bn_bwd(m, L[L_IT_C2], ts->G128a, true, st));
-        PCP_TRY(layer_bwd_mm(m, L[L_IT_C2], L[L_IT_C1].Y, ts->G128a, ts->G64a, false, st));
+        __nv_bfloat16 *g16 = g_tc.on ? ts->G16 : nullptr;
+        PCP_TRY(bn_bwd(m, L[L_IT_C2], ts->G128a, true, st, g16));
+        PCP_TRY(layer_bwd_mm(m, L[L_IT_C2], L[L_IT_C1].Y, ts->G128a, ts->G64a, false, st, g16));
         PCP_TRY(bn_bwd(m, L[L_IT_C1], ts->G64a, true, st));
         PCP_TRY(layer_bwd_mm(m, L[L_IT_C1], ts->pcn, ts->G64a, nullptr, false, st));
     }
