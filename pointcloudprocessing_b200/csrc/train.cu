@@ -767,6 +767,8 @@ struct ImgCache {
     PackJob *d_jobs = nullptr;
     int d_count = 0;              // jobs in the device table
     int fresh = 0;                // jobs[0 .. fresh) were packed by this step's refresh
+    const float *lo = nullptr, *hi = nullptr;   // the model's parameter buffer: only matrices inside it are cached (anything else — the
+                                                // pooled layers' per-step Q — lives in the arena and changes within the step)
 };
 // buffers of one implicitly handled max-pooled layer (train_pool.inl)
 struct PoolBufs {
@@ -1008,7 +1010,7 @@ static int tc_image(const float *W, int K, int N, int ldw, bool transpose, const
 {
     ImgCache *c = g_tc.cache;
     const size_t bytes = (gemm_b_image_bytes(K, N) + 1023) & ~(size_t)1023;
-    if (c && c->pool) {
+    if (c && c->pool && W >= c->lo && W < c->hi) {
         for (int i = 0; i < (int)c->jobs.size(); ++i) {
             const PackJob &j = c->jobs[i];
             if (j.W == W && j.K == K && j.N == N && j.ldw == ldw && j.transpose == (transpose ? 1 : 0)) {
@@ -1421,7 +1423,10 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     g_tc.img = ts->tc_img; g_tc.img_bytes = kImgBytes;
     static const bool no_img_cache = getenv("PCP_TRAIN_NO_IMG_CACHE") != nullptr;
     g_tc.cache = (g_tc.on && !no_img_cache) ? &ts->img_cache : nullptr;
-    if (g_tc.cache) PCP_TRY(img_cache_refresh(g_tc.cache, st));
+    if (g_tc.cache) {
+        g_tc.cache->lo = m->d_params; g_tc.cache->hi = m->d_params + m->n_params;
+        PCP_TRY(img_cache_refresh(g_tc.cache, st));
+    }
     g_colparts = ts->colparts;
     g_sync = SyncCtx();
     if (ts->sync_fn && global_batch > b) { g_sync.fn = ts->sync_fn; g_sync.user = ts->sync_user; g_sync.scale = (double)global_batch / (double)b; }

@@ -381,6 +381,43 @@ def test_bf16_tensor_core_training_step(lib, vanilla, trainable, weights, reg, s
     check_bf16_step_against_noise_floor(m, p, x, y, masks, vanilla, trainable, weights, reg, f"12x256 smooth={smooth} vanilla={vanilla}")
 
 
+@pytest.mark.parametrize("trainable,weights", [(ALL, (1.0, 0.5, 0.25)), (PRETRAIN, (1.0, 0.0, 0.0))])
+@pytest.mark.parametrize("batches", [((12, 256), (12, 256)), ((12, 256), (6, 128))])
+def test_bf16_second_step_matches_fresh_model(lib, trainable, weights, batches):
+    """State carried from step to step (the packed weight images of the previous step, re-packed by one launch at the start of
+    the next; the activation arena, rebuilt when the batch shape changes) must not leak into the arithmetic: after one applied
+    step, the second step of the SAME model object equals the first step of a FRESH model loaded with the same weights, on
+    the same batch — the same kernels in the same order, so only the order of the gradient atomics separates them (and the
+    bf16 re-rounding behind them: measured between two fresh models, every tensor within 5 x that)."""
+    C, P = 8, 8
+    (b1, n1), (b2, n2) = batches
+    m, p = build(C, P, False, trainable, weights, (True, True), precision="bf16")
+    x1, y1, k1 = make_batch(31, b1, n1, C, P)
+    m.train_on_batch(x1, y1, dropout_masks=k1, apply=True)
+    w1 = m.get_weights_dict()
+    x2, y2, k2 = make_batch(32, b2, n2, C, P)
+    met_a = m.train_on_batch(x2, y2, dropout_masks=k2, apply=False)
+    ga = m.gradients_dict()
+    fresh = []
+    for _ in range(2):                     # two fresh models: their own difference is the atomics' noise floor
+        f, _ = build(C, P, False, trainable, weights, (True, True), precision="bf16")
+        f.set_weights_dict(w1)
+        met_b = f.train_on_batch(x2, y2, dropout_masks=k2, apply=False)
+        fresh.append((met_b, f.gradients_dict()))
+    (met_b, gb), (_, gc) = fresh
+    assert abs(met_a["loss"] - met_b["loss"]) <= 1e-6 * max(1.0, abs(met_b["loss"])), (met_a["loss"], met_b["loss"])
+    gmax = max(float(np.abs(v).max()) for v in gb.values())
+    worst = {}
+    for k in gb:
+        scale = max(float(np.abs(gb[k]).max()), 1e-2 * gmax)
+        err = float(np.abs(ga[k].astype(np.float64) - gb[k]).max()) / scale
+        noise = float(np.abs(gc[k].astype(np.float64) - gb[k]).max()) / scale
+        worst[k] = (err, noise)
+        assert err <= max(3e-3, 5.0 * noise), (k, err, noise)
+    k = max(worst, key=lambda k: worst[k][0])
+    print(f"[second step] worst tensor {k}: {worst[k][0]:.2e} against the fresh models' own {worst[k][1]:.2e}")
+
+
 def test_bf16_fit_learns(lib):
     from pointcloudprocessing_b200.pointnet import keras_compat as K
     C, P, b, n = 4, 3, 16, 128
