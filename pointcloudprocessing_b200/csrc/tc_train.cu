@@ -23,7 +23,8 @@ using namespace umma;
 // (transpose = 1); tiles [nt][kt] of (bnt rows x 64 K) bf16, K-major SWIZZLE_128B (tc_gemm.cu:pack_gemm_b_image)
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void pack_weight_image_body(const float *__restrict__ W, int K, int N, int ldw, int transpose, int bnt,
-                                                       const float *__restrict__ colscale, uint16_t *__restrict__ img, int64_t first, int64_t stride)
+                                                       const float *__restrict__ colscale, const float *__restrict__ sgn,
+                                                       uint16_t *__restrict__ img, int64_t first, int64_t stride)
 {
     const int KT = K >> 6, ntiles = (N + bnt - 1) / bnt;
     const int64_t total = (int64_t)ntiles * KT * bnt * 64;
@@ -39,6 +40,7 @@ __device__ __forceinline__ void pack_weight_image_body(const float *__restrict__
         float v = 0.f;
         if (n < N) v = transpose ? __ldg(W + (int64_t)n * ldw + kk) : __ldg(W + (int64_t)kk * ldw + n);
         if (colscale && n < N) v *= __ldg(colscale + n);
+        if (sgn && n < N && !(__ldg(sgn + n) >= 0.f)) v = -v;
         const __nv_bfloat16 h = __float2bfloat16_rn(v);
         img[tile * (bnt * 64) + sw128_offset((uint32_t)bnt, (uint32_t)r, (uint32_t)k) / 2] = *reinterpret_cast<const uint16_t *>(&h);
     }
@@ -46,9 +48,9 @@ __device__ __forceinline__ void pack_weight_image_body(const float *__restrict__
 
 __global__ void __launch_bounds__(256)
 pack_weight_image_kernel(const float *__restrict__ W, int K, int N, int ldw, int transpose, int bnt, const float *__restrict__ colscale,
-                         uint16_t *__restrict__ img)
+                         const float *__restrict__ sgn, uint16_t *__restrict__ img)
 {
-    pack_weight_image_body(W, K, N, ldw, transpose, bnt, colscale, img, blockIdx.x * (int64_t)blockDim.x + threadIdx.x, (int64_t)gridDim.x * blockDim.x);
+    pack_weight_image_body(W, K, N, ldw, transpose, bnt, colscale, sgn, img, blockIdx.x * (int64_t)blockDim.x + threadIdx.x, (int64_t)gridDim.x * blockDim.x);
 }
 
 // every job of a table in one launch (blockIdx.y = job): the training step re-packs all its weight images once per step
@@ -56,7 +58,7 @@ __global__ void __launch_bounds__(256)
 pack_weight_images_kernel(const PackJob *__restrict__ jobs)
 {
     const PackJob j = jobs[blockIdx.y];
-    pack_weight_image_body(j.W, j.K, j.N, j.ldw, j.transpose, j.bnt, nullptr, j.img, blockIdx.x * (int64_t)blockDim.x + threadIdx.x,
+    pack_weight_image_body(j.W, j.K, j.N, j.ldw, j.transpose, j.bnt, nullptr, j.sgn, j.img, blockIdx.x * (int64_t)blockDim.x + threadIdx.x,
                            (int64_t)gridDim.x * blockDim.x);
 }
 
@@ -70,13 +72,14 @@ int pack_weight_images(const PackJob *d_jobs, int njobs, cudaStream_t st)
     return PCP_OK;
 }
 
-int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, uint8_t *d_img, cudaStream_t st, const float *d_colscale)
+int pack_weight_image(const float *d_W, int K, int N, int ldw, bool transpose, uint8_t *d_img, cudaStream_t st, const float *d_colscale,
+                      const float *d_sgn)
 {
     PCP_REQUIRE(K >= 64 && K % 64 == 0, PCP_ERR_UNSUPPORTED, "pack_weight_image: K=%d must be a multiple of 64", K);
     const int bnt = tc_gemm_bn_tile(N);
     const int64_t total = (int64_t)((N + bnt - 1) / bnt) * (K / 64) * bnt * 64;
     const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)sm_count() * 8);
-    pack_weight_image_kernel<<<grid, 256, 0, st>>>(d_W, K, N, ldw, transpose ? 1 : 0, bnt, d_colscale, reinterpret_cast<uint16_t *>(d_img));
+    pack_weight_image_kernel<<<grid, 256, 0, st>>>(d_W, K, N, ldw, transpose ? 1 : 0, bnt, d_colscale, d_sgn, reinterpret_cast<uint16_t *>(d_img));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
@@ -352,7 +355,7 @@ constexpr uint32_t kPxSmem = 3 * kPxTile + 1024;
 struct PoolExtParams {
     const float *A;                      // (b * n) x 128 fp32 row-major
     const uint8_t *Wimg;                 // pack_weight_image(W, 128, cout): [cout/128][2] tiles of 16 KB
-    unsigned long long *ext_max, *ext_min;   // b x cout packed keys (tc_gemm.cuh), zero-initialised
+    unsigned long long *ext_max;         // b x cout packed keys (tc_gemm.cuh), zero-initialised
     int n, cout, mtiles;
 };
 
@@ -417,8 +420,8 @@ tc_pool_extrema_kernel(const PoolExtParams p)
         for (int nt = wg; nt < NT; nt += 2) {
             mbar_wait(&acc_full[wg], (uint32_t)((nt >> 1) & 1), 61);
             tc_fence_after();
-            float mx = -INFINITY, mn = INFINITY;
-            int rmx = 0, rmn = 0;
+            float mx = -INFINITY;
+            int rmx = 0;
             for (int c0 = 0; c0 < rows_valid; c0 += 32) {
                 uint32_t v[32];
                 tmem_ld32(tacc + (uint32_t)c0, v);
@@ -428,15 +431,12 @@ tc_pool_extrema_kernel(const PoolExtParams p)
                     for (int e = 0; e < 32; ++e) {
                         const float f = __uint_as_float(v[e]);
                         if (f > mx) { mx = f; rmx = c0 + e; }
-                        if (f < mn) { mn = f; rmn = c0 + e; }
                     }
                 } else {
 #pragma unroll
                     for (int e = 0; e < 32; ++e) {
                         const float f = __uint_as_float(v[e]);
-                        const bool ok = c0 + e < rows_valid;
-                        if (ok && f > mx) { mx = f; rmx = c0 + e; }
-                        if (ok && f < mn) { mn = f; rmn = c0 + e; }
+                        if (c0 + e < rows_valid && f > mx) { mx = f; rmx = c0 + e; }
                     }
                 }
             }
@@ -446,8 +446,6 @@ tc_pool_extrema_kernel(const PoolExtParams p)
             const size_t o = (size_t)g * p.cout + (size_t)nt * 128 + ch;
             if (mx > -INFINITY)
                 atomicMax(p.ext_max + o, ((unsigned long long)tc_float_key(__float_as_uint(mx)) << 32) | (0xffffffffu - (uint32_t)(row0 + rmx)));
-            if (mn < INFINITY)
-                atomicMax(p.ext_min + o, ((unsigned long long)(~tc_float_key(__float_as_uint(mn))) << 32) | (0xffffffffu - (uint32_t)(row0 + rmn)));
         }
     } else if (warp == 8) {
         // ---------------- MMA issuer: D[channel, row] = W tile (128 ch x 128 K) . A tile^T ----------------
@@ -488,14 +486,13 @@ tc_pool_extrema_kernel(const PoolExtParams p)
     if (warp == 8) tmem_dealloc(tmem, 256);
 }
 
-int tc_pool_extrema(const float *A, int b, int64_t n, const uint8_t *Wimg, int cout, unsigned long long *ext_max, unsigned long long *ext_min,
-                    cudaStream_t st)
+int tc_pool_extrema(const float *A, int b, int64_t n, const uint8_t *Wimg, int cout, unsigned long long *ext_max, cudaStream_t st)
 {
-    PCP_REQUIRE(A && Wimg && ext_max && ext_min, PCP_ERR_INVALID, "tc_pool_extrema: null operand");
+    PCP_REQUIRE(A && Wimg && ext_max, PCP_ERR_INVALID, "tc_pool_extrema: null operand");
     PCP_REQUIRE(cout >= 128 && cout % 128 == 0 && n >= 1 && n <= 0x7fffffff, PCP_ERR_UNSUPPORTED, "tc_pool_extrema: cout=%d must be a multiple of 128", cout);
     if (b <= 0) return PCP_OK;
     PoolExtParams p;
-    p.A = A; p.Wimg = Wimg; p.ext_max = ext_max; p.ext_min = ext_min; p.n = (int)n; p.cout = cout; p.mtiles = (int)((n + 127) / 128);
+    p.A = A; p.Wimg = Wimg; p.ext_max = ext_max; p.n = (int)n; p.cout = cout; p.mtiles = (int)((n + 127) / 128);
     const int64_t grid = (int64_t)b * p.mtiles;
     PCP_REQUIRE(grid <= 0x7fffffff, PCP_ERR_UNSUPPORTED, "tc_pool_extrema: %lld row tiles exceed one launch", (long long)grid);
     static bool attr = false;

@@ -1006,15 +1006,15 @@ static int img_cache_refresh(ImgCache *c, cudaStream_t st)
 }
 
 // image of the logical (K x N) matrix B[k][n] = W[k*ldw + n] (or W[n*ldw + k], transpose) for tc_gemm
-static int tc_image(const float *W, int K, int N, int ldw, bool transpose, const uint8_t **img, cudaStream_t st)
+static int tc_image(const float *W, int K, int N, int ldw, bool transpose, const uint8_t **img, cudaStream_t st, const float *sgn = nullptr)
 {
     ImgCache *c = g_tc.cache;
     const size_t bytes = (gemm_b_image_bytes(K, N) + 1023) & ~(size_t)1023;
-    if (c && c->pool && W >= c->lo && W < c->hi) {
+    if (c && c->pool && W >= c->lo && W < c->hi && (!sgn || (sgn >= c->lo && sgn < c->hi))) {
         for (int i = 0; i < (int)c->jobs.size(); ++i) {
             const PackJob &j = c->jobs[i];
-            if (j.W == W && j.K == K && j.N == N && j.ldw == ldw && j.transpose == (transpose ? 1 : 0)) {
-                if (i >= c->fresh) PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, reinterpret_cast<uint8_t *>(j.img), st));
+            if (j.W == W && j.K == K && j.N == N && j.ldw == ldw && j.transpose == (transpose ? 1 : 0) && j.sgn == sgn) {
+                if (i >= c->fresh) PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, reinterpret_cast<uint8_t *>(j.img), st, nullptr, sgn));
                 *img = reinterpret_cast<const uint8_t *>(j.img);
                 return PCP_OK;
             }
@@ -1022,16 +1022,16 @@ static int tc_image(const float *W, int K, int N, int ldw, bool transpose, const
         if ((int)c->jobs.size() < kImgCacheMaxJobs && c->used + bytes <= c->cap) {
             PackJob j;
             j.W = W; j.img = reinterpret_cast<uint16_t *>(c->pool + c->used); j.K = K; j.N = N; j.ldw = ldw; j.transpose = transpose ? 1 : 0;
-            j.bnt = tc_gemm_bn_tile(N);
+            j.bnt = tc_gemm_bn_tile(N); j.sgn = sgn;
             c->used += bytes;
             c->jobs.push_back(j);
-            PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, reinterpret_cast<uint8_t *>(j.img), st));
+            PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, reinterpret_cast<uint8_t *>(j.img), st, nullptr, sgn));
             *img = reinterpret_cast<const uint8_t *>(j.img);
             return PCP_OK;
         }
     }
     PCP_REQUIRE(bytes <= g_tc.img_bytes, PCP_ERR_UNSUPPORTED, "tc_image: %d x %d does not fit the scratch image", K, N);
-    PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, g_tc.img, st));
+    PCP_TRY(pack_weight_image(W, K, N, ldw, transpose, g_tc.img, st, nullptr, sgn));
     *img = g_tc.img;
     return PCP_OK;
 }
@@ -1237,6 +1237,52 @@ atb3_kernel(const float *__restrict__ X, const float *__restrict__ dX, int64_t n
         for (int w = 0; w < 8; ++w) v += sh[w][threadIdx.x];
         dR[(int64_t)blockIdx.x * 9 + threadIdx.x] += v;
     }
+}
+
+// dR[g] (64 x 64) += X[g]^T (64 x n) . D[g] (n x 64) — the feature transform's gradient (X_64 = X @ R_64, PointNet.py:228).
+// A CTA takes kRows rows of one cloud through shared memory in 64-row slabs; thread (ty, tx) owns the 4 x 4 block
+// (X columns 4 ty .., D columns 4 tx ..): two 16-byte shared loads per 16 multiply-adds, the X one a broadcast.  The CTAs of a
+// cloud add their blocks with atomics (the generic 128 x 64 GEMM tile wastes half its rows on a 64 x 64 result: 133 us).
+constexpr int kAtbRows = 256;
+__global__ void __launch_bounds__(256)
+atb64_kernel(const float *__restrict__ X, const float *__restrict__ D, int64_t n, float *__restrict__ dR)
+{
+    __shared__ __align__(16) float xs[64][64], ds[64][64];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int64_t g = blockIdx.y, r0 = (int64_t)blockIdx.x * kAtbRows, r1 = min(n, r0 + kAtbRows);
+    const float4 *X4 = reinterpret_cast<const float4 *>(X + (g * n) * 64), *D4 = reinterpret_cast<const float4 *>(D + (g * n) * 64);
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int64_t s0 = r0; s0 < r1; s0 += 64) {
+        const int rows = (int)min((int64_t)64, r1 - s0);
+        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int idx = tid + 256 * u, r = idx >> 4, c4 = idx & 15;       // 64 rows x 16 float4
+            const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 xv = r < rows ? __ldg(X4 + (s0 + r) * 16 + c4) : zero, dv = r < rows ? __ldg(D4 + (s0 + r) * 16 + c4) : zero;
+            *reinterpret_cast<float4 *>(&xs[r][c4 * 4]) = xv;
+            *reinterpret_cast<float4 *>(&ds[r][c4 * 4]) = dv;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int k = 0; k < 64; ++k) {
+            const float4 a = *reinterpret_cast<const float4 *>(&xs[k][ty * 4]), bq = *reinterpret_cast<const float4 *>(&ds[k][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {bq.x, bq.y, bq.z, bq.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+    }
+    float *out = dR + g * 4096;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) atomicAdd(out + (ty * 4 + i) * 64 + tx * 4 + j, acc[i][j]);
 }
 
 // out[g, c] = beta[c] - sc[c] * mean[c] (+ sc[c] * add[g, c]): what a frozen BatchNorm leaves of itself once sc is folded into
@@ -1647,14 +1693,10 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         float *dX2 = ts->dX64;                     // vanilla: X_64 is X (:231)
         if (full) {
             // X_64 = X @ R_64: dR_64 = X^T . dX_64 per cloud ; dX = dX_64 . R_64^T
-            GemmArgs g;
-            g.A = ts->X2; g.lda = 64; g.strideA = n * 64; g.transA = 1; g.B = ts->dX64; g.ldb = 64; g.strideB = n * 64;
-            g.C = ts->dR64; g.ldc = 64; g.strideC = 4096; g.M = 64; g.N = 64; g.K = (int)n; g.groups = b;
-            // one 64 x 64 tile per cloud leaves the device idle (173 us at 256 clouds): split the points, atomics into the
-            // zero-initialised (+ regulariser) dR64, like every other weight-gradient reduction of the step
-            g.splitk = (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(n / 128, 65535 / std::max(b, 1)), (8 * (int64_t)sm_count() + b - 1) / b));
-            if (g.splitk == 1) g.accumulate = 1;
-            PCP_TRY(gemm_f32(g, st));
+            // atomics into the zero-initialised (+ regulariser) dR64, like every other weight-gradient reduction of the step
+            PCP_REQUIRE(b <= 65535, PCP_ERR_UNSUPPORTED, "training: more than 65535 clouds per step");
+            atb64_kernel<<<dim3((unsigned)((n + kAtbRows - 1) / kAtbRows), (unsigned)b), 256, 0, st>>>(ts->X2, ts->dX64, n, ts->dR64);
+            PCP_CHECK_LAUNCH();
             GemmArgs h;
             h.A = ts->dX64; h.lda = 64; h.strideA = n * 64; h.B = ts->R64; h.ldb = 64; h.strideB = 4096; h.transB = 1;
             h.C = ts->dX2; h.ldc = 64; h.strideC = n * 64; h.M = (int)n; h.N = 64; h.K = 64; h.groups = b;

@@ -85,16 +85,15 @@ pool_implicit_stats_kernel(const float *__restrict__ gram, const double *__restr
 
 // pooled output and the record the backward pass needs
 __global__ void __launch_bounds__(256)
-pool_select_kernel(const unsigned long long *__restrict__ emax, const unsigned long long *__restrict__ emin, BnP p, int64_t total, int cout,
+pool_select_kernel(const unsigned long long *__restrict__ emax, const float *__restrict__ gamma, BnP p, int64_t total, int cout,
                    float *__restrict__ g, float *__restrict__ zsel, int *__restrict__ arg)
-{
+{   // emax: maxima of z' = sign(gamma) z (tc_pool_extrema); the selected extremum of z is sign(gamma) max z'
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int j = (int)(i % cout);
         const float sc = __ldg(p.sc + j);
-        unsigned long long key = sc >= 0.f ? emax[i] : emin[i];
-        uint32_t hi = (uint32_t)(key >> 32);
-        if (sc < 0.f) hi = ~hi;
-        const float z = __uint_as_float(tc_key_float_bits(hi));
+        const unsigned long long key = emax[i];
+        const float zs = __uint_as_float(tc_key_float_bits((uint32_t)(key >> 32)));
+        const float z = __ldg(gamma + j) >= 0.f ? zs : -zs;
         zsel[i] = z;
         arg[i] = (int)(0xffffffffu - (uint32_t)key);
         g[i] = fmaxf(bn_pre(z, __ldg(p.mean + j), sc, __ldg(p.beta + j)), 0.f);
@@ -185,28 +184,30 @@ pool_dw_kernel(const float *__restrict__ gram, const double *__restrict__ asum, 
             for (int jj = 0; jj < 8; ++jj) acc[jj] = acc[jj] * __ldg(c1 + j0 + jj) + as * __ldg(c0 + j0 + jj);
         }
     } else {
-        for (int c = blockIdx.y; c < b; c += 2 * ycl) {            // two clouds per trip: 16 (S, arg) pairs, then 16 row gathers in flight
-            const int c2 = c + ycl;
-            const bool two = c2 < b;
-            const size_t i = (size_t)c * cout + j0, i2 = (size_t)(two ? c2 : c) * cout + j0;
-            float s[16];
-            int r[16];
+        // four clouds per trip: 32 (S, arg) pairs, then 32 row gathers in flight — the kernel is a chain of dependent L2 / HBM
+        // round trips (ncu: 17.7 of 22 stalled warps on the long scoreboard, 25 MB of DRAM traffic in 66 us)
+        for (int c = blockIdx.y; c < b; c += 4 * ycl) {
+            float s[32], a[32];
+            int r[32];
 #pragma unroll
-            for (int jj = 0; jj < 8; ++jj) {
-                s[jj] = __ldg(S + i + jj); r[jj] = __ldg(arg + i + jj);
-                s[8 + jj] = two ? __ldg(S + i2 + jj) : 0.f; r[8 + jj] = __ldg(arg + i2 + jj);
-            }
-            float a[16];
+            for (int u = 0; u < 4; ++u) {
+                const int cu = c + u * ycl;
+                const bool in = cu < b;
+                const size_t i = (size_t)(in ? cu : c) * cout + j0;
 #pragma unroll
-            for (int jj = 0; jj < 8; ++jj) {
-                a[jj] = __ldg(A + ((int64_t)c * n + r[jj]) * 128 + k);
-                a[8 + jj] = __ldg(A + ((int64_t)(two ? c2 : c) * n + r[8 + jj]) * 128 + k);
+                for (int jj = 0; jj < 8; ++jj) { s[u * 8 + jj] = in ? __ldg(S + i + jj) : 0.f; r[u * 8 + jj] = __ldg(arg + i + jj); }
             }
 #pragma unroll
-            for (int jj = 0; jj < 8; ++jj) {
-                if (s[jj] != 0.f) acc[jj] = fmaf(s[jj], bf16_round(a[jj]), acc[jj]);
-                if (s[8 + jj] != 0.f) acc[jj] = fmaf(s[8 + jj], bf16_round(a[8 + jj]), acc[jj]);
+            for (int u = 0; u < 4; ++u) {
+                const int cu = c + u * ycl < b ? c + u * ycl : c;
+#pragma unroll
+                for (int jj = 0; jj < 8; ++jj) a[u * 8 + jj] = __ldg(A + ((int64_t)cu * n + r[u * 8 + jj]) * 128 + k);
             }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int jj = 0; jj < 8; ++jj)
+                    if (s[u * 8 + jj] != 0.f) acc[jj] = fmaf(s[u * 8 + jj], bf16_round(a[u * 8 + jj]), acc[jj]);
         }
     }
 #pragma unroll
@@ -298,10 +299,10 @@ static bool pool_implicit_ok(int cin, int cout) { return g_tc.on && cin == 128 &
 static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStream_t st)
 {
     const int64_t rows = (int64_t)L.b * L.n, total = (int64_t)L.b * L.cout;
-    PCP_CUDA_OK(cudaMemsetAsync(L.pb.ext, 0, (size_t)total * 16, st));
+    PCP_CUDA_OK(cudaMemsetAsync(L.pb.ext, 0, (size_t)total * 8, st));
     const uint8_t *wimg = nullptr;
-    PCP_TRY(tc_image(L.W, 128, L.cout, L.cout, false, &wimg, st));
-    PCP_TRY(tc_pool_extrema(A, L.b, L.n, wimg, L.cout, L.pb.ext, L.pb.ext + total, st));
+    PCP_TRY(tc_image(L.W, 128, L.cout, L.cout, false, &wimg, st, L.gamma));          // W . diag(sign(gamma))
+    PCP_TRY(tc_pool_extrema(A, L.b, L.n, wimg, L.cout, L.pb.ext, st));
     if (L.batch) {
         // the Gram matrix feeds the layer's batch statistics, i.e. the FORWARD: it has to be the same bits on every run
         PCP_TRY(tc_gram_det(A, 128, rows, 128, L.pb.gram, L.pb.gram_parts, tc_gram_scratch_floats(128), st));
@@ -326,7 +327,7 @@ static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStre
     bn_finalize_kernel<<<L.cout, 256, 0, st>>>(L.red, 1, (double)rows * g_sync.scale, L.cout, L.batch ? 1 : 0, L.gamma, L.beta_in, L.mov_mean,
                                                         L.mov_var, L.mean, L.inv, L.sc, L.beta, kBnEpsT, kBnMomentum);
     PCP_CHECK_LAUNCH();
-    pool_select_kernel<<<grid_for(total), 256, 0, st>>>(L.pb.ext, L.pb.ext + total, L.bnp(), total, L.cout, g, L.pb.zsel, L.pb.arg);
+    pool_select_kernel<<<grid_for(total), 256, 0, st>>>(L.pb.ext, L.gamma, L.bnp(), total, L.cout, g, L.pb.zsel, L.pb.arg);
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }

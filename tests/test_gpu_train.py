@@ -388,7 +388,8 @@ def test_bf16_second_step_matches_fresh_model(lib, trainable, weights, batches):
     the next; the activation arena, rebuilt when the batch shape changes) must not leak into the arithmetic: after one applied
     step, the second step of the SAME model object equals the first step of a FRESH model loaded with the same weights, on
     the same batch — the same kernels in the same order, so only the order of the gradient atomics separates them (and the
-    bf16 re-rounding behind them: measured between two fresh models, every tensor within 5 x that)."""
+    bf16 re-rounding behind them: measured between two fresh models at up to 1e-2 of a tensor's largest entry; a stale image is an
+    O(1) error).  Every tensor within max(3e-2, 5 x that noise)."""
     C, P = 8, 8
     (b1, n1), (b2, n2) = batches
     m, p = build(C, P, False, trainable, weights, (True, True), precision="bf16")
@@ -413,7 +414,7 @@ def test_bf16_second_step_matches_fresh_model(lib, trainable, weights, batches):
         err = float(np.abs(ga[k].astype(np.float64) - gb[k]).max()) / scale
         noise = float(np.abs(gc[k].astype(np.float64) - gb[k]).max()) / scale
         worst[k] = (err, noise)
-        assert err <= max(3e-3, 5.0 * noise), (k, err, noise)
+        assert err <= max(3e-2, 5.0 * noise), (k, err, noise)
     k = max(worst, key=lambda k: worst[k][0])
     print(f"[second step] worst tensor {k}: {worst[k][0]:.2e} against the fresh models' own {worst[k][1]:.2e}")
 
