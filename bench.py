@@ -407,7 +407,8 @@ def main():
         extras["train_c3"] = {"value": world * tb / (ms_tr * 1e-3), "unit": "clouds/s", "ms_per_step": ms_tr, "global_batch": tb * world,
                               "precision": args.train_precision, "loss": last.get("loss"),
                               "config": "C3: PointNet training step (jitter + fwd + bwd + grad all-reduce + Adam), classification_pretrain profile, 1024 pts",
-                              "note": "both heads forward like the reference; per-shard BN statistics"}
+                              "note": "both heads forward like the reference (the frozen, unweighted segmentation head in its inference form: nothing is "
+                                      "differentiated through it); per-shard BN statistics"}
         # same step at a FIXED per-GPU batch of 256 (weak scaling of the training path; at N = 1 it is the run above)
         if world > 1:
             xw = torch.from_numpy(synth.gaussian_clouds(4004 + rank, 256, N_POINTS)).to(dev)

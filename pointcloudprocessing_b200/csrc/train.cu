@@ -1243,7 +1243,7 @@ atb3_kernel(const float *__restrict__ X, const float *__restrict__ dX, int64_t n
 // A CTA takes kRows rows of one cloud through shared memory in 64-row slabs; thread (ty, tx) owns the 4 x 4 block
 // (X columns 4 ty .., D columns 4 tx ..): two 16-byte shared loads per 16 multiply-adds, the X one a broadcast.  The CTAs of a
 // cloud add their blocks with atomics (the generic 128 x 64 GEMM tile wastes half its rows on a 64 x 64 result: 133 us).
-constexpr int kAtbRows = 256;
+constexpr int kAtbRows = 512;
 __global__ void __launch_bounds__(256)
 atb64_kernel(const float *__restrict__ X, const float *__restrict__ D, int64_t n, float *__restrict__ dR)
 {
@@ -1280,9 +1280,8 @@ atb64_kernel(const float *__restrict__ X, const float *__restrict__ D, int64_t n
     }
     float *out = dR + g * 4096;
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) atomicAdd(out + (ty * 4 + i) * 64 + tx * 4 + j, acc[i][j]);
+    for (int i = 0; i < 4; ++i)          // one 16-byte reduction per row of the thread's block (red.global.add.v4.f32)
+        atomicAdd(reinterpret_cast<float4 *>(out + (ty * 4 + i) * 64 + tx * 4), make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
 }
 
 // out[g, c] = beta[c] - sc[c] * mean[c] (+ sc[c] * add[g, c]): what a frozen BatchNorm leaves of itself once sc is folded into

@@ -210,8 +210,10 @@ pool_dw_kernel(const float *__restrict__ gram, const double *__restrict__ asum, 
                     if (s[u * 8 + jj] != 0.f) acc[jj] = fmaf(s[u * 8 + jj], bf16_round(a[u * 8 + jj]), acc[jj]);
         }
     }
-#pragma unroll
-    for (int jj = 0; jj < 8; ++jj) atomicAdd(dW + (size_t)k * cout + j0 + jj, acc[jj]);
+    // two 16-byte reductions per thread (cout and j0 are multiples of 8: aligned)
+    float4 *dst = reinterpret_cast<float4 *>(dW + (size_t)k * cout + j0);
+    atomicAdd(dst, make_float4(acc[0], acc[1], acc[2], acc[3]));
+    atomicAdd(dst + 1, make_float4(acc[4], acc[5], acc[6], acc[7]));
 }
 
 // Q[k, l] = sum_j Wr[k, j] c1_j Wr[l, j] ; q[k] = sum_j Wr[k, j] c0_j             (cin == 128; one CTA of 8 x 128 threads per k)
