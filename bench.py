@@ -403,12 +403,13 @@ def main():
 
         def step_train(i):
             last.update(tm.train_on_batch(ops.jitter(xt, (0.1, 0.1, 0.1), seed=i), yt, global_batch=tb * world, sample_offset=rank * tb))
-        ms_tr = timed(step_train, 5, 3)
+        ms_tr = timed(step_train, 8, 6)      # the step is replayed as a CUDA graph from its fourth run on: warm past the capture
         extras["train_c3"] = {"value": world * tb / (ms_tr * 1e-3), "unit": "clouds/s", "ms_per_step": ms_tr, "global_batch": tb * world,
                               "precision": args.train_precision, "loss": last.get("loss"),
                               "config": "C3: PointNet training step (jitter + fwd + bwd + grad all-reduce + Adam), classification_pretrain profile, 1024 pts",
                               "note": "both heads forward like the reference (the frozen, unweighted segmentation head in its inference form: nothing is "
-                                      "differentiated through it); per-shard BN statistics"}
+                                      "differentiated through it); per-shard BN statistics; the step (forward, losses, backward) is replayed as one CUDA "
+                                      "graph, the gradient all-reduce and Adam follow it"}
         # same step at a FIXED per-GPU batch of 256 (weak scaling of the training path; at N = 1 it is the run above)
         if world > 1:
             xw = torch.from_numpy(synth.gaussian_clouds(4004 + rank, 256, N_POINTS)).to(dev)
@@ -416,7 +417,7 @@ def main():
                   "segmentation_output": torch.from_numpy(rng.integers(0, P_PARTS, (256, N_POINTS)).astype(np.int32)).to(dev),
                   "se3": torch.eye(3, device=dev).repeat(256, 1, 1)}
             tm._reset_adam_state()
-            ms_tw = timed(lambda i: tm.train_on_batch(ops.jitter(xw, (0.1, 0.1, 0.1), seed=i), yw, global_batch=256 * world, sample_offset=rank * 256), 5, 3)
+            ms_tw = timed(lambda i: tm.train_on_batch(ops.jitter(xw, (0.1, 0.1, 0.1), seed=i), yw, global_batch=256 * world, sample_offset=rank * 256), 8, 6)
             extras["train_c3_weak"] = {"value": world * 256 / (ms_tw * 1e-3), "unit": "clouds/s", "ms_per_step": ms_tw, "global_batch": 256 * world,
                                        "precision": args.train_precision, "config": "C3 at 256 clouds per GPU (weak scaling)"}
             del xw, yw

@@ -549,8 +549,9 @@ __device__ __forceinline__ float dropout_factor(uint64_t seed, uint64_t sample, 
 // H = Y * factor ; explicit mask (0/1 floats) when given, else Philox.  Also used for the backward (dY = dH * factor).
 __global__ void __launch_bounds__(256)
 dropout_kernel(const float *Y, int64_t rows, int C, const float *__restrict__ mask, uint64_t seed, int64_t sample0,
-               uint32_t layer, float rate, float *H)
-{
+               uint32_t layer, float rate, float *H, const unsigned long long *__restrict__ dyn)
+{   // dyn (optional, device): {seed, sample0} of THIS step — a captured step graph is replayed with new values every step
+    if (dyn) { seed = dyn[0]; sample0 = (int64_t)dyn[1]; }
     const float scale = 1.0f / (1.0f - rate);
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < rows * C; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = i / C;
@@ -558,6 +559,11 @@ dropout_kernel(const float *Y, int64_t rows, int C, const float *__restrict__ ma
         const float f = mask ? mask[i] * scale : dropout_factor(seed, (uint64_t)(sample0 + r), (uint32_t)c, layer, rate, scale);
         H[i] = Y[i] * f;
     }
+}
+
+__global__ void set_step_scalars_kernel(unsigned long long *dyn, unsigned long long seed, long long sample0)
+{
+    dyn[0] = seed; dyn[1] = (unsigned long long)sample0;
 }
 
 // softmax + SCCE on probabilities (keras from_logits=False: clip to [1e-7, 1-1e-7], -log; pointnet_train.py:337-338)
@@ -829,6 +835,19 @@ struct TrainState {
     char *eval_buf = nullptr; size_t eval_bytes = 0;               // pcp_model_evaluate: metrics + logits
     uint8_t *tc_img = nullptr;                                     // scratch bf16 weight image of the tensor-core GEMMs (4 MB)
     ImgCache img_cache;                                            // the step's packed weight images (bf16 mode)
+    // the captured step (train_step_impl): one graph launch instead of ~220 kernel launches, which is what a small shard
+    // (32 clouds per GPU in the 8-GPU strong-scaling run) spends its time on
+    struct StepKey {
+        int b; long long n; int global_batch; float w_cls, w_seg, w_rot; int skip, tr[4], has_cls, has_seg, has_se3, jobs;
+    };
+    StepKey graph_key = {}; int graph_seen = 0;                    // consecutive eager steps with this key
+    cudaGraphExec_t graph_exec = nullptr;
+    cudaStream_t graph_stream = nullptr;                           // the graph's own stream (the caller's may be the legacy default
+    cudaEvent_t graph_in = nullptr, graph_out = nullptr;           // stream, which cannot be captured): fork / join by events
+    bool graph_broken = false;                                     // a capture failed: stay eager
+    float *stage_x = nullptr, *stage_se3 = nullptr; int32_t *stage_ycls = nullptr, *stage_yseg = nullptr;   // the graph's inputs
+    unsigned long long *step_scalars = nullptr;                    // {dropout seed, sample offset} of the step being replayed
+    void *norm_ws = nullptr; size_t norm_ws_bytes = 0;             // pcp_normalize_ws_f32 scratch (LiDAR-sized clouds)
     PoolBufs pool[3];                                              // L_IT_C3, L_FT_C3, L_S2_3 (bf16 mode)
     bool implicit_pool = false;                                    // pooled layers without their (rows x 1024) tensors (train_pool.inl)
     pcp_allreduce_fn sync_fn = nullptr; void *sync_user = nullptr; // data-parallel BatchNorm (pcp_model_set_bn_allreduce)
@@ -871,6 +890,10 @@ void train_destroy(pcp_model *m)
     PCP_RELEASE(cudaFree(ts->eval_buf));
     PCP_RELEASE(cudaFree(ts->tc_img));
     PCP_RELEASE(cudaFree(ts->img_cache.pool)); PCP_RELEASE(cudaFree(ts->img_cache.d_jobs));
+    if (ts->graph_exec) PCP_RELEASE(cudaGraphExecDestroy(ts->graph_exec));
+    if (ts->graph_stream) PCP_RELEASE(cudaStreamDestroy(ts->graph_stream));
+    if (ts->graph_in) PCP_RELEASE(cudaEventDestroy(ts->graph_in));
+    if (ts->graph_out) PCP_RELEASE(cudaEventDestroy(ts->graph_out));
     delete ts;
     m->train_ws = nullptr;
 }
@@ -921,6 +944,12 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
     want(&ts->gvec, (size_t)b * 2048); want(&ts->dgvec, (size_t)b * 2048); want(&ts->fshift, 2048);
     want(&ts->colparts, colparts_doubles() * 8);
     want(&ts->G16, (size_t)M * 128 * 2);
+    want(&ts->stage_x, (size_t)M * 12); want(&ts->stage_ycls, (size_t)b * 4); want(&ts->stage_yseg, (size_t)M * 4); want(&ts->stage_se3, (size_t)b * 36);
+    want(&ts->step_scalars, 16);
+    PCP_TRY(pcp_normalize_workspace_bytes(b, n, &ts->norm_ws_bytes));
+    want(&ts->norm_ws, ts->norm_ws_bytes + 256);
+    if (ts->graph_exec) { cudaGraphExecDestroy(ts->graph_exec); ts->graph_exec = nullptr; }
+    ts->graph_seen = 0;
     for (int i = 0; i < 4; ++i) want(&ts->dsmall[i], (size_t)b * 4096 * 4);
     want(&ts->Y64a, M * 256); want(&ts->Y64b, M * 256); want(&ts->Y128, M * 512); want(&ts->Y128b, M * 512);
     want(&ts->Y256, M * 1024); want(&ts->Y512, M * 2048);
@@ -985,7 +1014,8 @@ static thread_local TcCtx g_tc;
 constexpr size_t kImgCacheBytes = (size_t)48 << 20;
 constexpr int kImgCacheMaxJobs = 256;
 
-static int img_cache_refresh(ImgCache *c, cudaStream_t st)
+// allocation and the (pageable-source) table upload: never inside a stream capture
+static int img_cache_sync_table(ImgCache *c, cudaStream_t st)
 {
     if (!c->pool) {
         PCP_CUDA_OK(cudaMalloc(&c->pool, kImgCacheBytes));
@@ -1000,8 +1030,13 @@ static int img_cache_refresh(ImgCache *c, cudaStream_t st)
                                     cudaMemcpyHostToDevice, st));
         c->d_count = n;
     }
-    PCP_TRY(pack_weight_images(c->d_jobs, n, st));
-    c->fresh = n;
+    return PCP_OK;
+}
+// re-pack every image of the device table (stream-ordered, capturable)
+static int img_cache_refresh(ImgCache *c, cudaStream_t st)
+{
+    PCP_TRY(pack_weight_images(c->d_jobs, c->d_count, st));
+    c->fresh = c->d_count;
     return PCP_OK;
 }
 
@@ -1456,25 +1491,14 @@ static int tnet_tail_bwd(pcp_model *m, TrainState *ts, int first, int t_w, int t
     return PCP_OK;
 }
 
-static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *y_cls, const int32_t *y_seg, const float *y_se3,
-                           const pcp_train_config *cfg, int global_batch, const float *mask1, const float *mask2, float *h_metrics,
-                           cudaStream_t st)
+// Everything of the step that is ordered on the stream: forward, losses, backward into the flat gradient buffer.  No
+// allocation, no host synchronisation, no host-memory copies — the body is what train_step_impl captures into a graph.
+// dyn (device, optional): {dropout seed, sample offset} read by the dropout kernels instead of cfg's values.
+static int train_step_body(pcp_model *m, TrainState *ts, const float *d_x, int b, int64_t n, const int32_t *y_cls, const int32_t *y_seg,
+                           const float *y_se3, const pcp_train_config *cfg, int global_batch, const float *mask1, const float *mask2,
+                           const unsigned long long *dyn, cudaStream_t st)
 {
-    TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
-    PCP_TRY(ensure_arena(m, ts, b, n));
-    const size_t kImgBytes = (size_t)4 << 20;
-    if (!ts->tc_img) PCP_CUDA_OK(cudaMalloc(&ts->tc_img, kImgBytes));
-    g_tc.on = m->desc.precision == PCP_PRECISION_BF16;
-    g_tc.img = ts->tc_img; g_tc.img_bytes = kImgBytes;
-    static const bool no_img_cache = getenv("PCP_TRAIN_NO_IMG_CACHE") != nullptr;
-    g_tc.cache = (g_tc.on && !no_img_cache) ? &ts->img_cache : nullptr;
-    if (g_tc.cache) {
-        g_tc.cache->lo = m->d_params; g_tc.cache->hi = m->d_params + m->n_params;
-        PCP_TRY(img_cache_refresh(g_tc.cache, st));
-    }
-    g_colparts = ts->colparts;
-    g_sync = SyncCtx();
-    if (ts->sync_fn && global_batch > b) { g_sync.fn = ts->sync_fn; g_sync.user = ts->sync_user; g_sync.scale = (double)global_batch / (double)b; }
+    if (g_tc.cache) PCP_TRY(img_cache_refresh(g_tc.cache, st));
     const int64_t M = (int64_t)b * n;
     const int C = m->desc.num_classes, P = m->desc.num_parts;
     const bool full = !m->desc.vanilla;
@@ -1484,18 +1508,12 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     const bool seg_needed = !(cfg->skip_unweighted_heads && cfg->w_seg == 0.f && !tr_seg);
     const bool do_seg_bwd = seg_needed && cfg->w_seg != 0.f && y_seg;
     const bool do_cls_bwd = cfg->w_cls != 0.f && y_cls;
-    for (int i = 0; i < L_COUNT; ++i) {
-        TL &t = ts->L[i];
-        if (t.id < 0) continue;
-        t.trainable = m->trainable[m->layers[i].group];
-        t.batch = t.has_bn && t.trainable;                       // keras: batch statistics only when training AND trainable
-    }
     PCP_CUDA_OK(cudaMemsetAsync(m->d_grads, 0, m->n_params * sizeof(float), st));
     PCP_CUDA_OK(cudaMemsetAsync(ts->metrics, 0, 64, st));
     TL *L = ts->L;
 
     // =========================================== forward ===========================================
-    PCP_TRY(pcp_normalize_f32(d_x, b, n, ts->pcn, nullptr, nullptr, st));                               // PointNet.py:202
+    PCP_TRY(pcp_normalize_ws_f32(d_x, b, n, ts->pcn, nullptr, nullptr, ts->norm_ws, ts->norm_ws_bytes, st));   // PointNet.py:202
     const float *X3 = ts->pcn;
     // tensor-core mode: a 64-wide activation is also written in bf16 by its producer for the GEMM right behind it
     // (a16: ts->G16, the backward pass's scratch; a16b: ts->Y64b, needed across two layers)
@@ -1536,14 +1554,14 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
     const float *H1 = Yc1, *H2 = Yc2;
     if (use_drop) {
         dropout_kernel<<<grid_for((int64_t)b * 512), 256, 0, st>>>(Yc1, b, 512, cfg->use_dropout_masks ? mask1 : nullptr, cfg->dropout_seed,
-                                                                   cfg->sample_offset, 1u, rate, ts->H1);
+                                                                   cfg->sample_offset, 1u, rate, ts->H1, dyn);
         PCP_CHECK_LAUNCH();
         H1 = ts->H1;
     }
     PCP_TRY(layer_fwd_train(m, L[L_CLS2], H1, ts->Ys[5], st));
     if (use_drop) {
         dropout_kernel<<<grid_for((int64_t)b * 256), 256, 0, st>>>(Yc2, b, 256, cfg->use_dropout_masks ? mask2 : nullptr, cfg->dropout_seed,
-                                                                   cfg->sample_offset, 2u, rate, ts->H2);
+                                                                   cfg->sample_offset, 2u, rate, ts->H2, dyn);
         PCP_CHECK_LAUNCH();
         H2 = ts->H2;
     }
@@ -1620,14 +1638,14 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         PCP_TRY(mm_nt(dlog_cls, b, C, param(m, S3.t_kernel), C, 256, d256, false, st));
         if (use_drop) {
             dropout_kernel<<<grid_for((int64_t)b * 256), 256, 0, st>>>(d256, b, 256, cfg->use_dropout_masks ? mask2 : nullptr, cfg->dropout_seed,
-                                                                       cfg->sample_offset, 2u, rate, d256);
+                                                                       cfg->sample_offset, 2u, rate, d256, dyn);
             PCP_CHECK_LAUNCH();
         }
         PCP_TRY(bn_bwd(m, L[L_CLS2], d256, true, st));
         PCP_TRY(layer_bwd_mm(m, L[L_CLS2], H1, d256, d512, false, st));
         if (use_drop) {
             dropout_kernel<<<grid_for((int64_t)b * 512), 256, 0, st>>>(d512, b, 512, cfg->use_dropout_masks ? mask1 : nullptr, cfg->dropout_seed,
-                                                                       cfg->sample_offset, 1u, rate, d512);
+                                                                       cfg->sample_offset, 1u, rate, d512, dyn);
             PCP_CHECK_LAUNCH();
         }
         PCP_TRY(bn_bwd(m, L[L_CLS1], d512, true, st));
@@ -1729,6 +1747,101 @@ static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, con
         PCP_TRY(layer_bwd_mm(m, L[L_IT_C2], L[L_IT_C1].Y, ts->G128a, ts->G64a, false, st, g16));
         PCP_TRY(bn_bwd(m, L[L_IT_C1], ts->G64a, true, st));
         PCP_TRY(layer_bwd_mm(m, L[L_IT_C1], ts->pcn, ts->G64a, nullptr, false, st));
+    }
+    return PCP_OK;
+}
+
+static int train_step_impl(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *y_cls, const int32_t *y_seg, const float *y_se3,
+                           const pcp_train_config *cfg, int global_batch, const float *mask1, const float *mask2, float *h_metrics,
+                           cudaStream_t st)
+{
+    TrainState *ts = reinterpret_cast<TrainState *>(m->train_ws);
+    PCP_TRY(ensure_arena(m, ts, b, n));
+    const size_t kImgBytes = (size_t)4 << 20;
+    if (!ts->tc_img) PCP_CUDA_OK(cudaMalloc(&ts->tc_img, kImgBytes));
+    g_tc.on = m->desc.precision == PCP_PRECISION_BF16;
+    g_tc.img = ts->tc_img; g_tc.img_bytes = kImgBytes;
+    static const bool no_img_cache = getenv("PCP_TRAIN_NO_IMG_CACHE") != nullptr;
+    g_tc.cache = (g_tc.on && !no_img_cache) ? &ts->img_cache : nullptr;
+    if (g_tc.cache) {
+        g_tc.cache->lo = m->d_params; g_tc.cache->hi = m->d_params + m->n_params;
+        PCP_TRY(img_cache_sync_table(g_tc.cache, st));
+    }
+    g_colparts = ts->colparts;
+    g_sync = SyncCtx();
+    if (ts->sync_fn && global_batch > b) { g_sync.fn = ts->sync_fn; g_sync.user = ts->sync_user; g_sync.scale = (double)global_batch / (double)b; }
+    const bool tr_seg = m->trainable[PCP_GROUP_SEG_HEAD];
+    const bool seg_needed = !(cfg->skip_unweighted_heads && cfg->w_seg == 0.f && !tr_seg);
+    for (int i = 0; i < L_COUNT; ++i) {
+        TL &t = ts->L[i];
+        if (t.id < 0) continue;
+        t.trainable = m->trainable[m->layers[i].group];
+        t.batch = t.has_bn && t.trainable;                       // keras: batch statistics only when training AND trainable
+    }
+
+    // ---- the step as one graph launch.  Eligible: no host callback inside the step (sync-BN), no caller-owned dropout masks;
+    // the same configuration has run eagerly twice (every lazily created thing exists, the weight-image table is complete).
+    // The graph reads its inputs from staging buffers and the per-step dropout scalars from device memory.
+    // PCP_TRAIN_GRAPH=0 keeps every step eager.
+    const char *genv = getenv("PCP_TRAIN_GRAPH");
+    const bool graph_ok = !(genv && genv[0] == '0') && !ts->graph_broken && !g_sync.fn && !cfg->use_dropout_masks;
+    TrainState::StepKey key;
+    memset(&key, 0, sizeof(key));                                  // padding bytes too: the keys are compared with memcmp
+    key.b = b; key.n = n; key.global_batch = global_batch; key.w_cls = cfg->w_cls; key.w_seg = cfg->w_seg; key.w_rot = cfg->w_rot;
+    key.skip = cfg->skip_unweighted_heads;
+    for (int g = 0; g < 4; ++g) key.tr[g] = m->trainable[g] ? 1 : 0;
+    key.has_cls = y_cls != nullptr; key.has_seg = y_seg != nullptr; key.has_se3 = y_se3 != nullptr;
+    key.jobs = g_tc.cache ? (int)g_tc.cache->jobs.size() : 0;
+    if (memcmp(&key, &ts->graph_key, sizeof(key)) != 0) {
+        if (ts->graph_exec) { cudaGraphExecDestroy(ts->graph_exec); ts->graph_exec = nullptr; }
+        memcpy(&ts->graph_key, &key, sizeof(key)); ts->graph_seen = 0;
+    }
+    bool ran = false;
+    if (graph_ok && ts->graph_seen >= 2) {
+        const int64_t M = (int64_t)b * n;
+        if (!ts->graph_stream) {
+            PCP_CUDA_OK(cudaStreamCreateWithFlags(&ts->graph_stream, cudaStreamNonBlocking));
+            PCP_CUDA_OK(cudaEventCreateWithFlags(&ts->graph_in, cudaEventDisableTiming));
+            PCP_CUDA_OK(cudaEventCreateWithFlags(&ts->graph_out, cudaEventDisableTiming));
+        }
+        cudaStream_t gs = ts->graph_stream;
+        PCP_CUDA_OK(cudaEventRecord(ts->graph_in, st));            // fork: everything queued on the caller's stream comes first
+        PCP_CUDA_OK(cudaStreamWaitEvent(gs, ts->graph_in, 0));
+        PCP_CUDA_OK(cudaMemcpyAsync(ts->stage_x, d_x, (size_t)M * 12, cudaMemcpyDeviceToDevice, gs));
+        if (y_cls) PCP_CUDA_OK(cudaMemcpyAsync(ts->stage_ycls, y_cls, (size_t)b * 4, cudaMemcpyDeviceToDevice, gs));
+        if (y_seg) PCP_CUDA_OK(cudaMemcpyAsync(ts->stage_yseg, y_seg, (size_t)M * 4, cudaMemcpyDeviceToDevice, gs));
+        if (y_se3) PCP_CUDA_OK(cudaMemcpyAsync(ts->stage_se3, y_se3, (size_t)b * 36, cudaMemcpyDeviceToDevice, gs));
+        set_step_scalars_kernel<<<1, 1, 0, gs>>>(ts->step_scalars, (unsigned long long)cfg->dropout_seed, (long long)cfg->sample_offset);
+        PCP_CHECK_LAUNCH();
+        if (!ts->graph_exec) {
+            cudaGraph_t graph = nullptr;
+            cudaError_t e = cudaStreamBeginCapture(gs, cudaStreamCaptureModeThreadLocal);
+            int rc = PCP_ERR_CUDA;
+            if (e == cudaSuccess) {
+                rc = train_step_body(m, ts, ts->stage_x, b, n, y_cls ? ts->stage_ycls : nullptr, y_seg ? ts->stage_yseg : nullptr,
+                                     y_se3 ? ts->stage_se3 : nullptr, cfg, global_batch, nullptr, nullptr, ts->step_scalars, gs);
+                e = cudaStreamEndCapture(gs, &graph);
+            }
+            if (rc == PCP_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&ts->graph_exec, graph, 0);
+            if (graph) cudaGraphDestroy(graph);
+            if (rc != PCP_OK || e != cudaSuccess || !ts->graph_exec) {
+                if (getenv("PCP_TRAIN_GRAPH_DEBUG"))
+                    fprintf(stderr, "pcp: training-step capture failed (rc %d, %s; %s): steps stay eager\n", rc, cudaGetErrorString(e), pcp_last_error());
+                cudaGetLastError();                                  // the capture did not take: this model stays eager
+                ts->graph_exec = nullptr; ts->graph_broken = true;
+            }
+        }
+        if (ts->graph_exec) {
+            PCP_CUDA_OK(cudaGraphLaunch(ts->graph_exec, gs));
+            ran = true;
+            if (getenv("PCP_TRAIN_GRAPH_DEBUG")) fprintf(stderr, "pcp: training step replayed from its graph\n");
+        }
+        PCP_CUDA_OK(cudaEventRecord(ts->graph_out, gs));           // join: the caller's stream continues behind the step
+        PCP_CUDA_OK(cudaStreamWaitEvent(st, ts->graph_out, 0));
+    }
+    if (!ran) {
+        PCP_TRY(train_step_body(m, ts, d_x, b, n, y_cls, y_seg, y_se3, cfg, global_batch, mask1, mask2, nullptr, st));
+        ts->graph_seen++;
     }
     m->dev_newer = true;          // BN moving statistics were updated on the device
     m->prepared = false;

@@ -419,6 +419,34 @@ def test_bf16_second_step_matches_fresh_model(lib, trainable, weights, batches):
     print(f"[second step] worst tensor {k}: {worst[k][0]:.2e} against the fresh models' own {worst[k][1]:.2e}")
 
 
+@pytest.mark.parametrize("precision", ["bf16", "fp32"])
+def test_captured_step_matches_eager_steps(lib, precision, monkeypatch):
+    """From the third step of a configuration on, the step is replayed as one CUDA graph (inputs through staging buffers, the
+    dropout seed / sample offset of the step through device memory).  Six steps on six different batches with six different
+    Philox dropout seeds, weights held fixed (training itself is chaotic: Adam turns the atomics' 1e-7 into a different
+    trajectory within two updates): the losses of the graph-replaying model equal those of a model that stays eager
+    (PCP_TRAIN_GRAPH=0) — the forward is bit-reproducible — and the gradients of the last step agree to the atomics' noise."""
+    C, P, b, n = 8, 8, 12, 256
+    batches = [make_batch(100 + i, b, n, C, P)[:2] for i in range(6)]
+    runs = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("PCP_TRAIN_GRAPH", mode)
+        m, p = build(C, P, False, ALL, (1.0, 0.5, 0.25), (True, True), precision=precision)
+        losses = []
+        for i, (x, y) in enumerate(batches):
+            m._step = 7 * i                     # the dropout seed of the step is seed + step
+            losses.append(m.train_on_batch(x, y, apply=False)["loss"])
+        runs[mode] = (losses, m.gradients_dict())
+    (l0, g0), (l1, g1) = runs["0"], runs["1"]
+    assert len(set(l0)) == 6
+    for a, c in zip(l0, l1):
+        assert abs(a - c) <= 1e-6 * max(1.0, abs(a)), (l0, l1)
+    gmax = max(float(np.abs(v).max()) for v in g0.values())
+    worst = max(float(np.abs(g0[k].astype(np.float64) - g1[k]).max()) / max(float(np.abs(g0[k]).max()), 1e-2 * gmax) for k in g0)
+    print(f"[graph vs eager, {precision}] largest gradient difference {worst:.2e}")
+    assert worst <= (3e-2 if precision == "bf16" else 1e-4), worst
+
+
 def test_bf16_fit_learns(lib):
     from pointcloudprocessing_b200.pointnet import keras_compat as K
     C, P, b, n = 4, 3, 16, 128
