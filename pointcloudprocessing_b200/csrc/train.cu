@@ -295,9 +295,24 @@ bn_finalize_kernel(const double *__restrict__ parts, int nparts, double rows, in
     __shared__ double sh8[2][8];
     const int c = blockIdx.x;
     double sum = 0, sumsq = 0;
-    if (batch) {
-        sum = block_parts_sum(parts + c, (size_t)2 * C, nparts, sh8[0]);
-        sumsq = block_parts_sum(parts + C + c, (size_t)2 * C, nparts, sh8[1]);
+    if (batch) {                                       // both sums in one pass: their loads leave together, one pair of barriers
+        const int tid = threadIdx.x;
+        const size_t stride = (size_t)2 * C;
+        double a[4], q[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int p = tid + 256 * u;
+            a[u] = p < nparts ? parts[(size_t)p * stride + c] : 0.0;
+            q[u] = p < nparts ? parts[(size_t)p * stride + C + c] : 0.0;
+        }
+        double s = (a[0] + a[1]) + (a[2] + a[3]), s2 = (q[0] + q[1]) + (q[2] + q[3]);
+        for (int p = tid + 1024; p < nparts; p += 256) { s += parts[(size_t)p * stride + c]; s2 += parts[(size_t)p * stride + C + c]; }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
+        if ((tid & 31) == 0) { sh8[0][tid >> 5] = s; sh8[1][tid >> 5] = s2; }
+        __syncthreads();
+        sum = ((sh8[0][0] + sh8[0][1]) + (sh8[0][2] + sh8[0][3])) + ((sh8[0][4] + sh8[0][5]) + (sh8[0][6] + sh8[0][7]));
+        sumsq = ((sh8[1][0] + sh8[1][1]) + (sh8[1][2] + sh8[1][3])) + ((sh8[1][4] + sh8[1][5]) + (sh8[1][6] + sh8[1][7]));
     }
     if (threadIdx.x) return;
     float mu, var;

@@ -68,12 +68,15 @@ pool_implicit_stats_kernel(const float *__restrict__ gram, const double *__restr
         // G symmetric: coalesced over k.  Four independent chains, eight loads in flight: as ONE chain of 128 dependent fp64
         // multiply-adds behind 128 dependent loads the kernel took 49 us per layer.
         double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-#pragma unroll 2
-        for (int l = 0; l < 128; l += 4) {
-            const float g0 = __ldg(gram + l * 128 + k), g1 = __ldg(gram + (l + 1) * 128 + k), g2 = __ldg(gram + (l + 2) * 128 + k),
-                        g3 = __ldg(gram + (l + 3) * 128 + k);
-            t0 = fma((double)g0, ws[warp][l], t0); t1 = fma((double)g1, ws[warp][l + 1], t1);
-            t2 = fma((double)g2, ws[warp][l + 2], t2); t3 = fma((double)g3, ws[warp][l + 3], t3);
+        for (int l = 0; l < 128; l += 16) {                // sixteen loads in flight, four accumulation chains
+            float gv[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) gv[u] = __ldg(gram + (l + u) * 128 + k);
+#pragma unroll
+            for (int u = 0; u < 16; u += 4) {
+                t0 = fma((double)gv[u], ws[warp][l + u], t0); t1 = fma((double)gv[u + 1], ws[warp][l + u + 1], t1);
+                t2 = fma((double)gv[u + 2], ws[warp][l + u + 2], t2); t3 = fma((double)gv[u + 3], ws[warp][l + u + 3], t3);
+            }
         }
         const double t = (t0 + t1) + (t2 + t3);
         qd += ws[warp][k] * t;
