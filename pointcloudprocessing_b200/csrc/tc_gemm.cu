@@ -22,7 +22,9 @@ __device__ __forceinline__ float bf16_trunc_rn(float x) { return __bfloat162floa
 // kMinBlocks = 3: the K <= 128 per-point layers of the training step.  One k-tile or two means one or two ring stages
 // (33 / 65 KB of shared memory), and at 96 registers three CTAs fit an SM: each CTA is one dependent chain (weights and
 // activations in, one MMA group, TMEM out), so the tiles in flight per SM are what hides its latency.
-template <int kMinBlocks>
+// kSplitK: the k-tiles are dealt over grid.z CTAs which add their products with atomics (TcGemmParams::ksplit); a separate
+// instantiation so that the plain kernel's code is exactly what it was (the fp32_tc forward lost 5 % to the shared version).
+template <int kMinBlocks, bool kSplitK>
 __global__ void __launch_bounds__(kGemmThreads, kMinBlocks)
 tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nsplit)
 {   // bnt: MMA N of this CTA; img_rows: rows of a weight-image tile; nsplit = img_rows / bnt column blocks per image tile
@@ -40,8 +42,8 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
     const int g = blockIdx.y / mtiles, mt = blockIdx.y % mtiles;
     const int row0 = mt * 128;
     const int rows_valid = min(128, p.M - row0);
-    const int KT = (p.K >> 6) / (int)gridDim.z;          // this CTA's k-tiles: [kt0, kt0 + KT) of the matrix (split-K over grid.z)
-    const int kt0 = (int)blockIdx.z * KT;
+    const int KT = kSplitK ? (p.K >> 6) / (int)gridDim.z : (p.K >> 6);     // this CTA's k-tiles: [kt0, kt0 + KT) of the matrix
+    const int kt0 = kSplitK ? (int)blockIdx.z * KT : 0;
     const uint32_t b_tile_bytes = (uint32_t)bnt * 128u;
 
     if (tid == 0) {
@@ -158,7 +160,7 @@ tc_gemm_kernel(const TcGemmParams p, int bnt, int mtiles, int img_rows, int nspl
             if (p.C32) {
                 float *Cg = p.C32 + (size_t)g * p.c_group_stride;
                 if (p.dbg & 1) {
-                } else if (gridDim.z > 1) {
+                } else if (kSplitK) {
                     if (row_ok) {
                         float *dst = p.C32 + c_off + nbase;
 #pragma unroll
@@ -322,8 +324,9 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
     const int64_t gy = (int64_t)mtiles * p.groups;
     static bool attr = false;
     if (!attr) {
-        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
-        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
+        PCP_CUDA_OK(cudaFuncSetAttribute(tc_gemm_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
         attr = true;
     }
     PCP_REQUIRE(gy <= 65535, PCP_ERR_UNSUPPORTED, "tc_gemm: %lld row tiles exceed one launch", (long long)gy);
@@ -335,15 +338,16 @@ int tc_gemm(const TcGemmParams &p, cudaStream_t st)
     // the ring only uses min(K / 64, stages) stages
     const int stages_used = std::min(p.K / 64 / p.ksplit, kGemmStages);
     static const bool no_dense = getenv("PCP_TC_GEMM_NO_DENSE") != nullptr;
-    const bool dense = !no_dense && stages_used <= 2 && (int64_t)ntiles * nsplit * gy >= 3 * (int64_t)sm_count();
+    const bool dense = !no_dense && p.ksplit == 1 && stages_used <= 2 && (int64_t)ntiles * nsplit * gy >= 3 * (int64_t)sm_count();
     cfg.gridDim = dim3(ntiles * nsplit, (unsigned)gy, (unsigned)p.ksplit); cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = (size_t)stages_used * kGemmStageBytes + 1024; cfg.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = no_pdl ? 0 : 1;
-    if (dense) PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel<3>, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
-    else PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel<2>, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
+    if (p.ksplit > 1) PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel<2, true>, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
+    else if (dense) PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel<3, false>, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
+    else PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, tc_gemm_kernel<2, false>, p, bnt_img / nsplit, mtiles, bnt_img, nsplit));
     PCP_CHECK_LAUNCH();
     return PCP_OK;
 }
