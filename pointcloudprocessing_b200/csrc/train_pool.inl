@@ -51,32 +51,34 @@ pool_colsum_kernel(const float *__restrict__ A, int64_t rows, double *__restrict
     }
 }
 
-// column sums / sums of squares of Z = A.W from the Gram matrix: one warp per output channel
-__global__ void __launch_bounds__(128)
+// column sums / sums of squares of Z = A.W from the Gram matrix: one warp per output channel, eight channels per CTA.
+// The Gram matrix (64 KB) is staged in shared memory once per CTA: as global loads behind one another the 512 steps of a lane
+// were a chain of L2 round trips (49 us per layer; more loads in flight only traded them for register pressure).
+constexpr int kStatsWarps = 8;
+constexpr size_t kStatsSmem = 128 * 128 * sizeof(float) + kStatsWarps * 128 * sizeof(double);
+__global__ void __launch_bounds__(kStatsWarps * 32)
 pool_implicit_stats_kernel(const float *__restrict__ gram, const double *__restrict__ asum, const float *__restrict__ W, int cout,
                            double *__restrict__ sum, double *__restrict__ sumsq)
 {
-    __shared__ double ws[4][128];
+    extern __shared__ __align__(16) unsigned char stats_smem[];
+    float *gs = reinterpret_cast<float *>(stats_smem);                                    // [128][128]
+    double (*ws)[128] = reinterpret_cast<double (*)[128]>(stats_smem + 128 * 128 * sizeof(float));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int j = blockIdx.x * 4 + warp;
+    const int j = blockIdx.x * kStatsWarps + warp;
+    for (int i = threadIdx.x; i < 128 * 32; i += kStatsWarps * 32)
+        reinterpret_cast<float4 *>(gs)[i] = __ldg(reinterpret_cast<const float4 *>(gram) + i);
+    if (j < cout)
+        for (int k = lane; k < 128; k += 32) ws[warp][k] = (double)bf16_round(__ldg(W + (size_t)k * cout + j));
+    __syncthreads();
     if (j >= cout) return;
-    for (int k = lane; k < 128; k += 32) ws[warp][k] = (double)bf16_round(__ldg(W + (size_t)k * cout + j));
-    __syncwarp();
     double s = 0, qd = 0;
     for (int i = 0; i < 4; ++i) {
         const int k = lane + 32 * i;
-        // G symmetric: coalesced over k.  Four independent chains, eight loads in flight: as ONE chain of 128 dependent fp64
-        // multiply-adds behind 128 dependent loads the kernel took 49 us per layer.
-        double t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-        for (int l = 0; l < 128; l += 16) {                // sixteen loads in flight, four accumulation chains
-            float gv[16];
-#pragma unroll
-            for (int u = 0; u < 16; ++u) gv[u] = __ldg(gram + (l + u) * 128 + k);
-#pragma unroll
-            for (int u = 0; u < 16; u += 4) {
-                t0 = fma((double)gv[u], ws[warp][l + u], t0); t1 = fma((double)gv[u + 1], ws[warp][l + u + 1], t1);
-                t2 = fma((double)gv[u + 2], ws[warp][l + u + 2], t2); t3 = fma((double)gv[u + 3], ws[warp][l + u + 3], t3);
-            }
+        double t0 = 0, t1 = 0, t2 = 0, t3 = 0;                 // G symmetric: gs[l][k] is conflict-free over the lanes
+#pragma unroll 4
+        for (int l = 0; l < 128; l += 4) {
+            t0 = fma((double)gs[l * 128 + k], ws[warp][l], t0); t1 = fma((double)gs[(l + 1) * 128 + k], ws[warp][l + 1], t1);
+            t2 = fma((double)gs[(l + 2) * 128 + k], ws[warp][l + 2], t2); t3 = fma((double)gs[(l + 3) * 128 + k], ws[warp][l + 3], t3);
         }
         const double t = (t0 + t1) + (t2 + t3);
         qd += ws[warp][k] * t;
@@ -326,7 +328,15 @@ static int pooled_forward(const PoolLayer &L, const float *A, float *g, cudaStre
             PCP_TRY(sync_sum(L.pb.asum_g, 128, 1, st));
             gram_s = L.pb.gram_g; asum_s = L.pb.asum_g;
         }
-        pool_implicit_stats_kernel<<<(L.cout + 3) / 4, 128, 0, st>>>(gram_s, asum_s, L.W, L.cout, L.red, L.red + L.cout);
+        static bool stats_attr[64] = {};
+        int dev = 0;
+        PCP_CUDA_OK(cudaGetDevice(&dev));
+        if (dev >= 0 && dev < 64 && !stats_attr[dev]) {
+            PCP_CUDA_OK(cudaFuncSetAttribute(pool_implicit_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStatsSmem));
+            stats_attr[dev] = true;
+        }
+        pool_implicit_stats_kernel<<<(L.cout + kStatsWarps - 1) / kStatsWarps, kStatsWarps * 32, kStatsSmem, st>>>(gram_s, asum_s, L.W, L.cout, L.red,
+                                                                                                              L.red + L.cout);
         PCP_CHECK_LAUNCH();
     }
     bn_finalize_kernel<<<L.cout, 256, 0, st>>>(L.red, 1, (double)rows * g_sync.scale, L.cout, L.batch ? 1 : 0, L.gamma, L.beta_in, L.mov_mean,
