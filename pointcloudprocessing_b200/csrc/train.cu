@@ -4,11 +4,19 @@
 // PointNet.py:447-451), the full backward pass into one flat gradient buffer, and fused keras Adam.
 //
 // Structure: every weighted layer is Z = A . W (GEMM), then BN (batch or moving statistics) + ReLU as an
-// elementwise pass.  Pre-BN activations Z are kept for the backward pass; post-activation tensors are
-// recomputed from Z when a weight gradient needs them.  The reduce_max over points (PointNet.py:248,429) is
-// fused with BN + ReLU into one column-max pass and its gradient is split evenly between tied maxima (the
-// tf.reduce_max convention).  GEMMs go through train_mm_* below: fp32 CUDA-core tiles in
-// PCP_PRECISION_FP32, bf16 tcgen05 tiles with fp32 accumulation in PCP_PRECISION_BF16 (tc_train.cu).
+// elementwise pass.  Pre-BN activations Z are kept for the backward pass, and so are the trunk's post-activation
+// tensors (TL::Y); the heads' are recomputed from Z when a weight gradient needs them.  The reduce_max over points
+// (PointNet.py:248,429) is fused with BN + ReLU into one column-max pass and its gradient is split evenly between
+// tied maxima (the tf.reduce_max convention) — fp32 mode; the bf16 mode handles the pooled layers
+// without their (rows x 1024) tensors (train_pool.inl).  GEMMs go through mm_nn / mm_nt / mm_tn below: fp32 CUDA-core
+// tiles in PCP_PRECISION_FP32, bf16 tcgen05 tiles with fp32 accumulation in PCP_PRECISION_BF16 (tc_gemm.cu,
+// tc_gemm_tma.cu, tc_train.cu), their weight images re-packed once per step (ImgCache).
+//
+// Per-column reductions (BN statistics, BN backward sums, the 3-channel weight gradients) end in per-block partial
+// sums that one block per element adds in block order (reduce_parts_kernel / bn_finalize_kernel): no same-address
+// atomics, the same bits on every run.  train_step_impl splits the step into a prelude (allocation, tables), the
+// stream-ordered body (train_step_body) and the metric read-back; the body is replayed as one CUDA graph once a
+// configuration has run twice.
 #include <cmath>
 #include <cstdlib>
 #include <cstring>

@@ -9,7 +9,9 @@
 //   forward   Z is a linear image of the 128-wide input A, so its batch statistics follow from the Gram matrix of A:
 //               sum_i z_ij = (1^T A) w_j ,  sum_i z_ij^2 = w_j^T (A^T A) w_j            (A^T A on tcgen05, 128 x 128)
 //             and BN+ReLU are monotone per channel, so max_i relu(bn(z_ij)) = relu(bn(max_i z_ij)) for sc_j >= 0 (min for
-//             sc_j < 0): one GEMM whose epilogue keeps only the per-cloud column extrema and their rows (tc_gemm Ext_*).
+//             sc_j < 0 — folded away: the GEMM multiplies by W diag(sign gamma), so the pooled row is always the arg max
+//             of z' = sign(gamma) z, and z = sign(gamma) z' exactly): one GEMM whose epilogue keeps only the per-cloud
+//             column maximum and its row (tc_train.cu tc_pool_extrema).
 //   backward  dY is non-zero only at the selected row of each (cloud, channel), and BN backward adds an affine function
 //             of Z per channel:  dZ_ij = sc_j dY_ij + c0_j + c1_j z_ij , c1 = -sc inv s2 / M , c0 = -sc s1 / M - c1 mean.
 //             With Z = A W:   dW = A^T dZ = (A^T A) W diag(c1) + (A^T 1) c0^T + sum_c S_cj A[arg_cj, :]
