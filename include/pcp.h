@@ -259,14 +259,18 @@ typedef struct pcp_train_config {
 /* One training step on the local shard: forward (training BN on thawed layers, dropout),
  * losses (SCCE on probabilities clip 1e-7, MSE on R), backward into the flat gradient buffer.
  * h_metrics (8 floats): loss, cls_loss, seg_loss, se3_loss, cls_acc, seg_acc, se3_rmse, reg_loss.
- * global_batch: the loss mean divides by this (data parallel: sum over ranks == global mean). */
+ * global_batch: the loss mean divides by this (data parallel: sum over ranks == global mean).
+ * From the third call with the same configuration (shapes, loss weights, thawed groups, which labels are given) the step is
+ * replayed as one CUDA graph on a stream of the library's own, forked from and joined to `stream` by events; the inputs are
+ * copied into staging buffers first, so the caller's pointers may change from call to call.  Steps with a BatchNorm
+ * all-reduce callback or explicit dropout masks stay eager; PCP_TRAIN_GRAPH=0 in the environment keeps every step eager. */
 int pcp_model_loss_backward(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *d_y_cls,
                             const int32_t *d_y_seg, const float *d_y_se3, const pcp_train_config *cfg,
                             int global_batch, const float *d_mask1, const float *d_mask2, float *h_metrics,
                             pcp_stream stream);
 /* keras Model.evaluate / the validation pass of fit (pointnet_train.py:221-228): inference-mode forward and the
- * same 8 metrics as pcp_model_loss_backward (feature-transform regulariser excluded: R64 is not materialised at
- * inference).  Label pointers may be NULL (that loss reads 0; NULL d_y_seg skips the segmentation head). */
+ * same 8 metrics as pcp_model_loss_backward (both T-Net regularisers included when the model was built with them).
+ * Label pointers may be NULL (that loss reads 0; NULL d_y_seg skips the segmentation head). */
 int pcp_model_evaluate(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *d_y_cls, const int32_t *d_y_seg,
                        const float *d_y_se3, const pcp_train_config *cfg, float *h_metrics, pcp_stream stream);
 /* flat fp32 gradient buffer (device) for the NCCL all-reduce done by the host side */

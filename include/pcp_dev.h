@@ -28,6 +28,9 @@ int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t rows, int ci
  * weight-image packer + tcgen05 GEMM of the bf16 training step; W is (k x n) row-major, or (n x k) row-major when
  * transpose_w (dA = dZ . W^T).  Host pointers; h_c is read when accumulate != 0. */
 int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate, float *h_c);
+/* the same with split-K: the k / 64 k-tiles are dealt over ksplit CTAs that ADD their products into h_c with fp32 atomics
+ * (the long, skinny input-gradient GEMMs of the T-Net tails) */
+int pcp_selftest_tc_mm_splitk(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int ksplit, float *h_c);
 /* test hook: C[g] (m x n) = act(bf16(A[g]) . bf16(W) + bias[g]) with bf16 activations in HBM (large shapes run the persistent TMA
  * kernel, small ones the per-tile kernel); out_kind 0 fp32, 1 bf16, 2 softmax (n <= 32); h_c is fp32; h_bias (groups x n) or NULL */
 int pcp_selftest_tc_gemm_bf16(const float *h_a, const float *h_w, const float *h_bias, int64_t m, int groups, int k, int n,

@@ -98,6 +98,7 @@ SIGNATURES = {
     "pcp_selftest_umma2": (_i32, [_fp, _fp, _i32, _i32, _fp]),
     "pcp_selftest_wgrad": (_i32, [_fp, _fp, _i64, _i32, _i32, _fp]),
     "pcp_selftest_tc_mm": (_i32, [_fp, _fp, _i64, _i32, _i32, _i32, _i32, _fp]),
+    "pcp_selftest_tc_mm_splitk": (_i32, [_fp, _fp, _i64, _i32, _i32, _i32, _i32, _fp]),
     "pcp_selftest_tc_gemm_bf16": (_i32, [_fp, _fp, _fp, _i64, _i32, _i32, _i32, _i32, _i32, _fp]),
     "pcp_bench_tc_gemm": (_i32, [_i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _fp]),
     "pcp_selftest_pooled_layer": (_i32, [_fp, _fp, _fp, _fp, _fp, _i32, _i64, _i32, _i32, _fp, _fp, _fp, _fp, _fp, _fp, _fp]),

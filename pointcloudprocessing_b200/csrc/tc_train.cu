@@ -688,10 +688,10 @@ extern "C" int pcp_selftest_wgrad(const float *h_a, const float *h_dz, int64_t r
 
 // test hook: C (rows x n) (+)= A (rows x k) . W with the device-packed weight image; W is (k x n) row-major, or (n x k)
 // row-major when transpose_w (the input-gradient form dA = dZ . W^T); host in / host out, synchronous
-extern "C" int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate,
-                                  float *h_c)
+static int selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate, int ksplit, float *h_c)
 {
-    PCP_REQUIRE(h_a && h_w && h_c && rows >= 1 && k >= 64 && n >= 1, PCP_ERR_INVALID, "pcp_selftest_tc_mm: bad arguments");
+    using namespace pcp;
+    PCP_REQUIRE(h_a && h_w && h_c && rows >= 1 && k >= 64 && n >= 1 && ksplit >= 1, PCP_ERR_INVALID, "pcp_selftest_tc_mm: bad arguments");
     float *da = nullptr, *dw = nullptr, *dc = nullptr;
     uint8_t *img = nullptr;
     PCP_CUDA_OK(cudaMalloc(&da, (size_t)rows * k * 4)); PCP_CUDA_OK(cudaMalloc(&dw, (size_t)k * n * 4));
@@ -704,6 +704,7 @@ extern "C" int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t ro
         TcGemmParams p;
         p.A = da; p.a_f32 = 1; p.lda = k; p.Bimg = img; p.C32 = dc; p.ldc = n; p.M = (int)rows; p.N = n; p.K = k;
         p.accumulate = accumulate ? 1 : 0;
+        p.ksplit = ksplit;
         rc = tc_gemm(p, nullptr);
     }
     cudaError_t e = cudaDeviceSynchronize();
@@ -714,6 +715,19 @@ extern "C" int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t ro
     if (rc == PCP_OK) PCP_CUDA_OK(cudaMemcpy(h_c, dc, (size_t)rows * n * 4, cudaMemcpyDeviceToHost));
     cudaFree(da); cudaFree(dw); cudaFree(dc); cudaFree(img);
     return rc;
+}
+
+extern "C" int pcp_selftest_tc_mm(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int accumulate,
+                                  float *h_c)
+{
+    return selftest_tc_mm(h_a, h_w, rows, k, n, transpose_w, accumulate, 1, h_c);
+}
+
+// the same with the k-tiles dealt over ksplit CTAs that ADD their products into h_c (TcGemmParams::ksplit; k / 64 a multiple of it)
+extern "C" int pcp_selftest_tc_mm_splitk(const float *h_a, const float *h_w, int64_t rows, int k, int n, int transpose_w, int ksplit,
+                                         float *h_c)
+{
+    return selftest_tc_mm(h_a, h_w, rows, k, n, transpose_w, 0, ksplit, h_c);
 }
 
 // development hook: time tc_gemm alone on device-resident synthetic operands (bf16 or fp32 activations, zero weights are fine:

@@ -61,6 +61,25 @@ def test_wgrad_mn_major_tensor_core(lib, rows, cin, cout):
     assert err < 2e-5, err
 
 
+@pytest.mark.parametrize("rows,k,n,transpose,ksplit", [(256, 4096, 256, 1, 16), (100, 1024, 512, 1, 4), (300, 512, 64, 0, 8), (7, 1024, 9, 0, 2)])
+def test_training_gemm_split_k(lib, rows, k, n, transpose, ksplit):
+    """tc_gemm with the k-tiles dealt over `ksplit` CTAs that add their products with fp32 atomics (the T-Net tails' long,
+    skinny input-gradient GEMMs: 4096 -> 256 over 256 rows walked 64 dependent k-tiles on 16 CTAs) — on top of what C holds."""
+    import ctypes as C
+    rng = np.random.default_rng(rows + k + n + ksplit)
+    a = (rng.standard_normal((rows, k)) + 1.0).astype(np.float32)
+    w = rng.standard_normal((n, k) if transpose else (k, n)).astype(np.float32)
+    c0 = rng.standard_normal((rows, n)).astype(np.float32)
+    c = c0.copy()
+    fp = lambda x: x.ctypes.data_as(C.POINTER(C.c_float))
+    st = lib.pcp_selftest_tc_mm_splitk(fp(a), fp(w), rows, k, n, transpose, ksplit, fp(c))
+    assert st == 0, lib.pcp_last_error()
+    wr = _bf16_round(w).astype(np.float64)
+    ref = _bf16_round(a).astype(np.float64) @ (wr.T if transpose else wr) + c0
+    err = np.abs(c - ref).max() / np.abs(ref).max()
+    assert err < 2e-5, err
+
+
 @pytest.mark.parametrize("rows,k,n,transpose,acc", [(768, 64, 64, 0, 0), (768, 64, 128, 0, 0), (768, 128, 1024, 0, 0), (6, 1024, 512, 0, 0),
                                                     (6, 256, 9, 0, 0), (6, 256, 4096, 0, 0), (768, 128, 8, 0, 0), (300, 512, 256, 0, 0),
                                                     (768, 64, 3, 1, 0), (768, 1024, 128, 1, 0), (768, 128, 64, 1, 1), (6, 512, 1024, 1, 0),
