@@ -820,6 +820,7 @@ struct TL {                       // one weighted layer's training record
     int id = -1;
     float *Z = nullptr;           // pre-BN output (rows x cout)
     float *Y = nullptr;           // relu(bn(Z)) kept for the backward pass (trunk layers; 0.7 GB at 256 x 1024 instead of seven recomputations)
+    __nv_bfloat16 *Y16 = nullptr; // the same rounded to bf16 (the 128-wide inputs of the pooled layers: their backward GEMM streams it by TMA)
     int64_t rows = 0;
     int cin = 0, cout = 0;
     bool has_bn = false, batch = false, trainable = false;
@@ -951,6 +952,7 @@ static int ensure_arena(pcp_model *m, TrainState *ts, int b, int64_t n)
         if (i != L_SEG5 && i != L_CLS3 && !(pooled && ts->implicit_pool)) want(&t.Z, (size_t)t.rows * S.cout * 4);
         if (i == L_IT_C1 || i == L_IT_C2 || i == L_S1_1 || i == L_FT_C1 || i == L_FT_C2 || i == L_S2_1 || i == L_S2_2)
             want(&t.Y, (size_t)t.rows * S.cout * 4);
+        if (i == L_IT_C2 || i == L_FT_C2 || i == L_S2_2) want(&t.Y16, (size_t)t.rows * S.cout * 2);
         if (S.has_bn) {
             want(&t.mean, S.cout * 4); want(&t.inv, S.cout * 4); want(&t.sc, S.cout * 4); want(&t.beta, S.cout * 4);
             want(&t.red, (size_t)S.cout * 2 * 8);
@@ -1480,7 +1482,9 @@ static int pooled_layer_bwd(pcp_model *m, TrainState *ts, int li, int slot, int 
     const float *Aprev = nullptr;
     if (ts->implicit_pool) {
         PCP_TRY(layer_act(ts->L[lprev], ts->Y128, &Aprev, st));
-        return pooled_backward(make_pool_layer(m, ts, li, slot), Aprev, g, dg, grad(m, S.t_kernel), grad(m, S.t_gamma), grad(m, S.t_beta), dA, st);
+        PoolLayer PL = make_pool_layer(m, ts, li, slot);
+        PL.A16 = (g_tc.on && Aprev == ts->L[lprev].Y) ? ts->L[lprev].Y16 : nullptr;       // written by this step's forward bn_act
+        return pooled_backward(PL, Aprev, g, dg, grad(m, S.t_kernel), grad(m, S.t_gamma), grad(m, S.t_beta), dA, st);
     }
     PCP_TRY(pool_bwd(m, ts->L[li], ts->b, ts->n, g, dg, ts->cnt, ts->G1024, st));
     PCP_TRY(layer_act(ts->L[lprev], ts->Y128, &Aprev, st));
@@ -1543,7 +1547,7 @@ static int train_step_body(pcp_model *m, TrainState *ts, const float *d_x, int b
     __nv_bfloat16 *a16 = g_tc.on ? ts->G16 : nullptr, *a16b = g_tc.on ? reinterpret_cast<__nv_bfloat16 *>(ts->Y64b) : nullptr;
     if (full) {
         PCP_TRY(layer_fwd_train(m, L[L_IT_C1], ts->pcn, L[L_IT_C1].Y, st, nullptr, a16));                                 // TNet.call :423
-        PCP_TRY(layer_fwd_train(m, L[L_IT_C2], L[L_IT_C1].Y, L[L_IT_C2].Y, st, a16));                                // :424
+        PCP_TRY(layer_fwd_train(m, L[L_IT_C2], L[L_IT_C1].Y, L[L_IT_C2].Y, st, a16, a16 ? L[L_IT_C2].Y16 : nullptr));                                // :424
         PCP_TRY(pooled_layer_fwd(m, ts, L_IT_C3, 0, L[L_IT_C2].Y, ts->g1, st));                             // :425-429
         PCP_TRY(tnet_tail_fwd(m, ts, L_IT_C1, m->t_it_w, m->t_it_b, 3, ts->g1, ts->Ys[0], ts->Ys[1], ts->R, st));
         pc_matmul3_kernel<<<grid_for(M), 256, 0, st>>>(ts->pcn, ts->R, n, M, ts->X3);                    // X = pc @ R  :207
@@ -1557,7 +1561,7 @@ static int train_step_body(pcp_model *m, TrainState *ts, const float *d_x, int b
     const float *X64 = ts->X2;
     if (full) {
         PCP_TRY(layer_fwd_train(m, L[L_FT_C1], ts->X2, L[L_FT_C1].Y, st, a16b, a16));
-        PCP_TRY(layer_fwd_train(m, L[L_FT_C2], L[L_FT_C1].Y, L[L_FT_C2].Y, st, a16));
+        PCP_TRY(layer_fwd_train(m, L[L_FT_C2], L[L_FT_C1].Y, L[L_FT_C2].Y, st, a16, a16 ? L[L_FT_C2].Y16 : nullptr));
         PCP_TRY(pooled_layer_fwd(m, ts, L_FT_C3, 1, L[L_FT_C2].Y, ts->g2, st));
         PCP_TRY(tnet_tail_fwd(m, ts, L_FT_C1, m->t_ft_w, m->t_ft_b, 64, ts->g2, ts->Ys[2], ts->Ys[3], ts->R64, st));   // :227
         GemmArgs g;                                                                                     // X_64 = X @ R_64 :228
@@ -1567,7 +1571,7 @@ static int train_step_body(pcp_model *m, TrainState *ts, const float *d_x, int b
         X64 = ts->X64;
     }
     PCP_TRY(layer_fwd_train(m, L[L_S2_1], X64, L[L_S2_1].Y, st, nullptr, a16));                                          // :236
-    PCP_TRY(layer_fwd_train(m, L[L_S2_2], L[L_S2_1].Y, L[L_S2_2].Y, st, a16));                                     // :239
+    PCP_TRY(layer_fwd_train(m, L[L_S2_2], L[L_S2_1].Y, L[L_S2_2].Y, st, a16, a16 ? L[L_S2_2].Y16 : nullptr));                                     // :239
     PCP_TRY(pooled_layer_fwd(m, ts, L_S2_3, 2, L[L_S2_2].Y, ts->g3, st));                                  // :242-248
 
     // ---- classification head (:252-263) ----

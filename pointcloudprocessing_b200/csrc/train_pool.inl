@@ -299,6 +299,7 @@ struct PoolLayer {                      // everything one pooled layer's implici
     int b = 0; int64_t n = 0; int cout = 0;
     bool batch = false, trainable = false;
     PoolBufs pb;
+    const __nv_bfloat16 *A16 = nullptr; // optional: the layer's input already rounded to bf16 (same values the GEMMs round to)
     BnP bnp() const { return BnP{mean, sc, beta, inv}; }
 };
 
@@ -377,7 +378,7 @@ static int pooled_backward(const PoolLayer &L, const float *A, const float *g, c
         if (L.batch) {
             pool_q_kernel<<<128, 1024, (size_t)L.cout * 4, st>>>(L.pb.Wt, L.pb.c0, L.pb.c1, L.cout, L.pb.Q, L.pb.q);
             PCP_CHECK_LAUNCH();
-            PCP_TRY(mm_nn(A, rows, 128, L.pb.Q, 128, 128, dA, L.pb.q, st));
+            PCP_TRY(mm_nn(A, rows, 128, L.pb.Q, 128, 128, dA, L.pb.q, st, 1, 0, L.A16));
         } else {
             PCP_CUDA_OK(cudaMemsetAsync(dA, 0, (size_t)rows * 512, st));
         }
