@@ -119,9 +119,10 @@ __device__ __forceinline__ uint32_t wm2_slot(int s) { return s == 0 ? 0u : (s ==
 constexpr int kTraceEvents = 2048;
 constexpr uint64_t kFinalInFlight = 2;   // final-layer accumulator granules allowed in the tensor queue at once
 // role: 0 front (warp 0), 1 final epilogue (warp 4), 2 MMA issuer, 3 loader; slot = (cta*4 + role)
+template <bool kTrace>
 __device__ __forceinline__ void trace_ev(const ChainParams &p, uint32_t rank, int role, uint32_t &cnt, uint32_t code)
 {
-    if (p.trace && blockIdx.x < 2 && cnt < kTraceEvents) {
+    if (kTrace && p.trace && blockIdx.x < 2 && cnt < kTraceEvents) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         p.trace[((size_t)(rank * 4 + role) * kTraceEvents + cnt) * 2] = code;
@@ -138,6 +139,9 @@ struct Chain2Shared {
     alignas(16) float mid_t[3][128];
 };
 
+// kTrace: the PCP_CHAIN_TRACE build of the kernel (role timelines of cluster 0); the production instantiation carries no
+// trace code at all — its hot loops are sized for the instruction cache (section 4.1 of DESIGN.md)
+template <bool kTrace>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kChainThreads, 1)
 chain2_kernel(const ChainParams p)
 {
@@ -216,7 +220,7 @@ chain2_kernel(const ChainParams p)
         float q0 = 0.f, q1 = 0.f, q2 = 0.f, nq0 = 0.f, nq1 = 0.f, nq2 = 0.f;
         if (nsteps > fgp) load_point(fgp, nq0, nq1, nq2);
         for (int64_t it = fgp; it < nsteps; it += 2) {
-            if (tr) trace_ev(p, rank, 0, tcnt, 0x100);
+            if (tr) trace_ev<kTrace>(p, rank, 0, tcnt, 0x100);
             q0 = nq0; q1 = nq1; q2 = nq2;
 #pragma unroll 1                                           // code size: see the final epilogue below
             for (int c = 0; c < 8; ++c) {
@@ -238,11 +242,11 @@ chain2_kernel(const ChainParams p)
             // visible to the async proxy by fence.proxy.async above, in program order before the arrive; a
             // release.cluster here costs ~0.5 us of MEMBAR on the critical path of every layer.
             if (lane == 0) { if (rank == 0) mbar_arrive(&sh.a_full[fgp]); else mbar_arrive_cluster_relaxed(&sh.a_full[fgp], 0); }
-            if (tr) trace_ev(p, rank, 0, tcnt, 0x101);
+            if (tr) trace_ev<kTrace>(p, rank, 0, tcnt, 0x101);
             if (it + 2 < nsteps) load_point(it + 2, nq0, nq1, nq2);
             for (int l = 0; l < p.nmid; ++l) {
                 mbar_wait(&sh.mid_full[fgp], mid_phase, 11);
-                if (tr) trace_ev(p, rank, 0, tcnt, 0x110 + l);
+                if (tr) trace_ev<kTrace>(p, rank, 0, tcnt, 0x110 + l);
                 mid_phase ^= 1;
                 tc_fence_after();
                 const bool last = (l == p.nmid - 1);
@@ -251,7 +255,7 @@ chain2_kernel(const ChainParams p)
                 // step parity, so that a waiter is never more than one phase behind (a single barrier would skip phases per group
                 // and a parity wait would alias): completion k of h2_empty[q] = step 2 k + q consumed.
                 if (last && it >= 1) mbar_wait(&sh.h2_empty[(it - 1) & 1][half], (uint32_t)(((it - 1) >> 1) & 1), 12);
-                if (tr && last) trace_ev(p, rank, 0, tcnt, 0x120);
+                if (tr && last) trace_ev<kTrace>(p, rank, 0, tcnt, 0x120);
                 const int N = p.mid_n[l];
                 for (int c0 = 0; c0 < N; c0 += 64) {
                     uint32_t va[32], vb[32];
@@ -278,7 +282,7 @@ chain2_kernel(const ChainParams p)
                     uint64_t *bar = last ? &sh.h2_full[half] : &sh.a_full[fgp];
                     if (rank == 0) mbar_arrive(bar); else mbar_arrive_cluster_relaxed(bar, 0);
                 }
-                if (tr) trace_ev(p, rank, 0, tcnt, 0x130 + l);
+                if (tr) trace_ev<kTrace>(p, rank, 0, tcnt, 0x130 + l);
             }
         }
     } else if (warp < 8) {
@@ -315,7 +319,7 @@ chain2_kernel(const ChainParams p)
             for (int hj = 0; hj < 8; ++hj) {
                 const uint32_t buf = (uint32_t)(g & 1);      // two TMEM accumulator buffers (TMEM: 2 x 128 mid + 2 x 128 final)
                 mbar_wait(&sh.acc_full[buf], (uint32_t)((g >> 1) & 1), 13);
-                if (tid == 128) trace_ev(p, rank, 1, tcnt, 0x200 + hj);
+                if (tid == 128) trace_ev<kTrace>(p, rank, 1, tcnt, 0x200 + hj);
                 tc_fence_after();
                 // two passes of 64 columns (512 threads: 128 registers each); the buffer is released after the second load
                 const uint32_t taddr = tmem + lane_base + 256 + buf * 128;
@@ -337,7 +341,7 @@ chain2_kernel(const ChainParams p)
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive_cluster_relaxed(&sh.acc_empty[buf], 0);
-                    if (tid == 128) trace_ev(p, rank, 1, tcnt, 0x210 + hj);
+                    if (tid == 128) trace_ev<kTrace>(p, rank, 1, tcnt, 0x210 + hj);
 #pragma unroll
                     for (int e = 0; e < 32; e += 2) {
                         m2 = fmaxf(fmaxf(m2, __uint_as_float(v2[e])), __uint_as_float(v2[e + 1]));
@@ -372,7 +376,7 @@ chain2_kernel(const ChainParams p)
                     const uint32_t b_lo = percloud ? lo_wc + (uint32_t)(it & 1) * (4096u >> 4) : lo_wm + (wm2_slot(p.mid_slot[l]) >> 4);
                     const uint32_t idesc = make_idesc_bf16(256, (uint32_t)p.mid_n[l]);
                     if (elect_one_sync()) {
-                        if (ig == 0) trace_ev(p, rank, 2, tcnt, 0x300 + l);
+                        if (ig == 0) trace_ev<kTrace>(p, rank, 2, tcnt, 0x300 + l);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             mma2_bf16_ss(tmem + (uint32_t)(ig * 128), sdesc_from_lo(a_lo + k * 2), sdesc_from_lo(b_lo + k * 2), idesc, k > 0);
@@ -406,7 +410,7 @@ chain2_kernel(const ChainParams p)
                         const uint32_t b_lo = lo_h2 + (uint32_t)hf * (8192u >> 4);
                         const uint32_t d = tmem + 256 + buf * 128;
                         if (elect_one_sync()) {
-                            trace_ev(p, rank, 3, tcnt, 0x400 + hf * 16 + j * 2);
+                            trace_ev<kTrace>(p, rank, 3, tcnt, 0x400 + hf * 16 + j * 2);
 #pragma unroll
                             for (int kk = 0; kk < 8; ++kk)      // kk = kb*4 + k : K-block stride 16 KB, K-step 32 B
                                 mma2_bf16_ss(d, sdesc_from_lo(a_lo + (kk >> 2) * (16384u >> 4) + (kk & 3) * 2),
@@ -653,7 +657,8 @@ static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, 
     p.tiles_per_cloud = (int)((n + kTP - 1) / kTP);
     p.total_tiles = (int64_t)p.tiles_per_cloud * b;
     if (!ts->attr_set) {
-        PCP_CUDA_OK(cudaFuncSetAttribute(chain2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kChain2Smem));
+        PCP_CUDA_OK(cudaFuncSetAttribute(chain2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kChain2Smem));
+        PCP_CUDA_OK(cudaFuncSetAttribute(chain2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kChain2Smem));
         ts->attr_set = true;
     }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -680,7 +685,8 @@ static int launch_chain(TcState *ts, const TcChain &c, const float *d_x, int b, 
         at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = at; cfg.numAttrs = no_pdl ? 0 : 1;
-        PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, chain2_kernel, p));
+        if (trace_path) PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, chain2_kernel<true>, p));
+        else PCP_CUDA_OK(cudaLaunchKernelEx(&cfg, chain2_kernel<false>, p));
     }
     if (trace_path) {
         std::vector<unsigned long long> h(trace_bytes / 8);
