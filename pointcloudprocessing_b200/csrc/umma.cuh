@@ -54,19 +54,23 @@ __device__ __forceinline__ bool mbar_try(uint64_t *bar, uint32_t parity)
 // Bounded wait: a protocol bug must never hang the GPU — after ~2 s the kernel records where it
 // was stuck and traps (the launch then fails with an error instead of wedging the device).
 static __device__ unsigned int g_mbar_timeout_info[4];
+// the time-out path is ONE out-of-line function: inlined at every wait it put ~20 cold instructions into each hot loop, and the
+// chain kernel's hot code is sized for the instruction cache
+static __device__ __noinline__ void mbar_timeout_trap(int tag, uint32_t parity)
+{
+    g_mbar_timeout_info[0] = 0xdead0000u | (unsigned)tag;
+    g_mbar_timeout_info[1] = blockIdx.x;
+    g_mbar_timeout_info[2] = threadIdx.x;
+    g_mbar_timeout_info[3] = parity;
+    __threadfence_system();
+    __trap();
+}
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int tag = 0)
 {
     if (mbar_try(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try(bar, parity)) {
-        if (clock64() - t0 > 4000000000ll) {
-            g_mbar_timeout_info[0] = 0xdead0000u | (unsigned)tag;
-            g_mbar_timeout_info[1] = blockIdx.x;
-            g_mbar_timeout_info[2] = threadIdx.x;
-            g_mbar_timeout_info[3] = parity;
-            __threadfence_system();
-            __trap();
-        }
+        if (clock64() - t0 > 4000000000ll) mbar_timeout_trap(tag, parity);
     }
 }
 
@@ -185,14 +189,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t *bar, uint32_t parity
     if (mbar_try_cluster(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try_cluster(bar, parity)) {
-        if (clock64() - t0 > 4000000000ll) {
-            g_mbar_timeout_info[0] = 0xdead0000u | (unsigned)tag;
-            g_mbar_timeout_info[1] = blockIdx.x;
-            g_mbar_timeout_info[2] = threadIdx.x;
-            g_mbar_timeout_info[3] = parity;
-            __threadfence_system();
-            __trap();
-        }
+        if (clock64() - t0 > 4000000000ll) mbar_timeout_trap(tag, parity);
     }
 }
 __device__ __forceinline__ void tmem_alloc2(uint32_t *smem_result, uint32_t ncols)
