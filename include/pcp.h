@@ -260,8 +260,8 @@ typedef struct pcp_train_config {
  * losses (SCCE on probabilities clip 1e-7, MSE on R), backward into the flat gradient buffer.
  * h_metrics (8 floats): loss, cls_loss, seg_loss, se3_loss, cls_acc, seg_acc, se3_rmse, reg_loss.
  * global_batch: the loss mean divides by this (data parallel: sum over ranks == global mean).
- * From the third call with the same configuration (shapes, loss weights, thawed groups, which labels are given) the step is
- * replayed as one CUDA graph on a stream of the library's own, forked from and joined to `stream` by events; the inputs are
+ * Once a configuration (shapes, loss weights, thawed groups, which labels are given) has run eagerly two or three times (until
+ * the table of packed weight images is complete) the step is replayed as one CUDA graph on a stream of the library's own, forked from and joined to `stream` by events; the inputs are
  * copied into staging buffers first, so the caller's pointers may change from call to call.  Steps with a BatchNorm
  * all-reduce callback or explicit dropout masks stay eager; PCP_TRAIN_GRAPH=0 in the environment keeps every step eager. */
 int pcp_model_loss_backward(pcp_model *m, const float *d_x, int b, int64_t n, const int32_t *d_y_cls,
